@@ -1,0 +1,302 @@
+"""oracle/ -- TEST INFRASTRUCTURE (CPU oracle for the ORB front-end hot path).
+
+ctypes loader over ``liborboracle.so`` (strict build, defines results), ``liborboracle_fast.so``
+(-O3, timed CPU baseline only) and, when present, ``_ref/liborbref.so`` (the reference's own
+``src/ORBextractor.cc`` compiled unmodified against ``oracle/shim``).
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline legs may import this
+package.  The product package (``orbslam2commentedbyxcm_b200``) never does.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+KP_DTYPE = np.dtype(
+    [("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4")]
+)
+
+_c = ctypes
+_vp, _i, _f, _sz = _c.c_void_p, _c.c_int, _c.c_float, _c.c_size_t
+
+
+def build(ref=True):
+    """(Re)build the oracle libraries with oracle/Makefile. `ref` also builds _ref/ when /root/reference exists."""
+    subprocess.check_call(["make", "-s", "-C", _HERE, "all"])
+    if ref and os.path.exists("/root/reference/src/ORBextractor.cc"):
+        subprocess.check_call(["make", "-s", "-C", _HERE, "ref"])
+
+
+def _load(name):
+    path = os.path.join(_HERE, name)
+    if not os.path.exists(path):
+        if name.startswith("_ref"):
+            return None
+        build(ref=False)
+    return _c.CDLL(path)
+
+
+def _bind_extractor(lib, prefix):
+    g = lambda n: getattr(lib, prefix + n)
+    g("create").restype = _vp
+    g("create").argtypes = [_i, _f, _i, _i, _i]
+    g("destroy").argtypes = [_vp]
+    g("extract").restype = _i
+    g("extract").argtypes = [_vp, _vp, _i, _i, _sz]
+    g("get_keypoints").argtypes = [_vp, _vp]
+    g("get_descriptors").argtypes = [_vp, _vp]
+    g("get_levels").restype = _i
+    g("get_levels").argtypes = [_vp]
+    g("get_scale_factors").argtypes = [_vp, _vp]
+    g("get_inv_level_sigma2").argtypes = [_vp, _vp]
+    g("get_level_size").argtypes = [_vp, _i, _vp, _vp]
+    g("get_pyramid").argtypes = [_vp, _i, _vp]
+
+
+class _Libs:
+    strict = None
+    fast = None
+    ref = None
+
+
+def lib(kind="strict"):
+    if kind == "strict":
+        if _Libs.strict is None:
+            _Libs.strict = _load("liborboracle.so")
+            _bind_all(_Libs.strict)
+        return _Libs.strict
+    if kind == "fast":
+        if _Libs.fast is None:
+            _Libs.fast = _load("liborboracle_fast.so")
+            _bind_all(_Libs.fast)
+        return _Libs.fast
+    if kind == "ref":
+        if _Libs.ref is None:
+            _Libs.ref = _load("_ref/liborbref.so")
+            if _Libs.ref is not None:
+                _bind_extractor(_Libs.ref, "orbref_")
+        return _Libs.ref
+    raise ValueError(kind)
+
+
+def _bind_all(L):
+    _bind_extractor(L, "orbo_")
+    L.orbo_get_inv_scale_factors.argtypes = [_vp, _vp]
+    L.orbo_get_level_sigma2.argtypes = [_vp, _vp]
+    L.orbo_get_quotas.argtypes = [_vp, _vp]
+    L.orbo_get_umax.argtypes = [_vp, _vp]
+    L.orbo_get_blurred.restype = _i
+    L.orbo_get_blurred.argtypes = [_vp, _i, _vp]
+    L.orbo_get_num_candidates.restype = _i
+    L.orbo_get_num_candidates.argtypes = [_vp, _i]
+    L.orbo_get_candidates.argtypes = [_vp, _i, _vp]
+    L.orbo_get_num_level_keypoints.restype = _i
+    L.orbo_get_num_level_keypoints.argtypes = [_vp, _i]
+    L.orbo_distribute.restype = _i
+    L.orbo_distribute.argtypes = [_vp, _i, _i, _i, _i, _i, _i, _vp]
+    L.orbo_sincosf.argtypes = [_vp, _vp, _vp, _i]
+    L.orbo_libm_sincosf.argtypes = [_vp, _vp, _vp, _i]
+    L.orbo_extract_batch.restype = _c.c_long
+    L.orbo_extract_batch.argtypes = [_i, _f, _i, _i, _i, _vp, _i, _i, _i, _i, _vp]
+    # primitives
+    L.orbo_resize_linear_u8.argtypes = [_vp, _i, _i, _sz, _vp, _i, _i, _sz]
+    L.orbo_copy_make_border101.argtypes = [_vp, _i, _i, _vp, _i]
+    L.orbo_fast9_16.restype = _i
+    L.orbo_fast9_16.argtypes = [_vp, _i, _i, _sz, _i, _i, _vp, _i]
+    L.orbo_gaussian_blur_7x7_s2.argtypes = [_vp, _i, _i, _sz, _vp, _sz]
+    L.orbo_fast_atan2.argtypes = [_vp, _vp, _vp, _i]
+    L.orbo_cv_round_f.restype = _i
+    L.orbo_cv_round_f.argtypes = [_f]
+    # matcher
+    L.orbo_descriptor_distance.restype = _i
+    L.orbo_descriptor_distance.argtypes = [_vp, _vp]
+    L.orbo_bruteforce.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _vp, _i]
+    L.orbo_assign_grid.argtypes = [_vp, _vp, _i, _f, _f, _f, _f, _vp, _vp]
+    L.orbo_search_by_projection.restype = _i
+    L.orbo_search_by_projection.argtypes = (
+        [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _vp]
+        + [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
+        + [_f, _f, _vp]
+    )
+    L.orbo_stereo_rows.argtypes = [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _f, _f, _vp, _vp]
+    L.orbo_search_by_bow.restype = _i
+    L.orbo_search_by_bow.argtypes = (
+        [_i, _vp, _vp, _vp, _i, _vp, _vp, _vp] + [_i, _vp, _vp, _i, _vp, _vp, _vp] + [_f, _i, _vp]
+    )
+
+
+def _ptr(a):
+    return a.ctypes.data if a is not None else None
+
+
+class Extractor:
+    """CPU oracle extractor. kind: 'strict' | 'fast' (restatement) or 'ref' (reference source + shim)."""
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, kind="strict"):
+        self.kind = kind
+        self.L = lib(kind)
+        if self.L is None:
+            raise RuntimeError("oracle library for kind=%r is not built" % kind)
+        self.p = "orbref_" if kind == "ref" else "orbo_"
+        self.h = self._f("create")(nfeatures, scale_factor, nlevels, ini_th, min_th)
+        self.nlevels = nlevels
+        self.n = 0
+
+    def _f(self, name):
+        return getattr(self.L, self.p + name)
+
+    def close(self):
+        if self.h:
+            self._f("destroy")(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def extract(self, img):
+        img = np.ascontiguousarray(img, dtype=np.uint8)
+        self.n = self._f("extract")(self.h, img.ctypes.data, img.shape[0], img.shape[1], img.strides[0])
+        kps = np.zeros(self.n, KP_DTYPE)
+        desc = np.zeros((self.n, 32), np.uint8)
+        if self.n:
+            self._f("get_keypoints")(self.h, kps.ctypes.data)
+            self._f("get_descriptors")(self.h, desc.ctypes.data)
+        return kps, desc
+
+    def scale_factors(self):
+        out = np.zeros(self.nlevels, np.float32)
+        self._f("get_scale_factors")(self.h, out.ctypes.data)
+        return out
+
+    def inv_level_sigma2(self):
+        out = np.zeros(self.nlevels, np.float32)
+        self._f("get_inv_level_sigma2")(self.h, out.ctypes.data)
+        return out
+
+    def level_size(self, level):
+        w, h = _c.c_int(), _c.c_int()
+        self._f("get_level_size")(self.h, level, _c.byref(w), _c.byref(h))
+        return w.value, h.value
+
+    def pyramid(self, level):
+        w, h = self.level_size(level)
+        out = np.zeros((h + 38, w + 38), np.uint8)
+        self._f("get_pyramid")(self.h, level, out.ctypes.data)
+        return out
+
+    # --- restatement-only introspection ---
+    def quotas(self):
+        out = np.zeros(self.nlevels, np.int32)
+        self.L.orbo_get_quotas(self.h, out.ctypes.data)
+        return out
+
+    def umax(self):
+        out = np.zeros(16, np.int32)
+        self.L.orbo_get_umax(self.h, out.ctypes.data)
+        return out
+
+    def blurred(self, level):
+        w, h = self.level_size(level)
+        out = np.zeros((h, w), np.uint8)
+        ok = self.L.orbo_get_blurred(self.h, level, out.ctypes.data)
+        return out if ok else None
+
+    def candidates(self, level):
+        n = self.L.orbo_get_num_candidates(self.h, level)
+        out = np.zeros((n, 3), np.int32)
+        if n:
+            self.L.orbo_get_candidates(self.h, level, out.ctypes.data)
+        return out
+
+    def num_level_keypoints(self, level):
+        return self.L.orbo_get_num_level_keypoints(self.h, level)
+
+
+def distribute(xyr, min_x, max_x, min_y, max_y, n_wanted):
+    """Quad-tree selection on candidates (n,3) int32 (x, y, response) relative to the grid origin -> picked indices."""
+    L = lib()
+    xyr = np.ascontiguousarray(xyr, np.int32)
+    out = np.zeros(max(len(xyr), 1), np.int32)
+    k = L.orbo_distribute(xyr.ctypes.data, len(xyr), min_x, max_x, min_y, max_y, n_wanted, out.ctypes.data)
+    return out[:k].copy()
+
+
+def extract_batch(imgs, nfeatures, scale_factor, nlevels, ini_th, min_th, threads, kind="fast"):
+    L = lib(kind)
+    imgs = np.ascontiguousarray(imgs, np.uint8)
+    n, rows, cols = imgs.shape
+    counts = np.zeros(n, np.int32)
+    tot = L.orbo_extract_batch(nfeatures, scale_factor, nlevels, ini_th, min_th, imgs.ctypes.data, n, rows, cols, threads, counts.ctypes.data)
+    return tot, counts
+
+
+def bruteforce(q, db, threads=1, kind="strict"):
+    L = lib(kind)
+    q = np.ascontiguousarray(q, np.uint8)
+    db = np.ascontiguousarray(db, np.uint8)
+    nq, ndb = len(q), len(db)
+    best = np.zeros(nq, np.int32)
+    idx = np.zeros(nq, np.int32)
+    second = np.zeros(nq, np.int32)
+    L.orbo_bruteforce(q.ctypes.data, nq, db.ctypes.data, ndb, best.ctypes.data, idx.ctypes.data, second.ctypes.data, threads)
+    return best, idx, second
+
+
+def assign_grid(kx, ky, min_x, min_y, w_inv, h_inv):
+    L = lib()
+    kx = np.ascontiguousarray(kx, np.float32)
+    ky = np.ascontiguousarray(ky, np.float32)
+    start = np.zeros(64 * 48 + 1, np.int32)
+    items = np.zeros(max(len(kx), 1), np.int32)
+    L.orbo_assign_grid(kx.ctypes.data, ky.ctypes.data, len(kx), min_x, min_y, w_inv, h_inv, start.ctypes.data, items.ctypes.data)
+    return start, items[: start[-1]].copy()
+
+
+def search_by_projection(frame, mps, th, nnratio, kind="strict"):
+    """frame / mps: dicts of numpy arrays (see orbslam2commentedbyxcm_b200.matcher for the field names)."""
+    L = lib(kind)
+    nkp = len(frame["x"])
+    out = np.full(nkp, -1, np.int32)
+    ur = frame.get("u_right")
+    n = L.orbo_search_by_projection(
+        nkp, _ptr(frame["x"]), _ptr(frame["y"]), _ptr(frame["octave"]), _ptr(ur), _ptr(frame["desc"]),
+        _ptr(frame["occupied"]), _ptr(frame["cell_start"]), _ptr(frame["cell_items"]),
+        frame["min_x"], frame["min_y"], frame["w_inv"], frame["h_inv"], _ptr(frame["scale_factors"]),
+        len(mps["x"]), _ptr(mps["x"]), _ptr(mps["y"]), _ptr(mps["xr"]), _ptr(mps["level"]), _ptr(mps["view_cos"]),
+        _ptr(mps["valid"]), _ptr(mps["obs"]), _ptr(mps["desc"]),
+        th, nnratio, out.ctypes.data,
+    )
+    return n, out
+
+
+def stereo_rows(left, right, scale_factors, n_rows, min_d, max_d):
+    L = lib()
+    nl = len(left["x"])
+    best_r = np.zeros(nl, np.int32)
+    best_d = np.zeros(nl, np.int32)
+    L.orbo_stereo_rows(
+        nl, _ptr(left["x"]), _ptr(left["y"]), _ptr(left["octave"]), _ptr(left["desc"]),
+        len(right["x"]), _ptr(right["x"]), _ptr(right["y"]), _ptr(right["octave"]), _ptr(right["desc"]),
+        _ptr(scale_factors), n_rows, min_d, max_d, best_r.ctypes.data, best_d.ctypes.data,
+    )
+    return best_r, best_d
+
+
+def search_by_bow(kf, fr, nnratio, check_orientation):
+    L = lib()
+    nf = len(fr["angle"])
+    out = np.full(nf, -1, np.int32)
+    n = L.orbo_search_by_bow(
+        len(kf["angle"]), _ptr(kf["desc"]), _ptr(kf["angle"]), _ptr(kf["has_mp"]),
+        len(kf["node_id"]), _ptr(kf["node_id"]), _ptr(kf["node_start"]), _ptr(kf["node_feat"]),
+        nf, _ptr(fr["desc"]), _ptr(fr["angle"]),
+        len(fr["node_id"]), _ptr(fr["node_id"]), _ptr(fr["node_start"]), _ptr(fr["node_feat"]),
+        nnratio, int(check_orientation), out.ctypes.data,
+    )
+    return n, out

@@ -1,0 +1,276 @@
+// oracle/match_oracle.cc -- TEST INFRASTRUCTURE (CPU oracle). Never linked into / called by the product path.
+//
+// Flat-array restatements of the reference's Hamming-matching loops.  ORBmatcher.cc cannot be compiled
+// here (it drags in Frame/KeyFrame/MapPoint/DBoW2/g2o/Eigen), so these follow the reference line by line
+// over plain arrays; parity for them is pinned only by construction + self-consistency ("parity
+// unpinned" by any reference-side test -- the reference has none).
+//
+//   orbo_descriptor_distance   <- ORBmatcher::DescriptorDistance            src/ORBmatcher.cc:1983-2003
+//   orbo_bruteforce            <- sequential best/second scan with that distance (north_star config 5)
+//   orbo_search_by_projection  <- ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th)
+//                                 src/ORBmatcher.cc:61-183 + Frame::GetFeaturesInArea src/Frame.cc:488-548
+//   orbo_stereo_rows           <- coarse part of Frame::ComputeStereoMatches  src/Frame.cc:684-765
+//   orbo_search_by_bow         <- ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...) src/ORBmatcher.cc:228-392
+//                                 + ComputeThreeMaxima :1935-1977
+//   orbo_assign_grid           <- Frame::AssignFeaturesToGrid / PosInGrid    src/Frame.cc:351-370, 558-567
+#include <cstdint>
+#include <cstring>
+#include <cmath>
+#include <vector>
+#include <algorithm>
+#include <thread>
+
+namespace {
+
+const int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;
+const int GRID_COLS = 64, GRID_ROWS = 48;
+
+// the reference's SWAR popcount, word by word (src/ORBmatcher.cc:1992-2000)
+inline int hamming256(const uint8_t* a, const uint8_t* b)
+{
+    int dist = 0;
+    for (int i = 0; i < 8; i++) {
+        uint32_t x, y;
+        std::memcpy(&x, a + 4 * i, 4);
+        std::memcpy(&y, b + 4 * i, 4);
+        uint32_t v = x ^ y;
+        v = v - ((v >> 1) & 0x55555555);
+        v = (v & 0x33333333) + ((v >> 2) & 0x33333333);
+        dist += (((v + (v >> 4)) & 0xF0F0F0F) * 0x1010101) >> 24;
+    }
+    return dist;
+}
+
+}  // namespace
+
+extern "C" {
+
+int orbo_descriptor_distance(const uint8_t* a, const uint8_t* b) { return hamming256(a, b); }
+
+// For each query: best distance, index of the first database row attaining it, and the second-smallest
+// distance of the multiset (sequential scan: `if d < best {second = best; best = d} else if d < second`).
+// Empty database: best = second = 256, idx = -1.
+void orbo_bruteforce(const uint8_t* q, int nq, const uint8_t* db, int ndb, int32_t* best, int32_t* best_idx,
+                     int32_t* second, int threads)
+{
+    if (threads < 1) threads = 1;
+    std::vector<std::thread> th;
+    for (int t = 0; t < threads; t++)
+        th.emplace_back([=]() {
+            for (int i = t; i < nq; i += threads) {
+                int b1 = 256, b2 = 256, bi = -1;
+                for (int j = 0; j < ndb; j++) {
+                    int d = hamming256(q + 32 * (size_t)i, db + 32 * (size_t)j);
+                    if (d < b1) { b2 = b1; b1 = d; bi = j; }
+                    else if (d < b2) b2 = d;
+                }
+                best[i] = b1; best_idx[i] = bi; second[i] = b2;
+            }
+        });
+    for (auto& x : th) x.join();
+}
+
+// Frame::AssignFeaturesToGrid: cell (ix, iy) flattened as ix*48+iy; CSR output, items in keypoint order.
+void orbo_assign_grid(const float* kx, const float* ky, int n, float minX, float minY, float wInv, float hInv,
+                      int32_t* cell_start /*64*48+1*/, int32_t* cell_items /*n*/)
+{
+    std::vector<std::vector<int>> g(GRID_COLS * GRID_ROWS);
+    for (int i = 0; i < n; i++) {
+        int px = (int)std::round((kx[i] - minX) * wInv);
+        int py = (int)std::round((ky[i] - minY) * hInv);
+        if (px < 0 || px >= GRID_COLS || py < 0 || py >= GRID_ROWS) continue;
+        g[px * GRID_ROWS + py].push_back(i);
+    }
+    int off = 0;
+    for (int c = 0; c < GRID_COLS * GRID_ROWS; c++) {
+        cell_start[c] = off;
+        for (int v : g[c]) cell_items[off++] = v;
+    }
+    cell_start[GRID_COLS * GRID_ROWS] = off;
+}
+
+// SearchByProjection(Frame&, vector<MapPoint*>&, th).  out_match[idx] = index of the map point written into
+// F.mvpMapPoints[idx] by this call (the last writer), or -1 when untouched.  Returns nmatches.
+int orbo_search_by_projection(
+    // frame
+    int nkp, const float* kx, const float* ky, const int32_t* koct, const float* uright, const uint8_t* kdesc,
+    const uint8_t* occupied, const int32_t* cell_start, const int32_t* cell_items, float minX, float minY,
+    float wInv, float hInv, const float* scaleFactors,
+    // map points
+    int nmp, const float* px, const float* py, const float* pxr, const int32_t* plevel, const float* pviewcos,
+    const uint8_t* pvalid, const uint8_t* pobs, const uint8_t* pdesc,
+    float th, float nnratio, int32_t* out_match)
+{
+    (void)nkp;
+    std::vector<uint8_t> occ(occupied, occupied + nkp);
+    for (int i = 0; i < nkp; i++) out_match[i] = -1;
+    int nmatches = 0;
+    const bool bFactor = th != 1.0f;
+    for (int m = 0; m < nmp; m++) {
+        if (!pvalid[m]) continue;
+        const int level = plevel[m];
+        float r = pviewcos[m] > 0.998 ? 2.5f : 4.0f;
+        if (bFactor) r *= th;
+        const float rr = r * scaleFactors[level];
+        const int minLevel = level - 1, maxLevel = level;
+        // GetFeaturesInArea(x, y, rr, minLevel, maxLevel)
+        const float x = px[m], y = py[m];
+        const int c0 = std::max(0, (int)std::floor((x - minX - rr) * wInv));
+        if (c0 >= GRID_COLS) continue;
+        const int c1 = std::min(GRID_COLS - 1, (int)std::ceil((x - minX + rr) * wInv));
+        if (c1 < 0) continue;
+        const int r0 = std::max(0, (int)std::floor((y - minY - rr) * hInv));
+        if (r0 >= GRID_ROWS) continue;
+        const int r1 = std::min(GRID_ROWS - 1, (int)std::ceil((y - minY + rr) * hInv));
+        if (r1 < 0) continue;
+        const bool checkLevels = (minLevel > 0) || (maxLevel >= 0);
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        bool any = false;
+        for (int ix = c0; ix <= c1; ix++)
+            for (int iy = r0; iy <= r1; iy++) {
+                const int c = ix * GRID_ROWS + iy;
+                for (int k = cell_start[c]; k < cell_start[c + 1]; k++) {
+                    const int idx = cell_items[k];
+                    if (checkLevels) {
+                        if (koct[idx] < minLevel) continue;
+                        if (maxLevel >= 0 && koct[idx] > maxLevel) continue;
+                    }
+                    const float dx = kx[idx] - x, dy = ky[idx] - y;
+                    if (!(std::fabs(dx) < rr && std::fabs(dy) < rr)) continue;
+                    any = true;
+                    // candidate loop body (src/ORBmatcher.cc:113-151)
+                    if (occ[idx]) continue;
+                    if (uright && uright[idx] > 0) {
+                        const float er = std::fabs(pxr[m] - uright[idx]);
+                        if (er > rr) continue;
+                    }
+                    const int dist = hamming256(pdesc + 32 * (size_t)m, kdesc + 32 * (size_t)idx);
+                    if (dist < bestDist) {
+                        bestDist2 = bestDist; bestDist = dist;
+                        bestLevel2 = bestLevel; bestLevel = koct[idx];
+                        bestIdx = idx;
+                    } else if (dist < bestDist2) {
+                        bestLevel2 = koct[idx];
+                        bestDist2 = dist;
+                    }
+                }
+            }
+        if (!any) continue;
+        if (bestDist <= TH_HIGH) {
+            if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
+            out_match[bestIdx] = m;
+            occ[bestIdx] = pobs[m] ? 1 : 0;
+            nmatches++;
+        }
+    }
+    return nmatches;
+}
+
+// Coarse stereo search.  For each left keypoint: best right index (or -1) and its distance.
+// minZ = mb = mbf/fx (decision D5), minD = 0, maxD = mbf/minZ.
+void orbo_stereo_rows(int nl, const float* lx, const float* ly, const int32_t* loct, const uint8_t* ldesc,
+                      int nr, const float* rx, const float* ry, const int32_t* roct, const uint8_t* rdesc,
+                      const float* scaleFactors, int nRows, float minD, float maxD,
+                      int32_t* best_r, int32_t* best_dist)
+{
+    std::vector<std::vector<int>> rows(nRows);
+    for (int iR = 0; iR < nr; iR++) {
+        const float r = 2.0f * scaleFactors[roct[iR]];
+        const int maxr = (int)std::ceil(ry[iR] + r);
+        const int minr = (int)std::floor(ry[iR] - r);
+        for (int yi = minr; yi <= maxr; yi++)
+            if (yi >= 0 && yi < nRows) rows[yi].push_back(iR);
+    }
+    const int thOrbDist = (TH_HIGH + TH_LOW) / 2;
+    for (int iL = 0; iL < nl; iL++) {
+        best_r[iL] = -1; best_dist[iL] = TH_HIGH;
+        const int row = (int)ly[iL];
+        if (row < 0 || row >= nRows) continue;
+        const std::vector<int>& cand = rows[row];
+        if (cand.empty()) continue;
+        const float minU = lx[iL] - maxD, maxU = lx[iL] - minD;
+        if (maxU < 0) continue;
+        int bestDist = TH_HIGH, bestIdx = 0;
+        for (int iR : cand) {
+            if (roct[iR] < loct[iL] - 1 || roct[iR] > loct[iL] + 1) continue;
+            const float uR = rx[iR];
+            if (uR >= minU && uR <= maxU) {
+                const int d = hamming256(ldesc + 32 * (size_t)iL, rdesc + 32 * (size_t)iR);
+                if (d < bestDist) { bestDist = d; bestIdx = iR; }
+            }
+        }
+        best_dist[iL] = bestDist;
+        if (bestDist < thOrbDist) best_r[iL] = bestIdx;
+    }
+}
+
+// SearchByBoW(KeyFrame*, Frame&, matches).  Feature vectors are CSR: node ids ascending, features per node.
+// kf_has_mp[i] = vpMapPointsKF[i] != NULL && !isBad().  out_match[f] = KF feature index matched to frame
+// feature f, or -1.  Returns nmatches (after the orientation filter).
+int orbo_search_by_bow(
+    int nkf, const uint8_t* kf_desc, const float* kf_angle, const uint8_t* kf_has_mp,
+    int n_nodes_kf, const int32_t* kf_node_id, const int32_t* kf_node_start, const int32_t* kf_node_feat,
+    int nf, const uint8_t* f_desc, const float* f_angle,
+    int n_nodes_f, const int32_t* f_node_id, const int32_t* f_node_start, const int32_t* f_node_feat,
+    float nnratio, int checkOrientation, int32_t* out_match)
+{
+    (void)nkf;
+    for (int i = 0; i < nf; i++) out_match[i] = -1;
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = HISTO_LENGTH / 360.0f;
+    int a = 0, b = 0;
+    while (a < n_nodes_kf && b < n_nodes_f) {
+        if (kf_node_id[a] == f_node_id[b]) {
+            for (int ik = kf_node_start[a]; ik < kf_node_start[a + 1]; ik++) {
+                const int realIdxKF = kf_node_feat[ik];
+                if (!kf_has_mp[realIdxKF]) continue;
+                int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+                for (int jf = f_node_start[b]; jf < f_node_start[b + 1]; jf++) {
+                    const int realIdxF = f_node_feat[jf];
+                    if (out_match[realIdxF] >= 0) continue;
+                    const int dist = hamming256(kf_desc + 32 * (size_t)realIdxKF, f_desc + 32 * (size_t)realIdxF);
+                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = realIdxF; }
+                    else if (dist < bestDist2) bestDist2 = dist;
+                }
+                if (bestDist1 <= TH_LOW) {
+                    if ((float)bestDist1 < nnratio * (float)bestDist2) {
+                        out_match[bestIdxF] = realIdxKF;
+                        if (checkOrientation) {
+                            float rot = kf_angle[realIdxKF] - f_angle[bestIdxF];
+                            if (rot < 0.0) rot += 360.0f;
+                            int bin = (int)std::round(rot * factor);
+                            if (bin == HISTO_LENGTH) bin = 0;
+                            rotHist[bin].push_back(bestIdxF);
+                        }
+                        nmatches++;
+                    }
+                }
+            }
+            a++; b++;
+        } else if (kf_node_id[a] < f_node_id[b]) {
+            a = (int)(std::lower_bound(kf_node_id + a, kf_node_id + n_nodes_kf, f_node_id[b]) - kf_node_id);
+        } else {
+            b = (int)(std::lower_bound(f_node_id + b, f_node_id + n_nodes_f, kf_node_id[a]) - f_node_id);
+        }
+    }
+    if (checkOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        int max1 = 0, max2 = 0, max3 = 0;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            const int s = (int)rotHist[i].size();
+            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+            else if (s > max3) { max3 = s; ind3 = i; }
+        }
+        if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+        else if (max3 < 0.1f * (float)max1) ind3 = -1;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int f : rotHist[i]) { out_match[f] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}
+
+}  // extern "C"

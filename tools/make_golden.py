@@ -1,0 +1,89 @@
+"""Generates tests/golden/*.npz.  Run in the authoring container (needs cv2 4.13 and, for the extractor
+fixtures, oracle/_ref/liborbref.so built from /root/reference).  The fixtures pin:
+
+  prim_cv2.npz        cv2 4.13.0 outputs of the five OpenCV primitives on small seeded inputs
+                      (resize chain, copyMakeBorder, GaussianBlur, FAST 20/7, fastAtan2)
+  sincosf_libm.npz    host glibc 2.39 sinf/cosf on 4096 seeded angles deg*factorPI
+  extract_ref_*.npz   keypoints + descriptors produced by the reference's own ORBextractor.cc
+                      (compiled unmodified against oracle/shim, canonical tie-break) on seeded synthetic
+                      frames of reduced size (fast to re-run) and on the TUM-shaped frame, seed 0.
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import cv2  # noqa: E402
+
+import oracle  # noqa: E402
+from orbslam2commentedbyxcm_b200 import synth  # noqa: E402
+
+G = os.path.join(ROOT, "tests", "golden")
+os.makedirs(G, exist_ok=True)
+
+
+def prim():
+    rng = np.random.Generator(np.random.PCG64(7))
+    out = {}
+    img = synth.gen_frame((83, 97), 3)
+    out["img"] = img
+    prev = img
+    for l in range(1, 5):
+        s = np.float32(1.0) / (np.float32(1.2) ** l)
+        dw = int(np.rint(np.float32(img.shape[1]) * s))
+        dh = int(np.rint(np.float32(img.shape[0]) * s))
+        prev = cv2.resize(prev, (dw, dh), interpolation=cv2.INTER_LINEAR)
+        out["resize_l%d" % l] = prev
+    out["border19"] = cv2.copyMakeBorder(img, 19, 19, 19, 19, cv2.BORDER_REFLECT_101)
+    out["blur"] = cv2.GaussianBlur(img, (7, 7), 2, None, 2, cv2.BORDER_REFLECT_101)
+    for th in (20, 7):
+        det = cv2.FastFeatureDetector_create(th, True, cv2.FAST_FEATURE_DETECTOR_TYPE_9_16)
+        kps = det.detect(img)
+        out["fast_t%d" % th] = np.array([(int(k.pt[0]), int(k.pt[1]), int(k.response)) for k in kps], np.int32).reshape(-1, 3)
+    y = rng.integers(-200000, 200000, 4096).astype(np.float32)
+    x = rng.integers(-200000, 200000, 4096).astype(np.float32)
+    y[:5] = [0, 0, 1, 0, -1]
+    x[:5] = [0, 1, 0, -1, 0]
+    out["atan_y"], out["atan_x"] = y, x
+    out["atan_deg"] = np.array([cv2.fastAtan2(float(a), float(b)) for a, b in zip(y, x)], np.float32)
+    np.savez_compressed(os.path.join(G, "prim_cv2.npz"), **out)
+
+
+def sincos():
+    rng = np.random.Generator(np.random.PCG64(11))
+    deg = (rng.random(4096) * 360).astype(np.float32)
+    deg[:4] = [0, 90, 180, 360]
+    factor = np.float32(np.float32(np.pi) / np.float32(180.0))
+    # factorPI = (float)(CV_PI/180.f): double division then cast
+    factor = np.float32(3.1415926535897932384626433832795 / float(np.float32(180.0)))
+    ang = (deg * factor).astype(np.float32)
+    s = np.zeros_like(ang)
+    c = np.zeros_like(ang)
+    oracle.lib().orbo_libm_sincosf(ang.ctypes.data, s.ctypes.data, c.ctypes.data, len(ang))
+    np.savez_compressed(os.path.join(G, "sincosf_libm.npz"), angle=ang, sin=s, cos=c)
+
+
+def extract():
+    cases = {
+        "small_a": ((120, 160), 1, (300, 1.2, 4, 20, 7)),
+        "small_b": ((200, 333), 2, (500, 1.2, 6, 20, 7)),
+        "tum_s0": (synth.SHAPES["tum"], 0, synth.PRESETS["tum"]),
+    }
+    for name, (shape, seed, cfg) in cases.items():
+        img = synth.gen_frame(shape, seed)
+        ex = oracle.Extractor(*cfg, kind="ref")
+        kps, desc = ex.extract(img)
+        np.savez_compressed(
+            os.path.join(G, "extract_ref_%s.npz" % name),
+            shape=np.array(shape), seed=np.array(seed), cfg=np.array(cfg, np.float64), kps=kps, desc=desc,
+        )
+        print(name, len(kps))
+
+
+if __name__ == "__main__":
+    prim()
+    sincos()
+    extract()
+    print(sorted(os.listdir(G)))
