@@ -1,0 +1,221 @@
+/* include/orbx.h -- C-ABI of liborbx.so: the B200-native (sm_100a) ORB front-end.
+ *
+ * This is the drop-in boundary for the reference's feature hot path.  Plain C types, caller-allocated
+ * outputs, int status codes; no OpenCV / torch types cross it.  The C++ adapter classes in
+ * orbslam2commentedbyxcm_b200/host/ (ORB_SLAM2::ORBextractor / ORBmatcher with the reference's public surface) are
+ * thin marshalling layers over these entry points; INTEGRATION.md shows the reference-side binding.
+ *
+ * Each entry point cites the reference interface it replaces (paths relative to the reference tree).
+ * There is no CPU fallback: every compute entry point fails with ORBX_ERR_NO_DEVICE / ORBX_ERR_CUDA when
+ * no sm_100 device is usable.
+ */
+#ifndef ORBX_H_
+#define ORBX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORBX_OK 0
+#define ORBX_ERR_BAD_ARG (-1)   /* null pointer, non-positive size, nlevels > ORBX_MAX_LEVELS, ... */
+#define ORBX_ERR_TOO_SMALL (-2) /* image too small for the pyramid / 30-px cell grid at some level */
+#define ORBX_ERR_CUDA (-3)      /* a CUDA call failed; orbx_last_error() has the text */
+#define ORBX_ERR_CAPACITY (-4)  /* a caller-provided output buffer is too small */
+#define ORBX_ERR_NO_DEVICE (-5) /* no CUDA device */
+
+#define ORBX_MAX_LEVELS 16
+#define ORBX_EDGE 19       /* EDGE_THRESHOLD, src/ORBextractor.cc:46 */
+#define ORBX_DESC_BYTES 32 /* 256-bit rBRIEF */
+
+typedef struct orbx_handle orbx_handle;
+
+/* ORBextractor constructor arguments, include/ORBextractor.h:93, src/ORBextractor.cc:438-443 */
+typedef struct orbx_config {
+    int nfeatures;
+    float scale_factor;
+    int nlevels;
+    int ini_th_fast;
+    int min_th_fast;
+} orbx_config;
+
+/* cv::KeyPoint as the reference fills it (src/ORBextractor.cc:1146-1155, 1613-1622); class_id is always -1 */
+typedef struct orbx_keypoint {
+    float x, y;     /* pt, level-0 pixel frame (level coords * mvScaleFactor[octave]) */
+    float size;     /* (int)(31 * mvScaleFactor[octave]) */
+    float angle;    /* degrees, [0, 360], cv::fastAtan2 semantics */
+    float response; /* FAST score */
+    int octave;
+} orbx_keypoint;
+
+/* Text of the last error on this thread (never NULL). */
+const char* orbx_last_error(void);
+
+/* Number of CUDA devices visible, or a negative ORBX_ERR_* code. */
+int orbx_device_count(void);
+
+/* ---- extractor ------------------------------------------------------------------------------------ */
+
+/* Replaces ORBextractor::ORBextractor (src/ORBextractor.cc:438-550): computes the scale tables and per-level
+ * quotas, creates the device context (stream, buffers are sized lazily per image shape) on `device`. */
+int orbx_create(const orbx_config* cfg, int device, orbx_handle** out);
+void orbx_destroy(orbx_handle* h);
+
+/* Replaces GetLevels / GetScaleFactor(s) / GetInverseScaleFactors / GetScaleSigmaSquares /
+ * GetInverseScaleSigmaSquares (include/ORBextractor.h:119-159) and exposes mnFeaturesPerLevel.
+ * Any pointer may be NULL; arrays must hold nlevels entries. */
+int orbx_get_tables(const orbx_handle* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                    int* features_per_level);
+
+/* Upper bound on keypoints per frame for this configuration and image shape (rows x cols): the quad-tree can
+ * return up to quota+3 (or 4*nIni) nodes per level.  Size kps/desc buffers with it. */
+int orbx_max_keypoints(orbx_handle* h, int rows, int cols);
+
+/* Replaces ORBextractor::operator()(image, mask, keypoints, descriptors) (src/ORBextractor.cc:1513-1629) for
+ * n frames of identical shape.  HOST buffers in, HOST buffers out; H2D, all kernels, D2H and one stream
+ * synchronise happen inside.
+ *   imgs          n frames of CV_8UC1, frame i at imgs + i*frame_stride, rows `step` bytes apart
+ *   kps, desc     n * capacity entries / n * capacity * 32 bytes; frame i at offset i*capacity
+ *   counts        n entries: keypoints found per frame (0 for an "empty image" is not produced here:
+ *                 rows/cols <= 0 or imgs == NULL is ORBX_ERR_BAD_ARG; the adapter maps it to a silent return)
+ * Keypoints are ordered level 0..nlevels-1 and, inside a level, in the reference's quad-tree list order. */
+int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int cols, size_t step,
+                       size_t frame_stride, orbx_keypoint* kps, uint8_t* desc, int capacity, int* counts);
+
+/* Single frame convenience (n = 1). */
+int orbx_extract(orbx_handle* h, const uint8_t* img, int rows, int cols, size_t step, orbx_keypoint* kps,
+                 uint8_t* desc, int capacity, int* count);
+
+/* Same computation with DEVICE-resident inputs and outputs, asynchronous on the handle's stream (no copy, no
+ * host synchronisation): d_imgs are tight or pitched device frames, d_kps/d_desc/d_counts device buffers laid
+ * out as in orbx_extract_batch.  Use orbx_sync() (or your own event on orbx_stream()) before reading results. */
+int orbx_extract_batch_device(orbx_handle* h, const uint8_t* d_imgs, int n, int rows, int cols, size_t step,
+                              size_t frame_stride, orbx_keypoint* d_kps, uint8_t* d_desc, int capacity,
+                              int* d_counts);
+int orbx_sync(orbx_handle* h);
+/* cudaStream_t of the handle, as void*. */
+void* orbx_stream(orbx_handle* h);
+
+/* Replaces the public member mvImagePyramid (include/ORBextractor.h:162) of the LAST extracted batch:
+ * copies level `level` of frame `frame` INCLUDING its 19-px REFLECT_101 frame into dst
+ * ((rows_l + 38) rows of (cols_l + 38) bytes, dst_step bytes apart), so that an ROI at (19,19) of dst behaves
+ * like the reference's Mat (adjustROI by <= 19 stays valid, src/Frame.cc:782-831). */
+int orbx_get_level_size(orbx_handle* h, int level, int* rows_l, int* cols_l);
+int orbx_get_pyramid_level(orbx_handle* h, int frame, int level, uint8_t* dst, size_t dst_step);
+
+/* Per-stage device time of the last batch in milliseconds, measured with CUDA events when profiling is on
+ * (profiling serialises the stages; leave it off for throughput).  Stage order: ORBX_STAGE_*. */
+#define ORBX_STAGE_H2D 0
+#define ORBX_STAGE_PYRAMID 1
+#define ORBX_STAGE_FAST 2
+#define ORBX_STAGE_OCTREE 3 /* quad-tree distribution + IC_Angle */
+#define ORBX_STAGE_BLUR 4
+#define ORBX_STAGE_DESC 5
+#define ORBX_STAGE_D2H 6
+#define ORBX_NUM_STAGES 7
+int orbx_set_profiling(orbx_handle* h, int on);
+int orbx_stage_times(orbx_handle* h, float* ms /* ORBX_NUM_STAGES */);
+/* Number of kernel launches issued by the last extract call (for bench.py's gpu_launches). */
+int orbx_last_launch_count(orbx_handle* h);
+/* Use a captured CUDA graph per (shape, batch) for the kernel sequence (default on). */
+int orbx_set_use_graph(orbx_handle* h, int on);
+
+/* Stage introspection for parity tests (last batch): FAST candidates of one level as (x, y, response) triples
+ * in level pixel coordinates, unordered; the blurred interior of one level (rows_l x cols_l, tight). */
+int orbx_debug_get_candidates(orbx_handle* h, int frame, int level, int* xyr, int cap, int* n);
+int orbx_debug_get_blurred(orbx_handle* h, int frame, int level, uint8_t* dst);
+
+/* ---- matcher -------------------------------------------------------------------------------------- */
+
+/* ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1983-2003): 256-bit Hamming distance of two 32-byte rows.
+ * Host-side (a single pair never justifies a launch). */
+int orbm_descriptor_distance(const uint8_t* a, const uint8_t* b);
+
+typedef struct orbm_context orbm_context;
+int orbm_create(int device, orbm_context** out);
+void orbm_destroy(orbm_context* m);
+void* orbm_stream(orbm_context* m);
+int orbm_sync(orbm_context* m);
+
+/* Brute-force best / second-best Hamming search (north_star item 6, config 5): for every query row the smallest
+ * distance over db rows [0, ndb), the lowest index attaining it (reported + idx_offset) and the second
+ * smallest distance of the multiset -- the result of the reference's sequential
+ * `if(d<best){second=best;best=d;idx=j} else if(d<second) second=d` scan (src/ORBmatcher.cc:134-151) over the
+ * whole database.  Empty db: best = second = 256, idx = -1.  mem_kind 0: all pointers are HOST (copies inside,
+ * synchronous); 1: all pointers are DEVICE (asynchronous on orbm_stream()). */
+int orbm_bruteforce(orbm_context* m, const uint8_t* q, int nq, const uint8_t* db, int ndb, int idx_offset,
+                    int32_t* best, int32_t* best_idx, int32_t* second, int mem_kind);
+
+/* Deterministic merge of `nparts` partial results (e.g. one per database shard, parts ordered by ascending
+ * index range): equals the sequential scan over the concatenated database.  DEVICE pointers,
+ * best/best_idx/second laid out [part][nq].  Used after the all-gather in the sharded search. */
+int orbm_merge_partials(orbm_context* m, const int32_t* best, const int32_t* best_idx, const int32_t* second,
+                        int nparts, int nq, int32_t* out_best, int32_t* out_idx, int32_t* out_second);
+
+/* Frame-side inputs of the windowed searches: Frame::mvKeysUn, mvuRight, mDescriptors, mvpMapPoints occupancy,
+ * mGrid (src/Frame.cc:351-370) flattened as CSR with cell (ix, iy) at ix*48+iy, and the grid constants. */
+typedef struct orbm_frame_view {
+    int n;
+    const float* x;            /* mvKeysUn[i].pt.x */
+    const float* y;
+    const int32_t* octave;
+    const float* u_right;      /* mvuRight, may be NULL (monocular: all -1) */
+    const uint8_t* desc;       /* n x 32 */
+    const uint8_t* occupied;   /* 1 iff mvpMapPoints[i] && mvpMapPoints[i]->Observations() > 0 on entry */
+    const int32_t* cell_start; /* 64*48 + 1 */
+    const int32_t* cell_items;
+    float min_x, min_y, grid_w_inv, grid_h_inv; /* mnMinX, mnMinY, mfGridElementWidthInv, mfGridElementHeightInv */
+    const float* scale_factors; /* mvScaleFactors */
+    int nlevels;
+} orbm_frame_view;
+
+/* MapPoint-side inputs: the tracking scratch fields written by Frame::isInFrustum (include/MapPoint.h:149-156). */
+typedef struct orbm_mappoint_view {
+    int n;
+    const float* proj_x;     /* mTrackProjX */
+    const float* proj_y;     /* mTrackProjY */
+    const float* proj_xr;    /* mTrackProjXR */
+    const int32_t* level;    /* mnTrackScaleLevel */
+    const float* view_cos;   /* mTrackViewCos */
+    const uint8_t* valid;    /* mbTrackInView && !isBad() */
+    const uint8_t* obs_pos;  /* Observations() > 0 (a claim by such a point blocks later points) */
+    const uint8_t* desc;     /* GetDescriptor(), n x 32 */
+} orbm_mappoint_view;
+
+/* Replaces ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, float th) (src/ORBmatcher.cc:61-173,
+ * RadiusByViewingCos :176-183, Frame::GetFeaturesInArea src/Frame.cc:488-548) including its order-dependent
+ * claims.  HOST pointers.  out_match[i] = index of the map point the call would store in F.mvpMapPoints[i], or -1
+ * when it leaves the slot untouched.  *nmatches = the function's return value. */
+int orbm_search_by_projection(orbm_context* m, const orbm_frame_view* f, const orbm_mappoint_view* p, float th,
+                              float nnratio, int32_t* out_match, int* nmatches);
+
+/* Replaces the coarse Hamming search of Frame::ComputeStereoMatches (src/Frame.cc:684-765).  HOST pointers.
+ * best_r[i] = right keypoint index for left keypoint i or -1 (distance >= (TH_HIGH+TH_LOW)/2 or no candidate);
+ * best_dist[i] = the best distance found (TH_HIGH when none). */
+int orbm_stereo_rows(orbm_context* m, int nl, const float* lx, const float* ly, const int32_t* loct,
+                     const uint8_t* ldesc, int nr, const float* rx, const float* ry, const int32_t* roct,
+                     const uint8_t* rdesc, const float* scale_factors, int nlevels, int n_rows, float min_d,
+                     float max_d, int32_t* best_r, int32_t* best_dist);
+
+/* DBoW2::FeatureVector (std::map<NodeId, vector<unsigned>>) flattened as CSR with ascending node ids. */
+typedef struct orbm_featvec_view {
+    int n_nodes;
+    const int32_t* node_id;
+    const int32_t* node_start; /* n_nodes + 1 */
+    const int32_t* node_feat;
+} orbm_featvec_view;
+
+/* Replaces ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&) (src/ORBmatcher.cc:228-392 incl. the
+ * rotation-histogram filter, ComputeThreeMaxima :1935-1977).  HOST pointers.  kf_has_mp[i] = KF feature i has a
+ * non-bad MapPoint.  out_match[f] = KF feature index matched to frame feature f, or -1. */
+int orbm_search_by_bow(orbm_context* m, int nkf, const uint8_t* kf_desc, const float* kf_angle,
+                       const uint8_t* kf_has_mp, const orbm_featvec_view* kf_fv, int nf, const uint8_t* f_desc,
+                       const float* f_angle, const orbm_featvec_view* f_fv, float nnratio, int check_orientation,
+                       int32_t* out_match, int* nmatches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBX_H_ */

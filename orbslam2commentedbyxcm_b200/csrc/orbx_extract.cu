@@ -1,0 +1,1490 @@
+// orbx_extract.cu -- B200 (sm_100a) ORB extractor: pyramid, per-cell FAST, quad-tree distribution + orientation,
+// 7x7 Gaussian blur, steered BRIEF.  One launch per stage covers every frame of a batch (grid.y / grid.z = frame)
+// and every pyramid level that stage can process concurrently.
+//
+// Reference behaviour reproduced (paths in the reference tree):
+//   k_level0 / k_resize  ORBextractor::ComputePyramid            src/ORBextractor.cc:1635-1694
+//   k_fast_cells         cell loop of ComputeKeyPointsOctTree    src/ORBextractor.cc:1017-1122 (+ cv::FAST 9/16, NMS)
+//   k_octree             DistributeOctTree / DivideNode          src/ORBextractor.cc:581-1013, :1124-1164
+//                        + IC_Angle / cv::fastAtan2              src/ORBextractor.cc:59-106, :559-570
+//   k_blur               cv::GaussianBlur 7x7 sigma 2            src/ORBextractor.cc:1587-1595
+//   k_describe           computeOrbDescriptor                    src/ORBextractor.cc:118-172, :1613-1622
+// Results are bit-identical to the CPU oracle (oracle/orb_oracle.cc); tests/test_gpu_extractor.py checks that.
+#include "orbx_common.cuh"
+#include "sincosf_dev.cuh"
+#include <cmath>
+#include <cfloat>
+#include <cstdarg>
+#include <vector>
+#include <algorithm>
+
+namespace orbx {
+
+std::string& last_error()
+{
+    static thread_local std::string e;
+    return e;
+}
+void set_error(const char* fmt, ...)
+{
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    last_error() = buf;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Plan: everything that depends only on (config, image shape).  Passed to kernels by value.
+// ------------------------------------------------------------------------------------------------------
+struct LevelGeom {
+    int w, h;            // interior size of the level
+    int pitch;           // bytes per buffer row (multiple of 128)
+    int planeRows;       // h + 2*EDGE
+    long long planeOff;  // byte offset of frame 0's plane of this level inside the pyramid (and blurred) arena
+    long long planeBytes;
+    int nCols, nRows, wCell, hCell;  // 30-px cell grid (src/ORBextractor.cc:1043-1051)
+    int maxBX, maxBY;    // w - 16, h - 16
+    int cellOff;         // first CTA index of this level in k_fast_cells
+    int quota;           // mnFeaturesPerLevel
+    int candCap;         // capacity of the candidate list (worst case after 3x3 NMS)
+    long long candOff;   // offset (in candidates) of frame 0's list of this level
+    int nodeCap;         // quad-tree node capacity = per-level keypoint capacity
+    int kpOff;           // offset of this level in a frame's keypoint staging
+    int nIni;            // quad-tree roots
+    float hX;            // root width
+    float scale;         // mvScaleFactor[level]
+    int patchSize;       // (int)(31 * scale)
+    int xTab, yTab;      // offsets into the resize coefficient tables
+};
+
+struct Plan {
+    int nlevels, rows, cols;
+    int iniTh, minTh;
+    int totalCells;
+    int kpCapFrame;          // sum of nodeCap = keypoint capacity per frame
+    long long pyrFrameStride;  // not used for addressing (planes are [level][frame]); kept for sizing
+    long long candFrame;       // candidates per frame (sum of candCap)
+    LevelGeom lv[ORBX_MAX_LEVELS];
+};
+
+struct Cand {  // one FAST candidate
+    uint32_t xy;  // x | y << 16, relative to (minBorderX, minBorderY) = (16, 16) like the reference's vToDistributeKeys
+    uint32_t ro;  // response << 24 | (0xFFFFFF - ord); ord = rank key of the reference's candidate order
+};
+
+struct StagedKp {  // per-level keypoint between k_octree and k_describe
+    float x, y;    // level pixel coordinates (integers)
+    float angle;
+    float response;
+};
+
+struct Buffers {
+    uint8_t* pyr;        // [level][frame] padded planes
+    uint8_t* blur;       // same layout; only interiors are written
+    Cand* cand;          // [frame][level] lists
+    int* candCount;      // [frame][nlevels] atomic counters (reset by k_octree)
+    int* candCountDbg;   // [frame][nlevels] copy kept for introspection
+    StagedKp* staged;    // [frame][kpCapFrame]
+    int* levelCount;     // [frame][nlevels]
+    const short* xofs;   // resize tables
+    const short2* xw;
+    const short* yofs0;
+    const short* yofs1;
+    const short2* yw;
+    int* errFlag;        // device-side overflow flag
+    int frames;
+};
+
+// rBRIEF pattern: 256 pairs x (x0,y0,x1,y1), 1024 signed bytes
+__device__ const signed char d_pattern[1024] __attribute__((aligned(16))) = {
+#include "orb_pattern.inc"
+};
+
+__device__ __forceinline__ uint8_t* plane_ptr(uint8_t* arena, const LevelGeom& g, int frame)
+{
+    return arena + g.planeOff + (long long)frame * g.planeBytes;
+}
+__device__ __forceinline__ const uint8_t* interior_ptr(const uint8_t* arena, const LevelGeom& g, int frame)
+{
+    return arena + g.planeOff + (long long)frame * g.planeBytes + (long long)PAD_TOP * g.pitch + PAD_LEFT;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// K1a: level 0 = input image + REFLECT_101 frame.  One thread writes one aligned 32-bit word of a buffer row.
+// ------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_level0(Plan plan, Buffers buf, const uint8_t* __restrict__ in, long long inStep,
+                                                long long inFrameStride)
+{
+    const LevelGeom& g = plan.lv[0];
+    const int bx = 4 * (blockIdx.x * 128 + threadIdx.x);
+    if (bx >= g.pitch) return;
+    const int by = blockIdx.y, frame = blockIdx.z;
+    const int y = reflect101(by - PAD_TOP, g.h);
+    const uint8_t* src = in + (long long)frame * inFrameStride + (long long)y * inStep;
+    uint32_t v = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        int x = min(max(bx + j - PAD_LEFT, -EDGE), g.w - 1 + EDGE);
+        x = reflect101(x, g.w);
+        v |= (uint32_t)__ldg(src + x) << (8 * j);
+    }
+    *reinterpret_cast<uint32_t*>(plane_ptr(buf.pyr, g, frame) + (long long)by * g.pitch + bx) = v;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// K1b: level l = cv::resize(level l-1, INTER_LINEAR) + REFLECT_101 frame, fixed point (11-bit weights):
+//   T = S[sx]*a0 + S[sx+1]*a1;  dst = (((b0*(T0>>4))>>16) + ((b1*(T1>>4))>>16) + 2) >> 2
+// Frame pixels are recomputed from the reflected destination coordinate (no second pass over the plane).
+// ------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_resize(Plan plan, Buffers buf, int level)
+{
+    const LevelGeom& g = plan.lv[level];
+    const LevelGeom& gp = plan.lv[level - 1];
+    const int bx = 4 * (blockIdx.x * 128 + threadIdx.x);
+    if (bx >= g.pitch) return;
+    const int by = blockIdx.y, frame = blockIdx.z;
+    const int dy = reflect101(by - PAD_TOP, g.h);
+    const uint8_t* S = interior_ptr(buf.pyr, gp, frame);
+    const uint8_t* S0 = S + (long long)buf.yofs0[g.yTab + dy] * gp.pitch;
+    const uint8_t* S1 = S + (long long)buf.yofs1[g.yTab + dy] * gp.pitch;
+    const short2 b = buf.yw[g.yTab + dy];
+    uint32_t v = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        int dx = min(max(bx + j - PAD_LEFT, -EDGE), g.w - 1 + EDGE);
+        dx = reflect101(dx, g.w);
+        const int sx = buf.xofs[g.xTab + dx];
+        const int sx1 = min(sx + 1, gp.w - 1);
+        const short2 a = buf.xw[g.xTab + dx];
+        const int t0 = S0[sx] * a.x + S0[sx1] * a.y;
+        const int t1 = S1[sx] * a.x + S1[sx1] * a.y;
+        const int r = (((b.x * (t0 >> 4)) >> 16) + ((b.y * (t1 >> 4)) >> 16) + 2) >> 2;
+        v |= (uint32_t)min(max(r, 0), 255) << (8 * j);
+    }
+    *reinterpret_cast<uint32_t*>(plane_ptr(buf.pyr, g, frame) + (long long)by * g.pitch + bx) = v;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// K2: FAST-9/16 per 30-px cell with the iniThFAST -> minThFAST retry.  One CTA per (cell, frame).
+//   score S(p) = max over the 16 contiguous 9-arcs of max(min d, min -d) - 1, corner at t <=> S >= t;
+//   3x3 NMS inside the cell's evaluated region only (cv::FAST is run on the cell ROI);
+//   cell output = NMS survivors with S >= ini if there is one, else survivors with S >= min.
+// Candidates are appended to the level's list in arbitrary order; the reference's order (cell row-major, then
+// pixel row-major) is carried in `ord` and only matters for response ties inside a quad-tree node.
+// ------------------------------------------------------------------------------------------------------
+constexpr int FAST_T = 128;
+constexpr int FAST_TP = 80;    // ROI tile pitch (bytes): cells are at most 59 px wide -> ROI <= 65 + 3 alignment bytes
+constexpr int FAST_MAXR = 66;  // max ROI rows
+constexpr int FAST_SP = 64;    // score tile pitch (eval width <= 59, + 2 halo)
+
+__device__ __forceinline__ int fast_score(const uint8_t* p, int minTh)
+{
+    // ring offsets in ROI-tile coordinates (dx, dy) as in cv::FAST's 16-pixel circle
+    constexpr int O[16] = {
+        3 * FAST_TP + 0, 3 * FAST_TP + 1, 2 * FAST_TP + 2, 1 * FAST_TP + 3, 0 * FAST_TP + 3, -1 * FAST_TP + 3,
+        -2 * FAST_TP + 2, -3 * FAST_TP + 1, -3 * FAST_TP + 0, -3 * FAST_TP - 1, -2 * FAST_TP - 2, -1 * FAST_TP - 3,
+        0 * FAST_TP - 3, 1 * FAST_TP - 3, 2 * FAST_TP - 2, 3 * FAST_TP - 1};
+    const int c = p[0];
+    // high-speed test: every 9-arc contains at least two of the four compass pixels
+    const int d0 = c - p[O[0]], d4 = c - p[O[4]], d8 = c - p[O[8]], d12 = c - p[O[12]];
+    const int nb = (d0 > minTh) + (d4 > minTh) + (d8 > minTh) + (d12 > minTh);
+    const int nd = (d0 < -minTh) + (d4 < -minTh) + (d8 < -minTh) + (d12 < -minTh);
+    if (nb < 2 && nd < 2) return 0;
+    int d[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) d[k] = c - p[O[k]];
+    // sliding minimum / maximum over windows of 9 by doubling (1 -> 2 -> 4 -> 8 -> 9)
+    int mn[16], mx[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) { mn[k] = min(d[k], d[(k + 1) & 15]); mx[k] = max(d[k], d[(k + 1) & 15]); }
+    int mn4[16], mx4[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) { mn4[k] = min(mn[k], mn[(k + 2) & 15]); mx4[k] = max(mx[k], mx[(k + 2) & 15]); }
+    int a = -256, b = 256;
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        const int m8 = min(mn4[k], mn4[(k + 4) & 15]);
+        const int x8 = max(mx4[k], mx4[(k + 4) & 15]);
+        a = max(a, min(m8, d[(k + 8) & 15]));
+        b = min(b, max(x8, d[(k + 8) & 15]));
+    }
+    const int m = max(a, -b);
+    return m > minTh ? m - 1 : 0;
+}
+
+__global__ void __launch_bounds__(FAST_T) k_fast_cells(Plan plan, Buffers buf)
+{
+    __shared__ __align__(16) uint8_t tile[FAST_MAXR * FAST_TP];
+    __shared__ uint8_t sc[(FAST_MAXR - 4) * FAST_SP];
+    __shared__ int sCount, sBase;
+
+    const int frame = blockIdx.y;
+    int level = 0;
+    while (level + 1 < plan.nlevels && (int)blockIdx.x >= plan.lv[level + 1].cellOff) level++;
+    const LevelGeom& g = plan.lv[level];
+    const int cell = blockIdx.x - g.cellOff;
+    const int ci = cell / g.nCols, cj = cell - ci * g.nCols;
+
+    const int iniY = 16 + ci * g.hCell, iniX = 16 + cj * g.wCell;
+    if (iniY >= g.maxBY - 3 || iniX >= g.maxBX - 6) return;
+    const int maxY = min(iniY + g.hCell + 6, g.maxBY), maxX = min(iniX + g.wCell + 6, g.maxBX);
+    const int rw = maxX - iniX, rh = maxY - iniY;
+    if (rw < 7 || rh < 7) return;
+    const int ew = rw - 6, eh = rh - 6;
+
+    // stage the ROI with aligned 32-bit loads
+    const uint8_t* interior = interior_ptr(buf.pyr, g, frame);
+    const int bcol0 = PAD_LEFT + iniX;
+    const int shift = bcol0 & 3;
+    const int nw = (shift + rw + 3) >> 2;
+    const uint8_t* rowBase = interior + (long long)iniY * g.pitch + (iniX - shift);
+    for (int idx = threadIdx.x; idx < rh * nw; idx += FAST_T) {
+        const int r = idx / nw, wi = idx - r * nw;
+        const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(rowBase + (long long)r * g.pitch) + wi);
+        reinterpret_cast<uint32_t*>(tile + r * FAST_TP)[wi] = v;
+    }
+    for (int idx = threadIdx.x; idx < (eh + 2) * FAST_SP; idx += FAST_T) sc[idx] = 0;
+    if (threadIdx.x == 0) sCount = 0;
+    __syncthreads();
+
+    const int npx = ew * eh;
+    for (int idx = threadIdx.x; idx < npx; idx += FAST_T) {
+        const int ey = idx / ew, ex = idx - ey * ew;
+        const int s = fast_score(tile + (ey + 3) * FAST_TP + shift + ex + 3, plan.minTh);
+        sc[(ey + 1) * FAST_SP + ex + 1] = (uint8_t)s;
+    }
+    __syncthreads();
+
+    // 3x3 NMS; per-thread survivor mask (pixel k of this thread = bit k)
+    uint32_t keep = 0;
+    int hasIni = 0;
+    {
+        int k = 0;
+        for (int idx = threadIdx.x; idx < npx; idx += FAST_T, k++) {
+            const int ey = idx / ew, ex = idx - ey * ew;
+            const uint8_t* q = sc + (ey + 1) * FAST_SP + ex + 1;
+            const int s = q[0];
+            if (s >= plan.minTh && s > 0 && s > q[-1] && s > q[1] && s > q[-FAST_SP - 1] && s > q[-FAST_SP] &&
+                s > q[-FAST_SP + 1] && s > q[FAST_SP - 1] && s > q[FAST_SP] && s > q[FAST_SP + 1]) {
+                keep |= 1u << k;
+                hasIni |= (s >= plan.iniTh);
+            }
+        }
+    }
+    const int anyIni = __syncthreads_or(hasIni);
+    const int thEff = anyIni ? plan.iniTh : plan.minTh;
+    // count, reserve, write
+    int mine = 0;
+    {
+        int k = 0;
+        for (int idx = threadIdx.x; idx < npx; idx += FAST_T, k++) {
+            if (!(keep >> k & 1)) continue;
+            const int ey = idx / ew, ex = idx - ey * ew;
+            if (sc[(ey + 1) * FAST_SP + ex + 1] >= thEff) mine++;
+            else keep &= ~(1u << k);
+        }
+    }
+    int local = 0;
+    if (mine) local = atomicAdd(&sCount, mine);
+    __syncthreads();
+    if (threadIdx.x == 0) sBase = sCount ? atomicAdd(buf.candCount + frame * plan.nlevels + level, sCount) : 0;
+    __syncthreads();
+    if (!mine) return;
+    Cand* out = buf.cand + (long long)frame * plan.candFrame + g.candOff;
+    int pos = sBase + local;
+    int k = 0;
+    for (int idx = threadIdx.x; idx < npx; idx += FAST_T, k++) {
+        if (!(keep >> k & 1)) continue;
+        const int ey = idx / ew, ex = idx - ey * ew;
+        if (pos >= g.candCap) { atomicExch(buf.errFlag, 1); break; }
+        const int s = sc[(ey + 1) * FAST_SP + ex + 1];
+        const uint32_t xrel = cj * g.wCell + ex + 3, yrel = ci * g.hCell + ey + 3;
+        const uint32_t ord = ((uint32_t)cell * g.hCell + ey) * g.wCell + ex;
+        Cand c;
+        c.xy = xrel | (yrel << 16);
+        c.ro = ((uint32_t)s << 24) | (0xFFFFFFu - ord);
+        out[pos++] = c;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// K3: quad-tree distribution (+ orientation epilogue).  One CTA per (level, frame).
+//
+// The reference keeps a std::list of nodes and splits with push_front / erase; that list is reproduced as an
+// array in list order, rebuilt once per pass with prefix sums:
+//   phase 1 (expand every node with > 1 key):   L' = reverse(children in creation order) ++ [1-key nodes]
+//   phase 2 (expand by size until >= N nodes):  candidates sorted by (size desc, creation index desc), all split
+//            in parallel, the sequential "break when size >= N" becomes a prefix-sum cut; L' = reverse(children of
+//            the processed candidates) ++ [old list without those candidates].
+// Keys never move: each key carries the list position of its node, so node sizes are atomics and the final
+// "max response, first in candidate order" pick is one atomicMax on (response << 24 | ~ord).
+// ------------------------------------------------------------------------------------------------------
+constexpr int OCT_T = 512;
+
+struct OctSmem {
+    short4* geoA; short4* geoB;       // node rectangles (ulx, uly, brx, bry), list order, double buffered
+    int* cntA; int* cntB;             // keys per node
+    int* childCnt;                    // 4 per split slot
+    unsigned short* childPos;         // new list position of each child (0xFFFF = empty)
+    unsigned short* nodePos;          // new list position of surviving nodes
+    int* scanA; int* scanB;           // scratch for prefix sums
+    unsigned short* V; unsigned short* Vn;  // phase-2 candidates (list positions), creation order
+    short* slotOf;                    // list position -> split slot or -1
+    unsigned short* procOfSlot;       // slot -> rank in processing order
+    unsigned short* slotOfProc;       // processing rank -> slot
+    unsigned int* best;               // per node max(ro)
+    int* winner;                      // per node winning key index
+    unsigned short* keyNode;          // per key: list position of its node (smem when it fits)
+};
+
+__device__ __forceinline__ int warp_incl_scan(int v)
+{
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) >= o) v += t;
+    }
+    return v;
+}
+
+// in-place exclusive scan of data[0..n); returns the total.  All threads of the CTA must call it.
+__device__ int block_exscan(int* data, int n, int* warpSums)
+{
+    const int ipt = (n + OCT_T - 1) / OCT_T;
+    const int b = threadIdx.x * ipt, e = min(b + ipt, n);
+    int sum = 0;
+    for (int i = b; i < e; i++) sum += data[i];
+    const int incl = warp_incl_scan(sum);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 31) warpSums[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int w = lane < OCT_T / 32 ? warpSums[lane] : 0;
+        int wi = warp_incl_scan(w);
+        warpSums[lane] = wi - w;
+        if (lane == 31) warpSums[32] = wi;
+    }
+    __syncthreads();
+    int run = warpSums[wid] + incl - sum;
+    for (int i = b; i < e; i++) { int v = data[i]; data[i] = run; run += v; }
+    const int total = warpSums[32];
+    __syncthreads();
+    return total;
+}
+
+__device__ __forceinline__ int child_of(short4 r, uint32_t xy, int& mx, int& my)
+{
+    mx = r.x + ((r.z - r.x + 1) >> 1);  // UL.x + ceil((UR.x-UL.x)/2.f)
+    my = r.y + ((r.w - r.y + 1) >> 1);
+    const int x = xy & 0xffff, y = xy >> 16;
+    return (x < mx ? 0 : 1) + (y < my ? 0 : 2);  // n1 UL, n2 UR, n3 BL, n4 BR
+}
+__device__ __forceinline__ short4 child_rect(short4 r, int c, int mx, int my)
+{
+    short4 o;
+    o.x = (c & 1) ? mx : r.x;
+    o.z = (c & 1) ? r.z : mx;
+    o.y = (c & 2) ? my : r.y;
+    o.w = (c & 2) ? r.w : my;
+    return o;
+}
+
+// cv::fastAtan2, scalar float path, no contraction
+__device__ __forceinline__ float fast_atan2_dev(float y, float x)
+{
+    const float p1 = 57.2836266f, p3 = -18.6674461f, p5 = 8.91400051f, p7 = -2.53972459f;
+    const float ax = fabsf(x), ay = fabsf(y);
+    float a;
+    if (ax >= ay) {
+        const float c = __fdiv_rn(ay, __fadd_rn(ax, 2.22044605e-16f));
+        const float c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+    } else {
+        const float c = __fdiv_rn(ax, __fadd_rn(ay, 2.22044605e-16f));
+        const float c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+// circular patch half-widths umax[|v|] (src/ORBextractor.cc:519-549)
+__device__ __forceinline__ constexpr int umax_of(int av)
+{
+    constexpr int U[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
+    return U[av];
+}
+
+__global__ void __launch_bounds__(OCT_T) k_octree(Plan plan, Buffers buf, int nodeCapMax, int keySmemCap,
+                                                  unsigned short* keyNodeGlobal, long long keyNodeFrameStride)
+{
+    extern __shared__ __align__(16) unsigned char smemRaw[];
+    __shared__ int warpSums[33];
+    __shared__ int sN, sNV, sFinish, sCut, sCtot;
+
+    const int level = blockIdx.x, frame = blockIdx.y;
+    const LevelGeom& g = plan.lv[level];
+    int* counter = buf.candCount + frame * plan.nlevels + level;
+    const int M = min(*counter, g.candCap);
+    const Cand* __restrict__ cand = buf.cand + (long long)frame * plan.candFrame + g.candOff;
+    StagedKp* staged = buf.staged + (long long)frame * plan.kpCapFrame + g.kpOff;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        buf.candCountDbg[frame * plan.nlevels + level] = M;
+        *counter = 0;  // ready for the next batch
+    }
+    if (M == 0) {
+        if (threadIdx.x == 0) buf.levelCount[frame * plan.nlevels + level] = 0;
+        return;
+    }
+
+    // carve shared memory
+    OctSmem S;
+    {
+        unsigned char* p = smemRaw;
+        const int cap = nodeCapMax;
+        auto take = [&](size_t bytes) { unsigned char* r = p; p += (bytes + 15) & ~size_t(15); return r; };
+        S.geoA = (short4*)take(sizeof(short4) * cap);
+        S.geoB = (short4*)take(sizeof(short4) * cap);
+        S.cntA = (int*)take(4 * cap);
+        S.cntB = (int*)take(4 * cap);
+        S.childCnt = (int*)take(16 * cap);
+        S.scanA = (int*)take(4 * cap);
+        S.scanB = (int*)take(4 * cap);
+        S.best = (unsigned int*)take(4 * cap);
+        S.winner = (int*)take(4 * cap);
+        S.childPos = (unsigned short*)take(8 * cap);
+        S.nodePos = (unsigned short*)take(2 * cap);
+        S.V = (unsigned short*)take(2 * cap);
+        S.Vn = (unsigned short*)take(2 * cap);
+        S.slotOf = (short*)take(2 * cap);
+        S.procOfSlot = (unsigned short*)take(2 * cap);
+        S.slotOfProc = (unsigned short*)take(2 * cap);
+        S.keyNode = (M <= keySmemCap) ? (unsigned short*)take(2 * (size_t)keySmemCap)
+                                      : keyNodeGlobal + (long long)frame * keyNodeFrameStride + g.candOff;
+    }
+    const int N = g.quota;
+    const int tid = threadIdx.x;
+
+    // ---- roots (src/ORBextractor.cc:673-748) ----
+    const int nIni = g.nIni;
+    const float hX = g.hX;
+    for (int i = tid; i < nIni; i += OCT_T) {
+        short4 r;
+        r.x = (short)(int)__fmul_rn(hX, (float)i);
+        r.z = (short)(int)__fmul_rn(hX, (float)(i + 1));
+        r.y = 0;
+        r.w = (short)(g.maxBY - 16);
+        S.geoB[i] = r;
+        S.cntB[i] = 0;
+    }
+    __syncthreads();
+    for (int k = tid; k < M; k += OCT_T) {
+        const int x = cand[k].xy & 0xffff;
+        const int root = (int)__fdiv_rn((float)x, hX);
+        S.keyNode[k] = (unsigned short)root;
+        atomicAdd(&S.cntB[root], 1);
+    }
+    __syncthreads();
+    // drop empty roots, keep order
+    for (int i = tid; i < nIni; i += OCT_T) S.scanA[i] = S.cntB[i] > 0;
+    __syncthreads();
+    int n = block_exscan(S.scanA, nIni, warpSums);
+    for (int i = tid; i < nIni; i += OCT_T)
+        if (S.cntB[i] > 0) { S.geoA[S.scanA[i]] = S.geoB[i]; S.cntA[S.scanA[i]] = S.cntB[i]; S.nodePos[i] = (unsigned short)S.scanA[i]; }
+    __syncthreads();
+    for (int k = tid; k < M; k += OCT_T) S.keyNode[k] = S.nodePos[S.keyNode[k]];
+    __syncthreads();
+
+    short4* geo = S.geoA; short4* geoN = S.geoB;
+    int* cnt = S.cntA; int* cntN = S.cntB;
+    int nV = 0;
+    bool finish = false;
+
+    while (!finish) {
+        // ================= phase 1 pass: split every node holding more than one key =================
+        const int prevSize = n;
+        for (int i = tid; i < 4 * n; i += OCT_T) S.childCnt[i] = 0;
+        __syncthreads();
+        for (int k = tid; k < M; k += OCT_T) {
+            const int i = S.keyNode[k];
+            if (cnt[i] > 1) {
+                int mx, my;
+                const int c = child_of(geo[i], cand[k].xy, mx, my);
+                atomicAdd(&S.childCnt[4 * i + c], 1);
+            }
+        }
+        __syncthreads();
+        for (int i = tid; i < n; i += OCT_T) {
+            int nch = 0, nex = 0;
+            if (cnt[i] > 1) {
+#pragma unroll
+                for (int c = 0; c < 4; c++) { const int v = S.childCnt[4 * i + c]; nch += v > 0; nex += v > 1; }
+            }
+            S.scanA[i] = nch | (nex << 16);
+            S.scanB[i] = cnt[i] > 1 ? 0 : 1;
+        }
+        __syncthreads();
+        const int totA = block_exscan(S.scanA, n, warpSums);
+        const int totB = block_exscan(S.scanB, n, warpSums);
+        const int C = totA & 0xffff, nToExpand = totA >> 16;
+        const int nNew = C + totB;
+        // (capacity: nNew <= max(N, 4*nIni) <= nodeCap by construction)
+        for (int i = tid; i < n; i += OCT_T) {
+            if (cnt[i] > 1) {
+                int ci = S.scanA[i] & 0xffff, vi = S.scanA[i] >> 16;
+                const short4 r = geo[i];
+                const int mx = r.x + ((r.z - r.x + 1) >> 1), my = r.y + ((r.w - r.y + 1) >> 1);
+#pragma unroll
+                for (int c = 0; c < 4; c++) {
+                    const int v = S.childCnt[4 * i + c];
+                    if (v > 0) {
+                        const int pos = C - 1 - ci;
+                        geoN[pos] = child_rect(r, c, mx, my);
+                        cntN[pos] = v;
+                        S.childPos[4 * i + c] = (unsigned short)pos;
+                        if (v > 1) S.V[vi++] = (unsigned short)pos;
+                        ci++;
+                    }
+                }
+            } else {
+                const int pos = C + S.scanB[i];
+                geoN[pos] = geo[i];
+                cntN[pos] = cnt[i];
+                S.nodePos[i] = (unsigned short)pos;
+            }
+        }
+        __syncthreads();
+        for (int k = tid; k < M; k += OCT_T) {
+            const int i = S.keyNode[k];
+            if (cnt[i] > 1) {
+                int mx, my;
+                const int c = child_of(geo[i], cand[k].xy, mx, my);
+                S.keyNode[k] = S.childPos[4 * i + c];
+            } else {
+                S.keyNode[k] = S.nodePos[i];
+            }
+        }
+        __syncthreads();
+        { short4* t = geo; geo = geoN; geoN = t; int* u = cnt; cnt = cntN; cntN = u; }
+        n = nNew;
+        nV = nToExpand;
+        if (n >= N || n == prevSize) {
+            finish = true;
+        } else if (n + nToExpand * 3 > N) {
+            // ================= phase 2: split by size, largest first, until the list reaches N =================
+            unsigned short* V = S.V; unsigned short* Vn = S.Vn;
+            while (!finish) {
+                if (nV == 0) { finish = true; break; }  // nothing left to split: size unchanged (src/ORBextractor.cc:967)
+                const int prev2 = n;
+                // processing order: stable ascending sort on size, walked from the back
+                //   = descending size, ties by descending creation index (decision D1)
+                for (int s = tid; s < nV; s += OCT_T) {
+                    const int cs = cnt[V[s]];
+                    int rank = 0;
+                    for (int t = 0; t < nV; t++) {
+                        const int ct = cnt[V[t]];
+                        rank += (ct > cs) || (ct == cs && t > s);
+                    }
+                    S.procOfSlot[s] = (unsigned short)rank;
+                    S.slotOfProc[rank] = (unsigned short)s;
+                }
+                for (int i = tid; i < n; i += OCT_T) S.slotOf[i] = -1;
+                for (int i = tid; i < 4 * nV; i += OCT_T) S.childCnt[i] = 0;
+                __syncthreads();
+                for (int s = tid; s < nV; s += OCT_T) S.slotOf[V[s]] = (short)s;
+                __syncthreads();
+                for (int k = tid; k < M; k += OCT_T) {
+                    const int i = S.keyNode[k];
+                    const int s = S.slotOf[i];
+                    if (s >= 0) {
+                        int mx, my;
+                        const int c = child_of(geo[i], cand[k].xy, mx, my);
+                        atomicAdd(&S.childCnt[4 * s + c], 1);
+                    }
+                }
+                __syncthreads();
+                // children per candidate in processing order -> prefix -> cut where the list reaches N
+                for (int p = tid; p < nV; p += OCT_T) {
+                    const int s = S.slotOfProc[p];
+                    int nch = 0;
+#pragma unroll
+                    for (int c = 0; c < 4; c++) nch += S.childCnt[4 * s + c] > 0;
+                    S.scanA[p] = nch;
+                }
+                if (tid == 0) sCut = nV - 1;
+                __syncthreads();
+                block_exscan(S.scanA, nV, warpSums);
+                // inclusive gain after processing p: (excl[p] + nch_p) - (p + 1)
+                for (int p = tid; p < nV; p += OCT_T) {
+                    const int s = S.slotOfProc[p];
+                    int nch = 0;
+#pragma unroll
+                    for (int c = 0; c < 4; c++) nch += S.childCnt[4 * s + c] > 0;
+                    if (n + S.scanA[p] + nch - (p + 1) >= N) atomicMin(&sCut, p);
+                }
+                __syncthreads();
+                const int cut = sCut;  // last processed rank
+                if (tid == 0) {
+                    const int s = S.slotOfProc[cut];
+                    int nch = 0;
+                    for (int c = 0; c < 4; c++) nch += S.childCnt[4 * s + c] > 0;
+                    sCtot = S.scanA[cut] + nch;
+                }
+                // surviving old nodes keep their order behind the new children
+                for (int i = tid; i < n; i += OCT_T) {
+                    const int s = S.slotOf[i];
+                    S.scanB[i] = (s >= 0 && S.procOfSlot[s] <= cut) ? 0 : 1;
+                }
+                __syncthreads();
+                const int Ctot = sCtot;
+                const int keepOld = block_exscan(S.scanB, n, warpSums);
+                const int nNew2 = Ctot + keepOld;
+                // new expandable list (creation order) needs its own prefix over processing ranks
+                for (int p = tid; p < nV; p += OCT_T) {
+                    const int s = S.slotOfProc[p];
+                    int nex = 0;
+                    if (p <= cut) {
+#pragma unroll
+                        for (int c = 0; c < 4; c++) nex += S.childCnt[4 * s + c] > 1;
+                    }
+                    S.winner[p] = nex;  // scratch
+                }
+                __syncthreads();
+                const int nVnew = block_exscan(S.winner, nV, warpSums);
+                for (int p = tid; p <= cut; p += OCT_T) {
+                    const int s = S.slotOfProc[p];
+                    const int i = V[s];
+                    const short4 r = geo[i];
+                    const int mx = r.x + ((r.z - r.x + 1) >> 1), my = r.y + ((r.w - r.y + 1) >> 1);
+                    int ci = S.scanA[p], vi = S.winner[p];
+#pragma unroll
+                    for (int c = 0; c < 4; c++) {
+                        const int v = S.childCnt[4 * s + c];
+                        if (v > 0) {
+                            const int pos = Ctot - 1 - ci;
+                            geoN[pos] = child_rect(r, c, mx, my);
+                            cntN[pos] = v;
+                            S.childPos[4 * s + c] = (unsigned short)pos;
+                            if (v > 1) Vn[vi++] = (unsigned short)pos;
+                            ci++;
+                        }
+                    }
+                }
+                for (int i = tid; i < n; i += OCT_T) {
+                    const int s = S.slotOf[i];
+                    if (!(s >= 0 && S.procOfSlot[s] <= cut)) {
+                        const int pos = Ctot + S.scanB[i];
+                        geoN[pos] = geo[i];
+                        cntN[pos] = cnt[i];
+                        S.nodePos[i] = (unsigned short)pos;
+                    }
+                }
+                __syncthreads();
+                for (int k = tid; k < M; k += OCT_T) {
+                    const int i = S.keyNode[k];
+                    const int s = S.slotOf[i];
+                    if (s >= 0 && S.procOfSlot[s] <= cut) {
+                        int mx, my;
+                        const int c = child_of(geo[i], cand[k].xy, mx, my);
+                        S.keyNode[k] = S.childPos[4 * s + c];
+                    } else {
+                        S.keyNode[k] = S.nodePos[i];
+                    }
+                }
+                __syncthreads();
+                { short4* t = geo; geo = geoN; geoN = t; int* u = cnt; cnt = cntN; cntN = u; }
+                { unsigned short* t = V; V = Vn; Vn = t; }
+                n = nNew2;
+                nV = nVnew;
+                if (n >= N || n == prev2) finish = true;
+            }
+        }
+    }
+
+    // ---- one keypoint per node: max response, first in candidate order on ties (src/ORBextractor.cc:984-1009) ----
+    for (int i = tid; i < n; i += OCT_T) S.best[i] = 0;
+    __syncthreads();
+    for (int k = tid; k < M; k += OCT_T) atomicMax(&S.best[S.keyNode[k]], cand[k].ro);
+    __syncthreads();
+    for (int k = tid; k < M; k += OCT_T) {
+        const int i = S.keyNode[k];
+        if (cand[k].ro == S.best[i]) S.winner[i] = k;
+    }
+    __syncthreads();
+    if (tid == 0) buf.levelCount[frame * plan.nlevels + level] = n;
+
+    // ---- orientation: intensity centroid over the radius-15 disc, one warp per keypoint ----
+    const uint8_t* interior = interior_ptr(buf.pyr, g, frame);
+    const int lane = tid & 31, wid = tid >> 5;
+    for (int i = wid; i < n; i += OCT_T / 32) {
+        const Cand c = cand[S.winner[i]];
+        const int x = (int)(c.xy & 0xffff) + 16, y = (int)(c.xy >> 16) + 16;
+        const uint8_t* center = interior + (long long)y * g.pitch + x;
+        const int u = lane - 15;  // lane 31 idles
+        int m10 = 0, m01 = 0;
+        if (lane < 31) {
+#pragma unroll
+            for (int v = -15; v <= 15; v++) {
+                const int av = v < 0 ? -v : v;
+                if ((u < 0 ? -u : u) <= umax_of(av)) {
+                    const int val = center[(long long)v * g.pitch + u];
+                    m10 += u * val;
+                    m01 += v * val;
+                }
+            }
+        }
+        m10 = __reduce_add_sync(0xffffffffu, m10);
+        m01 = __reduce_add_sync(0xffffffffu, m01);
+        if (lane == 0) {
+            StagedKp kp;
+            kp.x = (float)x;
+            kp.y = (float)y;
+            kp.angle = fast_atan2_dev((float)m01, (float)m10);
+            kp.response = (float)(c.ro >> 24);
+            staged[i] = kp;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// K5: 7x7 Gaussian blur, sigma 2, OpenCV 4.x fixed point: taps {18,34,48,56,48,34,18}/256, 16-bit horizontal sums,
+// 32-bit vertical sums, dst = (v + 32768) >> 16.  Reads the padded plane (its 19-px REFLECT_101 frame makes the
+// border handling implicit) and writes the interior of the blurred plane.  Tile: 128 x 32 outputs per CTA.
+// ------------------------------------------------------------------------------------------------------
+constexpr int BLUR_T = 256;
+constexpr int BLUR_W = 128, BLUR_H = 32;
+constexpr int BLUR_IN_P = BLUR_W + 8;  // input tile pitch in bytes: 4 left + 128 + 4 right
+
+__global__ void __launch_bounds__(BLUR_T) k_blur(Plan plan, Buffers buf, int level, int tilesX)
+{
+    __shared__ __align__(16) uint8_t in[(BLUR_H + 6) * BLUR_IN_P];
+    __shared__ __align__(16) uint16_t hs[(BLUR_H + 6) * BLUR_W];
+    const LevelGeom& g = plan.lv[level];
+    const int frame = blockIdx.z;
+    const int tx = blockIdx.x % tilesX, ty = blockIdx.x / tilesX;
+    const int x0 = tx * BLUR_W, y0 = ty * BLUR_H;  // interior coordinates of the tile origin
+    const uint8_t* src = interior_ptr(buf.pyr, g, frame);
+    uint8_t* dst = const_cast<uint8_t*>(interior_ptr(buf.blur, g, frame));
+    const int tid = threadIdx.x;
+    // rows y0-3 .. y0+BLUR_H+2, columns x0-4 .. x0+BLUR_W+3 as aligned words.  Rows beyond the padded plane are
+    // clamped (their values only feed outputs that are never stored).
+    constexpr int WPR = BLUR_IN_P / 4;
+    for (int idx = tid; idx < (BLUR_H + 6) * WPR; idx += BLUR_T) {
+        const int r = idx / WPR, wi = idx - r * WPR;
+        const int y = min(y0 - 3 + r, g.h - 1 + EDGE);
+        int bx = PAD_LEFT + x0 - 4 + 4 * wi;  // buffer column, multiple of 4
+        bx = min(bx, g.pitch - 4);
+        const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(src + (long long)y * g.pitch - PAD_LEFT + bx));
+        reinterpret_cast<uint32_t*>(in + r * BLUR_IN_P)[wi] = v;
+    }
+    __syncthreads();
+    // horizontal pass: 4 outputs per item
+    for (int idx = tid; idx < (BLUR_H + 6) * (BLUR_W / 4); idx += BLUR_T) {
+        const int r = idx / (BLUR_W / 4), q = idx - r * (BLUR_W / 4);
+        const uint8_t* p = in + r * BLUR_IN_P + 4 + 4 * q;  // p[0] = column x0 + 4q
+        int v[10];
+#pragma unroll
+        for (int k = 0; k < 10; k++) v[k] = p[k - 3];
+        uint16_t o[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+            o[j] = (uint16_t)(18 * (v[j] + v[j + 6]) + 34 * (v[j + 1] + v[j + 5]) + 48 * (v[j + 2] + v[j + 4]) + 56 * v[j + 3]);
+        uint2 pk;
+        pk.x = o[0] | ((uint32_t)o[1] << 16);
+        pk.y = o[2] | ((uint32_t)o[3] << 16);
+        *reinterpret_cast<uint2*>(hs + r * BLUR_W + 4 * q) = pk;
+    }
+    __syncthreads();
+    // vertical pass: 4 outputs (one aligned word) per item
+    for (int idx = tid; idx < BLUR_H * (BLUR_W / 4); idx += BLUR_T) {
+        const int r = idx / (BLUR_W / 4), q = idx - r * (BLUR_W / 4);
+        const int y = y0 + r, x = x0 + 4 * q;
+        if (y >= g.h || x >= g.w) continue;
+        uint32_t acc[4] = {0, 0, 0, 0};
+        constexpr int T[7] = {18, 34, 48, 56, 48, 34, 18};
+#pragma unroll
+        for (int k = 0; k < 7; k++) {
+            const uint2 pk = *reinterpret_cast<const uint2*>(hs + (r + k) * BLUR_W + 4 * q);
+            acc[0] += T[k] * (pk.x & 0xffff);
+            acc[1] += T[k] * (pk.x >> 16);
+            acc[2] += T[k] * (pk.y & 0xffff);
+            acc[3] += T[k] * (pk.y >> 16);
+        }
+        uint32_t out = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) out |= ((acc[j] + 32768u) >> 16) << (8 * j);
+        // the word may run up to 3 bytes past the interior into the (unused) frame area of the blurred plane
+        *reinterpret_cast<uint32_t*>(dst + (long long)y * g.pitch + x) = out;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// K6: steered BRIEF.  One warp per keypoint; lane i produces descriptor byte i (16 rotated samples).
+//   a = cosf(angle*factorPI), b = sinf(...) (glibc-exact), sample (x,y) -> (round(x*a - y*b), round(x*b + y*a))
+//   with unfused float arithmetic and round-half-even, read from the blurred level staged in shared memory.
+// Also finalises the keypoint record (level-0 coordinates, size, octave) and the per-frame count.
+// ------------------------------------------------------------------------------------------------------
+constexpr int DESC_WARPS = 4;
+constexpr int DESC_PP = 40;  // patch pitch: 37 + up to 3 alignment bytes
+
+__global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(Plan plan, Buffers buf, orbx_keypoint* outKps,
+                                                               uint8_t* outDesc, int* outCounts, int capacity)
+{
+    __shared__ __align__(16) uint8_t patch[DESC_WARPS][37 * DESC_PP];
+    const int frame = blockIdx.y;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int gidx = blockIdx.x * DESC_WARPS + wid;
+    const int* lc = buf.levelCount + frame * plan.nlevels;
+    int level = -1, j = 0, total = 0;
+    for (int l = 0; l < plan.nlevels; l++) {
+        const int c = lc[l];
+        if (level < 0 && gidx < total + c) { level = l; j = gidx - total; }
+        total += c;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) outCounts[frame] = min(total, capacity);
+    if (level < 0 || gidx >= capacity) return;
+    const LevelGeom& g = plan.lv[level];
+    const StagedKp kp = buf.staged[(long long)frame * plan.kpCapFrame + g.kpOff + j];
+    const int cx = (int)kp.x, cy = (int)kp.y;
+
+    // stage the 37x37 neighbourhood (max sample reach is 18 px) with aligned words
+    const uint8_t* img = interior_ptr(buf.blur, g, frame);
+    const int bcol0 = PAD_LEFT + cx - 18;
+    const int shift = bcol0 & 3;
+    const uint8_t* rowBase = img + (long long)(cy - 18) * g.pitch + (cx - 18 - shift);
+    uint8_t* P = patch[wid];
+    for (int idx = lane; idx < 37 * (DESC_PP / 4); idx += 32) {
+        const int r = idx / (DESC_PP / 4), wi = idx - r * (DESC_PP / 4);
+        reinterpret_cast<uint32_t*>(P + r * DESC_PP)[wi] =
+            __ldg(reinterpret_cast<const uint32_t*>(rowBase + (long long)r * g.pitch) + wi);
+    }
+    const float factorPI = 0.0174532924f;  // (float)(CV_PI/180.f)
+    const SinCosOut sc = sincosf_glibc(__fmul_rn(kp.angle, factorPI));
+    const float a = sc.c, b = sc.s;
+    // this lane's 16 pattern points
+    const int4 q0 = *reinterpret_cast<const int4*>(d_pattern + 32 * lane);
+    const int4 q1 = *reinterpret_cast<const int4*>(d_pattern + 32 * lane + 16);
+    const int words[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+    __syncwarp();
+    const uint8_t* center = P + 18 * DESC_PP + shift + 18;
+    int val = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const int wv = words[k];
+        const float x0 = (float)(signed char)(wv & 0xff), y0 = (float)(signed char)((wv >> 8) & 0xff);
+        const float x1 = (float)(signed char)((wv >> 16) & 0xff), y1 = (float)(signed char)((wv >> 24) & 0xff);
+        const int iy0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
+        const int ix0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
+        const int iy1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
+        const int ix1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
+        const int t0 = center[iy0 * DESC_PP + ix0], t1 = center[iy1 * DESC_PP + ix1];
+        val |= (t0 < t1) << k;
+    }
+    const long long o = (long long)frame * capacity + gidx;
+    outDesc[o * 32 + lane] = (uint8_t)val;
+    if (lane == 0) {
+        orbx_keypoint r;
+        r.x = level ? __fmul_rn(kp.x, g.scale) : kp.x;
+        r.y = level ? __fmul_rn(kp.y, g.scale) : kp.y;
+        r.size = (float)g.patchSize;
+        r.angle = kp.angle;
+        r.response = kp.response;
+        r.octave = level;
+        outKps[o] = r;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------------
+static inline int cv_round_f(float v) { return (int)lrintf(v); }
+static inline int cv_floor_f(float v) { int i = (int)v; return i - (v < (float)i); }
+static inline short sat_short(float v)
+{
+    int i = cv_round_f(v);
+    return (short)(i < -32768 ? -32768 : (i > 32767 ? 32767 : i));
+}
+
+}  // namespace orbx
+
+using namespace orbx;
+
+struct orbx_handle {
+    orbx_config cfg;
+    int device;
+    std::vector<float> scale, invScale, sigma2, invSigma2;
+    std::vector<int> quota;
+    cudaStream_t stream = nullptr, streamBlur = nullptr;
+    cudaEvent_t evFork = nullptr, evJoin = nullptr;
+    cudaEvent_t evStage[ORBX_NUM_STAGES + 1] = {};
+    // plan + arenas (valid for planRows x planCols, frameCap frames)
+    bool havePlan = false;
+    Plan plan;
+    int frameCap = 0;
+    Buffers buf = {};
+    uint8_t* dIn = nullptr;      // staged input frames (host API)
+    size_t dInBytes = 0;
+    void* dOut = nullptr;        // [counts | kps | desc] for the host API
+    size_t dOutBytes = 0;
+    void* hOut = nullptr;        // pinned mirror
+    size_t hOutBytes = 0;
+    short* dTabs = nullptr;
+    unsigned short* dKeyNode = nullptr;
+    int octNodeCap = 0, octKeySmemCap = 0;
+    size_t octSmem = 0;
+    int lastFrames = 0;
+    bool profiling = false;
+    bool useGraph = true;
+    float stageMs[ORBX_NUM_STAGES] = {};
+    int lastLaunches = 0;
+    // graph cache for the device-resident path: key = (n, in ptr, steps, out ptrs)
+    struct GraphKey { const void* in; long long step, fstride; void* kps; void* desc; void* counts; int n, cap; };
+    GraphKey gkey = {};
+    cudaGraphExec_t gexec = nullptr;
+    int glaunches = 0;
+};
+
+static void free_arenas(orbx_handle* h)
+{
+    cudaFree(h->buf.pyr); cudaFree(h->buf.blur); cudaFree(h->buf.cand); cudaFree(h->buf.candCount);
+    cudaFree(h->buf.candCountDbg); cudaFree(h->buf.staged); cudaFree(h->buf.levelCount); cudaFree(h->buf.errFlag);
+    cudaFree(h->dTabs); cudaFree(h->dKeyNode);
+    h->buf = Buffers{};
+    h->dTabs = nullptr; h->dKeyNode = nullptr;
+    if (h->gexec) { cudaGraphExecDestroy(h->gexec); h->gexec = nullptr; }
+    h->havePlan = false;
+    h->frameCap = 0;
+}
+
+// Level geometry, cell grids, capacities, resize tables for one image shape.
+struct TabInfo { long long nx, ny, nxw, nyw; };  // padded lengths of xofs / yofs and true lengths of the weight arrays
+
+static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<short>& tabs, long long& pyrBytesPerFrame,
+                      TabInfo* ti = nullptr)
+{
+    const orbx_config& c = h->cfg;
+    memset(&P, 0, sizeof P);
+    P.nlevels = c.nlevels; P.rows = rows; P.cols = cols; P.iniTh = c.ini_th_fast; P.minTh = c.min_th_fast;
+    long long planeOff = 0, candOff = 0;
+    int cellOff = 0, kpOff = 0;
+    // tables: per level >= 1: xofs[w], xw[2w], yofs0[h], yofs1[h], yw[2h] -- stored in 5 separate arrays
+    std::vector<short> xofs, xw, y0v, y1v, yw;
+    for (int l = 0; l < c.nlevels; l++) {
+        LevelGeom& g = P.lv[l];
+        g.w = cv_round_f((float)cols * h->invScale[l]);
+        g.h = cv_round_f((float)rows * h->invScale[l]);
+        if (g.w >= (1 << 15) || g.h >= (1 << 15) || (long long)g.w * g.h >= (1 << 24)) {
+            set_error("level %d is %dx%d: larger than the supported 2^24 pixels per level", l, g.w, g.h);
+            return ORBX_ERR_BAD_ARG;
+        }
+        const int minB = EDGE - 3;
+        g.maxBX = g.w - EDGE + 3; g.maxBY = g.h - EDGE + 3;
+        const float width = (float)(g.maxBX - minB), height = (float)(g.maxBY - minB);
+        g.nCols = (int)(width / 30.f); g.nRows = (int)(height / 30.f);
+        if (g.nCols < 1 || g.nRows < 1) {
+            set_error("level %d is %dx%d: smaller than one 30-px FAST cell inside the 16-px border", l, g.w, g.h);
+            return ORBX_ERR_TOO_SMALL;
+        }
+        g.wCell = (int)std::ceil(width / g.nCols); g.hCell = (int)std::ceil(height / g.nRows);
+        g.nIni = (int)std::round((float)(g.maxBX - minB) / (g.maxBY - minB));
+        if (g.nIni < 1) {
+            set_error("level %d is %dx%d: aspect ratio gives zero quad-tree roots", l, g.w, g.h);
+            return ORBX_ERR_TOO_SMALL;
+        }
+        g.hX = (float)(g.maxBX - minB) / g.nIni;
+        g.pitch = align_up(PAD_LEFT + g.w + EDGE, 128);
+        g.planeRows = g.h + 2 * EDGE;
+        g.planeBytes = (long long)g.pitch * g.planeRows;
+        g.planeOff = planeOff;  // finalised below once the frame capacity is known (layout [level][frame])
+        planeOff += g.planeBytes;
+        g.cellOff = cellOff; cellOff += g.nCols * g.nRows;
+        g.quota = h->quota[l];
+        const int evalW = g.maxBX - minB - 6, evalH = g.maxBY - minB - 6;
+        g.candCap = ((evalW + 1) / 2 + 1) * ((evalH + 1) / 2 + 1);
+        g.candOff = candOff; candOff += g.candCap;
+        g.nodeCap = std::max(g.quota + 3, 4 * g.nIni) + 1;
+        g.kpOff = kpOff; kpOff += g.nodeCap;
+        g.scale = h->scale[l];
+        g.patchSize = (int)(31 * h->scale[l]);
+        g.xTab = (int)xofs.size(); g.yTab = (int)y0v.size();
+        if (l > 0) {
+            const LevelGeom& gp = P.lv[l - 1];
+            // cv::resize INTER_LINEAR coefficient tables (see oracle/cvprim.h: linear_coeffs)
+            {
+                double scale = 1.0 / ((double)g.w / gp.w);
+                for (int d = 0; d < g.w; d++) {
+                    float f = (float)((d + 0.5) * scale - 0.5);
+                    int s = cv_floor_f(f);
+                    f -= s;
+                    if (s < 0) { f = 0; s = 0; }
+                    if (s >= gp.w - 1) { f = 0; s = gp.w - 1; }
+                    xofs.push_back((short)s);
+                    xw.push_back(sat_short((1.f - f) * 2048)); xw.push_back(sat_short(f * 2048));
+                }
+            }
+            {
+                double scale = 1.0 / ((double)g.h / gp.h);
+                for (int d = 0; d < g.h; d++) {
+                    float f = (float)((d + 0.5) * scale - 0.5);
+                    int s = cv_floor_f(f);
+                    f -= s;
+                    auto clip = [&](int x) { return x >= 0 ? (x < gp.h ? x : gp.h - 1) : 0; };
+                    y0v.push_back((short)clip(s)); y1v.push_back((short)clip(s + 1));
+                    yw.push_back(sat_short((1.f - f) * 2048)); yw.push_back(sat_short(f * 2048));
+                }
+            }
+        }
+    }
+    P.totalCells = cellOff;
+    P.kpCapFrame = kpOff;
+    P.candFrame = candOff;
+    pyrBytesPerFrame = planeOff;
+    // pack tables: [xofs | y0 | y1 | xw | yw] with 4-byte alignment for the short2 parts
+    auto pad2 = [](std::vector<short>& v) { if (v.size() & 1) v.push_back(0); };
+    pad2(xofs); pad2(y0v); pad2(y1v);
+    tabs.clear();
+    tabs.insert(tabs.end(), xofs.begin(), xofs.end());
+    tabs.insert(tabs.end(), y0v.begin(), y0v.end());
+    tabs.insert(tabs.end(), y1v.begin(), y1v.end());
+    tabs.insert(tabs.end(), xw.begin(), xw.end());
+    tabs.insert(tabs.end(), yw.begin(), yw.end());
+    if (ti) *ti = TabInfo{(long long)xofs.size(), (long long)y0v.size(), (long long)xw.size(), (long long)yw.size()};
+    P.pyrFrameStride = pyrBytesPerFrame;
+    return ORBX_OK;
+}
+
+static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
+{
+    if (h->havePlan && h->plan.rows == rows && h->plan.cols == cols && frames <= h->frameCap) return ORBX_OK;
+    ORBX_CUDA_TRY(cudaSetDevice(h->device));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(h->streamBlur));
+    Plan P;
+    std::vector<short> tabs;
+    long long pyrPerFrame = 0;
+    TabInfo ti;
+    int rc = build_plan(h, rows, cols, P, tabs, pyrPerFrame, &ti);
+    if (rc != ORBX_OK) return rc;
+    const int cap = std::max(frames, (h->havePlan && h->plan.rows == rows && h->plan.cols == cols) ? h->frameCap : 0);
+    free_arenas(h);
+    // layout [level][frame]: level l starts at cap * (sum of planeBytes of lower levels)
+    for (int l = 0; l < P.nlevels; l++) P.lv[l].planeOff *= cap;
+    Buffers B = {};
+    B.frames = cap;
+    const size_t pyrBytes = (size_t)pyrPerFrame * cap + 256;
+    ORBX_CUDA_TRY(cudaMalloc(&B.pyr, pyrBytes));
+    ORBX_CUDA_TRY(cudaMalloc(&B.blur, pyrBytes));
+    ORBX_CUDA_TRY(cudaMemsetAsync(B.pyr, 0, pyrBytes, h->stream));
+    ORBX_CUDA_TRY(cudaMemsetAsync(B.blur, 0, pyrBytes, h->stream));
+    ORBX_CUDA_TRY(cudaMalloc(&B.cand, sizeof(Cand) * (size_t)P.candFrame * cap));
+    ORBX_CUDA_TRY(cudaMalloc(&B.candCount, sizeof(int) * (size_t)P.nlevels * cap));
+    ORBX_CUDA_TRY(cudaMalloc(&B.candCountDbg, sizeof(int) * (size_t)P.nlevels * cap));
+    ORBX_CUDA_TRY(cudaMemsetAsync(B.candCount, 0, sizeof(int) * (size_t)P.nlevels * cap, h->stream));
+    ORBX_CUDA_TRY(cudaMemsetAsync(B.candCountDbg, 0, sizeof(int) * (size_t)P.nlevels * cap, h->stream));
+    ORBX_CUDA_TRY(cudaMalloc(&B.staged, sizeof(StagedKp) * (size_t)P.kpCapFrame * cap));
+    ORBX_CUDA_TRY(cudaMalloc(&B.levelCount, sizeof(int) * (size_t)P.nlevels * cap));
+    ORBX_CUDA_TRY(cudaMemsetAsync(B.levelCount, 0, sizeof(int) * (size_t)P.nlevels * cap, h->stream));
+    ORBX_CUDA_TRY(cudaMalloc(&B.errFlag, sizeof(int)));
+    ORBX_CUDA_TRY(cudaMemsetAsync(B.errFlag, 0, sizeof(int), h->stream));
+    ORBX_CUDA_TRY(cudaMalloc(&h->dTabs, sizeof(short) * std::max<size_t>(tabs.size(), 2)));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(h->dTabs, tabs.data(), sizeof(short) * tabs.size(), cudaMemcpyHostToDevice, h->stream));
+    // xw / yw hold 2 shorts per destination column / row, indexed by xTab + dx / yTab + dy
+    B.xofs = h->dTabs;
+    B.yofs0 = h->dTabs + ti.nx;
+    B.yofs1 = h->dTabs + ti.nx + ti.ny;
+    B.xw = reinterpret_cast<const short2*>(h->dTabs + ti.nx + 2 * ti.ny);
+    B.yw = reinterpret_cast<const short2*>(h->dTabs + ti.nx + 2 * ti.ny + ti.nxw);
+    // quad-tree kernel shared memory
+    int nodeCapMax = 0, candCapMax = 0;
+    for (int l = 0; l < P.nlevels; l++) { nodeCapMax = std::max(nodeCapMax, P.lv[l].nodeCap); candCapMax = std::max(candCapMax, P.lv[l].candCap); }
+    nodeCapMax = align_up(nodeCapMax, 8);
+    if (nodeCapMax > 16000) {
+        set_error("per-level feature quota %d exceeds the quad-tree kernel's node capacity", nodeCapMax);
+        return ORBX_ERR_BAD_ARG;
+    }
+    const size_t perNode = 8 + 8 + 4 + 4 + 16 + 4 + 4 + 4 + 4 + 8 + 2 + 2 + 2 + 2 + 2 + 2;
+    const size_t nodeBytes = perNode * nodeCapMax + 16 * 16;
+    int devSmem = 0;
+    ORBX_CUDA_TRY(cudaDeviceGetAttribute(&devSmem, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
+    if (nodeBytes + 1024 > (size_t)devSmem) {
+        set_error("quad-tree node arrays (%zu B) exceed shared memory (%d B)", nodeBytes, devSmem);
+        return ORBX_ERR_BAD_ARG;
+    }
+    // keys in shared memory when they fit in what is left, capped so that several CTAs stay resident
+    size_t keyBudget = std::min<size_t>((size_t)devSmem - nodeBytes - 1024, 64 * 1024);
+    int keyCap = (int)std::min<size_t>(keyBudget / 2, (size_t)candCapMax);
+    keyCap &= ~7;
+    h->octNodeCap = nodeCapMax;
+    h->octKeySmemCap = keyCap;
+    h->octSmem = nodeBytes + 2 * (size_t)keyCap + 16;
+    ORBX_CUDA_TRY(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->octSmem));
+    ORBX_CUDA_TRY(cudaMalloc(&h->dKeyNode, sizeof(unsigned short) * (size_t)P.candFrame * cap));
+    h->plan = P;
+    h->buf = B;
+    h->frameCap = cap;
+    h->havePlan = true;
+    return ORBX_OK;
+}
+
+// Enqueue every kernel of one batch on h->stream (+ the blur branch on h->streamBlur).
+static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long long inFrameStride, int n,
+                   orbx_keypoint* dKps, uint8_t* dDesc, int* dCounts, int capacity, bool profile, int* launches)
+{
+    const Plan& P = h->plan;
+    Buffers B = h->buf;
+    cudaStream_t s = h->stream, sb = profile ? h->stream : h->streamBlur;
+    int nl = 0;
+    if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_PYRAMID], s));
+    {
+        const LevelGeom& g = P.lv[0];
+        dim3 grid((g.pitch / 4 + 127) / 128, g.planeRows, n);
+        k_level0<<<grid, 128, 0, s>>>(P, B, dIn, inStep, inFrameStride);
+        nl++;
+    }
+    for (int l = 1; l < P.nlevels; l++) {
+        const LevelGeom& g = P.lv[l];
+        dim3 grid((g.pitch / 4 + 127) / 128, g.planeRows, n);
+        k_resize<<<grid, 128, 0, s>>>(P, B, l);
+        nl++;
+    }
+    if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_FAST], s));
+    if (!profile) {
+        ORBX_CUDA_TRY(cudaEventRecord(h->evFork, s));
+        ORBX_CUDA_TRY(cudaStreamWaitEvent(sb, h->evFork, 0));
+    }
+    k_fast_cells<<<dim3(P.totalCells, n), FAST_T, 0, s>>>(P, B);
+    nl++;
+    if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_OCTREE], s));
+    k_octree<<<dim3(P.nlevels, n), OCT_T, h->octSmem, s>>>(P, B, h->octNodeCap, h->octKeySmemCap, h->dKeyNode, P.candFrame);
+    nl++;
+    if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_BLUR], s));
+    for (int l = 0; l < P.nlevels; l++) {
+        const LevelGeom& g = P.lv[l];
+        const int tx = (g.w + BLUR_W - 1) / BLUR_W, ty = (g.h + BLUR_H - 1) / BLUR_H;
+        k_blur<<<dim3(tx * ty, 1, n), BLUR_T, 0, sb>>>(P, B, l, tx);
+        nl++;
+    }
+    if (!profile) {
+        ORBX_CUDA_TRY(cudaEventRecord(h->evJoin, sb));
+        ORBX_CUDA_TRY(cudaStreamWaitEvent(s, h->evJoin, 0));
+    }
+    if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_DESC], s));
+    k_describe<<<dim3((capacity + DESC_WARPS - 1) / DESC_WARPS, n), DESC_WARPS * 32, 0, s>>>(P, B, dKps, dDesc, dCounts, capacity);
+    nl++;
+    if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_D2H], s));
+    ORBX_CUDA_TRY(cudaGetLastError());
+    if (launches) *launches = nl;
+    return ORBX_OK;
+}
+
+extern "C" {
+
+const char* orbx_last_error(void) { return last_error().c_str(); }
+
+int orbx_device_count(void)
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) { set_error("cudaGetDeviceCount: %s", cudaGetErrorString(e)); return ORBX_ERR_NO_DEVICE; }
+    return n;
+}
+
+int orbx_create(const orbx_config* cfg, int device, orbx_handle** out)
+{
+    if (!cfg || !out) { set_error("orbx_create: null argument"); return ORBX_ERR_BAD_ARG; }
+    if (cfg->nlevels < 1 || cfg->nlevels > ORBX_MAX_LEVELS || cfg->nfeatures < 0 || !(cfg->scale_factor > 1.0f) ||
+        cfg->ini_th_fast < 0 || cfg->min_th_fast < 0 || cfg->ini_th_fast > 255 || cfg->min_th_fast > 255) {
+        set_error("orbx_create: unsupported configuration (nlevels 1..%d, scale_factor > 1, thresholds 0..255)", ORBX_MAX_LEVELS);
+        return ORBX_ERR_BAD_ARG;
+    }
+    int ndev = orbx_device_count();
+    if (ndev <= 0) { if (ndev == 0) set_error("no CUDA device"); return ORBX_ERR_NO_DEVICE; }
+    if (device < 0 || device >= ndev) { set_error("device %d out of range (%d devices)", device, ndev); return ORBX_ERR_BAD_ARG; }
+    orbx_handle* h = new orbx_handle;
+    h->cfg = *cfg;
+    h->device = device;
+    const int nl = cfg->nlevels;
+    // src/ORBextractor.cc:445-500
+    h->scale.resize(nl); h->invScale.resize(nl); h->sigma2.resize(nl); h->invSigma2.resize(nl); h->quota.resize(nl);
+    h->scale[0] = 1.f; h->sigma2[0] = 1.f;
+    for (int i = 1; i < nl; i++) { h->scale[i] = h->scale[i - 1] * cfg->scale_factor; h->sigma2[i] = h->scale[i] * h->scale[i]; }
+    for (int i = 0; i < nl; i++) { h->invScale[i] = 1.f / h->scale[i]; h->invSigma2[i] = 1.f / h->sigma2[i]; }
+    float factor = 1.f / cfg->scale_factor;
+    float want = cfg->nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)nl));
+    int sum = 0;
+    for (int l = 0; l < nl - 1; l++) { h->quota[l] = cv_round_f(want); sum += h->quota[l]; want *= factor; }
+    h->quota[nl - 1] = std::max(cfg->nfeatures - sum, 0);
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->streamBlur, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->evFork, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->evJoin, cudaEventDisableTiming);
+    for (int i = 0; i <= ORBX_NUM_STAGES && e == cudaSuccess; i++) e = cudaEventCreate(&h->evStage[i]);
+    if (e != cudaSuccess) {
+        set_error("orbx_create: %s", cudaGetErrorString(e));
+        delete h;
+        return ORBX_ERR_CUDA;
+    }
+    *out = h;
+    return ORBX_OK;
+}
+
+void orbx_destroy(orbx_handle* h)
+{
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->streamBlur) cudaStreamSynchronize(h->streamBlur);
+    free_arenas(h);
+    cudaFree(h->dIn); cudaFree(h->dOut);
+    if (h->hOut) cudaFreeHost(h->hOut);
+    for (auto& ev : h->evStage) if (ev) cudaEventDestroy(ev);
+    if (h->evFork) cudaEventDestroy(h->evFork);
+    if (h->evJoin) cudaEventDestroy(h->evJoin);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    if (h->streamBlur) cudaStreamDestroy(h->streamBlur);
+    delete h;
+}
+
+int orbx_get_tables(const orbx_handle* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2, int* fpl)
+{
+    if (!h) { set_error("null handle"); return ORBX_ERR_BAD_ARG; }
+    const int nl = h->cfg.nlevels;
+    if (scale) std::copy(h->scale.begin(), h->scale.end(), scale);
+    if (inv_scale) std::copy(h->invScale.begin(), h->invScale.end(), inv_scale);
+    if (sigma2) std::copy(h->sigma2.begin(), h->sigma2.end(), sigma2);
+    if (inv_sigma2) std::copy(h->invSigma2.begin(), h->invSigma2.end(), inv_sigma2);
+    if (fpl) std::copy(h->quota.begin(), h->quota.end(), fpl);
+    (void)nl;
+    return ORBX_OK;
+}
+
+int orbx_max_keypoints(orbx_handle* h, int rows, int cols)
+{
+    if (!h || rows <= 0 || cols <= 0) { set_error("orbx_max_keypoints: bad argument"); return ORBX_ERR_BAD_ARG; }
+    Plan P;
+    std::vector<short> tabs;
+    long long per = 0;
+    int rc = build_plan(h, rows, cols, P, tabs, per);
+    if (rc != ORBX_OK) return rc;
+    return P.kpCapFrame;
+}
+
+int orbx_sync(orbx_handle* h)
+{
+    if (!h) { set_error("null handle"); return ORBX_ERR_BAD_ARG; }
+    ORBX_CUDA_TRY(cudaSetDevice(h->device));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+    int err = 0;
+    if (h->havePlan) {
+        ORBX_CUDA_TRY(cudaMemcpy(&err, h->buf.errFlag, sizeof(int), cudaMemcpyDeviceToHost));
+        if (err) { set_error("candidate list overflow on device"); return ORBX_ERR_CAPACITY; }
+    }
+    return ORBX_OK;
+}
+
+void* orbx_stream(orbx_handle* h) { return h ? (void*)h->stream : nullptr; }
+
+int orbx_extract_batch_device(orbx_handle* h, const uint8_t* d_imgs, int n, int rows, int cols, size_t step,
+                              size_t frame_stride, orbx_keypoint* d_kps, uint8_t* d_desc, int capacity, int* d_counts)
+{
+    if (!h || !d_imgs || !d_kps || !d_desc || !d_counts || n <= 0 || rows <= 0 || cols <= 0 || step < (size_t)cols || capacity <= 0) {
+        set_error("orbx_extract_batch_device: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    ORBX_CUDA_TRY(cudaSetDevice(h->device));
+    int rc = ensure_plan(h, rows, cols, n);
+    if (rc != ORBX_OK) return rc;
+    h->lastFrames = n;
+    if (h->profiling || !h->useGraph) {
+        rc = enqueue(h, d_imgs, (long long)step, (long long)frame_stride, n, d_kps, d_desc, d_counts, capacity, h->profiling, &h->lastLaunches);
+        if (rc != ORBX_OK) return rc;
+        if (h->profiling) {
+            ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+            for (int sgi = ORBX_STAGE_PYRAMID; sgi <= ORBX_STAGE_DESC; sgi++)
+                ORBX_CUDA_TRY(cudaEventElapsedTime(&h->stageMs[sgi], h->evStage[sgi], h->evStage[sgi + 1]));
+        }
+        return ORBX_OK;
+    }
+    orbx_handle::GraphKey k = {d_imgs, (long long)step, (long long)frame_stride, d_kps, d_desc, d_counts, n, capacity};
+    if (!h->gexec || memcmp(&k, &h->gkey, sizeof k) != 0) {
+        if (h->gexec) { cudaGraphExecDestroy(h->gexec); h->gexec = nullptr; }
+        cudaGraph_t graph = nullptr;
+        ORBX_CUDA_TRY(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+        rc = enqueue(h, d_imgs, (long long)step, (long long)frame_stride, n, d_kps, d_desc, d_counts, capacity, false, &h->glaunches);
+        cudaError_t e = cudaStreamEndCapture(h->stream, &graph);
+        if (rc != ORBX_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+        if (e != cudaSuccess) { set_error("cudaStreamEndCapture: %s", cudaGetErrorString(e)); return ORBX_ERR_CUDA; }
+        e = cudaGraphInstantiate(&h->gexec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (e != cudaSuccess) { set_error("cudaGraphInstantiate: %s", cudaGetErrorString(e)); h->gexec = nullptr; return ORBX_ERR_CUDA; }
+        h->gkey = k;
+    }
+    ORBX_CUDA_TRY(cudaGraphLaunch(h->gexec, h->stream));
+    h->lastLaunches = h->glaunches;
+    return ORBX_OK;
+}
+
+int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int cols, size_t step, size_t frame_stride,
+                       orbx_keypoint* kps, uint8_t* desc, int capacity, int* counts)
+{
+    if (!h || !imgs || !kps || !desc || !counts || n <= 0 || rows <= 0 || cols <= 0 || step < (size_t)cols || capacity <= 0) {
+        set_error("orbx_extract_batch: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    ORBX_CUDA_TRY(cudaSetDevice(h->device));
+    int rc = ensure_plan(h, rows, cols, n);
+    if (rc != ORBX_OK) return rc;
+    if (capacity < h->plan.kpCapFrame) {
+        set_error("orbx_extract_batch: capacity %d < orbx_max_keypoints() = %d", capacity, h->plan.kpCapFrame);
+        return ORBX_ERR_CAPACITY;
+    }
+    const int devCap = h->plan.kpCapFrame;
+    // device staging for input and packed output [counts | kps | desc]
+    const size_t inBytes = (size_t)n * rows * cols;
+    if (inBytes > h->dInBytes) {
+        ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+        cudaFree(h->dIn); h->dIn = nullptr; h->dInBytes = 0;
+        ORBX_CUDA_TRY(cudaMalloc(&h->dIn, inBytes));
+        h->dInBytes = inBytes;
+    }
+    const size_t cntBytes = ((size_t)n * sizeof(int) + 255) & ~size_t(255);
+    const size_t kpBytes = ((size_t)n * devCap * sizeof(orbx_keypoint) + 255) & ~size_t(255);
+    const size_t dsBytes = (size_t)n * devCap * 32;
+    const size_t outBytes = cntBytes + kpBytes + dsBytes;
+    if (outBytes > h->dOutBytes) {
+        ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+        cudaFree(h->dOut); h->dOut = nullptr; h->dOutBytes = 0;
+        if (h->hOut) { cudaFreeHost(h->hOut); h->hOut = nullptr; }
+        ORBX_CUDA_TRY(cudaMalloc(&h->dOut, outBytes));
+        ORBX_CUDA_TRY(cudaMallocHost(&h->hOut, outBytes));
+        h->dOutBytes = outBytes;
+        h->hOutBytes = outBytes;
+    }
+    if (h->profiling) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_H2D], h->stream));
+    if (step == (size_t)cols && frame_stride == (size_t)rows * cols) {
+        ORBX_CUDA_TRY(cudaMemcpyAsync(h->dIn, imgs, inBytes, cudaMemcpyHostToDevice, h->stream));
+    } else {
+        for (int i = 0; i < n; i++)
+            ORBX_CUDA_TRY(cudaMemcpy2DAsync(h->dIn + (size_t)i * rows * cols, cols, imgs + (size_t)i * frame_stride, step, cols, rows,
+                                            cudaMemcpyHostToDevice, h->stream));
+    }
+    int* dCounts = (int*)h->dOut;
+    orbx_keypoint* dKps = (orbx_keypoint*)((char*)h->dOut + cntBytes);
+    uint8_t* dDesc = (uint8_t*)h->dOut + cntBytes + kpBytes;
+    rc = orbx_extract_batch_device(h, h->dIn, n, rows, cols, (size_t)cols, (size_t)rows * cols, dKps, dDesc, devCap, dCounts);
+    if (rc != ORBX_OK) return rc;
+    ORBX_CUDA_TRY(cudaMemcpyAsync(h->hOut, h->dOut, outBytes, cudaMemcpyDeviceToHost, h->stream));
+    if (h->profiling) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_NUM_STAGES], h->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+    if (h->profiling) {
+        ORBX_CUDA_TRY(cudaEventElapsedTime(&h->stageMs[ORBX_STAGE_H2D], h->evStage[ORBX_STAGE_H2D], h->evStage[ORBX_STAGE_PYRAMID]));
+        ORBX_CUDA_TRY(cudaEventElapsedTime(&h->stageMs[ORBX_STAGE_D2H], h->evStage[ORBX_STAGE_D2H], h->evStage[ORBX_NUM_STAGES]));
+    }
+    const int* hc = (const int*)h->hOut;
+    const orbx_keypoint* hk = (const orbx_keypoint*)((const char*)h->hOut + cntBytes);
+    const uint8_t* hd = (const uint8_t*)h->hOut + cntBytes + kpBytes;
+    for (int i = 0; i < n; i++) {
+        const int c = hc[i];
+        counts[i] = c;
+        memcpy(kps + (size_t)i * capacity, hk + (size_t)i * devCap, sizeof(orbx_keypoint) * c);
+        memcpy(desc + (size_t)i * capacity * 32, hd + (size_t)i * devCap * 32, (size_t)32 * c);
+    }
+    int err = 0;
+    ORBX_CUDA_TRY(cudaMemcpy(&err, h->buf.errFlag, sizeof(int), cudaMemcpyDeviceToHost));
+    if (err) { set_error("candidate list overflow on device"); return ORBX_ERR_CAPACITY; }
+    return ORBX_OK;
+}
+
+int orbx_extract(orbx_handle* h, const uint8_t* img, int rows, int cols, size_t step, orbx_keypoint* kps, uint8_t* desc,
+                 int capacity, int* count)
+{
+    return orbx_extract_batch(h, img, 1, rows, cols, step, step * (size_t)rows, kps, desc, capacity, count);
+}
+
+int orbx_get_level_size(orbx_handle* h, int level, int* rows_l, int* cols_l)
+{
+    if (!h || !h->havePlan || level < 0 || level >= h->cfg.nlevels) { set_error("orbx_get_level_size: no plan / bad level"); return ORBX_ERR_BAD_ARG; }
+    if (rows_l) *rows_l = h->plan.lv[level].h;
+    if (cols_l) *cols_l = h->plan.lv[level].w;
+    return ORBX_OK;
+}
+
+int orbx_get_pyramid_level(orbx_handle* h, int frame, int level, uint8_t* dst, size_t dst_step)
+{
+    if (!h || !h->havePlan || !dst || level < 0 || level >= h->cfg.nlevels || frame < 0 || frame >= h->lastFrames) {
+        set_error("orbx_get_pyramid_level: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    const LevelGeom& g = h->plan.lv[level];
+    if (dst_step < (size_t)(g.w + 2 * EDGE)) { set_error("dst_step too small"); return ORBX_ERR_CAPACITY; }
+    ORBX_CUDA_TRY(cudaSetDevice(h->device));
+    const uint8_t* src = h->buf.pyr + g.planeOff + (long long)frame * g.planeBytes + (PAD_LEFT - EDGE);
+    ORBX_CUDA_TRY(cudaMemcpy2DAsync(dst, dst_step, src, g.pitch, g.w + 2 * EDGE, g.planeRows, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return ORBX_OK;
+}
+
+int orbx_set_profiling(orbx_handle* h, int on)
+{
+    if (!h) return ORBX_ERR_BAD_ARG;
+    h->profiling = on != 0;
+    return ORBX_OK;
+}
+int orbx_set_use_graph(orbx_handle* h, int on)
+{
+    if (!h) return ORBX_ERR_BAD_ARG;
+    h->useGraph = on != 0;
+    return ORBX_OK;
+}
+int orbx_stage_times(orbx_handle* h, float* ms)
+{
+    if (!h || !ms) return ORBX_ERR_BAD_ARG;
+    for (int i = 0; i < ORBX_NUM_STAGES; i++) ms[i] = h->stageMs[i];
+    return ORBX_OK;
+}
+int orbx_last_launch_count(orbx_handle* h) { return h ? h->lastLaunches : ORBX_ERR_BAD_ARG; }
+
+int orbx_debug_get_candidates(orbx_handle* h, int frame, int level, int* xyr, int cap, int* n)
+{
+    if (!h || !h->havePlan || !n || level < 0 || level >= h->cfg.nlevels || frame < 0 || frame >= h->lastFrames) {
+        set_error("orbx_debug_get_candidates: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    ORBX_CUDA_TRY(cudaSetDevice(h->device));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+    int m = 0;
+    ORBX_CUDA_TRY(cudaMemcpy(&m, h->buf.candCountDbg + frame * h->plan.nlevels + level, sizeof(int), cudaMemcpyDeviceToHost));
+    *n = m;
+    if (!xyr || cap <= 0) return ORBX_OK;
+    const int k = std::min(m, cap);
+    std::vector<Cand> tmp(k);
+    const LevelGeom& g = h->plan.lv[level];
+    if (k) ORBX_CUDA_TRY(cudaMemcpy(tmp.data(), h->buf.cand + (long long)frame * h->plan.candFrame + g.candOff, sizeof(Cand) * k, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < k; i++) {
+        xyr[3 * i] = (int)(tmp[i].xy & 0xffff) + 16;
+        xyr[3 * i + 1] = (int)(tmp[i].xy >> 16) + 16;
+        xyr[3 * i + 2] = (int)(tmp[i].ro >> 24);
+    }
+    return ORBX_OK;
+}
+
+int orbx_debug_get_blurred(orbx_handle* h, int frame, int level, uint8_t* dst)
+{
+    if (!h || !h->havePlan || !dst || level < 0 || level >= h->cfg.nlevels || frame < 0 || frame >= h->lastFrames) {
+        set_error("orbx_debug_get_blurred: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    const LevelGeom& g = h->plan.lv[level];
+    ORBX_CUDA_TRY(cudaSetDevice(h->device));
+    const uint8_t* src = h->buf.blur + g.planeOff + (long long)frame * g.planeBytes + (long long)PAD_TOP * g.pitch + PAD_LEFT;
+    ORBX_CUDA_TRY(cudaMemcpy2DAsync(dst, g.w, src, g.pitch, g.w, g.h, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return ORBX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,731 @@
+// orbx_match.cu -- B200 (sm_100a) Hamming matchers behind the orbm_* C-ABI (include/orbx.h).
+//
+//   k_bruteforce / k_merge_partials   brute-force best / second-best over a descriptor database (north_star (6),
+//                                     config 5), distance = ORBmatcher::DescriptorDistance src/ORBmatcher.cc:1983-2003
+//   k_proj_search                     ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th)
+//                                     src/ORBmatcher.cc:61-183 + Frame::GetFeaturesInArea src/Frame.cc:488-548
+//   k_stereo_rows                     coarse search of Frame::ComputeStereoMatches src/Frame.cc:684-765
+//   k_bow_nodes / k_bow_rotation      ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...) src/ORBmatcher.cc:228-392,
+//                                     ComputeThreeMaxima :1935-1977
+// 256-bit distances are 8 x (LOP3 xor, POPC) on the integer pipe; best / second-best selection is a min over packed
+// (distance, order) keys, reduced across lanes with warp shuffles.  sm_100a has no native b1 AND-POPC MMA
+// (SURVEY.md F10), so there is no tensor-core variant.
+#include "orbx_common.cuh"
+#include <cooperative_groups.h>
+#include <algorithm>
+#include <vector>
+
+namespace cg = cooperative_groups;
+
+namespace orbx {
+
+constexpr int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;
+constexpr int GRID_COLS = 64, GRID_ROWS = 48;
+
+struct Desc { uint32_t w[8]; };
+
+__device__ __forceinline__ Desc load_desc(const uint8_t* p)
+{
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(p));
+    const uint4 b = __ldg(reinterpret_cast<const uint4*>(p) + 1);
+    Desc d;
+    d.w[0] = a.x; d.w[1] = a.y; d.w[2] = a.z; d.w[3] = a.w;
+    d.w[4] = b.x; d.w[5] = b.y; d.w[6] = b.z; d.w[7] = b.w;
+    return d;
+}
+__device__ __forceinline__ int hamming(const Desc& a, const Desc& b)
+{
+    int d = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) d += __popc(a.w[i] ^ b.w[i]);
+    return d;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// K7a: brute force.  CTA = 256 threads x BF_RQ queries in registers; the database chunk of the CTA streams through
+// shared memory in tiles and is read with broadcast 128-bit loads.  Per (query, chunk): packed best key
+// (dist << 22 | local index) and second-best distance.  Chunks are merged in index order by k_merge_partials, which
+// reproduces the sequential scan (first minimum wins, second = second smallest of the multiset).
+// ------------------------------------------------------------------------------------------------------
+constexpr int BF_T = 256;
+constexpr int BF_RQ = 4;
+constexpr int BF_TILE = 256;  // descriptors per shared-memory tile (8 KB)
+constexpr int BF_IDX_BITS = 22;
+
+__global__ void __launch_bounds__(BF_T) k_bruteforce(const uint8_t* __restrict__ q, int nq, const uint8_t* __restrict__ db,
+                                                     int ndb, int chunk, int idxOffset, int32_t* __restrict__ pBest,
+                                                     int32_t* __restrict__ pIdx, int32_t* __restrict__ pSecond)
+{
+    __shared__ __align__(16) uint4 tile[BF_TILE * 2];
+    const int c0 = blockIdx.x * chunk, c1 = min(c0 + chunk, ndb);
+    const int qBase = blockIdx.y * (BF_T * BF_RQ);
+    Desc Q[BF_RQ];
+    uint32_t best[BF_RQ], second[BF_RQ];
+#pragma unroll
+    for (int r = 0; r < BF_RQ; r++) {
+        const int qi = qBase + r * BF_T + threadIdx.x;
+        if (qi < nq) Q[r] = load_desc(q + 32 * (size_t)qi);
+        else {
+#pragma unroll
+            for (int i = 0; i < 8; i++) Q[r].w[i] = 0;
+        }
+        best[r] = (256u << BF_IDX_BITS) | ((1u << BF_IDX_BITS) - 1);
+        second[r] = 256u << BF_IDX_BITS;
+    }
+    for (int t0 = c0; t0 < c1; t0 += BF_TILE) {
+        const int nt = min(BF_TILE, c1 - t0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < nt * 2; i += BF_T)
+            tile[i] = __ldg(reinterpret_cast<const uint4*>(db + 32 * (size_t)t0) + i);
+        __syncthreads();
+        const uint32_t jBase = (uint32_t)(t0 - c0);
+#pragma unroll 2
+        for (int j = 0; j < nt; j++) {
+            const uint4 a = tile[2 * j], b = tile[2 * j + 1];
+#pragma unroll
+            for (int r = 0; r < BF_RQ; r++) {
+                const int d = __popc(Q[r].w[0] ^ a.x) + __popc(Q[r].w[1] ^ a.y) + __popc(Q[r].w[2] ^ a.z) +
+                              __popc(Q[r].w[3] ^ a.w) + __popc(Q[r].w[4] ^ b.x) + __popc(Q[r].w[5] ^ b.y) +
+                              __popc(Q[r].w[6] ^ b.z) + __popc(Q[r].w[7] ^ b.w);
+                const uint32_t key = ((uint32_t)d << BF_IDX_BITS) | (jBase + j);
+                second[r] = min(second[r], max(key, best[r]));
+                best[r] = min(best[r], key);
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < BF_RQ; r++) {
+        const int qi = qBase + r * BF_T + threadIdx.x;
+        if (qi >= nq) continue;
+        const size_t o = (size_t)blockIdx.x * nq + qi;
+        const int bd = best[r] >> BF_IDX_BITS;
+        pBest[o] = bd;
+        pIdx[o] = bd < 256 || c1 > c0 ? (int)(best[r] & ((1u << BF_IDX_BITS) - 1)) + c0 + idxOffset : -1;
+        pSecond[o] = min((int)(second[r] >> BF_IDX_BITS), 256);
+    }
+}
+
+// sequential-scan-equivalent merge of partials ordered by ascending index range
+__global__ void k_merge_partials(const int32_t* __restrict__ pBest, const int32_t* __restrict__ pIdx,
+                                 const int32_t* __restrict__ pSecond, int nparts, int nq, int32_t* __restrict__ oBest,
+                                 int32_t* __restrict__ oIdx, int32_t* __restrict__ oSecond)
+{
+    const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (qi >= nq) return;
+    int b = 256, s = 256, id = -1;
+    for (int p = 0; p < nparts; p++) {
+        const size_t o = (size_t)p * nq + qi;
+        const int pb = pBest[o], ps = pSecond[o], pi = pIdx[o];
+        if (pi < 0) continue;  // empty part
+        if (pb < b) { s = min(b, ps); b = pb; id = pi; }
+        else s = min(s, pb);
+    }
+    oBest[qi] = b; oIdx[qi] = id; oSecond[qi] = s;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// two-smallest tracking on packed keys (dist << 20 | visit order) with a payload for the best entry
+// ------------------------------------------------------------------------------------------------------
+struct Top2 {
+    uint32_t k1, k2;  // smallest and second smallest key
+    int p1, p2;       // payloads
+};
+__device__ __forceinline__ void top2_init(Top2& t) { t.k1 = t.k2 = 0xFFFFFFFFu; t.p1 = t.p2 = -1; }
+__device__ __forceinline__ void top2_push(Top2& t, uint32_t k, int p)
+{
+    if (k < t.k1) { t.k2 = t.k1; t.p2 = t.p1; t.k1 = k; t.p1 = p; }
+    else if (k < t.k2) { t.k2 = k; t.p2 = p; }
+}
+__device__ __forceinline__ void top2_warp_reduce(Top2& t)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const uint32_t ok1 = __shfl_xor_sync(0xffffffffu, t.k1, o), ok2 = __shfl_xor_sync(0xffffffffu, t.k2, o);
+        const int op1 = __shfl_xor_sync(0xffffffffu, t.p1, o), op2 = __shfl_xor_sync(0xffffffffu, t.p2, o);
+        top2_push(t, ok1, op1);
+        top2_push(t, ok2, op2);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// K7b: SearchByProjection(Frame, MapPoints, th).  The reference is a greedy sequential loop: a keypoint claimed by
+// an earlier map point (with Observations() > 0) is skipped by later ones.  result(m) depends only on the claims of
+// map points j < m, so the sequential result is the unique fixed point of "recompute every map point against the
+// claims of the previous sweep"; sweeps are fully parallel (one warp per map point) and repeat inside one cooperative
+// kernel until nothing changes (at most the longest claim chain + 1 sweeps, typically 2-3).
+// ------------------------------------------------------------------------------------------------------
+struct ProjArgs {
+    // frame
+    int nkp;
+    const float* kx; const float* ky; const int32_t* koct; const float* uright; const uint8_t* kdesc;
+    const uint8_t* occupied; const int32_t* cellStart; const int32_t* cellItems;
+    float minX, minY, wInv, hInv;
+    const float* scaleFactors;
+    // map points
+    int nmp;
+    const float* px; const float* py; const float* pxr; const int32_t* plevel; const float* pviewcos;
+    const uint8_t* pvalid; const uint8_t* pobs; const uint8_t* pdesc;
+    float th, nnratio;
+    // work / output
+    int32_t* res;       // per map point: claimed keypoint or -1
+    int32_t* claimA;    // per keypoint: smallest blocking map point index claiming it (INT_MAX = none)
+    int32_t* claimB;
+    int32_t* outMatch;  // per keypoint: last writer or -1
+    int* changed;       // [2]
+    int* nmatches;
+    int* sweeps;
+};
+
+__device__ int proj_one(const ProjArgs& A, int m, const int32_t* claimPrev, int lane)
+{
+    if (!A.pvalid[m]) return -1;
+    const int level = A.plevel[m];
+    float r = A.pviewcos[m] > 0.998 ? 2.5f : 4.0f;
+    if (A.th != 1.0f) r = __fmul_rn(r, A.th);
+    const float rr = __fmul_rn(r, A.scaleFactors[level]);
+    const float x = A.px[m], y = A.py[m];
+    const int c0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, A.minX), rr), A.wInv)));
+    if (c0 >= GRID_COLS) return -1;
+    const int c1 = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, A.minX), rr), A.wInv)));
+    if (c1 < 0) return -1;
+    const int r0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, A.minY), rr), A.hInv)));
+    if (r0 >= GRID_ROWS) return -1;
+    const int r1 = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, A.minY), rr), A.hInv)));
+    if (r1 < 0) return -1;
+    const int minLevel = level - 1, maxLevel = level;
+    const bool checkLevels = (minLevel > 0) || (maxLevel >= 0);
+    const Desc D = load_desc(A.pdesc + 32 * (size_t)m);
+    const float xr = A.pxr[m];
+    Top2 t;
+    top2_init(t);
+    uint32_t visit = 0;  // enumeration counter (same on all lanes)
+    for (int ix = c0; ix <= c1; ix++)
+        for (int iy = r0; iy <= r1; iy++) {
+            const int c = ix * GRID_ROWS + iy;
+            const int s = A.cellStart[c], e = A.cellStart[c + 1];
+            for (int k = s + lane; k < e; k += 32) {
+                const int idx = A.cellItems[k];
+                const int oct = A.koct[idx];
+                if (checkLevels) {
+                    if (oct < minLevel) continue;
+                    if (maxLevel >= 0 && oct > maxLevel) continue;
+                }
+                const float dx = __fsub_rn(A.kx[idx], x), dy = __fsub_rn(A.ky[idx], y);
+                if (!(fabsf(dx) < rr && fabsf(dy) < rr)) continue;
+                if (A.occupied[idx] || claimPrev[idx] < m) continue;
+                if (A.uright) {
+                    const float ur = A.uright[idx];
+                    if (ur > 0 && fabsf(__fsub_rn(xr, ur)) > rr) continue;
+                }
+                const int dist = hamming(D, load_desc(A.kdesc + 32 * (size_t)idx));
+                top2_push(t, ((uint32_t)dist << 20) | (visit + (uint32_t)(k - s)), idx);
+            }
+            visit += (uint32_t)(e - s);
+        }
+    top2_warp_reduce(t);
+    if (t.p1 < 0) return -1;
+    const int bestDist = t.k1 >> 20;
+    if (bestDist > TH_HIGH) return -1;
+    const int bestLevel = A.koct[t.p1];
+    const int bestLevel2 = t.p2 >= 0 ? A.koct[t.p2] : -1;
+    const int bestDist2 = t.p2 >= 0 ? (int)(t.k2 >> 20) : 256;
+    if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(A.nnratio, (float)bestDist2)) return -1;
+    return t.p1;
+}
+
+__global__ void __launch_bounds__(256) k_proj_search(ProjArgs A)
+{
+    cg::grid_group grid = cg::this_grid();
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gthreads = gridDim.x * blockDim.x;
+    int32_t* claimPrev = A.claimA;
+    int32_t* claimNext = A.claimB;
+    for (int i = gtid; i < A.nkp; i += gthreads) { claimPrev[i] = 0x7fffffff; A.outMatch[i] = -1; }
+    for (int m = gtid; m < A.nmp; m += gthreads) A.res[m] = -1;
+    if (gtid == 0) { A.changed[0] = 0; A.changed[1] = 0; *A.nmatches = 0; }
+    grid.sync();
+    int sweep = 0;
+    for (;; sweep++) {
+        int* chg = A.changed + (sweep & 1);
+        for (int m = warp; m < A.nmp; m += nwarps) {
+            const int r = proj_one(A, m, claimPrev, lane);
+            if (lane == 0 && r != A.res[m]) { A.res[m] = r; *chg = 1; }
+        }
+        for (int i = gtid; i < A.nkp; i += gthreads) claimNext[i] = 0x7fffffff;
+        if (gtid == 0) A.changed[(sweep + 1) & 1] = 0;
+        grid.sync();
+        if (*chg == 0) break;  // fixed point: res == sequential result
+        for (int m = gtid; m < A.nmp; m += gthreads) {
+            const int r = A.res[m];
+            if (r >= 0 && A.pobs[m]) atomicMin(&claimNext[r], m);
+        }
+        grid.sync();
+        int32_t* t = claimPrev; claimPrev = claimNext; claimNext = t;
+    }
+    // F.mvpMapPoints[bestIdx] = pMP: the last writer wins
+    int local = 0;
+    for (int m = gtid; m < A.nmp; m += gthreads) {
+        const int r = A.res[m];
+        if (r >= 0) { atomicMax(&A.outMatch[r], m); local++; }
+    }
+    if (local) atomicAdd(A.nmatches, local);
+    if (gtid == 0) *A.sweeps = sweep + 1;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// K7c: stereo row search.  One warp per left keypoint; the reference's per-row candidate lists hold right keypoint
+// iR in every row of [floor(y - r), ceil(y + r)], r = 2*scale[octave], in ascending iR, so "first minimum in list
+// order" is the minimum over (distance, iR) of the right keypoints whose band contains row (int)vL.
+// ------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_stereo_rows(int nl, const float* __restrict__ lx, const float* __restrict__ ly,
+                                                     const int32_t* __restrict__ loct, const uint8_t* __restrict__ ldesc,
+                                                     int nr, const float* __restrict__ rx, const float* __restrict__ ry,
+                                                     const int32_t* __restrict__ roct, const uint8_t* __restrict__ rdesc,
+                                                     const float* __restrict__ scaleFactors, int nRows, float minD,
+                                                     float maxD, int32_t* __restrict__ bestR, int32_t* __restrict__ bestDist)
+{
+    const int lane = threadIdx.x & 31;
+    const int iL = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (iL >= nl) return;
+    const float uL = lx[iL];
+    const int row = (int)ly[iL];
+    const int levelL = loct[iL];
+    const float minU = __fsub_rn(uL, maxD), maxU = __fsub_rn(uL, minD);
+    uint32_t best = 0xFFFFFFFFu;
+    if (row >= 0 && row < nRows && !(maxU < 0)) {
+        const Desc D = load_desc(ldesc + 32 * (size_t)iL);
+        for (int iR = lane; iR < nr; iR += 32) {
+            const int oR = roct[iR];
+            const float r = __fmul_rn(2.0f, scaleFactors[oR]);
+            const float y = ry[iR];
+            const int maxr = (int)ceilf(__fadd_rn(y, r)), minr = (int)floorf(__fsub_rn(y, r));
+            if (row < minr || row > maxr) continue;
+            if (oR < levelL - 1 || oR > levelL + 1) continue;
+            const float uR = rx[iR];
+            if (!(uR >= minU && uR <= maxU)) continue;
+            const int d = hamming(D, load_desc(rdesc + 32 * (size_t)iR));
+            best = min(best, ((uint32_t)d << 22) | (uint32_t)iR);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    if (lane == 0) {
+        int d = TH_HIGH, idx = -1;
+        if (best != 0xFFFFFFFFu && (int)(best >> 22) < TH_HIGH) { d = best >> 22; idx = best & ((1u << 22) - 1); }
+        bestDist[iL] = d;
+        bestR[iL] = (d < (TH_HIGH + TH_LOW) / 2) ? idx : -1;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// K7d: SearchByBoW(KF, F).  A frame feature belongs to exactly one vocabulary node (DBoW2 FeatureVector invariant),
+// so the order-dependent "skip frame features already matched" only couples KF features of the same node: one warp
+// per shared node walks its KF features in order, lanes scan the node's frame features.
+// ------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_bow_nodes(const uint8_t* __restrict__ kfDesc, const float* __restrict__ kfAngle,
+                                                   const uint8_t* __restrict__ kfHasMp, int nNodesKF,
+                                                   const int32_t* __restrict__ kfNodeId, const int32_t* __restrict__ kfNodeStart,
+                                                   const int32_t* __restrict__ kfNodeFeat, const uint8_t* __restrict__ fDesc,
+                                                   const float* __restrict__ fAngle, int nNodesF,
+                                                   const int32_t* __restrict__ fNodeId, const int32_t* __restrict__ fNodeStart,
+                                                   const int32_t* __restrict__ fNodeFeat, float nnratio,
+                                                   int32_t* outMatch, int32_t* binOf)
+{
+    const int lane = threadIdx.x & 31;
+    const int a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (a >= nNodesKF) return;
+    // locate the same node id in the frame's feature vector
+    const int id = kfNodeId[a];
+    int lo = 0, hi = nNodesF;
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (fNodeId[mid] < id) lo = mid + 1; else hi = mid; }
+    if (lo >= nNodesF || fNodeId[lo] != id) return;
+    const int fs = fNodeStart[lo], fe = fNodeStart[lo + 1];
+    const float factor = 0.0833333358f;  // HISTO_LENGTH / 360.0f
+    for (int ik = kfNodeStart[a]; ik < kfNodeStart[a + 1]; ik++) {
+        const int realIdxKF = kfNodeFeat[ik];
+        if (!kfHasMp[realIdxKF]) continue;
+        const Desc D = load_desc(kfDesc + 32 * (size_t)realIdxKF);
+        Top2 t;
+        top2_init(t);
+        for (int jf = fs + lane; jf < fe; jf += 32) {
+            const int realIdxF = fNodeFeat[jf];
+            if (outMatch[realIdxF] >= 0) continue;
+            const int dist = hamming(D, load_desc(fDesc + 32 * (size_t)realIdxF));
+            top2_push(t, ((uint32_t)dist << 20) | (uint32_t)(jf - fs), realIdxF);
+        }
+        top2_warp_reduce(t);
+        if (t.p1 >= 0) {
+            const int bestDist1 = t.k1 >> 20;
+            const int bestDist2 = t.p2 >= 0 ? (int)(t.k2 >> 20) : 256;
+            if (bestDist1 <= TH_LOW && (float)bestDist1 < __fmul_rn(nnratio, (float)bestDist2)) {
+                if (lane == 0) {
+                    outMatch[t.p1] = realIdxKF;
+                    float rot = __fsub_rn(kfAngle[realIdxKF], fAngle[t.p1]);
+                    if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+                    int bin = (int)roundf(__fmul_rn(rot, factor));
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    binOf[t.p1] = bin;
+                }
+            }
+        }
+        __syncwarp();
+        __threadfence_block();
+    }
+}
+
+// histogram of rotation bins, ComputeThreeMaxima, removal of the matches outside the three main bins, final count
+__global__ void __launch_bounds__(256) k_bow_rotation(int nf, int32_t* outMatch, const int32_t* __restrict__ binOf,
+                                                      int checkOrientation, int* nmatches)
+{
+    __shared__ int hist[HISTO_LENGTH];
+    __shared__ int keepBin[HISTO_LENGTH];
+    __shared__ int total;
+    if (threadIdx.x < HISTO_LENGTH) { hist[threadIdx.x] = 0; keepBin[threadIdx.x] = 0; }
+    if (threadIdx.x == 0) total = 0;
+    __syncthreads();
+    int mine = 0;
+    for (int f = threadIdx.x; f < nf; f += blockDim.x)
+        if (outMatch[f] >= 0) { mine++; atomicAdd(&hist[binOf[f]], 1); }
+    if (mine) atomicAdd(&total, mine);
+    __syncthreads();
+    if (!checkOrientation) {
+        if (threadIdx.x == 0) *nmatches = total;
+        return;
+    }
+    if (threadIdx.x == 0) {
+        int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            const int s = hist[i];
+            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+            else if (s > max3) { max3 = s; ind3 = i; }
+        }
+        if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+        else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) ind3 = -1;
+        int kept = 0;
+        for (int i = 0; i < HISTO_LENGTH; i++)
+            if (i == ind1 || i == ind2 || i == ind3) { keepBin[i] = 1; kept += hist[i]; }
+        *nmatches = kept;
+    }
+    __syncthreads();
+    for (int f = threadIdx.x; f < nf; f += blockDim.x)
+        if (outMatch[f] >= 0 && !keepBin[binOf[f]]) outMatch[f] = -1;
+}
+
+}  // namespace orbx
+
+using namespace orbx;
+
+struct orbm_context {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int numSMs = 0;
+    // growable device scratch
+    char* arena = nullptr;
+    size_t arenaBytes = 0;
+    // partial results of the brute-force kernel
+    int32_t* partials = nullptr;
+    size_t partialsBytes = 0;
+    void* pinned = nullptr;
+    size_t pinnedBytes = 0;
+};
+
+namespace {
+
+struct Carver {
+    size_t off = 0;
+    size_t take(size_t bytes) { size_t o = off; off += (bytes + 255) & ~size_t(255); return o; }
+};
+
+int ensure_arena(orbm_context* m, size_t bytes)
+{
+    if (bytes <= m->arenaBytes) return ORBX_OK;
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    cudaFree(m->arena); m->arena = nullptr; m->arenaBytes = 0;
+    ORBX_CUDA_TRY(cudaMalloc(&m->arena, bytes));
+    m->arenaBytes = bytes;
+    return ORBX_OK;
+}
+int ensure_partials(orbm_context* m, size_t bytes)
+{
+    if (bytes <= m->partialsBytes) return ORBX_OK;
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    cudaFree(m->partials); m->partials = nullptr; m->partialsBytes = 0;
+    ORBX_CUDA_TRY(cudaMalloc(&m->partials, bytes));
+    m->partialsBytes = bytes;
+    return ORBX_OK;
+}
+
+template <typename T> int up(orbm_context* m, T* dst, const T* src, size_t n)
+{
+    if (n) ORBX_CUDA_TRY(cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyHostToDevice, m->stream));
+    return ORBX_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int orbm_descriptor_distance(const uint8_t* a, const uint8_t* b)
+{
+    int d = 0;
+    for (int i = 0; i < 8; i++) {
+        uint32_t x, y;
+        memcpy(&x, a + 4 * i, 4);
+        memcpy(&y, b + 4 * i, 4);
+        d += __builtin_popcount(x ^ y);
+    }
+    return d;
+}
+
+int orbm_create(int device, orbm_context** out)
+{
+    if (!out) { set_error("orbm_create: null argument"); return ORBX_ERR_BAD_ARG; }
+    int ndev = orbx_device_count();
+    if (ndev <= 0) { if (ndev == 0) set_error("no CUDA device"); return ORBX_ERR_NO_DEVICE; }
+    if (device < 0 || device >= ndev) { set_error("device %d out of range", device); return ORBX_ERR_BAD_ARG; }
+    orbm_context* m = new orbm_context;
+    m->device = device;
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&m->numSMs, cudaDevAttrMultiProcessorCount, device);
+    if (e != cudaSuccess) { set_error("orbm_create: %s", cudaGetErrorString(e)); delete m; return ORBX_ERR_CUDA; }
+    *out = m;
+    return ORBX_OK;
+}
+
+void orbm_destroy(orbm_context* m)
+{
+    if (!m) return;
+    cudaSetDevice(m->device);
+    if (m->stream) cudaStreamSynchronize(m->stream);
+    cudaFree(m->arena); cudaFree(m->partials);
+    if (m->pinned) cudaFreeHost(m->pinned);
+    if (m->stream) cudaStreamDestroy(m->stream);
+    delete m;
+}
+
+void* orbm_stream(orbm_context* m) { return m ? (void*)m->stream : nullptr; }
+
+int orbm_sync(orbm_context* m)
+{
+    if (!m) { set_error("null context"); return ORBX_ERR_BAD_ARG; }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    return ORBX_OK;
+}
+
+static int bruteforce_device(orbm_context* m, const uint8_t* dq, int nq, const uint8_t* ddb, int ndb, int idxOffset,
+                             int32_t* dBest, int32_t* dIdx, int32_t* dSecond)
+{
+    const int qBlocks = (nq + BF_T * BF_RQ - 1) / (BF_T * BF_RQ);
+    // enough chunks to fill the GPU ~4 CTAs per SM, each chunk a multiple of the tile and below 2^22 rows
+    int target = std::max(1, (m->numSMs * 4) / qBlocks);
+    int chunk = (ndb + target - 1) / target;
+    chunk = std::max(BF_TILE, (chunk + BF_TILE - 1) / BF_TILE * BF_TILE);
+    chunk = std::min(chunk, 1 << 21);
+    const int nChunks = std::max(1, (ndb + chunk - 1) / chunk);
+    const size_t pBytes = sizeof(int32_t) * 3 * (size_t)nChunks * nq;
+    int rc = ensure_partials(m, pBytes);
+    if (rc != ORBX_OK) return rc;
+    int32_t* pBest = m->partials;
+    int32_t* pIdx = pBest + (size_t)nChunks * nq;
+    int32_t* pSecond = pIdx + (size_t)nChunks * nq;
+    k_bruteforce<<<dim3(nChunks, qBlocks), BF_T, 0, m->stream>>>(dq, nq, ddb, ndb, chunk, idxOffset, pBest, pIdx, pSecond);
+    k_merge_partials<<<(nq + 127) / 128, 128, 0, m->stream>>>(pBest, pIdx, pSecond, nChunks, nq, dBest, dIdx, dSecond);
+    ORBX_CUDA_TRY(cudaGetLastError());
+    return ORBX_OK;
+}
+
+int orbm_bruteforce(orbm_context* m, const uint8_t* q, int nq, const uint8_t* db, int ndb, int idx_offset, int32_t* best,
+                    int32_t* best_idx, int32_t* second, int mem_kind)
+{
+    if (!m || !q || nq <= 0 || ndb < 0 || (ndb > 0 && !db) || !best || !best_idx || !second) {
+        set_error("orbm_bruteforce: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    if (mem_kind == 1) return bruteforce_device(m, q, nq, db, ndb, idx_offset, best, best_idx, second);
+    Carver c;
+    const size_t oq = c.take(32 * (size_t)nq), odb = c.take(32 * (size_t)std::max(ndb, 1)), ob = c.take(4 * (size_t)nq),
+                 oi = c.take(4 * (size_t)nq), os = c.take(4 * (size_t)nq);
+    int rc = ensure_arena(m, c.off);
+    if (rc != ORBX_OK) return rc;
+    char* A = m->arena;
+    ORBX_CUDA_TRY(cudaMemcpyAsync(A + oq, q, 32 * (size_t)nq, cudaMemcpyHostToDevice, m->stream));
+    if (ndb) ORBX_CUDA_TRY(cudaMemcpyAsync(A + odb, db, 32 * (size_t)ndb, cudaMemcpyHostToDevice, m->stream));
+    rc = bruteforce_device(m, (uint8_t*)(A + oq), nq, (uint8_t*)(A + odb), ndb, idx_offset, (int32_t*)(A + ob),
+                           (int32_t*)(A + oi), (int32_t*)(A + os));
+    if (rc != ORBX_OK) return rc;
+    ORBX_CUDA_TRY(cudaMemcpyAsync(best, A + ob, 4 * (size_t)nq, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(best_idx, A + oi, 4 * (size_t)nq, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(second, A + os, 4 * (size_t)nq, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    return ORBX_OK;
+}
+
+int orbm_merge_partials(orbm_context* m, const int32_t* best, const int32_t* best_idx, const int32_t* second, int nparts,
+                        int nq, int32_t* out_best, int32_t* out_idx, int32_t* out_second)
+{
+    if (!m || !best || !best_idx || !second || nparts <= 0 || nq <= 0 || !out_best || !out_idx || !out_second) {
+        set_error("orbm_merge_partials: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    k_merge_partials<<<(nq + 127) / 128, 128, 0, m->stream>>>(best, best_idx, second, nparts, nq, out_best, out_idx, out_second);
+    ORBX_CUDA_TRY(cudaGetLastError());
+    return ORBX_OK;
+}
+
+int orbm_search_by_projection(orbm_context* m, const orbm_frame_view* f, const orbm_mappoint_view* p, float th,
+                              float nnratio, int32_t* out_match, int* nmatches)
+{
+    if (!m || !f || !p || !out_match || !nmatches || f->n < 0 || p->n < 0 || !f->scale_factors || f->nlevels <= 0) {
+        set_error("orbm_search_by_projection: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    const int nkp = f->n, nmp = p->n;
+    if (nkp == 0 || nmp == 0) {
+        for (int i = 0; i < nkp; i++) out_match[i] = -1;
+        *nmatches = 0;
+        return ORBX_OK;
+    }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    const int ncell = GRID_COLS * GRID_ROWS;
+    const int nitems = f->cell_start[ncell];
+    Carver c;
+    const size_t oKx = c.take(4 * (size_t)nkp), oKy = c.take(4 * (size_t)nkp), oKo = c.take(4 * (size_t)nkp),
+                 oUr = c.take(4 * (size_t)nkp), oKd = c.take(32 * (size_t)nkp), oOcc = c.take(nkp),
+                 oCs = c.take(4 * (size_t)(ncell + 1)), oCi = c.take(4 * (size_t)std::max(nitems, 1)),
+                 oSf = c.take(4 * (size_t)f->nlevels);
+    const size_t oPx = c.take(4 * (size_t)nmp), oPy = c.take(4 * (size_t)nmp), oPxr = c.take(4 * (size_t)nmp),
+                 oPl = c.take(4 * (size_t)nmp), oPv = c.take(4 * (size_t)nmp), oPva = c.take(nmp), oPo = c.take(nmp),
+                 oPd = c.take(32 * (size_t)nmp);
+    const size_t oRes = c.take(4 * (size_t)nmp), oCa = c.take(4 * (size_t)nkp), oCb = c.take(4 * (size_t)nkp),
+                 oOut = c.take(4 * (size_t)nkp), oMisc = c.take(64);
+    int rc = ensure_arena(m, c.off);
+    if (rc != ORBX_OK) return rc;
+    char* A = m->arena;
+#define UP(off, ptr, count, T) if ((rc = up<T>(m, (T*)(A + off), ptr, count)) != ORBX_OK) return rc
+    UP(oKx, f->x, nkp, float); UP(oKy, f->y, nkp, float); UP(oKo, f->octave, nkp, int32_t);
+    if (f->u_right) UP(oUr, f->u_right, nkp, float);
+    UP(oKd, f->desc, 32 * (size_t)nkp, uint8_t); UP(oOcc, f->occupied, nkp, uint8_t);
+    UP(oCs, f->cell_start, ncell + 1, int32_t); UP(oCi, f->cell_items, nitems, int32_t);
+    UP(oSf, f->scale_factors, f->nlevels, float);
+    UP(oPx, p->proj_x, nmp, float); UP(oPy, p->proj_y, nmp, float); UP(oPxr, p->proj_xr, nmp, float);
+    UP(oPl, p->level, nmp, int32_t); UP(oPv, p->view_cos, nmp, float); UP(oPva, p->valid, nmp, uint8_t);
+    UP(oPo, p->obs_pos, nmp, uint8_t); UP(oPd, p->desc, 32 * (size_t)nmp, uint8_t);
+#undef UP
+    ProjArgs a;
+    a.nkp = nkp;
+    a.kx = (float*)(A + oKx); a.ky = (float*)(A + oKy); a.koct = (int32_t*)(A + oKo);
+    a.uright = f->u_right ? (float*)(A + oUr) : nullptr;
+    a.kdesc = (uint8_t*)(A + oKd); a.occupied = (uint8_t*)(A + oOcc);
+    a.cellStart = (int32_t*)(A + oCs); a.cellItems = (int32_t*)(A + oCi);
+    a.minX = f->min_x; a.minY = f->min_y; a.wInv = f->grid_w_inv; a.hInv = f->grid_h_inv;
+    a.scaleFactors = (float*)(A + oSf);
+    a.nmp = nmp;
+    a.px = (float*)(A + oPx); a.py = (float*)(A + oPy); a.pxr = (float*)(A + oPxr); a.plevel = (int32_t*)(A + oPl);
+    a.pviewcos = (float*)(A + oPv); a.pvalid = (uint8_t*)(A + oPva); a.pobs = (uint8_t*)(A + oPo);
+    a.pdesc = (uint8_t*)(A + oPd);
+    a.th = th; a.nnratio = nnratio;
+    a.res = (int32_t*)(A + oRes); a.claimA = (int32_t*)(A + oCa); a.claimB = (int32_t*)(A + oCb);
+    a.outMatch = (int32_t*)(A + oOut);
+    a.changed = (int*)(A + oMisc); a.nmatches = a.changed + 2; a.sweeps = a.changed + 3;
+    int perSM = 0;
+    ORBX_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_proj_search, 256, 0));
+    const int want = (nmp + 7) / 8;  // 8 warps per CTA, one warp per map point
+    const int grid = std::max(1, std::min(want, perSM * m->numSMs));
+    void* args[] = {&a};
+    ORBX_CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_proj_search, dim3(grid), dim3(256), args, 0, m->stream));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(out_match, a.outMatch, 4 * (size_t)nkp, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(nmatches, a.nmatches, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    return ORBX_OK;
+}
+
+int orbm_stereo_rows(orbm_context* m, int nl, const float* lx, const float* ly, const int32_t* loct, const uint8_t* ldesc,
+                     int nr, const float* rx, const float* ry, const int32_t* roct, const uint8_t* rdesc,
+                     const float* scale_factors, int nlevels, int n_rows, float min_d, float max_d, int32_t* best_r,
+                     int32_t* best_dist)
+{
+    if (!m || nl < 0 || nr < 0 || !best_r || !best_dist || !scale_factors || nlevels <= 0 || nr >= (1 << 22)) {
+        set_error("orbm_stereo_rows: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    if (nl == 0) return ORBX_OK;
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    Carver c;
+    const size_t oLx = c.take(4 * (size_t)nl), oLy = c.take(4 * (size_t)nl), oLo = c.take(4 * (size_t)nl),
+                 oLd = c.take(32 * (size_t)nl);
+    const int nrA = std::max(nr, 1);
+    const size_t oRx = c.take(4 * (size_t)nrA), oRy = c.take(4 * (size_t)nrA), oRo = c.take(4 * (size_t)nrA),
+                 oRd = c.take(32 * (size_t)nrA), oSf = c.take(4 * (size_t)nlevels);
+    const size_t oBr = c.take(4 * (size_t)nl), oBd = c.take(4 * (size_t)nl);
+    int rc = ensure_arena(m, c.off);
+    if (rc != ORBX_OK) return rc;
+    char* A = m->arena;
+#define UP(off, ptr, count, T) if ((rc = up<T>(m, (T*)(A + off), ptr, count)) != ORBX_OK) return rc
+    UP(oLx, lx, nl, float); UP(oLy, ly, nl, float); UP(oLo, loct, nl, int32_t); UP(oLd, ldesc, 32 * (size_t)nl, uint8_t);
+    UP(oRx, rx, nr, float); UP(oRy, ry, nr, float); UP(oRo, roct, nr, int32_t); UP(oRd, rdesc, 32 * (size_t)nr, uint8_t);
+    UP(oSf, scale_factors, nlevels, float);
+#undef UP
+    k_stereo_rows<<<(nl + 7) / 8, 256, 0, m->stream>>>(nl, (float*)(A + oLx), (float*)(A + oLy), (int32_t*)(A + oLo),
+                                                      (uint8_t*)(A + oLd), nr, (float*)(A + oRx), (float*)(A + oRy),
+                                                      (int32_t*)(A + oRo), (uint8_t*)(A + oRd), (float*)(A + oSf), n_rows,
+                                                      min_d, max_d, (int32_t*)(A + oBr), (int32_t*)(A + oBd));
+    ORBX_CUDA_TRY(cudaGetLastError());
+    ORBX_CUDA_TRY(cudaMemcpyAsync(best_r, A + oBr, 4 * (size_t)nl, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(best_dist, A + oBd, 4 * (size_t)nl, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    return ORBX_OK;
+}
+
+int orbm_search_by_bow(orbm_context* m, int nkf, const uint8_t* kf_desc, const float* kf_angle, const uint8_t* kf_has_mp,
+                       const orbm_featvec_view* kf_fv, int nf, const uint8_t* f_desc, const float* f_angle,
+                       const orbm_featvec_view* f_fv, float nnratio, int check_orientation, int32_t* out_match,
+                       int* nmatches)
+{
+    if (!m || !kf_fv || !f_fv || !out_match || !nmatches || nkf < 0 || nf < 0) {
+        set_error("orbm_search_by_bow: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    for (int i = 0; i < nf; i++) out_match[i] = -1;
+    *nmatches = 0;
+    if (nkf == 0 || nf == 0 || kf_fv->n_nodes == 0 || f_fv->n_nodes == 0) return ORBX_OK;
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    const int nnk = kf_fv->n_nodes, nnf = f_fv->n_nodes;
+    const int nfk = kf_fv->node_start[nnk], nff = f_fv->node_start[nnf];
+    Carver c;
+    const size_t oKd = c.take(32 * (size_t)nkf), oKa = c.take(4 * (size_t)nkf), oKm = c.take(nkf),
+                 oKi = c.take(4 * (size_t)nnk), oKs = c.take(4 * (size_t)(nnk + 1)), oKf = c.take(4 * (size_t)std::max(nfk, 1));
+    const size_t oFd = c.take(32 * (size_t)nf), oFa = c.take(4 * (size_t)nf), oFi = c.take(4 * (size_t)nnf),
+                 oFs = c.take(4 * (size_t)(nnf + 1)), oFf = c.take(4 * (size_t)std::max(nff, 1));
+    const size_t oOut = c.take(4 * (size_t)nf), oBin = c.take(4 * (size_t)nf), oN = c.take(64);
+    int rc = ensure_arena(m, c.off);
+    if (rc != ORBX_OK) return rc;
+    char* A = m->arena;
+#define UP(off, ptr, count, T) if ((rc = up<T>(m, (T*)(A + off), ptr, count)) != ORBX_OK) return rc
+    UP(oKd, kf_desc, 32 * (size_t)nkf, uint8_t); UP(oKa, kf_angle, nkf, float); UP(oKm, kf_has_mp, nkf, uint8_t);
+    UP(oKi, kf_fv->node_id, nnk, int32_t); UP(oKs, kf_fv->node_start, nnk + 1, int32_t); UP(oKf, kf_fv->node_feat, nfk, int32_t);
+    UP(oFd, f_desc, 32 * (size_t)nf, uint8_t); UP(oFa, f_angle, nf, float);
+    UP(oFi, f_fv->node_id, nnf, int32_t); UP(oFs, f_fv->node_start, nnf + 1, int32_t); UP(oFf, f_fv->node_feat, nff, int32_t);
+#undef UP
+    ORBX_CUDA_TRY(cudaMemsetAsync(A + oOut, 0xff, 4 * (size_t)nf, m->stream));
+    ORBX_CUDA_TRY(cudaMemsetAsync(A + oBin, 0, 4 * (size_t)nf, m->stream));
+    k_bow_nodes<<<(nnk + 3) / 4, 128, 0, m->stream>>>((uint8_t*)(A + oKd), (float*)(A + oKa), (uint8_t*)(A + oKm), nnk,
+                                                     (int32_t*)(A + oKi), (int32_t*)(A + oKs), (int32_t*)(A + oKf),
+                                                     (uint8_t*)(A + oFd), (float*)(A + oFa), nnf, (int32_t*)(A + oFi),
+                                                     (int32_t*)(A + oFs), (int32_t*)(A + oFf), nnratio,
+                                                     (int32_t*)(A + oOut), (int32_t*)(A + oBin));
+    k_bow_rotation<<<1, 256, 0, m->stream>>>(nf, (int32_t*)(A + oOut), (int32_t*)(A + oBin), check_orientation, (int*)(A + oN));
+    ORBX_CUDA_TRY(cudaGetLastError());
+    ORBX_CUDA_TRY(cudaMemcpyAsync(out_match, A + oOut, 4 * (size_t)nf, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(nmatches, A + oN, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    return ORBX_OK;
+}
+
+}  // extern "C"

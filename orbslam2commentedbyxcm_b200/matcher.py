@@ -1,0 +1,154 @@
+"""Python mirror of the Hamming side of ORB_SLAM2::ORBmatcher (reference include/ORBmatcher.h:48-264) over the C-ABI.
+
+Frames, key frames and map points are passed as dicts of flat numpy arrays (the same flat views the C++ adapter
+host/ORBmatcher.h gathers from Frame / KeyFrame / MapPoint):
+
+  frame:  x, y (float32, mvKeysUn), octave (int32), u_right (float32 or None), desc (n,32 uint8), occupied (uint8),
+          cell_start (64*48+1 int32), cell_items (int32), min_x, min_y, w_inv, h_inv (float), scale_factors (float32)
+  mps:    x, y, xr (float32 mTrackProjX/Y/XR), level (int32), view_cos (float32), valid, obs (uint8), desc (n,32)
+  featvec: node_id, node_start, node_feat (int32 CSR of DBoW2::FeatureVector)
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import check
+
+
+def _p(a):
+    return a.ctypes.data if a is not None else None
+
+
+class ORBmatcher:
+    TH_LOW = 50
+    TH_HIGH = 100
+    HISTO_LENGTH = 30
+
+    def __init__(self, nnratio=0.6, checkOri=True, device=0):
+        self._L = _lib.load()
+        self.mfNNratio = float(nnratio)
+        self.mbCheckOrientation = bool(checkOri)
+        m = C.c_void_p()
+        check(self._L.orbm_create(int(device), C.byref(m)), "orbm_create")
+        self._m = m
+
+    def close(self):
+        if getattr(self, "_m", None):
+            self._L.orbm_destroy(self._m)
+            self._m = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @staticmethod
+    def DescriptorDistance(a, b):
+        a = np.ascontiguousarray(a, np.uint8).reshape(-1)
+        b = np.ascontiguousarray(b, np.uint8).reshape(-1)
+        assert a.size == 32 and b.size == 32
+        return _lib.load().orbm_descriptor_distance(a.ctypes.data, b.ctypes.data)
+
+    @property
+    def stream(self):
+        return self._L.orbm_stream(self._m)
+
+    def sync(self):
+        check(self._L.orbm_sync(self._m), "orbm_sync")
+
+    # ---- brute force (north_star item 6 / config 5) ----
+    def BruteForce(self, q, db, idx_offset=0):
+        q = np.ascontiguousarray(q, np.uint8)
+        db = np.ascontiguousarray(db, np.uint8)
+        nq = len(q)
+        best, idx, second = (np.zeros(nq, np.int32) for _ in range(3))
+        check(self._L.orbm_bruteforce(self._m, q.ctypes.data, nq, _p(db) if len(db) else None, len(db), idx_offset,
+                                      best.ctypes.data, idx.ctypes.data, second.ctypes.data, 0), "orbm_bruteforce")
+        return best, idx, second
+
+    def bruteforce_device(self, dq, nq, ddb, ndb, idx_offset, d_best, d_idx, d_second):
+        check(self._L.orbm_bruteforce(self._m, dq, nq, ddb, ndb, idx_offset, d_best, d_idx, d_second, 1), "orbm_bruteforce")
+
+    def merge_partials_device(self, d_best, d_idx, d_second, nparts, nq, o_best, o_idx, o_second):
+        check(self._L.orbm_merge_partials(self._m, d_best, d_idx, d_second, nparts, nq, o_best, o_idx, o_second),
+              "orbm_merge_partials")
+
+    # ---- SearchByProjection(Frame&, vector<MapPoint*>&, th) ----
+    def SearchByProjection(self, frame, mps, th=3.0):
+        keep = []
+
+        def arr(v, dt):
+            a = np.ascontiguousarray(v, dt)
+            keep.append(a)
+            return a
+
+        n = len(frame["x"])
+        fv = _lib.FrameView()
+        fv.n = n
+        fv.x = _p(arr(frame["x"], np.float32)); fv.y = _p(arr(frame["y"], np.float32))
+        fv.octave = _p(arr(frame["octave"], np.int32))
+        fv.u_right = _p(arr(frame["u_right"], np.float32)) if frame.get("u_right") is not None else None
+        fv.desc = _p(arr(frame["desc"], np.uint8)); fv.occupied = _p(arr(frame["occupied"], np.uint8))
+        fv.cell_start = _p(arr(frame["cell_start"], np.int32)); fv.cell_items = _p(arr(frame["cell_items"], np.int32))
+        fv.min_x, fv.min_y, fv.grid_w_inv, fv.grid_h_inv = frame["min_x"], frame["min_y"], frame["w_inv"], frame["h_inv"]
+        sf = arr(frame["scale_factors"], np.float32)
+        fv.scale_factors = _p(sf); fv.nlevels = len(sf)
+        mv = _lib.MapPointView()
+        mv.n = len(mps["x"])
+        mv.proj_x = _p(arr(mps["x"], np.float32)); mv.proj_y = _p(arr(mps["y"], np.float32))
+        mv.proj_xr = _p(arr(mps["xr"], np.float32)); mv.level = _p(arr(mps["level"], np.int32))
+        mv.view_cos = _p(arr(mps["view_cos"], np.float32)); mv.valid = _p(arr(mps["valid"], np.uint8))
+        mv.obs_pos = _p(arr(mps["obs"], np.uint8)); mv.desc = _p(arr(mps["desc"], np.uint8))
+        out = np.full(max(n, 1), -1, np.int32)
+        nm = C.c_int()
+        check(self._L.orbm_search_by_projection(self._m, C.byref(fv), C.byref(mv), float(th), self.mfNNratio,
+                                                out.ctypes.data, C.byref(nm)), "orbm_search_by_projection")
+        return nm.value, out[:n]
+
+    # ---- stereo row search (Frame::ComputeStereoMatches coarse part) ----
+    def StereoRows(self, left, right, scale_factors, n_rows, min_d, max_d):
+        keep = []
+
+        def arr(v, dt):
+            a = np.ascontiguousarray(v, dt)
+            keep.append(a)
+            return a
+
+        nl, nr = len(left["x"]), len(right["x"])
+        sf = arr(scale_factors, np.float32)
+        best_r = np.full(max(nl, 1), -1, np.int32)
+        best_d = np.zeros(max(nl, 1), np.int32)
+        check(self._L.orbm_stereo_rows(
+            self._m, nl, _p(arr(left["x"], np.float32)), _p(arr(left["y"], np.float32)), _p(arr(left["octave"], np.int32)),
+            _p(arr(left["desc"], np.uint8)), nr, _p(arr(right["x"], np.float32)), _p(arr(right["y"], np.float32)),
+            _p(arr(right["octave"], np.int32)), _p(arr(right["desc"], np.uint8)), _p(sf), len(sf), int(n_rows),
+            float(min_d), float(max_d), best_r.ctypes.data, best_d.ctypes.data), "orbm_stereo_rows")
+        return best_r[:nl], best_d[:nl]
+
+    # ---- SearchByBoW(KeyFrame*, Frame&, matches) ----
+    def SearchByBoW(self, kf, fr):
+        keep = []
+
+        def arr(v, dt):
+            a = np.ascontiguousarray(v, dt)
+            keep.append(a)
+            return a
+
+        def fvview(d):
+            v = _lib.FeatVecView()
+            v.n_nodes = len(d["node_id"])
+            v.node_id = _p(arr(d["node_id"], np.int32)); v.node_start = _p(arr(d["node_start"], np.int32))
+            v.node_feat = _p(arr(d["node_feat"], np.int32))
+            return v
+
+        nkf, nf = len(kf["angle"]), len(fr["angle"])
+        kv, fv = fvview(kf), fvview(fr)
+        out = np.full(max(nf, 1), -1, np.int32)
+        nm = C.c_int()
+        check(self._L.orbm_search_by_bow(
+            self._m, nkf, _p(arr(kf["desc"], np.uint8)), _p(arr(kf["angle"], np.float32)), _p(arr(kf["has_mp"], np.uint8)),
+            C.byref(kv), nf, _p(arr(fr["desc"], np.uint8)), _p(arr(fr["angle"], np.float32)), C.byref(fv),
+            self.mfNNratio, int(self.mbCheckOrientation), out.ctypes.data, C.byref(nm)), "orbm_search_by_bow")
+        return nm.value, out[:nf]

@@ -1,0 +1,191 @@
+"""GPU parity: the CUDA extractor (through the C-ABI) against the CPU oracle, stage by stage and end to end.
+Bit-exact everywhere: pyramid bytes, FAST candidate sets, blurred planes, keypoint records (coordinates, octave,
+size, response, ANGLE BITS) in quad-tree order, descriptor bytes."""
+import os
+
+import numpy as np
+import pytest
+
+from orbslam2commentedbyxcm_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def gpu():
+    import orbslam2commentedbyxcm_b200 as pkg
+
+    return pkg
+
+
+def _sorted_rows(a):
+    a = np.asarray(a)
+    if len(a) == 0:
+        return a
+    return a[np.lexsort((a[:, 0], a[:, 1], a[:, 2]))]
+
+
+CASES = [
+    ("tum", 0), ("euroc", 1), ("kitti", 2),
+]
+
+
+def test_tables_match_oracle(gpu, oracle_mod):
+    for cfg in [(1000, 1.2, 8, 20, 7), (2000, 1.2, 8, 20, 7), (500, 1.5, 5, 30, 10), (1200, 1.2, 8, 20, 7)]:
+        ex = gpu.ORBextractor(*cfg)
+        o = oracle_mod.Extractor(*cfg)
+        img = synth.gen_frame((200, 300), 0)
+        o.extract(img)
+        assert np.array_equal(ex.GetScaleFactors(), o.scale_factors())
+        assert np.array_equal(ex.GetInverseScaleSigmaSquares(), o.inv_level_sigma2())
+        assert np.array_equal(ex.mnFeaturesPerLevel, o.quotas())
+        assert ex.GetLevels() == cfg[2] and ex.GetScaleFactor() == np.float32(cfg[1])
+        ex.close()
+
+
+@pytest.mark.parametrize("shape_name,seed", CASES)
+def test_stages_and_output_bit_exact(gpu, oracle_mod, shape_name, seed):
+    img = synth.gen_frame(synth.SHAPES[shape_name], seed)
+    cfg = synth.PRESETS[shape_name]
+    o = oracle_mod.Extractor(*cfg)
+    okps, odesc = o.extract(img)
+    ex = gpu.ORBextractor(*cfg)
+    kps, desc = ex(img)
+    nl = cfg[2]
+    # K1 pyramid
+    for l in range(nl):
+        w, h = o.level_size(l)
+        assert ex.level_size(l) == (h, w)
+        assert np.array_equal(ex.pyramid_level_padded(l), o.pyramid(l)), "pyramid level %d" % l
+    # K2 FAST candidates (unordered on the GPU)
+    for l in range(nl):
+        assert np.array_equal(_sorted_rows(ex.debug_candidates(l)), _sorted_rows(o.candidates(l))), "candidates level %d" % l
+    # K5 blur
+    for l in range(nl):
+        ob = o.blurred(l)
+        if ob is not None:
+            assert np.array_equal(ex.debug_blurred(l), ob), "blur level %d" % l
+    # K3/K4/K6 final output
+    assert len(kps) == len(okps)
+    for f in ("x", "y", "octave", "response", "size"):
+        assert np.array_equal(kps[f], okps[f]), f
+    assert np.array_equal(kps["angle"].view(np.uint32), okps["angle"].view(np.uint32)), "angle bits"
+    assert kps.tobytes() == okps.tobytes()
+    assert np.array_equal(desc, odesc)
+    ex.close()
+
+
+@pytest.mark.parametrize("name", ["small_a", "small_b", "tum_s0"])
+def test_against_reference_golden(gpu, golden_dir, name):
+    """CUDA path == the reference's own ORBextractor.cc output (committed fixture)."""
+    g = np.load(os.path.join(golden_dir, "extract_ref_%s.npz" % name))
+    shape = tuple(int(v) for v in g["shape"])
+    cfg = g["cfg"]
+    img = synth.gen_frame(shape, int(g["seed"]))
+    ex = gpu.ORBextractor(int(cfg[0]), float(cfg[1]), int(cfg[2]), int(cfg[3]), int(cfg[4]))
+    kps, desc = ex(img)
+    assert kps.tobytes() == g["kps"].tobytes()
+    assert np.array_equal(desc, g["desc"])
+    ex.close()
+
+
+def test_batch_equals_per_frame_oracle(gpu, oracle_mod):
+    shape = (240, 320)
+    cfg = (500, 1.2, 8, 20, 7)
+    imgs = np.stack([synth.gen_frame(shape, s) for s in range(6)])
+    ex = gpu.ORBextractor(*cfg)
+    kps, desc, counts = ex.extract_batch(imgs)
+    o = oracle_mod.Extractor(*cfg)
+    for i in range(len(imgs)):
+        ok, od = o.extract(imgs[i])
+        assert counts[i] == len(ok)
+        assert kps[i, : counts[i]].tobytes() == ok.tobytes()
+        assert np.array_equal(desc[i, : counts[i]], od)
+    # a second batch on the same handle (buffers reused, counters reset by the kernels themselves)
+    kps2, desc2, counts2 = ex.extract_batch(imgs[::-1].copy())
+    assert np.array_equal(counts2, counts[::-1])
+    assert kps2[0, : counts2[0]].tobytes() == kps[5, : counts[5]].tobytes()
+    ex.close()
+
+
+def test_graph_and_plain_launch_agree(gpu):
+    img = synth.gen_frame((480, 640), 3)
+    ex = gpu.ORBextractor(1000, 1.2, 8, 20, 7)
+    a = ex(img)
+    ex.set_use_graph(False)
+    b = ex(img)
+    ex.set_profiling(True)
+    c = ex(img)
+    t = ex.stage_times()
+    assert a[0].tobytes() == b[0].tobytes() == c[0].tobytes()
+    assert np.array_equal(a[1], b[1]) and np.array_equal(a[1], c[1])
+    assert all(v >= 0 for v in t.values()) and t["fast"] > 0
+    ex.close()
+
+
+@pytest.mark.parametrize("shape,cfg,seed", [
+    ((130, 170), (2000, 1.2, 3, 20, 7), 3),     # quota never reached: tree runs until every node holds one key
+    ((240, 320), (50, 1.3, 5, 30, 10), 4),      # tiny quota, other scale / thresholds
+    ((97, 401), (300, 1.2, 2, 20, 7), 5),       # wide strip: several quad-tree roots
+    ((333, 201), (300, 1.2, 2, 12, 5), 6),      # tall image, odd sizes
+    ((480, 640), (4000, 1.2, 8, 20, 7), 7),     # mono-initialisation style doubled quota
+])
+def test_odd_configurations(gpu, oracle_mod, shape, cfg, seed):
+    img = synth.gen_frame(shape, seed)
+    ok, od = oracle_mod.Extractor(*cfg).extract(img)
+    ex = gpu.ORBextractor(*cfg)
+    kps, desc = ex(img)
+    assert kps.tobytes() == ok.tobytes()
+    assert np.array_equal(desc, od)
+    ex.close()
+
+
+def test_flat_and_empty_inputs(gpu, oracle_mod):
+    ex = gpu.ORBextractor(1000, 1.2, 8, 20, 7)
+    flat = np.full((480, 640), 127, np.uint8)
+    kps, desc = ex(flat)
+    assert len(kps) == 0 and desc.shape == (0, 32)
+    kps, desc = ex(np.zeros((0, 0), np.uint8))  # empty image: silent return (src/ORBextractor.cc:1517)
+    assert len(kps) == 0
+    # binary noise: many equal responses -> exercises the candidate-order tie-break
+    rng = np.random.default_rng(5)
+    img = (rng.integers(0, 2, (240, 320)) * 255).astype(np.uint8)
+    ok, od = oracle_mod.Extractor(1000, 1.2, 8, 20, 7).extract(img)
+    kps, desc = ex(img)
+    assert kps.tobytes() == ok.tobytes() and np.array_equal(desc, od)
+    ex.close()
+
+
+def test_too_small_image_is_an_error_not_a_crash(gpu):
+    ex = gpu.ORBextractor(1000, 1.2, 8, 20, 7)
+    with pytest.raises(gpu.OrbxError):
+        ex(np.zeros((60, 60), np.uint8))
+    ex.close()
+
+
+def test_full_size_batch_properties(gpu):
+    """KITTI-shaped batch at BASELINE size through size-independent properties: determinism across runs, every
+    keypoint inside the 19-px border of its level, per-level counts >= quota when candidates allow, octave order."""
+    shape = synth.SHAPES["kitti"]
+    cfg = synth.PRESETS["kitti"]
+    base = [synth.gen_frame(shape, s) for s in range(4)]
+    imgs = np.stack([base[i % 4] for i in range(32)])
+    ex = gpu.ORBextractor(*cfg)
+    k1, d1, c1 = ex.extract_batch(imgs)
+    k2, d2, c2 = ex.extract_batch(imgs)
+    assert np.array_equal(c1, c2) and k1.tobytes() == k2.tobytes() and np.array_equal(d1, d2)
+    for i in range(4, 32):
+        assert c1[i] == c1[i % 4] and k1[i, : c1[i]].tobytes() == k1[i % 4, : c1[i]].tobytes()
+        assert np.array_equal(d1[i, : c1[i]], d1[i % 4, : c1[i]])
+    sf = ex.GetScaleFactors()
+    for i in range(4):
+        k = k1[i, : c1[i]]
+        assert c1[i] >= cfg[0] * 0.9
+        assert np.all(np.diff(k["octave"]) >= 0)
+        lx, ly = k["x"] / sf[k["octave"]], k["y"] / sf[k["octave"]]
+        for l in range(cfg[2]):
+            rows, cols = ex.level_size(l)
+            m = k["octave"] == l
+            assert np.all(lx[m] >= 18.99) and np.all(lx[m] <= cols - 19.99)
+            assert np.all(ly[m] >= 18.99) and np.all(ly[m] <= rows - 19.99)
+    ex.close()

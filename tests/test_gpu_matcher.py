@@ -1,0 +1,191 @@
+"""GPU parity: the CUDA matchers (through the C-ABI) against the CPU oracle restatements of the reference loops.
+Bit-exact: match indices, distances, second-best distances, match counts."""
+import numpy as np
+import pytest
+
+from orbslam2commentedbyxcm_b200 import synth
+
+import helpers
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def gpu():
+    import orbslam2commentedbyxcm_b200 as pkg
+
+    return pkg
+
+
+def test_descriptor_distance(gpu, oracle_mod):
+    rng = np.random.default_rng(0)
+    L = oracle_mod.lib()
+    for _ in range(200):
+        a = rng.integers(0, 256, 32, dtype=np.uint8)
+        b = rng.integers(0, 256, 32, dtype=np.uint8)
+        d = gpu.ORBmatcher.DescriptorDistance(a, b)
+        assert d == L.orbo_descriptor_distance(a.ctypes.data, b.ctypes.data) == helpers.popcount_dist(a, b)
+    z = np.zeros(32, np.uint8)
+    assert gpu.ORBmatcher.DescriptorDistance(z, ~z) == 256 and gpu.ORBmatcher.DescriptorDistance(z, z) == 0
+
+
+@pytest.mark.parametrize("nq,ndb", [(1, 1), (37, 1000), (2000, 20000), (1025, 7777), (300, 0), (5, 3)])
+def test_bruteforce_vs_oracle(gpu, oracle_mod, nq, ndb):
+    db = synth.gen_descriptors(max(ndb, 1), seed=ndb + 1)[:ndb]
+    if ndb:
+        q, _ = synth.gen_queries(db, nq, seed=nq)
+        # force exact duplicates and ties
+        if ndb > 10:
+            db[ndb // 2] = db[3]
+            db[ndb - 1] = db[3]
+    else:
+        q = synth.gen_descriptors(nq, seed=5)
+    m = gpu.ORBmatcher()
+    best, idx, second = m.BruteForce(q, db)
+    ob, oi, os_ = oracle_mod.bruteforce(q, db, threads=8)
+    assert np.array_equal(best, ob)
+    assert np.array_equal(idx, oi)
+    assert np.array_equal(second, os_)
+    m.close()
+
+
+def test_bruteforce_low_entropy_ties(gpu, oracle_mod):
+    """descriptors drawn from a tiny alphabet: many equal distances -> first-index and second-best semantics."""
+    rng = np.random.default_rng(7)
+    base = rng.integers(0, 256, (4, 32), dtype=np.uint8)
+    db = base[rng.integers(0, 4, 5000)]
+    q = base[rng.integers(0, 4, 300)]
+    m = gpu.ORBmatcher()
+    best, idx, second = m.BruteForce(q, db)
+    ob, oi, os_ = oracle_mod.bruteforce(q, db, threads=8)
+    assert np.array_equal(best, ob) and np.array_equal(idx, oi) and np.array_equal(second, os_)
+    assert (best == 0).all() and (second == 0).all()
+    m.close()
+
+
+def test_bruteforce_full_size_properties(gpu):
+    """2000 x 1M (config 5 on one GPU) through properties: the planted match is found with the planted distance,
+    second >= best, and a sharded search + merge equals the unsharded one bit for bit."""
+    import torch
+
+    ndb, nq = 1_000_000, 2000
+    db = synth.gen_descriptors(ndb)
+    q, pick = synth.gen_queries(db, nq)
+    m = gpu.ORBmatcher()
+    best, idx, second = m.BruteForce(q, db)
+    planted = np.unpackbits(np.bitwise_xor(q, db[pick]), axis=1).sum(1)
+    assert np.array_equal(best, np.minimum(best, planted))  # never worse than the planted row
+    hit = idx == pick
+    assert hit.mean() > 0.99
+    assert np.array_equal(best[hit], planted[hit])
+    assert (second >= best).all()
+    got = np.unpackbits(np.bitwise_xor(q, db[idx]), axis=1).sum(1)
+    assert np.array_equal(got, best)
+    # sharded: 8 contiguous shards searched separately on the device, then merged
+    dev = torch.device("cuda:0")
+    dq = torch.from_numpy(q).to(dev)
+    ddb = torch.from_numpy(db).to(dev)
+    parts = 8
+    pb = torch.empty((parts, nq), dtype=torch.int32, device=dev)
+    pi = torch.empty_like(pb)
+    ps = torch.empty_like(pb)
+    per = ndb // parts
+    for s in range(parts):
+        m.bruteforce_device(dq.data_ptr(), nq, ddb[s * per:].data_ptr(), per, s * per, pb[s].data_ptr(), pi[s].data_ptr(), ps[s].data_ptr())
+    ob = torch.empty(nq, dtype=torch.int32, device=dev)
+    oi = torch.empty_like(ob)
+    os_ = torch.empty_like(ob)
+    m.merge_partials_device(pb.data_ptr(), pi.data_ptr(), ps.data_ptr(), parts, nq, ob.data_ptr(), oi.data_ptr(), os_.data_ptr())
+    m.sync()
+    assert np.array_equal(ob.cpu().numpy(), best) and np.array_equal(oi.cpu().numpy(), idx) and np.array_equal(os_.cpu().numpy(), second)
+    m.close()
+
+
+@pytest.mark.parametrize("shape_name,seed,nmp,th,stereo", [
+    ("kitti", 0, 4000, 1.0, False), ("kitti", 1, 4000, 3.0, True), ("tum", 2, 1500, 5.0, False), ("euroc", 3, 50, 1.0, True),
+])
+def test_search_by_projection_vs_oracle(gpu, oracle_mod, shape_name, seed, nmp, th, stereo):
+    img, cfg, oex, kps, desc = helpers.extract_with_oracle(oracle_mod, shape_name, seed)
+    rows, cols = synth.SHAPES[shape_name]
+    frame = helpers.make_frame_view(oracle_mod, kps, desc, rows, cols, oex.scale_factors(), seed=seed, stereo=stereo)
+    mps = helpers.make_mappoints(frame, nmp, seed=seed, stereo=stereo)
+    m = gpu.ORBmatcher(0.8, True)
+    n_gpu, out_gpu = m.SearchByProjection(frame, mps, th)
+    n_ref, out_ref = oracle_mod.search_by_projection(frame, mps, th, 0.8)
+    assert n_ref > 0.2 * nmp * 0.5
+    assert n_gpu == n_ref
+    assert np.array_equal(out_gpu, out_ref)
+    m.close()
+
+
+def test_search_by_projection_claim_chain(gpu, oracle_mod):
+    """a long chain of map points that all want the same few keypoints: worst case for the fixed-point sweeps."""
+    img, cfg, oex, kps, desc = helpers.extract_with_oracle(oracle_mod, "tum", 4)
+    rows, cols = synth.SHAPES["tum"]
+    frame = helpers.make_frame_view(oracle_mod, kps, desc, rows, cols, oex.scale_factors(), occupied_p=0.0, seed=4)
+    tgt = int(np.argmax((kps["octave"] == 0)))
+    nmp = 64
+    rng = np.random.default_rng(0)
+    mps = dict(
+        x=np.full(nmp, frame["x"][tgt], np.float32), y=np.full(nmp, frame["y"][tgt], np.float32),
+        xr=np.full(nmp, -1, np.float32), level=np.zeros(nmp, np.int32), view_cos=np.full(nmp, 0.9, np.float32),
+        valid=np.ones(nmp, np.uint8), obs=(rng.random(nmp) < 0.7).astype(np.uint8),
+        desc=np.ascontiguousarray(np.repeat(frame["desc"][tgt][None], nmp, 0)),
+    )
+    m = gpu.ORBmatcher(0.8, True)
+    n_gpu, out_gpu = m.SearchByProjection(frame, mps, 15.0)
+    n_ref, out_ref = oracle_mod.search_by_projection(frame, mps, 15.0, 0.8)
+    assert n_gpu == n_ref and np.array_equal(out_gpu, out_ref)
+    m.close()
+
+
+@pytest.mark.parametrize("seed", [0, 1])
+def test_stereo_rows_vs_oracle(gpu, oracle_mod, seed):
+    left, right = synth.gen_stereo_pair(synth.SHAPES["euroc"], seed)
+    cfg = synth.PRESETS["euroc"]
+    oex = oracle_mod.Extractor(*cfg)
+    kl, dl = oex.extract(left)
+    sf = oex.scale_factors()
+    kr, dr = oracle_mod.Extractor(*cfg).extract(right)
+    L = dict(x=kl["x"].copy(), y=kl["y"].copy(), octave=kl["octave"].astype(np.int32), desc=dl)
+    R = dict(x=kr["x"].copy(), y=kr["y"].copy(), octave=kr["octave"].astype(np.int32), desc=dr)
+    fx, bf = 435.2, 47.9
+    mb = bf / fx
+    min_d, max_d = 0.0, float(np.float32(bf) / np.float32(mb))
+    m = gpu.ORBmatcher()
+    br, bd = m.StereoRows(L, R, sf, synth.SHAPES["euroc"][0], min_d, max_d)
+    obr, obd = oracle_mod.stereo_rows(L, R, sf, synth.SHAPES["euroc"][0], min_d, max_d)
+    assert (obr >= 0).sum() > 100
+    assert np.array_equal(br, obr) and np.array_equal(bd, obd)
+    m.close()
+
+
+@pytest.mark.parametrize("seed,check_ori", [(0, True), (1, False), (2, True)])
+def test_search_by_bow_vs_oracle(gpu, oracle_mod, seed, check_ori):
+    img, cfg, oex, kps, desc = helpers.extract_with_oracle(oracle_mod, "tum", seed)
+    rng = np.random.default_rng(seed)
+    n = len(kps)
+    # key frame = same features in shuffled order with perturbed descriptors and mostly consistent rotation
+    perm = rng.permutation(n)
+    flips = rng.random((n, 256)) < 0.06
+    kf_desc = np.ascontiguousarray(desc[perm] ^ np.packbits(flips, axis=1, bitorder="little"))
+    rot = np.where(rng.random(n) < 0.8, 24.0, rng.random(n) * 360).astype(np.float32)
+    kf_angle = np.mod(kps["angle"][perm] + rot, 360).astype(np.float32)
+    fvF, node_of = helpers.make_featvec(n, 400, seed)
+    # the KF feature falls in the same node as its source feature most of the time
+    kf_node = np.where(rng.random(n) < 0.9, node_of[perm], rng.integers(0, 400, n))
+    ids = np.unique(kf_node)
+    start, feat = [0], []
+    for nid in ids:
+        f = np.nonzero(kf_node == nid)[0]
+        feat.extend(f.tolist())
+        start.append(len(feat))
+    kf = dict(desc=kf_desc, angle=kf_angle, has_mp=(rng.random(n) < 0.8).astype(np.uint8), node_id=ids.astype(np.int32),
+              node_start=np.array(start, np.int32), node_feat=np.array(feat, np.int32))
+    fr = dict(desc=np.ascontiguousarray(desc), angle=kps["angle"].astype(np.float32).copy(), **fvF)
+    m = gpu.ORBmatcher(0.7, check_ori)
+    n_gpu, out_gpu = m.SearchByBoW(kf, fr)
+    n_ref, out_ref = oracle_mod.search_by_bow(kf, fr, 0.7, check_ori)
+    assert n_ref > 50
+    assert n_gpu == n_ref and np.array_equal(out_gpu, out_ref)
+    m.close()
