@@ -1,0 +1,403 @@
+#!/usr/bin/env python
+"""bench.py -- ORB front-end hot path on B200: frames/s of ORB extraction (640x480, 1000 features) + Hamming pairs/s.
+
+  python bench.py --gpus N --steps K --warmup W            our CUDA path (one rank per GPU; torchrun for N > 1)
+  python bench.py --impl reference --gpus N --steps K ...  the reference's own CPU ORBextractor on the host cores
+
+A "step" = one pass of the extractor over a batch of synthetic frames (BATCH frames per GPU, weak scaling).
+  value : frames/s with the frames already resident in HBM (device in, device out, CUDA events on the handle's stream)
+  e2e   : frames/s through the C-ABI host entry point orbx_extract_batch (pinned host input, H2D + kernels + D2H +
+          the copy into caller arrays inside the timed region)
+  roofline      : dominant kernel stage, algorithmic bytes / its measured duration vs MEASURED_PEAKS
+  cpu_baseline  : the CPU oracle / reference build on the host cores, on a bounded sample of the same workload
+Prints ONE JSON line (rank 0).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from orbslam2commentedbyxcm_b200 import synth  # noqa: E402
+
+WORKLOAD = "tum"  # BASELINE.json metric: "ORB extract frames/s @640x480 1k feats"
+BATCH = 256       # frames per GPU per step
+N_DISTINCT = 32   # distinct synthetic frames (seeds 0..31), tiled to BATCH
+
+
+def level_geometry(rows, cols, nlevels, scale_factor):
+    s = np.float32(1.0)
+    out = []
+    for l in range(nlevels):
+        inv = np.float32(1.0) / s
+        out.append((int(np.rint(np.float32(cols) * inv)), int(np.rint(np.float32(rows) * inv))))
+        s = np.float32(s * np.float32(scale_factor))
+    return out
+
+
+def algorithmic_bytes(rows, cols, cfg):
+    """algorithmic bytes per frame and per stage."""
+    nf, sf, nl = cfg[0], cfg[1], cfg[2]
+    lv = level_geometry(rows, cols, nl, sf)
+    interior = [w * h for w, h in lv]
+    padded = [(w + 38) * (h + 38) for w, h in lv]
+    pyr = rows * cols + padded[0] + sum(interior[l - 1] + padded[l] for l in range(1, nl))
+    return {
+        "pyramid": pyr,
+        "fast": sum(interior) + 12 * 10 * nf,
+        "blur": 2 * sum(interior),
+        "octree": nf * (749 + 16),   # orientation reads; the quad-tree itself moves 8 B per candidate
+        "desc": nf * (512 + 32),
+    }
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "200"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            p = [x.strip() for x in ln.split(",")]
+            if len(p) < 6:
+                continue
+            try:
+                sm.append(float(p[0])); mx.append(float(p[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, p[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def make_frames(shape, n_distinct, batch):
+    base = np.stack([synth.gen_frame(shape, s) for s in range(n_distinct)])
+    reps = (batch + n_distinct - 1) // n_distinct
+    return np.concatenate([base] * reps)[:batch].copy()
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+# ------------------------------------------------------------------------------------------------------------------
+def run_reference(args):
+    """--impl reference: the reference's own ORBextractor.cc (oracle/_ref, compiled unmodified against the mini-cv shim) on
+    the host cores, frame-parallel with one extractor object per thread; falls back to the restated oracle port."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle
+
+    shape = synth.SHAPES[WORKLOAD]
+    cfg = synth.PRESETS[WORKLOAD]
+    threads = host_threads()
+    kind = "ref_fast" if oracle.lib("ref_fast") is not None else "fast"
+    sample = max(threads * 4, 16)  # frames per step: a bounded sample of the BATCH-frame workload
+    frames = make_frames(shape, min(N_DISTINCT, sample), sample)
+    for _ in range(max(args.warmup, 1)):
+        oracle.extract_batch(frames[: threads * 2], *cfg, threads=threads, kind=kind)
+    t0 = time.perf_counter()
+    total_kp = 0
+    for _ in range(args.steps):
+        tot, _ = oracle.extract_batch(frames, *cfg, threads=threads, kind=kind)
+        total_kp += tot
+    dt = time.perf_counter() - t0
+    fps = sample * args.steps / dt
+    line = {
+        "impl": "reference", "metric": "orb_extract_frames_per_s_640x480_1000feat", "value": fps, "unit": "frames/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "C1 TUM 640x480, 1000 feats, scale 1.2, 8 levels, FAST 20/7; %d-frame sample per step" % sample},
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads,
+                         "kind": "reference" if kind == "ref_fast" else "port",
+                         "sample": "%d frames x %d steps, %d host threads, %s" % (sample, args.steps, threads,
+                                   "reference src/ORBextractor.cc + mini-cv shim (-O3 x86-64-v3)" if kind == "ref_fast" else "oracle port (-O3 x86-64-v3)")},
+        "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "keypoints_per_frame": total_kp / (sample * args.steps),
+    }
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+
+    import orbslam2commentedbyxcm_b200 as pkg
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+
+    shape = synth.SHAPES[WORKLOAD]
+    cfg = synth.PRESETS[WORKLOAD]
+    rows, cols = shape
+    B = args.batch
+    frames = make_frames(shape, N_DISTINCT, B)
+    # each rank gets its own rotation of the frame set (independent units, no data-path collective)
+    frames = np.roll(frames, rank, axis=0).copy()
+
+    ex = pkg.ORBextractor(*cfg, device=local)
+    cap = ex.max_keypoints(rows, cols)
+    stream = torch.cuda.ExternalStream(ex.stream, device=dev)
+
+    # ---- device-resident buffers ----
+    d_imgs = torch.from_numpy(frames).to(dev)
+    d_kps = torch.empty((B, cap, 6), dtype=torch.float32, device=dev)
+    d_desc = torch.empty((B, cap, 32), dtype=torch.uint8, device=dev)
+    d_counts = torch.empty(B, dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+
+    def step_device():
+        ex.extract_batch_device(d_imgs.data_ptr(), B, rows, cols, d_kps.data_ptr(), d_desc.data_ptr(), d_counts.data_ptr(), cap)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    ex.sync()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+    e1.record(stream)
+    ex.sync()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = ex.last_launch_count() * args.steps
+    counts = d_counts.cpu().numpy()
+
+    # ---- per-stage timing (CUDA events between stages on the handle's stream; serialised, no graph) ----
+    ex.set_profiling(True)
+    stage_ms = {}
+    reps = max(3, min(args.steps, 10))
+    for i in range(reps + 1):
+        step_device()
+        ex.sync()
+        if i == 0:
+            continue
+        for k, v in ex.stage_times().items():
+            stage_ms[k] = stage_ms.get(k, 0.0) + v / reps
+    ex.set_profiling(False)
+
+    # ---- end to end through the host C-ABI (pinned host input) ----
+    h_imgs = torch.from_numpy(frames).pin_memory()
+    out = ex.alloc_outputs(B, rows, cols)
+    e2e_steps = max(2, min(args.steps, 10))
+    for _ in range(2):
+        ex.extract_batch(h_imgs.numpy(), out=out)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        ex.extract_batch(h_imgs.numpy(), out=out)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- single-frame latency through the host C-ABI ----
+    one = frames[:1].copy()
+    out1 = ex.alloc_outputs(1, rows, cols)
+    for _ in range(20):
+        ex.extract_batch(one, out=out1)
+    lat = []
+    for _ in range(200):
+        t = time.perf_counter()
+        ex.extract_batch(one, out=out1)
+        lat.append(time.perf_counter() - t)
+    lat_ms = 1e3 * float(np.median(lat))
+
+    # ---- brute-force Hamming (config 5 shape: 2000 queries x 1M map descriptors, sharded by rank) ----
+    m = pkg.ORBmatcher(0.6, True, device=local)
+    ndb_total, nq = 1_000_000, 2000
+    per = ndb_total // world
+    db = synth.gen_descriptors(per, seed=12345 + rank)
+    q, _ = synth.gen_queries(synth.gen_descriptors(4096, seed=777), nq)
+    ddb = torch.from_numpy(db).to(dev)
+    dq = torch.from_numpy(q).to(dev)
+    pb = torch.empty(nq, dtype=torch.int32, device=dev)
+    pi = torch.empty_like(pb)
+    ps = torch.empty_like(pb)
+    mstream = torch.cuda.ExternalStream(m.stream, device=dev)
+
+    def bf_step():
+        m.bruteforce_device(dq.data_ptr(), nq, ddb.data_ptr(), per, rank * per, pb.data_ptr(), pi.data_ptr(), ps.data_ptr())
+
+    for _ in range(3):
+        bf_step()
+    m.sync()
+    barrier()
+    b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    bf_reps = 20
+    b0.record(mstream)
+    for _ in range(bf_reps):
+        bf_step()
+    b1.record(mstream)
+    m.sync()
+    bf_ms = b0.elapsed_time(b1) / bf_reps
+    if dist is not None:
+        # the only exchange step of the path: all-gather the per-shard (best, idx, second), identical merge on every rank
+        gb = [torch.empty_like(pb) for _ in range(world)]
+        gi = [torch.empty_like(pb) for _ in range(world)]
+        gs = [torch.empty_like(pb) for _ in range(world)]
+        dist.all_gather(gb, pb); dist.all_gather(gi, pi); dist.all_gather(gs, ps)
+        ob, oi, os_ = torch.empty_like(pb), torch.empty_like(pb), torch.empty_like(pb)
+        torch.cuda.synchronize()
+        m.merge_partials_device(torch.stack(gb).data_ptr(), torch.stack(gi).data_ptr(), torch.stack(gs).data_ptr(), world, nq,
+                                ob.data_ptr(), oi.data_ptr(), os_.data_ptr())
+        m.sync()
+
+    # ---- max over ranks ----
+    t = torch.tensor([ms, e2e_s, bf_ms], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_s, bf_ms = t.tolist()
+
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        ab = algorithmic_bytes(rows, cols, cfg)
+        stages = {}
+        for k in ("pyramid", "fast", "octree", "blur", "desc"):
+            t_ms = stage_ms.get(k, 0.0)
+            gbs = ab[k] * B / (t_ms * 1e-3) / 1e9 if t_ms > 0 else 0.0
+            stages[k] = {"ms": t_ms, "algo_bytes_per_frame": ab[k], "GB_per_s": gbs, "frac_of_hbm_peak": gbs / peak}
+        dom = max(("pyramid", "fast", "octree", "blur", "desc"), key=lambda k: stage_ms.get(k, 0.0))
+        fps = world * B * args.steps / (ms * 1e-3)
+        e2e_fps = world * B * e2e_steps / e2e_s
+        d2h = out[0].nbytes + out[1].nbytes + out[2].nbytes
+        line = {
+            "metric": "orb_extract_frames_per_s_640x480_1000feat", "value": fps, "unit": "frames/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {
+                "workload": "C1 TUM 640x480, 1000 feats, scale 1.2, 8 levels, FAST 20/7; %d frames per GPU per step "
+                            "(%d distinct seeded frames tiled)" % (B, N_DISTINCT),
+                "frames_per_gpu_per_step": B, "parallelism": "frames sharded by rank, no data-path collective",
+                "l2": "working set per step (%d MB of frames + pyramid + blurred planes) exceeds the 126 MB L2" %
+                      (B * (rows * cols + 2 * 1.2e6) / 1e6),
+            },
+            "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": int(frames.nbytes),
+                    "d2h_bytes_per_step": int(d2h), "steps": e2e_steps},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": {
+                "kernel": dom, "bound": "hbm", "achieved": stages[dom]["GB_per_s"], "peak": peak, "unit": "GB/s",
+                "frac": stages[dom]["frac_of_hbm_peak"], "traffic": None, "peak_source": peak_src,
+                "whole_step_GB_per_s": sum(ab.values()) * B * args.steps / (ms * 1e-3) / 1e9,
+            },
+            "stages": stages,
+            "keypoints_per_frame": float(counts.mean()),
+            "latency_ms_single_frame_e2e": lat_ms,
+            "hamming": {"pairs_per_s": world * nq * per / (bf_ms * 1e-3), "queries": nq, "db_rows_per_gpu": per,
+                        "ms_per_search": bf_ms, "unit": "descriptor pairs/s"},
+        }
+        # CPU baseline on rank 0 at N = 1 only (bounded sample)
+        if world == 1 and not args.no_cpu_baseline:
+            import oracle
+
+            threads = host_threads()
+            kind = "ref_fast" if oracle.lib("ref_fast") is not None else "fast"
+            sample = max(4 * threads, 16)
+            oracle.extract_batch(frames[:threads], *cfg, threads=threads, kind=kind)
+            reps_cpu, t_cpu = 0, 0.0
+            while t_cpu < 10.0 and reps_cpu < 50:
+                t0 = time.perf_counter()
+                oracle.extract_batch(frames[:sample], *cfg, threads=threads, kind=kind)
+                t_cpu += time.perf_counter() - t0
+                reps_cpu += 1
+            line["cpu_baseline"] = {
+                "value": sample * reps_cpu / t_cpu, "unit": "frames/s", "cores": threads,
+                "kind": "reference" if kind == "ref_fast" else "port",
+                "sample": "%d frames x %d passes (%.1f s), %d host threads, %s" % (
+                    sample, reps_cpu, t_cpu, threads,
+                    "reference src/ORBextractor.cc + mini-cv shim" if kind == "ref_fast" else "oracle port"),
+            }
+        print(json.dumps(line))
+    ex.close()
+    m.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

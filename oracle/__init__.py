@@ -60,6 +60,13 @@ class _Libs:
     strict = None
     fast = None
     ref = None
+    ref_fast = None
+
+
+def _bind_ref(L):
+    _bind_extractor(L, "orbref_")
+    L.orbref_extract_batch.restype = _c.c_long
+    L.orbref_extract_batch.argtypes = [_i, _f, _i, _i, _i, _vp, _i, _i, _i, _i, _vp]
 
 
 def lib(kind="strict"):
@@ -77,8 +84,14 @@ def lib(kind="strict"):
         if _Libs.ref is None:
             _Libs.ref = _load("_ref/liborbref.so")
             if _Libs.ref is not None:
-                _bind_extractor(_Libs.ref, "orbref_")
+                _bind_ref(_Libs.ref)
         return _Libs.ref
+    if kind == "ref_fast":
+        if _Libs.ref_fast is None:
+            _Libs.ref_fast = _load("_ref/liborbref_fast.so")
+            if _Libs.ref_fast is not None:
+                _bind_ref(_Libs.ref_fast)
+        return _Libs.ref_fast
     raise ValueError(kind)
 
 
@@ -106,6 +119,8 @@ def _bind_all(L):
     L.orbo_copy_make_border101.argtypes = [_vp, _i, _i, _vp, _i]
     L.orbo_fast9_16.restype = _i
     L.orbo_fast9_16.argtypes = [_vp, _i, _i, _sz, _i, _i, _vp, _i]
+    L.orbo_fast9_16_simple.restype = _i
+    L.orbo_fast9_16_simple.argtypes = [_vp, _i, _i, _sz, _i, _i, _vp, _i]
     L.orbo_gaussian_blur_7x7_s2.argtypes = [_vp, _i, _i, _sz, _vp, _sz]
     L.orbo_fast_atan2.argtypes = [_vp, _vp, _vp, _i]
     L.orbo_cv_round_f.restype = _i
@@ -140,7 +155,7 @@ class Extractor:
         self.L = lib(kind)
         if self.L is None:
             raise RuntimeError("oracle library for kind=%r is not built" % kind)
-        self.p = "orbref_" if kind == "ref" else "orbo_"
+        self.p = "orbref_" if kind.startswith("ref") else "orbo_"
         self.h = self._f("create")(nfeatures, scale_factor, nlevels, ini_th, min_th)
         self.nlevels = nlevels
         self.n = 0
@@ -228,11 +243,16 @@ def distribute(xyr, min_x, max_x, min_y, max_y, n_wanted):
 
 
 def extract_batch(imgs, nfeatures, scale_factor, nlevels, ini_th, min_th, threads, kind="fast"):
+    """Frame-parallel CPU extraction (timed baseline).  kind: 'fast'/'strict' = restated oracle, 'ref_fast'/'ref' =
+    the reference's own ORBextractor.cc (oracle/_ref)."""
     L = lib(kind)
+    if L is None:
+        raise RuntimeError("oracle library for kind=%r is not built" % kind)
     imgs = np.ascontiguousarray(imgs, np.uint8)
     n, rows, cols = imgs.shape
     counts = np.zeros(n, np.int32)
-    tot = L.orbo_extract_batch(nfeatures, scale_factor, nlevels, ini_th, min_th, imgs.ctypes.data, n, rows, cols, threads, counts.ctypes.data)
+    fn = L.orbref_extract_batch if kind.startswith("ref") else L.orbo_extract_batch
+    tot = fn(nfeatures, scale_factor, nlevels, ini_th, min_th, imgs.ctypes.data, n, rows, cols, threads, counts.ctypes.data)
     return tot, counts
 
 

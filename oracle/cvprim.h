@@ -175,8 +175,9 @@ static inline int fast_arc_measure(const uint8_t* p, ptrdiff_t step)
     return best;
 }
 
-static inline void fast9_16(const uint8_t* img, int w, int h, size_t step, int threshold, bool nms,
-                            std::vector<FastPoint>& out)
+// plain transcription of the definition above; kept as the cross-check for the optimised fast9_16 below
+static inline void fast9_16_simple(const uint8_t* img, int w, int h, size_t step, int threshold, bool nms,
+                                   std::vector<FastPoint>& out)
 {
     out.clear();
     threshold = std::min(std::max(threshold, 0), 255);
@@ -208,6 +209,74 @@ static inline void fast9_16(const uint8_t* img, int w, int h, size_t step, int t
         }
 }
 
+// Same result as fast9_16_simple, organised like cv::FAST itself so that the timed CPU baseline is not a strawman:
+// high-speed rejection on the four compass pixels (every 9-arc contains at least two of them), sliding min/max by
+// doubling for the arc measure, three rolling score rows for the 3x3 non-maximum suppression.
+static inline int fast_arc_measure_fast(const uint8_t* p, const ptrdiff_t* off, int threshold)
+{
+    const int c = p[0];
+    const int d0 = c - p[off[0]], d4 = c - p[off[4]], d8 = c - p[off[8]], d12 = c - p[off[12]];
+    const int nb = (d0 > threshold) + (d4 > threshold) + (d8 > threshold) + (d12 > threshold);
+    const int nd = (d0 < -threshold) + (d4 < -threshold) + (d8 < -threshold) + (d12 < -threshold);
+    if (nb < 2 && nd < 2) return -256;
+    int d[16], mn2[16], mx2[16], mn4[16], mx4[16];
+    for (int k = 0; k < 16; k++) d[k] = c - p[off[k]];
+    for (int k = 0; k < 16; k++) { mn2[k] = std::min(d[k], d[(k + 1) & 15]); mx2[k] = std::max(d[k], d[(k + 1) & 15]); }
+    for (int k = 0; k < 16; k++) { mn4[k] = std::min(mn2[k], mn2[(k + 2) & 15]); mx4[k] = std::max(mx2[k], mx2[(k + 2) & 15]); }
+    int a = -256, b = 256;
+    for (int k = 0; k < 16; k++) {
+        const int m8 = std::min(mn4[k], mn4[(k + 4) & 15]), x8 = std::max(mx4[k], mx4[(k + 4) & 15]);
+        a = std::max(a, std::min(m8, d[(k + 8) & 15]));
+        b = std::min(b, std::max(x8, d[(k + 8) & 15]));
+    }
+    return std::max(a, -b);
+}
+
+static inline void fast9_16(const uint8_t* img, int w, int h, size_t step, int threshold, bool nms,
+                            std::vector<FastPoint>& out)
+{
+    out.clear();
+    threshold = std::min(std::max(threshold, 0), 255);
+    if (w < 7 || h < 7) return;
+    ptrdiff_t off[16];
+    for (int k = 0; k < 16; k++) off[k] = (ptrdiff_t)kFastRing[k][1] * (ptrdiff_t)step + kFastRing[k][0];
+    thread_local std::vector<uint8_t> scoreRows;
+    thread_local std::vector<int> cornerPos;
+    scoreRows.assign((size_t)3 * w, 0);
+    cornerPos.assign((size_t)3 * (w + 1), 0);
+    uint8_t* buf[3] = {scoreRows.data(), scoreRows.data() + w, scoreRows.data() + 2 * (size_t)w};
+    int* cpbuf[3] = {cornerPos.data() + 1, cornerPos.data() + (w + 1) + 1, cornerPos.data() + 2 * (size_t)(w + 1) + 1};
+    for (int i = 3; i < h - 2; i++) {
+        uint8_t* curr = buf[(i - 3) % 3];
+        int* cpos = cpbuf[(i - 3) % 3];
+        std::memset(curr, 0, (size_t)w);
+        int ncorners = 0;
+        if (i < h - 3) {
+            const uint8_t* row = img + (size_t)i * step;
+            for (int j = 3; j < w - 3; j++) {
+                const int m = fast_arc_measure_fast(row + j, off, threshold);
+                if (m > threshold) {
+                    cpos[ncorners++] = j;
+                    curr[j] = (uint8_t)(m - 1);
+                }
+            }
+        }
+        cpos[-1] = ncorners;
+        if (i == 3) continue;
+        const uint8_t* prev = buf[(i - 4 + 3) % 3];
+        const uint8_t* pprev = buf[(i - 5 + 3) % 3];
+        const int* ppos = cpbuf[(i - 4 + 3) % 3];
+        const int np = ppos[-1];
+        for (int k = 0; k < np; k++) {
+            const int j = ppos[k];
+            const int s = prev[j];
+            if (!nms || (s > prev[j + 1] && s > prev[j - 1] && s > pprev[j - 1] && s > pprev[j] && s > pprev[j + 1] &&
+                         s > curr[j - 1] && s > curr[j] && s > curr[j + 1]))
+                out.push_back({j, i - 1, s});
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // cv::GaussianBlur 7x7, sigma 2, 8-bit, BORDER_REFLECT_101 -- OpenCV 4.x fixed-point path:
 // taps (8.8 fixed point) {18,34,48,56,48,34,18}, sum 256.  h = sum T*src (16 bit), v = sum T*h
@@ -218,23 +287,30 @@ static inline void fast9_16(const uint8_t* img, int w, int h, size_t step, int t
 static inline void gaussian_blur_7x7_s2(const uint8_t* src, int w, int h, size_t sstep,
                                         uint8_t* dst, size_t dstep)
 {
-    static const int T[7] = {18, 34, 48, 56, 48, 34, 18};
-    std::vector<uint32_t> hbuf((size_t)w * h);
+    // horizontal pass into 16-bit rows (one padded source row at a time), vertical pass over 7 of them
+    thread_local std::vector<uint16_t> hbuf;
+    thread_local std::vector<uint8_t> prow;
+    hbuf.resize((size_t)w * h);
+    prow.resize((size_t)w + 6);
     for (int y = 0; y < h; y++) {
         const uint8_t* S = src + (size_t)y * sstep;
-        for (int x = 0; x < w; x++) {
-            uint32_t a = 0;
-            for (int k = -3; k <= 3; k++) a += (uint32_t)T[k + 3] * S[reflect101(x + k, w)];
-            hbuf[(size_t)y * w + x] = a;
-        }
+        for (int k = 0; k < 3; k++) { prow[k] = S[reflect101(k - 3, w)]; prow[w + 3 + k] = S[reflect101(w + k, w)]; }
+        std::memcpy(prow.data() + 3, S, (size_t)w);
+        uint16_t* H = &hbuf[(size_t)y * w];
+        const uint8_t* P = prow.data();
+        for (int x = 0; x < w; x++)
+            H[x] = (uint16_t)(18 * (P[x] + P[x + 6]) + 34 * (P[x + 1] + P[x + 5]) + 48 * (P[x + 2] + P[x + 4]) + 56 * P[x + 3]);
     }
+    thread_local std::vector<uint8_t> orow;
+    orow.resize((size_t)w);
     for (int y = 0; y < h; y++) {
-        uint8_t* D = dst + (size_t)y * dstep;
+        const uint16_t* r[7];
+        for (int k = 0; k < 7; k++) r[k] = &hbuf[(size_t)reflect101(y + k - 3, h) * w];
         for (int x = 0; x < w; x++) {
-            uint32_t a = 0;
-            for (int k = -3; k <= 3; k++) a += (uint32_t)T[k + 3] * hbuf[(size_t)reflect101(y + k, h) * w + x];
-            D[x] = (uint8_t)((a + 32768u) >> 16);
+            const uint32_t a = 18u * (r[0][x] + r[6][x]) + 34u * (r[1][x] + r[5][x]) + 48u * (r[2][x] + r[4][x]) + 56u * r[3][x];
+            orow[x] = (uint8_t)((a + 32768u) >> 16);
         }
+        std::memcpy(dst + (size_t)y * dstep, orow.data(), (size_t)w);
     }
 }
 

@@ -33,6 +33,19 @@ int orbo_fast9_16(const uint8_t* img, int w, int h, size_t step, int threshold, 
     return n;
 }
 
+int orbo_fast9_16_simple(const uint8_t* img, int w, int h, size_t step, int threshold, int nms, int* out_xys, int cap)
+{
+    std::vector<orbo::FastPoint> v;
+    orbo::fast9_16_simple(img, w, h, step, threshold, nms != 0, v);
+    int n = (int)v.size();
+    for (int i = 0; i < n && i < cap; i++) {
+        out_xys[3 * i] = v[i].x;
+        out_xys[3 * i + 1] = v[i].y;
+        out_xys[3 * i + 2] = v[i].score;
+    }
+    return n;
+}
+
 void orbo_gaussian_blur_7x7_s2(const uint8_t* src, int w, int h, size_t sstep, uint8_t* dst, size_t dstep)
 {
     orbo::gaussian_blur_7x7_s2(src, w, h, sstep, dst, dstep);

@@ -5,6 +5,7 @@
 // Used to (a) validate oracle/orb_oracle.cc and (b) optionally as the timed CPU baseline.
 #include "ORBextractor.h"  // from /root/reference/include via -I
 #include <cstdint>
+#include <thread>
 #include <vector>
 
 struct RefKp { float x, y, size, angle, response; int octave; };
@@ -84,6 +85,32 @@ void orbref_get_pyramid(void* p, int level, uint8_t* out)
     const int pad = 19;
     for (int y = -pad; y < m.rows + pad; y++)
         std::memcpy(out + (size_t)(y + pad) * (m.cols + 2 * pad), m.data + (ptrdiff_t)y * (ptrdiff_t)m.step - pad, m.cols + 2 * pad);
+}
+
+// Frame-parallel batch for the timed CPU baseline: one ORBextractor object per worker thread, exactly how the
+// reference runs two extractors from two std::threads in stereo (src/Frame.cc:127-131).  Returns total keypoints.
+long orbref_extract_batch(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh, const uint8_t* imgs, int n,
+                          int rows, int cols, int threads, int* out_counts)
+{
+    if (threads < 1) threads = 1;
+    std::vector<long> tot(threads, 0);
+    std::vector<std::thread> th;
+    for (int t = 0; t < threads; t++)
+        th.emplace_back([&, t]() {
+            ORB_SLAM2::ORBextractor ex(nfeatures, scaleFactor, nlevels, iniTh, minTh);
+            std::vector<cv::KeyPoint> kps;
+            for (int i = t; i < n; i += threads) {
+                cv::Mat im(rows, cols, CV_8UC1, (void*)(imgs + (size_t)i * rows * cols), (size_t)cols);
+                cv::Mat mask, desc;
+                ex(im, mask, kps, desc);
+                if (out_counts) out_counts[i] = (int)kps.size();
+                tot[t] += (long)kps.size();
+            }
+        });
+    for (auto& x : th) x.join();
+    long s = 0;
+    for (long v : tot) s += v;
+    return s;
 }
 
 }  // extern "C"

@@ -84,14 +84,17 @@ class ORBextractor:
         k, d, c = self.extract_batch(image[None])
         return k[0, : c[0]].copy(), d[0, : c[0]].copy()
 
-    def extract_batch(self, images):
-        """images: (n, rows, cols) uint8 host array.  Returns (kps[n, cap], desc[n, cap, 32], counts[n])."""
+    def alloc_outputs(self, n, rows, cols):
+        cap = self.max_keypoints(rows, cols)
+        return np.zeros((n, cap), KP_DTYPE), np.zeros((n, cap, 32), np.uint8), np.zeros(n, np.int32)
+
+    def extract_batch(self, images, out=None):
+        """images: (n, rows, cols) uint8 host array.  Returns (kps[n, cap], desc[n, cap, 32], counts[n]); pass
+        out=alloc_outputs(...) to reuse host buffers across calls."""
         images = np.ascontiguousarray(images, np.uint8)
         n, rows, cols = images.shape
-        cap = self.max_keypoints(rows, cols)
-        kps = np.zeros((n, cap), KP_DTYPE)
-        desc = np.zeros((n, cap, 32), np.uint8)
-        counts = np.zeros(n, np.int32)
+        kps, desc, counts = out if out is not None else self.alloc_outputs(n, rows, cols)
+        cap = kps.shape[1]
         check(self._L.orbx_extract_batch(self._h, images.ctypes.data, n, rows, cols, cols, rows * cols, kps.ctypes.data,
                                          desc.ctypes.data, cap, counts.ctypes.data), "orbx_extract_batch")
         self._last_n = n

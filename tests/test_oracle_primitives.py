@@ -161,3 +161,17 @@ def test_atan2_vs_cv2(oracle_mod):
     x = rng.integers(-3000000, 3000000, 20000).astype(np.float32)
     ref = np.array([cv2.fastAtan2(float(a), float(b)) for a, b in zip(y, x)], np.float32)
     assert np.array_equal(_atan(L, y, x).view(np.uint32), ref.view(np.uint32))
+
+
+def test_optimised_fast_equals_plain_definition(oracle_mod):
+    """fast9_16 (rolling rows + high-speed test, used by the timed baseline) == the plain transcription."""
+    L = oracle_mod.lib()
+    rng = np.random.default_rng(4)
+    for t in range(40):
+        w, h = int(rng.integers(7, 90)), int(rng.integers(7, 90))
+        img = synth.gen_frame((h, w), t, n_rects=12, flat_regions=0) if t % 2 else rng.integers(0, 256, (h, w), dtype=np.uint8)
+        for th in (20, 7, 0, 60):
+            a = _fast(L, img, th)
+            buf = np.zeros((img.size, 3), np.int32)
+            n = L.orbo_fast9_16_simple(img.ctypes.data, w, h, img.strides[0], th, 1, buf.ctypes.data, img.size)
+            assert np.array_equal(a, buf[:n])
