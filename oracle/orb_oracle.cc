@@ -56,9 +56,11 @@ struct Oracle {
     {
         scale.resize(nl); invScale.resize(nl); sigma2.resize(nl); invSigma2.resize(nl); quota.resize(nl);
         scale[0] = 1.f; sigma2[0] = 1.f;
-        for (int i = 1; i < nl; i++) { scale[i] = scale[i - 1] * sf; sigma2[i] = scale[i] * scale[i]; }
+        // the reference keeps scaleFactor as a double member (include/ORBextractor.h): float * double -> float
+        const double sfd = (double)sf;
+        for (int i = 1; i < nl; i++) { scale[i] = (float)(scale[i - 1] * sfd); sigma2[i] = scale[i] * scale[i]; }
         for (int i = 0; i < nl; i++) { invScale[i] = 1.f / scale[i]; invSigma2[i] = 1.f / sigma2[i]; }
-        float factor = 1.f / sf;
+        float factor = (float)(1.0f / sfd);
         float want = nf * (1 - factor) / (1 - (float)std::pow((double)factor, (double)nl));
         int sum = 0;
         for (int l = 0; l < nl - 1; l++) { quota[l] = orbo::cv_round(want); sum += quota[l]; want *= factor; }

@@ -1211,9 +1211,11 @@ int orbx_create(const orbx_config* cfg, int device, orbx_handle** out)
     // src/ORBextractor.cc:445-500
     h->scale.resize(nl); h->invScale.resize(nl); h->sigma2.resize(nl); h->invSigma2.resize(nl); h->quota.resize(nl);
     h->scale[0] = 1.f; h->sigma2[0] = 1.f;
-    for (int i = 1; i < nl; i++) { h->scale[i] = h->scale[i - 1] * cfg->scale_factor; h->sigma2[i] = h->scale[i] * h->scale[i]; }
+    // the reference keeps scaleFactor as a double member (include/ORBextractor.h): float * double -> float
+    const double sfd = (double)cfg->scale_factor;
+    for (int i = 1; i < nl; i++) { h->scale[i] = (float)(h->scale[i - 1] * sfd); h->sigma2[i] = h->scale[i] * h->scale[i]; }
     for (int i = 0; i < nl; i++) { h->invScale[i] = 1.f / h->scale[i]; h->invSigma2[i] = 1.f / h->sigma2[i]; }
-    float factor = 1.f / cfg->scale_factor;
+    float factor = (float)(1.0f / sfd);
     float want = cfg->nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)nl));
     int sum = 0;
     for (int l = 0; l < nl - 1; l++) { h->quota[l] = cv_round_f(want); sum += h->quota[l]; want *= factor; }
