@@ -4,7 +4,7 @@
 //
 // Reference behaviour reproduced (paths in the reference tree):
 //   k_level0 / k_resize  ORBextractor::ComputePyramid            src/ORBextractor.cc:1635-1694
-//   k_fast_cells         cell loop of ComputeKeyPointsOctTree    src/ORBextractor.cc:1017-1122 (+ cv::FAST 9/16, NMS)
+//   k_fast_band          cell loop of ComputeKeyPointsOctTree    src/ORBextractor.cc:1017-1122 (+ cv::FAST 9/16, NMS)
 //   k_octree             DistributeOctTree / DivideNode          src/ORBextractor.cc:581-1013, :1124-1164
 //                        + IC_Angle / cv::fastAtan2              src/ORBextractor.cc:59-106, :559-570
 //   k_blur               cv::GaussianBlur 7x7 sigma 2            src/ORBextractor.cc:1587-1595
@@ -46,7 +46,8 @@ struct LevelGeom {
     long long planeBytes;
     int nCols, nRows, wCell, hCell;  // 30-px cell grid (src/ORBextractor.cc:1043-1051)
     int maxBX, maxBY;    // w - 16, h - 16
-    int cellOff;         // first CTA index of this level in k_fast_cells
+    int blurOff;         // first CTA index of this level in k_blur
+    int fastG, fastGroups, fastOff;  // k_fast_band: cells per CTA, CTAs per cell row, first CTA index of the level
     int quota;           // mnFeaturesPerLevel
     int candCap;         // capacity of the candidate list (worst case after 3x3 NMS)
     long long candOff;   // offset (in candidates) of frame 0's list of this level
@@ -62,7 +63,8 @@ struct LevelGeom {
 struct Plan {
     int nlevels, rows, cols;
     int iniTh, minTh;
-    int totalCells;
+    int totalFastUnits, totalBlurUnits;
+    int fastTileBytes, fastQCap;   // k_fast_band shared-memory carve-up
     int kpCapFrame;          // sum of nodeCap = keypoint capacity per frame
     long long pyrFrameStride;  // not used for addressing (planes are [level][frame]); kept for sizing
     long long candFrame;       // candidates per frame (sum of candCap)
@@ -136,176 +138,288 @@ __global__ void __launch_bounds__(128) k_level0(Plan plan, Buffers buf, const ui
 // ------------------------------------------------------------------------------------------------------
 // K1b: level l = cv::resize(level l-1, INTER_LINEAR) + REFLECT_101 frame, fixed point (11-bit weights):
 //   T = S[sx]*a0 + S[sx+1]*a1;  dst = (((b0*(T0>>4))>>16) + ((b1*(T1>>4))>>16) + 2) >> 2
-// Frame pixels are recomputed from the reflected destination coordinate (no second pass over the plane).
+// A thread owns one aligned 32-bit word (4 columns) of the destination buffer row -- frame columns included, their
+// source column being the reflected one -- and walks RS_ROWS interior rows: column taps and weights stay in
+// registers, the horizontally interpolated source row T1 of one output row is reused as T0 of the next whenever the
+// source row advances by one (80 % of rows at scale 1.2), and rows that the frame mirrors are stored twice.
 // ------------------------------------------------------------------------------------------------------
+constexpr int RS_ROWS = 16;
+
 __global__ void __launch_bounds__(128) k_resize(Plan plan, Buffers buf, int level)
 {
     const LevelGeom& g = plan.lv[level];
     const LevelGeom& gp = plan.lv[level - 1];
-    const int bx = 4 * (blockIdx.x * 128 + threadIdx.x);
-    if (bx >= g.pitch) return;
-    const int by = blockIdx.y, frame = blockIdx.z;
-    const int dy = reflect101(by - PAD_TOP, g.h);
-    const uint8_t* S = interior_ptr(buf.pyr, gp, frame);
-    const uint8_t* S0 = S + (long long)buf.yofs0[g.yTab + dy] * gp.pitch;
-    const uint8_t* S1 = S + (long long)buf.yofs1[g.yTab + dy] * gp.pitch;
-    const short2 b = buf.yw[g.yTab + dy];
-    uint32_t v = 0;
+    const int bx = 4 * (blockIdx.x * 32 + (threadIdx.x & 31));  // pitch is a multiple of 128: always inside the row
+    const int frame = blockIdx.z;
+    const int dy0 = (blockIdx.y * 4 + (threadIdx.x >> 5)) * RS_ROWS;
+    if (dy0 >= g.h) return;
+    const int dy1 = min(dy0 + RS_ROWS, g.h);
+    int sx[4], sx1[4];
+    short2 a[4];
 #pragma unroll
     for (int j = 0; j < 4; j++) {
         int dx = min(max(bx + j - PAD_LEFT, -EDGE), g.w - 1 + EDGE);
         dx = reflect101(dx, g.w);
-        const int sx = buf.xofs[g.xTab + dx];
-        const int sx1 = min(sx + 1, gp.w - 1);
-        const short2 a = buf.xw[g.xTab + dx];
-        const int t0 = S0[sx] * a.x + S0[sx1] * a.y;
-        const int t1 = S1[sx] * a.x + S1[sx1] * a.y;
-        const int r = (((b.x * (t0 >> 4)) >> 16) + ((b.y * (t1 >> 4)) >> 16) + 2) >> 2;
-        v |= (uint32_t)min(max(r, 0), 255) << (8 * j);
+        sx[j] = buf.xofs[g.xTab + dx];
+        sx1[j] = min(sx[j] + 1, gp.w - 1);
+        a[j] = buf.xw[g.xTab + dx];
     }
-    *reinterpret_cast<uint32_t*>(plane_ptr(buf.pyr, g, frame) + (long long)by * g.pitch + bx) = v;
+    const uint8_t* S = interior_ptr(buf.pyr, gp, frame);
+    uint8_t* D = plane_ptr(buf.pyr, g, frame) + bx;
+    int t0[4], t1[4];
+    int rowInT1 = -1;
+    for (int dy = dy0; dy < dy1; dy++) {
+        const int r0 = buf.yofs0[g.yTab + dy], r1 = buf.yofs1[g.yTab + dy];
+        const short2 b = buf.yw[g.yTab + dy];
+        if (r0 == rowInT1) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) t0[j] = t1[j];
+        } else {
+            const uint8_t* R = S + (long long)r0 * gp.pitch;
+#pragma unroll
+            for (int j = 0; j < 4; j++) t0[j] = R[sx[j]] * a[j].x + R[sx1[j]] * a[j].y;
+        }
+        if (r1 == r0) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) t1[j] = t0[j];
+        } else {
+            const uint8_t* R = S + (long long)r1 * gp.pitch;
+#pragma unroll
+            for (int j = 0; j < 4; j++) t1[j] = R[sx[j]] * a[j].x + R[sx1[j]] * a[j].y;
+        }
+        rowInT1 = r1;
+        uint32_t v = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int r = (((b.x * (t0[j] >> 4)) >> 16) + ((b.y * (t1[j] >> 4)) >> 16) + 2) >> 2;
+            v |= (uint32_t)min(max(r, 0), 255) << (8 * j);
+        }
+        *reinterpret_cast<uint32_t*>(D + (long long)(PAD_TOP + dy) * g.pitch) = v;
+        if (dy >= 1 && dy <= EDGE) *reinterpret_cast<uint32_t*>(D + (long long)(PAD_TOP - dy) * g.pitch) = v;
+        if (dy >= g.h - 1 - EDGE && dy <= g.h - 2)
+            *reinterpret_cast<uint32_t*>(D + (long long)(PAD_TOP + 2 * (g.h - 1) - dy) * g.pitch) = v;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------------
-// K2: FAST-9/16 per 30-px cell with the iniThFAST -> minThFAST retry.  One CTA per (cell, frame).
+// K2: FAST-9/16 per 30-px cell with the iniThFAST -> minThFAST retry.  One CTA per band = up to fastG horizontally
+// adjacent cells of one cell row (<= 124 px wide), 256 threads, lane = one aligned 32-bit word (4 pixels) of a row.
 //   score S(p) = max over the 16 contiguous 9-arcs of max(min d, min -d) - 1, corner at t <=> S >= t;
-//   3x3 NMS inside the cell's evaluated region only (cv::FAST is run on the cell ROI);
+//   3x3 NMS inside each cell's evaluated region only (cv::FAST is run on the cell ROI);
 //   cell output = NMS survivors with S >= ini if there is one, else survivors with S >= min.
-// Candidates are appended to the level's list in arbitrary order; the reference's order (cell row-major, then
-// pixel row-major) is carried in `ord` and only matters for response ties inside a quad-tree node.
+// Passes (all through shared memory):
+//   1. SWAR rejection on 4 pixels at a time: a 9-arc contains one pixel of every opposite ring pair, so a corner needs
+//      |I(p)-I(q)| > minTh for q in {N or S} and q in {E or W}  (VABSDIFF4 + a carry trick; ~90 % of pixels stop here);
+//      survivors are compacted into a queue.
+//   2. exact score for queued pixels: the 16 ring differences packed as 8 x s16x2, sliding min/max over windows of 9
+//      as min3(min3) with VIMNMX3.S16x2.
+//   3. NMS for corners only (sparse), per-cell ini/min decision, unordered append to the level's candidate list.
+// The reference's candidate order (cell row-major, then pixel row-major) is carried in `ord` and only matters for
+// response ties inside a quad-tree node.
 // ------------------------------------------------------------------------------------------------------
-constexpr int FAST_T = 128;
-constexpr int FAST_TP = 80;    // ROI tile pitch (bytes): cells are at most 59 px wide -> ROI <= 65 + 3 alignment bytes
-constexpr int FAST_MAXR = 66;  // max ROI rows
-constexpr int FAST_SP = 64;    // score tile pitch (eval width <= 59, + 2 halo)
+constexpr int FAST_T = 256;
+constexpr int FAST_P = 144;   // tile pitch in bytes: <= 124 + 6 px band + 3 alignment bytes, multiple of 16
+constexpr int FAST_P4 = FAST_P / 4;
+constexpr int FAST_MAXG = 4;
 
-__device__ __forceinline__ int fast_score(const uint8_t* p, int minTh)
+__device__ __forceinline__ uint32_t swap16(uint32_t v) { return __byte_perm(v, 0, 0x1032); }
+
+// exact arc measure M(p) = max over 9-arcs of max(min d, min -d), d_k = I(p) - I(ring_k)
+__device__ __forceinline__ int fast_measure_packed(const uint8_t* p)
 {
-    // ring offsets in ROI-tile coordinates (dx, dy) as in cv::FAST's 16-pixel circle
     constexpr int O[16] = {
-        3 * FAST_TP + 0, 3 * FAST_TP + 1, 2 * FAST_TP + 2, 1 * FAST_TP + 3, 0 * FAST_TP + 3, -1 * FAST_TP + 3,
-        -2 * FAST_TP + 2, -3 * FAST_TP + 1, -3 * FAST_TP + 0, -3 * FAST_TP - 1, -2 * FAST_TP - 2, -1 * FAST_TP - 3,
-        0 * FAST_TP - 3, 1 * FAST_TP - 3, 2 * FAST_TP - 2, 3 * FAST_TP - 1};
-    const int c = p[0];
-    // high-speed test: every 9-arc contains at least two of the four compass pixels
-    const int d0 = c - p[O[0]], d4 = c - p[O[4]], d8 = c - p[O[8]], d12 = c - p[O[12]];
-    const int nb = (d0 > minTh) + (d4 > minTh) + (d8 > minTh) + (d12 > minTh);
-    const int nd = (d0 < -minTh) + (d4 < -minTh) + (d8 < -minTh) + (d12 < -minTh);
-    if (nb < 2 && nd < 2) return 0;
-    int d[16];
+        3 * FAST_P + 0, 3 * FAST_P + 1, 2 * FAST_P + 2, 1 * FAST_P + 3, 0 * FAST_P + 3, -1 * FAST_P + 3,
+        -2 * FAST_P + 2, -3 * FAST_P + 1, -3 * FAST_P + 0, -3 * FAST_P - 1, -2 * FAST_P - 2, -1 * FAST_P - 3,
+        0 * FAST_P - 3, 1 * FAST_P - 3, 2 * FAST_P - 2, 3 * FAST_P - 1};
+    const uint32_t cc = (uint32_t)p[0] * 0x10001u;
+    uint32_t dp[10];  // dp[k] = (d[k], d[k+8]) as s16x2
 #pragma unroll
-    for (int k = 0; k < 16; k++) d[k] = c - p[O[k]];
-    // sliding minimum / maximum over windows of 9 by doubling (1 -> 2 -> 4 -> 8 -> 9)
-    int mn[16], mx[16];
+    for (int k = 0; k < 8; k++) dp[k] = __vsub2(cc, (uint32_t)p[O[k]] | ((uint32_t)p[O[k + 8]] << 16));
+    dp[8] = swap16(dp[0]);
+    dp[9] = swap16(dp[1]);
+    uint32_t tn[14], tx[14];  // min / max over 3 consecutive differences, (k, k+8) packed
 #pragma unroll
-    for (int k = 0; k < 16; k++) { mn[k] = min(d[k], d[(k + 1) & 15]); mx[k] = max(d[k], d[(k + 1) & 15]); }
-    int mn4[16], mx4[16];
-#pragma unroll
-    for (int k = 0; k < 16; k++) { mn4[k] = min(mn[k], mn[(k + 2) & 15]); mx4[k] = max(mx[k], mx[(k + 2) & 15]); }
-    int a = -256, b = 256;
-#pragma unroll
-    for (int k = 0; k < 16; k++) {
-        const int m8 = min(mn4[k], mn4[(k + 4) & 15]);
-        const int x8 = max(mx4[k], mx4[(k + 4) & 15]);
-        a = max(a, min(m8, d[(k + 8) & 15]));
-        b = min(b, max(x8, d[(k + 8) & 15]));
+    for (int k = 0; k < 8; k++) {
+        tn[k] = __vimin3_s16x2(dp[k], dp[k + 1], dp[k + 2]);
+        tx[k] = __vimax3_s16x2(dp[k], dp[k + 1], dp[k + 2]);
     }
-    const int m = max(a, -b);
-    return m > minTh ? m - 1 : 0;
+#pragma unroll
+    for (int k = 0; k < 6; k++) { tn[8 + k] = swap16(tn[k]); tx[8 + k] = swap16(tx[k]); }
+    uint32_t a = 0x80008000u, b = 0x7fff7fffu;  // running max of window minima / min of window maxima
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        a = __vmaxs2(a, __vimin3_s16x2(tn[k], tn[k + 3], tn[k + 6]));
+        b = __vmins2(b, __vimax3_s16x2(tx[k], tx[k + 3], tx[k + 6]));
+    }
+    const int A = max((int)(short)(a & 0xffff), (int)(short)(a >> 16));
+    const int B = min((int)(short)(b & 0xffff), (int)(short)(b >> 16));
+    return max(A, -B);
 }
 
-__global__ void __launch_bounds__(FAST_T) k_fast_cells(Plan plan, Buffers buf)
+__global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
 {
-    __shared__ __align__(16) uint8_t tile[FAST_MAXR * FAST_TP];
-    __shared__ uint8_t sc[(FAST_MAXR - 4) * FAST_SP];
-    __shared__ int sCount, sBase;
+    extern __shared__ __align__(16) unsigned char fsm[];
+    __shared__ int sQ1, sQ2, sQ3, sCnt, sBase, sPos;
+    __shared__ int sHasIni[FAST_MAXG];
 
     const int frame = blockIdx.y;
     int level = 0;
-    while (level + 1 < plan.nlevels && (int)blockIdx.x >= plan.lv[level + 1].cellOff) level++;
+    while (level + 1 < plan.nlevels && (int)blockIdx.x >= plan.lv[level + 1].fastOff) level++;
     const LevelGeom& g = plan.lv[level];
-    const int cell = blockIdx.x - g.cellOff;
-    const int ci = cell / g.nCols, cj = cell - ci * g.nCols;
+    const int unit = blockIdx.x - g.fastOff;
+    const int ci = unit / g.fastGroups, gi = unit - ci * g.fastGroups;
+    const int j0 = gi * g.fastG;
 
-    const int iniY = 16 + ci * g.hCell, iniX = 16 + cj * g.wCell;
+    const int iniY = 16 + ci * g.hCell, iniX = 16 + j0 * g.wCell;
     if (iniY >= g.maxBY - 3 || iniX >= g.maxBX - 6) return;
-    const int maxY = min(iniY + g.hCell + 6, g.maxBY), maxX = min(iniX + g.wCell + 6, g.maxBX);
-    const int rw = maxX - iniX, rh = maxY - iniY;
-    if (rw < 7 || rh < 7) return;
-    const int ew = rw - 6, eh = rh - 6;
+    const int maxY = min(iniY + g.hCell + 6, g.maxBY);
+    const int rh = maxY - iniY;
+    if (rh < 7) return;
+    int j1 = min(j0 + g.fastG - 1, g.nCols - 1);
+    while (16 + j1 * g.wCell >= g.maxBX - 6) j1--;  // cells skipped by the reference (src/ORBextractor.cc:1081)
+    const int bandEnd = min(16 + j1 * g.wCell + g.wCell + 6, g.maxBX);
+    const int bw = bandEnd - iniX;
+    if (bw < 7) return;
+    const int evalW = bw - 6, eh = rh - 6;
 
-    // stage the ROI with aligned 32-bit loads
+    uint8_t* tile = fsm;
+    uint8_t* sc = fsm + plan.fastTileBytes;
+    unsigned short* q1 = reinterpret_cast<unsigned short*>(fsm + 2 * plan.fastTileBytes);
+    unsigned short* q2 = q1 + plan.fastQCap;
+
+    // stage the band with aligned 32-bit loads, zero the score tile
     const uint8_t* interior = interior_ptr(buf.pyr, g, frame);
-    const int bcol0 = PAD_LEFT + iniX;
-    const int shift = bcol0 & 3;
-    const int nw = (shift + rw + 3) >> 2;
+    const int shift = (PAD_LEFT + iniX) & 3;
+    const int nw = (shift + bw + 3) >> 2;
     const uint8_t* rowBase = interior + (long long)iniY * g.pitch + (iniX - shift);
     for (int idx = threadIdx.x; idx < rh * nw; idx += FAST_T) {
         const int r = idx / nw, wi = idx - r * nw;
-        const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(rowBase + (long long)r * g.pitch) + wi);
-        reinterpret_cast<uint32_t*>(tile + r * FAST_TP)[wi] = v;
+        reinterpret_cast<uint32_t*>(tile + r * FAST_P)[wi] =
+            __ldg(reinterpret_cast<const uint32_t*>(rowBase + (long long)r * g.pitch) + wi);
     }
-    for (int idx = threadIdx.x; idx < (eh + 2) * FAST_SP; idx += FAST_T) sc[idx] = 0;
-    if (threadIdx.x == 0) sCount = 0;
+    for (int idx = threadIdx.x; idx < rh * (FAST_P / 16); idx += FAST_T) reinterpret_cast<uint4*>(sc)[idx] = make_uint4(0, 0, 0, 0);
+    if (threadIdx.x < FAST_MAXG) sHasIni[threadIdx.x] = 0;
+    if (threadIdx.x == 0) { sQ1 = 0; sQ2 = 0; sQ3 = 0; sCnt = 0; sPos = 0; }
     __syncthreads();
 
-    const int npx = ew * eh;
-    for (int idx = threadIdx.x; idx < npx; idx += FAST_T) {
-        const int ey = idx / ew, ex = idx - ey * ew;
-        const int s = fast_score(tile + (ey + 3) * FAST_TP + shift + ex + 3, plan.minTh);
-        sc[(ey + 1) * FAST_SP + ex + 1] = (uint8_t)s;
-    }
-    __syncthreads();
-
-    // 3x3 NMS; per-thread survivor mask (pixel k of this thread = bit k)
-    uint32_t keep = 0;
-    int hasIni = 0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int minTh = plan.minTh, iniTh = plan.iniTh;
+    // ---- pass 1: SWAR rejection, 4 pixels per lane ----
     {
-        int k = 0;
-        for (int idx = threadIdx.x; idx < npx; idx += FAST_T, k++) {
-            const int ey = idx / ew, ex = idx - ey * ew;
-            const uint8_t* q = sc + (ey + 1) * FAST_SP + ex + 1;
-            const int s = q[0];
-            if (s >= plan.minTh && s > 0 && s > q[-1] && s > q[1] && s > q[-FAST_SP - 1] && s > q[-FAST_SP] &&
-                s > q[-FAST_SP + 1] && s > q[FAST_SP - 1] && s > q[FAST_SP] && s > q[FAST_SP + 1]) {
-                keep |= 1u << k;
-                hasIni |= (s >= plan.iniTh);
+        const int txFirst = shift + 3, txEnd = shift + 3 + evalW;  // evaluated tile columns [txFirst, txEnd)
+        const int gFirst = txFirst >> 2, nG = ((txEnd - 1) >> 2) - gFirst + 1;  // <= 32 words by construction
+        const uint32_t K = (uint32_t)(0x7f - min(minTh, 0x7f)) * 0x01010101u;
+        const bool filter = minTh < 0x80;
+        const uint32_t* t32 = reinterpret_cast<const uint32_t*>(tile);
+        const int gw = gFirst + lane;
+        // bytes of this word that are evaluated pixels
+        uint32_t vmask = 0;
+#pragma unroll
+        for (int bb = 0; bb < 4; bb++)
+            if (lane < nG && 4 * gw + bb >= txFirst && 4 * gw + bb < txEnd) vmask |= 0x80u << (8 * bb);
+        for (int row = warp; row < eh; row += FAST_T / 32) {
+            const int ty = row + 3;
+            uint32_t m = 0;
+            if (vmask) {
+                const uint32_t C = t32[ty * FAST_P4 + gw];
+                const uint32_t Lw = t32[ty * FAST_P4 + gw - 1], Rw = t32[ty * FAST_P4 + gw + 1];
+                const uint32_t N = t32[(ty - 3) * FAST_P4 + gw], S = t32[(ty + 3) * FAST_P4 + gw];
+                const uint32_t W4 = __byte_perm(Lw, C, 0x4321);  // pixels x-3 .. x
+                const uint32_t E4 = __byte_perm(C, Rw, 0x6543);  // pixels x+3 .. x+6
+                if (filter) {
+                    const uint32_t an = __vabsdiffu4(C, N), as = __vabsdiffu4(C, S), aw = __vabsdiffu4(C, W4), ae = __vabsdiffu4(C, E4);
+                    // bit 7 of each byte: |d| > minTh
+                    const uint32_t gn = ((an & 0x7f7f7f7fu) + K) | an, gs = ((as & 0x7f7f7f7fu) + K) | as;
+                    const uint32_t gww = ((aw & 0x7f7f7f7fu) + K) | aw, ge = ((ae & 0x7f7f7f7fu) + K) | ae;
+                    m = (gn | gs) & (gww | ge) & vmask;
+                } else {
+                    m = vmask;
+                }
             }
+            const int cnt = __popc(m);
+            int incl = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            const int total = __shfl_sync(0xffffffffu, incl, 31);
+            if (total == 0) continue;
+            int base = 0;
+            if (lane == 0) base = atomicAdd(&sQ1, total);
+            base = __shfl_sync(0xffffffffu, base, 0) + incl - cnt;
+#pragma unroll
+            for (int bb = 0; bb < 4; bb++)
+                if (m & (0x80u << (8 * bb))) q1[base++] = (unsigned short)((ty << 8) | (4 * gw + bb));
         }
     }
-    const int anyIni = __syncthreads_or(hasIni);
-    const int thEff = anyIni ? plan.iniTh : plan.minTh;
-    // count, reserve, write
-    int mine = 0;
-    {
-        int k = 0;
-        for (int idx = threadIdx.x; idx < npx; idx += FAST_T, k++) {
-            if (!(keep >> k & 1)) continue;
-            const int ey = idx / ew, ex = idx - ey * ew;
-            if (sc[(ey + 1) * FAST_SP + ex + 1] >= thEff) mine++;
-            else keep &= ~(1u << k);
-        }
-    }
-    int local = 0;
-    if (mine) local = atomicAdd(&sCount, mine);
     __syncthreads();
-    if (threadIdx.x == 0) sBase = sCount ? atomicAdd(buf.candCount + frame * plan.nlevels + level, sCount) : 0;
+    // ---- pass 2: exact score of the queued pixels ----
+    const int n1 = sQ1;
+    for (int q = threadIdx.x; q < n1; q += FAST_T) {
+        const int e = q1[q];
+        const int ty = e >> 8, tx = e & 0xff;
+        const int mval = fast_measure_packed(tile + ty * FAST_P + tx);
+        if (mval > minTh) {
+            sc[ty * FAST_P + tx] = (uint8_t)(mval - 1);
+            q2[atomicAdd(&sQ2, 1)] = (unsigned short)e;
+        }
+    }
+    __syncthreads();
+    // ---- pass 3: 3x3 NMS inside the cell, for corners only ----
+    const int n2 = sQ2;
+    const int wCell = g.wCell;
+    for (int q = threadIdx.x; q < n2; q += FAST_T) {
+        const int e = q2[q];
+        const int ty = e >> 8, tx = e & 0xff;
+        const int ex = tx - (shift + 3);
+        const int c = (ex >= wCell) + (ex >= 2 * wCell) + (ex >= 3 * wCell);
+        const int r = ex - c * wCell;
+        const uint8_t* s0 = sc + ty * FAST_P + tx;
+        const int s = s0[0];
+        const bool hasL = r > 0, hasR = r < wCell - 1;  // neighbours in another cell's region count as 0
+        bool keep = s > 0 && s > s0[-FAST_P] && s > s0[FAST_P];
+        if (hasL) keep = keep && s > s0[-1] && s > s0[-FAST_P - 1] && s > s0[FAST_P - 1];
+        if (hasR) keep = keep && s > s0[1] && s > s0[-FAST_P + 1] && s > s0[FAST_P + 1];
+        if (keep) {
+            q1[atomicAdd(&sQ3, 1)] = (unsigned short)e;
+            if (s >= iniTh) sHasIni[c] = 1;
+        }
+    }
+    __syncthreads();
+    // ---- pass 4: per-cell threshold, count, reserve, write ----
+    const int n3 = sQ3;
+    int mine = 0;
+    for (int q = threadIdx.x; q < n3; q += FAST_T) {
+        const int e = q1[q];
+        const int ty = e >> 8, tx = e & 0xff;
+        const int ex = tx - (shift + 3);
+        const int c = (ex >= wCell) + (ex >= 2 * wCell) + (ex >= 3 * wCell);
+        mine += sc[ty * FAST_P + tx] >= (sHasIni[c] ? iniTh : minTh);
+    }
+    if (mine) atomicAdd(&sCnt, mine);
+    __syncthreads();
+    if (threadIdx.x == 0) sBase = sCnt ? atomicAdd(buf.candCount + frame * plan.nlevels + level, sCnt) : 0;
     __syncthreads();
     if (!mine) return;
     Cand* out = buf.cand + (long long)frame * plan.candFrame + g.candOff;
-    int pos = sBase + local;
-    int k = 0;
-    for (int idx = threadIdx.x; idx < npx; idx += FAST_T, k++) {
-        if (!(keep >> k & 1)) continue;
-        const int ey = idx / ew, ex = idx - ey * ew;
+    for (int q = threadIdx.x; q < n3; q += FAST_T) {
+        const int e = q1[q];
+        const int ty = e >> 8, tx = e & 0xff;
+        const int ex = tx - (shift + 3), ey = ty - 3;
+        const int c = (ex >= wCell) + (ex >= 2 * wCell) + (ex >= 3 * wCell);
+        const int s = sc[ty * FAST_P + tx];
+        if (s < (sHasIni[c] ? iniTh : minTh)) continue;
+        const int pos = sBase + atomicAdd(&sPos, 1);
         if (pos >= g.candCap) { atomicExch(buf.errFlag, 1); break; }
-        const int s = sc[(ey + 1) * FAST_SP + ex + 1];
-        const uint32_t xrel = cj * g.wCell + ex + 3, yrel = ci * g.hCell + ey + 3;
-        const uint32_t ord = ((uint32_t)cell * g.hCell + ey) * g.wCell + ex;
-        Cand c;
-        c.xy = xrel | (yrel << 16);
-        c.ro = ((uint32_t)s << 24) | (0xFFFFFFu - ord);
-        out[pos++] = c;
+        const int r = ex - c * wCell;
+        const uint32_t xrel = (j0 + c) * wCell + r + 3, yrel = ci * g.hCell + ey + 3;
+        const uint32_t cell = (uint32_t)ci * g.nCols + j0 + c;
+        const uint32_t ord = (cell * g.hCell + ey) * wCell + r;
+        Cand cd;
+        cd.xy = xrel | (yrel << 16);
+        cd.ro = ((uint32_t)s << 24) | (0xFFFFFFu - ord);
+        out[pos] = cd;
     }
 }
 
@@ -753,72 +867,85 @@ __global__ void __launch_bounds__(OCT_T) k_octree(Plan plan, Buffers buf, int no
 // ------------------------------------------------------------------------------------------------------
 // K5: 7x7 Gaussian blur, sigma 2, OpenCV 4.x fixed point: taps {18,34,48,56,48,34,18}/256, 16-bit horizontal sums,
 // 32-bit vertical sums, dst = (v + 32768) >> 16.  Reads the padded plane (its 19-px REFLECT_101 frame makes the
-// border handling implicit) and writes the interior of the blurred plane.  Tile: 128 x 32 outputs per CTA.
+// border handling implicit) and writes the interior of the blurred plane.  All levels in one launch.
+// A thread owns 4 adjacent columns and slides down BLUR_ROWS rows, two rows per step:
+//   horizontal pass on bytes with IDP.4A: h = dp4a(p[x-3..x], {18,34,48,56}) + dp4a(p[x+1..x+4], {48,34,18,0})
+//   vertical pass on row pairs packed as u16x2 with IDP.2A (two taps per instruction, 32-bit accumulate); the
+//   rounding constant is the accumulator's initial value.
 // ------------------------------------------------------------------------------------------------------
-constexpr int BLUR_T = 256;
-constexpr int BLUR_W = 128, BLUR_H = 32;
-constexpr int BLUR_IN_P = BLUR_W + 8;  // input tile pitch in bytes: 4 left + 128 + 4 right
+constexpr int BLUR_ROWS = 32;  // output rows per thread (even)
 
-__global__ void __launch_bounds__(BLUR_T) k_blur(Plan plan, Buffers buf, int level, int tilesX)
+__device__ __forceinline__ void blur_hrow(const uint8_t* row, uint32_t h[4])
 {
-    __shared__ __align__(16) uint8_t in[(BLUR_H + 6) * BLUR_IN_P];
-    __shared__ __align__(16) uint16_t hs[(BLUR_H + 6) * BLUR_W];
+    // row points at the thread's first column (4-byte aligned)
+    const uint32_t L = __ldg(reinterpret_cast<const uint32_t*>(row) - 1);
+    const uint32_t C = __ldg(reinterpret_cast<const uint32_t*>(row));
+    const uint32_t R = __ldg(reinterpret_cast<const uint32_t*>(row) + 1);
+    constexpr uint32_t TLO = 0x38302212u;  // taps 18,34,48,56 for bytes x-3..x
+    constexpr uint32_t THI = 0x00122230u;  // taps 48,34,18,0  for bytes x+1..x+4
+    h[0] = __dp4a(__funnelshift_r(C, R, 8), THI, __dp4a(__funnelshift_r(L, C, 8), TLO, 0u));
+    h[1] = __dp4a(__funnelshift_r(C, R, 16), THI, __dp4a(__funnelshift_r(L, C, 16), TLO, 0u));
+    h[2] = __dp4a(__funnelshift_r(C, R, 24), THI, __dp4a(__funnelshift_r(L, C, 24), TLO, 0u));
+    h[3] = __dp4a(R, THI, __dp4a(C, TLO, 0u));
+}
+
+__global__ void __launch_bounds__(128) k_blur(Plan plan, Buffers buf)
+{
+    int level = 0;
+    while (level + 1 < plan.nlevels && (int)blockIdx.x >= plan.lv[level + 1].blurOff) level++;
     const LevelGeom& g = plan.lv[level];
-    const int frame = blockIdx.z;
-    const int tx = blockIdx.x % tilesX, ty = blockIdx.x / tilesX;
-    const int x0 = tx * BLUR_W, y0 = ty * BLUR_H;  // interior coordinates of the tile origin
-    const uint8_t* src = interior_ptr(buf.pyr, g, frame);
-    uint8_t* dst = const_cast<uint8_t*>(interior_ptr(buf.blur, g, frame));
-    const int tid = threadIdx.x;
-    // rows y0-3 .. y0+BLUR_H+2, columns x0-4 .. x0+BLUR_W+3 as aligned words.  Rows beyond the padded plane are
-    // clamped (their values only feed outputs that are never stored).
-    constexpr int WPR = BLUR_IN_P / 4;
-    for (int idx = tid; idx < (BLUR_H + 6) * WPR; idx += BLUR_T) {
-        const int r = idx / WPR, wi = idx - r * WPR;
-        const int y = min(y0 - 3 + r, g.h - 1 + EDGE);
-        int bx = PAD_LEFT + x0 - 4 + 4 * wi;  // buffer column, multiple of 4
-        bx = min(bx, g.pitch - 4);
-        const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(src + (long long)y * g.pitch - PAD_LEFT + bx));
-        reinterpret_cast<uint32_t*>(in + r * BLUR_IN_P)[wi] = v;
-    }
-    __syncthreads();
-    // horizontal pass: 4 outputs per item
-    for (int idx = tid; idx < (BLUR_H + 6) * (BLUR_W / 4); idx += BLUR_T) {
-        const int r = idx / (BLUR_W / 4), q = idx - r * (BLUR_W / 4);
-        const uint8_t* p = in + r * BLUR_IN_P + 4 + 4 * q;  // p[0] = column x0 + 4q
-        int v[10];
+    const int frame = blockIdx.y;
+    const int unit = blockIdx.x - g.blurOff;
+    const int cgroups = (g.w + 127) >> 7;  // CTAs across (32 threads x 4 columns)
+    const int cy = unit / cgroups, cxg = unit - cy * cgroups;
+    const int x = 4 * (cxg * 32 + (threadIdx.x & 31));
+    const int y0 = (cy * 4 + (threadIdx.x >> 5)) * BLUR_ROWS;
+    if (x >= g.w || y0 >= g.h) return;
+    const int y1 = min(y0 + BLUR_ROWS, g.h);
+    const uint8_t* src = interior_ptr(buf.pyr, g, frame) + x;
+    uint8_t* dst = const_cast<uint8_t*>(interior_ptr(buf.blur, g, frame)) + x;
+    const long long pitch = g.pitch;
+    // window of 8 rows (y-3 .. y+4) as 4 vertical pairs per column
+    uint32_t P[4][4];
+    {
+        uint32_t ha[4], hb[4];
 #pragma unroll
-        for (int k = 0; k < 10; k++) v[k] = p[k - 3];
-        uint16_t o[4];
+        for (int k = 0; k < 4; k++) {
+            blur_hrow(src + (long long)(y0 - 3 + 2 * k) * pitch, ha);
+            blur_hrow(src + (long long)(y0 - 2 + 2 * k) * pitch, hb);
 #pragma unroll
-        for (int j = 0; j < 4; j++)
-            o[j] = (uint16_t)(18 * (v[j] + v[j + 6]) + 34 * (v[j + 1] + v[j + 5]) + 48 * (v[j + 2] + v[j + 4]) + 56 * v[j + 3]);
-        uint2 pk;
-        pk.x = o[0] | ((uint32_t)o[1] << 16);
-        pk.y = o[2] | ((uint32_t)o[3] << 16);
-        *reinterpret_cast<uint2*>(hs + r * BLUR_W + 4 * q) = pk;
-    }
-    __syncthreads();
-    // vertical pass: 4 outputs (one aligned word) per item
-    for (int idx = tid; idx < BLUR_H * (BLUR_W / 4); idx += BLUR_T) {
-        const int r = idx / (BLUR_W / 4), q = idx - r * (BLUR_W / 4);
-        const int y = y0 + r, x = x0 + 4 * q;
-        if (y >= g.h || x >= g.w) continue;
-        uint32_t acc[4] = {0, 0, 0, 0};
-        constexpr int T[7] = {18, 34, 48, 56, 48, 34, 18};
-#pragma unroll
-        for (int k = 0; k < 7; k++) {
-            const uint2 pk = *reinterpret_cast<const uint2*>(hs + (r + k) * BLUR_W + 4 * q);
-            acc[0] += T[k] * (pk.x & 0xffff);
-            acc[1] += T[k] * (pk.x >> 16);
-            acc[2] += T[k] * (pk.y & 0xffff);
-            acc[3] += T[k] * (pk.y >> 16);
+            for (int j = 0; j < 4; j++) P[k][j] = ha[j] | (hb[j] << 16);
         }
-        uint32_t out = 0;
+    }
+    constexpr uint32_t TA = 0x12002212u;  // lo pair taps (18,34): row y   | hi pair taps (0,18):  row y+1
+    constexpr uint32_t TB = 0x30223830u;  // (48,56) | (34,48)
+    constexpr uint32_t TC = 0x30382230u;  // (48,34) | (56,48)
+    constexpr uint32_t TD = 0x12220012u;  // (18,0)  | (34,18)
+    for (int y = y0; y < y1; y += 2) {
+        uint32_t o0 = 0, o1 = 0;
 #pragma unroll
-        for (int j = 0; j < 4; j++) out |= ((acc[j] + 32768u) >> 16) << (8 * j);
-        // the word may run up to 3 bytes past the interior into the (unused) frame area of the blurred plane
-        *reinterpret_cast<uint32_t*>(dst + (long long)y * g.pitch + x) = out;
+        for (int j = 0; j < 4; j++) {
+            uint32_t acc0 = __dp2a_lo(P[0][j], TA, 32768u);
+            uint32_t acc1 = __dp2a_hi(P[0][j], TA, 32768u);
+            acc0 = __dp2a_lo(P[1][j], TB, acc0); acc1 = __dp2a_hi(P[1][j], TB, acc1);
+            acc0 = __dp2a_lo(P[2][j], TC, acc0); acc1 = __dp2a_hi(P[2][j], TC, acc1);
+            acc0 = __dp2a_lo(P[3][j], TD, acc0); acc1 = __dp2a_hi(P[3][j], TD, acc1);
+            o0 |= ((acc0 >> 16) & 0xffu) << (8 * j);
+            o1 |= ((acc1 >> 16) & 0xffu) << (8 * j);
+        }
+        // words may run up to 3 bytes / one row past the interior into the (unused) frame area of the blurred plane
+        *reinterpret_cast<uint32_t*>(dst + (long long)y * pitch) = o0;
+        *reinterpret_cast<uint32_t*>(dst + (long long)(y + 1) * pitch) = o1;
+        if (y + 2 < y1) {
+            uint32_t ha[4], hb[4];
+            blur_hrow(src + (long long)(y + 5) * pitch, ha);
+            blur_hrow(src + (long long)(y + 6) * pitch, hb);
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                P[0][j] = P[1][j]; P[1][j] = P[2][j]; P[2][j] = P[3][j];
+                P[3][j] = ha[j] | (hb[j] << 16);
+            }
+        }
     }
 }
 
@@ -935,6 +1062,7 @@ struct orbx_handle {
     short* dTabs = nullptr;
     unsigned short* dKeyNode = nullptr;
     int octNodeCap = 0, octKeySmemCap = 0;
+    size_t fastSmem = 0;
     size_t octSmem = 0;
     int lastFrames = 0;
     bool profiling = false;
@@ -970,7 +1098,7 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
     memset(&P, 0, sizeof P);
     P.nlevels = c.nlevels; P.rows = rows; P.cols = cols; P.iniTh = c.ini_th_fast; P.minTh = c.min_th_fast;
     long long planeOff = 0, candOff = 0;
-    int cellOff = 0, kpOff = 0;
+    int fastOff = 0, kpOff = 0, fastRows = 0, fastQ = 0, blurOff = 0;
     // tables: per level >= 1: xofs[w], xw[2w], yofs0[h], yofs1[h], yw[2h] -- stored in 5 separate arrays
     std::vector<short> xofs, xw, y0v, y1v, yw;
     for (int l = 0; l < c.nlevels; l++) {
@@ -1001,7 +1129,12 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
         g.planeBytes = (long long)g.pitch * g.planeRows;
         g.planeOff = planeOff;  // finalised below once the frame capacity is known (layout [level][frame])
         planeOff += g.planeBytes;
-        g.cellOff = cellOff; cellOff += g.nCols * g.nRows;
+        g.blurOff = blurOff; blurOff += ((g.w + 127) / 128) * ((g.h + 4 * BLUR_ROWS - 1) / (4 * BLUR_ROWS));
+        g.fastG = std::max(1, std::min(FAST_MAXG, 124 / g.wCell));
+        g.fastGroups = (g.nCols + g.fastG - 1) / g.fastG;
+        g.fastOff = fastOff; fastOff += g.nRows * g.fastGroups;
+        fastRows = std::max(fastRows, g.hCell + 6);
+        fastQ = std::max(fastQ, g.hCell * std::min(g.fastG * g.wCell, 124));
         g.quota = h->quota[l];
         const int evalW = g.maxBX - minB - 6, evalH = g.maxBY - minB - 6;
         g.candCap = ((evalW + 1) / 2 + 1) * ((evalH + 1) / 2 + 1);
@@ -1039,7 +1172,10 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
             }
         }
     }
-    P.totalCells = cellOff;
+    P.totalFastUnits = fastOff;
+    P.totalBlurUnits = blurOff;
+    P.fastTileBytes = fastRows * FAST_P;
+    P.fastQCap = align_up(fastQ + 8, 8);
     P.kpCapFrame = kpOff;
     P.candFrame = candOff;
     pyrBytesPerFrame = planeOff;
@@ -1122,6 +1258,8 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
     h->octKeySmemCap = keyCap;
     h->octSmem = nodeBytes + 2 * (size_t)keyCap + 16;
     ORBX_CUDA_TRY(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->octSmem));
+    h->fastSmem = 2 * (size_t)P.fastTileBytes + 4 * (size_t)P.fastQCap;
+    ORBX_CUDA_TRY(cudaFuncSetAttribute(k_fast_band, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fastSmem));
     ORBX_CUDA_TRY(cudaMalloc(&h->dKeyNode, sizeof(unsigned short) * (size_t)P.candFrame * cap));
     h->plan = P;
     h->buf = B;
@@ -1147,7 +1285,7 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
     }
     for (int l = 1; l < P.nlevels; l++) {
         const LevelGeom& g = P.lv[l];
-        dim3 grid((g.pitch / 4 + 127) / 128, g.planeRows, n);
+        dim3 grid(g.pitch / 128, (g.h + 4 * RS_ROWS - 1) / (4 * RS_ROWS), n);
         k_resize<<<grid, 128, 0, s>>>(P, B, l);
         nl++;
     }
@@ -1156,18 +1294,14 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
         ORBX_CUDA_TRY(cudaEventRecord(h->evFork, s));
         ORBX_CUDA_TRY(cudaStreamWaitEvent(sb, h->evFork, 0));
     }
-    k_fast_cells<<<dim3(P.totalCells, n), FAST_T, 0, s>>>(P, B);
+    k_fast_band<<<dim3(P.totalFastUnits, n), FAST_T, h->fastSmem, s>>>(P, B);
     nl++;
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_OCTREE], s));
     k_octree<<<dim3(P.nlevels, n), OCT_T, h->octSmem, s>>>(P, B, h->octNodeCap, h->octKeySmemCap, h->dKeyNode, P.candFrame);
     nl++;
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_BLUR], s));
-    for (int l = 0; l < P.nlevels; l++) {
-        const LevelGeom& g = P.lv[l];
-        const int tx = (g.w + BLUR_W - 1) / BLUR_W, ty = (g.h + BLUR_H - 1) / BLUR_H;
-        k_blur<<<dim3(tx * ty, 1, n), BLUR_T, 0, sb>>>(P, B, l, tx);
-        nl++;
-    }
+    k_blur<<<dim3(P.totalBlurUnits, n), 128, 0, sb>>>(P, B);
+    nl++;
     if (!profile) {
         ORBX_CUDA_TRY(cudaEventRecord(h->evJoin, sb));
         ORBX_CUDA_TRY(cudaStreamWaitEvent(s, h->evJoin, 0));
