@@ -114,46 +114,59 @@ __device__ __forceinline__ const uint8_t* interior_ptr(const uint8_t* arena, con
 }
 
 // ------------------------------------------------------------------------------------------------------
-// K1a: level 0 = input image + REFLECT_101 frame.  One thread writes one aligned 32-bit word of a buffer row.
+// K1a: level 0 = input image + REFLECT_101 frame.  One thread writes one aligned 16-byte chunk of a buffer row; chunks
+// inside the interior are 128-bit copies when the source row is 16-byte aligned, edge chunks go byte by byte through
+// the reflected column.
 // ------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) k_level0(Plan plan, Buffers buf, const uint8_t* __restrict__ in, long long inStep,
                                                 long long inFrameStride)
 {
     const LevelGeom& g = plan.lv[0];
-    const int bx = 4 * (blockIdx.x * 128 + threadIdx.x);
+    const int bx = 16 * (blockIdx.x * 128 + threadIdx.x);
     if (bx >= g.pitch) return;
     const int by = blockIdx.y, frame = blockIdx.z;
     const int y = reflect101(by - PAD_TOP, g.h);
     const uint8_t* src = in + (long long)frame * inFrameStride + (long long)y * inStep;
-    uint32_t v = 0;
+    uint4 out;
+    const int x0 = bx - PAD_LEFT;
+    if (x0 >= 0 && x0 + 16 <= g.w && ((reinterpret_cast<uintptr_t>(src + x0) & 15) == 0)) {
+        out = __ldg(reinterpret_cast<const uint4*>(src + x0));
+    } else {
+        uint32_t v[4];
 #pragma unroll
-    for (int j = 0; j < 4; j++) {
-        int x = min(max(bx + j - PAD_LEFT, -EDGE), g.w - 1 + EDGE);
-        x = reflect101(x, g.w);
-        v |= (uint32_t)__ldg(src + x) << (8 * j);
+        for (int q = 0; q < 4; q++) {
+            uint32_t w = 0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                int x = min(max(x0 + 4 * q + j, -EDGE), g.w - 1 + EDGE);
+                x = reflect101(x, g.w);
+                w |= (uint32_t)__ldg(src + x) << (8 * j);
+            }
+            v[q] = w;
+        }
+        out = make_uint4(v[0], v[1], v[2], v[3]);
     }
-    *reinterpret_cast<uint32_t*>(plane_ptr(buf.pyr, g, frame) + (long long)by * g.pitch + bx) = v;
+    *reinterpret_cast<uint4*>(plane_ptr(buf.pyr, g, frame) + (long long)by * g.pitch + bx) = out;
 }
 
 // ------------------------------------------------------------------------------------------------------
 // K1b: level l = cv::resize(level l-1, INTER_LINEAR) + REFLECT_101 frame, fixed point (11-bit weights):
 //   T = S[sx]*a0 + S[sx+1]*a1;  dst = (((b0*(T0>>4))>>16) + ((b1*(T1>>4))>>16) + 2) >> 2
 // A thread owns one aligned 32-bit word (4 columns) of the destination buffer row -- frame columns included, their
-// source column being the reflected one -- and walks RS_ROWS interior rows: column taps and weights stay in
-// registers, the horizontally interpolated source row T1 of one output row is reused as T0 of the next whenever the
+// source column being the reflected one -- and walks rowsPerThread interior rows: column taps and weights stay in
+// registers (rowsPerThread rows per thread, fewer for small grids), the horizontally interpolated source row T1 of one output row is reused as T0 of the next whenever the
 // source row advances by one (80 % of rows at scale 1.2), and rows that the frame mirrors are stored twice.
 // ------------------------------------------------------------------------------------------------------
-constexpr int RS_ROWS = 16;
 
-__global__ void __launch_bounds__(128) k_resize(Plan plan, Buffers buf, int level)
+__global__ void __launch_bounds__(128) k_resize(Plan plan, Buffers buf, int level, int rowsPerThread)
 {
     const LevelGeom& g = plan.lv[level];
     const LevelGeom& gp = plan.lv[level - 1];
     const int bx = 4 * (blockIdx.x * 32 + (threadIdx.x & 31));  // pitch is a multiple of 128: always inside the row
     const int frame = blockIdx.z;
-    const int dy0 = (blockIdx.y * 4 + (threadIdx.x >> 5)) * RS_ROWS;
+    const int dy0 = (blockIdx.y * 4 + (threadIdx.x >> 5)) * rowsPerThread;
     if (dy0 >= g.h) return;
-    const int dy1 = min(dy0 + RS_ROWS, g.h);
+    const int dy1 = min(dy0 + rowsPerThread, g.h);
     int sx[4], sx1[4];
     short2 a[4];
 #pragma unroll
@@ -292,10 +305,14 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
     const int shift = (PAD_LEFT + iniX) & 3;
     const int nw = (shift + bw + 3) >> 2;
     const uint8_t* rowBase = interior + (long long)iniY * g.pitch + (iniX - shift);
-    for (int idx = threadIdx.x; idx < rh * nw; idx += FAST_T) {
-        const int r = idx / nw, wi = idx - r * nw;
-        reinterpret_cast<uint32_t*>(tile + r * FAST_P)[wi] =
-            __ldg(reinterpret_cast<const uint32_t*>(rowBase + (long long)r * g.pitch) + wi);
+    {
+        const int ln = threadIdx.x & 31;
+        for (int r = threadIdx.x >> 5; r < rh; r += FAST_T / 32) {
+            const uint32_t* srcRow = reinterpret_cast<const uint32_t*>(rowBase + (long long)r * g.pitch);
+            uint32_t* dstRow = reinterpret_cast<uint32_t*>(tile + r * FAST_P);
+            if (ln < nw) dstRow[ln] = __ldg(srcRow + ln);
+            if (ln + 32 < nw) dstRow[ln + 32] = __ldg(srcRow + ln + 32);
+        }
     }
     for (int idx = threadIdx.x; idx < rh * (FAST_P / 16); idx += FAST_T) reinterpret_cast<uint4*>(sc)[idx] = make_uint4(0, 0, 0, 0);
     if (threadIdx.x < FAST_MAXG) sHasIni[threadIdx.x] = 0;
@@ -317,10 +334,13 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
 #pragma unroll
         for (int bb = 0; bb < 4; bb++)
             if (lane < nG && 4 * gw + bb >= txFirst && 4 * gw + bb < txEnd) vmask |= 0x80u << (8 * bb);
-        for (int row = warp; row < eh; row += FAST_T / 32) {
-            const int ty = row + 3;
+        uint32_t ms[8];  // survivor masks of this lane's rows (eh <= 59 -> at most 8 rows per warp)
+        int cnt = 0;
+#pragma unroll
+        for (int it = 0; it < 8; it++) {
+            const int ty = warp + it * (FAST_T / 32) + 3;
             uint32_t m = 0;
-            if (vmask) {
+            if (vmask && ty < eh + 3) {
                 const uint32_t C = t32[ty * FAST_P4 + gw];
                 const uint32_t Lw = t32[ty * FAST_P4 + gw - 1], Rw = t32[ty * FAST_P4 + gw + 1];
                 const uint32_t N = t32[(ty - 3) * FAST_P4 + gw], S = t32[(ty + 3) * FAST_P4 + gw];
@@ -336,21 +356,21 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
                     m = vmask;
                 }
             }
-            const int cnt = __popc(m);
-            int incl = cnt;
+            ms[it] = m;
+            cnt += __popc(m);
+        }
+        if (cnt) {
+            int base = atomicAdd(&sQ1, cnt);
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int t = __shfl_up_sync(0xffffffffu, incl, o);
-                if (lane >= o) incl += t;
+            for (int it = 0; it < 8; it++) {
+                uint32_t m = ms[it];
+                const int ty = warp + it * (FAST_T / 32) + 3;
+                while (m) {
+                    const int bit = __ffs(m) - 1;  // 7, 15, 23 or 31
+                    m &= m - 1;
+                    q1[base++] = (unsigned short)((ty << 8) | (4 * gw + (bit >> 3)));
+                }
             }
-            const int total = __shfl_sync(0xffffffffu, incl, 31);
-            if (total == 0) continue;
-            int base = 0;
-            if (lane == 0) base = atomicAdd(&sQ1, total);
-            base = __shfl_sync(0xffffffffu, base, 0) + incl - cnt;
-#pragma unroll
-            for (int bb = 0; bb < 4; bb++)
-                if (m & (0x80u << (8 * bb))) q1[base++] = (unsigned short)((ty << 8) | (4 * gw + bb));
         }
     }
     __syncthreads();
@@ -424,7 +444,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
 }
 
 // ------------------------------------------------------------------------------------------------------
-// K3: quad-tree distribution (+ orientation epilogue).  One CTA per (level, frame).
+// K3: quad-tree distribution.  One CTA per (level, frame).
 //
 // The reference keeps a std::list of nodes and splits with push_front / erase; that list is reproduced as an
 // array in list order, rebuilt once per pass with prefix sums:
@@ -831,36 +851,15 @@ __global__ void __launch_bounds__(OCT_T) k_octree(Plan plan, Buffers buf, int no
     __syncthreads();
     if (tid == 0) buf.levelCount[frame * plan.nlevels + level] = n;
 
-    // ---- orientation: intensity centroid over the radius-15 disc, one warp per keypoint ----
-    const uint8_t* interior = interior_ptr(buf.pyr, g, frame);
-    const int lane = tid & 31, wid = tid >> 5;
-    for (int i = wid; i < n; i += OCT_T / 32) {
+    // ---- stage the picked keypoints in list order (orientation + descriptor follow in k_describe) ----
+    for (int i = tid; i < n; i += OCT_T) {
         const Cand c = cand[S.winner[i]];
-        const int x = (int)(c.xy & 0xffff) + 16, y = (int)(c.xy >> 16) + 16;
-        const uint8_t* center = interior + (long long)y * g.pitch + x;
-        const int u = lane - 15;  // lane 31 idles
-        int m10 = 0, m01 = 0;
-        if (lane < 31) {
-#pragma unroll
-            for (int v = -15; v <= 15; v++) {
-                const int av = v < 0 ? -v : v;
-                if ((u < 0 ? -u : u) <= umax_of(av)) {
-                    const int val = center[(long long)v * g.pitch + u];
-                    m10 += u * val;
-                    m01 += v * val;
-                }
-            }
-        }
-        m10 = __reduce_add_sync(0xffffffffu, m10);
-        m01 = __reduce_add_sync(0xffffffffu, m01);
-        if (lane == 0) {
-            StagedKp kp;
-            kp.x = (float)x;
-            kp.y = (float)y;
-            kp.angle = fast_atan2_dev((float)m01, (float)m10);
-            kp.response = (float)(c.ro >> 24);
-            staged[i] = kp;
-        }
+        StagedKp kp;
+        kp.x = (float)((int)(c.xy & 0xffff) + 16);
+        kp.y = (float)((int)(c.xy >> 16) + 16);
+        kp.angle = -1.f;
+        kp.response = (float)(c.ro >> 24);
+        staged[i] = kp;
     }
 }
 
@@ -950,78 +949,147 @@ __global__ void __launch_bounds__(128) k_blur(Plan plan, Buffers buf)
 }
 
 // ------------------------------------------------------------------------------------------------------
-// K6: steered BRIEF.  One warp per keypoint; lane i produces descriptor byte i (16 rotated samples).
-//   a = cosf(angle*factorPI), b = sinf(...) (glibc-exact), sample (x,y) -> (round(x*a - y*b), round(x*b + y*a))
-//   with unfused float arithmetic and round-half-even, read from the blurred level staged in shared memory.
+// K4+K6: orientation (IC_Angle) and steered BRIEF.  One warp per keypoint (a warp loops over several keypoints).
+//   orientation: the 31 rows of the radius-15 disc are staged from the pyramid level into shared memory; lane r owns row
+//     v = r - 15: 8 re-aligned words x IDP.4A against per-lane constant weight words (u masked by |u| <= umax[|v|], and
+//     the 0/1 mask itself for the row sum), m10 = sum u*I, m01 = sum v*I, __reduce_add_sync, then cv::fastAtan2 in
+//     unfused float arithmetic.
+//   descriptor: a = cosf(angle*factorPI), b = sinf(...) (glibc-exact), sample (x,y) -> (round(x*a - y*b), round(x*b + y*a))
+//     with unfused float arithmetic and round-half-even, read from the 37x37 blurred neighbourhood staged in shared
+//     memory; lane i produces descriptor byte i (16 samples).
 // Also finalises the keypoint record (level-0 coordinates, size, octave) and the per-frame count.
 // ------------------------------------------------------------------------------------------------------
 constexpr int DESC_WARPS = 4;
-constexpr int DESC_PP = 40;  // patch pitch: 37 + up to 3 alignment bytes
+constexpr int DESC_PP = 40;   // blurred patch pitch: 37 + up to 3 alignment bytes
+constexpr int ORI_PW = 9;     // raw patch pitch in words (odd: lanes reading different rows hit different banks)
+
+__device__ __forceinline__ int dp4a_u8s8(uint32_t a, uint32_t b, int c)
+{
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
 
 __global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(Plan plan, Buffers buf, orbx_keypoint* outKps,
                                                                uint8_t* outDesc, int* outCounts, int capacity)
 {
     __shared__ __align__(16) uint8_t patch[DESC_WARPS][37 * DESC_PP];
+    __shared__ __align__(16) uint32_t raw[DESC_WARPS][31 * ORI_PW + 1];
     const int frame = blockIdx.y;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int gidx = blockIdx.x * DESC_WARPS + wid;
-    const int* lc = buf.levelCount + frame * plan.nlevels;
-    int level = -1, j = 0, total = 0;
-    for (int l = 0; l < plan.nlevels; l++) {
-        const int c = lc[l];
-        if (level < 0 && gidx < total + c) { level = l; j = gidx - total; }
-        total += c;
+    __shared__ int cum[ORBX_MAX_LEVELS + 1];
+    if (threadIdx.x == 0) {
+        const int* lc = buf.levelCount + frame * plan.nlevels;
+        int acc = 0;
+        cum[0] = 0;
+        for (int l = 0; l < plan.nlevels; l++) { acc += lc[l]; cum[l + 1] = acc; }
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) outCounts[frame] = min(total, capacity);
-    if (level < 0 || gidx >= capacity) return;
-    const LevelGeom& g = plan.lv[level];
-    const StagedKp kp = buf.staged[(long long)frame * plan.kpCapFrame + g.kpOff + j];
-    const int cx = (int)kp.x, cy = (int)kp.y;
+    __syncthreads();
+    const int total = min(cum[plan.nlevels], capacity);
+    if (blockIdx.x == 0 && threadIdx.x == 0) outCounts[frame] = total;
 
-    // stage the 37x37 neighbourhood (max sample reach is 18 px) with aligned words
-    const uint8_t* img = interior_ptr(buf.blur, g, frame);
-    const int bcol0 = PAD_LEFT + cx - 18;
-    const int shift = bcol0 & 3;
-    const uint8_t* rowBase = img + (long long)(cy - 18) * g.pitch + (cx - 18 - shift);
-    uint8_t* P = patch[wid];
-    for (int idx = lane; idx < 37 * (DESC_PP / 4); idx += 32) {
-        const int r = idx / (DESC_PP / 4), wi = idx - r * (DESC_PP / 4);
-        reinterpret_cast<uint32_t*>(P + r * DESC_PP)[wi] =
-            __ldg(reinterpret_cast<const uint32_t*>(rowBase + (long long)r * g.pitch) + wi);
+    // per-lane constants of the orientation pass: row v = lane - 15, columns u = 4k + b - 16
+    const int v = lane - 15;
+    const int dmax = lane < 31 ? umax_of(v < 0 ? -v : v) : -1;
+    uint32_t wU[8], wOne[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        uint32_t a = 0, o = 0;
+#pragma unroll
+        for (int bb = 0; bb < 4; bb++) {
+            const int u = 4 * k + bb - 16;
+            const bool in = (u < 0 ? -u : u) <= dmax;
+            a |= (in ? (uint32_t)(u & 0xff) : 0u) << (8 * bb);
+            o |= (in ? 1u : 0u) << (8 * bb);
+        }
+        wU[k] = a;
+        wOne[k] = o;
     }
-    const float factorPI = 0.0174532924f;  // (float)(CV_PI/180.f)
-    const SinCosOut sc = sincosf_glibc(__fmul_rn(kp.angle, factorPI));
-    const float a = sc.c, b = sc.s;
-    // this lane's 16 pattern points
+    // this lane's 16 descriptor pattern points
     const int4 q0 = *reinterpret_cast<const int4*>(d_pattern + 32 * lane);
     const int4 q1 = *reinterpret_cast<const int4*>(d_pattern + 32 * lane + 16);
     const int words[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
-    __syncwarp();
-    const uint8_t* center = P + 18 * DESC_PP + shift + 18;
-    int val = 0;
+    uint8_t* P = patch[wid];
+    uint32_t* R = raw[wid];
+
+    for (int gidx = blockIdx.x * DESC_WARPS + wid; gidx < total; gidx += gridDim.x * DESC_WARPS) {
+        int level = 0;
+        while (gidx >= cum[level + 1]) level++;
+        const int j = gidx - cum[level];
+        const LevelGeom& g = plan.lv[level];
+        const StagedKp kp = buf.staged[(long long)frame * plan.kpCapFrame + g.kpOff + j];
+        const int cx = (int)kp.x, cy = (int)kp.y;
+        __syncwarp();
+        // ---- stage raw rows cy-15..cy+15, columns from the aligned word containing cx-16 (9 words per row) ----
+        {
+            const uint8_t* img = interior_ptr(buf.pyr, g, frame);
+            const int sh = cx & 3;  // (PAD_LEFT + cx - 16) & 3
+            const uint8_t* rowBase = img + (long long)(cy - 15) * g.pitch + (cx - 16 - sh);
+            for (int idx = lane; idx < 31 * ORI_PW; idx += 32) {
+                const int r = idx / ORI_PW, wi = idx - r * ORI_PW;
+                R[idx] = __ldg(reinterpret_cast<const uint32_t*>(rowBase + (long long)r * g.pitch) + wi);
+            }
+        }
+        // ---- stage the blurred 37x37 neighbourhood (max sample reach is 18 px) with aligned words ----
+        const int shift = (PAD_LEFT + cx - 18) & 3;
+        {
+            const uint8_t* img = interior_ptr(buf.blur, g, frame);
+            const uint8_t* rowBase = img + (long long)(cy - 18) * g.pitch + (cx - 18 - shift);
+            for (int idx = lane; idx < 37 * (DESC_PP / 4); idx += 32) {
+                const int r = idx / (DESC_PP / 4), wi = idx - r * (DESC_PP / 4);
+                reinterpret_cast<uint32_t*>(P + r * DESC_PP)[wi] =
+                    __ldg(reinterpret_cast<const uint32_t*>(rowBase + (long long)r * g.pitch) + wi);
+            }
+        }
+        __syncwarp();
+        // ---- IC_Angle ----
+        int m10 = 0, rs = 0;
+        if (lane < 31) {
+            const int sh8 = 8 * (cx & 3);
+            const uint32_t* rw = R + lane * ORI_PW;
+            uint32_t w0 = rw[0];
 #pragma unroll
-    for (int k = 0; k < 8; k++) {
-        const int wv = words[k];
-        const float x0 = (float)(signed char)(wv & 0xff), y0 = (float)(signed char)((wv >> 8) & 0xff);
-        const float x1 = (float)(signed char)((wv >> 16) & 0xff), y1 = (float)(signed char)((wv >> 24) & 0xff);
-        const int iy0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
-        const int ix0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
-        const int iy1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
-        const int ix1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
-        const int t0 = center[iy0 * DESC_PP + ix0], t1 = center[iy1 * DESC_PP + ix1];
-        val |= (t0 < t1) << k;
-    }
-    const long long o = (long long)frame * capacity + gidx;
-    outDesc[o * 32 + lane] = (uint8_t)val;
-    if (lane == 0) {
-        orbx_keypoint r;
-        r.x = level ? __fmul_rn(kp.x, g.scale) : kp.x;
-        r.y = level ? __fmul_rn(kp.y, g.scale) : kp.y;
-        r.size = (float)g.patchSize;
-        r.angle = kp.angle;
-        r.response = kp.response;
-        r.octave = level;
-        outKps[o] = r;
+            for (int k = 0; k < 8; k++) {
+                const uint32_t w1 = rw[k + 1];
+                const uint32_t px = __funnelshift_r(w0, w1, sh8);  // columns 4k-16 .. 4k-13 relative to cx
+                m10 = dp4a_u8s8(px, wU[k], m10);
+                rs = (int)__dp4a(px, wOne[k], (uint32_t)rs);
+                w0 = w1;
+            }
+        }
+        m10 = __reduce_add_sync(0xffffffffu, m10);
+        const int m01 = __reduce_add_sync(0xffffffffu, v * rs);
+        const float angle = fast_atan2_dev((float)m01, (float)m10);
+        // ---- descriptor ----
+        const float factorPI = 0.0174532924f;  // (float)(CV_PI/180.f)
+        const SinCosOut sc = sincosf_glibc(__fmul_rn(angle, factorPI));
+        const float a = sc.c, b = sc.s;
+        const uint8_t* center = P + 18 * DESC_PP + shift + 18;
+        int val = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const int wv = words[k];
+            const float x0 = (float)(signed char)(wv & 0xff), y0 = (float)(signed char)((wv >> 8) & 0xff);
+            const float x1 = (float)(signed char)((wv >> 16) & 0xff), y1 = (float)(signed char)((wv >> 24) & 0xff);
+            const int iy0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
+            const int ix0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
+            const int iy1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
+            const int ix1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
+            const int t0 = center[iy0 * DESC_PP + ix0], t1 = center[iy1 * DESC_PP + ix1];
+            val |= (t0 < t1) << k;
+        }
+        const long long o = (long long)frame * capacity + gidx;
+        outDesc[o * 32 + lane] = (uint8_t)val;
+        if (lane == 0) {
+            orbx_keypoint r;
+            r.x = level ? __fmul_rn(kp.x, g.scale) : kp.x;
+            r.y = level ? __fmul_rn(kp.y, g.scale) : kp.y;
+            r.size = (float)g.patchSize;
+            r.angle = angle;
+            r.response = kp.response;
+            r.octave = level;
+            outKps[o] = r;
+        }
     }
 }
 
@@ -1279,14 +1347,17 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_PYRAMID], s));
     {
         const LevelGeom& g = P.lv[0];
-        dim3 grid((g.pitch / 4 + 127) / 128, g.planeRows, n);
+        dim3 grid((g.pitch / 16 + 127) / 128, g.planeRows, n);
         k_level0<<<grid, 128, 0, s>>>(P, B, dIn, inStep, inFrameStride);
         nl++;
     }
     for (int l = 1; l < P.nlevels; l++) {
         const LevelGeom& g = P.lv[l];
-        dim3 grid(g.pitch / 128, (g.h + 4 * RS_ROWS - 1) / (4 * RS_ROWS), n);
-        k_resize<<<grid, 128, 0, s>>>(P, B, l);
+        // enough threads to fill the GPU: 16 rows per thread when the level is large, down to 4 for small grids
+        int rpt = 16;
+        while (rpt > 4 && (long long)(g.pitch / 4) * ((g.h + rpt - 1) / rpt) * n < 148LL * 2048) rpt >>= 1;
+        dim3 grid(g.pitch / 128, (g.h + 4 * rpt - 1) / (4 * rpt), n);
+        k_resize<<<grid, 128, 0, s>>>(P, B, l, rpt);
         nl++;
     }
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_FAST], s));
@@ -1307,7 +1378,7 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
         ORBX_CUDA_TRY(cudaStreamWaitEvent(s, h->evJoin, 0));
     }
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_DESC], s));
-    k_describe<<<dim3((capacity + DESC_WARPS - 1) / DESC_WARPS, n), DESC_WARPS * 32, 0, s>>>(P, B, dKps, dDesc, dCounts, capacity);
+    k_describe<<<dim3((capacity + 2 * DESC_WARPS - 1) / (2 * DESC_WARPS), n), DESC_WARPS * 32, 0, s>>>(P, B, dKps, dDesc, dCounts, capacity);
     nl++;
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_D2H], s));
     ORBX_CUDA_TRY(cudaGetLastError());
