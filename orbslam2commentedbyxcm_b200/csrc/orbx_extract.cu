@@ -76,6 +76,10 @@ struct Cand {  // one FAST candidate
     uint32_t ro;  // response << 24 | (0xFFFFFF - ord); ord = rank key of the reference's candidate order
 };
 
+struct FastUnit {  // one k_fast_band CTA: level, cell row, first cell column
+    short level, ci, j0, pad;
+};
+
 struct StagedKp {  // per-level keypoint between k_octree and k_describe
     float x, y;    // level pixel coordinates (integers)
     float angle;
@@ -95,6 +99,7 @@ struct Buffers {
     const short* yofs0;
     const short* yofs1;
     const short2* yw;
+    const FastUnit* fastUnits;  // [totalFastUnits]
     int* errFlag;        // device-side overflow flag
     int frames;
 };
@@ -204,8 +209,8 @@ __global__ void __launch_bounds__(128) k_resize(Plan plan, Buffers buf, int leve
         uint32_t v = 0;
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-            const int r = (((b.x * (t0[j] >> 4)) >> 16) + ((b.y * (t1[j] >> 4)) >> 16) + 2) >> 2;
-            v |= (uint32_t)min(max(r, 0), 255) << (8 * j);
+            const int r = (((b.x * (t0[j] >> 4)) >> 16) + ((b.y * (t1[j] >> 4)) >> 16) + 2) >> 2;  // in [0, 255]
+            v |= (uint32_t)r << (8 * j);
         }
         *reinterpret_cast<uint32_t*>(D + (long long)(PAD_TOP + dy) * g.pitch) = v;
         if (dy >= 1 && dy <= EDGE) *reinterpret_cast<uint32_t*>(D + (long long)(PAD_TOP - dy) * g.pitch) = v;
@@ -276,12 +281,9 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
     __shared__ int sHasIni[FAST_MAXG];
 
     const int frame = blockIdx.y;
-    int level = 0;
-    while (level + 1 < plan.nlevels && (int)blockIdx.x >= plan.lv[level + 1].fastOff) level++;
+    const FastUnit fu = buf.fastUnits[blockIdx.x];
+    const int level = fu.level, ci = fu.ci, j0 = fu.j0;
     const LevelGeom& g = plan.lv[level];
-    const int unit = blockIdx.x - g.fastOff;
-    const int ci = unit / g.fastGroups, gi = unit - ci * g.fastGroups;
-    const int j0 = gi * g.fastG;
 
     const int iniY = 16 + ci * g.hCell, iniX = 16 + j0 * g.wCell;
     if (iniY >= g.maxBY - 3 || iniX >= g.maxBX - 6) return;
@@ -970,7 +972,7 @@ __device__ __forceinline__ int dp4a_u8s8(uint32_t a, uint32_t b, int c)
     return d;
 }
 
-__global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(Plan plan, Buffers buf, orbx_keypoint* outKps,
+__global__ void __launch_bounds__(DESC_WARPS * 32, 5) k_describe(Plan plan, Buffers buf, orbx_keypoint* outKps,
                                                                uint8_t* outDesc, int* outCounts, int capacity)
 {
     __shared__ __align__(16) uint8_t patch[DESC_WARPS][37 * DESC_PP];
@@ -1020,26 +1022,33 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(Plan plan, Buffers
         const StagedKp kp = buf.staged[(long long)frame * plan.kpCapFrame + g.kpOff + j];
         const int cx = (int)kp.x, cy = (int)kp.y;
         __syncwarp();
-        // ---- stage raw rows cy-15..cy+15, columns from the aligned word containing cx-16 (9 words per row) ----
-        {
-            const uint8_t* img = interior_ptr(buf.pyr, g, frame);
-            const int sh = cx & 3;  // (PAD_LEFT + cx - 16) & 3
-            const uint8_t* rowBase = img + (long long)(cy - 15) * g.pitch + (cx - 16 - sh);
-            for (int idx = lane; idx < 31 * ORI_PW; idx += 32) {
-                const int r = idx / ORI_PW, wi = idx - r * ORI_PW;
-                R[idx] = __ldg(reinterpret_cast<const uint32_t*>(rowBase + (long long)r * g.pitch) + wi);
-            }
-        }
-        // ---- stage the blurred 37x37 neighbourhood (max sample reach is 18 px) with aligned words ----
+        // ---- stage raw rows cy-15..cy+15 (9 aligned words per row from the word containing cx-16) and the blurred 37x37
+        //      neighbourhood (10 aligned words per row); every load is issued before the first store ----
         const int shift = (PAD_LEFT + cx - 18) & 3;
         {
-            const uint8_t* img = interior_ptr(buf.blur, g, frame);
-            const uint8_t* rowBase = img + (long long)(cy - 18) * g.pitch + (cx - 18 - shift);
-            for (int idx = lane; idx < 37 * (DESC_PP / 4); idx += 32) {
-                const int r = idx / (DESC_PP / 4), wi = idx - r * (DESC_PP / 4);
-                reinterpret_cast<uint32_t*>(P + r * DESC_PP)[wi] =
-                    __ldg(reinterpret_cast<const uint32_t*>(rowBase + (long long)r * g.pitch) + wi);
+            const uint8_t* imgR = interior_ptr(buf.pyr, g, frame);
+            const uint8_t* rowR = imgR + (long long)(cy - 15) * g.pitch + (cx - 16 - (cx & 3));
+            const uint8_t* imgB = interior_ptr(buf.blur, g, frame);
+            const uint8_t* rowB = imgB + (long long)(cy - 18) * g.pitch + (cx - 18 - shift);
+            uint32_t tr[9], tb[12];
+#pragma unroll
+            for (int i = 0; i < 9; i++) {
+                const int idx = lane + 32 * i;
+                const int r = idx / ORI_PW, wi = idx - r * ORI_PW;
+                tr[i] = idx < 31 * ORI_PW ? __ldg(reinterpret_cast<const uint32_t*>(rowR + r * g.pitch) + wi) : 0u;
             }
+#pragma unroll
+            for (int i = 0; i < 12; i++) {
+                const int idx = lane + 32 * i;
+                const int r = idx / (DESC_PP / 4), wi = idx - r * (DESC_PP / 4);
+                tb[i] = idx < 37 * (DESC_PP / 4) ? __ldg(reinterpret_cast<const uint32_t*>(rowB + r * g.pitch) + wi) : 0u;
+            }
+#pragma unroll
+            for (int i = 0; i < 9; i++)
+                if (lane + 32 * i < 31 * ORI_PW) R[lane + 32 * i] = tr[i];
+#pragma unroll
+            for (int i = 0; i < 12; i++)
+                if (lane + 32 * i < 37 * (DESC_PP / 4)) reinterpret_cast<uint32_t*>(P)[lane + 32 * i] = tb[i];
         }
         __syncwarp();
         // ---- IC_Angle ----
@@ -1129,6 +1138,7 @@ struct orbx_handle {
     size_t hOutBytes = 0;
     short* dTabs = nullptr;
     unsigned short* dKeyNode = nullptr;
+    FastUnit* dFastUnits = nullptr;
     int octNodeCap = 0, octKeySmemCap = 0;
     size_t fastSmem = 0;
     size_t octSmem = 0;
@@ -1148,16 +1158,16 @@ static void free_arenas(orbx_handle* h)
 {
     cudaFree(h->buf.pyr); cudaFree(h->buf.blur); cudaFree(h->buf.cand); cudaFree(h->buf.candCount);
     cudaFree(h->buf.candCountDbg); cudaFree(h->buf.staged); cudaFree(h->buf.levelCount); cudaFree(h->buf.errFlag);
-    cudaFree(h->dTabs); cudaFree(h->dKeyNode);
+    cudaFree(h->dTabs); cudaFree(h->dKeyNode); cudaFree(h->dFastUnits);
     h->buf = Buffers{};
-    h->dTabs = nullptr; h->dKeyNode = nullptr;
+    h->dTabs = nullptr; h->dKeyNode = nullptr; h->dFastUnits = nullptr;
     if (h->gexec) { cudaGraphExecDestroy(h->gexec); h->gexec = nullptr; }
     h->havePlan = false;
     h->frameCap = 0;
 }
 
 // Level geometry, cell grids, capacities, resize tables for one image shape.
-struct TabInfo { long long nx, ny, nxw, nyw; };  // padded lengths of xofs / yofs and true lengths of the weight arrays
+struct TabInfo { long long nx, ny, nxw, nyw; std::vector<FastUnit> units; };  // padded lengths of xofs / yofs and true lengths of the weight arrays
 
 static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<short>& tabs, long long& pyrBytesPerFrame,
                       TabInfo* ti = nullptr)
@@ -1256,7 +1266,15 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
     tabs.insert(tabs.end(), y1v.begin(), y1v.end());
     tabs.insert(tabs.end(), xw.begin(), xw.end());
     tabs.insert(tabs.end(), yw.begin(), yw.end());
-    if (ti) *ti = TabInfo{(long long)xofs.size(), (long long)y0v.size(), (long long)xw.size(), (long long)yw.size()};
+    if (ti) {
+        ti->nx = (long long)xofs.size(); ti->ny = (long long)y0v.size(); ti->nxw = (long long)xw.size(); ti->nyw = (long long)yw.size();
+        ti->units.clear();
+        for (int l = 0; l < c.nlevels; l++) {
+            const LevelGeom& g = P.lv[l];
+            for (int i = 0; i < g.nRows; i++)
+                for (int gi = 0; gi < g.fastGroups; gi++) ti->units.push_back(FastUnit{(short)l, (short)i, (short)(gi * g.fastG), 0});
+        }
+    }
     P.pyrFrameStride = pyrBytesPerFrame;
     return ORBX_OK;
 }
@@ -1297,6 +1315,10 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
     ORBX_CUDA_TRY(cudaMalloc(&h->dTabs, sizeof(short) * std::max<size_t>(tabs.size(), 2)));
     ORBX_CUDA_TRY(cudaMemcpyAsync(h->dTabs, tabs.data(), sizeof(short) * tabs.size(), cudaMemcpyHostToDevice, h->stream));
     // xw / yw hold 2 shorts per destination column / row, indexed by xTab + dx / yTab + dy
+    ORBX_CUDA_TRY(cudaMalloc(&h->dFastUnits, sizeof(FastUnit) * std::max<size_t>(ti.units.size(), 1)));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(h->dFastUnits, ti.units.data(), sizeof(FastUnit) * ti.units.size(), cudaMemcpyHostToDevice, h->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));  // ti.units is a local
+    B.fastUnits = h->dFastUnits;
     B.xofs = h->dTabs;
     B.yofs0 = h->dTabs + ti.nx;
     B.yofs1 = h->dTabs + ti.nx + ti.ny;
