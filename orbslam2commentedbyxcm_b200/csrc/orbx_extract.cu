@@ -433,7 +433,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
         const int s = sc[ty * FAST_P + tx];
         if (s < (sHasIni[c] ? iniTh : minTh)) continue;
         const int pos = sBase + atomicAdd(&sPos, 1);
-        if (pos >= g.candCap) { atomicExch(buf.errFlag, 1); break; }
+        if (pos >= g.candCap) { *reinterpret_cast<volatile int*>(buf.errFlag) = 1; break; }
         const int r = ex - c * wCell;
         const uint32_t xrel = (j0 + c) * wCell + r + 3, yrel = ci * g.hCell + ey + 3;
         const uint32_t cell = (uint32_t)ci * g.nCols + j0 + c;
@@ -1122,7 +1122,11 @@ struct orbx_handle {
     int device;
     std::vector<float> scale, invScale, sigma2, invSigma2;
     std::vector<int> quota;
-    cudaStream_t stream = nullptr, streamBlur = nullptr;
+    cudaStream_t stream = nullptr, streamBlur = nullptr, streamH2D = nullptr, streamD2H = nullptr;
+    cudaEvent_t evInReady[2] = {}, evInFree[2] = {};
+    std::vector<cudaEvent_t> evChunkDone;
+    int* hErrFlag = nullptr;   // mapped pinned host word written by kernels on candidate overflow
+    int* dErrFlag = nullptr;
     cudaEvent_t evFork = nullptr, evJoin = nullptr;
     cudaEvent_t evStage[ORBX_NUM_STAGES + 1] = {};
     // plan + arenas (valid for planRows x planCols, frameCap frames)
@@ -1157,7 +1161,7 @@ struct orbx_handle {
 static void free_arenas(orbx_handle* h)
 {
     cudaFree(h->buf.pyr); cudaFree(h->buf.blur); cudaFree(h->buf.cand); cudaFree(h->buf.candCount);
-    cudaFree(h->buf.candCountDbg); cudaFree(h->buf.staged); cudaFree(h->buf.levelCount); cudaFree(h->buf.errFlag);
+    cudaFree(h->buf.candCountDbg); cudaFree(h->buf.staged); cudaFree(h->buf.levelCount);
     cudaFree(h->dTabs); cudaFree(h->dKeyNode); cudaFree(h->dFastUnits);
     h->buf = Buffers{};
     h->dTabs = nullptr; h->dKeyNode = nullptr; h->dFastUnits = nullptr;
@@ -1310,8 +1314,7 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
     ORBX_CUDA_TRY(cudaMalloc(&B.staged, sizeof(StagedKp) * (size_t)P.kpCapFrame * cap));
     ORBX_CUDA_TRY(cudaMalloc(&B.levelCount, sizeof(int) * (size_t)P.nlevels * cap));
     ORBX_CUDA_TRY(cudaMemsetAsync(B.levelCount, 0, sizeof(int) * (size_t)P.nlevels * cap, h->stream));
-    ORBX_CUDA_TRY(cudaMalloc(&B.errFlag, sizeof(int)));
-    ORBX_CUDA_TRY(cudaMemsetAsync(B.errFlag, 0, sizeof(int), h->stream));
+    B.errFlag = h->dErrFlag;
     ORBX_CUDA_TRY(cudaMalloc(&h->dTabs, sizeof(short) * std::max<size_t>(tabs.size(), 2)));
     ORBX_CUDA_TRY(cudaMemcpyAsync(h->dTabs, tabs.data(), sizeof(short) * tabs.size(), cudaMemcpyHostToDevice, h->stream));
     // xw / yw hold 2 shorts per destination column / row, indexed by xTab + dx / yTab + dy
@@ -1450,6 +1453,14 @@ int orbx_create(const orbx_config* cfg, int device, orbx_handle** out)
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->streamBlur, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->streamH2D, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->streamD2H, cudaStreamNonBlocking);
+    for (int i = 0; i < 2 && e == cudaSuccess; i++) {
+        e = cudaEventCreateWithFlags(&h->evInReady[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->evInFree[i], cudaEventDisableTiming);
+    }
+    if (e == cudaSuccess) e = cudaHostAlloc((void**)&h->hErrFlag, sizeof(int), cudaHostAllocMapped);
+    if (e == cudaSuccess) { *h->hErrFlag = 0; e = cudaHostGetDevicePointer((void**)&h->dErrFlag, h->hErrFlag, 0); }
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->evFork, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->evJoin, cudaEventDisableTiming);
     for (int i = 0; i <= ORBX_NUM_STAGES && e == cudaSuccess; i++) e = cudaEventCreate(&h->evStage[i]);
@@ -1476,6 +1487,11 @@ void orbx_destroy(orbx_handle* h)
     if (h->evJoin) cudaEventDestroy(h->evJoin);
     if (h->stream) cudaStreamDestroy(h->stream);
     if (h->streamBlur) cudaStreamDestroy(h->streamBlur);
+    if (h->streamH2D) cudaStreamDestroy(h->streamH2D);
+    if (h->streamD2H) cudaStreamDestroy(h->streamD2H);
+    for (int i = 0; i < 2; i++) { if (h->evInReady[i]) cudaEventDestroy(h->evInReady[i]); if (h->evInFree[i]) cudaEventDestroy(h->evInFree[i]); }
+    for (auto& ev : h->evChunkDone) cudaEventDestroy(ev);
+    if (h->hErrFlag) cudaFreeHost(h->hErrFlag);
     delete h;
 }
 
@@ -1508,11 +1524,7 @@ int orbx_sync(orbx_handle* h)
     if (!h) { set_error("null handle"); return ORBX_ERR_BAD_ARG; }
     ORBX_CUDA_TRY(cudaSetDevice(h->device));
     ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
-    int err = 0;
-    if (h->havePlan) {
-        ORBX_CUDA_TRY(cudaMemcpy(&err, h->buf.errFlag, sizeof(int), cudaMemcpyDeviceToHost));
-        if (err) { set_error("candidate list overflow on device"); return ORBX_ERR_CAPACITY; }
-    }
+    if (*h->hErrFlag) { *h->hErrFlag = 0; set_error("candidate list overflow on device"); return ORBX_ERR_CAPACITY; }
     return ORBX_OK;
 }
 
@@ -1558,6 +1570,24 @@ int orbx_extract_batch_device(orbx_handle* h, const uint8_t* d_imgs, int n, int 
     return ORBX_OK;
 }
 
+// Host entry point.  Small batches: one H2D, one graph launch, one D2H.  Large batches are cut into chunks of
+// PIPE_CHUNK frames and software-pipelined over three streams (H2D of chunk k+1 | kernels of chunk k | D2H + copy-out of
+// chunk k-1), so that PCIe transfers, which dominate the end-to-end time, overlap the kernels.
+static const int PIPE_CHUNK = 32;
+
+static int copy_in(orbx_handle* h, uint8_t* dDst, const uint8_t* imgs, int n, int rows, int cols, size_t step, size_t frame_stride,
+                   cudaStream_t st)
+{
+    if (step == (size_t)cols && frame_stride == (size_t)rows * cols) {
+        ORBX_CUDA_TRY(cudaMemcpyAsync(dDst, imgs, (size_t)n * rows * cols, cudaMemcpyHostToDevice, st));
+    } else {
+        for (int i = 0; i < n; i++)
+            ORBX_CUDA_TRY(cudaMemcpy2DAsync(dDst + (size_t)i * rows * cols, cols, imgs + (size_t)i * frame_stride, step, cols, rows,
+                                            cudaMemcpyHostToDevice, st));
+    }
+    return ORBX_OK;
+}
+
 int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int cols, size_t step, size_t frame_stride,
                        orbx_keypoint* kps, uint8_t* desc, int capacity, int* counts)
 {
@@ -1566,17 +1596,20 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
         return ORBX_ERR_BAD_ARG;
     }
     ORBX_CUDA_TRY(cudaSetDevice(h->device));
-    int rc = ensure_plan(h, rows, cols, n);
+    const bool piped = !h->profiling && n > PIPE_CHUNK + PIPE_CHUNK / 2;
+    const int chunk = piped ? PIPE_CHUNK : n;
+    int rc = ensure_plan(h, rows, cols, chunk);
     if (rc != ORBX_OK) return rc;
     if (capacity < h->plan.kpCapFrame) {
         set_error("orbx_extract_batch: capacity %d < orbx_max_keypoints() = %d", capacity, h->plan.kpCapFrame);
         return ORBX_ERR_CAPACITY;
     }
     const int devCap = h->plan.kpCapFrame;
-    // device staging for input and packed output [counts | kps | desc]
-    const size_t inBytes = (size_t)n * rows * cols;
+    // device staging for input (double buffered when pipelined) and packed output [counts | kps | desc]
+    const size_t frameBytes = (size_t)rows * cols;
+    const size_t inBytes = frameBytes * chunk * (piped ? 2 : 1);
     if (inBytes > h->dInBytes) {
-        ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+        ORBX_CUDA_TRY(cudaDeviceSynchronize());
         cudaFree(h->dIn); h->dIn = nullptr; h->dInBytes = 0;
         ORBX_CUDA_TRY(cudaMalloc(&h->dIn, inBytes));
         h->dInBytes = inBytes;
@@ -1586,7 +1619,7 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
     const size_t dsBytes = (size_t)n * devCap * 32;
     const size_t outBytes = cntBytes + kpBytes + dsBytes;
     if (outBytes > h->dOutBytes) {
-        ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+        ORBX_CUDA_TRY(cudaDeviceSynchronize());
         cudaFree(h->dOut); h->dOut = nullptr; h->dOutBytes = 0;
         if (h->hOut) { cudaFreeHost(h->hOut); h->hOut = nullptr; }
         ORBX_CUDA_TRY(cudaMalloc(&h->dOut, outBytes));
@@ -1594,38 +1627,73 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
         h->dOutBytes = outBytes;
         h->hOutBytes = outBytes;
     }
-    if (h->profiling) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_H2D], h->stream));
-    if (step == (size_t)cols && frame_stride == (size_t)rows * cols) {
-        ORBX_CUDA_TRY(cudaMemcpyAsync(h->dIn, imgs, inBytes, cudaMemcpyHostToDevice, h->stream));
-    } else {
-        for (int i = 0; i < n; i++)
-            ORBX_CUDA_TRY(cudaMemcpy2DAsync(h->dIn + (size_t)i * rows * cols, cols, imgs + (size_t)i * frame_stride, step, cols, rows,
-                                            cudaMemcpyHostToDevice, h->stream));
-    }
     int* dCounts = (int*)h->dOut;
     orbx_keypoint* dKps = (orbx_keypoint*)((char*)h->dOut + cntBytes);
     uint8_t* dDesc = (uint8_t*)h->dOut + cntBytes + kpBytes;
-    rc = orbx_extract_batch_device(h, h->dIn, n, rows, cols, (size_t)cols, (size_t)rows * cols, dKps, dDesc, devCap, dCounts);
-    if (rc != ORBX_OK) return rc;
-    ORBX_CUDA_TRY(cudaMemcpyAsync(h->hOut, h->dOut, outBytes, cudaMemcpyDeviceToHost, h->stream));
-    if (h->profiling) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_NUM_STAGES], h->stream));
-    ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
-    if (h->profiling) {
-        ORBX_CUDA_TRY(cudaEventElapsedTime(&h->stageMs[ORBX_STAGE_H2D], h->evStage[ORBX_STAGE_H2D], h->evStage[ORBX_STAGE_PYRAMID]));
-        ORBX_CUDA_TRY(cudaEventElapsedTime(&h->stageMs[ORBX_STAGE_D2H], h->evStage[ORBX_STAGE_D2H], h->evStage[ORBX_NUM_STAGES]));
-    }
     const int* hc = (const int*)h->hOut;
     const orbx_keypoint* hk = (const orbx_keypoint*)((const char*)h->hOut + cntBytes);
     const uint8_t* hd = (const uint8_t*)h->hOut + cntBytes + kpBytes;
-    for (int i = 0; i < n; i++) {
-        const int c = hc[i];
-        counts[i] = c;
-        memcpy(kps + (size_t)i * capacity, hk + (size_t)i * devCap, sizeof(orbx_keypoint) * c);
-        memcpy(desc + (size_t)i * capacity * 32, hd + (size_t)i * devCap * 32, (size_t)32 * c);
+    auto copy_out = [&](int f0, int f1) {
+        for (int i = f0; i < f1; i++) {
+            const int c = hc[i];
+            counts[i] = c;
+            memcpy(kps + (size_t)i * capacity, hk + (size_t)i * devCap, sizeof(orbx_keypoint) * c);
+            memcpy(desc + (size_t)i * capacity * 32, hd + (size_t)i * devCap * 32, (size_t)32 * c);
+        }
+    };
+    *h->hErrFlag = 0;
+
+    if (!piped) {
+        if (h->profiling) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_H2D], h->stream));
+        if ((rc = copy_in(h, h->dIn, imgs, n, rows, cols, step, frame_stride, h->stream)) != ORBX_OK) return rc;
+        rc = orbx_extract_batch_device(h, h->dIn, n, rows, cols, (size_t)cols, frameBytes, dKps, dDesc, devCap, dCounts);
+        if (rc != ORBX_OK) return rc;
+        ORBX_CUDA_TRY(cudaMemcpyAsync(h->hOut, h->dOut, outBytes, cudaMemcpyDeviceToHost, h->stream));
+        if (h->profiling) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_NUM_STAGES], h->stream));
+        ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+        if (h->profiling) {
+            ORBX_CUDA_TRY(cudaEventElapsedTime(&h->stageMs[ORBX_STAGE_H2D], h->evStage[ORBX_STAGE_H2D], h->evStage[ORBX_STAGE_PYRAMID]));
+            ORBX_CUDA_TRY(cudaEventElapsedTime(&h->stageMs[ORBX_STAGE_D2H], h->evStage[ORBX_STAGE_D2H], h->evStage[ORBX_NUM_STAGES]));
+        }
+        copy_out(0, n);
+    } else {
+        const int nchunks = (n + chunk - 1) / chunk;
+        while ((int)h->evChunkDone.size() < nchunks) {
+            cudaEvent_t e;
+            ORBX_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            h->evChunkDone.push_back(e);
+        }
+        h->lastFrames = chunk;
+        int launches = 0;
+        for (int k = 0; k < nchunks; k++) {
+            const int f0 = k * chunk, nk = std::min(chunk, n - f0), b = k & 1;
+            uint8_t* dInB = h->dIn + (size_t)b * chunk * frameBytes;
+            if (k >= 2) ORBX_CUDA_TRY(cudaStreamWaitEvent(h->streamH2D, h->evInFree[b], 0));
+            if ((rc = copy_in(h, dInB, imgs + (size_t)f0 * frame_stride, nk, rows, cols, step, frame_stride, h->streamH2D)) != ORBX_OK) return rc;
+            ORBX_CUDA_TRY(cudaEventRecord(h->evInReady[b], h->streamH2D));
+            ORBX_CUDA_TRY(cudaStreamWaitEvent(h->stream, h->evInReady[b], 0));
+            int nl = 0;
+            rc = enqueue(h, dInB, (long long)cols, (long long)frameBytes, nk, dKps + (size_t)f0 * devCap, dDesc + (size_t)f0 * devCap * 32,
+                         dCounts + f0, devCap, false, &nl);
+            if (rc != ORBX_OK) return rc;
+            launches += nl;
+            ORBX_CUDA_TRY(cudaEventRecord(h->evInFree[b], h->stream));
+            ORBX_CUDA_TRY(cudaStreamWaitEvent(h->streamD2H, h->evInFree[b], 0));
+            ORBX_CUDA_TRY(cudaMemcpyAsync((char*)h->hOut + (size_t)f0 * sizeof(int), dCounts + f0, sizeof(int) * nk, cudaMemcpyDeviceToHost, h->streamD2H));
+            ORBX_CUDA_TRY(cudaMemcpyAsync((char*)h->hOut + cntBytes + (size_t)f0 * devCap * sizeof(orbx_keypoint), dKps + (size_t)f0 * devCap,
+                                          sizeof(orbx_keypoint) * (size_t)nk * devCap, cudaMemcpyDeviceToHost, h->streamD2H));
+            ORBX_CUDA_TRY(cudaMemcpyAsync((char*)h->hOut + cntBytes + kpBytes + (size_t)f0 * devCap * 32, dDesc + (size_t)f0 * devCap * 32,
+                                          (size_t)32 * nk * devCap, cudaMemcpyDeviceToHost, h->streamD2H));
+            ORBX_CUDA_TRY(cudaEventRecord(h->evChunkDone[k], h->streamD2H));
+        }
+        h->lastLaunches = launches;
+        for (int k = 0; k < nchunks; k++) {
+            ORBX_CUDA_TRY(cudaEventSynchronize(h->evChunkDone[k]));
+            copy_out(k * chunk, std::min(n, (k + 1) * chunk));
+        }
+        ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
     }
-    int err = 0;
-    ORBX_CUDA_TRY(cudaMemcpy(&err, h->buf.errFlag, sizeof(int), cudaMemcpyDeviceToHost));
-    if (err) { set_error("candidate list overflow on device"); return ORBX_ERR_CAPACITY; }
+    if (*h->hErrFlag) { set_error("candidate list overflow on device"); return ORBX_ERR_CAPACITY; }
     return ORBX_OK;
 }
 
