@@ -26,7 +26,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-from orbslam2commentedbyxcm_b200 import synth  # noqa: E402
+from orbslam2commentedbyxcm_b200 import sharding, synth  # noqa: E402
 
 WORKLOAD = "tum"  # BASELINE.json metric: "ORB extract frames/s @640x480 1k feats"
 BATCH = 256       # frames per GPU per step
@@ -275,7 +275,8 @@ def run_ours(args):
     # ---- brute-force Hamming (config 5 shape: 2000 queries x 1M map descriptors, sharded by rank) ----
     m = pkg.ORBmatcher(0.6, True, device=local)
     ndb_total, nq = 1_000_000, 2000
-    per = ndb_total // world
+    lo, hi = sharding.db_shard(ndb_total, rank, world)
+    per = hi - lo
     db = synth.gen_descriptors(per, seed=12345 + rank)
     q, _ = synth.gen_queries(synth.gen_descriptors(4096, seed=777), nq)
     ddb = torch.from_numpy(db).to(dev)
@@ -286,7 +287,7 @@ def run_ours(args):
     mstream = torch.cuda.ExternalStream(m.stream, device=dev)
 
     def bf_step():
-        m.bruteforce_device(dq.data_ptr(), nq, ddb.data_ptr(), per, rank * per, pb.data_ptr(), pi.data_ptr(), ps.data_ptr())
+        m.bruteforce_device(dq.data_ptr(), nq, ddb.data_ptr(), per, lo, pb.data_ptr(), pi.data_ptr(), ps.data_ptr())
 
     for _ in range(3):
         bf_step()
