@@ -13,6 +13,7 @@
 #include "orbx_common.cuh"
 #include <cooperative_groups.h>
 #include <algorithm>
+#include <cstdlib>
 #include <vector>
 
 namespace cg = cooperative_groups;
@@ -51,7 +52,47 @@ constexpr int BF_T = 256;
 constexpr int BF_RQ = 4;
 constexpr int BF_TILE = 256;  // descriptors per shared-memory tile (8 KB)
 constexpr int BF_IDX_BITS = 22;
+constexpr int BF_DEFAULT_VARIANT = 1;  // 6-POPC variant: fastest on B200 (profiles/r1_bruteforce_variants.md)
 
+// 256-bit Hamming distance of (q ^ db) with fewer POPC than words: a carry-save adder on bit planes
+// (sum = a^b^c, carry = maj(a,b,c), both single LOP3) turns three population counts into two.
+//   VARIANT 0: 8 POPC (plain)          VARIANT 1: two 3:2 compressors -> 6 POPC
+//   VARIANT 2: full 8 -> 4 tree (ones, twos, fours, eights planes)
+template <int VARIANT>
+__device__ __forceinline__ int hamming_regs(const Desc& Q, const uint4& a, const uint4& b)
+{
+    const uint32_t x0 = Q.w[0] ^ a.x, x1 = Q.w[1] ^ a.y, x2 = Q.w[2] ^ a.z, x3 = Q.w[3] ^ a.w;
+    const uint32_t x4 = Q.w[4] ^ b.x, x5 = Q.w[5] ^ b.y, x6 = Q.w[6] ^ b.z, x7 = Q.w[7] ^ b.w;
+    if (VARIANT == 0) {
+        return __popc(x0) + __popc(x1) + __popc(x2) + __popc(x3) + __popc(x4) + __popc(x5) + __popc(x6) + __popc(x7);
+    } else if (VARIANT == 1) {
+        const uint32_t s1 = x0 ^ x1 ^ x2, c1 = (x0 & x1) | (x2 & (x0 | x1));
+        const uint32_t s2 = x3 ^ x4 ^ x5, c2 = (x3 & x4) | (x5 & (x3 | x4));
+        return __popc(s1) + __popc(s2) + __popc(x6) + __popc(x7) + 2 * (__popc(c1) + __popc(c2));
+    } else if (VARIANT == 3) {  // three compressors -> 5 POPC
+        const uint32_t s1 = x0 ^ x1 ^ x2, c1 = (x0 & x1) | (x2 & (x0 | x1));
+        const uint32_t s2 = x3 ^ x4 ^ x5, c2 = (x3 & x4) | (x5 & (x3 | x4));
+        const uint32_t s3 = s1 ^ s2 ^ x6, c3 = (s1 & s2) | (x6 & (s1 | s2));
+        return __popc(s3) + __popc(x7) + 2 * (__popc(c1) + __popc(c2) + __popc(c3));
+    } else if (VARIANT == 4) {  // four compressors -> 4 POPC
+        const uint32_t s1 = x0 ^ x1 ^ x2, c1 = (x0 & x1) | (x2 & (x0 | x1));
+        const uint32_t s2 = x3 ^ x4 ^ x5, c2 = (x3 & x4) | (x5 & (x3 | x4));
+        const uint32_t s3 = s1 ^ s2 ^ x6, c3 = (s1 & s2) | (x6 & (s1 | s2));
+        const uint32_t t = c1 ^ c2 ^ c3, f = (c1 & c2) | (c3 & (c1 | c2));
+        return __popc(s3) + __popc(x7) + 2 * __popc(t) + 4 * __popc(f);
+    } else {
+        const uint32_t s1 = x0 ^ x1 ^ x2, c1 = (x0 & x1) | (x2 & (x0 | x1));
+        const uint32_t s2 = x3 ^ x4 ^ x5, c2 = (x3 & x4) | (x5 & (x3 | x4));
+        const uint32_t s3 = s1 ^ s2 ^ x6, c3 = (s1 & s2) | (x6 & (s1 | s2));
+        const uint32_t ones = s3 ^ x7, c4 = s3 & x7;
+        const uint32_t t1 = c1 ^ c2 ^ c3, f1 = (c1 & c2) | (c3 & (c1 | c2));
+        const uint32_t twos = t1 ^ c4, f2 = t1 & c4;
+        const uint32_t fours = f1 ^ f2, eights = f1 & f2;
+        return __popc(ones) + 2 * __popc(twos) + 4 * __popc(fours) + 8 * __popc(eights);
+    }
+}
+
+template <int VARIANT>
 __global__ void __launch_bounds__(BF_T) k_bruteforce(const uint8_t* __restrict__ q, int nq, const uint8_t* __restrict__ db,
                                                      int ndb, int chunk, int idxOffset, int32_t* __restrict__ pBest,
                                                      int32_t* __restrict__ pIdx, int32_t* __restrict__ pSecond)
@@ -84,9 +125,7 @@ __global__ void __launch_bounds__(BF_T) k_bruteforce(const uint8_t* __restrict__
             const uint4 a = tile[2 * j], b = tile[2 * j + 1];
 #pragma unroll
             for (int r = 0; r < BF_RQ; r++) {
-                const int d = __popc(Q[r].w[0] ^ a.x) + __popc(Q[r].w[1] ^ a.y) + __popc(Q[r].w[2] ^ a.z) +
-                              __popc(Q[r].w[3] ^ a.w) + __popc(Q[r].w[4] ^ b.x) + __popc(Q[r].w[5] ^ b.y) +
-                              __popc(Q[r].w[6] ^ b.z) + __popc(Q[r].w[7] ^ b.w);
+                const int d = hamming_regs<VARIANT>(Q[r], a, b);
                 const uint32_t key = ((uint32_t)d << BF_IDX_BITS) | (jBase + j);
                 second[r] = min(second[r], max(key, best[r]));
                 best[r] = min(best[r], key);
@@ -533,7 +572,13 @@ static int bruteforce_device(orbm_context* m, const uint8_t* dq, int nq, const u
     int32_t* pBest = m->partials;
     int32_t* pIdx = pBest + (size_t)nChunks * nq;
     int32_t* pSecond = pIdx + (size_t)nChunks * nq;
-    k_bruteforce<<<dim3(nChunks, qBlocks), BF_T, 0, m->stream>>>(dq, nq, ddb, ndb, chunk, idxOffset, pBest, pIdx, pSecond);
+    static const int variant = [] { const char* e = std::getenv("ORBX_BF_VARIANT"); return e ? std::atoi(e) : BF_DEFAULT_VARIANT; }();
+    const dim3 grid(nChunks, qBlocks);
+    if (variant == 0) k_bruteforce<0><<<grid, BF_T, 0, m->stream>>>(dq, nq, ddb, ndb, chunk, idxOffset, pBest, pIdx, pSecond);
+    else if (variant == 1) k_bruteforce<1><<<grid, BF_T, 0, m->stream>>>(dq, nq, ddb, ndb, chunk, idxOffset, pBest, pIdx, pSecond);
+    else if (variant == 3) k_bruteforce<3><<<grid, BF_T, 0, m->stream>>>(dq, nq, ddb, ndb, chunk, idxOffset, pBest, pIdx, pSecond);
+    else if (variant == 4) k_bruteforce<4><<<grid, BF_T, 0, m->stream>>>(dq, nq, ddb, ndb, chunk, idxOffset, pBest, pIdx, pSecond);
+    else k_bruteforce<2><<<grid, BF_T, 0, m->stream>>>(dq, nq, ddb, ndb, chunk, idxOffset, pBest, pIdx, pSecond);
     k_merge_partials<<<(nq + 127) / 128, 128, 0, m->stream>>>(pBest, pIdx, pSecond, nChunks, nq, dBest, dIdx, dSecond);
     ORBX_CUDA_TRY(cudaGetLastError());
     return ORBX_OK;
