@@ -184,7 +184,9 @@ __global__ void __launch_bounds__(128) k_resize(Plan plan, Buffers buf, int leve
     }
     const uint8_t* S = interior_ptr(buf.pyr, gp, frame);
     uint8_t* D = plane_ptr(buf.pyr, g, frame) + bx;
-    int t0[4], t1[4];
+    // T rows are kept as T >> 4 (what the vertical pass consumes); ((b * (T >> 4)) >> 16) is the high half of
+    // (b << 16) * (T >> 4), one IMAD.HI per tap.
+    uint32_t t0[4], t1[4];
     int rowInT1 = -1;
     for (int dy = dy0; dy < dy1; dy++) {
         const int r0 = buf.yofs0[g.yTab + dy], r1 = buf.yofs1[g.yTab + dy];
@@ -195,7 +197,7 @@ __global__ void __launch_bounds__(128) k_resize(Plan plan, Buffers buf, int leve
         } else {
             const uint8_t* R = S + (long long)r0 * gp.pitch;
 #pragma unroll
-            for (int j = 0; j < 4; j++) t0[j] = R[sx[j]] * a[j].x + R[sx1[j]] * a[j].y;
+            for (int j = 0; j < 4; j++) t0[j] = (uint32_t)(R[sx[j]] * a[j].x + R[sx1[j]] * a[j].y) >> 4;
         }
         if (r1 == r0) {
 #pragma unroll
@@ -203,15 +205,14 @@ __global__ void __launch_bounds__(128) k_resize(Plan plan, Buffers buf, int leve
         } else {
             const uint8_t* R = S + (long long)r1 * gp.pitch;
 #pragma unroll
-            for (int j = 0; j < 4; j++) t1[j] = R[sx[j]] * a[j].x + R[sx1[j]] * a[j].y;
+            for (int j = 0; j < 4; j++) t1[j] = (uint32_t)(R[sx[j]] * a[j].x + R[sx1[j]] * a[j].y) >> 4;
         }
         rowInT1 = r1;
-        uint32_t v = 0;
+        const uint32_t b0 = (uint32_t)b.x << 16, b1 = (uint32_t)b.y << 16;
+        uint32_t o[4];
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const int r = (((b.x * (t0[j] >> 4)) >> 16) + ((b.y * (t1[j] >> 4)) >> 16) + 2) >> 2;  // in [0, 255]
-            v |= (uint32_t)r << (8 * j);
-        }
+        for (int j = 0; j < 4; j++) o[j] = (__umulhi(b0, t0[j]) + __umulhi(b1, t1[j]) + 2u) >> 2;  // in [0, 255]
+        const uint32_t v = __byte_perm(__byte_perm(o[0], o[1], 0x0040), __byte_perm(o[2], o[3], 0x0040), 0x5410);
         *reinterpret_cast<uint32_t*>(D + (long long)(PAD_TOP + dy) * g.pitch) = v;
         if (dy >= 1 && dy <= EDGE) *reinterpret_cast<uint32_t*>(D + (long long)(PAD_TOP - dy) * g.pitch) = v;
         if (dy >= g.h - 1 - EDGE && dy <= g.h - 2)
@@ -221,7 +222,7 @@ __global__ void __launch_bounds__(128) k_resize(Plan plan, Buffers buf, int leve
 
 // ------------------------------------------------------------------------------------------------------
 // K2: FAST-9/16 per 30-px cell with the iniThFAST -> minThFAST retry.  One CTA per band = up to fastG horizontally
-// adjacent cells of one cell row (<= 124 px wide), 256 threads, lane = one aligned 32-bit word (4 pixels) of a row.
+// adjacent cells of one cell row (<= 124 px wide), 128 threads, lane = one aligned 32-bit word (4 pixels) of a row.
 //   score S(p) = max over the 16 contiguous 9-arcs of max(min d, min -d) - 1, corner at t <=> S >= t;
 //   3x3 NMS inside each cell's evaluated region only (cv::FAST is run on the cell ROI);
 //   cell output = NMS survivors with S >= ini if there is one, else survivors with S >= min.
@@ -235,7 +236,7 @@ __global__ void __launch_bounds__(128) k_resize(Plan plan, Buffers buf, int leve
 // The reference's candidate order (cell row-major, then pixel row-major) is carried in `ord` and only matters for
 // response ties inside a quad-tree node.
 // ------------------------------------------------------------------------------------------------------
-constexpr int FAST_T = 256;
+constexpr int FAST_T = 128;
 constexpr int FAST_P = 144;   // tile pitch in bytes: <= 124 + 6 px band + 3 alignment bytes, multiple of 16
 constexpr int FAST_P4 = FAST_P / 4;
 constexpr int FAST_MAXG = 4;
@@ -336,10 +337,11 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
 #pragma unroll
         for (int bb = 0; bb < 4; bb++)
             if (lane < nG && 4 * gw + bb >= txFirst && 4 * gw + bb < txEnd) vmask |= 0x80u << (8 * bb);
-        uint32_t ms[8];  // survivor masks of this lane's rows (eh <= 59 -> at most 8 rows per warp)
+        constexpr int FAST_RPW = (59 + FAST_T / 32 - 1) / (FAST_T / 32);  // rows per warp: eh <= 59
+        uint32_t ms[FAST_RPW];  // survivor masks of this lane's rows
         int cnt = 0;
 #pragma unroll
-        for (int it = 0; it < 8; it++) {
+        for (int it = 0; it < FAST_RPW; it++) {
             const int ty = warp + it * (FAST_T / 32) + 3;
             uint32_t m = 0;
             if (vmask && ty < eh + 3) {
@@ -364,7 +366,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
         if (cnt) {
             int base = atomicAdd(&sQ1, cnt);
 #pragma unroll
-            for (int it = 0; it < 8; it++) {
+            for (int it = 0; it < FAST_RPW; it++) {
                 uint32_t m = ms[it];
                 const int ty = warp + it * (FAST_T / 32) + 3;
                 while (m) {
@@ -986,7 +988,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 5) k_describe(Plan plan, Buff
         cum[0] = 0;
         for (int l = 0; l < plan.nlevels; l++) { acc += lc[l]; cum[l + 1] = acc; }
     }
-    __syncthreads();
+    __syncthreads();  // cum and patF (filled below, before the first use after another barrier)
     const int total = min(cum[plan.nlevels], capacity);
     if (blockIdx.x == 0 && threadIdx.x == 0) outCounts[frame] = total;
 
@@ -1007,10 +1009,14 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 5) k_describe(Plan plan, Buff
         wU[k] = a;
         wOne[k] = o;
     }
-    // this lane's 16 descriptor pattern points
-    const int4 q0 = *reinterpret_cast<const int4*>(d_pattern + 32 * lane);
-    const int4 q1 = *reinterpret_cast<const int4*>(d_pattern + 32 * lane + 16);
-    const int words[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+    // pattern coordinates as floats, [pair k][lane] as (x0, y0, x1, y1): conflict-free 128-bit reads, no I2F in the loop
+    __shared__ __align__(16) float4 patF[8 * 32];
+    for (int i = threadIdx.x; i < 256; i += DESC_WARPS * 32) {
+        const int k = i >> 5, ln = i & 31;
+        const signed char* pp = d_pattern + 32 * ln + 4 * k;
+        patF[i] = make_float4((float)pp[0], (float)pp[1], (float)pp[2], (float)pp[3]);
+    }
+    __syncthreads();
     uint8_t* P = patch[wid];
     uint32_t* R = raw[wid];
 
@@ -1075,15 +1081,16 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 5) k_describe(Plan plan, Buff
         const float a = sc.c, b = sc.s;
         const uint8_t* center = P + 18 * DESC_PP + shift + 18;
         int val = 0;
+        // cvRound = round-half-even: adding 1.5 * 2^23 leaves the rounded integer in the low mantissa bits (|v| < 2^22)
+        const float RND = 12582912.f;
+        const int RNDI = 0x4B400000;
 #pragma unroll
         for (int k = 0; k < 8; k++) {
-            const int wv = words[k];
-            const float x0 = (float)(signed char)(wv & 0xff), y0 = (float)(signed char)((wv >> 8) & 0xff);
-            const float x1 = (float)(signed char)((wv >> 16) & 0xff), y1 = (float)(signed char)((wv >> 24) & 0xff);
-            const int iy0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
-            const int ix0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
-            const int iy1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
-            const int ix1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
+            const float4 pt = patF[k * 32 + lane];
+            const int iy0 = __float_as_int(__fadd_rn(__fadd_rn(__fmul_rn(pt.x, b), __fmul_rn(pt.y, a)), RND)) - RNDI;
+            const int ix0 = __float_as_int(__fadd_rn(__fsub_rn(__fmul_rn(pt.x, a), __fmul_rn(pt.y, b)), RND)) - RNDI;
+            const int iy1 = __float_as_int(__fadd_rn(__fadd_rn(__fmul_rn(pt.z, b), __fmul_rn(pt.w, a)), RND)) - RNDI;
+            const int ix1 = __float_as_int(__fadd_rn(__fsub_rn(__fmul_rn(pt.z, a), __fmul_rn(pt.w, b)), RND)) - RNDI;
             const int t0 = center[iy0 * DESC_PP + ix0], t1 = center[iy1 * DESC_PP + ix1];
             val |= (t0 < t1) << k;
         }
@@ -1403,7 +1410,7 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
         ORBX_CUDA_TRY(cudaStreamWaitEvent(s, h->evJoin, 0));
     }
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_DESC], s));
-    k_describe<<<dim3((capacity + 2 * DESC_WARPS - 1) / (2 * DESC_WARPS), n), DESC_WARPS * 32, 0, s>>>(P, B, dKps, dDesc, dCounts, capacity);
+    k_describe<<<dim3((capacity + 4 * DESC_WARPS - 1) / (4 * DESC_WARPS), n), DESC_WARPS * 32, 0, s>>>(P, B, dKps, dDesc, dCounts, capacity);
     nl++;
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_D2H], s));
     ORBX_CUDA_TRY(cudaGetLastError());
