@@ -137,6 +137,10 @@ def _bind_all(L):
         + [_f, _f, _vp]
     )
     L.orbo_stereo_rows.argtypes = [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _f, _f, _vp, _vp]
+    L.orbo_get_level_ptr.restype = _vp
+    L.orbo_get_level_ptr.argtypes = [_vp, _i, _vp]
+    L.orbo_stereo_match.restype = _i
+    L.orbo_stereo_match.argtypes = [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _f, _vp, _vp]
     L.orbo_search_by_bow.restype = _i
     L.orbo_search_by_bow.argtypes = (
         [_i, _vp, _vp, _vp, _i, _vp, _vp, _vp] + [_i, _vp, _vp, _i, _vp, _vp, _vp] + [_f, _i, _vp]
@@ -320,3 +324,30 @@ def search_by_bow(kf, fr, nnratio, check_orientation):
         nnratio, int(check_orientation), out.ctypes.data,
     )
     return n, out
+
+
+def stereo_match(exL, exR, left, right, n_rows, mbf, mb):
+    """Full ComputeStereoMatches on two oracle Extractor objects that have just extracted the left / right image."""
+    L = lib()
+    nl, nlev = len(left["x"]), exL.nlevels
+    sf = exL.scale_factors()
+    inv = np.zeros(nlev, np.float32)
+    L.orbo_get_inv_scale_factors(exL.h, inv.ctypes.data)
+    lp = (_c.c_void_p * nlev)()
+    rp = (_c.c_void_p * nlev)()
+    ls = np.zeros(nlev, np.int32)
+    rs = np.zeros(nlev, np.int32)
+    rc = np.zeros(nlev, np.int32)
+    for l in range(nlev):
+        st = _c.c_int()
+        lp[l] = L.orbo_get_level_ptr(exL.h, l, _c.byref(st)); ls[l] = st.value
+        rp[l] = L.orbo_get_level_ptr(exR.h, l, _c.byref(st)); rs[l] = st.value
+        rc[l] = exR.level_size(l)[0]
+    ur = np.zeros(max(nl, 1), np.float32)
+    dp = np.zeros(max(nl, 1), np.float32)
+    n = L.orbo_stereo_match(
+        nl, _ptr(left["x"]), _ptr(left["y"]), _ptr(left["octave"]), _ptr(left["desc"]),
+        len(right["x"]), _ptr(right["x"]), _ptr(right["y"]), _ptr(right["octave"]), _ptr(right["desc"]),
+        nlev, sf.ctypes.data, inv.ctypes.data, lp, rp, ls.ctypes.data, rs.ctypes.data, rc.ctypes.data,
+        n_rows, mbf, mb, ur.ctypes.data, dp.ctypes.data)
+    return n, ur[:nl], dp[:nl]

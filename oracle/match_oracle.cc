@@ -14,6 +14,7 @@
 //                                 + ComputeThreeMaxima :1935-1977
 //   orbo_assign_grid           <- Frame::AssignFeaturesToGrid / PosInGrid    src/Frame.cc:351-370, 558-567
 #include <cstdint>
+#include <cstddef>
 #include <cstring>
 #include <cmath>
 #include <vector>
@@ -274,3 +275,80 @@ int orbo_search_by_bow(
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Full Frame::ComputeStereoMatches (src/Frame.cc:673-885): coarse row search (orbo_stereo_rows above) + SAD refinement
+// on the pyramid levels with sub-pixel parabola fit (:767-866) + removal of matches whose SAD distance is >= 2.1 x median
+// (:868-884).  Decision D7: the fork executes the outlier block INSIDE the per-keypoint loop (indexing an empty vector on
+// the first iterations); the oracle follows upstream ORB-SLAM2 and runs it once after the loop.  Decision D5: minZ = mb.
+// Level planes are given as pointers to the interior pixel (0,0) of the padded pyramid planes.
+// ---------------------------------------------------------------------------------------------------------------------
+extern "C" int orbo_stereo_match(
+    int nl, const float* lx, const float* ly, const int32_t* loct, const uint8_t* ldesc,
+    int nr, const float* rx, const float* ry, const int32_t* roct, const uint8_t* rdesc,
+    int nlevels, const float* scaleFactors, const float* invScaleFactors,
+    const uint8_t* const* lplane, const uint8_t* const* rplane, const int32_t* lstep, const int32_t* rstep, const int32_t* rcols,
+    int nRows, float mbf, float mb, float* uRight, float* depth)
+{
+    (void)nlevels;
+    const float minZ = mb, minD = 0, maxD = mbf / minZ;
+    std::vector<int32_t> bestR(nl > 0 ? nl : 1), bestDistCoarse(nl > 0 ? nl : 1);
+    orbo_stereo_rows(nl, lx, ly, loct, ldesc, nr, rx, ry, roct, rdesc, scaleFactors, nRows, minD, maxD, bestR.data(), bestDistCoarse.data());
+    std::vector<std::pair<int, int>> vDistIdx;
+    for (int iL = 0; iL < nl; iL++) { uRight[iL] = -1.0f; depth[iL] = -1.0f; }
+    for (int iL = 0; iL < nl; iL++) {
+        if (bestR[iL] < 0) continue;
+        const int oct = loct[iL];
+        const float uL = lx[iL];
+        const float uR0 = rx[bestR[iL]];
+        const float scaleFactor = invScaleFactors[oct];
+        const float scaleduL = std::round(lx[iL] * scaleFactor);
+        const float scaledvL = std::round(ly[iL] * scaleFactor);
+        const float scaleduR0 = std::round(uR0 * scaleFactor);
+        const int w = 5, L = 5;
+        const uint8_t* PL = lplane[oct];
+        const uint8_t* PR = rplane[oct];
+        const int cvL = (int)scaledvL, cuL = (int)scaleduL;
+        const float iniu = scaleduR0 + L - w, endu = scaleduR0 + L + w + 1;
+        if (iniu < 0 || endu >= rcols[oct]) continue;
+        int bestDist = INT32_MAX, bestincR = 0;
+        float vDists[2 * 5 + 1];
+        const float centerL = (float)PL[(ptrdiff_t)cvL * lstep[oct] + cuL];
+        for (int incR = -L; incR <= L; incR++) {
+            const int cuR = (int)(scaleduR0 + incR);
+            const float centerR = (float)PR[(ptrdiff_t)cvL * rstep[oct] + cuR];
+            float dist = 0;  // cv::norm(IL, IR, NORM_L1): integer-valued, exact in float
+            for (int dy = -w; dy <= w; dy++)
+                for (int dx = -w; dx <= w; dx++) {
+                    const float a = (float)PL[(ptrdiff_t)(cvL + dy) * lstep[oct] + cuL + dx] - centerL;
+                    const float b = (float)PR[(ptrdiff_t)(cvL + dy) * rstep[oct] + cuR + dx] - centerR;
+                    dist += std::fabs(a - b);
+                }
+            if (dist < bestDist) { bestDist = (int)dist; bestincR = incR; }
+            vDists[L + incR] = dist;
+        }
+        if (bestincR == -L || bestincR == L) continue;
+        const float dist1 = vDists[L + bestincR - 1], dist2 = vDists[L + bestincR], dist3 = vDists[L + bestincR + 1];
+        const float deltaR = (dist1 - dist3) / (2.0f * (dist1 + dist3 - 2.0f * dist2));
+        if (deltaR < -1 || deltaR > 1) continue;
+        float bestuR = scaleFactors[oct] * ((float)scaleduR0 + (float)bestincR + deltaR);
+        float disparity = (uL - bestuR);
+        if (disparity >= minD && disparity < maxD) {
+            if (disparity <= 0) { disparity = 0.01; bestuR = uL - 0.01; }
+            depth[iL] = mbf / disparity;
+            uRight[iL] = bestuR;
+            vDistIdx.push_back(std::pair<int, int>(bestDist, iL));
+        }
+    }
+    if (!vDistIdx.empty()) {
+        std::sort(vDistIdx.begin(), vDistIdx.end());
+        const float median = vDistIdx[vDistIdx.size() / 2].first;
+        const float thDist = 1.5f * 1.4f * median;
+        for (int i = (int)vDistIdx.size() - 1; i >= 0; i--) {
+            if (vDistIdx[i].first < thDist) break;
+            uRight[vDistIdx[i].second] = -1;
+            depth[vDistIdx[i].second] = -1;
+        }
+    }
+    return (int)vDistIdx.size();
+}

@@ -353,6 +353,13 @@ int orbo_get_blurred(void* h, int level, uint8_t* out)
     std::copy(o->blurred[level].begin(), o->blurred[level].end(), out);
     return 1;
 }
+// pointer to interior pixel (0,0) of a padded level (valid until the next extract on this handle) and its row stride
+const uint8_t* orbo_get_level_ptr(void* h, int level, int* step)
+{
+    Oracle* o = (Oracle*)h;
+    *step = (int)o->pyr[level].step;
+    return o->pyr[level].interior();
+}
 int orbo_get_num_candidates(void* h, int level) { return (int)((Oracle*)h)->cands[level].size(); }
 // candidates in reference order, as (x, y, response) in level pixel coordinates (minBorder already added)
 void orbo_get_candidates(void* h, int level, int* out_xyr)

@@ -12,6 +12,7 @@
 // Results are bit-identical to the CPU oracle (oracle/orb_oracle.cc); tests/test_gpu_extractor.py checks that.
 #include "orbx_common.cuh"
 #include "sincosf_dev.cuh"
+#include "orbx_internal.h"
 #include <cmath>
 #include <cfloat>
 #include <cstdarg>
@@ -1417,6 +1418,23 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
     if (launches) *launches = nl;
     return ORBX_OK;
 }
+
+namespace orbx {
+int pyramid_view(orbx_handle* h, int frame, PyramidView* out)
+{
+    if (!h || !out || !h->havePlan || frame < 0 || frame >= h->lastFrames) { set_error("pyramid_view: nothing extracted / bad frame"); return ORBX_ERR_BAD_ARG; }
+    out->nlevels = h->cfg.nlevels;
+    out->device = h->device;
+    for (int l = 0; l < h->cfg.nlevels; l++) {
+        const LevelGeom& g = h->plan.lv[l];
+        out->interior[l] = h->buf.pyr + g.planeOff + (long long)frame * g.planeBytes + (long long)PAD_TOP * g.pitch + PAD_LEFT;
+        out->pitch[l] = g.pitch;
+        out->w[l] = g.w; out->h[l] = g.h;
+        out->scale[l] = h->scale[l]; out->invScale[l] = h->invScale[l];
+    }
+    return ORBX_OK;
+}
+}  // namespace orbx
 
 extern "C" {
 

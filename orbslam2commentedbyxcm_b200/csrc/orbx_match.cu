@@ -11,6 +11,7 @@
 // (distance, order) keys, reduced across lanes with warp shuffles.  sm_100a has no native b1 AND-POPC MMA
 // (SURVEY.md F10), so there is no tensor-core variant.
 #include "orbx_common.cuh"
+#include "orbx_internal.h"
 #include <cooperative_groups.h>
 #include <algorithm>
 #include <cstdlib>
@@ -355,6 +356,123 @@ __global__ void __launch_bounds__(256) k_stereo_rows(int nl, const float* __rest
         if (best != 0xFFFFFFFFu && (int)(best >> 22) < TH_HIGH) { d = best >> 22; idx = best & ((1u << 22) - 1); }
         bestDist[iL] = d;
         bestR[iL] = (d < (TH_HIGH + TH_LOW) / 2) ? idx : -1;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// K7c': SAD refinement of Frame::ComputeStereoMatches (src/Frame.cc:767-866) on the device-resident pyramids of the two
+// extractor handles: for every coarse match, an 11x11 window (centre-subtracted) slides over 11 horizontal shifts in the
+// right level image; L1 distances are integers (exact in float, as in the reference's cv::norm of CV_32F patches);
+// parabola fit of the minimum in unfused float arithmetic; depth = mbf / disparity.  One warp per left keypoint.
+// ------------------------------------------------------------------------------------------------------
+struct StereoPyr {
+    const uint8_t* interior[ORBX_MAX_LEVELS];
+    int pitch[ORBX_MAX_LEVELS];
+    int w[ORBX_MAX_LEVELS];
+    float scale[ORBX_MAX_LEVELS], invScale[ORBX_MAX_LEVELS];
+};
+
+__global__ void __launch_bounds__(256) k_stereo_refine(int nl, const float* __restrict__ lx, const float* __restrict__ ly,
+                                                       const int32_t* __restrict__ loct, const float* __restrict__ rx,
+                                                       const int32_t* __restrict__ bestR, StereoPyr PLv, StereoPyr PRv,
+                                                       float mbf, float minD, float maxD, float* __restrict__ uRight,
+                                                       float* __restrict__ depth, int32_t* __restrict__ sad)
+{
+    const int lane = threadIdx.x & 31;
+    const int iL = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (iL >= nl) return;
+    float outU = -1.0f, outD = -1.0f;
+    int outS = -1;
+    const int br = bestR[iL];
+    if (br >= 0) {
+        const int oct = loct[iL];
+        const float uL = lx[iL];
+        const float sF = PLv.invScale[oct];
+        const float scaleduL = roundf(__fmul_rn(uL, sF));
+        const float scaledvL = roundf(__fmul_rn(ly[iL], sF));
+        const float scaleduR0 = roundf(__fmul_rn(rx[br], sF));
+        const float iniu = scaleduR0, endu = __fadd_rn(scaleduR0, 11.0f);  // scaleduR0 + L - w, scaleduR0 + L + w + 1
+        if (!(iniu < 0 || endu >= (float)PRv.w[oct])) {
+            const int pl = PLv.pitch[oct], pr = PRv.pitch[oct];
+            const uint8_t* cL = PLv.interior[oct] + (long long)(int)scaledvL * pl + (int)scaleduL;
+            const uint8_t* cR = PRv.interior[oct] + (long long)(int)scaledvL * pr + (int)scaleduR0;
+            const int centerL = cL[0];
+            int acc[11];
+#pragma unroll
+            for (int s = 0; s < 11; s++) acc[s] = 0;
+            for (int p = lane; p < 121; p += 32) {
+                const int dy = p / 11 - 5, dx = p - (p / 11) * 11 - 5;
+                const int a = (int)cL[dy * pl + dx] - centerL;
+                const uint8_t* rrow = cR + dy * pr + dx;
+#pragma unroll
+                for (int s = 0; s < 11; s++) {
+                    const int b = (int)rrow[s - 5] - (int)cR[s - 5];
+                    acc[s] += abs(a - b);
+                }
+            }
+            int bestDist = 0x7fffffff, bestinc = 0;
+            float vd[11];
+#pragma unroll
+            for (int s = 0; s < 11; s++) {
+                const int d = __reduce_add_sync(0xffffffffu, acc[s]);
+                vd[s] = (float)d;
+                if (d < bestDist) { bestDist = d; bestinc = s - 5; }
+            }
+            if (bestinc != -5 && bestinc != 5) {
+                float dist1 = 0, dist2 = 0, dist3 = 0;
+#pragma unroll
+                for (int s = 1; s < 10; s++)
+                    if (s - 5 == bestinc) { dist1 = vd[s - 1]; dist2 = vd[s]; dist3 = vd[s + 1]; }
+                const float den = __fmul_rn(2.0f, __fsub_rn(__fadd_rn(dist1, dist3), __fmul_rn(2.0f, dist2)));
+                const float deltaR = __fdiv_rn(__fsub_rn(dist1, dist3), den);
+                if (!(deltaR < -1 || deltaR > 1)) {
+                    float bestuR = __fmul_rn(PLv.scale[oct], __fadd_rn(__fadd_rn(scaleduR0, (float)bestinc), deltaR));
+                    float disparity = __fsub_rn(uL, bestuR);
+                    if (disparity >= minD && disparity < maxD) {
+                        if (disparity <= 0) {
+                            disparity = 0.01f;                                           // (float)0.01
+                            bestuR = __double2float_rn(__dsub_rn((double)uL, 0.01));    // float - double literal
+                        }
+                        outD = __fdiv_rn(mbf, disparity);
+                        outU = bestuR;
+                        outS = bestDist;
+                    }
+                }
+            }
+        }
+    }
+    if (lane == 0) { uRight[iL] = outU; depth[iL] = outD; sad[iL] = outS; }
+}
+
+// Outlier removal (src/Frame.cc:868-884, upstream placement): sort accepted (SAD, iL), median = element size/2,
+// reject every match with SAD >= 1.5f * 1.4f * median.  Rank by counting (n <= a few thousand).
+__global__ void __launch_bounds__(1024) k_stereo_outliers(int nl, const int32_t* __restrict__ sad, float* uRight, float* depth)
+{
+    __shared__ int sN, sMedian;
+    if (threadIdx.x == 0) { sN = 0; sMedian = -1; }
+    __syncthreads();
+    int mine = 0;
+    for (int i = threadIdx.x; i < nl; i += blockDim.x) mine += sad[i] >= 0;
+    if (mine) atomicAdd(&sN, mine);
+    __syncthreads();
+    const int n = sN;
+    if (n == 0) return;
+    const int target = n / 2;
+    for (int i = threadIdx.x; i < nl; i += blockDim.x) {
+        const int d = sad[i];
+        if (d < 0) continue;
+        int rank = 0;
+        for (int j = 0; j < nl; j++) {
+            const int e = sad[j];
+            rank += (e >= 0) && (e < d || (e == d && j < i));
+        }
+        if (rank == target) sMedian = d;
+    }
+    __syncthreads();
+    const float thDist = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)sMedian);
+    for (int i = threadIdx.x; i < nl; i += blockDim.x) {
+        const int d = sad[i];
+        if (d >= 0 && !((float)d < thDist)) { uRight[i] = -1.0f; depth[i] = -1.0f; }
     }
 }
 
@@ -770,6 +888,72 @@ int orbm_search_by_bow(orbm_context* m, int nkf, const uint8_t* kf_desc, const f
     ORBX_CUDA_TRY(cudaMemcpyAsync(out_match, A + oOut, 4 * (size_t)nf, cudaMemcpyDeviceToHost, m->stream));
     ORBX_CUDA_TRY(cudaMemcpyAsync(nmatches, A + oN, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
     ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    return ORBX_OK;
+}
+
+int orbm_stereo_match(orbm_context* m, orbx_handle* ex_left, int frame_left, orbx_handle* ex_right, int frame_right, int nl,
+                      const float* lx, const float* ly, const int32_t* loct, const uint8_t* ldesc, int nr, const float* rx,
+                      const float* ry, const int32_t* roct, const uint8_t* rdesc, float mbf, float mb, float* u_right,
+                      float* depth, int* n_matched)
+{
+    if (!m || !ex_left || !ex_right || nl < 0 || nr < 0 || !u_right || !depth || nr >= (1 << 22) || !(mb > 0)) {
+        set_error("orbm_stereo_match: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    if (n_matched) *n_matched = 0;
+    if (nl == 0) return ORBX_OK;
+    PyramidView vl, vr;
+    int rc = pyramid_view(ex_left, frame_left, &vl);
+    if (rc == ORBX_OK) rc = pyramid_view(ex_right, frame_right, &vr);
+    if (rc != ORBX_OK) return rc;
+    if (vl.device != m->device || vr.device != m->device || vl.nlevels != vr.nlevels) {
+        set_error("orbm_stereo_match: extractor handles and matcher context must share a device and a level count");
+        return ORBX_ERR_BAD_ARG;
+    }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    StereoPyr pl, pr;
+    for (int l = 0; l < ORBX_MAX_LEVELS; l++) {
+        const bool ok = l < vl.nlevels;
+        pl.interior[l] = ok ? vl.interior[l] : nullptr; pr.interior[l] = ok ? vr.interior[l] : nullptr;
+        pl.pitch[l] = ok ? vl.pitch[l] : 0; pr.pitch[l] = ok ? vr.pitch[l] : 0;
+        pl.w[l] = ok ? vl.w[l] : 0; pr.w[l] = ok ? vr.w[l] : 0;
+        pl.scale[l] = ok ? vl.scale[l] : 0; pr.scale[l] = ok ? vr.scale[l] : 0;
+        pl.invScale[l] = ok ? vl.invScale[l] : 0; pr.invScale[l] = ok ? vr.invScale[l] : 0;
+    }
+    const float minD = 0.0f, maxD = mbf / mb;  // src/Frame.cc:711-713 with decision D5 (minZ = mb)
+    const int nRows = vl.h[0];
+    Carver c;
+    const size_t oLx = c.take(4 * (size_t)nl), oLy = c.take(4 * (size_t)nl), oLo = c.take(4 * (size_t)nl), oLd = c.take(32 * (size_t)nl);
+    const int nrA = std::max(nr, 1);
+    const size_t oRx = c.take(4 * (size_t)nrA), oRy = c.take(4 * (size_t)nrA), oRo = c.take(4 * (size_t)nrA), oRd = c.take(32 * (size_t)nrA),
+                 oSf = c.take(4 * (size_t)ORBX_MAX_LEVELS);
+    const size_t oBr = c.take(4 * (size_t)nl), oBd = c.take(4 * (size_t)nl), oU = c.take(4 * (size_t)nl), oD = c.take(4 * (size_t)nl),
+                 oS = c.take(4 * (size_t)nl);
+    rc = ensure_arena(m, c.off);
+    if (rc != ORBX_OK) return rc;
+    char* A = m->arena;
+#define UP(off, ptr, count, T) if ((rc = up<T>(m, (T*)(A + off), ptr, count)) != ORBX_OK) return rc
+    UP(oLx, lx, nl, float); UP(oLy, ly, nl, float); UP(oLo, loct, nl, int32_t); UP(oLd, ldesc, 32 * (size_t)nl, uint8_t);
+    UP(oRx, rx, nr, float); UP(oRy, ry, nr, float); UP(oRo, roct, nr, int32_t); UP(oRd, rdesc, 32 * (size_t)nr, uint8_t);
+    UP(oSf, vl.scale, vl.nlevels, float);
+#undef UP
+    k_stereo_rows<<<(nl + 7) / 8, 256, 0, m->stream>>>(nl, (float*)(A + oLx), (float*)(A + oLy), (int32_t*)(A + oLo),
+                                                      (uint8_t*)(A + oLd), nr, (float*)(A + oRx), (float*)(A + oRy),
+                                                      (int32_t*)(A + oRo), (uint8_t*)(A + oRd), (float*)(A + oSf), nRows, minD,
+                                                      maxD, (int32_t*)(A + oBr), (int32_t*)(A + oBd));
+    k_stereo_refine<<<(nl + 7) / 8, 256, 0, m->stream>>>(nl, (float*)(A + oLx), (float*)(A + oLy), (int32_t*)(A + oLo),
+                                                        (float*)(A + oRx), (int32_t*)(A + oBr), pl, pr, mbf, minD, maxD,
+                                                        (float*)(A + oU), (float*)(A + oD), (int32_t*)(A + oS));
+    k_stereo_outliers<<<1, 1024, 0, m->stream>>>(nl, (int32_t*)(A + oS), (float*)(A + oU), (float*)(A + oD));
+    ORBX_CUDA_TRY(cudaGetLastError());
+    ORBX_CUDA_TRY(cudaMemcpyAsync(u_right, A + oU, 4 * (size_t)nl, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(depth, A + oD, 4 * (size_t)nl, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    if (n_matched) {
+        int k = 0;
+        for (int i = 0; i < nl; i++) k += u_right[i] >= 0;
+        *n_matched = k;
+    }
     return ORBX_OK;
 }
 

@@ -53,6 +53,8 @@ public:
     // Extension: monocular / RGB-D callers never read mvImagePyramid; switching the download off saves the largest D2H
     // transfer of the call (default on = reference behaviour).
     void SetPyramidDownload(bool on) { mbDownloadPyramid = on; }
+    // Extension: the C-ABI handle, so that orbx_adapter::ComputeStereoMatches can read the device-resident pyramid.
+    orbx_handle* NativeHandle() { return mpHandle; }
 
 protected:
     int nfeatures;

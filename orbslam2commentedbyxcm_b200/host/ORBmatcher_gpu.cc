@@ -6,6 +6,7 @@
 //   ORBmatcher::SearchByBoW(KeyFrame*, Frame&, std::vector<MapPoint*>&)                     src/ORBmatcher.cc:228-392
 //   ORBmatcher::DescriptorDistance(const cv::Mat&, const cv::Mat&)                          src/ORBmatcher.cc:1983-2003
 //   orbx_adapter::StereoCoarseSearch(...)   coarse part of Frame::ComputeStereoMatches      src/Frame.cc:684-765
+//   orbx_adapter::ComputeStereoMatches(...) the whole of Frame::ComputeStereoMatches        src/Frame.cc:673-885
 //
 // Each function gathers flat views from Frame / KeyFrame / MapPoint (under the same locks the reference takes through
 // the objects' accessors), calls the C-ABI of include/orbx.h, and applies the result to the objects in the reference's
@@ -17,6 +18,7 @@
 #include <vector>
 
 #include "orbx.h"
+#include "ORBextractor.h"
 
 namespace ORB_SLAM2 {
 
@@ -201,6 +203,42 @@ int StereoCoarseSearch(const std::vector<cv::KeyPoint>& vKeysLeft, const cv::Mat
     }
     for (int i = 0; i < nl; i++) { vBestIdxR[i] = br[i]; vBestDist[i] = bd[i]; }
     return 0;
+}
+
+// The whole of Frame::ComputeStereoMatches on the GPU: coarse search + SAD refinement on the two extractors' device
+// pyramids + outlier removal.  Body replacement for src/Frame.cc:673-885:
+//     orbx_adapter::ComputeStereoMatches(mpORBextractorLeft, mpORBextractorRight, mvKeys, mDescriptors, mvKeysRight,
+//                                        mDescriptorsRight, mbf, mbf / fx, mvuRight, mvDepth);
+int ComputeStereoMatches(ORB_SLAM2::ORBextractor* pLeft, ORB_SLAM2::ORBextractor* pRight, const std::vector<cv::KeyPoint>& vKeysLeft,
+                         const cv::Mat& descLeft, const std::vector<cv::KeyPoint>& vKeysRight, const cv::Mat& descRight, float mbf,
+                         float mb, std::vector<float>& vuRight, std::vector<float>& vDepth)
+{
+    static thread_local orbm_context* ctx = NULL;
+    if (!ctx && orbm_create(std::getenv("ORBX_DEVICE") ? std::atoi(std::getenv("ORBX_DEVICE")) : 0, &ctx) != ORBX_OK) return -1;
+    const int nl = (int)vKeysLeft.size(), nr = (int)vKeysRight.size();
+    vuRight.assign(nl, -1.0f);
+    vDepth.assign(nl, -1.0f);
+    if (nl == 0 || !pLeft->NativeHandle() || !pRight->NativeHandle()) return 0;
+    std::vector<float> lx(nl), ly(nl), rx(nr), ry(nr);
+    std::vector<int32_t> lo(nl), ro(nr);
+    std::vector<uint8_t> ld((size_t)nl * 32), rd((size_t)nr * 32);
+    for (int i = 0; i < nl; i++) {
+        lx[i] = vKeysLeft[i].pt.x; ly[i] = vKeysLeft[i].pt.y; lo[i] = vKeysLeft[i].octave;
+        std::memcpy(&ld[(size_t)i * 32], descLeft.ptr(i), 32);
+    }
+    for (int i = 0; i < nr; i++) {
+        rx[i] = vKeysRight[i].pt.x; ry[i] = vKeysRight[i].pt.y; ro[i] = vKeysRight[i].octave;
+        std::memcpy(&rd[(size_t)i * 32], descRight.ptr(i), 32);
+    }
+    int nMatched = 0;
+    const int rc = orbm_stereo_match(ctx, pLeft->NativeHandle(), 0, pRight->NativeHandle(), 0, nl, lx.data(), ly.data(), lo.data(),
+                                     ld.data(), nr, rx.data(), ry.data(), ro.data(), rd.data(), mbf, mb, vuRight.data(), vDepth.data(),
+                                     &nMatched);
+    if (rc != ORBX_OK) {
+        std::fprintf(stderr, "ComputeStereoMatches: %s\n", orbx_last_error());
+        return rc;
+    }
+    return nMatched;
 }
 
 }  // namespace orbx_adapter

@@ -127,6 +127,28 @@ class ORBmatcher:
             float(min_d), float(max_d), best_r.ctypes.data, best_d.ctypes.data), "orbm_stereo_rows")
         return best_r[:nl], best_d[:nl]
 
+    # ---- Frame::ComputeStereoMatches, complete (coarse search + SAD refinement + outlier removal) ----
+    def ComputeStereoMatches(self, ex_left, ex_right, left, right, mbf, mb, frame_left=0, frame_right=0):
+        """ex_left / ex_right: ORBextractor objects that have just extracted the left / right image (their device
+        pyramids are read in place).  Returns (mvuRight, mvDepth)."""
+        keep = []
+
+        def arr(v, dt):
+            a = np.ascontiguousarray(v, dt)
+            keep.append(a)
+            return a
+
+        nl, nr = len(left["x"]), len(right["x"])
+        ur = np.full(max(nl, 1), -1, np.float32)
+        dp = np.full(max(nl, 1), -1, np.float32)
+        nm = C.c_int()
+        check(self._L.orbm_stereo_match(
+            self._m, ex_left._h, frame_left, ex_right._h, frame_right, nl, _p(arr(left["x"], np.float32)),
+            _p(arr(left["y"], np.float32)), _p(arr(left["octave"], np.int32)), _p(arr(left["desc"], np.uint8)), nr,
+            _p(arr(right["x"], np.float32)), _p(arr(right["y"], np.float32)), _p(arr(right["octave"], np.int32)),
+            _p(arr(right["desc"], np.uint8)), float(mbf), float(mb), ur.ctypes.data, dp.ctypes.data, C.byref(nm)), "orbm_stereo_match")
+        return ur[:nl], dp[:nl]
+
     # ---- SearchByBoW(KeyFrame*, Frame&, matches) ----
     def SearchByBoW(self, kf, fr):
         keep = []

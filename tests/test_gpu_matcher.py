@@ -189,3 +189,29 @@ def test_search_by_bow_vs_oracle(gpu, oracle_mod, seed, check_ori):
     assert n_ref > 50
     assert n_gpu == n_ref and np.array_equal(out_gpu, out_ref)
     m.close()
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_full_stereo_matching_vs_oracle(gpu, oracle_mod, seed):
+    """Frame::ComputeStereoMatches complete: coarse search + SAD refinement on the device-resident pyramids + outlier
+    removal; mvuRight / mvDepth bit-exact (float bits)."""
+    left, right = synth.gen_stereo_pair(synth.SHAPES["euroc"], seed)
+    cfg = synth.PRESETS["euroc"]
+    oL, oR = oracle_mod.Extractor(*cfg), oracle_mod.Extractor(*cfg)
+    kl, dl = oL.extract(left)
+    kr, dr = oR.extract(right)
+    gL, gR = gpu.ORBextractor(*cfg), gpu.ORBextractor(*cfg)
+    gkl, gdl = gL(left)
+    gkr, gdr = gR(right)
+    assert gkl.tobytes() == kl.tobytes() and gkr.tobytes() == kr.tobytes()
+    L = dict(x=kl["x"].copy(), y=kl["y"].copy(), octave=kl["octave"].astype(np.int32), desc=dl)
+    R = dict(x=kr["x"].copy(), y=kr["y"].copy(), octave=kr["octave"].astype(np.int32), desc=dr)
+    fx, bf = 435.2, 47.9
+    mb = float(np.float32(bf) / np.float32(fx))
+    n_ref, ur_ref, dp_ref = oracle_mod.stereo_match(oL, oR, L, R, synth.SHAPES["euroc"][0], bf, mb)
+    m = gpu.ORBmatcher()
+    ur, dp = m.ComputeStereoMatches(gL, gR, L, R, bf, mb)
+    assert (ur_ref >= 0).sum() > 50
+    assert np.array_equal(ur.view(np.uint32), ur_ref.view(np.uint32))
+    assert np.array_equal(dp.view(np.uint32), dp_ref.view(np.uint32))
+    m.close(); gL.close(); gR.close()
