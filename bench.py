@@ -54,8 +54,8 @@ def algorithmic_bytes(rows, cols, cfg):
         "pyramid": pyr,
         "fast": sum(interior) + 12 * 10 * nf,
         "blur": 2 * sum(interior),
-        "octree": nf * (749 + 16),   # orientation reads; the quad-tree itself moves 8 B per candidate
-        "desc": nf * (512 + 32),
+        "octree": 8 * 10 * nf,       # the quad-tree reads 8 B per FAST candidate (~10 x nfeatures)
+        "desc": nf * (749 + 16) + nf * (512 + 32),   # IC_Angle disc reads + rBRIEF samples/descriptor (fused in k_describe)
     }
 
 
@@ -118,6 +118,16 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_traffic(stage, frames):
+    """DRAM bytes per launch of a stage from the committed ncu capture (profiles/r1_traffic.json), or None."""
+    p = os.path.join(ROOT, "profiles", "r1_traffic.json")
+    try:
+        d = json.load(open(p))
+        return int(d["bytes_per_frame"][stage] * frames)
+    except Exception:
+        return None
+
+
 def make_frames(shape, n_distinct, batch):
     base = np.stack([synth.gen_frame(shape, s) for s in range(n_distinct)])
     reps = (batch + n_distinct - 1) // n_distinct
@@ -168,6 +178,98 @@ def run_reference(args):
         "keypoints_per_frame": total_kp / (sample * args.steps),
     }
     print(json.dumps(line))
+
+
+def other_configs(pkg, torch, dev, local):
+    """BASELINE.json configs 2 and 3 on one GPU (reported beside the headline; parity for them is in tests/):
+    C2 EuRoC stereo 752x480 x2, 1200 feats: two extractor handles on two host threads' worth of streams + the complete
+       Frame::ComputeStereoMatches (row search + SAD refinement on the device pyramids);
+    C3 KITTI 1241x376, 2000 feats: batched extraction + SearchByProjection against a synthetic local map of 4000 points."""
+    from orbslam2commentedbyxcm_b200.matcher import frame_grid
+
+    out = {}
+    # ---- C2 ----
+    shape, cfg = synth.SHAPES["euroc"], synth.PRESETS["euroc"]
+    left, right = synth.gen_stereo_pair(shape, 0)
+    exL, exR = pkg.ORBextractor(*cfg, device=local), pkg.ORBextractor(*cfg, device=local)
+    mt = pkg.ORBmatcher(0.6, True, device=local)
+    oL, oR = exL.alloc_outputs(1, *shape), exR.alloc_outputs(1, *shape)
+    fx, bf = 435.2, 47.9
+    mb = float(np.float32(bf) / np.float32(fx))
+
+    def stereo_frame():
+        kl, dl, cl = exL.extract_batch(left[None], out=oL)
+        kr, dr, cr = exR.extract_batch(right[None], out=oR)
+        L = dict(x=kl[0, :cl[0]]["x"], y=kl[0, :cl[0]]["y"], octave=kl[0, :cl[0]]["octave"], desc=dl[0, :cl[0]])
+        R = dict(x=kr[0, :cr[0]]["x"], y=kr[0, :cr[0]]["y"], octave=kr[0, :cr[0]]["octave"], desc=dr[0, :cr[0]])
+        t = time.perf_counter()
+        ur, dp = mt.ComputeStereoMatches(exL, exR, L, R, bf, mb)
+        return time.perf_counter() - t, int(cl[0]), int(cr[0]), int((ur >= 0).sum())
+
+    for _ in range(10):
+        stereo_frame()
+    tt, tm = [], []
+    for _ in range(100):
+        t0 = time.perf_counter()
+        dm, nl, nr, nmatch = stereo_frame()
+        tt.append(time.perf_counter() - t0)
+        tm.append(dm)
+    out["C2_euroc_stereo_752x480_1200"] = {
+        "ms_per_stereo_frame_e2e": 1e3 * float(np.median(tt)), "ms_stereo_match_e2e": 1e3 * float(np.median(tm)),
+        "keypoints_left": nl, "keypoints_right": nr, "stereo_matches": nmatch,
+        "note": "extract L + extract R (host in/out, sequential calls) + orbm_stereo_match (row search + SAD + outliers)"}
+    exL.close(); exR.close()
+    # ---- C3 ----
+    shape, cfg = synth.SHAPES["kitti"], synth.PRESETS["kitti"]
+    rows, cols = shape
+    Bk = 64
+    frames = make_frames(shape, 8, Bk)
+    ex = pkg.ORBextractor(*cfg, device=local)
+    cap = ex.max_keypoints(rows, cols)
+    d_imgs = torch.from_numpy(frames).to(dev)
+    d_kps = torch.empty((Bk, cap, 6), dtype=torch.float32, device=dev)
+    d_desc = torch.empty((Bk, cap, 32), dtype=torch.uint8, device=dev)
+    d_counts = torch.empty(Bk, dtype=torch.int32, device=dev)
+    st = torch.cuda.ExternalStream(ex.stream, device=dev)
+    for _ in range(3):
+        ex.extract_batch_device(d_imgs.data_ptr(), Bk, rows, cols, d_kps.data_ptr(), d_desc.data_ptr(), d_counts.data_ptr(), cap)
+    ex.sync()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(st)
+    for _ in range(10):
+        ex.extract_batch_device(d_imgs.data_ptr(), Bk, rows, cols, d_kps.data_ptr(), d_desc.data_ptr(), d_counts.data_ptr(), cap)
+    e1.record(st)
+    ex.sync()
+    fps = Bk * 10 / (e0.elapsed_time(e1) * 1e-3)
+    kps, desc = ex(frames[0])
+    n = len(kps)
+    w_inv, h_inv = float(np.float32(64.0) / np.float32(cols)), float(np.float32(48.0) / np.float32(rows))
+    cs, ci = frame_grid(kps["x"], kps["y"], 0.0, 0.0, w_inv, h_inv)
+    rng = np.random.Generator(np.random.PCG64(99))
+    nmp = 4000
+    pick = rng.integers(0, n, nmp)
+    flips = rng.random((nmp, 256)) < 0.08
+    frame = dict(x=kps["x"].copy(), y=kps["y"].copy(), octave=kps["octave"].astype(np.int32), u_right=None, desc=desc,
+                 occupied=np.zeros(n, np.uint8), cell_start=cs, cell_items=ci, min_x=0.0, min_y=0.0, w_inv=w_inv, h_inv=h_inv,
+                 scale_factors=ex.GetScaleFactors())
+    mps = dict(x=(kps["x"][pick] + rng.normal(0, 2, nmp)).astype(np.float32), y=(kps["y"][pick] + rng.normal(0, 2, nmp)).astype(np.float32),
+               xr=np.full(nmp, -1, np.float32), level=kps["octave"][pick].astype(np.int32), view_cos=np.full(nmp, 0.9, np.float32),
+               valid=np.ones(nmp, np.uint8), obs=np.ones(nmp, np.uint8),
+               desc=np.ascontiguousarray(desc[pick] ^ np.packbits(flips, axis=1, bitorder="little")))
+    mt2 = pkg.ORBmatcher(0.8, True, device=local)
+    for _ in range(5):
+        nm, _o = mt2.SearchByProjection(frame, mps, 3.0)
+    ts = []
+    for _ in range(50):
+        t0 = time.perf_counter()
+        nm, _o = mt2.SearchByProjection(frame, mps, 3.0)
+        ts.append(time.perf_counter() - t0)
+    out["C3_kitti_1241x376_2000"] = {
+        "extract_frames_per_s_device_resident": fps, "frames_per_step": Bk, "keypoints_per_frame": n,
+        "search_by_projection_ms_e2e": 1e3 * float(np.median(ts)), "map_points": nmp, "matches": int(nm),
+        "note": "SearchByProjection(Frame, 4000 local map points, th=3) through the host C-ABI (uploads included)"}
+    ex.close(); mt.close(); mt2.close()
+    return out
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -348,7 +450,8 @@ def run_ours(args):
             "clocks": clocks,
             "roofline": {
                 "kernel": dom, "bound": "hbm", "achieved": stages[dom]["GB_per_s"], "peak": peak, "unit": "GB/s",
-                "frac": stages[dom]["frac_of_hbm_peak"], "traffic": None, "peak_source": peak_src,
+                "frac": stages[dom]["frac_of_hbm_peak"], "traffic": measured_traffic(dom, B), "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": ab[dom] * B,
                 "whole_step_GB_per_s": sum(ab.values()) * B * args.steps / (ms * 1e-3) / 1e9,
             },
             "stages": stages,
@@ -357,6 +460,8 @@ def run_ours(args):
             "hamming": {"pairs_per_s": world * nq * per / (bf_ms * 1e-3), "queries": nq, "db_rows_per_gpu": per,
                         "ms_per_search": bf_ms, "unit": "descriptor pairs/s"},
         }
+        if world == 1 and not args.no_extra:
+            line["configs"] = other_configs(pkg, torch, dev, local)
         # CPU baseline on rank 0 at N = 1 only (bounded sample)
         if world == 1 and not args.no_cpu_baseline:
             import oracle
@@ -393,6 +498,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the C2 / C3 side measurements")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -20,6 +20,28 @@ def _p(a):
     return a.ctypes.data if a is not None else None
 
 
+def frame_grid(x, y, min_x, min_y, w_inv, h_inv):
+    """Host-side Frame::AssignFeaturesToGrid / PosInGrid (reference src/Frame.cc:351-370, 558-567): 64x48 grid, cell
+    (ix, iy) flattened as ix*48+iy, CSR (cell_start, cell_items) with items in keypoint order.  Caller-side glue (the
+    reference keeps it in Frame); shipped so Python callers can build an orbm_frame_view."""
+    x = np.asarray(x, np.float32)
+    y = np.asarray(y, np.float32)
+    fx = (x - np.float32(min_x)) * np.float32(w_inv)
+    fy = (y - np.float32(min_y)) * np.float32(h_inv)
+    # C round(): half away from zero
+    px = np.where(fx >= 0, np.floor(fx + np.float32(0.5)), np.ceil(fx - np.float32(0.5))).astype(np.int64)
+    py = np.where(fy >= 0, np.floor(fy + np.float32(0.5)), np.ceil(fy - np.float32(0.5))).astype(np.int64)
+    ok = (px >= 0) & (px < 64) & (py >= 0) & (py < 48)
+    idx = np.nonzero(ok)[0]
+    cell = px[idx] * 48 + py[idx]
+    order = np.argsort(cell, kind="stable")
+    items = idx[order].astype(np.int32)
+    counts = np.bincount(cell, minlength=64 * 48)
+    start = np.zeros(64 * 48 + 1, np.int32)
+    start[1:] = np.cumsum(counts)
+    return start, items
+
+
 class ORBmatcher:
     TH_LOW = 50
     TH_HIGH = 100

@@ -56,3 +56,18 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cc")):
                 src = open(os.path.join(dp, f), errors="replace").read()
                 assert "import oracle" not in src and "from oracle" not in src and '#include "../../oracle' not in src, f
+
+
+def test_frame_grid_helper_matches_oracle():
+    """matcher.frame_grid (host glue for orbm_frame_view) == the oracle's restatement of Frame::AssignFeaturesToGrid."""
+    import oracle
+    from orbslam2commentedbyxcm_b200.matcher import frame_grid
+
+    rng = np.random.default_rng(0)
+    x = (rng.random(3000) * 1300 - 20).astype(np.float32)
+    y = (rng.random(3000) * 400 - 10).astype(np.float32)
+    x[:50] = np.float32(19.390625) * np.arange(50, dtype=np.float32) + np.float32(9.6953125)  # exact .5 cells
+    w_inv, h_inv = float(np.float32(64.0) / np.float32(1241.0)), float(np.float32(48.0) / np.float32(376.0))
+    s1, i1 = frame_grid(x, y, 0.0, 0.0, w_inv, h_inv)
+    s2, i2 = oracle.assign_grid(x, y, 0.0, 0.0, w_inv, h_inv)
+    assert np.array_equal(s1, s2) and np.array_equal(i1, i2)
