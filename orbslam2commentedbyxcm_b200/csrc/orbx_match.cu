@@ -145,22 +145,46 @@ __global__ void __launch_bounds__(BF_T) k_bruteforce(const uint8_t* __restrict__
     }
 }
 
-// sequential-scan-equivalent merge of partials ordered by ascending index range
-__global__ void k_merge_partials(const int32_t* __restrict__ pBest, const int32_t* __restrict__ pIdx,
-                                 const int32_t* __restrict__ pSecond, int nparts, int nq, int32_t* __restrict__ oBest,
-                                 int32_t* __restrict__ oIdx, int32_t* __restrict__ oSecond)
+// sequential-scan-equivalent merge of partials ordered by ascending index range.  (best, idx) is the lexicographic
+// minimum of (distance, global index) -- parts cover ascending index ranges, so "first minimum in scan order" is the
+// smallest index -- and second is the second smallest distance of the multiset; that merge is associative and
+// commutative, so one warp per query reduces its lanes' partial results with shuffles.
+struct BfTriple { int b, id, s; };
+__device__ __forceinline__ BfTriple bf_merge(BfTriple x, BfTriple y)
 {
-    const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (y.id < 0) return x;
+    if (x.id < 0) return y;
+    const bool yWins = y.b < x.b || (y.b == x.b && y.id < x.id);
+    BfTriple o;
+    o.b = yWins ? y.b : x.b;
+    o.id = yWins ? y.id : x.id;
+    o.s = min(min(x.s, y.s), yWins ? x.b : y.b);
+    return o;
+}
+
+__global__ void __launch_bounds__(256) k_merge_partials(const int32_t* __restrict__ pBest, const int32_t* __restrict__ pIdx,
+                                                        const int32_t* __restrict__ pSecond, int nparts, int nq,
+                                                        int32_t* __restrict__ oBest, int32_t* __restrict__ oIdx,
+                                                        int32_t* __restrict__ oSecond)
+{
+    const int lane = threadIdx.x & 31;
+    const int qi = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (qi >= nq) return;
-    int b = 256, s = 256, id = -1;
-    for (int p = 0; p < nparts; p++) {
+    BfTriple acc = {256, -1, 256};
+    for (int p = lane; p < nparts; p += 32) {
         const size_t o = (size_t)p * nq + qi;
-        const int pb = pBest[o], ps = pSecond[o], pi = pIdx[o];
-        if (pi < 0) continue;  // empty part
-        if (pb < b) { s = min(b, ps); b = pb; id = pi; }
-        else s = min(s, pb);
+        BfTriple t = {pBest[o], pIdx[o], pSecond[o]};
+        acc = bf_merge(acc, t);
     }
-    oBest[qi] = b; oIdx[qi] = id; oSecond[qi] = s;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        BfTriple t;
+        t.b = __shfl_xor_sync(0xffffffffu, acc.b, o);
+        t.id = __shfl_xor_sync(0xffffffffu, acc.id, o);
+        t.s = __shfl_xor_sync(0xffffffffu, acc.s, o);
+        acc = bf_merge(acc, t);
+    }
+    if (lane == 0) { oBest[qi] = acc.b; oIdx[qi] = acc.id; oSecond[qi] = acc.s; }
 }
 
 // ------------------------------------------------------------------------------------------------------
@@ -238,37 +262,38 @@ __device__ int proj_one(const ProjArgs& A, int m, const int32_t* claimPrev, int 
     const float xr = A.pxr[m];
     Top2 t;
     top2_init(t);
-    uint32_t visit = 0;  // enumeration counter (same on all lanes)
-    for (int ix = c0; ix <= c1; ix++)
-        for (int iy = r0; iy <= r1; iy++) {
-            const int c = ix * GRID_ROWS + iy;
-            const int s = A.cellStart[c], e = A.cellStart[c + 1];
-            for (int k = s + lane; k < e; k += 32) {
-                const int idx = A.cellItems[k];
-                const int oct = A.koct[idx];
-                if (checkLevels) {
-                    if (oct < minLevel) continue;
-                    if (maxLevel >= 0 && oct > maxLevel) continue;
-                }
-                const float dx = __fsub_rn(A.kx[idx], x), dy = __fsub_rn(A.ky[idx], y);
-                if (!(fabsf(dx) < rr && fabsf(dy) < rr)) continue;
-                if (A.occupied[idx] || claimPrev[idx] < m) continue;
-                if (A.uright) {
-                    const float ur = A.uright[idx];
-                    if (ur > 0 && fabsf(__fsub_rn(xr, ur)) > rr) continue;
-                }
-                const int dist = hamming(D, load_desc(A.kdesc + 32 * (size_t)idx));
-                top2_push(t, ((uint32_t)dist << 20) | (visit + (uint32_t)(k - s)), idx);
+    // one lane per grid cell of the window (ix outer, iy inner = the reference's visiting order); the order key is
+    // (cell sequence number, index inside the cell): 12 + 11 bits below the 9-bit distance
+    const int nr = r1 - r0 + 1, ncell = (c1 - c0 + 1) * nr;
+    for (int qc = lane; qc < ncell; qc += 32) {
+        const int ix = c0 + qc / nr, iy = r0 + qc % nr;
+        const int c = ix * GRID_ROWS + iy;
+        const int s = A.cellStart[c], e = A.cellStart[c + 1];
+        for (int k = s; k < e; k++) {
+            const int idx = A.cellItems[k];
+            const int oct = A.koct[idx];
+            if (checkLevels) {
+                if (oct < minLevel) continue;
+                if (maxLevel >= 0 && oct > maxLevel) continue;
             }
-            visit += (uint32_t)(e - s);
+            const float dx = __fsub_rn(A.kx[idx], x), dy = __fsub_rn(A.ky[idx], y);
+            if (!(fabsf(dx) < rr && fabsf(dy) < rr)) continue;
+            if (A.occupied[idx] || claimPrev[idx] < m) continue;
+            if (A.uright) {
+                const float ur = A.uright[idx];
+                if (ur > 0 && fabsf(__fsub_rn(xr, ur)) > rr) continue;
+            }
+            const int dist = hamming(D, load_desc(A.kdesc + 32 * (size_t)idx));
+            top2_push(t, ((uint32_t)dist << 23) | ((uint32_t)qc << 11) | (uint32_t)(k - s), idx);
         }
+    }
     top2_warp_reduce(t);
     if (t.p1 < 0) return -1;
-    const int bestDist = t.k1 >> 20;
+    const int bestDist = t.k1 >> 23;
     if (bestDist > TH_HIGH) return -1;
     const int bestLevel = A.koct[t.p1];
     const int bestLevel2 = t.p2 >= 0 ? A.koct[t.p2] : -1;
-    const int bestDist2 = t.p2 >= 0 ? (int)(t.k2 >> 20) : 256;
+    const int bestDist2 = t.p2 >= 0 ? (int)(t.k2 >> 23) : 256;
     if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(A.nnratio, (float)bestDist2)) return -1;
     return t.p1;
 }
@@ -697,7 +722,7 @@ static int bruteforce_device(orbm_context* m, const uint8_t* dq, int nq, const u
     else if (variant == 3) k_bruteforce<3><<<grid, BF_T, 0, m->stream>>>(dq, nq, ddb, ndb, chunk, idxOffset, pBest, pIdx, pSecond);
     else if (variant == 4) k_bruteforce<4><<<grid, BF_T, 0, m->stream>>>(dq, nq, ddb, ndb, chunk, idxOffset, pBest, pIdx, pSecond);
     else k_bruteforce<2><<<grid, BF_T, 0, m->stream>>>(dq, nq, ddb, ndb, chunk, idxOffset, pBest, pIdx, pSecond);
-    k_merge_partials<<<(nq + 127) / 128, 128, 0, m->stream>>>(pBest, pIdx, pSecond, nChunks, nq, dBest, dIdx, dSecond);
+    k_merge_partials<<<(nq + 7) / 8, 256, 0, m->stream>>>(pBest, pIdx, pSecond, nChunks, nq, dBest, dIdx, dSecond);
     ORBX_CUDA_TRY(cudaGetLastError());
     return ORBX_OK;
 }
@@ -737,7 +762,7 @@ int orbm_merge_partials(orbm_context* m, const int32_t* best, const int32_t* bes
         return ORBX_ERR_BAD_ARG;
     }
     ORBX_CUDA_TRY(cudaSetDevice(m->device));
-    k_merge_partials<<<(nq + 127) / 128, 128, 0, m->stream>>>(best, best_idx, second, nparts, nq, out_best, out_idx, out_second);
+    k_merge_partials<<<(nq + 7) / 8, 256, 0, m->stream>>>(best, best_idx, second, nparts, nq, out_best, out_idx, out_second);
     ORBX_CUDA_TRY(cudaGetLastError());
     return ORBX_OK;
 }
@@ -758,6 +783,11 @@ int orbm_search_by_projection(orbm_context* m, const orbm_frame_view* f, const o
     ORBX_CUDA_TRY(cudaSetDevice(m->device));
     const int ncell = GRID_COLS * GRID_ROWS;
     const int nitems = f->cell_start[ncell];
+    for (int ci = 0; ci < ncell; ci++)
+        if (f->cell_start[ci + 1] - f->cell_start[ci] >= 2048) {
+            set_error("orbm_search_by_projection: a grid cell holds %d keypoints (limit 2047)", f->cell_start[ci + 1] - f->cell_start[ci]);
+            return ORBX_ERR_BAD_ARG;
+        }
     Carver c;
     const size_t oKx = c.take(4 * (size_t)nkp), oKy = c.take(4 * (size_t)nkp), oKo = c.take(4 * (size_t)nkp),
                  oUr = c.take(4 * (size_t)nkp), oKd = c.take(32 * (size_t)nkp), oOcc = c.take(nkp),
