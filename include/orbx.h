@@ -226,6 +226,24 @@ int orbm_search_by_bow(orbm_context* m, int nkf, const uint8_t* kf_desc, const f
                        const float* f_angle, const orbm_featvec_view* f_fv, float nnratio, int check_orientation,
                        int32_t* out_match, int* nmatches);
 
+/* ---- DBoW2 vocabulary descent ("next" row) ------------------------------------ */
+
+/* A vocabulary tree on the device.  Flat form of TemplatedVocabulary::m_nodes (Thirdparty/DBoW2/DBoW2/
+ * TemplatedVocabulary.h:1338-1420 builds it from ORBvoc.txt): node 0 is the root, the children of node i are
+ * child_ids[child_start[i] .. child_start[i+1]) in the order of m_nodes[i].children, node_desc is n_nodes x 32 bytes,
+ * word_id[i] >= 0 and weight[i] are meaningful for leaves.  L = tree depth (m_L). */
+typedef struct orbm_vocab orbm_vocab;
+int orbm_vocab_create(orbm_context* m, int n_nodes, int L, const int32_t* child_start, const int32_t* child_ids,
+                      const uint8_t* node_desc, const int32_t* word_id, const double* weight, orbm_vocab** out);
+void orbm_vocab_destroy(orbm_vocab* v);
+
+/* Replaces the per-feature TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup) (:1218-1259) that
+ * Frame::ComputeBoW / KeyFrame::ComputeBoW run for every descriptor: word id, weight and the node id `levelsup` levels
+ * above the leaves (0 = root when L - levelsup <= 0).  HOST pointers.  The caller folds the triples into
+ * DBoW2::BowVector / FeatureVector in feature order exactly as :1127-1192 does (addWeight / addFeature, L1 normalise). */
+int orbm_bow_transform(orbm_context* m, const orbm_vocab* v, const uint8_t* desc, int n, int levelsup, int32_t* word_id,
+                       int32_t* node_id, double* weight);
+
 #ifdef __cplusplus
 }
 #endif

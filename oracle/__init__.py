@@ -141,6 +141,7 @@ def _bind_all(L):
     L.orbo_get_level_ptr.argtypes = [_vp, _i, _vp]
     L.orbo_stereo_match.restype = _i
     L.orbo_stereo_match.argtypes = [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _f, _vp, _vp]
+    L.orbo_bow_transform.argtypes = [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]
     L.orbo_search_by_bow.restype = _i
     L.orbo_search_by_bow.argtypes = (
         [_i, _vp, _vp, _vp, _i, _vp, _vp, _vp] + [_i, _vp, _vp, _i, _vp, _vp, _vp] + [_f, _i, _vp]
@@ -351,3 +352,17 @@ def stereo_match(exL, exR, left, right, n_rows, mbf, mb):
         nlev, sf.ctypes.data, inv.ctypes.data, lp, rp, ls.ctypes.data, rs.ctypes.data, rc.ctypes.data,
         n_rows, mbf, mb, ur.ctypes.data, dp.ctypes.data)
     return n, ur[:nl], dp[:nl]
+
+
+def bow_transform(vocab, desc, levelsup=4):
+    """vocab: dict(L, child_start, child_ids, node_desc, word_id, weight) -> (word, node, weight) per descriptor."""
+    L = lib()
+    desc = np.ascontiguousarray(desc, np.uint8)
+    n = len(desc)
+    w = np.zeros(max(n, 1), np.int32)
+    nd = np.zeros(max(n, 1), np.int32)
+    wt = np.zeros(max(n, 1), np.float64)
+    L.orbo_bow_transform(len(vocab["word_id"]), vocab["L"], _ptr(vocab["child_start"]), _ptr(vocab["child_ids"]),
+                         _ptr(vocab["node_desc"]), _ptr(vocab["word_id"]), _ptr(vocab["weight"]), desc.ctypes.data, n, levelsup,
+                         w.ctypes.data, nd.ctypes.data, wt.ctypes.data)
+    return w[:n], nd[:n], wt[:n]

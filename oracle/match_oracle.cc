@@ -352,3 +352,38 @@ extern "C" int orbo_stereo_match(
     }
     return (int)vDistIdx.size();
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// DBoW2 vocabulary descent: TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup)
+// (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1218-1259) with F::distance = FORB::distance (FORB.cpp:81-101, the same
+// bit-hack Hamming).  The tree is flat: children of node i are child_ids[child_start[i] .. child_start[i+1]), a node
+// without children is a leaf carrying word_id / weight.  First minimum in child order wins (strict <).
+// ---------------------------------------------------------------------------------------------------------------------
+extern "C" void orbo_bow_transform(int n_nodes, int L, const int32_t* child_start, const int32_t* child_ids,
+                                   const uint8_t* node_desc, const int32_t* word_id, const double* weight,
+                                   const uint8_t* desc, int n, int levelsup, int32_t* out_word, int32_t* out_node,
+                                   double* out_weight)
+{
+    (void)n_nodes;
+    const int nid_level = L - levelsup;
+    for (int f = 0; f < n; f++) {
+        int nid = 0;
+        int final_id = 0, current_level = 0;
+        do {
+            ++current_level;
+            const int cs = child_start[final_id], ce = child_start[final_id + 1];
+            int best = child_ids[cs];
+            double best_d = hamming256(desc + 32 * (size_t)f, node_desc + 32 * (size_t)best);
+            for (int c = cs + 1; c < ce; c++) {
+                const int id = child_ids[c];
+                const double d = hamming256(desc + 32 * (size_t)f, node_desc + 32 * (size_t)id);
+                if (d < best_d) { best_d = d; best = id; }
+            }
+            final_id = best;
+            if (current_level == nid_level) nid = final_id;
+        } while (child_start[final_id + 1] > child_start[final_id]);
+        out_word[f] = word_id[final_id];
+        out_weight[f] = weight[final_id];
+        out_node[f] = nid;
+    }
+}

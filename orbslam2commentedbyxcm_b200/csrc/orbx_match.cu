@@ -5,6 +5,7 @@
 //   k_proj_search                     ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th)
 //                                     src/ORBmatcher.cc:61-183 + Frame::GetFeaturesInArea src/Frame.cc:488-548
 //   k_stereo_rows                     coarse search of Frame::ComputeStereoMatches src/Frame.cc:684-765
+//   k_bow_transform                   DBoW2 TemplatedVocabulary::transform (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1218-1259)
 //   k_bow_nodes / k_bow_rotation      ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...) src/ORBmatcher.cc:228-392,
 //                                     ComputeThreeMaxima :1935-1977
 // 256-bit distances are 8 x (LOP3 xor, POPC) on the integer pipe; best / second-best selection is a min over packed
@@ -502,6 +503,42 @@ __global__ void __launch_bounds__(1024) k_stereo_outliers(int nl, const int32_t*
 }
 
 // ------------------------------------------------------------------------------------------------------
+// K8: DBoW2 vocabulary descent (TemplatedVocabulary::transform, Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1218-1259).
+// One warp per descriptor walks the k-ary tree: the lanes take the children of the current node (k = 10 in ORBvoc),
+// compute their Hamming distances and the warp keeps the first minimum in child order (strict <).
+// ------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_bow_transform(int L, const int32_t* __restrict__ childStart,
+                                                       const int32_t* __restrict__ childIds, const uint8_t* __restrict__ nodeDesc,
+                                                       const int32_t* __restrict__ wordId, const double* __restrict__ weight,
+                                                       const uint8_t* __restrict__ desc, int n, int levelsup,
+                                                       int32_t* __restrict__ outWord, int32_t* __restrict__ outNode,
+                                                       double* __restrict__ outWeight)
+{
+    const int lane = threadIdx.x & 31;
+    const int f = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (f >= n) return;
+    const Desc D = load_desc(desc + 32 * (size_t)f);
+    const int nidLevel = L - levelsup;
+    int nid = 0, cur = 0, level = 0;
+    for (;;) {
+        ++level;
+        const int cs = childStart[cur], ce = childStart[cur + 1];
+        uint32_t best = 0xFFFFFFFFu;  // dist << 22 | child position
+        for (int c = cs + lane; c < ce; c += 32) {
+            const int id = childIds[c];
+            const int d = hamming(D, load_desc(nodeDesc + 32 * (size_t)id));
+            best = min(best, ((uint32_t)d << 22) | (uint32_t)(c - cs));
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+        cur = childIds[cs + (int)(best & ((1u << 22) - 1))];
+        if (level == nidLevel) nid = cur;
+        if (childStart[cur + 1] <= childStart[cur]) break;  // leaf
+    }
+    if (lane == 0) { outWord[f] = wordId[cur]; outNode[f] = nid; outWeight[f] = weight[cur]; }
+}
+
+// ------------------------------------------------------------------------------------------------------
 // K7d: SearchByBoW(KF, F).  A frame feature belongs to exactly one vocabulary node (DBoW2 FeatureVector invariant),
 // so the order-dependent "skip frame features already matched" only couples KF features of the same node: one warp
 // per shared node walks its KF features in order, lanes scan the node's frame features.
@@ -984,6 +1021,76 @@ int orbm_stereo_match(orbm_context* m, orbx_handle* ex_left, int frame_left, orb
         for (int i = 0; i < nl; i++) k += u_right[i] >= 0;
         *n_matched = k;
     }
+    return ORBX_OK;
+}
+
+struct orbm_vocab {
+    int device, nNodes, L;
+    char* mem;
+    int32_t* childStart; int32_t* childIds; uint8_t* nodeDesc; int32_t* wordId; double* weight;
+};
+
+int orbm_vocab_create(orbm_context* m, int n_nodes, int L, const int32_t* child_start, const int32_t* child_ids,
+                      const uint8_t* node_desc, const int32_t* word_id, const double* weight, orbm_vocab** out)
+{
+    if (!m || !out || n_nodes <= 0 || L <= 0 || !child_start || !child_ids || !node_desc || !word_id || !weight ||
+        child_start[1] <= child_start[0]) {
+        set_error("orbm_vocab_create: bad argument (the root, node 0, must have children)");
+        return ORBX_ERR_BAD_ARG;
+    }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    const int nEdges = child_start[n_nodes];
+    Carver c;
+    const size_t oW = c.take(8 * (size_t)n_nodes), oD = c.take(32 * (size_t)n_nodes), oS = c.take(4 * (size_t)(n_nodes + 1)),
+                 oC = c.take(4 * (size_t)std::max(nEdges, 1)), oI = c.take(4 * (size_t)n_nodes);
+    orbm_vocab* v = new orbm_vocab;
+    v->device = m->device; v->nNodes = n_nodes; v->L = L; v->mem = nullptr;
+    cudaError_t e = cudaMalloc(&v->mem, c.off);
+    if (e != cudaSuccess) { set_error("orbm_vocab_create: %s", cudaGetErrorString(e)); delete v; return ORBX_ERR_CUDA; }
+    v->weight = (double*)(v->mem + oW); v->nodeDesc = (uint8_t*)(v->mem + oD); v->childStart = (int32_t*)(v->mem + oS);
+    v->childIds = (int32_t*)(v->mem + oC); v->wordId = (int32_t*)(v->mem + oI);
+    int rc;
+    if ((rc = up<double>(m, v->weight, weight, n_nodes)) != ORBX_OK || (rc = up<uint8_t>(m, v->nodeDesc, node_desc, 32 * (size_t)n_nodes)) != ORBX_OK ||
+        (rc = up<int32_t>(m, v->childStart, child_start, n_nodes + 1)) != ORBX_OK || (rc = up<int32_t>(m, v->childIds, child_ids, nEdges)) != ORBX_OK ||
+        (rc = up<int32_t>(m, v->wordId, word_id, n_nodes)) != ORBX_OK) {
+        cudaFree(v->mem); delete v; return rc;
+    }
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    *out = v;
+    return ORBX_OK;
+}
+
+void orbm_vocab_destroy(orbm_vocab* v)
+{
+    if (!v) return;
+    cudaSetDevice(v->device);
+    cudaFree(v->mem);
+    delete v;
+}
+
+int orbm_bow_transform(orbm_context* m, const orbm_vocab* v, const uint8_t* desc, int n, int levelsup, int32_t* word_id,
+                       int32_t* node_id, double* weight)
+{
+    if (!m || !v || n < 0 || (n > 0 && (!desc || !word_id || !node_id || !weight)) || v->device != m->device) {
+        set_error("orbm_bow_transform: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    if (n == 0) return ORBX_OK;
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    Carver c;
+    const size_t oWt = c.take(8 * (size_t)n), oD = c.take(32 * (size_t)n), oW = c.take(4 * (size_t)n), oN = c.take(4 * (size_t)n);
+    int rc = ensure_arena(m, c.off);
+    if (rc != ORBX_OK) return rc;
+    char* A = m->arena;
+    if ((rc = up<uint8_t>(m, (uint8_t*)(A + oD), desc, 32 * (size_t)n)) != ORBX_OK) return rc;
+    k_bow_transform<<<(n + 7) / 8, 256, 0, m->stream>>>(v->L, v->childStart, v->childIds, v->nodeDesc, v->wordId, v->weight,
+                                                       (uint8_t*)(A + oD), n, levelsup, (int32_t*)(A + oW), (int32_t*)(A + oN),
+                                                       (double*)(A + oWt));
+    ORBX_CUDA_TRY(cudaGetLastError());
+    ORBX_CUDA_TRY(cudaMemcpyAsync(word_id, A + oW, 4 * (size_t)n, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(node_id, A + oN, 4 * (size_t)n, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(weight, A + oWt, 8 * (size_t)n, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
     return ORBX_OK;
 }
 

@@ -215,3 +215,34 @@ def test_full_stereo_matching_vs_oracle(gpu, oracle_mod, seed):
     assert np.array_equal(ur.view(np.uint32), ur_ref.view(np.uint32))
     assert np.array_equal(dp.view(np.uint32), dp_ref.view(np.uint32))
     m.close(); gL.close(); gR.close()
+
+
+@pytest.mark.parametrize("k,L,levelsup", [(10, 3, 2), (10, 4, 4), (7, 5, 4), (3, 2, 4)])
+def test_bow_transform_vs_oracle(gpu, oracle_mod, k, L, levelsup):
+    """DBoW2 vocabulary descent on a synthetic k-ary tree: word id, node id `levelsup` above the leaves, weight."""
+    from orbslam2commentedbyxcm_b200 import vocabulary
+
+    vocab = vocabulary.synthetic_vocabulary(k, L, seed=k * 10 + L)
+    # duplicate child descriptors so that the "first minimum in child order" rule is exercised
+    vocab["node_desc"][2] = vocab["node_desc"][1]
+    vocab["node_desc"][k + 3] = vocab["node_desc"][k + 2]
+    desc = synth.gen_descriptors(1500, seed=5)
+    desc[:50] = vocab["node_desc"][1]
+    m = gpu.ORBmatcher()
+    voc = vocabulary.ORBVocabulary(vocab, m)
+    w, nd, wt = voc.transform_features(desc, levelsup)
+    ow, ond, owt = oracle_mod.bow_transform(vocab, desc, levelsup)
+    assert np.array_equal(w, ow) and np.array_equal(nd, ond) and np.array_equal(wt.view(np.uint64), owt.view(np.uint64))
+    if L - levelsup <= 0:
+        assert (nd == 0).all()
+    # the folded FeatureVector feeds SearchByBoW: frame vs itself must match every non-stopped feature to itself
+    (ids, vals), fv = voc.transform(desc[100:600], levelsup)
+    assert abs(vals.sum() - 1.0) < 1e-9 and np.all(np.diff(ids) > 0)
+    d = np.ascontiguousarray(desc[100:600])
+    ang = np.zeros(len(d), np.float32)
+    kf = dict(desc=d, angle=ang, has_mp=np.ones(len(d), np.uint8), **fv)
+    fr = dict(desc=d, angle=ang, **fv)
+    n, out = gpu.ORBmatcher(0.9, True).SearchByBoW(kf, fr)
+    on, oout = oracle_mod.search_by_bow(kf, fr, 0.9, True)
+    assert n == on and np.array_equal(out, oout)
+    voc.close(); m.close()
