@@ -191,6 +191,33 @@ typedef struct orbm_mappoint_view {
 int orbm_search_by_projection(orbm_context* m, const orbm_frame_view* f, const orbm_mappoint_view* p, float th,
                               float nnratio, int32_t* out_match, int* nmatches);
 
+/* Source features of a windowed search AFTER the caller's projection step (the adapter keeps the reference's own
+ * cv::Mat arithmetic for Rcw*x3Dw+tcw, fx*xc*invzc+cx, PredictScale, ...). */
+typedef struct orbm_window_query_view {
+    int n;
+    const float* x;              /* projected u */
+    const float* y;              /* projected v */
+    const float* radius;         /* window half-size handed to Frame::GetFeaturesInArea */
+    const int32_t* min_level;    /* minLevel / maxLevel arguments of GetFeaturesInArea (-1 = open) */
+    const int32_t* max_level;
+    const float* xr;             /* predicted right coordinate u - mbf*invz for the stereo gate; NULL = no gate */
+    const float* angle;          /* source keypoint angle (rotation histogram); NULL when check_orientation == 0 */
+    const uint8_t* valid;        /* 0 = skipped by the reference before the search (no map point, outlier, behind camera, ...) */
+    const uint8_t* claims_block; /* 1 = a keypoint claimed by this query is skipped by later queries */
+    const uint8_t* desc;         /* n x 32 */
+} orbm_window_query_view;
+
+/* Windowed search with the reference's order-dependent claims, shared by
+ *   ORBmatcher::SearchByProjection(Frame& Cur, const Frame& Last, th, bMono)          src/ORBmatcher.cc:1620-1789
+ *   ORBmatcher::SearchByProjection(Frame& Cur, KeyFrame*, sAlreadyFound, th, ORBdist)  src/ORBmatcher.cc:1792-1924
+ * (max_dist = TH_HIGH resp. ORBdist, ratio_mode 0, check_orientation = mbCheckOrientation; for the KeyFrame overload
+ * pass occupied[i] = (mvpMapPoints[i] != NULL), claims_block = 1 and xr = NULL) and, with ratio_mode 1, by
+ * orbm_search_by_projection.  f_angle = Cur.mvKeysUn[i].angle.  HOST pointers.
+ * out_match[i]: -1 = slot untouched, -2 = set to NULL by the rotation-histogram filter, >= 0 = query index stored. */
+int orbm_search_window(orbm_context* m, const orbm_frame_view* f, const float* f_angle, const orbm_window_query_view* q,
+                       int max_dist, int ratio_mode, float nnratio, int check_orientation, int32_t* out_match,
+                       int* nmatches);
+
 /* Replaces the coarse Hamming search of Frame::ComputeStereoMatches (src/Frame.cc:684-765).  HOST pointers.
  * best_r[i] = right keypoint index for left keypoint i or -1 (distance >= (TH_HIGH+TH_LOW)/2 or no candidate);
  * best_dist[i] = the best distance found (TH_HIGH when none). */

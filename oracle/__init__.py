@@ -141,6 +141,9 @@ def _bind_all(L):
     L.orbo_get_level_ptr.argtypes = [_vp, _i, _vp]
     L.orbo_stereo_match.restype = _i
     L.orbo_stereo_match.argtypes = [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _f, _vp, _vp]
+    L.orbo_search_window.restype = _i
+    L.orbo_search_window.argtypes = ([_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _vp]
+                                     + [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp] + [_i, _i, _f, _i, _vp])
     L.orbo_bow_transform.argtypes = [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]
     L.orbo_search_by_bow.restype = _i
     L.orbo_search_by_bow.argtypes = (
@@ -366,3 +369,18 @@ def bow_transform(vocab, desc, levelsup=4):
                          _ptr(vocab["node_desc"]), _ptr(vocab["word_id"]), _ptr(vocab["weight"]), desc.ctypes.data, n, levelsup,
                          w.ctypes.data, nd.ctypes.data, wt.ctypes.data)
     return w[:n], nd[:n], wt[:n]
+
+
+def search_window(frame, q, max_dist, ratio_mode, nnratio, check_orientation):
+    """Generic windowed search (SearchByProjection(Cur, Last) / (Cur, KF, found) after projection); see match_oracle.cc."""
+    L = lib()
+    nkp = len(frame["x"])
+    out = np.full(max(nkp, 1), -1, np.int32)
+    n = L.orbo_search_window(
+        nkp, _ptr(frame["x"]), _ptr(frame["y"]), _ptr(frame["octave"]), _ptr(frame.get("u_right")), _ptr(frame["desc"]),
+        _ptr(frame["occupied"]), _ptr(frame["cell_start"]), _ptr(frame["cell_items"]),
+        frame["min_x"], frame["min_y"], frame["w_inv"], frame["h_inv"], _ptr(frame.get("angle")),
+        len(q["x"]), _ptr(q["x"]), _ptr(q["y"]), _ptr(q["radius"]), _ptr(q["min_level"]), _ptr(q["max_level"]), _ptr(q["xr"]),
+        _ptr(q.get("angle")), _ptr(q["valid"]), _ptr(q["blocks"]), _ptr(q["desc"]),
+        int(max_dist), int(ratio_mode), float(nnratio), int(check_orientation), out.ctypes.data)
+    return n, out[:nkp]

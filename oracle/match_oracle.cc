@@ -387,3 +387,98 @@ extern "C" void orbo_bow_transform(int n_nodes, int L, const int32_t* child_star
         out_node[f] = nid;
     }
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Windowed search shared by the remaining SearchByProjection overloads ("next" row):
+//   ORBmatcher::SearchByProjection(Frame& Cur, const Frame& Last, th, bMono)              src/ORBmatcher.cc:1620-1789
+//   ORBmatcher::SearchByProjection(Frame& Cur, KeyFrame*, sAlreadyFound, th, ORBdist)     src/ORBmatcher.cc:1792-1924
+// after their projection step (done by the caller with the reference's own cv::Mat arithmetic): per source feature a
+// projected position (u, v), window radius, the level arguments handed to Frame::GetFeaturesInArea, the predicted right
+// coordinate `ur` and the source keypoint angle.  Candidate loop, acceptance `bestDist <= maxDist`, claims, rotation
+// histogram and ComputeThreeMaxima exactly as in those functions.  ratio_mode 1 adds the level-aware ratio test of the
+// (Frame, MapPoints) overload.  out_match: -1 untouched, -2 set to NULL by the orientation filter, else query index.
+// ---------------------------------------------------------------------------------------------------------------------
+extern "C" int orbo_search_window(
+    int nkp, const float* kx, const float* ky, const int32_t* koct, const float* uright, const uint8_t* kdesc,
+    const uint8_t* occupied, const int32_t* cell_start, const int32_t* cell_items, float minX, float minY, float wInv,
+    float hInv, const float* kangle,
+    int nq, const float* qx, const float* qy, const float* qradius, const int32_t* qmin, const int32_t* qmax,
+    const float* qxr, const float* qangle, const uint8_t* qvalid, const uint8_t* qblocks, const uint8_t* qdesc,
+    int maxDist, int ratioMode, float nnratio, int checkOrientation, int32_t* out_match)
+{
+    std::vector<uint8_t> occ(occupied, occupied + nkp);
+    for (int i = 0; i < nkp; i++) out_match[i] = -1;
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = HISTO_LENGTH / 360.0f;
+    for (int m = 0; m < nq; m++) {
+        if (!qvalid[m]) continue;
+        const float x = qx[m], y = qy[m], rr = qradius[m];
+        const int minLevel = qmin[m], maxLevel = qmax[m];
+        const int c0 = std::max(0, (int)std::floor((x - minX - rr) * wInv));
+        if (c0 >= GRID_COLS) continue;
+        const int c1 = std::min(GRID_COLS - 1, (int)std::ceil((x - minX + rr) * wInv));
+        if (c1 < 0) continue;
+        const int r0 = std::max(0, (int)std::floor((y - minY - rr) * hInv));
+        if (r0 >= GRID_ROWS) continue;
+        const int r1 = std::min(GRID_ROWS - 1, (int)std::ceil((y - minY + rr) * hInv));
+        if (r1 < 0) continue;
+        const bool checkLevels = (minLevel > 0) || (maxLevel >= 0);
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (int ix = c0; ix <= c1; ix++)
+            for (int iy = r0; iy <= r1; iy++) {
+                const int c = ix * GRID_ROWS + iy;
+                for (int k = cell_start[c]; k < cell_start[c + 1]; k++) {
+                    const int idx = cell_items[k];
+                    if (checkLevels) {
+                        if (koct[idx] < minLevel) continue;
+                        if (maxLevel >= 0 && koct[idx] > maxLevel) continue;
+                    }
+                    const float dx = kx[idx] - x, dy = ky[idx] - y;
+                    if (!(std::fabs(dx) < rr && std::fabs(dy) < rr)) continue;
+                    if (occ[idx]) continue;
+                    if (uright && uright[idx] > 0) {
+                        const float er = std::fabs(qxr[m] - uright[idx]);
+                        if (er > rr) continue;
+                    }
+                    const int dist = hamming256(qdesc + 32 * (size_t)m, kdesc + 32 * (size_t)idx);
+                    if (dist < bestDist) {
+                        bestDist2 = bestDist; bestDist = dist;
+                        bestLevel2 = bestLevel; bestLevel = koct[idx];
+                        bestIdx = idx;
+                    } else if (dist < bestDist2) {
+                        bestLevel2 = koct[idx];
+                        bestDist2 = dist;
+                    }
+                }
+            }
+        if (bestIdx < 0 || bestDist > maxDist) continue;
+        if (ratioMode == 1 && bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
+        out_match[bestIdx] = m;
+        occ[bestIdx] = qblocks[m] ? 1 : 0;
+        nmatches++;
+        if (checkOrientation) {
+            float rot = qangle[m] - kangle[bestIdx];
+            if (rot < 0.0) rot += 360.0f;
+            int bin = (int)std::round(rot * factor);
+            if (bin == HISTO_LENGTH) bin = 0;
+            rotHist[bin].push_back(bestIdx);
+        }
+    }
+    if (checkOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            const int s = (int)rotHist[i].size();
+            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+            else if (s > max3) { max3 = s; ind3 = i; }
+        }
+        if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+        else if (max3 < 0.1f * (float)max1) ind3 = -1;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int f : rotHist[i]) { out_match[f] = -2; nmatches--; }
+        }
+    }
+    return nmatches;
+}

@@ -37,6 +37,12 @@ class MapPointView(C.Structure):
                 ("desc", C.c_void_p)]
 
 
+class WindowQueryView(C.Structure):
+    _fields_ = [("n", C.c_int), ("x", C.c_void_p), ("y", C.c_void_p), ("radius", C.c_void_p), ("min_level", C.c_void_p),
+                ("max_level", C.c_void_p), ("xr", C.c_void_p), ("angle", C.c_void_p), ("valid", C.c_void_p),
+                ("claims_block", C.c_void_p), ("desc", C.c_void_p)]
+
+
 class FeatVecView(C.Structure):
     _fields_ = [("n_nodes", C.c_int), ("node_id", C.c_void_p), ("node_start", C.c_void_p), ("node_feat", C.c_void_p)]
 
@@ -72,6 +78,7 @@ SIGNATURES = {
     "orbm_bruteforce": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _i]),
     "orbm_merge_partials": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]),
     "orbm_search_by_projection": (_i, [_vp, C.POINTER(FrameView), C.POINTER(MapPointView), _f, _f, _vp, _vp]),
+    "orbm_search_window": (_i, [_vp, C.POINTER(FrameView), _vp, C.POINTER(WindowQueryView), _i, _i, _f, _i, _vp, _vp]),
     "orbm_stereo_rows": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _f, _f, _vp, _vp]),
     "orbm_stereo_match": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp]),
     "orbm_vocab_create": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, C.POINTER(_vp)]),

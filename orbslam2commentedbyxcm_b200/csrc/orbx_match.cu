@@ -225,12 +225,15 @@ struct ProjArgs {
     const float* kx; const float* ky; const int32_t* koct; const float* uright; const uint8_t* kdesc;
     const uint8_t* occupied; const int32_t* cellStart; const int32_t* cellItems;
     float minX, minY, wInv, hInv;
-    const float* scaleFactors;
-    // map points
+    const float* kangle;  // mvKeysUn[i].angle (orientation histogram only)
+    // queries (map points / source features after projection)
     int nmp;
-    const float* px; const float* py; const float* pxr; const int32_t* plevel; const float* pviewcos;
+    const float* px; const float* py; const float* pxr; const float* prr; const int32_t* pmin; const int32_t* pmax;
+    const float* pangle;
     const uint8_t* pvalid; const uint8_t* pobs; const uint8_t* pdesc;
-    float th, nnratio;
+    float nnratio;
+    int maxDist, ratioMode, checkOri;
+    int* hist;          // [HISTO_LENGTH] rotation histogram
     // work / output
     int32_t* res;       // per map point: claimed keypoint or -1
     int32_t* claimA;    // per keypoint: smallest blocking map point index claiming it (INT_MAX = none)
@@ -241,13 +244,19 @@ struct ProjArgs {
     int* sweeps;
 };
 
+// rotation-histogram bin of a match (src/ORBmatcher.cc:1731-1738): round((a1 - a2 [+360]) * HISTO_LENGTH/360), 30 -> 0
+__device__ __forceinline__ int rot_bin(float a1, float a2)
+{
+    float rot = __fsub_rn(a1, a2);
+    if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+    int bin = (int)roundf(__fmul_rn(rot, 0.0833333358f));
+    return bin == HISTO_LENGTH ? 0 : bin;
+}
+
 __device__ int proj_one(const ProjArgs& A, int m, const int32_t* claimPrev, int lane)
 {
     if (!A.pvalid[m]) return -1;
-    const int level = A.plevel[m];
-    float r = A.pviewcos[m] > 0.998 ? 2.5f : 4.0f;
-    if (A.th != 1.0f) r = __fmul_rn(r, A.th);
-    const float rr = __fmul_rn(r, A.scaleFactors[level]);
+    const float rr = A.prr[m];
     const float x = A.px[m], y = A.py[m];
     const int c0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, A.minX), rr), A.wInv)));
     if (c0 >= GRID_COLS) return -1;
@@ -257,7 +266,7 @@ __device__ int proj_one(const ProjArgs& A, int m, const int32_t* claimPrev, int 
     if (r0 >= GRID_ROWS) return -1;
     const int r1 = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, A.minY), rr), A.hInv)));
     if (r1 < 0) return -1;
-    const int minLevel = level - 1, maxLevel = level;
+    const int minLevel = A.pmin[m], maxLevel = A.pmax[m];
     const bool checkLevels = (minLevel > 0) || (maxLevel >= 0);
     const Desc D = load_desc(A.pdesc + 32 * (size_t)m);
     const float xr = A.pxr[m];
@@ -291,11 +300,13 @@ __device__ int proj_one(const ProjArgs& A, int m, const int32_t* claimPrev, int 
     top2_warp_reduce(t);
     if (t.p1 < 0) return -1;
     const int bestDist = t.k1 >> 23;
-    if (bestDist > TH_HIGH) return -1;
-    const int bestLevel = A.koct[t.p1];
-    const int bestLevel2 = t.p2 >= 0 ? A.koct[t.p2] : -1;
-    const int bestDist2 = t.p2 >= 0 ? (int)(t.k2 >> 23) : 256;
-    if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(A.nnratio, (float)bestDist2)) return -1;
+    if (bestDist > A.maxDist) return -1;
+    if (A.ratioMode == 1) {
+        const int bestLevel = A.koct[t.p1];
+        const int bestLevel2 = t.p2 >= 0 ? A.koct[t.p2] : -1;
+        const int bestDist2 = t.p2 >= 0 ? (int)(t.k2 >> 23) : 256;
+        if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(A.nnratio, (float)bestDist2)) return -1;
+    }
     return t.p1;
 }
 
@@ -311,6 +322,7 @@ __global__ void __launch_bounds__(256) k_proj_search(ProjArgs A)
     for (int i = gtid; i < A.nkp; i += gthreads) { claimPrev[i] = 0x7fffffff; A.outMatch[i] = -1; }
     for (int m = gtid; m < A.nmp; m += gthreads) A.res[m] = -1;
     if (gtid == 0) { A.changed[0] = 0; A.changed[1] = 0; *A.nmatches = 0; }
+    if (gtid < HISTO_LENGTH) A.hist[gtid] = 0;
     grid.sync();
     int sweep = 0;
     for (;; sweep++) {
@@ -334,10 +346,37 @@ __global__ void __launch_bounds__(256) k_proj_search(ProjArgs A)
     int local = 0;
     for (int m = gtid; m < A.nmp; m += gthreads) {
         const int r = A.res[m];
-        if (r >= 0) { atomicMax(&A.outMatch[r], m); local++; }
+        if (r >= 0) {
+            atomicMax(&A.outMatch[r], m);
+            local++;
+            if (A.checkOri) atomicAdd(&A.hist[rot_bin(A.pangle[m], A.kangle[r])], 1);
+        }
     }
     if (local) atomicAdd(A.nmatches, local);
     if (gtid == 0) *A.sweeps = sweep + 1;
+    if (!A.checkOri) return;
+    grid.sync();
+    // ComputeThreeMaxima + removal of the matches outside the three main rotation bins (set to NULL: -2)
+    __shared__ int keepBin[HISTO_LENGTH];
+    if (threadIdx.x == 0) {
+        int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            const int sN = A.hist[i];
+            if (sN > max1) { max3 = max2; max2 = max1; max1 = sN; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (sN > max2) { max3 = max2; max2 = sN; ind3 = ind2; ind2 = i; }
+            else if (sN > max3) { max3 = sN; ind3 = i; }
+        }
+        if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+        else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) ind3 = -1;
+        for (int i = 0; i < HISTO_LENGTH; i++) keepBin[i] = (i == ind1 || i == ind2 || i == ind3);
+    }
+    __syncthreads();
+    int removed = 0;
+    for (int m = gtid; m < A.nmp; m += gthreads) {
+        const int r = A.res[m];
+        if (r >= 0 && !keepBin[rot_bin(A.pangle[m], A.kangle[r])]) { A.outMatch[r] = -2; removed++; }
+    }
+    if (removed) atomicSub(A.nmatches, removed);
 }
 
 // ------------------------------------------------------------------------------------------------------
@@ -804,14 +843,15 @@ int orbm_merge_partials(orbm_context* m, const int32_t* best, const int32_t* bes
     return ORBX_OK;
 }
 
-int orbm_search_by_projection(orbm_context* m, const orbm_frame_view* f, const orbm_mappoint_view* p, float th,
-                              float nnratio, int32_t* out_match, int* nmatches)
+int orbm_search_window(orbm_context* m, const orbm_frame_view* f, const float* f_angle, const orbm_window_query_view* q,
+                       int max_dist, int ratio_mode, float nnratio, int check_orientation, int32_t* out_match, int* nmatches)
 {
-    if (!m || !f || !p || !out_match || !nmatches || f->n < 0 || p->n < 0 || !f->scale_factors || f->nlevels <= 0) {
-        set_error("orbm_search_by_projection: bad argument");
+    if (!m || !f || !q || !out_match || !nmatches || f->n < 0 || q->n < 0 || (check_orientation && (!f_angle || !q->angle)) ||
+        f->n >= (1 << 30)) {
+        set_error("orbm_search_window: bad argument");
         return ORBX_ERR_BAD_ARG;
     }
-    const int nkp = f->n, nmp = p->n;
+    const int nkp = f->n, nmp = q->n;
     if (nkp == 0 || nmp == 0) {
         for (int i = 0; i < nkp; i++) out_match[i] = -1;
         *nmatches = 0;
@@ -822,51 +862,52 @@ int orbm_search_by_projection(orbm_context* m, const orbm_frame_view* f, const o
     const int nitems = f->cell_start[ncell];
     for (int ci = 0; ci < ncell; ci++)
         if (f->cell_start[ci + 1] - f->cell_start[ci] >= 2048) {
-            set_error("orbm_search_by_projection: a grid cell holds %d keypoints (limit 2047)", f->cell_start[ci + 1] - f->cell_start[ci]);
+            set_error("orbm_search_window: a grid cell holds %d keypoints (limit 2047)", f->cell_start[ci + 1] - f->cell_start[ci]);
             return ORBX_ERR_BAD_ARG;
         }
     Carver c;
     const size_t oKx = c.take(4 * (size_t)nkp), oKy = c.take(4 * (size_t)nkp), oKo = c.take(4 * (size_t)nkp),
-                 oUr = c.take(4 * (size_t)nkp), oKd = c.take(32 * (size_t)nkp), oOcc = c.take(nkp),
-                 oCs = c.take(4 * (size_t)(ncell + 1)), oCi = c.take(4 * (size_t)std::max(nitems, 1)),
-                 oSf = c.take(4 * (size_t)f->nlevels);
+                 oUr = c.take(4 * (size_t)nkp), oKa = c.take(4 * (size_t)nkp), oKd = c.take(32 * (size_t)nkp), oOcc = c.take(nkp),
+                 oCs = c.take(4 * (size_t)(ncell + 1)), oCi = c.take(4 * (size_t)std::max(nitems, 1));
     const size_t oPx = c.take(4 * (size_t)nmp), oPy = c.take(4 * (size_t)nmp), oPxr = c.take(4 * (size_t)nmp),
-                 oPl = c.take(4 * (size_t)nmp), oPv = c.take(4 * (size_t)nmp), oPva = c.take(nmp), oPo = c.take(nmp),
-                 oPd = c.take(32 * (size_t)nmp);
+                 oPr = c.take(4 * (size_t)nmp), oPmin = c.take(4 * (size_t)nmp), oPmax = c.take(4 * (size_t)nmp),
+                 oPa = c.take(4 * (size_t)nmp), oPva = c.take(nmp), oPo = c.take(nmp), oPd = c.take(32 * (size_t)nmp);
     const size_t oRes = c.take(4 * (size_t)nmp), oCa = c.take(4 * (size_t)nkp), oCb = c.take(4 * (size_t)nkp),
-                 oOut = c.take(4 * (size_t)nkp), oMisc = c.take(64);
+                 oOut = c.take(4 * (size_t)nkp), oMisc = c.take(256);
     int rc = ensure_arena(m, c.off);
     if (rc != ORBX_OK) return rc;
     char* A = m->arena;
 #define UP(off, ptr, count, T) if ((rc = up<T>(m, (T*)(A + off), ptr, count)) != ORBX_OK) return rc
     UP(oKx, f->x, nkp, float); UP(oKy, f->y, nkp, float); UP(oKo, f->octave, nkp, int32_t);
     if (f->u_right) UP(oUr, f->u_right, nkp, float);
+    if (f_angle) UP(oKa, f_angle, nkp, float);
     UP(oKd, f->desc, 32 * (size_t)nkp, uint8_t); UP(oOcc, f->occupied, nkp, uint8_t);
     UP(oCs, f->cell_start, ncell + 1, int32_t); UP(oCi, f->cell_items, nitems, int32_t);
-    UP(oSf, f->scale_factors, f->nlevels, float);
-    UP(oPx, p->proj_x, nmp, float); UP(oPy, p->proj_y, nmp, float); UP(oPxr, p->proj_xr, nmp, float);
-    UP(oPl, p->level, nmp, int32_t); UP(oPv, p->view_cos, nmp, float); UP(oPva, p->valid, nmp, uint8_t);
-    UP(oPo, p->obs_pos, nmp, uint8_t); UP(oPd, p->desc, 32 * (size_t)nmp, uint8_t);
+    UP(oPx, q->x, nmp, float); UP(oPy, q->y, nmp, float);
+    if (q->xr) UP(oPxr, q->xr, nmp, float);
+    UP(oPr, q->radius, nmp, float); UP(oPmin, q->min_level, nmp, int32_t); UP(oPmax, q->max_level, nmp, int32_t);
+    if (q->angle) UP(oPa, q->angle, nmp, float);
+    UP(oPva, q->valid, nmp, uint8_t); UP(oPo, q->claims_block, nmp, uint8_t); UP(oPd, q->desc, 32 * (size_t)nmp, uint8_t);
 #undef UP
     ProjArgs a;
     a.nkp = nkp;
     a.kx = (float*)(A + oKx); a.ky = (float*)(A + oKy); a.koct = (int32_t*)(A + oKo);
-    a.uright = f->u_right ? (float*)(A + oUr) : nullptr;
+    a.uright = (f->u_right && q->xr) ? (float*)(A + oUr) : nullptr;
     a.kdesc = (uint8_t*)(A + oKd); a.occupied = (uint8_t*)(A + oOcc);
     a.cellStart = (int32_t*)(A + oCs); a.cellItems = (int32_t*)(A + oCi);
     a.minX = f->min_x; a.minY = f->min_y; a.wInv = f->grid_w_inv; a.hInv = f->grid_h_inv;
-    a.scaleFactors = (float*)(A + oSf);
+    a.kangle = (float*)(A + oKa);
     a.nmp = nmp;
-    a.px = (float*)(A + oPx); a.py = (float*)(A + oPy); a.pxr = (float*)(A + oPxr); a.plevel = (int32_t*)(A + oPl);
-    a.pviewcos = (float*)(A + oPv); a.pvalid = (uint8_t*)(A + oPva); a.pobs = (uint8_t*)(A + oPo);
-    a.pdesc = (uint8_t*)(A + oPd);
-    a.th = th; a.nnratio = nnratio;
+    a.px = (float*)(A + oPx); a.py = (float*)(A + oPy); a.pxr = (float*)(A + oPxr); a.prr = (float*)(A + oPr);
+    a.pmin = (int32_t*)(A + oPmin); a.pmax = (int32_t*)(A + oPmax); a.pangle = (float*)(A + oPa);
+    a.pvalid = (uint8_t*)(A + oPva); a.pobs = (uint8_t*)(A + oPo); a.pdesc = (uint8_t*)(A + oPd);
+    a.nnratio = nnratio; a.maxDist = max_dist; a.ratioMode = ratio_mode; a.checkOri = check_orientation ? 1 : 0;
     a.res = (int32_t*)(A + oRes); a.claimA = (int32_t*)(A + oCa); a.claimB = (int32_t*)(A + oCb);
     a.outMatch = (int32_t*)(A + oOut);
-    a.changed = (int*)(A + oMisc); a.nmatches = a.changed + 2; a.sweeps = a.changed + 3;
+    a.changed = (int*)(A + oMisc); a.nmatches = a.changed + 2; a.sweeps = a.changed + 3; a.hist = a.changed + 8;
     int perSM = 0;
     ORBX_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_proj_search, 256, 0));
-    const int want = (nmp + 7) / 8;  // 8 warps per CTA, one warp per map point
+    const int want = (nmp + 7) / 8;  // 8 warps per CTA, one warp per query
     const int grid = std::max(1, std::min(want, perSM * m->numSMs));
     void* args[] = {&a};
     ORBX_CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_proj_search, dim3(grid), dim3(256), args, 0, m->stream));
@@ -874,6 +915,34 @@ int orbm_search_by_projection(orbm_context* m, const orbm_frame_view* f, const o
     ORBX_CUDA_TRY(cudaMemcpyAsync(nmatches, a.nmatches, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
     ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
     return ORBX_OK;
+}
+
+int orbm_search_by_projection(orbm_context* m, const orbm_frame_view* f, const orbm_mappoint_view* p, float th,
+                              float nnratio, int32_t* out_match, int* nmatches)
+{
+    if (!m || !f || !p || !out_match || !nmatches || f->n < 0 || p->n < 0 || !f->scale_factors || f->nlevels <= 0) {
+        set_error("orbm_search_by_projection: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    // window radius and level range per map point (src/ORBmatcher.cc:84-96, RadiusByViewingCos :176-183)
+    const int n = p->n;
+    std::vector<float> radius(n > 0 ? n : 1);
+    std::vector<int32_t> lmin(n > 0 ? n : 1), lmax(n > 0 ? n : 1);
+    std::vector<uint8_t> valid(n > 0 ? n : 1);
+    const bool bFactor = th != 1.0f;
+    for (int i = 0; i < n; i++) {
+        const int level = p->level[i];
+        valid[i] = p->valid[i] && level >= 0 && level < f->nlevels;
+        float r = p->view_cos[i] > 0.998 ? 2.5f : 4.0f;
+        if (bFactor) r *= th;
+        radius[i] = valid[i] ? r * f->scale_factors[level] : 0.f;
+        lmin[i] = level - 1;
+        lmax[i] = level;
+    }
+    orbm_window_query_view q;
+    q.n = n; q.x = p->proj_x; q.y = p->proj_y; q.radius = radius.data(); q.min_level = lmin.data(); q.max_level = lmax.data();
+    q.xr = p->proj_xr; q.angle = nullptr; q.valid = valid.data(); q.claims_block = p->obs_pos; q.desc = p->desc;
+    return orbm_search_window(m, f, nullptr, &q, TH_HIGH, 1, nnratio, 0, out_match, nmatches);
 }
 
 int orbm_stereo_rows(orbm_context* m, int nl, const float* lx, const float* ly, const int32_t* loct, const uint8_t* ldesc,

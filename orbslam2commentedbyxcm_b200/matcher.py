@@ -129,6 +129,45 @@ class ORBmatcher:
                                                 out.ctypes.data, C.byref(nm)), "orbm_search_by_projection")
         return nm.value, out[:n]
 
+    # ---- windowed search shared by SearchByProjection(Cur, Last, th, bMono) and (Cur, KF, found, th, ORBdist) ----
+    def SearchWindow(self, frame, q, max_dist=100, ratio_mode=0):
+        """frame: frame dict (+ "angle" = mvKeysUn angles when mbCheckOrientation); q: dict with x, y, radius, min_level,
+        max_level, xr (or None), angle (or None), valid, blocks, desc -- the source features after projection.
+        Returns (nmatches, out) with out[i] = -1 untouched, -2 set to NULL by the rotation filter, else query index."""
+        keep = []
+
+        def arr(v, dt):
+            a = np.ascontiguousarray(v, dt)
+            keep.append(a)
+            return a
+
+        n = len(frame["x"])
+        fv = _lib.FrameView()
+        fv.n = n
+        fv.x = _p(arr(frame["x"], np.float32)); fv.y = _p(arr(frame["y"], np.float32))
+        fv.octave = _p(arr(frame["octave"], np.int32))
+        fv.u_right = _p(arr(frame["u_right"], np.float32)) if frame.get("u_right") is not None else None
+        fv.desc = _p(arr(frame["desc"], np.uint8)); fv.occupied = _p(arr(frame["occupied"], np.uint8))
+        fv.cell_start = _p(arr(frame["cell_start"], np.int32)); fv.cell_items = _p(arr(frame["cell_items"], np.int32))
+        fv.min_x, fv.min_y, fv.grid_w_inv, fv.grid_h_inv = frame["min_x"], frame["min_y"], frame["w_inv"], frame["h_inv"]
+        sf = arr(frame["scale_factors"], np.float32)
+        fv.scale_factors = _p(sf); fv.nlevels = len(sf)
+        f_angle = arr(frame["angle"], np.float32) if self.mbCheckOrientation else None
+        qv = _lib.WindowQueryView()
+        qv.n = len(q["x"])
+        qv.x = _p(arr(q["x"], np.float32)); qv.y = _p(arr(q["y"], np.float32)); qv.radius = _p(arr(q["radius"], np.float32))
+        qv.min_level = _p(arr(q["min_level"], np.int32)); qv.max_level = _p(arr(q["max_level"], np.int32))
+        qv.xr = _p(arr(q["xr"], np.float32)) if q.get("xr") is not None else None
+        qv.angle = _p(arr(q["angle"], np.float32)) if self.mbCheckOrientation else None
+        qv.valid = _p(arr(q["valid"], np.uint8)); qv.claims_block = _p(arr(q["blocks"], np.uint8))
+        qv.desc = _p(arr(q["desc"], np.uint8))
+        out = np.full(max(n, 1), -1, np.int32)
+        nm = C.c_int()
+        check(self._L.orbm_search_window(self._m, C.byref(fv), _p(f_angle), C.byref(qv), int(max_dist), int(ratio_mode),
+                                         self.mfNNratio, int(self.mbCheckOrientation), out.ctypes.data, C.byref(nm)),
+              "orbm_search_window")
+        return nm.value, out[:n]
+
     # ---- stereo row search (Frame::ComputeStereoMatches coarse part) ----
     def StereoRows(self, left, right, scale_factors, n_rows, min_d, max_d):
         keep = []

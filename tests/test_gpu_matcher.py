@@ -246,3 +246,52 @@ def test_bow_transform_vs_oracle(gpu, oracle_mod, k, L, levelsup):
     on, oout = oracle_mod.search_by_bow(kf, fr, 0.9, True)
     assert n == on and np.array_equal(out, oout)
     voc.close(); m.close()
+
+
+def _window_queries(frame, kps, nq, seed, mode, nlevels=8):
+    """source features 'after projection': mode 'forward' / 'backward' / 'band' = the three GetFeaturesInArea level
+    patterns of SearchByProjection(Cur, Last), 'kf' = the (Cur, KF, found) overload (band, every claim blocks, no gate)."""
+    rng = np.random.Generator(np.random.PCG64(seed + 7))
+    n = len(frame["x"])
+    pick = rng.integers(0, n, nq)
+    pick[nq * 3 // 4:] = pick[rng.integers(0, nq * 3 // 4, nq - nq * 3 // 4)]  # several sources per keypoint
+    octv = np.clip(frame["octave"][pick] + rng.integers(-1, 2, nq), 0, nlevels - 1).astype(np.int32)
+    th = 7.0 if mode != "kf" else 10.0
+    radius = (np.float32(th) * frame["scale_factors"][octv]).astype(np.float32)
+    if mode == "forward":
+        lmin, lmax = octv.copy(), np.full(nq, -1, np.int32)
+    elif mode == "backward":
+        lmin, lmax = np.zeros(nq, np.int32), octv.copy()
+    else:
+        lmin, lmax = octv - 1, octv + 1
+    flips = rng.random((nq, 256)) < rng.choice([0.03, 0.1, 0.3], nq)[:, None]
+    x = (frame["x"][pick] + rng.normal(0, 3.0, nq)).astype(np.float32)
+    rot = np.where(rng.random(nq) < 0.75, 12.0, rng.random(nq) * 360)
+    return dict(x=x, y=(frame["y"][pick] + rng.normal(0, 3.0, nq)).astype(np.float32), radius=radius,
+                min_level=lmin.astype(np.int32), max_level=lmax.astype(np.int32),
+                xr=None if mode == "kf" else (x - rng.random(nq).astype(np.float32) * 40).astype(np.float32),
+                angle=np.mod(kps["angle"][pick] + rot, 360).astype(np.float32), valid=(rng.random(nq) < 0.9).astype(np.uint8),
+                blocks=np.ones(nq, np.uint8) if mode == "kf" else (rng.random(nq) < 0.8).astype(np.uint8),
+                desc=np.ascontiguousarray(frame["desc"][pick] ^ np.packbits(flips, axis=1, bitorder="little")))
+
+
+@pytest.mark.parametrize("shape_name,seed,mode,check_ori,max_dist", [
+    ("kitti", 0, "forward", True, 100), ("kitti", 1, "backward", True, 100), ("tum", 2, "band", True, 100),
+    ("euroc", 3, "band", False, 100), ("tum", 4, "kf", True, 64), ("kitti", 5, "kf", False, 100),
+])
+def test_search_window_vs_oracle(gpu, oracle_mod, shape_name, seed, mode, check_ori, max_dist):
+    """the windowed search behind SearchByProjection(Cur, Last, th, bMono) and (Cur, KF, found, th, ORBdist)."""
+    img, cfg, oex, kps, desc = helpers.extract_with_oracle(oracle_mod, shape_name, seed)
+    rows, cols = synth.SHAPES[shape_name]
+    frame = helpers.make_frame_view(oracle_mod, kps, desc, rows, cols, oex.scale_factors(), seed=seed, stereo=(mode != "kf"),
+                                    occupied_p=0.15)
+    frame["angle"] = kps["angle"].astype(np.float32).copy()
+    q = _window_queries(frame, kps, 1500, seed, mode)
+    m = gpu.ORBmatcher(0.9, check_ori)
+    n_gpu, out_gpu = m.SearchWindow(frame, q, max_dist, 0)
+    n_ref, out_ref = oracle_mod.search_window(frame, q, max_dist, 0, 0.9, check_ori)
+    assert n_ref > 100
+    if check_ori:
+        assert (out_ref == -2).sum() > 0
+    assert n_gpu == n_ref and np.array_equal(out_gpu, out_ref)
+    m.close()
