@@ -271,6 +271,13 @@ void orbm_vocab_destroy(orbm_vocab* v);
 int orbm_bow_transform(orbm_context* m, const orbm_vocab* v, const uint8_t* desc, int n, int levelsup, int32_t* word_id,
                        int32_t* node_id, double* weight);
 
+/* Replaces the arithmetic of MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:295-360) for a batch of map
+ * points ("next" row): descriptor sets in CSR form (rows set_start[s] .. set_start[s+1] of desc);
+ * best_idx[s] = index inside set s of the descriptor with the least median Hamming distance to the set (first minimum;
+ * -1 for an empty set).  HOST pointers. */
+int orbm_distinctive_descriptors(orbm_context* m, int n_sets, const int32_t* set_start, const uint8_t* desc,
+                                 int32_t* best_idx);
+
 #ifdef __cplusplus
 }
 #endif

@@ -144,6 +144,7 @@ def _bind_all(L):
     L.orbo_search_window.restype = _i
     L.orbo_search_window.argtypes = ([_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _vp]
                                      + [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp] + [_i, _i, _f, _i, _vp])
+    L.orbo_distinctive_descriptors.argtypes = [_i, _vp, _vp, _vp]
     L.orbo_bow_transform.argtypes = [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]
     L.orbo_search_by_bow.restype = _i
     L.orbo_search_by_bow.argtypes = (
@@ -384,3 +385,12 @@ def search_window(frame, q, max_dist, ratio_mode, nnratio, check_orientation):
         _ptr(q.get("angle")), _ptr(q["valid"]), _ptr(q["blocks"]), _ptr(q["desc"]),
         int(max_dist), int(ratio_mode), float(nnratio), int(check_orientation), out.ctypes.data)
     return n, out[:nkp]
+
+
+def distinctive_descriptors(set_start, desc):
+    L = lib()
+    set_start = np.ascontiguousarray(set_start, np.int32)
+    desc = np.ascontiguousarray(desc, np.uint8)
+    out = np.zeros(max(len(set_start) - 1, 1), np.int32)
+    L.orbo_distinctive_descriptors(len(set_start) - 1, set_start.ctypes.data, desc.ctypes.data, out.ctypes.data)
+    return out[: len(set_start) - 1]

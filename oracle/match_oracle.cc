@@ -482,3 +482,30 @@ extern "C" int orbo_search_window(
     }
     return nmatches;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:295-360), batched over map points: for every set of
+// observation descriptors the index of the descriptor with the least median distance to the others
+// (median = sorted row element [0.5*(N-1)], first minimum wins).  Sets are CSR: rows set_start[s] .. set_start[s+1].
+// ---------------------------------------------------------------------------------------------------------------------
+extern "C" void orbo_distinctive_descriptors(int n_sets, const int32_t* set_start, const uint8_t* desc, int32_t* best_idx)
+{
+    for (int s = 0; s < n_sets; s++) {
+        const int b = set_start[s], N = set_start[s + 1] - b;
+        if (N <= 0) { best_idx[s] = -1; continue; }
+        std::vector<std::vector<float>> D(N, std::vector<float>(N, 0));
+        for (int i = 0; i < N; i++)
+            for (int j = i + 1; j < N; j++) {
+                const int d = hamming256(desc + 32 * (size_t)(b + i), desc + 32 * (size_t)(b + j));
+                D[i][j] = (float)d; D[j][i] = (float)d;
+            }
+        int bestMedian = INT32_MAX, bestIdx = 0;
+        for (int i = 0; i < N; i++) {
+            std::vector<int> v(D[i].begin(), D[i].end());
+            std::sort(v.begin(), v.end());
+            const int median = v[(size_t)(0.5 * (N - 1))];
+            if (median < bestMedian) { bestMedian = median; bestIdx = i; }
+        }
+        best_idx[s] = bestIdx;
+    }
+}

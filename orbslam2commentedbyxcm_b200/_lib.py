@@ -84,6 +84,7 @@ SIGNATURES = {
     "orbm_vocab_create": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, C.POINTER(_vp)]),
     "orbm_vocab_destroy": (None, [_vp]),
     "orbm_bow_transform": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp]),
+    "orbm_distinctive_descriptors": (_i, [_vp, _i, _vp, _vp, _vp]),
     "orbm_search_by_bow": (_i, [_vp, _i, _vp, _vp, _vp, C.POINTER(FeatVecView), _i, _vp, _vp, C.POINTER(FeatVecView), _f, _i, _vp, _vp]),
 }
 

@@ -578,6 +578,56 @@ __global__ void __launch_bounds__(256) k_bow_transform(int L, const int32_t* __r
 }
 
 // ------------------------------------------------------------------------------------------------------
+// K9: MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:295-360), batched: one warp per map point.  For each
+// observation descriptor i the median of its distances to the set is the value at sorted position (int)(0.5*(N-1));
+// distances are in [0, 256], so the order statistic comes from a 257-bin histogram in shared memory instead of a sort.
+// ------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_distinctive(int nSets, const int32_t* __restrict__ setStart,
+                                                     const uint8_t* __restrict__ desc, int32_t* __restrict__ bestIdx)
+{
+    __shared__ int hist[4][288];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int s = blockIdx.x * 4 + wid;
+    if (s >= nSets) return;
+    const int b = setStart[s], N = setStart[s + 1] - b;
+    if (N <= 0) { if (lane == 0) bestIdx[s] = -1; return; }
+    const int k = (int)(0.5 * (N - 1));
+    int* H = hist[wid];
+    int bestMedian = 0x7fffffff, best = 0;
+    for (int i = 0; i < N; i++) {
+#pragma unroll
+        for (int t = 0; t < 9; t++) H[lane * 9 + t] = 0;
+        __syncwarp();
+        const Desc D = load_desc(desc + 32 * (size_t)(b + i));
+        for (int j = lane; j < N; j += 32) atomicAdd(&H[hamming(D, load_desc(desc + 32 * (size_t)(b + j)))], 1);
+        __syncwarp();
+        int mine = 0;
+#pragma unroll
+        for (int t = 0; t < 9; t++) mine += H[lane * 9 + t];
+        int incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        // the lane whose bins contain sorted position k
+        const bool has = (incl - mine) <= k && k < incl;
+        int median = 0;
+        if (has) {
+            int cum = incl - mine;
+            for (int t = 0; t < 9; t++) {
+                cum += H[lane * 9 + t];
+                if (k < cum) { median = lane * 9 + t; break; }
+            }
+        }
+        median = __reduce_max_sync(0xffffffffu, has ? median : 0);
+        if (median < bestMedian) { bestMedian = median; best = i; }
+        __syncwarp();
+    }
+    if (lane == 0) bestIdx[s] = best;
+}
+
+// ------------------------------------------------------------------------------------------------------
 // K7d: SearchByBoW(KF, F).  A frame feature belongs to exactly one vocabulary node (DBoW2 FeatureVector invariant),
 // so the order-dependent "skip frame features already matched" only couples KF features of the same node: one warp
 // per shared node walks its KF features in order, lanes scan the node's frame features.
@@ -1159,6 +1209,30 @@ int orbm_bow_transform(orbm_context* m, const orbm_vocab* v, const uint8_t* desc
     ORBX_CUDA_TRY(cudaMemcpyAsync(word_id, A + oW, 4 * (size_t)n, cudaMemcpyDeviceToHost, m->stream));
     ORBX_CUDA_TRY(cudaMemcpyAsync(node_id, A + oN, 4 * (size_t)n, cudaMemcpyDeviceToHost, m->stream));
     ORBX_CUDA_TRY(cudaMemcpyAsync(weight, A + oWt, 8 * (size_t)n, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    return ORBX_OK;
+}
+
+int orbm_distinctive_descriptors(orbm_context* m, int n_sets, const int32_t* set_start, const uint8_t* desc, int32_t* best_idx)
+{
+    if (!m || n_sets < 0 || (n_sets > 0 && (!set_start || !best_idx))) {
+        set_error("orbm_distinctive_descriptors: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    if (n_sets == 0) return ORBX_OK;
+    const int total = set_start[n_sets];
+    if (total > 0 && !desc) { set_error("orbm_distinctive_descriptors: null descriptors"); return ORBX_ERR_BAD_ARG; }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    Carver c;
+    const size_t oS = c.take(4 * (size_t)(n_sets + 1)), oD = c.take(32 * (size_t)std::max(total, 1)), oB = c.take(4 * (size_t)n_sets);
+    int rc = ensure_arena(m, c.off);
+    if (rc != ORBX_OK) return rc;
+    char* A = m->arena;
+    if ((rc = up<int32_t>(m, (int32_t*)(A + oS), set_start, n_sets + 1)) != ORBX_OK) return rc;
+    if ((rc = up<uint8_t>(m, (uint8_t*)(A + oD), desc, 32 * (size_t)total)) != ORBX_OK) return rc;
+    k_distinctive<<<(n_sets + 3) / 4, 128, 0, m->stream>>>(n_sets, (int32_t*)(A + oS), (uint8_t*)(A + oD), (int32_t*)(A + oB));
+    ORBX_CUDA_TRY(cudaGetLastError());
+    ORBX_CUDA_TRY(cudaMemcpyAsync(best_idx, A + oB, 4 * (size_t)n_sets, cudaMemcpyDeviceToHost, m->stream));
     ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
     return ORBX_OK;
 }

@@ -210,6 +210,16 @@ class ORBmatcher:
             _p(arr(right["desc"], np.uint8)), float(mbf), float(mb), ur.ctypes.data, dp.ctypes.data, C.byref(nm)), "orbm_stereo_match")
         return ur[:nl], dp[:nl]
 
+    # ---- MapPoint::ComputeDistinctiveDescriptors, batched ----
+    def ComputeDistinctiveDescriptors(self, set_start, desc):
+        set_start = np.ascontiguousarray(set_start, np.int32)
+        desc = np.ascontiguousarray(desc, np.uint8)
+        n = len(set_start) - 1
+        out = np.zeros(max(n, 1), np.int32)
+        check(self._L.orbm_distinctive_descriptors(self._m, n, set_start.ctypes.data, desc.ctypes.data, out.ctypes.data),
+              "orbm_distinctive_descriptors")
+        return out[:n]
+
     # ---- SearchByBoW(KeyFrame*, Frame&, matches) ----
     def SearchByBoW(self, kf, fr):
         keep = []

@@ -295,3 +295,22 @@ def test_search_window_vs_oracle(gpu, oracle_mod, shape_name, seed, mode, check_
         assert (out_ref == -2).sum() > 0
     assert n_gpu == n_ref and np.array_equal(out_gpu, out_ref)
     m.close()
+
+
+def test_distinctive_descriptors_vs_oracle(gpu, oracle_mod):
+    """MapPoint::ComputeDistinctiveDescriptors batched: set sizes 0..70 incl. duplicates (median ties -> first index)."""
+    rng = np.random.default_rng(3)
+    sizes = np.concatenate([[0, 1, 2, 3, 33, 64, 70], rng.integers(1, 40, 500)])
+    start = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    base = synth.gen_descriptors(len(sizes), seed=8)
+    desc = np.zeros((start[-1], 32), np.uint8)
+    for s, n in enumerate(sizes):
+        flips = rng.random((n, 256)) < 0.1
+        desc[start[s]:start[s + 1]] = base[s] ^ np.packbits(flips, axis=1, bitorder="little")
+        if n > 4:
+            desc[start[s] + 3] = desc[start[s] + 1]
+    m = gpu.ORBmatcher()
+    got = m.ComputeDistinctiveDescriptors(start, desc)
+    ref = oracle_mod.distinctive_descriptors(start, desc)
+    assert np.array_equal(got, ref)
+    m.close()
