@@ -18,6 +18,7 @@
 #include <cstdarg>
 #include <vector>
 #include <algorithm>
+#include <mutex>
 
 namespace orbx {
 
@@ -1155,6 +1156,7 @@ struct orbx_handle {
     size_t fastSmem = 0;
     size_t octSmem = 0;
     int lastFrames = 0;
+    int plainRuns = 0;           // batches enqueued without a graph since the plan was (re)built
     bool profiling = false;
     bool useGraph = true;
     float stageMs[ORBX_NUM_STAGES] = {};
@@ -1291,9 +1293,17 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
     return ORBX_OK;
 }
 
+// Plan (re)builds and graph captures are rare; they are serialised across handles: allocation, function-attribute
+// changes and first-launch module loading in one host thread must not overlap a stream capture in another (two
+// extractor objects are driven from two std::threads in stereo, src/Frame.cc:127-131).  Steady-state graph launches
+// and copies of different handles run concurrently.
+static std::mutex g_setupMutex;
+
 static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
 {
     if (h->havePlan && h->plan.rows == rows && h->plan.cols == cols && frames <= h->frameCap) return ORBX_OK;
+    std::lock_guard<std::mutex> setupLock(g_setupMutex);
+    h->plainRuns = 0;
     ORBX_CUDA_TRY(cudaSetDevice(h->device));
     ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
     ORBX_CUDA_TRY(cudaStreamSynchronize(h->streamBlur));
@@ -1577,7 +1587,14 @@ int orbx_extract_batch_device(orbx_handle* h, const uint8_t* d_imgs, int n, int 
         return ORBX_OK;
     }
     orbx_handle::GraphKey k = {d_imgs, (long long)step, (long long)frame_stride, d_kps, d_desc, d_counts, n, capacity};
+    if (h->plainRuns == 0) {
+        // first batch on a fresh plan: plain launches (kernels get loaded outside any capture)
+        std::lock_guard<std::mutex> setupLock(g_setupMutex);
+        h->plainRuns = 1;
+        return enqueue(h, d_imgs, (long long)step, (long long)frame_stride, n, d_kps, d_desc, d_counts, capacity, false, &h->lastLaunches);
+    }
     if (!h->gexec || memcmp(&k, &h->gkey, sizeof k) != 0) {
+        std::lock_guard<std::mutex> setupLock(g_setupMutex);
         if (h->gexec) { cudaGraphExecDestroy(h->gexec); h->gexec = nullptr; }
         cudaGraph_t graph = nullptr;
         ORBX_CUDA_TRY(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
@@ -1634,6 +1651,7 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
     const size_t frameBytes = (size_t)rows * cols;
     const size_t inBytes = frameBytes * chunk * (piped ? 2 : 1);
     if (inBytes > h->dInBytes) {
+        std::lock_guard<std::mutex> setupLock(g_setupMutex);
         ORBX_CUDA_TRY(cudaDeviceSynchronize());
         cudaFree(h->dIn); h->dIn = nullptr; h->dInBytes = 0;
         ORBX_CUDA_TRY(cudaMalloc(&h->dIn, inBytes));
@@ -1644,6 +1662,7 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
     const size_t dsBytes = (size_t)n * devCap * 32;
     const size_t outBytes = cntBytes + kpBytes + dsBytes;
     if (outBytes > h->dOutBytes) {
+        std::lock_guard<std::mutex> setupLock(g_setupMutex);
         ORBX_CUDA_TRY(cudaDeviceSynchronize());
         cudaFree(h->dOut); h->dOut = nullptr; h->dOutBytes = 0;
         if (h->hOut) { cudaFreeHost(h->hOut); h->hOut = nullptr; }

@@ -189,3 +189,72 @@ def test_full_size_batch_properties(gpu):
             assert np.all(lx[m] >= 18.99) and np.all(lx[m] <= cols - 19.99)
             assert np.all(ly[m] >= 18.99) and np.all(ly[m] <= rows - 19.99)
     ex.close()
+
+
+def test_two_extractors_from_two_threads(gpu, oracle_mod):
+    """the reference calls two extractor objects concurrently from two std::threads in stereo (src/Frame.cc:127-131):
+    each handle owns its stream and buffers, results must not depend on the interleaving."""
+    import threading
+
+    left, right = synth.gen_stereo_pair(synth.SHAPES["euroc"], 5)
+    cfg = synth.PRESETS["euroc"]
+    exL, exR = gpu.ORBextractor(*cfg), gpu.ORBextractor(*cfg)
+    refL = oracle_mod.Extractor(*cfg).extract(left)
+    refR = oracle_mod.Extractor(*cfg).extract(right)
+    out = {}
+
+    def work(name, ex, img):
+        try:
+            res = None
+            for _ in range(25):
+                res = ex(img)
+            out[name] = res
+        except Exception as e:  # surfaced below with its message
+            out[name] = e
+
+    ts = [threading.Thread(target=work, args=("L", exL, left)), threading.Thread(target=work, args=("R", exR, right))]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not isinstance(out["L"], Exception), out["L"]
+    assert not isinstance(out["R"], Exception), out["R"]
+    assert out["L"][0].tobytes() == refL[0].tobytes() and np.array_equal(out["L"][1], refL[1])
+    assert out["R"][0].tobytes() == refR[0].tobytes() and np.array_equal(out["R"][1], refR[1])
+    exL.close(); exR.close()
+
+
+def test_pitched_host_input_and_shape_changes(gpu, oracle_mod):
+    """cv::Mat inputs may be ROIs (step > cols); one handle must also survive changing image shapes."""
+    import ctypes as C
+
+    from orbslam2commentedbyxcm_b200 import _lib
+
+    cfg = (500, 1.2, 8, 20, 7)
+    ex = gpu.ORBextractor(*cfg)
+    o = oracle_mod.Extractor(*cfg)
+    big = synth.gen_frame((300, 500), 11)
+    roi = big[20:260, 40:360]  # 240 x 320 view with step 500
+    L = _lib.load()
+    cap = ex.max_keypoints(240, 320)
+    kps = np.zeros(cap, gpu.KP_DTYPE)
+    desc = np.zeros((cap, 32), np.uint8)
+    n = C.c_int()
+    _lib.check(L.orbx_extract(ex._h, big.ctypes.data + 20 * 500 + 40, 240, 320, 500, kps.ctypes.data, desc.ctypes.data, cap,
+                              C.byref(n)), "orbx_extract")
+    ok, od = o.extract(np.ascontiguousarray(roi))
+    assert n.value == len(ok) and kps[: n.value].tobytes() == ok.tobytes() and np.array_equal(desc[: n.value], od)
+    for shape, seed in [((480, 640), 1), ((240, 320), 2), ((376, 1241), 3), ((240, 320), 4)]:
+        img = synth.gen_frame(shape, seed)
+        k, d = ex(img)
+        ok, od = o.extract(img)
+        assert k.tobytes() == ok.tobytes() and np.array_equal(d, od), shape
+    ex.close()
+
+
+def test_degenerate_configurations(gpu, oracle_mod):
+    img = synth.gen_frame((240, 320), 6)
+    for cfg in [(0, 1.2, 4, 20, 7), (1, 1.2, 1, 20, 7), (300, 1.2, 8, 255, 200), (300, 2.5, 2, 20, 7), (300, 1.05, 8, 20, 20)]:
+        ok, od = oracle_mod.Extractor(*cfg).extract(img)
+        ex = gpu.ORBextractor(*cfg)
+        k, d = ex(img)
+        assert k.tobytes() == ok.tobytes() and np.array_equal(d, od), cfg
+        ex.close()
