@@ -253,6 +253,14 @@ int orbm_search_by_bow(orbm_context* m, int nkf, const uint8_t* kf_desc, const f
                        const float* f_angle, const orbm_featvec_view* f_fv, float nnratio, int check_orientation,
                        int32_t* out_match, int* nmatches);
 
+/* Replaces ORBmatcher::SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12)
+ * (src/ORBmatcher.cc:696-850; loop closing).  has_mp1/2[i] = feature i of that key frame has a non-bad MapPoint.
+ * out_match12[i1] = matched feature index of KF2 or -1 (the caller stores vpMapPoints2[that index]).  HOST pointers. */
+int orbm_search_by_bow_kf(orbm_context* m, int n1, const uint8_t* desc1, const float* angle1, const uint8_t* has_mp1,
+                          const orbm_featvec_view* fv1, int n2, const uint8_t* desc2, const float* angle2,
+                          const uint8_t* has_mp2, const orbm_featvec_view* fv2, float nnratio, int check_orientation,
+                          int32_t* out_match12, int* nmatches);
+
 /* ---- DBoW2 vocabulary descent ("next" row) ------------------------------------ */
 
 /* A vocabulary tree on the device.  Flat form of TemplatedVocabulary::m_nodes (Thirdparty/DBoW2/DBoW2/

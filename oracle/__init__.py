@@ -145,6 +145,8 @@ def _bind_all(L):
     L.orbo_search_window.argtypes = ([_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _vp]
                                      + [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp] + [_i, _i, _f, _i, _vp])
     L.orbo_distinctive_descriptors.argtypes = [_i, _vp, _vp, _vp]
+    L.orbo_search_by_bow_kf.restype = _i
+    L.orbo_search_by_bow_kf.argtypes = [_i, _vp, _vp, _vp, _i, _vp, _vp, _vp] * 2 + [_f, _i, _vp]
     L.orbo_bow_transform.argtypes = [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]
     L.orbo_search_by_bow.restype = _i
     L.orbo_search_by_bow.argtypes = (
@@ -394,3 +396,15 @@ def distinctive_descriptors(set_start, desc):
     out = np.zeros(max(len(set_start) - 1, 1), np.int32)
     L.orbo_distinctive_descriptors(len(set_start) - 1, set_start.ctypes.data, desc.ctypes.data, out.ctypes.data)
     return out[: len(set_start) - 1]
+
+
+def search_by_bow_kf(kf1, kf2, nnratio, check_orientation):
+    L = lib()
+    n1 = len(kf1["angle"])
+    out = np.full(max(n1, 1), -1, np.int32)
+    args = []
+    for kf in (kf1, kf2):
+        args += [len(kf["angle"]), _ptr(kf["desc"]), _ptr(kf["angle"]), _ptr(kf["has_mp"]), len(kf["node_id"]), _ptr(kf["node_id"]),
+                 _ptr(kf["node_start"]), _ptr(kf["node_feat"])]
+    n = L.orbo_search_by_bow_kf(*args, nnratio, int(check_orientation), out.ctypes.data)
+    return n, out[:n1]

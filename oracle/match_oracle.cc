@@ -509,3 +509,74 @@ extern "C" void orbo_distinctive_descriptors(int n_sets, const int32_t* set_star
         best_idx[s] = bestIdx;
     }
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// ORBmatcher::SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12)  src/ORBmatcher.cc:696-850.
+// has_mp1/2[i] = feature i of that key frame has a non-bad MapPoint.  out12[i1] = matched feature of KF2 or -1.
+// Differences to the (KeyFrame, Frame) overload: both sides need map points, KF2 features are blocked through
+// vbMatched2, acceptance is bestDist1 < TH_LOW (strict), the rotation histogram stores idx1.
+// ---------------------------------------------------------------------------------------------------------------------
+extern "C" int orbo_search_by_bow_kf(
+    int n1, const uint8_t* desc1, const float* angle1, const uint8_t* has_mp1,
+    int n_nodes1, const int32_t* node_id1, const int32_t* node_start1, const int32_t* node_feat1,
+    int n2, const uint8_t* desc2, const float* angle2, const uint8_t* has_mp2,
+    int n_nodes2, const int32_t* node_id2, const int32_t* node_start2, const int32_t* node_feat2,
+    float nnratio, int checkOrientation, int32_t* out12)
+{
+    for (int i = 0; i < n1; i++) out12[i] = -1;
+    std::vector<uint8_t> matched2(n2 > 0 ? n2 : 1, 0);
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = HISTO_LENGTH / 360.0f;
+    int nmatches = 0, a = 0, b = 0;
+    while (a < n_nodes1 && b < n_nodes2) {
+        if (node_id1[a] == node_id2[b]) {
+            for (int i1 = node_start1[a]; i1 < node_start1[a + 1]; i1++) {
+                const int idx1 = node_feat1[i1];
+                if (!has_mp1[idx1]) continue;
+                int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+                for (int i2 = node_start2[b]; i2 < node_start2[b + 1]; i2++) {
+                    const int idx2 = node_feat2[i2];
+                    if (matched2[idx2] || !has_mp2[idx2]) continue;
+                    const int dist = hamming256(desc1 + 32 * (size_t)idx1, desc2 + 32 * (size_t)idx2);
+                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx2 = idx2; }
+                    else if (dist < bestDist2) bestDist2 = dist;
+                }
+                if (bestDist1 < TH_LOW) {
+                    if ((float)bestDist1 < nnratio * (float)bestDist2) {
+                        out12[idx1] = bestIdx2;
+                        matched2[bestIdx2] = 1;
+                        if (checkOrientation) {
+                            float rot = angle1[idx1] - angle2[bestIdx2];
+                            if (rot < 0.0) rot += 360.0f;
+                            int bin = (int)std::round(rot * factor);
+                            if (bin == HISTO_LENGTH) bin = 0;
+                            rotHist[bin].push_back(idx1);
+                        }
+                        nmatches++;
+                    }
+                }
+            }
+            a++; b++;
+        } else if (node_id1[a] < node_id2[b]) {
+            a = (int)(std::lower_bound(node_id1 + a, node_id1 + n_nodes1, node_id2[b]) - node_id1);
+        } else {
+            b = (int)(std::lower_bound(node_id2 + b, node_id2 + n_nodes2, node_id1[a]) - node_id2);
+        }
+    }
+    if (checkOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1, max1 = 0, max2 = 0, max3 = 0;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            const int s = (int)rotHist[i].size();
+            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+            else if (s > max3) { max3 = s; ind3 = i; }
+        }
+        if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+        else if (max3 < 0.1f * (float)max1) ind3 = -1;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int f : rotHist[i]) { out12[f] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}

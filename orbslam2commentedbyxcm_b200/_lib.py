@@ -81,6 +81,7 @@ SIGNATURES = {
     "orbm_search_window": (_i, [_vp, C.POINTER(FrameView), _vp, C.POINTER(WindowQueryView), _i, _i, _f, _i, _vp, _vp]),
     "orbm_stereo_rows": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _f, _f, _vp, _vp]),
     "orbm_stereo_match": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp]),
+    "orbm_search_by_bow_kf": (_i, [_vp, _i, _vp, _vp, _vp, C.POINTER(FeatVecView), _i, _vp, _vp, _vp, C.POINTER(FeatVecView), _f, _i, _vp, _vp]),
     "orbm_vocab_create": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, C.POINTER(_vp)]),
     "orbm_vocab_destroy": (None, [_vp]),
     "orbm_bow_transform": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp]),

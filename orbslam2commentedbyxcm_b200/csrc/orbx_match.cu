@@ -639,6 +639,7 @@ __global__ void __launch_bounds__(128) k_bow_nodes(const uint8_t* __restrict__ k
                                                    const float* __restrict__ fAngle, int nNodesF,
                                                    const int32_t* __restrict__ fNodeId, const int32_t* __restrict__ fNodeStart,
                                                    const int32_t* __restrict__ fNodeFeat, float nnratio,
+                                                   const uint8_t* __restrict__ fHasMp, int strictLow,
                                                    int32_t* outMatch, int32_t* binOf)
 {
     const int lane = threadIdx.x & 31;
@@ -660,6 +661,7 @@ __global__ void __launch_bounds__(128) k_bow_nodes(const uint8_t* __restrict__ k
         for (int jf = fs + lane; jf < fe; jf += 32) {
             const int realIdxF = fNodeFeat[jf];
             if (outMatch[realIdxF] >= 0) continue;
+            if (fHasMp && !fHasMp[realIdxF]) continue;
             const int dist = hamming(D, load_desc(fDesc + 32 * (size_t)realIdxF));
             top2_push(t, ((uint32_t)dist << 20) | (uint32_t)(jf - fs), realIdxF);
         }
@@ -667,7 +669,7 @@ __global__ void __launch_bounds__(128) k_bow_nodes(const uint8_t* __restrict__ k
         if (t.p1 >= 0) {
             const int bestDist1 = t.k1 >> 20;
             const int bestDist2 = t.p2 >= 0 ? (int)(t.k2 >> 20) : 256;
-            if (bestDist1 <= TH_LOW && (float)bestDist1 < __fmul_rn(nnratio, (float)bestDist2)) {
+            if ((strictLow ? bestDist1 < TH_LOW : bestDist1 <= TH_LOW) && (float)bestDist1 < __fmul_rn(nnratio, (float)bestDist2)) {
                 if (lane == 0) {
                     outMatch[t.p1] = realIdxKF;
                     float rot = __fsub_rn(kfAngle[realIdxKF], fAngle[t.p1]);
@@ -720,6 +722,13 @@ __global__ void __launch_bounds__(256) k_bow_rotation(int nf, int32_t* outMatch,
     __syncthreads();
     for (int f = threadIdx.x; f < nf; f += blockDim.x)
         if (outMatch[f] >= 0 && !keepBin[binOf[f]]) outMatch[f] = -1;
+}
+
+// (KeyFrame, KeyFrame) overload: turn "feature of KF2 -> feature of KF1" into vpMatches12 (feature of KF1 -> feature of KF2)
+__global__ void k_bow_scatter12(int n2, const int32_t* __restrict__ match21, int32_t* __restrict__ out12)
+{
+    const int i2 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i2 < n2 && match21[i2] >= 0) out12[match21[i2]] = i2;
 }
 
 }  // namespace orbx
@@ -1067,7 +1076,7 @@ int orbm_search_by_bow(orbm_context* m, int nkf, const uint8_t* kf_desc, const f
     k_bow_nodes<<<(nnk + 3) / 4, 128, 0, m->stream>>>((uint8_t*)(A + oKd), (float*)(A + oKa), (uint8_t*)(A + oKm), nnk,
                                                      (int32_t*)(A + oKi), (int32_t*)(A + oKs), (int32_t*)(A + oKf),
                                                      (uint8_t*)(A + oFd), (float*)(A + oFa), nnf, (int32_t*)(A + oFi),
-                                                     (int32_t*)(A + oFs), (int32_t*)(A + oFf), nnratio,
+                                                     (int32_t*)(A + oFs), (int32_t*)(A + oFf), nnratio, nullptr, 0,
                                                      (int32_t*)(A + oOut), (int32_t*)(A + oBin));
     k_bow_rotation<<<1, 256, 0, m->stream>>>(nf, (int32_t*)(A + oOut), (int32_t*)(A + oBin), check_orientation, (int*)(A + oN));
     ORBX_CUDA_TRY(cudaGetLastError());
@@ -1233,6 +1242,53 @@ int orbm_distinctive_descriptors(orbm_context* m, int n_sets, const int32_t* set
     k_distinctive<<<(n_sets + 3) / 4, 128, 0, m->stream>>>(n_sets, (int32_t*)(A + oS), (uint8_t*)(A + oD), (int32_t*)(A + oB));
     ORBX_CUDA_TRY(cudaGetLastError());
     ORBX_CUDA_TRY(cudaMemcpyAsync(best_idx, A + oB, 4 * (size_t)n_sets, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    return ORBX_OK;
+}
+
+int orbm_search_by_bow_kf(orbm_context* m, int n1, const uint8_t* desc1, const float* angle1, const uint8_t* has_mp1,
+                          const orbm_featvec_view* fv1, int n2, const uint8_t* desc2, const float* angle2,
+                          const uint8_t* has_mp2, const orbm_featvec_view* fv2, float nnratio, int check_orientation,
+                          int32_t* out_match12, int* nmatches)
+{
+    if (!m || !fv1 || !fv2 || !out_match12 || !nmatches || n1 < 0 || n2 < 0) {
+        set_error("orbm_search_by_bow_kf: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    for (int i = 0; i < n1; i++) out_match12[i] = -1;
+    *nmatches = 0;
+    if (n1 == 0 || n2 == 0 || fv1->n_nodes == 0 || fv2->n_nodes == 0) return ORBX_OK;
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    const int nn1 = fv1->n_nodes, nn2 = fv2->n_nodes;
+    const int nf1 = fv1->node_start[nn1], nf2 = fv2->node_start[nn2];
+    Carver c;
+    const size_t o1d = c.take(32 * (size_t)n1), o1a = c.take(4 * (size_t)n1), o1m = c.take(n1), o1i = c.take(4 * (size_t)nn1),
+                 o1s = c.take(4 * (size_t)(nn1 + 1)), o1f = c.take(4 * (size_t)std::max(nf1, 1));
+    const size_t o2d = c.take(32 * (size_t)n2), o2a = c.take(4 * (size_t)n2), o2m = c.take(n2), o2i = c.take(4 * (size_t)nn2),
+                 o2s = c.take(4 * (size_t)(nn2 + 1)), o2f = c.take(4 * (size_t)std::max(nf2, 1));
+    const size_t o21 = c.take(4 * (size_t)n2), oBin = c.take(4 * (size_t)n2), o12 = c.take(4 * (size_t)n1), oN = c.take(64);
+    int rc = ensure_arena(m, c.off);
+    if (rc != ORBX_OK) return rc;
+    char* A = m->arena;
+#define UP(off, ptr, count, T) if ((rc = up<T>(m, (T*)(A + off), ptr, count)) != ORBX_OK) return rc
+    UP(o1d, desc1, 32 * (size_t)n1, uint8_t); UP(o1a, angle1, n1, float); UP(o1m, has_mp1, n1, uint8_t);
+    UP(o1i, fv1->node_id, nn1, int32_t); UP(o1s, fv1->node_start, nn1 + 1, int32_t); UP(o1f, fv1->node_feat, nf1, int32_t);
+    UP(o2d, desc2, 32 * (size_t)n2, uint8_t); UP(o2a, angle2, n2, float); UP(o2m, has_mp2, n2, uint8_t);
+    UP(o2i, fv2->node_id, nn2, int32_t); UP(o2s, fv2->node_start, nn2 + 1, int32_t); UP(o2f, fv2->node_feat, nf2, int32_t);
+#undef UP
+    ORBX_CUDA_TRY(cudaMemsetAsync(A + o21, 0xff, 4 * (size_t)n2, m->stream));
+    ORBX_CUDA_TRY(cudaMemsetAsync(A + oBin, 0, 4 * (size_t)n2, m->stream));
+    ORBX_CUDA_TRY(cudaMemsetAsync(A + o12, 0xff, 4 * (size_t)n1, m->stream));
+    k_bow_nodes<<<(nn1 + 3) / 4, 128, 0, m->stream>>>((uint8_t*)(A + o1d), (float*)(A + o1a), (uint8_t*)(A + o1m), nn1,
+                                                     (int32_t*)(A + o1i), (int32_t*)(A + o1s), (int32_t*)(A + o1f),
+                                                     (uint8_t*)(A + o2d), (float*)(A + o2a), nn2, (int32_t*)(A + o2i),
+                                                     (int32_t*)(A + o2s), (int32_t*)(A + o2f), nnratio, (uint8_t*)(A + o2m), 1,
+                                                     (int32_t*)(A + o21), (int32_t*)(A + oBin));
+    k_bow_rotation<<<1, 256, 0, m->stream>>>(n2, (int32_t*)(A + o21), (int32_t*)(A + oBin), check_orientation, (int*)(A + oN));
+    k_bow_scatter12<<<(n2 + 255) / 256, 256, 0, m->stream>>>(n2, (int32_t*)(A + o21), (int32_t*)(A + o12));
+    ORBX_CUDA_TRY(cudaGetLastError());
+    ORBX_CUDA_TRY(cudaMemcpyAsync(out_match12, A + o12, 4 * (size_t)n1, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(nmatches, A + oN, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
     ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
     return ORBX_OK;
 }

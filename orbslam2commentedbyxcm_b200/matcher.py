@@ -210,6 +210,32 @@ class ORBmatcher:
             _p(arr(right["desc"], np.uint8)), float(mbf), float(mb), ur.ctypes.data, dp.ctypes.data, C.byref(nm)), "orbm_stereo_match")
         return ur[:nl], dp[:nl]
 
+    # ---- SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12) ----
+    def SearchByBoWKF(self, kf1, kf2):
+        keep = []
+
+        def arr(v, dt):
+            a = np.ascontiguousarray(v, dt)
+            keep.append(a)
+            return a
+
+        def fvview(d):
+            v = _lib.FeatVecView()
+            v.n_nodes = len(d["node_id"])
+            v.node_id = _p(arr(d["node_id"], np.int32)); v.node_start = _p(arr(d["node_start"], np.int32))
+            v.node_feat = _p(arr(d["node_feat"], np.int32))
+            return v
+
+        n1, n2 = len(kf1["angle"]), len(kf2["angle"])
+        v1, v2 = fvview(kf1), fvview(kf2)
+        out = np.full(max(n1, 1), -1, np.int32)
+        nm = C.c_int()
+        check(self._L.orbm_search_by_bow_kf(
+            self._m, n1, _p(arr(kf1["desc"], np.uint8)), _p(arr(kf1["angle"], np.float32)), _p(arr(kf1["has_mp"], np.uint8)), C.byref(v1),
+            n2, _p(arr(kf2["desc"], np.uint8)), _p(arr(kf2["angle"], np.float32)), _p(arr(kf2["has_mp"], np.uint8)), C.byref(v2),
+            self.mfNNratio, int(self.mbCheckOrientation), out.ctypes.data, C.byref(nm)), "orbm_search_by_bow_kf")
+        return nm.value, out[:n1]
+
     # ---- MapPoint::ComputeDistinctiveDescriptors, batched ----
     def ComputeDistinctiveDescriptors(self, set_start, desc):
         set_start = np.ascontiguousarray(set_start, np.int32)

@@ -314,3 +314,33 @@ def test_distinctive_descriptors_vs_oracle(gpu, oracle_mod):
     ref = oracle_mod.distinctive_descriptors(start, desc)
     assert np.array_equal(got, ref)
     m.close()
+
+
+@pytest.mark.parametrize("seed,check_ori", [(0, True), (1, False), (2, True)])
+def test_search_by_bow_kf_kf_vs_oracle(gpu, oracle_mod, seed, check_ori):
+    """SearchByBoW(KeyFrame, KeyFrame): both sides need map points, strict < TH_LOW, output indexed by KF1 feature."""
+    img, cfg, oex, kps, desc = helpers.extract_with_oracle(oracle_mod, "tum", seed + 10)
+    rng = np.random.default_rng(seed)
+    n = len(kps)
+    perm = rng.permutation(n)
+    flips = rng.random((n, 256)) < 0.06
+    d1 = np.ascontiguousarray(desc[perm] ^ np.packbits(flips, axis=1, bitorder="little"))
+    rot = np.where(rng.random(n) < 0.8, 40.0, rng.random(n) * 360).astype(np.float32)
+    a1 = np.mod(kps["angle"][perm] + rot, 360).astype(np.float32)
+    fv2, node_of = helpers.make_featvec(n, 300, seed)
+    node1 = np.where(rng.random(n) < 0.9, node_of[perm], rng.integers(0, 300, n))
+    ids = np.unique(node1)
+    start, feat = [0], []
+    for nid in ids:
+        f = np.nonzero(node1 == nid)[0]
+        feat.extend(f.tolist())
+        start.append(len(feat))
+    kf1 = dict(desc=d1, angle=a1, has_mp=(rng.random(n) < 0.8).astype(np.uint8), node_id=ids.astype(np.int32),
+               node_start=np.array(start, np.int32), node_feat=np.array(feat, np.int32))
+    kf2 = dict(desc=np.ascontiguousarray(desc), angle=kps["angle"].astype(np.float32).copy(), has_mp=(rng.random(n) < 0.85).astype(np.uint8), **fv2)
+    m = gpu.ORBmatcher(0.8, check_ori)
+    n_gpu, out_gpu = m.SearchByBoWKF(kf1, kf2)
+    n_ref, out_ref = oracle_mod.search_by_bow_kf(kf1, kf2, 0.8, check_ori)
+    assert n_ref > 50
+    assert n_gpu == n_ref and np.array_equal(out_gpu, out_ref)
+    m.close()
