@@ -361,7 +361,7 @@ def run_ours(args):
 
     # ---- end to end through the host C-ABI (pinned host input) ----
     h_imgs = torch.from_numpy(frames).pin_memory()
-    out = ex.alloc_outputs(B, rows, cols)
+    out = ex.alloc_outputs(B, rows, cols, pinned=True)
     e2e_steps = max(2, min(args.steps, 10))
     for _ in range(2):
         ex.extract_batch(h_imgs.numpy(), out=out)

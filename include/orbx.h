@@ -84,6 +84,12 @@ int orbx_max_keypoints(orbx_handle* h, int rows, int cols);
 int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int cols, size_t step,
                        size_t frame_stride, orbx_keypoint* kps, uint8_t* desc, int capacity, int* counts);
 
+/* Page-locked host memory for images and results.  When kps / desc / counts of orbx_extract_batch live in such memory
+ * and capacity == orbx_max_keypoints(), results are DMA'd straight into them (no staging copy on the host); note that
+ * then all `capacity` entries of a frame are transferred and only the first counts[i] are meaningful. */
+void* orbx_alloc_pinned(size_t bytes);
+void orbx_free_pinned(void* p);
+
 /* Single frame convenience (n = 1). */
 int orbx_extract(orbx_handle* h, const uint8_t* img, int rows, int cols, size_t step, orbx_keypoint* kps,
                  uint8_t* desc, int capacity, int* count);

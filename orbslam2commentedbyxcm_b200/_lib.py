@@ -58,6 +58,8 @@ SIGNATURES = {
     "orbx_get_tables": (_i, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "orbx_max_keypoints": (_i, [_vp, _i, _i]),
     "orbx_extract_batch": (_i, [_vp, _vp, _i, _i, _i, _sz, _sz, _vp, _vp, _i, _vp]),
+    "orbx_alloc_pinned": (_vp, [_sz]),
+    "orbx_free_pinned": (None, [_vp]),
     "orbx_extract": (_i, [_vp, _vp, _i, _i, _sz, _vp, _vp, _i, _vp]),
     "orbx_extract_batch_device": (_i, [_vp, _vp, _i, _i, _i, _sz, _sz, _vp, _vp, _i, _vp]),
     "orbx_sync": (_i, [_vp]),

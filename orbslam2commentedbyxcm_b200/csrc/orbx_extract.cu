@@ -16,6 +16,7 @@
 #include <cmath>
 #include <cfloat>
 #include <cstdarg>
+#include <cstdlib>
 #include <vector>
 #include <algorithm>
 #include <mutex>
@@ -1163,9 +1164,9 @@ struct orbx_handle {
     int lastLaunches = 0;
     // graph cache for the device-resident path: key = (n, in ptr, steps, out ptrs)
     struct GraphKey { const void* in; long long step, fstride; void* kps; void* desc; void* counts; int n, cap; };
-    GraphKey gkey = {};
-    cudaGraphExec_t gexec = nullptr;
-    int glaunches = 0;
+    struct GraphEntry { GraphKey key; cudaGraphExec_t exec; int launches; unsigned long long stamp; };
+    std::vector<GraphEntry> graphs;   // small LRU cache (the pipelined host path uses one graph per chunk slot)
+    unsigned long long graphStamp = 0;
 };
 
 static void free_arenas(orbx_handle* h)
@@ -1175,7 +1176,8 @@ static void free_arenas(orbx_handle* h)
     cudaFree(h->dTabs); cudaFree(h->dKeyNode); cudaFree(h->dFastUnits);
     h->buf = Buffers{};
     h->dTabs = nullptr; h->dKeyNode = nullptr; h->dFastUnits = nullptr;
-    if (h->gexec) { cudaGraphExecDestroy(h->gexec); h->gexec = nullptr; }
+    for (auto& g : h->graphs) cudaGraphExecDestroy(g.exec);
+    h->graphs.clear();
     h->havePlan = false;
     h->frameCap = 0;
 }
@@ -1429,6 +1431,54 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
     return ORBX_OK;
 }
 
+// Launch the kernel sequence of one batch through a cached CUDA graph (captured on first use of a
+// (pointers, batch) combination; the first batch on a fresh plan runs with plain launches so that kernels are loaded
+// outside any capture).
+static const size_t GRAPH_CACHE = 24;
+
+static int launch_cached(orbx_handle* h, const uint8_t* dIn, long long inStep, long long inFrameStride, int n, orbx_keypoint* dKps,
+                         uint8_t* dDesc, int* dCounts, int capacity, int* launches)
+{
+    if (h->plainRuns == 0 || !h->useGraph) {
+        std::lock_guard<std::mutex> setupLock(g_setupMutex);
+        h->plainRuns = 1;
+        return enqueue(h, dIn, inStep, inFrameStride, n, dKps, dDesc, dCounts, capacity, false, launches);
+    }
+    orbx_handle::GraphKey k;
+    memset(&k, 0, sizeof k);
+    k.in = dIn; k.step = inStep; k.fstride = inFrameStride; k.kps = dKps; k.desc = dDesc; k.counts = dCounts; k.n = n; k.cap = capacity;
+    orbx_handle::GraphEntry* hit = nullptr;
+    for (auto& g : h->graphs)
+        if (memcmp(&g.key, &k, sizeof k) == 0) { hit = &g; break; }
+    if (!hit) {
+        std::lock_guard<std::mutex> setupLock(g_setupMutex);
+        if (h->graphs.size() >= GRAPH_CACHE) {
+            size_t victim = 0;
+            for (size_t i = 1; i < h->graphs.size(); i++)
+                if (h->graphs[i].stamp < h->graphs[victim].stamp) victim = i;
+            cudaGraphExecDestroy(h->graphs[victim].exec);
+            h->graphs.erase(h->graphs.begin() + victim);
+        }
+        cudaGraph_t graph = nullptr;
+        int nl = 0;
+        ORBX_CUDA_TRY(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+        const int rc = enqueue(h, dIn, inStep, inFrameStride, n, dKps, dDesc, dCounts, capacity, false, &nl);
+        cudaError_t e = cudaStreamEndCapture(h->stream, &graph);
+        if (rc != ORBX_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+        if (e != cudaSuccess) { set_error("cudaStreamEndCapture: %s", cudaGetErrorString(e)); return ORBX_ERR_CUDA; }
+        cudaGraphExec_t exec = nullptr;
+        e = cudaGraphInstantiate(&exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (e != cudaSuccess) { set_error("cudaGraphInstantiate: %s", cudaGetErrorString(e)); return ORBX_ERR_CUDA; }
+        h->graphs.push_back(orbx_handle::GraphEntry{k, exec, nl, 0});
+        hit = &h->graphs.back();
+    }
+    hit->stamp = ++h->graphStamp;
+    ORBX_CUDA_TRY(cudaGraphLaunch(hit->exec, h->stream));
+    if (launches) *launches = hit->launches;
+    return ORBX_OK;
+}
+
 namespace orbx {
 int pyramid_view(orbx_handle* h, int frame, PyramidView* out)
 {
@@ -1576,7 +1626,7 @@ int orbx_extract_batch_device(orbx_handle* h, const uint8_t* d_imgs, int n, int 
     int rc = ensure_plan(h, rows, cols, n);
     if (rc != ORBX_OK) return rc;
     h->lastFrames = n;
-    if (h->profiling || !h->useGraph) {
+    if (h->profiling) {
         rc = enqueue(h, d_imgs, (long long)step, (long long)frame_stride, n, d_kps, d_desc, d_counts, capacity, h->profiling, &h->lastLaunches);
         if (rc != ORBX_OK) return rc;
         if (h->profiling) {
@@ -1586,36 +1636,13 @@ int orbx_extract_batch_device(orbx_handle* h, const uint8_t* d_imgs, int n, int 
         }
         return ORBX_OK;
     }
-    orbx_handle::GraphKey k = {d_imgs, (long long)step, (long long)frame_stride, d_kps, d_desc, d_counts, n, capacity};
-    if (h->plainRuns == 0) {
-        // first batch on a fresh plan: plain launches (kernels get loaded outside any capture)
-        std::lock_guard<std::mutex> setupLock(g_setupMutex);
-        h->plainRuns = 1;
-        return enqueue(h, d_imgs, (long long)step, (long long)frame_stride, n, d_kps, d_desc, d_counts, capacity, false, &h->lastLaunches);
-    }
-    if (!h->gexec || memcmp(&k, &h->gkey, sizeof k) != 0) {
-        std::lock_guard<std::mutex> setupLock(g_setupMutex);
-        if (h->gexec) { cudaGraphExecDestroy(h->gexec); h->gexec = nullptr; }
-        cudaGraph_t graph = nullptr;
-        ORBX_CUDA_TRY(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
-        rc = enqueue(h, d_imgs, (long long)step, (long long)frame_stride, n, d_kps, d_desc, d_counts, capacity, false, &h->glaunches);
-        cudaError_t e = cudaStreamEndCapture(h->stream, &graph);
-        if (rc != ORBX_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
-        if (e != cudaSuccess) { set_error("cudaStreamEndCapture: %s", cudaGetErrorString(e)); return ORBX_ERR_CUDA; }
-        e = cudaGraphInstantiate(&h->gexec, graph, 0);
-        cudaGraphDestroy(graph);
-        if (e != cudaSuccess) { set_error("cudaGraphInstantiate: %s", cudaGetErrorString(e)); h->gexec = nullptr; return ORBX_ERR_CUDA; }
-        h->gkey = k;
-    }
-    ORBX_CUDA_TRY(cudaGraphLaunch(h->gexec, h->stream));
-    h->lastLaunches = h->glaunches;
-    return ORBX_OK;
+    return launch_cached(h, d_imgs, (long long)step, (long long)frame_stride, n, d_kps, d_desc, d_counts, capacity, &h->lastLaunches);
 }
 
 // Host entry point.  Small batches: one H2D, one graph launch, one D2H.  Large batches are cut into chunks of
 // PIPE_CHUNK frames and software-pipelined over three streams (H2D of chunk k+1 | kernels of chunk k | D2H + copy-out of
 // chunk k-1), so that PCIe transfers, which dominate the end-to-end time, overlap the kernels.
-static const int PIPE_CHUNK = 32;
+static const int PIPE_CHUNK = [] { const char* e = std::getenv("ORBX_PIPE_CHUNK"); const int v = e ? std::atoi(e) : 0; return v > 0 ? v : 32; }();
 
 static int copy_in(orbx_handle* h, uint8_t* dDst, const uint8_t* imgs, int n, int rows, int cols, size_t step, size_t frame_stride,
                    cudaStream_t st)
@@ -1686,20 +1713,37 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
         }
     };
     *h->hErrFlag = 0;
+    // caller buffers in page-locked memory with the device layout (capacity == orbx_max_keypoints): results are DMA'd
+    // straight into them, no staging copy on the host
+    auto is_pinned = [](const void* p) {
+        cudaPointerAttributes a;
+        if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+        return a.type == cudaMemoryTypeHost;
+    };
+    const bool direct = capacity == devCap && is_pinned(kps) && is_pinned(desc) && is_pinned(counts);
+    char* hCnt = direct ? (char*)counts : (char*)h->hOut;
+    char* hKps = direct ? (char*)kps : (char*)h->hOut + cntBytes;
+    char* hDesc = direct ? (char*)desc : (char*)h->hOut + cntBytes + kpBytes;
 
     if (!piped) {
         if (h->profiling) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_H2D], h->stream));
         if ((rc = copy_in(h, h->dIn, imgs, n, rows, cols, step, frame_stride, h->stream)) != ORBX_OK) return rc;
         rc = orbx_extract_batch_device(h, h->dIn, n, rows, cols, (size_t)cols, frameBytes, dKps, dDesc, devCap, dCounts);
         if (rc != ORBX_OK) return rc;
-        ORBX_CUDA_TRY(cudaMemcpyAsync(h->hOut, h->dOut, outBytes, cudaMemcpyDeviceToHost, h->stream));
+        if (direct) {
+            ORBX_CUDA_TRY(cudaMemcpyAsync(hCnt, dCounts, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, h->stream));
+            ORBX_CUDA_TRY(cudaMemcpyAsync(hKps, dKps, sizeof(orbx_keypoint) * (size_t)n * devCap, cudaMemcpyDeviceToHost, h->stream));
+            ORBX_CUDA_TRY(cudaMemcpyAsync(hDesc, dDesc, (size_t)32 * n * devCap, cudaMemcpyDeviceToHost, h->stream));
+        } else {
+            ORBX_CUDA_TRY(cudaMemcpyAsync(h->hOut, h->dOut, outBytes, cudaMemcpyDeviceToHost, h->stream));
+        }
         if (h->profiling) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_NUM_STAGES], h->stream));
         ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
         if (h->profiling) {
             ORBX_CUDA_TRY(cudaEventElapsedTime(&h->stageMs[ORBX_STAGE_H2D], h->evStage[ORBX_STAGE_H2D], h->evStage[ORBX_STAGE_PYRAMID]));
             ORBX_CUDA_TRY(cudaEventElapsedTime(&h->stageMs[ORBX_STAGE_D2H], h->evStage[ORBX_STAGE_D2H], h->evStage[ORBX_NUM_STAGES]));
         }
-        copy_out(0, n);
+        if (!direct) copy_out(0, n);
     } else {
         const int nchunks = (n + chunk - 1) / chunk;
         while ((int)h->evChunkDone.size() < nchunks) {
@@ -1717,23 +1761,27 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
             ORBX_CUDA_TRY(cudaEventRecord(h->evInReady[b], h->streamH2D));
             ORBX_CUDA_TRY(cudaStreamWaitEvent(h->stream, h->evInReady[b], 0));
             int nl = 0;
-            rc = enqueue(h, dInB, (long long)cols, (long long)frameBytes, nk, dKps + (size_t)f0 * devCap, dDesc + (size_t)f0 * devCap * 32,
-                         dCounts + f0, devCap, false, &nl);
+            rc = launch_cached(h, dInB, (long long)cols, (long long)frameBytes, nk, dKps + (size_t)f0 * devCap,
+                               dDesc + (size_t)f0 * devCap * 32, dCounts + f0, devCap, &nl);
             if (rc != ORBX_OK) return rc;
             launches += nl;
             ORBX_CUDA_TRY(cudaEventRecord(h->evInFree[b], h->stream));
             ORBX_CUDA_TRY(cudaStreamWaitEvent(h->streamD2H, h->evInFree[b], 0));
-            ORBX_CUDA_TRY(cudaMemcpyAsync((char*)h->hOut + (size_t)f0 * sizeof(int), dCounts + f0, sizeof(int) * nk, cudaMemcpyDeviceToHost, h->streamD2H));
-            ORBX_CUDA_TRY(cudaMemcpyAsync((char*)h->hOut + cntBytes + (size_t)f0 * devCap * sizeof(orbx_keypoint), dKps + (size_t)f0 * devCap,
+            ORBX_CUDA_TRY(cudaMemcpyAsync(hCnt + (size_t)f0 * sizeof(int), dCounts + f0, sizeof(int) * nk, cudaMemcpyDeviceToHost, h->streamD2H));
+            ORBX_CUDA_TRY(cudaMemcpyAsync(hKps + (size_t)f0 * devCap * sizeof(orbx_keypoint), dKps + (size_t)f0 * devCap,
                                           sizeof(orbx_keypoint) * (size_t)nk * devCap, cudaMemcpyDeviceToHost, h->streamD2H));
-            ORBX_CUDA_TRY(cudaMemcpyAsync((char*)h->hOut + cntBytes + kpBytes + (size_t)f0 * devCap * 32, dDesc + (size_t)f0 * devCap * 32,
+            ORBX_CUDA_TRY(cudaMemcpyAsync(hDesc + (size_t)f0 * devCap * 32, dDesc + (size_t)f0 * devCap * 32,
                                           (size_t)32 * nk * devCap, cudaMemcpyDeviceToHost, h->streamD2H));
             ORBX_CUDA_TRY(cudaEventRecord(h->evChunkDone[k], h->streamD2H));
         }
         h->lastLaunches = launches;
-        for (int k = 0; k < nchunks; k++) {
-            ORBX_CUDA_TRY(cudaEventSynchronize(h->evChunkDone[k]));
-            copy_out(k * chunk, std::min(n, (k + 1) * chunk));
+        if (direct) {
+            ORBX_CUDA_TRY(cudaStreamSynchronize(h->streamD2H));
+        } else {
+            for (int k = 0; k < nchunks; k++) {
+                ORBX_CUDA_TRY(cudaEventSynchronize(h->evChunkDone[k]));
+                copy_out(k * chunk, std::min(n, (k + 1) * chunk));
+            }
         }
         ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
     }
@@ -1769,6 +1817,14 @@ int orbx_get_pyramid_level(orbx_handle* h, int frame, int level, uint8_t* dst, s
     ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
     return ORBX_OK;
 }
+
+void* orbx_alloc_pinned(size_t bytes)
+{
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { set_error("cudaMallocHost(%zu) failed", bytes); cudaGetLastError(); return nullptr; }
+    return p;
+}
+void orbx_free_pinned(void* p) { if (p) cudaFreeHost(p); }
 
 int orbx_set_profiling(orbx_handle* h, int on)
 {

@@ -33,11 +33,15 @@ class ORBextractor:
         check(self._L.orbx_get_tables(h, self._scale.ctypes.data, self._inv_scale.ctypes.data, self._sigma2.ctypes.data,
                                       self._inv_sigma2.ctypes.data, self._quota.ctypes.data), "orbx_get_tables")
         self._last_n = 0
+        self._pinned = []
 
     def close(self):
         if getattr(self, "_h", None):
             self._L.orbx_destroy(self._h)
             self._h = None
+            for p in self._pinned:
+                self._L.orbx_free_pinned(p)
+            self._pinned = []
 
     def __del__(self):
         try:
@@ -84,9 +88,24 @@ class ORBextractor:
         k, d, c = self.extract_batch(image[None])
         return k[0, : c[0]].copy(), d[0, : c[0]].copy()
 
-    def alloc_outputs(self, n, rows, cols):
+    def alloc_outputs(self, n, rows, cols, pinned=False):
+        """Output arrays for extract_batch.  pinned=True puts them in page-locked memory (orbx_alloc_pinned) so that results
+        are DMA'd straight into them; the arrays stay valid until this extractor object is closed."""
         cap = self.max_keypoints(rows, cols)
-        return np.zeros((n, cap), KP_DTYPE), np.zeros((n, cap, 32), np.uint8), np.zeros(n, np.int32)
+        if not pinned:
+            return np.zeros((n, cap), KP_DTYPE), np.zeros((n, cap, 32), np.uint8), np.zeros(n, np.int32)
+        return (self._pinned_array((n, cap), KP_DTYPE), self._pinned_array((n, cap, 32), np.uint8), self._pinned_array((n,), np.int32))
+
+    def _pinned_array(self, shape, dtype):
+        nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        p = self._L.orbx_alloc_pinned(nbytes)
+        if not p:
+            check(-3, "orbx_alloc_pinned")
+        self._pinned.append(p)
+        buf = (C.c_uint8 * nbytes).from_address(p)
+        a = np.frombuffer(buf, dtype=dtype).reshape(shape)
+        a[...] = np.zeros((), dtype)
+        return a
 
     def extract_batch(self, images, out=None):
         """images: (n, rows, cols) uint8 host array.  Returns (kps[n, cap], desc[n, cap, 32], counts[n]); pass

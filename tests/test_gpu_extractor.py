@@ -258,3 +258,23 @@ def test_degenerate_configurations(gpu, oracle_mod):
         k, d = ex(img)
         assert k.tobytes() == ok.tobytes() and np.array_equal(d, od), cfg
         ex.close()
+
+
+def test_pinned_outputs_and_chunked_pipeline(gpu, oracle_mod):
+    """large host batches are cut into pipelined chunks (graph per chunk slot); with page-locked output arrays the
+    results are written straight into them.  Both variants must equal the per-frame oracle."""
+    shape, cfg = (240, 320), (400, 1.2, 8, 20, 7)
+    distinct = [synth.gen_frame(shape, s) for s in range(5)]
+    imgs = np.stack([distinct[i % 5] for i in range(80)])
+    ex = gpu.ORBextractor(*cfg)
+    o = oracle_mod.Extractor(*cfg)
+    refs = [o.extract(d) for d in distinct]
+    for pinned in (False, True):
+        out = ex.alloc_outputs(len(imgs), *shape, pinned=pinned)
+        for rep in range(3):  # plain launches, graph capture, graph replay
+            kps, desc, counts = ex.extract_batch(imgs, out=out)
+            for i in range(len(imgs)):
+                ok, od = refs[i % 5]
+                assert counts[i] == len(ok), (pinned, rep, i)
+                assert kps[i, : counts[i]].tobytes() == ok.tobytes() and np.array_equal(desc[i, : counts[i]], od), (pinned, rep, i)
+    ex.close()
