@@ -1666,6 +1666,17 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
     }
     ORBX_CUDA_TRY(cudaSetDevice(h->device));
     const bool piped = !h->profiling && n > PIPE_CHUNK + PIPE_CHUNK / 2;
+    // chunk schedule: a short first chunk (its H2D is exposed), then growing to PIPE_CHUNK (larger launches are more efficient)
+    std::vector<int> chunkStart;
+    if (piped) {
+        int f = 0, sz = std::max(8, PIPE_CHUNK / 4);
+        while (f < n) {
+            chunkStart.push_back(f);
+            f += std::min(sz, n - f);
+            sz = std::min(PIPE_CHUNK, sz * 3);
+        }
+    }
+    chunkStart.push_back(n);
     const int chunk = piped ? PIPE_CHUNK : n;
     int rc = ensure_plan(h, rows, cols, chunk);
     if (rc != ORBX_OK) return rc;
@@ -1745,7 +1756,7 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
         }
         if (!direct) copy_out(0, n);
     } else {
-        const int nchunks = (n + chunk - 1) / chunk;
+        const int nchunks = (int)chunkStart.size() - 1;
         while ((int)h->evChunkDone.size() < nchunks) {
             cudaEvent_t e;
             ORBX_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -1754,7 +1765,7 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
         h->lastFrames = chunk;
         int launches = 0;
         for (int k = 0; k < nchunks; k++) {
-            const int f0 = k * chunk, nk = std::min(chunk, n - f0), b = k & 1;
+            const int f0 = chunkStart[k], nk = chunkStart[k + 1] - f0, b = k & 1;
             uint8_t* dInB = h->dIn + (size_t)b * chunk * frameBytes;
             if (k >= 2) ORBX_CUDA_TRY(cudaStreamWaitEvent(h->streamH2D, h->evInFree[b], 0));
             if ((rc = copy_in(h, dInB, imgs + (size_t)f0 * frame_stride, nk, rows, cols, step, frame_stride, h->streamH2D)) != ORBX_OK) return rc;
@@ -1780,7 +1791,7 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
         } else {
             for (int k = 0; k < nchunks; k++) {
                 ORBX_CUDA_TRY(cudaEventSynchronize(h->evChunkDone[k]));
-                copy_out(k * chunk, std::min(n, (k + 1) * chunk));
+                copy_out(chunkStart[k], chunkStart[k + 1]);
             }
         }
         ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));

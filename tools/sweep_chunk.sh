@@ -1,6 +1,6 @@
 #!/bin/bash
 # e2e frames/s of bench.py for several host-pipeline chunk sizes (ORBX_PIPE_CHUNK)
-for c in 16 32 48 64 96 128; do
+for c in 12 16 20 24 28 32 40; do
   v=$(ORBX_PIPE_CHUNK=$c python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-extra 2>/dev/null | tail -1 | python -c "import json,sys; d=json.loads(sys.stdin.read()); print(round(d['e2e']['value']))")
   echo "chunk $c e2e $v"
 done
