@@ -105,6 +105,7 @@ struct Buffers {
     const FastUnit* fastUnits;  // [totalFastUnits]
     int* errFlag;        // device-side overflow flag
     int frames;
+    int frameBase;       // arena slot offset: arena frame = launch-local frame index + frameBase
 };
 
 // rBRIEF pattern: 256 pairs x (x0,y0,x1,y1), 1024 signed bytes
@@ -132,9 +133,9 @@ __global__ void __launch_bounds__(128) k_level0(Plan plan, Buffers buf, const ui
     const LevelGeom& g = plan.lv[0];
     const int bx = 16 * (blockIdx.x * 128 + threadIdx.x);
     if (bx >= g.pitch) return;
-    const int by = blockIdx.y, frame = blockIdx.z;
+    const int by = blockIdx.y, lframe = blockIdx.z, frame = lframe + buf.frameBase;
     const int y = reflect101(by - PAD_TOP, g.h);
-    const uint8_t* src = in + (long long)frame * inFrameStride + (long long)y * inStep;
+    const uint8_t* src = in + (long long)lframe * inFrameStride + (long long)y * inStep;
     uint4 out;
     const int x0 = bx - PAD_LEFT;
     if (x0 >= 0 && x0 + 16 <= g.w && ((reinterpret_cast<uintptr_t>(src + x0) & 15) == 0)) {
@@ -171,7 +172,7 @@ __global__ void __launch_bounds__(128) k_resize(Plan plan, Buffers buf, int leve
     const LevelGeom& g = plan.lv[level];
     const LevelGeom& gp = plan.lv[level - 1];
     const int bx = 4 * (blockIdx.x * 32 + (threadIdx.x & 31));  // pitch is a multiple of 128: always inside the row
-    const int frame = blockIdx.z;
+    const int frame = blockIdx.z + buf.frameBase;
     const int dy0 = (blockIdx.y * 4 + (threadIdx.x >> 5)) * rowsPerThread;
     if (dy0 >= g.h) return;
     const int dy1 = min(dy0 + rowsPerThread, g.h);
@@ -284,7 +285,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
     __shared__ int sQ1, sQ2, sQ3, sCnt, sBase, sPos;
     __shared__ int sHasIni[FAST_MAXG];
 
-    const int frame = blockIdx.y;
+    const int frame = blockIdx.y + buf.frameBase;
     const FastUnit fu = buf.fastUnits[blockIdx.x];
     const int level = fu.level, ci = fu.ci, j0 = fu.j0;
     const LevelGeom& g = plan.lv[level];
@@ -566,7 +567,7 @@ __global__ void __launch_bounds__(OCT_T) k_octree(Plan plan, Buffers buf, int no
     __shared__ int warpSums[33];
     __shared__ int sN, sNV, sFinish, sCut, sCtot;
 
-    const int level = blockIdx.x, frame = blockIdx.y;
+    const int level = blockIdx.x, frame = blockIdx.y + buf.frameBase;
     const LevelGeom& g = plan.lv[level];
     int* counter = buf.candCount + frame * plan.nlevels + level;
     const int M = min(*counter, g.candCap);
@@ -900,7 +901,7 @@ __global__ void __launch_bounds__(128) k_blur(Plan plan, Buffers buf)
     int level = 0;
     while (level + 1 < plan.nlevels && (int)blockIdx.x >= plan.lv[level + 1].blurOff) level++;
     const LevelGeom& g = plan.lv[level];
-    const int frame = blockIdx.y;
+    const int frame = blockIdx.y + buf.frameBase;
     const int unit = blockIdx.x - g.blurOff;
     const int cgroups = (g.w + 127) >> 7;  // CTAs across (32 threads x 4 columns)
     const int cy = unit / cgroups, cxg = unit - cy * cgroups;
@@ -982,7 +983,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 5) k_describe(Plan plan, Buff
 {
     __shared__ __align__(16) uint8_t patch[DESC_WARPS][37 * DESC_PP];
     __shared__ __align__(16) uint32_t raw[DESC_WARPS][31 * ORI_PW + 1];
-    const int frame = blockIdx.y;
+    const int lframe = blockIdx.y, frame = lframe + buf.frameBase;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     __shared__ int cum[ORBX_MAX_LEVELS + 1];
     if (threadIdx.x == 0) {
@@ -993,7 +994,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 5) k_describe(Plan plan, Buff
     }
     __syncthreads();  // cum and patF (filled below, before the first use after another barrier)
     const int total = min(cum[plan.nlevels], capacity);
-    if (blockIdx.x == 0 && threadIdx.x == 0) outCounts[frame] = total;
+    if (blockIdx.x == 0 && threadIdx.x == 0) outCounts[lframe] = total;
 
     // per-lane constants of the orientation pass: row v = lane - 15, columns u = 4k + b - 16
     const int v = lane - 15;
@@ -1097,7 +1098,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 5) k_describe(Plan plan, Buff
             const int t0 = center[iy0 * DESC_PP + ix0], t1 = center[iy1 * DESC_PP + ix1];
             val |= (t0 < t1) << k;
         }
-        const long long o = (long long)frame * capacity + gidx;
+        const long long o = (long long)lframe * capacity + gidx;
         outDesc[o * 32 + lane] = (uint8_t)val;
         if (lane == 0) {
             orbx_keypoint r;
@@ -1134,6 +1135,8 @@ struct orbx_handle {
     std::vector<int> quota;
     cudaStream_t stream = nullptr, streamBlur = nullptr, streamH2D = nullptr, streamD2H = nullptr;
     cudaEvent_t evInReady[2] = {}, evInFree[2] = {};
+    cudaStream_t stream2 = nullptr, streamBlur2 = nullptr;   // second compute lane of the pipelined host path
+    cudaEvent_t evFork2 = nullptr, evJoin2 = nullptr;
     std::vector<cudaEvent_t> evChunkDone;
     int* hErrFlag = nullptr;   // mapped pinned host word written by kernels on candidate overflow
     int* dErrFlag = nullptr;
@@ -1163,7 +1166,7 @@ struct orbx_handle {
     float stageMs[ORBX_NUM_STAGES] = {};
     int lastLaunches = 0;
     // graph cache for the device-resident path: key = (n, in ptr, steps, out ptrs)
-    struct GraphKey { const void* in; long long step, fstride; void* kps; void* desc; void* counts; int n, cap; };
+    struct GraphKey { const void* in; long long step, fstride; void* kps; void* desc; void* counts; int n, cap, slot, frameBase; };
     struct GraphEntry { GraphKey key; cudaGraphExec_t exec; int launches; unsigned long long stamp; };
     std::vector<GraphEntry> graphs;   // small LRU cache (the pipelined host path uses one graph per chunk slot)
     unsigned long long graphStamp = 0;
@@ -1382,12 +1385,17 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
 }
 
 // Enqueue every kernel of one batch on h->stream (+ the blur branch on h->streamBlur).
+// slot 0 = the handle's main stream; slot 1 = a second compute lane (own streams / events, arena frames offset by
+// frameBase) used by the pipelined host path so that consecutive chunks overlap.
 static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long long inFrameStride, int n,
-                   orbx_keypoint* dKps, uint8_t* dDesc, int* dCounts, int capacity, bool profile, int* launches)
+                   orbx_keypoint* dKps, uint8_t* dDesc, int* dCounts, int capacity, bool profile, int* launches,
+                   int slot = 0, int frameBase = 0)
 {
     const Plan& P = h->plan;
     Buffers B = h->buf;
-    cudaStream_t s = h->stream, sb = profile ? h->stream : h->streamBlur;
+    B.frameBase = frameBase;
+    cudaStream_t s = slot ? h->stream2 : h->stream, sb = profile ? s : (slot ? h->streamBlur2 : h->streamBlur);
+    cudaEvent_t evFork = slot ? h->evFork2 : h->evFork, evJoin = slot ? h->evJoin2 : h->evJoin;
     int nl = 0;
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_PYRAMID], s));
     {
@@ -1407,8 +1415,8 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
     }
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_FAST], s));
     if (!profile) {
-        ORBX_CUDA_TRY(cudaEventRecord(h->evFork, s));
-        ORBX_CUDA_TRY(cudaStreamWaitEvent(sb, h->evFork, 0));
+        ORBX_CUDA_TRY(cudaEventRecord(evFork, s));
+        ORBX_CUDA_TRY(cudaStreamWaitEvent(sb, evFork, 0));
     }
     k_fast_band<<<dim3(P.totalFastUnits, n), FAST_T, h->fastSmem, s>>>(P, B);
     nl++;
@@ -1419,8 +1427,8 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
     k_blur<<<dim3(P.totalBlurUnits, n), 128, 0, sb>>>(P, B);
     nl++;
     if (!profile) {
-        ORBX_CUDA_TRY(cudaEventRecord(h->evJoin, sb));
-        ORBX_CUDA_TRY(cudaStreamWaitEvent(s, h->evJoin, 0));
+        ORBX_CUDA_TRY(cudaEventRecord(evJoin, sb));
+        ORBX_CUDA_TRY(cudaStreamWaitEvent(s, evJoin, 0));
     }
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_DESC], s));
     k_describe<<<dim3((capacity + 4 * DESC_WARPS - 1) / (4 * DESC_WARPS), n), DESC_WARPS * 32, 0, s>>>(P, B, dKps, dDesc, dCounts, capacity);
@@ -1437,16 +1445,17 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
 static const size_t GRAPH_CACHE = 24;
 
 static int launch_cached(orbx_handle* h, const uint8_t* dIn, long long inStep, long long inFrameStride, int n, orbx_keypoint* dKps,
-                         uint8_t* dDesc, int* dCounts, int capacity, int* launches)
+                         uint8_t* dDesc, int* dCounts, int capacity, int* launches, int slot = 0, int frameBase = 0)
 {
+    cudaStream_t cs = slot ? h->stream2 : h->stream;
     if (h->plainRuns == 0 || !h->useGraph) {
         std::lock_guard<std::mutex> setupLock(g_setupMutex);
         h->plainRuns = 1;
-        return enqueue(h, dIn, inStep, inFrameStride, n, dKps, dDesc, dCounts, capacity, false, launches);
+        return enqueue(h, dIn, inStep, inFrameStride, n, dKps, dDesc, dCounts, capacity, false, launches, slot, frameBase);
     }
     orbx_handle::GraphKey k;
     memset(&k, 0, sizeof k);
-    k.in = dIn; k.step = inStep; k.fstride = inFrameStride; k.kps = dKps; k.desc = dDesc; k.counts = dCounts; k.n = n; k.cap = capacity;
+    k.in = dIn; k.step = inStep; k.fstride = inFrameStride; k.kps = dKps; k.desc = dDesc; k.counts = dCounts; k.n = n; k.cap = capacity; k.slot = slot; k.frameBase = frameBase;
     orbx_handle::GraphEntry* hit = nullptr;
     for (auto& g : h->graphs)
         if (memcmp(&g.key, &k, sizeof k) == 0) { hit = &g; break; }
@@ -1461,9 +1470,9 @@ static int launch_cached(orbx_handle* h, const uint8_t* dIn, long long inStep, l
         }
         cudaGraph_t graph = nullptr;
         int nl = 0;
-        ORBX_CUDA_TRY(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
-        const int rc = enqueue(h, dIn, inStep, inFrameStride, n, dKps, dDesc, dCounts, capacity, false, &nl);
-        cudaError_t e = cudaStreamEndCapture(h->stream, &graph);
+        ORBX_CUDA_TRY(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+        const int rc = enqueue(h, dIn, inStep, inFrameStride, n, dKps, dDesc, dCounts, capacity, false, &nl, slot, frameBase);
+        cudaError_t e = cudaStreamEndCapture(cs, &graph);
         if (rc != ORBX_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
         if (e != cudaSuccess) { set_error("cudaStreamEndCapture: %s", cudaGetErrorString(e)); return ORBX_ERR_CUDA; }
         cudaGraphExec_t exec = nullptr;
@@ -1474,7 +1483,7 @@ static int launch_cached(orbx_handle* h, const uint8_t* dIn, long long inStep, l
         hit = &h->graphs.back();
     }
     hit->stamp = ++h->graphStamp;
-    ORBX_CUDA_TRY(cudaGraphLaunch(hit->exec, h->stream));
+    ORBX_CUDA_TRY(cudaGraphLaunch(hit->exec, cs));
     if (launches) *launches = hit->launches;
     return ORBX_OK;
 }
@@ -1544,6 +1553,10 @@ int orbx_create(const orbx_config* cfg, int device, orbx_handle** out)
         e = cudaEventCreateWithFlags(&h->evInReady[i], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->evInFree[i], cudaEventDisableTiming);
     }
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->streamBlur2, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->evFork2, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->evJoin2, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaHostAlloc((void**)&h->hErrFlag, sizeof(int), cudaHostAllocMapped);
     if (e == cudaSuccess) { *h->hErrFlag = 0; e = cudaHostGetDevicePointer((void**)&h->dErrFlag, h->hErrFlag, 0); }
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->evFork, cudaEventDisableTiming);
@@ -1576,6 +1589,10 @@ void orbx_destroy(orbx_handle* h)
     if (h->streamD2H) cudaStreamDestroy(h->streamD2H);
     for (int i = 0; i < 2; i++) { if (h->evInReady[i]) cudaEventDestroy(h->evInReady[i]); if (h->evInFree[i]) cudaEventDestroy(h->evInFree[i]); }
     for (auto& ev : h->evChunkDone) cudaEventDestroy(ev);
+    if (h->stream2) { cudaStreamSynchronize(h->stream2); cudaStreamDestroy(h->stream2); }
+    if (h->streamBlur2) cudaStreamDestroy(h->streamBlur2);
+    if (h->evFork2) cudaEventDestroy(h->evFork2);
+    if (h->evJoin2) cudaEventDestroy(h->evJoin2);
     if (h->hErrFlag) cudaFreeHost(h->hErrFlag);
     delete h;
 }
@@ -1678,7 +1695,7 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
     }
     chunkStart.push_back(n);
     const int chunk = piped ? PIPE_CHUNK : n;
-    int rc = ensure_plan(h, rows, cols, chunk);
+    int rc = ensure_plan(h, rows, cols, piped ? 2 * chunk : chunk);  // pipelined: two arena slots of `chunk` frames
     if (rc != ORBX_OK) return rc;
     if (capacity < h->plan.kpCapFrame) {
         set_error("orbx_extract_batch: capacity %d < orbx_max_keypoints() = %d", capacity, h->plan.kpCapFrame);
@@ -1770,13 +1787,14 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
             if (k >= 2) ORBX_CUDA_TRY(cudaStreamWaitEvent(h->streamH2D, h->evInFree[b], 0));
             if ((rc = copy_in(h, dInB, imgs + (size_t)f0 * frame_stride, nk, rows, cols, step, frame_stride, h->streamH2D)) != ORBX_OK) return rc;
             ORBX_CUDA_TRY(cudaEventRecord(h->evInReady[b], h->streamH2D));
-            ORBX_CUDA_TRY(cudaStreamWaitEvent(h->stream, h->evInReady[b], 0));
+            cudaStream_t cs = b ? h->stream2 : h->stream;  // chunk k computes in arena slot b on compute lane b
+            ORBX_CUDA_TRY(cudaStreamWaitEvent(cs, h->evInReady[b], 0));
             int nl = 0;
             rc = launch_cached(h, dInB, (long long)cols, (long long)frameBytes, nk, dKps + (size_t)f0 * devCap,
-                               dDesc + (size_t)f0 * devCap * 32, dCounts + f0, devCap, &nl);
+                               dDesc + (size_t)f0 * devCap * 32, dCounts + f0, devCap, &nl, b, b * chunk);
             if (rc != ORBX_OK) return rc;
             launches += nl;
-            ORBX_CUDA_TRY(cudaEventRecord(h->evInFree[b], h->stream));
+            ORBX_CUDA_TRY(cudaEventRecord(h->evInFree[b], cs));
             ORBX_CUDA_TRY(cudaStreamWaitEvent(h->streamD2H, h->evInFree[b], 0));
             ORBX_CUDA_TRY(cudaMemcpyAsync(hCnt + (size_t)f0 * sizeof(int), dCounts + f0, sizeof(int) * nk, cudaMemcpyDeviceToHost, h->streamD2H));
             ORBX_CUDA_TRY(cudaMemcpyAsync(hKps + (size_t)f0 * devCap * sizeof(orbx_keypoint), dKps + (size_t)f0 * devCap,
@@ -1795,6 +1813,7 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
             }
         }
         ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+        ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream2));
     }
     if (*h->hErrFlag) { set_error("candidate list overflow on device"); return ORBX_ERR_CAPACITY; }
     return ORBX_OK;
