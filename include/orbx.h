@@ -216,6 +216,9 @@ typedef struct orbm_window_query_view {
 /* Windowed search with the reference's order-dependent claims, shared by
  *   ORBmatcher::SearchByProjection(Frame& Cur, const Frame& Last, th, bMono)          src/ORBmatcher.cc:1620-1789
  *   ORBmatcher::SearchByProjection(Frame& Cur, KeyFrame*, sAlreadyFound, th, ORBdist)  src/ORBmatcher.cc:1792-1924
+ *   ORBmatcher::SearchByProjection(KeyFrame*, cv::Mat Scw, vpPoints, vpMatched, th)   src/ORBmatcher.cc:398-520
+ *     (loop closing; KeyFrame::GetFeaturesInArea is the same window walk: occupied[i] = (vpMatched[i] != NULL),
+ *      claims_block = 1, max_dist = TH_LOW, ratio_mode 0, check_orientation 0, levels [pred-1, pred], xr = NULL)
  * (max_dist = TH_HIGH resp. ORBdist, ratio_mode 0, check_orientation = mbCheckOrientation; for the KeyFrame overload
  * pass occupied[i] = (mvpMapPoints[i] != NULL), claims_block = 1 and xr = NULL) and, with ratio_mode 1, by
  * orbm_search_by_projection.  f_angle = Cur.mvKeysUn[i].angle.  HOST pointers.
@@ -266,6 +269,66 @@ int orbm_search_by_bow_kf(orbm_context* m, int n1, const uint8_t* desc1, const f
                           const orbm_featvec_view* fv1, int n2, const uint8_t* desc2, const float* angle2,
                           const uint8_t* has_mp2, const orbm_featvec_view* fv2, float nnratio, int check_orientation,
                           int32_t* out_match12, int* nmatches);
+
+/* Claim-free windowed search ("next" row): the candidate loop of
+ *   ORBmatcher::Fuse(KeyFrame*, const vector<MapPoint*>&, th)          src/ORBmatcher.cc:1067-1222  gate = 1
+ *   ORBmatcher::Fuse(KeyFrame*, cv::Mat Scw, vpPoints, th, vpReplace)  src/ORBmatcher.cc:1225-1357  gate = 0
+ * after the caller's projection (x, y = u, v; xr = u - bf*invz; radius = th * mvScaleFactors[nPredictedLevel];
+ * min_level / max_level = nPredictedLevel-1 / nPredictedLevel; valid = 0 for the points the reference skips before the
+ * search).  f describes the KeyFrame (mvKeysUn, mvuRight, mDescriptors, mGrid as in orbm_frame_view; `occupied`,
+ * q->angle and q->claims_block are not read).  Candidates are KeyFrame::GetFeaturesInArea(u, v, radius)
+ * (src/KeyFrame.cc:623-658); gate 1 adds Fuse's reprojection test e2 * inv_level_sigma2[octave] > 7.8 (stereo keypoint,
+ * e2 includes (xr - mvuRight)^2) resp. > 5.99 (monocular).  max_dist = TH_LOW (50) for both Fuse overloads.
+ * best_idx[q] = KeyFrame feature (first minimum in visiting order) or -1 (no candidate / distance > max_dist);
+ * best_dist (may be NULL) = the smallest distance seen (256 when none).  The map mutations (Replace / AddObservation /
+ * AddMapPoint / vpReplacePoint, :1198-1217 and :1333-1350) stay with the caller.  HOST pointers. */
+int orbm_search_best(orbm_context* m, const orbm_frame_view* f, const orbm_window_query_view* q, int gate,
+                     const float* inv_level_sigma2, int max_dist, int32_t* best_idx, int32_t* best_dist);
+
+/* Replaces the two projection passes and the agreement check of ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1361-1602).
+ * q1_in_2: one entry per KF1 feature = its map point transformed into camera 2 and projected (valid = has a good map
+ * point, !vbAlreadyMatched1, in image, inside the scale-invariance distances), searched in kf2; q2_in_1 likewise, one
+ * entry per KF2 feature, searched in kf1; radius = th * mvScaleFactors[nPredictedLevel], levels [pred-1, pred],
+ * acceptance bestDist <= TH_HIGH.  out_match12[i1] = idx2 when both directions agree, else -1 (the caller stores
+ * vpMapPoints2[idx2] into vpMatches12[i1]); *nfound = the return value.  HOST pointers. */
+int orbm_search_by_sim3(orbm_context* m, const orbm_frame_view* kf1, const orbm_window_query_view* q2_in_1,
+                        const orbm_frame_view* kf2, const orbm_window_query_view* q1_in_2, int32_t* out_match12,
+                        int* nfound);
+
+/* Replaces ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)
+ * (src/ORBmatcher.cc:539-683) including vMatchedDistance / vnMatches21 (a later, strictly better match steals an F2
+ * feature; the stolen match still counts in the rotation histogram).  F1 side: octave1 = mvKeysUn[i].octave (only level
+ * 0 searches), angle1, desc1 = mDescriptors, prev_x / prev_y = vbPrevMatched.  f2 = F2 as orbm_frame_view (`occupied`
+ * and `u_right` not read), f2_angle = F2.mvKeysUn[i].angle.  out_match12[i1] = vnMatches12; the caller updates
+ * vbPrevMatched[i1] = F2.mvKeysUn[out_match12[i1]].pt for the matched ones (:677-680).  HOST pointers. */
+int orbm_search_for_initialization(orbm_context* m, int n1, const int32_t* octave1, const float* angle1,
+                                   const uint8_t* desc1, const float* prev_x, const float* prev_y,
+                                   const orbm_frame_view* f2, const float* f2_angle, int window_size, float nnratio,
+                                   int check_orientation, int32_t* out_match12, int* nmatches);
+
+/* One key frame of SearchForTriangulation: mvKeysUn (pt, octave, angle), mvuRight (>= 0 = stereo), mDescriptors,
+ * has_mp[i] = (GetMapPoint(i) != NULL), mFeatVec. */
+typedef struct orbm_kf_view {
+    int n;
+    const float* x;
+    const float* y;
+    const int32_t* octave;
+    const float* angle;
+    const float* u_right;
+    const uint8_t* desc;
+    const uint8_t* has_mp;
+    const orbm_featvec_view* fv;
+} orbm_kf_view;
+
+/* Replaces ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo)
+ * (src/ORBmatcher.cc:850-1056) with CheckDistEpipolarLine (:186-213).  F12 = 3x3 row-major; (ex, ey) = projection of
+ * KF1's camera centre into KF2 (:858-865, computed by the caller); scale_factors2 / level_sigma2_2 = pKF2->mvScaleFactors
+ * / mvLevelSigma2.  out_match12[idx1] = idx2 or -1: vMatchedPairs is the list of (i, out_match12[i]) with
+ * out_match12[i] >= 0 in ascending i.  HOST pointers. */
+int orbm_search_for_triangulation(orbm_context* m, const orbm_kf_view* kf1, const orbm_kf_view* kf2, const float* F12,
+                                  float ex, float ey, const float* scale_factors2, const float* level_sigma2_2,
+                                  int nlevels2, int only_stereo, int check_orientation, int32_t* out_match12,
+                                  int* nmatches);
 
 /* ---- DBoW2 vocabulary descent ("next" row) ------------------------------------ */
 

@@ -145,6 +145,18 @@ def _bind_all(L):
     L.orbo_search_window.argtypes = ([_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _vp]
                                      + [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp] + [_i, _i, _f, _i, _vp])
     L.orbo_distinctive_descriptors.argtypes = [_i, _vp, _vp, _vp]
+    L.orbo_search_best.restype = None
+    L.orbo_search_best.argtypes = ([_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _f, _f]
+                                   + [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _vp])
+    L.orbo_sim3_cross_check.restype = _i
+    L.orbo_sim3_cross_check.argtypes = [_i, _vp, _i, _vp, _vp]
+    L.orbo_search_for_initialization.restype = _i
+    L.orbo_search_for_initialization.argtypes = ([_i, _vp, _vp, _vp, _vp, _vp] + [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _f, _f]
+                                                 + [_i, _f, _i, _vp])
+    L.orbo_search_for_triangulation.restype = _i
+    L.orbo_search_for_triangulation.argtypes = ([_i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp]
+                                                + [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp]
+                                                + [_vp, _f, _f, _vp, _vp, _i, _i, _vp])
     L.orbo_search_by_bow_kf.restype = _i
     L.orbo_search_by_bow_kf.argtypes = [_i, _vp, _vp, _vp, _i, _vp, _vp, _vp] * 2 + [_f, _i, _vp]
     L.orbo_bow_transform.argtypes = [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]
@@ -407,4 +419,62 @@ def search_by_bow_kf(kf1, kf2, nnratio, check_orientation):
         args += [len(kf["angle"]), _ptr(kf["desc"]), _ptr(kf["angle"]), _ptr(kf["has_mp"]), len(kf["node_id"]), _ptr(kf["node_id"]),
                  _ptr(kf["node_start"]), _ptr(kf["node_feat"])]
     n = L.orbo_search_by_bow_kf(*args, nnratio, int(check_orientation), out.ctypes.data)
+    return n, out[:n1]
+
+
+def _frame_args(frame):
+    return [len(frame["x"]), _ptr(frame["x"]), _ptr(frame["y"]), _ptr(frame["octave"]), _ptr(frame.get("u_right")), _ptr(frame["desc"]),
+            _ptr(frame["cell_start"]), _ptr(frame["cell_items"]), frame["min_x"], frame["min_y"], frame["w_inv"], frame["h_inv"]]
+
+
+def search_best(kf, q, gate, inv_level_sigma2, max_dist):
+    """Claim-free windowed search (Fuse x2, SearchBySim3 passes); see match_oracle.cc."""
+    L = lib()
+    nq = len(q["x"])
+    bi = np.full(max(nq, 1), -1, np.int32)
+    bd = np.full(max(nq, 1), 256, np.int32)
+    sig = np.ascontiguousarray(inv_level_sigma2, np.float32) if inv_level_sigma2 is not None else None
+    L.orbo_search_best(*_frame_args(kf), nq, _ptr(q["x"]), _ptr(q["y"]), _ptr(q["radius"]), _ptr(q["min_level"]),
+                       _ptr(q["max_level"]), _ptr(q.get("xr")), _ptr(q["valid"]), _ptr(q["desc"]), int(gate), _ptr(sig),
+                       int(max_dist), bi.ctypes.data, bd.ctypes.data)
+    return bi[:nq], bd[:nq]
+
+
+def search_by_sim3(kf1, q2_in_1, kf2, q1_in_2):
+    L = lib()
+    m1, _ = search_best(kf2, q1_in_2, 0, None, 100)
+    m2, _ = search_best(kf1, q2_in_1, 0, None, 100)
+    m1 = np.ascontiguousarray(m1); m2 = np.ascontiguousarray(m2)
+    out = np.full(max(len(m1), 1), -1, np.int32)
+    n = L.orbo_sim3_cross_check(len(m1), m1.ctypes.data, len(m2), m2.ctypes.data, out.ctypes.data)
+    return n, out[: len(m1)]
+
+
+def search_for_initialization(f1, f2, prev_matched, window_size, nnratio, check_orientation):
+    L = lib()
+    n1 = len(f1["octave"])
+    pm = np.ascontiguousarray(prev_matched, np.float32).reshape(-1, 2)
+    px, py = np.ascontiguousarray(pm[:, 0]), np.ascontiguousarray(pm[:, 1])
+    out = np.full(max(n1, 1), -1, np.int32)
+    n = L.orbo_search_for_initialization(
+        n1, _ptr(f1["octave"]), _ptr(f1["angle"]), _ptr(f1["desc"]), px.ctypes.data, py.ctypes.data,
+        len(f2["x"]), _ptr(f2["x"]), _ptr(f2["y"]), _ptr(f2["octave"]), _ptr(f2["angle"]), _ptr(f2["desc"]),
+        _ptr(f2["cell_start"]), _ptr(f2["cell_items"]), f2["min_x"], f2["min_y"], f2["w_inv"], f2["h_inv"],
+        int(window_size), float(nnratio), int(check_orientation), out.ctypes.data)
+    return n, out[:n1]
+
+
+def search_for_triangulation(kf1, kf2, F12, ex, ey, scale_factors2, level_sigma2_2, only_stereo, check_orientation):
+    L = lib()
+    n1 = len(kf1["x"])
+    out = np.full(max(n1, 1), -1, np.int32)
+    F = np.ascontiguousarray(np.asarray(F12, np.float32).reshape(9))
+    sf = np.ascontiguousarray(scale_factors2, np.float32)
+    sg = np.ascontiguousarray(level_sigma2_2, np.float32)
+    n = L.orbo_search_for_triangulation(
+        n1, _ptr(kf1["x"]), _ptr(kf1["y"]), _ptr(kf1["angle"]), _ptr(kf1["u_right"]), _ptr(kf1["desc"]), _ptr(kf1["has_mp"]),
+        len(kf1["node_id"]), _ptr(kf1["node_id"]), _ptr(kf1["node_start"]), _ptr(kf1["node_feat"]),
+        len(kf2["x"]), _ptr(kf2["x"]), _ptr(kf2["y"]), _ptr(kf2["octave"]), _ptr(kf2["angle"]), _ptr(kf2["u_right"]), _ptr(kf2["desc"]),
+        _ptr(kf2["has_mp"]), len(kf2["node_id"]), _ptr(kf2["node_id"]), _ptr(kf2["node_start"]), _ptr(kf2["node_feat"]),
+        F.ctypes.data, float(ex), float(ey), sf.ctypes.data, sg.ctypes.data, int(only_stereo), int(check_orientation), out.ctypes.data)
     return n, out[:n1]

@@ -13,6 +13,8 @@
 //   orbo_search_by_bow         <- ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...) src/ORBmatcher.cc:228-392
 //                                 + ComputeThreeMaxima :1935-1977
 //   orbo_assign_grid           <- Frame::AssignFeaturesToGrid / PosInGrid    src/Frame.cc:351-370, 558-567
+//   orbo_search_for_initialization / orbo_search_best (Fuse x2, SearchBySim3) / orbo_search_for_triangulation
+//                              <- src/ORBmatcher.cc:539-683, 1067-1357, 1361-1602, 850-1056 (see the headers below)
 #include <cstdint>
 #include <cstddef>
 #include <cstring>
@@ -579,4 +581,250 @@ extern "C" int orbo_search_by_bow_kf(
         }
     }
     return nmatches;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Shared by the four remaining matcher overloads below: ComputeThreeMaxima (src/ORBmatcher.cc:1935-1977) on bin sizes.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+void three_maxima(const std::vector<int>* rotHist, int& ind1, int& ind2, int& ind3)
+{
+    int max1 = 0, max2 = 0, max3 = 0;
+    ind1 = ind2 = ind3 = -1;
+    for (int i = 0; i < HISTO_LENGTH; i++) {
+        const int s = (int)rotHist[i].size();
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+        else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) ind3 = -1;
+}
+inline int rot_bin(float a1, float a2)
+{
+    const float factor = HISTO_LENGTH / 360.0f;
+    float rot = a1 - a2;
+    if (rot < 0.0) rot += 360.0f;
+    int bin = (int)std::round(rot * factor);
+    if (bin == HISTO_LENGTH) bin = 0;
+    return bin;
+}
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------------------------
+// ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)  src/ORBmatcher.cc:539-683.
+// Frame 2 is given as in orbo_search_window (keypoints + grid); frame 1 as octave / angle / descriptor and the
+// vbPrevMatched positions.  Only level-0 features of F1 search, inside F2.GetFeaturesInArea(x, y, windowSize, 0, 0); a
+// candidate is skipped when an earlier F1 feature already holds it with a distance <= this one (vMatchedDistance), a
+// later better match steals it (vnMatches21 / vnMatches12 reset); the stolen match stays in the rotation histogram.
+// out12[i1] = matched F2 feature or -1; returns nmatches.
+// ---------------------------------------------------------------------------------------------------------------------
+extern "C" int orbo_search_for_initialization(
+    int n1, const int32_t* oct1, const float* angle1, const uint8_t* desc1, const float* prevx, const float* prevy,
+    int n2, const float* kx, const float* ky, const int32_t* koct, const float* kangle, const uint8_t* kdesc,
+    const int32_t* cell_start, const int32_t* cell_items, float minX, float minY, float wInv, float hInv,
+    int windowSize, float nnratio, int checkOrientation, int32_t* out12)
+{
+    int nmatches = 0;
+    for (int i = 0; i < n1; i++) out12[i] = -1;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    std::vector<int> vMatchedDistance(n2 > 0 ? n2 : 1, 0x7fffffff), vnMatches21(n2 > 0 ? n2 : 1, -1);
+    for (int i1 = 0; i1 < n1; i1++) {
+        const int level1 = oct1[i1];
+        if (level1 > 0) continue;
+        const float x = prevx[i1], y = prevy[i1], rr = (float)windowSize;
+        const int c0 = std::max(0, (int)std::floor((x - minX - rr) * wInv));
+        if (c0 >= GRID_COLS) continue;
+        const int c1 = std::min(GRID_COLS - 1, (int)std::ceil((x - minX + rr) * wInv));
+        if (c1 < 0) continue;
+        const int r0 = std::max(0, (int)std::floor((y - minY - rr) * hInv));
+        if (r0 >= GRID_ROWS) continue;
+        const int r1 = std::min(GRID_ROWS - 1, (int)std::ceil((y - minY + rr) * hInv));
+        if (r1 < 0) continue;
+        int bestDist = 0x7fffffff, bestDist2 = 0x7fffffff, bestIdx2 = -1;
+        for (int ix = c0; ix <= c1; ix++)
+            for (int iy = r0; iy <= r1; iy++) {
+                const int c = ix * GRID_ROWS + iy;
+                for (int k = cell_start[c]; k < cell_start[c + 1]; k++) {
+                    const int i2 = cell_items[k];
+                    if (koct[i2] < level1) continue;   // bCheckLevels: minLevel = maxLevel = level1 = 0
+                    if (koct[i2] > level1) continue;
+                    const float dx = kx[i2] - x, dy = ky[i2] - y;
+                    if (!(std::fabs(dx) < rr && std::fabs(dy) < rr)) continue;
+                    const int dist = hamming256(desc1 + 32 * (size_t)i1, kdesc + 32 * (size_t)i2);
+                    if (vMatchedDistance[i2] <= dist) continue;
+                    if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+                    else if (dist < bestDist2) bestDist2 = dist;
+                }
+            }
+        if (bestDist <= TH_LOW) {
+            if (bestDist < (float)bestDist2 * nnratio) {
+                if (vnMatches21[bestIdx2] >= 0) { out12[vnMatches21[bestIdx2]] = -1; nmatches--; }
+                out12[i1] = bestIdx2;
+                vnMatches21[bestIdx2] = i1;
+                vMatchedDistance[bestIdx2] = bestDist;
+                nmatches++;
+                if (checkOrientation) rotHist[rot_bin(angle1[i1], kangle[bestIdx2])].push_back(i1);
+            }
+        }
+    }
+    if (checkOrientation) {
+        int ind1, ind2, ind3;
+        three_maxima(rotHist, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx1 : rotHist[i])
+                if (out12[idx1] >= 0) { out12[idx1] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Claim-free windowed search: the candidate loop shared by
+//   ORBmatcher::Fuse(KeyFrame*, const vector<MapPoint*>&, th)                      src/ORBmatcher.cc:1067-1222  (gate 1)
+//   ORBmatcher::Fuse(KeyFrame*, Scw, vpPoints, th, vpReplacePoint)                 src/ORBmatcher.cc:1225-1357  (gate 0)
+//   the two projection passes of ORBmatcher::SearchBySim3                          src/ORBmatcher.cc:1361-1602  (gate 0)
+// after the caller's projection (u, v, ur, radius = th * scale[predicted level], levels [pred-1, pred]).  Candidates come
+// from KeyFrame::GetFeaturesInArea(u, v, radius) (src/KeyFrame.cc:623-658), best = first minimum (strict <).  gate 1 is
+// Fuse's reprojection test: stereo keypoints (mvuRight >= 0) e2 = ex^2+ey^2+er^2, e2*invSigma2 > 7.8 rejects, monocular
+// ones e2 = ex^2+ey^2, > 5.99 rejects.  best_idx[q] = -1 when there is no candidate or bestDist > maxDist.
+// ---------------------------------------------------------------------------------------------------------------------
+extern "C" void orbo_search_best(
+    int nkp, const float* kx, const float* ky, const int32_t* koct, const float* uright, const uint8_t* kdesc,
+    const int32_t* cell_start, const int32_t* cell_items, float minX, float minY, float wInv, float hInv,
+    int nq, const float* qx, const float* qy, const float* qradius, const int32_t* qmin, const int32_t* qmax,
+    const float* qxr, const uint8_t* qvalid, const uint8_t* qdesc, int gate, const float* invLevelSigma2, int maxDist,
+    int32_t* best_idx, int32_t* best_dist)
+{
+    (void)nkp;
+    for (int m = 0; m < nq; m++) {
+        best_idx[m] = -1;
+        best_dist[m] = 256;
+        if (!qvalid[m]) continue;
+        const float u = qx[m], v = qy[m], rr = qradius[m];
+        const int c0 = std::max(0, (int)std::floor((u - minX - rr) * wInv));
+        if (c0 >= GRID_COLS) continue;
+        const int c1 = std::min(GRID_COLS - 1, (int)std::ceil((u - minX + rr) * wInv));
+        if (c1 < 0) continue;
+        const int r0 = std::max(0, (int)std::floor((v - minY - rr) * hInv));
+        if (r0 >= GRID_ROWS) continue;
+        const int r1 = std::min(GRID_ROWS - 1, (int)std::ceil((v - minY + rr) * hInv));
+        if (r1 < 0) continue;
+        int bestDist = 256, bestIdx = -1;
+        for (int ix = c0; ix <= c1; ix++)
+            for (int iy = r0; iy <= r1; iy++) {
+                const int c = ix * GRID_ROWS + iy;
+                for (int k = cell_start[c]; k < cell_start[c + 1]; k++) {
+                    const int idx = cell_items[k];
+                    const float dx = kx[idx] - u, dy = ky[idx] - v;
+                    if (!(std::fabs(dx) < rr && std::fabs(dy) < rr)) continue;
+                    const int kpLevel = koct[idx];
+                    if (kpLevel < qmin[m] || kpLevel > qmax[m]) continue;
+                    if (gate == 1) {
+                        if (uright && uright[idx] >= 0) {
+                            const float ex = u - kx[idx], ey = v - ky[idx], er = qxr[m] - uright[idx];
+                            const float e2 = ex * ex + ey * ey + er * er;
+                            if (e2 * invLevelSigma2[kpLevel] > 7.8) continue;
+                        } else {
+                            const float ex = u - kx[idx], ey = v - ky[idx];
+                            const float e2 = ex * ex + ey * ey;
+                            if (e2 * invLevelSigma2[kpLevel] > 5.99) continue;
+                        }
+                    }
+                    const int dist = hamming256(qdesc + 32 * (size_t)m, kdesc + 32 * (size_t)idx);
+                    if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+                }
+            }
+        best_dist[m] = bestDist;
+        if (bestIdx >= 0 && bestDist <= maxDist) best_idx[m] = bestIdx;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo)  src/ORBmatcher.cc:850-1056 with
+// CheckDistEpipolarLine :186-213.  Feature vectors in CSR form; has_mp = GetMapPoint(idx) != NULL; ur = mvuRight (>= 0 is
+// stereo); (ex, ey) = epipole of KF1's centre in KF2 (computed by the caller, :858-865); F12 row-major 3x3.
+// Candidate rule: `dist > TH_LOW || dist > bestDist` skips, so among the candidates passing the gates the minimum
+// distance wins and, on ties, the LAST one in node order.  out12[idx1] = idx2 or -1; returns nmatches.
+// ---------------------------------------------------------------------------------------------------------------------
+extern "C" int orbo_search_for_triangulation(
+    int n1, const float* x1, const float* y1, const float* angle1, const float* ur1, const uint8_t* desc1, const uint8_t* has_mp1,
+    int n_nodes1, const int32_t* node_id1, const int32_t* node_start1, const int32_t* node_feat1,
+    int n2, const float* x2, const float* y2, const int32_t* oct2, const float* angle2, const float* ur2, const uint8_t* desc2,
+    const uint8_t* has_mp2, int n_nodes2, const int32_t* node_id2, const int32_t* node_start2, const int32_t* node_feat2,
+    const float* F12, float ex, float ey, const float* scaleFactors2, const float* levelSigma2_2, int onlyStereo,
+    int checkOrientation, int32_t* out12)
+{
+    for (int i = 0; i < n1; i++) out12[i] = -1;
+    std::vector<uint8_t> matched2(n2 > 0 ? n2 : 1, 0);
+    std::vector<int> rotHist[HISTO_LENGTH];
+    int nmatches = 0, a = 0, b = 0;
+    while (a < n_nodes1 && b < n_nodes2) {
+        if (node_id1[a] == node_id2[b]) {
+            for (int i1 = node_start1[a]; i1 < node_start1[a + 1]; i1++) {
+                const int idx1 = node_feat1[i1];
+                if (has_mp1[idx1]) continue;
+                const bool bStereo1 = ur1[idx1] >= 0;
+                if (onlyStereo && !bStereo1) continue;
+                int bestDist = TH_LOW, bestIdx2 = -1;
+                for (int i2 = node_start2[b]; i2 < node_start2[b + 1]; i2++) {
+                    const int idx2 = node_feat2[i2];
+                    if (matched2[idx2] || has_mp2[idx2]) continue;
+                    const bool bStereo2 = ur2[idx2] >= 0;
+                    if (onlyStereo && !bStereo2) continue;
+                    const int dist = hamming256(desc1 + 32 * (size_t)idx1, desc2 + 32 * (size_t)idx2);
+                    if (dist > TH_LOW || dist > bestDist) continue;
+                    if (!bStereo1 && !bStereo2) {
+                        const float distex = ex - x2[idx2], distey = ey - y2[idx2];
+                        if (distex * distex + distey * distey < 100 * scaleFactors2[oct2[idx2]]) continue;
+                    }
+                    // CheckDistEpipolarLine
+                    const float la = x1[idx1] * F12[0] + y1[idx1] * F12[3] + F12[6];
+                    const float lb = x1[idx1] * F12[1] + y1[idx1] * F12[4] + F12[7];
+                    const float lc = x1[idx1] * F12[2] + y1[idx1] * F12[5] + F12[8];
+                    const float num = la * x2[idx2] + lb * y2[idx2] + lc;
+                    const float den = la * la + lb * lb;
+                    if (den == 0) continue;
+                    const float dsqr = num * num / den;
+                    if (dsqr < 3.84 * levelSigma2_2[oct2[idx2]]) { bestIdx2 = idx2; bestDist = dist; }
+                }
+                if (bestIdx2 >= 0) {
+                    out12[idx1] = bestIdx2;
+                    matched2[bestIdx2] = 1;
+                    nmatches++;
+                    if (checkOrientation) rotHist[rot_bin(angle1[idx1], angle2[bestIdx2])].push_back(idx1);
+                }
+            }
+            a++; b++;
+        } else if (node_id1[a] < node_id2[b]) {
+            a = (int)(std::lower_bound(node_id1 + a, node_id1 + n_nodes1, node_id2[b]) - node_id1);
+        } else {
+            b = (int)(std::lower_bound(node_id2 + b, node_id2 + n_nodes2, node_id1[a]) - node_id2);
+        }
+    }
+    if (checkOrientation) {
+        int ind1, ind2, ind3;
+        three_maxima(rotHist, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx1 : rotHist[i]) { out12[idx1] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Tail of ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1585-1602): keep i1 -> idx2 only when the reverse search agrees.
+// vnMatch1 / vnMatch2 are the results of orbo_search_best for the two projection passes (maxDist = TH_HIGH).
+// ---------------------------------------------------------------------------------------------------------------------
+extern "C" int orbo_sim3_cross_check(int n1, const int32_t* vnMatch1, int n2, const int32_t* vnMatch2, int32_t* out12)
+{
+    int nFound = 0;
+    for (int i1 = 0; i1 < n1; i1++) {
+        out12[i1] = -1;
+        const int idx2 = vnMatch1[i1];
+        if (idx2 >= 0 && idx2 < n2 && vnMatch2[idx2] == i1) { out12[i1] = idx2; nFound++; }
+    }
+    return nFound;
 }

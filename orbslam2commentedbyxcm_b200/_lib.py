@@ -47,6 +47,11 @@ class FeatVecView(C.Structure):
     _fields_ = [("n_nodes", C.c_int), ("node_id", C.c_void_p), ("node_start", C.c_void_p), ("node_feat", C.c_void_p)]
 
 
+class KFView(C.Structure):
+    _fields_ = [("n", C.c_int), ("x", C.c_void_p), ("y", C.c_void_p), ("octave", C.c_void_p), ("angle", C.c_void_p),
+                ("u_right", C.c_void_p), ("desc", C.c_void_p), ("has_mp", C.c_void_p), ("fv", C.POINTER(FeatVecView))]
+
+
 _vp, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
 
 # every symbol include/orbx.h declares: (restype, argtypes)
@@ -81,6 +86,11 @@ SIGNATURES = {
     "orbm_merge_partials": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]),
     "orbm_search_by_projection": (_i, [_vp, C.POINTER(FrameView), C.POINTER(MapPointView), _f, _f, _vp, _vp]),
     "orbm_search_window": (_i, [_vp, C.POINTER(FrameView), _vp, C.POINTER(WindowQueryView), _i, _i, _f, _i, _vp, _vp]),
+    "orbm_search_best": (_i, [_vp, C.POINTER(FrameView), C.POINTER(WindowQueryView), _i, _vp, _i, _vp, _vp]),
+    "orbm_search_by_sim3": (_i, [_vp, C.POINTER(FrameView), C.POINTER(WindowQueryView), C.POINTER(FrameView),
+                                 C.POINTER(WindowQueryView), _vp, _vp]),
+    "orbm_search_for_initialization": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, C.POINTER(FrameView), _vp, _i, _f, _i, _vp, _vp]),
+    "orbm_search_for_triangulation": (_i, [_vp, C.POINTER(KFView), C.POINTER(KFView), _vp, _f, _f, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "orbm_stereo_rows": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _f, _f, _vp, _vp]),
     "orbm_stereo_match": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp]),
     "orbm_search_by_bow_kf": (_i, [_vp, _i, _vp, _vp, _vp, C.POINTER(FeatVecView), _i, _vp, _vp, _vp, C.POINTER(FeatVecView), _f, _i, _vp, _vp]),

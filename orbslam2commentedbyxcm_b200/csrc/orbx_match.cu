@@ -731,6 +731,307 @@ __global__ void k_bow_scatter12(int n2, const int32_t* __restrict__ match21, int
     if (i2 < n2 && match21[i2] >= 0) out12[match21[i2]] = i2;
 }
 
+
+// ------------------------------------------------------------------------------------------------------
+// K7e: claim-free windowed search -- Fuse(KF, MapPoints, th) src/ORBmatcher.cc:1067-1222 (gate 1: reprojection chi2),
+// Fuse(KF, Scw, ...) :1225-1357 and the two passes of SearchBySim3 :1361-1602 (gate 0).  One warp per query, one lane
+// per grid cell of KeyFrame::GetFeaturesInArea's window (src/KeyFrame.cc:623-658); first minimum in visiting order.
+// ------------------------------------------------------------------------------------------------------
+struct BestArgs {
+    const float* kx; const float* ky; const int32_t* koct; const float* uright; const uint8_t* kdesc;
+    const int32_t* cellStart; const int32_t* cellItems;
+    float minX, minY, wInv, hInv;
+    int nq;
+    const float* qx; const float* qy; const float* qr; const int32_t* qmin; const int32_t* qmax; const float* qxr;
+    const uint8_t* qvalid; const uint8_t* qdesc;
+    int gate, maxDist;
+    const float* invSigma2;
+    int32_t* bestIdx; int32_t* bestDist;
+};
+
+__global__ void __launch_bounds__(256) k_search_best(BestArgs A)
+{
+    const int lane = threadIdx.x & 31;
+    const int m = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (m >= A.nq) return;
+    int outIdx = -1, outDist = 256;
+    if (A.qvalid[m]) {
+        const float rr = A.qr[m], u = A.qx[m], v = A.qy[m];
+        const int c0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(u, A.minX), rr), A.wInv)));
+        const int c1 = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(u, A.minX), rr), A.wInv)));
+        const int r0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(v, A.minY), rr), A.hInv)));
+        const int r1 = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(v, A.minY), rr), A.hInv)));
+        if (c0 < GRID_COLS && c1 >= 0 && r0 < GRID_ROWS && r1 >= 0) {
+            const int minLevel = A.qmin[m], maxLevel = A.qmax[m];
+            const Desc D = load_desc(A.qdesc + 32 * (size_t)m);
+            const float ur = A.qxr ? A.qxr[m] : 0.f;
+            uint32_t bestKey = 0xFFFFFFFFu;
+            int best = -1;
+            const int nr = r1 - r0 + 1, ncell = (c1 - c0 + 1) * nr;
+            for (int qc = lane; qc < ncell; qc += 32) {
+                const int ix = c0 + qc / nr, iy = r0 + qc % nr;
+                const int c = ix * GRID_ROWS + iy;
+                const int s = A.cellStart[c], e = A.cellStart[c + 1];
+                for (int k = s; k < e; k++) {
+                    const int idx = A.cellItems[k];
+                    const float kpx = A.kx[idx], kpy = A.ky[idx];
+                    if (!(fabsf(__fsub_rn(kpx, u)) < rr && fabsf(__fsub_rn(kpy, v)) < rr)) continue;
+                    const int oct = A.koct[idx];
+                    if (oct < minLevel || oct > maxLevel) continue;
+                    if (A.gate == 1) {
+                        const float ex = __fsub_rn(u, kpx), ey = __fsub_rn(v, kpy);
+                        float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                        const float kpr = A.uright ? A.uright[idx] : -1.f;
+                        double lim = 5.99;
+                        if (kpr >= 0) {
+                            const float er = __fsub_rn(ur, kpr);
+                            e2 = __fadd_rn(e2, __fmul_rn(er, er));
+                            lim = 7.8;
+                        }
+                        if ((double)__fmul_rn(e2, A.invSigma2[oct]) > lim) continue;
+                    }
+                    const int dist = hamming(D, load_desc(A.kdesc + 32 * (size_t)idx));
+                    const uint32_t key = ((uint32_t)dist << 23) | ((uint32_t)qc << 11) | (uint32_t)(k - s);
+                    if (key < bestKey) { bestKey = key; best = idx; }
+                }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const uint32_t ok = __shfl_xor_sync(0xffffffffu, bestKey, o);
+                const int ob = __shfl_xor_sync(0xffffffffu, best, o);
+                if (ok < bestKey) { bestKey = ok; best = ob; }
+            }
+            if (best >= 0) {
+                outDist = (int)(bestKey >> 23);
+                if (outDist <= A.maxDist) outIdx = best;
+            }
+        }
+    }
+    if (lane == 0) { A.bestIdx[m] = outIdx; A.bestDist[m] = outDist; }
+}
+
+
+// ------------------------------------------------------------------------------------------------------
+// K7f: SearchForInitialization src/ORBmatcher.cc:539-683.  The reference loop is sequential in i1: a candidate i2 is
+// skipped when an EARLIER F1 feature already holds it with a distance <= this one (vMatchedDistance), and a later,
+// better match steals it.  result(i1) depends only on the results of j < i1, so -- as in k_proj_search -- the
+// sequential answer is the unique fixed point of "recompute every i1 against the previous sweep's results".  One CTA
+// (the problem is a few hundred level-0 features x ~50 candidates), one warp per i1, one lane per grid cell; the
+// previous sweep's accepted matches hang off their F2 feature as linked lists (head / next).
+// ------------------------------------------------------------------------------------------------------
+struct InitArgs {
+    int n1; const int32_t* oct1; const float* angle1; const uint8_t* desc1; const float* prevx; const float* prevy;
+    int n2; const float* kx; const float* ky; const int32_t* koct; const float* kangle; const uint8_t* kdesc;
+    const int32_t* cellStart; const int32_t* cellItems;
+    float minX, minY, wInv, hInv, window, nnratio;
+    int checkOri;
+    int32_t* resA; int32_t* resB;   // [n1] accepted F2 feature or -1 (double buffered across sweeps)
+    int32_t* distA; int32_t* distB; // [n1] Hamming distance of the accepted match
+    int32_t* head; int32_t* next;   // [n2], [n1]
+    int32_t* out12; int* nmatches; int* sweeps;
+};
+
+__device__ int init_one(const InitArgs& A, int i1, const int32_t* distPrev, int lane, int* distOut)
+{
+    if (A.oct1[i1] > 0) return -1;
+    const float rr = A.window, x = A.prevx[i1], y = A.prevy[i1];
+    const int c0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, A.minX), rr), A.wInv)));
+    if (c0 >= GRID_COLS) return -1;
+    const int c1 = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, A.minX), rr), A.wInv)));
+    if (c1 < 0) return -1;
+    const int r0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, A.minY), rr), A.hInv)));
+    if (r0 >= GRID_ROWS) return -1;
+    const int r1 = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, A.minY), rr), A.hInv)));
+    if (r1 < 0) return -1;
+    const Desc D = load_desc(A.desc1 + 32 * (size_t)i1);
+    Top2 t;
+    top2_init(t);
+    const int nr = r1 - r0 + 1, ncell = (c1 - c0 + 1) * nr;
+    for (int qc = lane; qc < ncell; qc += 32) {
+        const int ix = c0 + qc / nr, iy = r0 + qc % nr;
+        const int c = ix * GRID_ROWS + iy;
+        const int s = A.cellStart[c], e = A.cellStart[c + 1];
+        for (int k = s; k < e; k++) {
+            const int i2 = A.cellItems[k];
+            if (A.koct[i2] != 0) continue;
+            if (!(fabsf(__fsub_rn(A.kx[i2], x)) < rr && fabsf(__fsub_rn(A.ky[i2], y)) < rr)) continue;
+            const int d = hamming(D, load_desc(A.kdesc + 32 * (size_t)i2));
+            bool blocked = false;  // vMatchedDistance[i2] <= dist, as left by the features j < i1
+            for (int j = A.head[i2]; j >= 0; j = A.next[j])
+                if (j < i1 && distPrev[j] <= d) { blocked = true; break; }
+            if (blocked) continue;
+            top2_push(t, ((uint32_t)d << 23) | ((uint32_t)qc << 11) | (uint32_t)(k - s), i2);
+        }
+    }
+    top2_warp_reduce(t);
+    if (t.p1 < 0) return -1;
+    const int bestDist = t.k1 >> 23;
+    const int bestDist2 = t.p2 >= 0 ? (int)(t.k2 >> 23) : 0x7fffffff;
+    if (bestDist > TH_LOW) return -1;
+    if (!((float)bestDist < __fmul_rn((float)bestDist2, A.nnratio))) return -1;
+    *distOut = bestDist;
+    return t.p1;
+}
+
+__global__ void __launch_bounds__(1024) k_init_search(InitArgs A)
+{
+    __shared__ int changed;
+    __shared__ int hist[HISTO_LENGTH];
+    __shared__ int keepBin[HISTO_LENGTH];
+    __shared__ int total;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    int32_t* resPrev = A.resA;
+    int32_t* resNext = A.resB;
+    int32_t* distPrev = A.distA;
+    int32_t* distNext = A.distB;
+    for (int i = tid; i < A.n2; i += blockDim.x) A.head[i] = -1;
+    for (int i = tid; i < A.n1; i += blockDim.x) { resPrev[i] = -1; A.next[i] = -1; distPrev[i] = 0; }
+    if (tid < HISTO_LENGTH) hist[tid] = 0;
+    if (tid == 0) total = 0;
+    __syncthreads();
+    int sweep = 0;
+    for (;; sweep++) {
+        if (tid == 0) changed = 0;
+        __syncthreads();
+        for (int i1 = warp; i1 < A.n1; i1 += nwarps) {
+            int d = 0;
+            const int r = init_one(A, i1, distPrev, lane, &d);
+            if (lane == 0) {
+                resNext[i1] = r;
+                distNext[i1] = d;
+                if (r != resPrev[i1]) changed = 1;
+            }
+        }
+        __syncthreads();
+        if (!changed) break;
+        for (int i = tid; i < A.n2; i += blockDim.x) A.head[i] = -1;
+        __syncthreads();
+        for (int j = tid; j < A.n1; j += blockDim.x) {
+            const int r = resNext[j];
+            A.next[j] = r >= 0 ? atomicExch(&A.head[r], j) : -1;
+        }
+        __syncthreads();
+        int32_t* t = resPrev; resPrev = resNext; resNext = t;
+        t = distPrev; distPrev = distNext; distNext = t;
+    }
+    // resNext == resPrev == the sequential result.  vnMatches21[i2] = the LAST accepted i1 (later matches steal).
+    for (int i = tid; i < A.n2; i += blockDim.x) A.head[i] = -1;
+    __syncthreads();
+    for (int j = tid; j < A.n1; j += blockDim.x) {
+        const int r = resNext[j];
+        if (r >= 0) {
+            atomicMax(&A.head[r], j);
+            if (A.checkOri) atomicAdd(&hist[rot_bin(A.angle1[j], A.kangle[r])], 1);   // stolen matches stay in rotHist
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            const int sN = hist[i];
+            if (sN > max1) { max3 = max2; max2 = max1; max1 = sN; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (sN > max2) { max3 = max2; max2 = sN; ind3 = ind2; ind2 = i; }
+            else if (sN > max3) { max3 = sN; ind3 = i; }
+        }
+        if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+        else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) ind3 = -1;
+        for (int i = 0; i < HISTO_LENGTH; i++) keepBin[i] = !A.checkOri || (i == ind1 || i == ind2 || i == ind3);
+    }
+    __syncthreads();
+    int mine = 0;
+    for (int j = tid; j < A.n1; j += blockDim.x) {
+        const int r = resNext[j];
+        int o = -1;
+        if (r >= 0 && A.head[r] == j && keepBin[A.checkOri ? rot_bin(A.angle1[j], A.kangle[r]) : 0]) { o = r; mine++; }
+        A.out12[j] = o;
+    }
+    if (mine) atomicAdd(&total, mine);
+    __syncthreads();
+    if (tid == 0) { *A.nmatches = total; *A.sweeps = sweep + 1; }
+}
+
+
+// ------------------------------------------------------------------------------------------------------
+// K7g: SearchForTriangulation src/ORBmatcher.cc:850-1056 (+ CheckDistEpipolarLine :186-213).  As in SearchByBoW the
+// vbMatched2 claims only couple features of the same vocabulary node: one warp per shared node walks KF1's features in
+// order, lanes scan KF2's.  `dist > bestDist` skips, so among the candidates passing the gates the minimum distance
+// wins and ties go to the LAST one: key = dist << 20 | (0xFFFFF - position).
+// ------------------------------------------------------------------------------------------------------
+struct TriArgs {
+    const float* x1; const float* y1; const float* angle1; const float* ur1; const uint8_t* desc1; const uint8_t* hasMp1;
+    int nNodes1; const int32_t* nodeId1; const int32_t* nodeStart1; const int32_t* nodeFeat1;
+    const float* x2; const float* y2; const int32_t* oct2; const float* angle2; const float* ur2; const uint8_t* desc2;
+    const uint8_t* hasMp2;
+    int nNodes2; const int32_t* nodeId2; const int32_t* nodeStart2; const int32_t* nodeFeat2;
+    float F[9];
+    float ex, ey;
+    const float* scale2; const float* sigma2_2;
+    int onlyStereo;
+    int32_t* matched2;  // [n2] 0/1
+    int32_t* out12;     // [n1]
+    int32_t* binOf;     // [n1]
+};
+
+__global__ void __launch_bounds__(128) k_triang_nodes(TriArgs A)
+{
+    const int lane = threadIdx.x & 31;
+    const int a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (a >= A.nNodes1) return;
+    const int id = A.nodeId1[a];
+    int lo = 0, hi = A.nNodes2;
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (A.nodeId2[mid] < id) lo = mid + 1; else hi = mid; }
+    if (lo >= A.nNodes2 || A.nodeId2[lo] != id) return;
+    const int fs = A.nodeStart2[lo], fe = A.nodeStart2[lo + 1];
+    for (int ik = A.nodeStart1[a]; ik < A.nodeStart1[a + 1]; ik++) {
+        const int idx1 = A.nodeFeat1[ik];
+        if (A.hasMp1[idx1]) continue;
+        const bool bStereo1 = A.ur1[idx1] >= 0;
+        if (A.onlyStereo && !bStereo1) continue;
+        const Desc D = load_desc(A.desc1 + 32 * (size_t)idx1);
+        // epipolar line of kp1 in image 2: l = x1^T F12
+        const float px = A.x1[idx1], py = A.y1[idx1];
+        const float la = __fadd_rn(__fadd_rn(__fmul_rn(px, A.F[0]), __fmul_rn(py, A.F[3])), A.F[6]);
+        const float lb = __fadd_rn(__fadd_rn(__fmul_rn(px, A.F[1]), __fmul_rn(py, A.F[4])), A.F[7]);
+        const float lc = __fadd_rn(__fadd_rn(__fmul_rn(px, A.F[2]), __fmul_rn(py, A.F[5])), A.F[8]);
+        const float den = __fadd_rn(__fmul_rn(la, la), __fmul_rn(lb, lb));
+        uint32_t bestKey = 0xFFFFFFFFu;
+        int best = -1;
+        for (int jf = fs + lane; jf < fe; jf += 32) {
+            const int idx2 = A.nodeFeat2[jf];
+            if (A.matched2[idx2] || A.hasMp2[idx2]) continue;
+            const bool bStereo2 = A.ur2[idx2] >= 0;
+            if (A.onlyStereo && !bStereo2) continue;
+            const int dist = hamming(D, load_desc(A.desc2 + 32 * (size_t)idx2));
+            if (dist > TH_LOW) continue;
+            const float qx = A.x2[idx2], qy = A.y2[idx2];
+            const int oct = A.oct2[idx2];
+            if (!bStereo1 && !bStereo2) {
+                const float dex = __fsub_rn(A.ex, qx), dey = __fsub_rn(A.ey, qy);
+                if (__fadd_rn(__fmul_rn(dex, dex), __fmul_rn(dey, dey)) < __fmul_rn(100.0f, A.scale2[oct])) continue;
+            }
+            const float num = __fadd_rn(__fadd_rn(__fmul_rn(la, qx), __fmul_rn(lb, qy)), lc);
+            if (den == 0) continue;
+            const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+            if (!((double)dsqr < 3.84 * (double)A.sigma2_2[oct])) continue;
+            const uint32_t key = ((uint32_t)dist << 20) | (0xFFFFFu - (uint32_t)(jf - fs));
+            if (key < bestKey) { bestKey = key; best = idx2; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const uint32_t ok = __shfl_xor_sync(0xffffffffu, bestKey, o);
+            const int ob = __shfl_xor_sync(0xffffffffu, best, o);
+            if (ok < bestKey) { bestKey = ok; best = ob; }
+        }
+        if (best >= 0 && lane == 0) {
+            A.out12[idx1] = best;
+            A.matched2[best] = 1;
+            A.binOf[idx1] = rot_bin(A.angle1[idx1], A.angle2[best]);
+        }
+        __syncwarp();
+        __threadfence_block();
+    }
+}
+
 }  // namespace orbx
 
 using namespace orbx;
@@ -1288,6 +1589,237 @@ int orbm_search_by_bow_kf(orbm_context* m, int n1, const uint8_t* desc1, const f
     k_bow_scatter12<<<(n2 + 255) / 256, 256, 0, m->stream>>>(n2, (int32_t*)(A + o21), (int32_t*)(A + o12));
     ORBX_CUDA_TRY(cudaGetLastError());
     ORBX_CUDA_TRY(cudaMemcpyAsync(out_match12, A + o12, 4 * (size_t)n1, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(nmatches, A + oN, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    return ORBX_OK;
+}
+
+
+// uploads one frame view + query view, launches k_search_best, queues the D2H of the results (no synchronisation)
+static int search_best_enqueue(orbm_context* m, const char* who, const orbm_frame_view* f, const orbm_window_query_view* q,
+                               int gate, const float* inv_level_sigma2, int max_dist, int32_t* best_idx, int32_t* best_dist)
+{
+    const int nkp = f->n, nq = q->n;
+    const int ncell = GRID_COLS * GRID_ROWS;
+    const int nitems = f->cell_start[ncell];
+    for (int ci = 0; ci < ncell; ci++)
+        if (f->cell_start[ci + 1] - f->cell_start[ci] >= 2048) {
+            set_error("%s: a grid cell holds %d keypoints (limit 2047)", who, f->cell_start[ci + 1] - f->cell_start[ci]);
+            return ORBX_ERR_BAD_ARG;
+        }
+    const int nlev = std::max(f->nlevels, 1);
+    Carver c;
+    const size_t oKx = c.take(4 * (size_t)nkp), oKy = c.take(4 * (size_t)nkp), oKo = c.take(4 * (size_t)nkp),
+                 oUr = c.take(4 * (size_t)nkp), oKd = c.take(32 * (size_t)nkp), oCs = c.take(4 * (size_t)(ncell + 1)),
+                 oCi = c.take(4 * (size_t)std::max(nitems, 1)), oSig = c.take(4 * (size_t)nlev);
+    const size_t oPx = c.take(4 * (size_t)nq), oPy = c.take(4 * (size_t)nq), oPxr = c.take(4 * (size_t)nq),
+                 oPr = c.take(4 * (size_t)nq), oPmin = c.take(4 * (size_t)nq), oPmax = c.take(4 * (size_t)nq),
+                 oPva = c.take(nq), oPd = c.take(32 * (size_t)nq), oBi = c.take(4 * (size_t)nq), oBd = c.take(4 * (size_t)nq);
+    int rc = ensure_arena(m, c.off);
+    if (rc != ORBX_OK) return rc;
+    char* A = m->arena;
+#define UP(off, ptr, count, T) if ((rc = up<T>(m, (T*)(A + off), ptr, count)) != ORBX_OK) return rc
+    UP(oKx, f->x, nkp, float); UP(oKy, f->y, nkp, float); UP(oKo, f->octave, nkp, int32_t);
+    if (f->u_right) UP(oUr, f->u_right, nkp, float);
+    UP(oKd, f->desc, 32 * (size_t)nkp, uint8_t);
+    UP(oCs, f->cell_start, ncell + 1, int32_t); UP(oCi, f->cell_items, nitems, int32_t);
+    if (gate == 1) UP(oSig, inv_level_sigma2, f->nlevels, float);
+    UP(oPx, q->x, nq, float); UP(oPy, q->y, nq, float);
+    if (q->xr) UP(oPxr, q->xr, nq, float);
+    UP(oPr, q->radius, nq, float); UP(oPmin, q->min_level, nq, int32_t); UP(oPmax, q->max_level, nq, int32_t);
+    UP(oPva, q->valid, nq, uint8_t); UP(oPd, q->desc, 32 * (size_t)nq, uint8_t);
+#undef UP
+    BestArgs a;
+    a.kx = (float*)(A + oKx); a.ky = (float*)(A + oKy); a.koct = (int32_t*)(A + oKo);
+    a.uright = f->u_right ? (float*)(A + oUr) : nullptr;
+    a.kdesc = (uint8_t*)(A + oKd); a.cellStart = (int32_t*)(A + oCs); a.cellItems = (int32_t*)(A + oCi);
+    a.minX = f->min_x; a.minY = f->min_y; a.wInv = f->grid_w_inv; a.hInv = f->grid_h_inv;
+    a.nq = nq;
+    a.qx = (float*)(A + oPx); a.qy = (float*)(A + oPy); a.qr = (float*)(A + oPr); a.qmin = (int32_t*)(A + oPmin);
+    a.qmax = (int32_t*)(A + oPmax); a.qxr = q->xr ? (float*)(A + oPxr) : nullptr;
+    a.qvalid = (uint8_t*)(A + oPva); a.qdesc = (uint8_t*)(A + oPd);
+    a.gate = gate; a.maxDist = max_dist; a.invSigma2 = (float*)(A + oSig);
+    a.bestIdx = (int32_t*)(A + oBi); a.bestDist = (int32_t*)(A + oBd);
+    k_search_best<<<(nq + 7) / 8, 256, 0, m->stream>>>(a);
+    ORBX_CUDA_TRY(cudaGetLastError());
+    ORBX_CUDA_TRY(cudaMemcpyAsync(best_idx, a.bestIdx, 4 * (size_t)nq, cudaMemcpyDeviceToHost, m->stream));
+    if (best_dist) ORBX_CUDA_TRY(cudaMemcpyAsync(best_dist, a.bestDist, 4 * (size_t)nq, cudaMemcpyDeviceToHost, m->stream));
+    return ORBX_OK;
+}
+
+static bool best_args_ok(const orbm_frame_view* f, const orbm_window_query_view* q, int gate, const float* sig)
+{
+    if (!f || !q || f->n < 0 || q->n < 0) return false;
+    if (f->n > 0 && (!f->x || !f->y || !f->octave || !f->desc || !f->cell_start || !f->cell_items)) return false;
+    if (q->n > 0 && (!q->x || !q->y || !q->radius || !q->min_level || !q->max_level || !q->valid || !q->desc)) return false;
+    if (gate != 0 && gate != 1) return false;
+    if (gate == 1 && (!sig || f->nlevels <= 0 || (f->u_right && !q->xr))) return false;
+    return true;
+}
+
+int orbm_search_best(orbm_context* m, const orbm_frame_view* f, const orbm_window_query_view* q, int gate,
+                     const float* inv_level_sigma2, int max_dist, int32_t* best_idx, int32_t* best_dist)
+{
+    if (!m || !best_idx || !best_args_ok(f, q, gate, inv_level_sigma2)) {
+        set_error("orbm_search_best: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    if (q->n == 0) return ORBX_OK;
+    if (f->n == 0) {
+        for (int i = 0; i < q->n; i++) { best_idx[i] = -1; if (best_dist) best_dist[i] = 256; }
+        return ORBX_OK;
+    }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    int rc = search_best_enqueue(m, "orbm_search_best", f, q, gate, inv_level_sigma2, max_dist, best_idx, best_dist);
+    if (rc != ORBX_OK) return rc;
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    return ORBX_OK;
+}
+
+int orbm_search_by_sim3(orbm_context* m, const orbm_frame_view* kf1, const orbm_window_query_view* q2_in_1,
+                        const orbm_frame_view* kf2, const orbm_window_query_view* q1_in_2, int32_t* out_match12, int* nfound)
+{
+    if (!m || !out_match12 || !nfound || !best_args_ok(kf1, q2_in_1, 0, nullptr) || !best_args_ok(kf2, q1_in_2, 0, nullptr) ||
+        q1_in_2->n != kf1->n || q2_in_1->n != kf2->n) {
+        set_error("orbm_search_by_sim3: bad argument (q1_in_2 needs one entry per KF1 feature, q2_in_1 one per KF2 feature)");
+        return ORBX_ERR_BAD_ARG;
+    }
+    const int n1 = kf1->n, n2 = kf2->n;
+    *nfound = 0;
+    for (int i = 0; i < n1; i++) out_match12[i] = -1;
+    if (n1 == 0 || n2 == 0) return ORBX_OK;
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    std::vector<int32_t> vnMatch1(n1), vnMatch2(n2);
+    int rc = search_best_enqueue(m, "orbm_search_by_sim3", kf2, q1_in_2, 0, nullptr, TH_HIGH, vnMatch1.data(), nullptr);
+    if (rc != ORBX_OK) return rc;
+    rc = search_best_enqueue(m, "orbm_search_by_sim3", kf1, q2_in_1, 0, nullptr, TH_HIGH, vnMatch2.data(), nullptr);
+    if (rc != ORBX_OK) return rc;
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    // agreement check, src/ORBmatcher.cc:1585-1602
+    int found = 0;
+    for (int i1 = 0; i1 < n1; i1++) {
+        const int idx2 = vnMatch1[i1];
+        if (idx2 >= 0 && vnMatch2[idx2] == i1) { out_match12[i1] = idx2; found++; }
+    }
+    *nfound = found;
+    return ORBX_OK;
+}
+
+
+int orbm_search_for_initialization(orbm_context* m, int n1, const int32_t* octave1, const float* angle1, const uint8_t* desc1,
+                                   const float* prev_x, const float* prev_y, const orbm_frame_view* f2, const float* f2_angle,
+                                   int window_size, float nnratio, int check_orientation, int32_t* out_match12, int* nmatches)
+{
+    if (!m || n1 < 0 || !f2 || f2->n < 0 || !out_match12 || !nmatches ||
+        (n1 > 0 && (!octave1 || !desc1 || !prev_x || !prev_y)) || (check_orientation && n1 > 0 && f2->n > 0 && (!angle1 || !f2_angle))) {
+        set_error("orbm_search_for_initialization: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    const int n2 = f2->n;
+    *nmatches = 0;
+    for (int i = 0; i < n1; i++) out_match12[i] = -1;
+    if (n1 == 0 || n2 == 0) return ORBX_OK;
+    const int ncell = GRID_COLS * GRID_ROWS;
+    const int nitems = f2->cell_start[ncell];
+    for (int ci = 0; ci < ncell; ci++)
+        if (f2->cell_start[ci + 1] - f2->cell_start[ci] >= 2048) {
+            set_error("orbm_search_for_initialization: a grid cell holds %d keypoints (limit 2047)", f2->cell_start[ci + 1] - f2->cell_start[ci]);
+            return ORBX_ERR_BAD_ARG;
+        }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    Carver c;
+    const size_t o1o = c.take(4 * (size_t)n1), o1a = c.take(4 * (size_t)n1), o1d = c.take(32 * (size_t)n1), o1x = c.take(4 * (size_t)n1),
+                 o1y = c.take(4 * (size_t)n1);
+    const size_t oKx = c.take(4 * (size_t)n2), oKy = c.take(4 * (size_t)n2), oKo = c.take(4 * (size_t)n2), oKa = c.take(4 * (size_t)n2),
+                 oKd = c.take(32 * (size_t)n2), oCs = c.take(4 * (size_t)(ncell + 1)), oCi = c.take(4 * (size_t)std::max(nitems, 1));
+    const size_t oRa = c.take(4 * (size_t)n1), oRb = c.take(4 * (size_t)n1), oDa = c.take(4 * (size_t)n1), oDb = c.take(4 * (size_t)n1),
+                 oHead = c.take(4 * (size_t)n2), oNext = c.take(4 * (size_t)n1), oOut = c.take(4 * (size_t)n1), oMisc = c.take(64);
+    int rc = ensure_arena(m, c.off);
+    if (rc != ORBX_OK) return rc;
+    char* A = m->arena;
+#define UP(off, ptr, count, T) if ((rc = up<T>(m, (T*)(A + off), ptr, count)) != ORBX_OK) return rc
+    UP(o1o, octave1, n1, int32_t); UP(o1d, desc1, 32 * (size_t)n1, uint8_t); UP(o1x, prev_x, n1, float); UP(o1y, prev_y, n1, float);
+    if (check_orientation) { UP(o1a, angle1, n1, float); UP(oKa, f2_angle, n2, float); }
+    UP(oKx, f2->x, n2, float); UP(oKy, f2->y, n2, float); UP(oKo, f2->octave, n2, int32_t); UP(oKd, f2->desc, 32 * (size_t)n2, uint8_t);
+    UP(oCs, f2->cell_start, ncell + 1, int32_t); UP(oCi, f2->cell_items, nitems, int32_t);
+#undef UP
+    InitArgs a;
+    a.n1 = n1; a.oct1 = (int32_t*)(A + o1o); a.angle1 = (float*)(A + o1a); a.desc1 = (uint8_t*)(A + o1d);
+    a.prevx = (float*)(A + o1x); a.prevy = (float*)(A + o1y);
+    a.n2 = n2; a.kx = (float*)(A + oKx); a.ky = (float*)(A + oKy); a.koct = (int32_t*)(A + oKo); a.kangle = (float*)(A + oKa);
+    a.kdesc = (uint8_t*)(A + oKd); a.cellStart = (int32_t*)(A + oCs); a.cellItems = (int32_t*)(A + oCi);
+    a.minX = f2->min_x; a.minY = f2->min_y; a.wInv = f2->grid_w_inv; a.hInv = f2->grid_h_inv;
+    a.window = (float)window_size; a.nnratio = nnratio; a.checkOri = check_orientation ? 1 : 0;
+    a.resA = (int32_t*)(A + oRa); a.resB = (int32_t*)(A + oRb); a.distA = (int32_t*)(A + oDa); a.distB = (int32_t*)(A + oDb);
+    a.head = (int32_t*)(A + oHead); a.next = (int32_t*)(A + oNext); a.out12 = (int32_t*)(A + oOut);
+    a.nmatches = (int*)(A + oMisc); a.sweeps = a.nmatches + 1;
+    k_init_search<<<1, 1024, 0, m->stream>>>(a);
+    ORBX_CUDA_TRY(cudaGetLastError());
+    ORBX_CUDA_TRY(cudaMemcpyAsync(out_match12, a.out12, 4 * (size_t)n1, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(nmatches, a.nmatches, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    return ORBX_OK;
+}
+
+int orbm_search_for_triangulation(orbm_context* m, const orbm_kf_view* kf1, const orbm_kf_view* kf2, const float* F12, float ex,
+                                  float ey, const float* scale_factors2, const float* level_sigma2_2, int nlevels2,
+                                  int only_stereo, int check_orientation, int32_t* out_match12, int* nmatches)
+{
+    if (!m || !kf1 || !kf2 || !F12 || !scale_factors2 || !level_sigma2_2 || nlevels2 <= 0 || !out_match12 || !nmatches ||
+        kf1->n < 0 || kf2->n < 0 || !kf1->fv || !kf2->fv) {
+        set_error("orbm_search_for_triangulation: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    const int n1 = kf1->n, n2 = kf2->n;
+    *nmatches = 0;
+    for (int i = 0; i < n1; i++) out_match12[i] = -1;
+    const int nn1 = kf1->fv->n_nodes, nn2 = kf2->fv->n_nodes;
+    if (n1 == 0 || n2 == 0 || nn1 == 0 || nn2 == 0) return ORBX_OK;
+    for (int i = 0; i < n2; i++)
+        if (kf2->octave[i] < 0 || kf2->octave[i] >= nlevels2) {
+            set_error("orbm_search_for_triangulation: KF2 octave %d outside [0, %d)", kf2->octave[i], nlevels2);
+            return ORBX_ERR_BAD_ARG;
+        }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    const int nf1 = kf1->fv->node_start[nn1], nf2 = kf2->fv->node_start[nn2];
+    Carver c;
+    const size_t o1x = c.take(4 * (size_t)n1), o1y = c.take(4 * (size_t)n1), o1a = c.take(4 * (size_t)n1), o1u = c.take(4 * (size_t)n1),
+                 o1d = c.take(32 * (size_t)n1), o1m = c.take(n1), o1i = c.take(4 * (size_t)nn1), o1s = c.take(4 * (size_t)(nn1 + 1)),
+                 o1f = c.take(4 * (size_t)std::max(nf1, 1));
+    const size_t o2x = c.take(4 * (size_t)n2), o2y = c.take(4 * (size_t)n2), o2o = c.take(4 * (size_t)n2), o2a = c.take(4 * (size_t)n2),
+                 o2u = c.take(4 * (size_t)n2), o2d = c.take(32 * (size_t)n2), o2m = c.take(n2), o2i = c.take(4 * (size_t)nn2),
+                 o2s = c.take(4 * (size_t)(nn2 + 1)), o2f = c.take(4 * (size_t)std::max(nf2, 1));
+    const size_t oSc = c.take(4 * (size_t)nlevels2), oSg = c.take(4 * (size_t)nlevels2), oM2 = c.take(4 * (size_t)n2),
+                 o12 = c.take(4 * (size_t)n1), oBin = c.take(4 * (size_t)n1), oN = c.take(64);
+    int rc = ensure_arena(m, c.off);
+    if (rc != ORBX_OK) return rc;
+    char* A = m->arena;
+#define UP(off, ptr, count, T) if ((rc = up<T>(m, (T*)(A + off), ptr, count)) != ORBX_OK) return rc
+    UP(o1x, kf1->x, n1, float); UP(o1y, kf1->y, n1, float); UP(o1a, kf1->angle, n1, float); UP(o1u, kf1->u_right, n1, float);
+    UP(o1d, kf1->desc, 32 * (size_t)n1, uint8_t); UP(o1m, kf1->has_mp, n1, uint8_t);
+    UP(o1i, kf1->fv->node_id, nn1, int32_t); UP(o1s, kf1->fv->node_start, nn1 + 1, int32_t); UP(o1f, kf1->fv->node_feat, nf1, int32_t);
+    UP(o2x, kf2->x, n2, float); UP(o2y, kf2->y, n2, float); UP(o2o, kf2->octave, n2, int32_t); UP(o2a, kf2->angle, n2, float);
+    UP(o2u, kf2->u_right, n2, float); UP(o2d, kf2->desc, 32 * (size_t)n2, uint8_t); UP(o2m, kf2->has_mp, n2, uint8_t);
+    UP(o2i, kf2->fv->node_id, nn2, int32_t); UP(o2s, kf2->fv->node_start, nn2 + 1, int32_t); UP(o2f, kf2->fv->node_feat, nf2, int32_t);
+    UP(oSc, scale_factors2, nlevels2, float); UP(oSg, level_sigma2_2, nlevels2, float);
+#undef UP
+    ORBX_CUDA_TRY(cudaMemsetAsync(A + oM2, 0, 4 * (size_t)n2, m->stream));
+    ORBX_CUDA_TRY(cudaMemsetAsync(A + o12, 0xff, 4 * (size_t)n1, m->stream));
+    ORBX_CUDA_TRY(cudaMemsetAsync(A + oBin, 0, 4 * (size_t)n1, m->stream));
+    TriArgs a;
+    a.x1 = (float*)(A + o1x); a.y1 = (float*)(A + o1y); a.angle1 = (float*)(A + o1a); a.ur1 = (float*)(A + o1u);
+    a.desc1 = (uint8_t*)(A + o1d); a.hasMp1 = (uint8_t*)(A + o1m);
+    a.nNodes1 = nn1; a.nodeId1 = (int32_t*)(A + o1i); a.nodeStart1 = (int32_t*)(A + o1s); a.nodeFeat1 = (int32_t*)(A + o1f);
+    a.x2 = (float*)(A + o2x); a.y2 = (float*)(A + o2y); a.oct2 = (int32_t*)(A + o2o); a.angle2 = (float*)(A + o2a);
+    a.ur2 = (float*)(A + o2u); a.desc2 = (uint8_t*)(A + o2d); a.hasMp2 = (uint8_t*)(A + o2m);
+    a.nNodes2 = nn2; a.nodeId2 = (int32_t*)(A + o2i); a.nodeStart2 = (int32_t*)(A + o2s); a.nodeFeat2 = (int32_t*)(A + o2f);
+    for (int i = 0; i < 9; i++) a.F[i] = F12[i];
+    a.ex = ex; a.ey = ey; a.scale2 = (float*)(A + oSc); a.sigma2_2 = (float*)(A + oSg); a.onlyStereo = only_stereo ? 1 : 0;
+    a.matched2 = (int32_t*)(A + oM2); a.out12 = (int32_t*)(A + o12); a.binOf = (int32_t*)(A + oBin);
+    k_triang_nodes<<<(nn1 + 3) / 4, 128, 0, m->stream>>>(a);
+    k_bow_rotation<<<1, 256, 0, m->stream>>>(n1, a.out12, a.binOf, check_orientation, (int*)(A + oN));
+    ORBX_CUDA_TRY(cudaGetLastError());
+    ORBX_CUDA_TRY(cudaMemcpyAsync(out_match12, a.out12, 4 * (size_t)n1, cudaMemcpyDeviceToHost, m->stream));
     ORBX_CUDA_TRY(cudaMemcpyAsync(nmatches, A + oN, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
     ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
     return ORBX_OK;

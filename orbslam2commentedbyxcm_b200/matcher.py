@@ -271,3 +271,127 @@ class ORBmatcher:
             C.byref(kv), nf, _p(arr(fr["desc"], np.uint8)), _p(arr(fr["angle"], np.float32)), C.byref(fv),
             self.mfNNratio, int(self.mbCheckOrientation), out.ctypes.data, C.byref(nm)), "orbm_search_by_bow")
         return nm.value, out[:nf]
+
+    # ---- shared view builders for the remaining overloads ----
+    @staticmethod
+    def _frame_view(frame, keep):
+        def arr(v, dt):
+            a = np.ascontiguousarray(v, dt)
+            keep.append(a)
+            return a
+
+        fv = _lib.FrameView()
+        fv.n = len(frame["x"])
+        fv.x = _p(arr(frame["x"], np.float32)); fv.y = _p(arr(frame["y"], np.float32))
+        fv.octave = _p(arr(frame["octave"], np.int32))
+        fv.u_right = _p(arr(frame["u_right"], np.float32)) if frame.get("u_right") is not None else None
+        fv.desc = _p(arr(frame["desc"], np.uint8))
+        fv.occupied = _p(arr(frame["occupied"], np.uint8)) if frame.get("occupied") is not None else None
+        fv.cell_start = _p(arr(frame["cell_start"], np.int32)); fv.cell_items = _p(arr(frame["cell_items"], np.int32))
+        fv.min_x, fv.min_y, fv.grid_w_inv, fv.grid_h_inv = frame["min_x"], frame["min_y"], frame["w_inv"], frame["h_inv"]
+        sf = arr(frame["scale_factors"], np.float32)
+        fv.scale_factors = _p(sf); fv.nlevels = len(sf)
+        return fv
+
+    @staticmethod
+    def _query_view(q, keep):
+        def arr(v, dt):
+            a = np.ascontiguousarray(v, dt)
+            keep.append(a)
+            return a
+
+        qv = _lib.WindowQueryView()
+        qv.n = len(q["x"])
+        qv.x = _p(arr(q["x"], np.float32)); qv.y = _p(arr(q["y"], np.float32)); qv.radius = _p(arr(q["radius"], np.float32))
+        qv.min_level = _p(arr(q["min_level"], np.int32)); qv.max_level = _p(arr(q["max_level"], np.int32))
+        qv.xr = _p(arr(q["xr"], np.float32)) if q.get("xr") is not None else None
+        qv.angle = None
+        qv.valid = _p(arr(q["valid"], np.uint8)); qv.claims_block = None
+        qv.desc = _p(arr(q["desc"], np.uint8))
+        return qv
+
+    # ---- Fuse (both overloads): the claim-free search; the map mutation stays with the caller ----
+    def FuseSearch(self, kf, q, gate=1, inv_level_sigma2=None, max_dist=None):
+        """kf: frame dict of the KeyFrame; q: projected map points (x, y, xr, radius, min_level, max_level, valid, desc).
+        gate=1: Fuse(pKF, vpMapPoints, th) (chi2 gate), gate=0: Fuse(pKF, Scw, ...).  Returns (best_idx, best_dist)."""
+        keep = []
+        fv, qv = self._frame_view(kf, keep), self._query_view(q, keep)
+        sig = np.ascontiguousarray(inv_level_sigma2, np.float32) if inv_level_sigma2 is not None else None
+        nq = qv.n
+        bi = np.full(max(nq, 1), -1, np.int32)
+        bd = np.full(max(nq, 1), 256, np.int32)
+        check(self._L.orbm_search_best(self._m, C.byref(fv), C.byref(qv), int(gate), _p(sig),
+                                       self.TH_LOW if max_dist is None else int(max_dist), bi.ctypes.data, bd.ctypes.data),
+              "orbm_search_best")
+        return bi[:nq], bd[:nq]
+
+    def SearchBySim3(self, kf1, q2_in_1, kf2, q1_in_2):
+        """kf1/kf2: frame dicts; q1_in_2: KF1's map points projected into KF2 (one per KF1 feature), q2_in_1 the reverse.
+        Returns (nFound, match12)."""
+        keep = []
+        f1, f2 = self._frame_view(kf1, keep), self._frame_view(kf2, keep)
+        qa, qb = self._query_view(q2_in_1, keep), self._query_view(q1_in_2, keep)
+        out = np.full(max(f1.n, 1), -1, np.int32)
+        nf = C.c_int()
+        check(self._L.orbm_search_by_sim3(self._m, C.byref(f1), C.byref(qa), C.byref(f2), C.byref(qb), out.ctypes.data,
+                                          C.byref(nf)), "orbm_search_by_sim3")
+        return nf.value, out[: f1.n]
+
+    def SearchForInitialization(self, f1, f2, prev_matched, windowSize=10):
+        """f1: dict octave, angle, desc; f2: frame dict (+ "angle"); prev_matched: (n1, 2) float32 = vbPrevMatched.
+        Returns (nmatches, vnMatches12, updated vbPrevMatched)."""
+        keep = []
+        fv = self._frame_view(f2, keep)
+        n1 = len(f1["octave"])
+        oct1 = np.ascontiguousarray(f1["octave"], np.int32)
+        ang1 = np.ascontiguousarray(f1["angle"], np.float32)
+        d1 = np.ascontiguousarray(f1["desc"], np.uint8)
+        pm = np.ascontiguousarray(prev_matched, np.float32).reshape(-1, 2)
+        px, py = np.ascontiguousarray(pm[:, 0]), np.ascontiguousarray(pm[:, 1])
+        ang2 = np.ascontiguousarray(f2["angle"], np.float32)
+        out = np.full(max(n1, 1), -1, np.int32)
+        nm = C.c_int()
+        check(self._L.orbm_search_for_initialization(
+            self._m, n1, _p(oct1), _p(ang1), _p(d1), _p(px), _p(py), C.byref(fv), _p(ang2), int(windowSize), self.mfNNratio,
+            int(self.mbCheckOrientation), out.ctypes.data, C.byref(nm)), "orbm_search_for_initialization")
+        out = out[:n1]
+        new_prev = pm.copy()
+        ok = out >= 0
+        x2 = np.asarray(f2["x"], np.float32); y2 = np.asarray(f2["y"], np.float32)
+        new_prev[ok, 0] = x2[out[ok]]
+        new_prev[ok, 1] = y2[out[ok]]
+        return nm.value, out, new_prev
+
+    def SearchForTriangulation(self, kf1, kf2, F12, ex, ey, scale_factors2, level_sigma2_2, bOnlyStereo=False):
+        """kf1/kf2: dicts x, y, octave, angle, u_right, desc, has_mp, node_id, node_start, node_feat.
+        Returns (nmatches, match12); vMatchedPairs = [(i, match12[i]) for i where match12[i] >= 0]."""
+        keep = []
+
+        def arr(v, dt):
+            a = np.ascontiguousarray(v, dt)
+            keep.append(a)
+            return a
+
+        def kfview(d):
+            fv = _lib.FeatVecView()
+            fv.n_nodes = len(d["node_id"])
+            fv.node_id = _p(arr(d["node_id"], np.int32)); fv.node_start = _p(arr(d["node_start"], np.int32))
+            fv.node_feat = _p(arr(d["node_feat"], np.int32))
+            keep.append(fv)
+            v = _lib.KFView()
+            v.n = len(d["x"])
+            v.x = _p(arr(d["x"], np.float32)); v.y = _p(arr(d["y"], np.float32)); v.octave = _p(arr(d["octave"], np.int32))
+            v.angle = _p(arr(d["angle"], np.float32)); v.u_right = _p(arr(d["u_right"], np.float32))
+            v.desc = _p(arr(d["desc"], np.uint8)); v.has_mp = _p(arr(d["has_mp"], np.uint8))
+            v.fv = C.pointer(fv)
+            return v
+
+        v1, v2 = kfview(kf1), kfview(kf2)
+        F = arr(np.asarray(F12, np.float32).reshape(9), np.float32)
+        sf = arr(scale_factors2, np.float32); sg = arr(level_sigma2_2, np.float32)
+        out = np.full(max(v1.n, 1), -1, np.int32)
+        nm = C.c_int()
+        check(self._L.orbm_search_for_triangulation(
+            self._m, C.byref(v1), C.byref(v2), _p(F), float(ex), float(ey), _p(sf), _p(sg), len(sf), int(bool(bOnlyStereo)),
+            int(self.mbCheckOrientation), out.ctypes.data, C.byref(nm)), "orbm_search_for_triangulation")
+        return nm.value, out[: v1.n]
