@@ -61,6 +61,7 @@ struct LevelGeom {
     float scale;         // mvScaleFactor[level]
     int patchSize;       // (int)(31 * scale)
     int xTab, yTab;      // offsets into the resize coefficient tables
+    int resizeWords;     // 1: k_resize_words applies (4-column groups read within 8 source columns)
 };
 
 struct Plan {
@@ -79,8 +80,8 @@ struct Cand {  // one FAST candidate
     uint32_t ro;  // response << 24 | (0xFFFFFF - ord); ord = rank key of the reference's candidate order
 };
 
-struct FastUnit {  // one k_fast_band CTA: level, cell row, first cell column
-    short level, ci, j0, pad;
+struct FastUnit {  // one k_fast_band CTA (16 bytes, geometry precomputed on the host): level, cell row, first cell column,
+    short level, ci, j0, iniX, iniY, rh, bw, pad;  // band origin in level pixels, band rows, band width (rh, bw >= 7)
 };
 
 struct StagedKp {  // per-level keypoint between k_octree and k_describe
@@ -224,6 +225,76 @@ __global__ void __launch_bounds__(128) k_resize(Plan plan, Buffers buf, int leve
     }
 }
 
+// K1b, word variant (used when every aligned group of 4 destination columns reads source bytes that lie within 8
+// consecutive source columns, i.e. scale factors up to 2; build_plan checks the tables and sets LevelGeom::resizeWords):
+// instead of 8 byte loads per source row a thread loads the 3 aligned words covering its window, funnel-shifts them to
+// the window start and picks each column's (S[sx], S[sx+1]) pair with one PRMT (selector precomputed per thread); the
+// horizontal tap pair is one IDP.2A.  Addresses are 32-bit offsets from a CTA-uniform base.
+__global__ void __launch_bounds__(128) k_resize_words(Plan plan, Buffers buf, int level, int rowsPerThread)
+{
+    const LevelGeom& g = plan.lv[level];
+    const LevelGeom& gp = plan.lv[level - 1];
+    const int bx = 4 * (blockIdx.x * 32 + (threadIdx.x & 31));  // pitch is a multiple of 128: always inside the row
+    const int frame = blockIdx.z + buf.frameBase;
+    const int dy0 = (blockIdx.y * 4 + (threadIdx.x >> 5)) * rowsPerThread;
+    if (dy0 >= g.h) return;
+    const int dy1 = min(dy0 + rowsPerThread, g.h);
+    int sx[4], sx1[4];
+    uint32_t a[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        int dx = min(max(bx + j - PAD_LEFT, -EDGE), g.w - 1 + EDGE);
+        dx = reflect101(dx, g.w);
+        sx[j] = buf.xofs[g.xTab + dx];
+        sx1[j] = min(sx[j] + 1, gp.w - 1);
+        const short2 w = buf.xw[g.xTab + dx];
+        a[j] = (uint32_t)(unsigned short)w.x | ((uint32_t)(unsigned short)w.y << 16);
+    }
+    const int base = min(min(sx[0], sx[1]), min(sx[2], sx[3]));
+    uint32_t sel[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) sel[j] = (uint32_t)(sx[j] - base) | ((uint32_t)(sx1[j] - base) << 4);
+    const uint32_t colOff = (uint32_t)(PAD_LEFT + base) & ~3u, sh = 8u * ((uint32_t)(PAD_LEFT + base) & 3u);
+    const uint8_t* S = plane_ptr(buf.pyr, gp, frame) + (long long)PAD_TOP * gp.pitch;  // row 0 of the interior, buffer column 0
+    uint8_t* D = plane_ptr(buf.pyr, g, frame);
+    const uint32_t spitch = (uint32_t)gp.pitch, dpitch = (uint32_t)g.pitch;
+    uint32_t t0[4], t1[4];
+    int rowInT1 = -1;
+    auto hrow = [&](int r, uint32_t* t) {
+        const uint32_t* R = reinterpret_cast<const uint32_t*>(S + ((uint32_t)r * spitch + colOff));
+        const uint32_t w0 = R[0], w1 = R[1], w2 = R[2];
+        const uint32_t u0 = __funnelshift_r(w0, w1, sh), u1 = __funnelshift_r(w1, w2, sh);
+#pragma unroll
+        for (int j = 0; j < 4; j++) t[j] = __dp2a_lo(a[j], __byte_perm(u0, u1, sel[j]), 0u) >> 4;
+    };
+    for (int dy = dy0; dy < dy1; dy++) {
+        const int r0 = buf.yofs0[g.yTab + dy], r1 = buf.yofs1[g.yTab + dy];
+        const short2 b = buf.yw[g.yTab + dy];
+        if (r0 == rowInT1) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) t0[j] = t1[j];
+        } else {
+            hrow(r0, t0);
+        }
+        if (r1 == r0) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) t1[j] = t0[j];
+        } else {
+            hrow(r1, t1);
+        }
+        rowInT1 = r1;
+        const uint32_t b0 = (uint32_t)b.x << 16, b1 = (uint32_t)b.y << 16;
+        uint32_t o[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) o[j] = (__umulhi(b0, t0[j]) + __umulhi(b1, t1[j]) + 2u) >> 2;  // in [0, 255]
+        const uint32_t v = __byte_perm(__byte_perm(o[0], o[1], 0x0040), __byte_perm(o[2], o[3], 0x0040), 0x5410);
+        *reinterpret_cast<uint32_t*>(D + ((uint32_t)(PAD_TOP + dy) * dpitch + bx)) = v;
+        if (dy >= 1 && dy <= EDGE) *reinterpret_cast<uint32_t*>(D + ((uint32_t)(PAD_TOP - dy) * dpitch + bx)) = v;
+        if (dy >= g.h - 1 - EDGE && dy <= g.h - 2)
+            *reinterpret_cast<uint32_t*>(D + ((uint32_t)(PAD_TOP + 2 * (g.h - 1) - dy) * dpitch + bx)) = v;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------------
 // K2: FAST-9/16 per 30-px cell with the iniThFAST -> minThFAST retry.  One CTA per band = up to fastG horizontally
 // adjacent cells of one cell row (<= 124 px wide), 128 threads, lane = one aligned 32-bit word (4 pixels) of a row.
@@ -241,7 +312,7 @@ __global__ void __launch_bounds__(128) k_resize(Plan plan, Buffers buf, int leve
 // response ties inside a quad-tree node.
 // ------------------------------------------------------------------------------------------------------
 constexpr int FAST_T = 128;
-constexpr int FAST_P = 144;   // tile pitch in bytes: <= 124 + 6 px band + 3 alignment bytes, multiple of 16
+constexpr int FAST_P = 160;   // tile pitch in bytes: <= 124 + 6 px band + 15 alignment bytes, multiple of 16
 constexpr int FAST_P4 = FAST_P / 4;
 constexpr int FAST_MAXG = 4;
 
@@ -286,20 +357,10 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
     __shared__ int sHasIni[FAST_MAXG];
 
     const int frame = blockIdx.y + buf.frameBase;
-    const FastUnit fu = buf.fastUnits[blockIdx.x];
-    const int level = fu.level, ci = fu.ci, j0 = fu.j0;
+    const int4 fuw = __ldg(reinterpret_cast<const int4*>(buf.fastUnits) + blockIdx.x);
+    const int level = (short)(fuw.x & 0xffff), ci = fuw.x >> 16, j0 = (short)(fuw.y & 0xffff), iniX = fuw.y >> 16;
+    const int iniY = (short)(fuw.z & 0xffff), rh = fuw.z >> 16, bw = (short)(fuw.w & 0xffff);
     const LevelGeom& g = plan.lv[level];
-
-    const int iniY = 16 + ci * g.hCell, iniX = 16 + j0 * g.wCell;
-    if (iniY >= g.maxBY - 3 || iniX >= g.maxBX - 6) return;
-    const int maxY = min(iniY + g.hCell + 6, g.maxBY);
-    const int rh = maxY - iniY;
-    if (rh < 7) return;
-    int j1 = min(j0 + g.fastG - 1, g.nCols - 1);
-    while (16 + j1 * g.wCell >= g.maxBX - 6) j1--;  // cells skipped by the reference (src/ORBextractor.cc:1081)
-    const int bandEnd = min(16 + j1 * g.wCell + g.wCell + 6, g.maxBX);
-    const int bw = bandEnd - iniX;
-    if (bw < 7) return;
     const int evalW = bw - 6, eh = rh - 6;
 
     uint8_t* tile = fsm;
@@ -307,76 +368,74 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
     unsigned short* q1 = reinterpret_cast<unsigned short*>(fsm + 2 * plan.fastTileBytes);
     unsigned short* q2 = q1 + plan.fastQCap;
 
-    // stage the band with aligned 32-bit loads, zero the score tile
+    // stage the band with 16-byte asynchronous copies (16 lanes per row, 8 rows per pass), zero the score tile
     const uint8_t* interior = interior_ptr(buf.pyr, g, frame);
-    const int shift = (PAD_LEFT + iniX) & 3;
-    const int nw = (shift + bw + 3) >> 2;
-    const uint8_t* rowBase = interior + (long long)iniY * g.pitch + (iniX - shift);
+    const int shift = (PAD_LEFT + iniX) & 15;
+    const int nw16 = (shift + bw + 15) >> 4;  // <= 10
     {
-        const int ln = threadIdx.x & 31;
-        for (int r = threadIdx.x >> 5; r < rh; r += FAST_T / 32) {
-            const uint32_t* srcRow = reinterpret_cast<const uint32_t*>(rowBase + (long long)r * g.pitch);
-            uint32_t* dstRow = reinterpret_cast<uint32_t*>(tile + r * FAST_P);
-            if (ln < nw) dstRow[ln] = __ldg(srcRow + ln);
-            if (ln + 32 < nw) dstRow[ln + 32] = __ldg(srcRow + ln + 32);
+        const int c16 = threadIdx.x & 15;
+        if (c16 < nw16) {
+            const uint8_t* src = interior + (long long)iniY * g.pitch + (iniX - shift) + 16 * c16;
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(tile) + 16 * c16;
+            for (int r = threadIdx.x >> 4; r < rh; r += FAST_T / 16)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + r * FAST_P), "l"(src + (long long)r * g.pitch) : "memory");
         }
     }
     for (int idx = threadIdx.x; idx < rh * (FAST_P / 16); idx += FAST_T) reinterpret_cast<uint4*>(sc)[idx] = make_uint4(0, 0, 0, 0);
     if (threadIdx.x < FAST_MAXG) sHasIni[threadIdx.x] = 0;
     if (threadIdx.x == 0) { sQ1 = 0; sQ2 = 0; sQ3 = 0; sCnt = 0; sPos = 0; }
+    asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int minTh = plan.minTh, iniTh = plan.iniTh;
-    // ---- pass 1: SWAR rejection, 4 pixels per lane ----
+    // ---- pass 1: SWAR rejection, 4 pixels per lane; the survivors of a lane's rows are kept as 4-bit groups of a
+    //      60-bit mask and written to the queue by ONE loop per lane (one divergent region instead of one per row) ----
     {
         const int txFirst = shift + 3, txEnd = shift + 3 + evalW;  // evaluated tile columns [txFirst, txEnd)
-        const int gFirst = txFirst >> 2, nG = ((txEnd - 1) >> 2) - gFirst + 1;  // <= 32 words by construction
+        const int gFirst = txFirst >> 2;                             // ((txEnd-1)>>2) - gFirst + 1 <= 32 words
         const uint32_t K = (uint32_t)(0x7f - min(minTh, 0x7f)) * 0x01010101u;
         const bool filter = minTh < 0x80;
         const uint32_t* t32 = reinterpret_cast<const uint32_t*>(tile);
         const int gw = gFirst + lane;
-        // bytes of this word that are evaluated pixels
-        uint32_t vmask = 0;
+        uint32_t vmask = 0;  // bytes of this word that are evaluated pixels
 #pragma unroll
         for (int bb = 0; bb < 4; bb++)
-            if (lane < nG && 4 * gw + bb >= txFirst && 4 * gw + bb < txEnd) vmask |= 0x80u << (8 * bb);
+            if (4 * gw + bb >= txFirst && 4 * gw + bb < txEnd) vmask |= 0x80u << (8 * bb);
         constexpr int FAST_RPW = (59 + FAST_T / 32 - 1) / (FAST_T / 32);  // rows per warp: eh <= 59
-        uint32_t ms[FAST_RPW];  // survivor masks of this lane's rows
-        int cnt = 0;
+        static_assert(FAST_RPW <= 16, "survivor nibbles must fit 64 bits");
+        uint32_t mlo = 0, mhi = 0;
+        const uint32_t* rowp = t32 + (warp + 3) * FAST_P4 + gw;
 #pragma unroll
         for (int it = 0; it < FAST_RPW; it++) {
-            const int ty = warp + it * (FAST_T / 32) + 3;
-            uint32_t m = 0;
-            if (vmask && ty < eh + 3) {
-                const uint32_t C = t32[ty * FAST_P4 + gw];
-                const uint32_t Lw = t32[ty * FAST_P4 + gw - 1], Rw = t32[ty * FAST_P4 + gw + 1];
-                const uint32_t N = t32[(ty - 3) * FAST_P4 + gw], S = t32[(ty + 3) * FAST_P4 + gw];
-                const uint32_t W4 = __byte_perm(Lw, C, 0x4321);  // pixels x-3 .. x
-                const uint32_t E4 = __byte_perm(C, Rw, 0x6543);  // pixels x+3 .. x+6
-                if (filter) {
-                    const uint32_t an = __vabsdiffu4(C, N), as = __vabsdiffu4(C, S), aw = __vabsdiffu4(C, W4), ae = __vabsdiffu4(C, E4);
-                    // bit 7 of each byte: |d| > minTh
-                    const uint32_t gn = ((an & 0x7f7f7f7fu) + K) | an, gs = ((as & 0x7f7f7f7fu) + K) | as;
-                    const uint32_t gww = ((aw & 0x7f7f7f7fu) + K) | aw, ge = ((ae & 0x7f7f7f7fu) + K) | ae;
-                    m = (gn | gs) & (gww | ge) & vmask;
-                } else {
-                    m = vmask;
-                }
+            if (warp + it * (FAST_T / 32) >= eh) break;  // warp-uniform
+            const uint32_t* cp = rowp + it * (FAST_T / 32) * FAST_P4;
+            const uint32_t C = cp[0], Lw = cp[-1], Rw = cp[1], N = cp[-3 * FAST_P4], S = cp[3 * FAST_P4];
+            const uint32_t W4 = __byte_perm(Lw, C, 0x4321);  // pixels x-3 .. x
+            const uint32_t E4 = __byte_perm(C, Rw, 0x6543);  // pixels x+3 .. x+6
+            uint32_t m = vmask;
+            if (filter) {
+                const uint32_t an = __vabsdiffu4(C, N), as = __vabsdiffu4(C, S), aw = __vabsdiffu4(C, W4), ae = __vabsdiffu4(C, E4);
+                // bit 7 of each byte: |d| > minTh
+                const uint32_t gn = ((an & 0x7f7f7f7fu) + K) | an, gs = ((as & 0x7f7f7f7fu) + K) | as;
+                const uint32_t gww = ((aw & 0x7f7f7f7fu) + K) | aw, ge = ((ae & 0x7f7f7f7fu) + K) | ae;
+                m = (gn | gs) & (gww | ge) & vmask;
             }
-            ms[it] = m;
-            cnt += __popc(m);
+            const uint32_t nib = (m * 0x00204081u) >> 28;  // bits 7, 15, 23, 31 -> 0..3
+            if (it < 8) mlo |= nib << (4 * it); else mhi |= nib << (4 * (it - 8));
         }
+        const int cnt = __popc(mlo) + __popc(mhi);
         if (cnt) {
             int base = atomicAdd(&sQ1, cnt);
+            const uint32_t e0 = ((uint32_t)(warp + 3) << 8) | (uint32_t)(4 * gw);
 #pragma unroll
-            for (int it = 0; it < FAST_RPW; it++) {
-                uint32_t m = ms[it];
-                const int ty = warp + it * (FAST_T / 32) + 3;
+            for (int half = 0; half < 2; half++) {
+                uint32_t m = half ? mhi : mlo;
+                const uint32_t eh0 = e0 + (half ? (8u * (FAST_T / 32)) << 8 : 0u);
                 while (m) {
-                    const int bit = __ffs(m) - 1;  // 7, 15, 23 or 31
+                    const int bit = __ffs(m) - 1;
                     m &= m - 1;
-                    q1[base++] = (unsigned short)((ty << 8) | (4 * gw + (bit >> 3)));
+                    q1[base++] = (unsigned short)(eh0 + (((uint32_t)bit >> 2) * ((FAST_T / 32) << 8)) + (bit & 3));
                 }
             }
         }
@@ -1267,9 +1326,22 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
                     yw.push_back(sat_short((1.f - f) * 2048)); yw.push_back(sat_short(f * 2048));
                 }
             }
+            // k_resize_words eligibility: every aligned group of 4 buffer columns (frame columns map to the reflected
+            // destination column) must read source columns inside [base, base + 7]
+            g.resizeWords = 1;
+            for (int bx = 0; bx < g.pitch && g.resizeWords; bx += 4) {
+                int lo = 1 << 30, hi = -1;
+                for (int j = 0; j < 4; j++) {
+                    int dx = std::min(std::max(bx + j - PAD_LEFT, -EDGE), g.w - 1 + EDGE);
+                    if (dx < 0) dx = -dx;
+                    if (dx >= g.w) dx = 2 * (g.w - 1) - dx;
+                    const int sxv = xofs[g.xTab + dx];
+                    lo = std::min(lo, sxv); hi = std::max(hi, std::min(sxv + 1, gp.w - 1));
+                }
+                if (hi - lo > 7) g.resizeWords = 0;
+            }
         }
     }
-    P.totalFastUnits = fastOff;
     P.totalBlurUnits = blurOff;
     P.fastTileBytes = fastRows * FAST_P;
     P.fastQCap = align_up(fastQ + 8, 8);
@@ -1285,14 +1357,28 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
     tabs.insert(tabs.end(), y1v.begin(), y1v.end());
     tabs.insert(tabs.end(), xw.begin(), xw.end());
     tabs.insert(tabs.end(), yw.begin(), yw.end());
+    std::vector<FastUnit> units;
+    for (int l = 0; l < c.nlevels; l++) {
+        const LevelGeom& g = P.lv[l];
+        for (int i = 0; i < g.nRows; i++)
+            for (int gi = 0; gi < g.fastGroups; gi++) {
+                // band geometry: cells skipped by the reference (src/ORBextractor.cc:1064, :1081) never become units
+                const int j0 = gi * g.fastG;
+                const int iniY = 16 + i * g.hCell, iniX = 16 + j0 * g.wCell;
+                if (iniY >= g.maxBY - 3 || iniX >= g.maxBX - 6) continue;
+                const int rh = std::min(iniY + g.hCell + 6, g.maxBY) - iniY;
+                if (rh < 7) continue;
+                int j1 = std::min(j0 + g.fastG - 1, g.nCols - 1);
+                while (16 + j1 * g.wCell >= g.maxBX - 6) j1--;
+                const int bw = std::min(16 + j1 * g.wCell + g.wCell + 6, g.maxBX) - iniX;
+                if (bw < 7) continue;
+                units.push_back(FastUnit{(short)l, (short)i, (short)j0, (short)iniX, (short)iniY, (short)rh, (short)bw, 0});
+            }
+    }
+    P.totalFastUnits = (int)units.size();
     if (ti) {
         ti->nx = (long long)xofs.size(); ti->ny = (long long)y0v.size(); ti->nxw = (long long)xw.size(); ti->nyw = (long long)yw.size();
-        ti->units.clear();
-        for (int l = 0; l < c.nlevels; l++) {
-            const LevelGeom& g = P.lv[l];
-            for (int i = 0; i < g.nRows; i++)
-                for (int gi = 0; gi < g.fastGroups; gi++) ti->units.push_back(FastUnit{(short)l, (short)i, (short)(gi * g.fastG), 0});
-        }
+        ti->units.swap(units);
     }
     P.pyrFrameStride = pyrBytesPerFrame;
     return ORBX_OK;
@@ -1410,7 +1496,8 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
         int rpt = 16;
         while (rpt > 4 && (long long)(g.pitch / 4) * ((g.h + rpt - 1) / rpt) * n < 148LL * 2048) rpt >>= 1;
         dim3 grid(g.pitch / 128, (g.h + 4 * rpt - 1) / (4 * rpt), n);
-        k_resize<<<grid, 128, 0, s>>>(P, B, l, rpt);
+        if (g.resizeWords) k_resize_words<<<grid, 128, 0, s>>>(P, B, l, rpt);
+        else k_resize<<<grid, 128, 0, s>>>(P, B, l, rpt);
         nl++;
     }
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_FAST], s));
