@@ -124,39 +124,40 @@ __device__ __forceinline__ const uint8_t* interior_ptr(const uint8_t* arena, con
 }
 
 // ------------------------------------------------------------------------------------------------------
-// K1a: level 0 = input image + REFLECT_101 frame.  One thread writes one aligned 16-byte chunk of a buffer row; chunks
-// inside the interior are 128-bit copies when the source row is 16-byte aligned, edge chunks go byte by byte through
-// the reflected column.
+// K1a: level 0 = input image + REFLECT_101 frame.  A CTA writes L0_ROWS buffer rows of one frame, 16 lanes per row:
+// first the interior as 128-bit copies (when the source rows are 16-byte aligned), then the few 32-bit words that hold
+// the 19-px frame (and an unaligned interior tail) byte by byte through the reflected column.  Buffer columns outside
+// [12, 32 + w + 19] are never read by any kernel and stay unwritten.
 // ------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_level0(Plan plan, Buffers buf, const uint8_t* __restrict__ in, long long inStep,
-                                                long long inFrameStride)
+constexpr int L0_ROWS = 8;
+
+__global__ void __launch_bounds__(16 * L0_ROWS) k_level0(Plan plan, Buffers buf, const uint8_t* __restrict__ in, long long inStep,
+                                                         long long inFrameStride)
 {
     const LevelGeom& g = plan.lv[0];
-    const int bx = 16 * (blockIdx.x * 128 + threadIdx.x);
-    if (bx >= g.pitch) return;
-    const int by = blockIdx.y, lframe = blockIdx.z, frame = lframe + buf.frameBase;
+    const int lframe = blockIdx.y, frame = lframe + buf.frameBase;
+    const int by = blockIdx.x * L0_ROWS + (threadIdx.x >> 4);
+    if (by >= g.planeRows) return;
+    const int l16 = threadIdx.x & 15;
     const int y = reflect101(by - PAD_TOP, g.h);
     const uint8_t* src = in + (long long)lframe * inFrameStride + (long long)y * inStep;
-    uint4 out;
-    const int x0 = bx - PAD_LEFT;
-    if (x0 >= 0 && x0 + 16 <= g.w && ((reinterpret_cast<uintptr_t>(src + x0) & 15) == 0)) {
-        out = __ldg(reinterpret_cast<const uint4*>(src + x0));
-    } else {
-        uint32_t v[4];
+    uint8_t* dst = plane_ptr(buf.pyr, g, frame) + (long long)by * g.pitch + PAD_LEFT;
+    const bool aligned = ((reinterpret_cast<uintptr_t>(in) | (uintptr_t)inStep | (uintptr_t)inFrameStride) & 15) == 0;
+    const int nfast = aligned ? g.w >> 4 : 0;
+    for (int c = l16; c < nfast; c += 16) reinterpret_cast<uint4*>(dst)[c] = __ldg(reinterpret_cast<const uint4*>(src) + c);
+    const int xr = 16 * nfast;                              // first interior column not covered by the 128-bit copies
+    const int nEdge = 5 + ((g.w - xr + EDGE + 3) >> 2);     // 5 words left of the interior, the rest from column xr on
+    for (int e = l16; e < nEdge; e += 16) {
+        const int x0 = e < 5 ? 4 * e - 20 : xr + 4 * (e - 5);
+        uint32_t wv = 0;
 #pragma unroll
-        for (int q = 0; q < 4; q++) {
-            uint32_t w = 0;
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                int x = min(max(x0 + 4 * q + j, -EDGE), g.w - 1 + EDGE);
-                x = reflect101(x, g.w);
-                w |= (uint32_t)__ldg(src + x) << (8 * j);
-            }
-            v[q] = w;
+        for (int j = 0; j < 4; j++) {
+            int x = min(max(x0 + j, -EDGE), g.w - 1 + EDGE);
+            x = reflect101(x, g.w);
+            wv |= (uint32_t)__ldg(src + x) << (8 * j);
         }
-        out = make_uint4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<uint32_t*>(dst + x0) = wv;
     }
-    *reinterpret_cast<uint4*>(plane_ptr(buf.pyr, g, frame) + (long long)by * g.pitch + bx) = out;
 }
 
 // ------------------------------------------------------------------------------------------------------
@@ -971,47 +972,50 @@ __global__ void __launch_bounds__(128) k_blur(Plan plan, Buffers buf)
     const uint8_t* src = interior_ptr(buf.pyr, g, frame) + x;
     uint8_t* dst = const_cast<uint8_t*>(interior_ptr(buf.blur, g, frame)) + x;
     const long long pitch = g.pitch;
-    // window of 8 rows (y-3 .. y+4) as 4 vertical pairs per column
+    // window of 8 rows (y-3 .. y+4) as 4 vertical pairs per column: P[k][j] = h(y-3+2k, j) | h(y-2+2k, j) << 16
     uint32_t P[4][4];
-    {
+    auto hpair = [&](const uint8_t* row, uint32_t (&Q)[4]) {  // rows `row` and `row + pitch`
         uint32_t ha[4], hb[4];
+        blur_hrow(row, ha);
+        blur_hrow(row + pitch, hb);
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            blur_hrow(src + (long long)(y0 - 3 + 2 * k) * pitch, ha);
-            blur_hrow(src + (long long)(y0 - 2 + 2 * k) * pitch, hb);
+        for (int j = 0; j < 4; j++) Q[j] = __byte_perm(ha[j], hb[j], 0x5410);
+    };
+    const uint8_t* sp = src + (long long)(y0 - 3) * pitch;
 #pragma unroll
-            for (int j = 0; j < 4; j++) P[k][j] = ha[j] | (hb[j] << 16);
-        }
-    }
+    for (int k = 0; k < 4; k++) { hpair(sp, P[k]); sp += 2 * pitch; }   // sp -> row y0 + 5
+    uint8_t* dp = dst + (long long)y0 * pitch;
     constexpr uint32_t TA = 0x12002212u;  // lo pair taps (18,34): row y   | hi pair taps (0,18):  row y+1
     constexpr uint32_t TB = 0x30223830u;  // (48,56) | (34,48)
     constexpr uint32_t TC = 0x30382230u;  // (48,34) | (56,48)
     constexpr uint32_t TD = 0x12220012u;  // (18,0)  | (34,18)
-    for (int y = y0; y < y1; y += 2) {
-        uint32_t o0 = 0, o1 = 0;
+    // two output rows from the window (A,B,C,D); sums stay below 2^24, so the result is byte 2 of the accumulator
+    auto vout = [&](const uint32_t (&A)[4], const uint32_t (&B)[4], const uint32_t (&C)[4], const uint32_t (&D)[4]) {
+        uint32_t a0[4], a1[4];
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-            uint32_t acc0 = __dp2a_lo(P[0][j], TA, 32768u);
-            uint32_t acc1 = __dp2a_hi(P[0][j], TA, 32768u);
-            acc0 = __dp2a_lo(P[1][j], TB, acc0); acc1 = __dp2a_hi(P[1][j], TB, acc1);
-            acc0 = __dp2a_lo(P[2][j], TC, acc0); acc1 = __dp2a_hi(P[2][j], TC, acc1);
-            acc0 = __dp2a_lo(P[3][j], TD, acc0); acc1 = __dp2a_hi(P[3][j], TD, acc1);
-            o0 |= ((acc0 >> 16) & 0xffu) << (8 * j);
-            o1 |= ((acc1 >> 16) & 0xffu) << (8 * j);
+            a0[j] = __dp2a_lo(D[j], TD, __dp2a_lo(C[j], TC, __dp2a_lo(B[j], TB, __dp2a_lo(A[j], TA, 32768u))));
+            a1[j] = __dp2a_hi(D[j], TD, __dp2a_hi(C[j], TC, __dp2a_hi(B[j], TB, __dp2a_hi(A[j], TA, 32768u))));
         }
         // words may run up to 3 bytes / one row past the interior into the (unused) frame area of the blurred plane
-        *reinterpret_cast<uint32_t*>(dst + (long long)y * pitch) = o0;
-        *reinterpret_cast<uint32_t*>(dst + (long long)(y + 1) * pitch) = o1;
-        if (y + 2 < y1) {
-            uint32_t ha[4], hb[4];
-            blur_hrow(src + (long long)(y + 5) * pitch, ha);
-            blur_hrow(src + (long long)(y + 6) * pitch, hb);
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                P[0][j] = P[1][j]; P[1][j] = P[2][j]; P[2][j] = P[3][j];
-                P[3][j] = ha[j] | (hb[j] << 16);
-            }
-        }
+        *reinterpret_cast<uint32_t*>(dp) = __byte_perm(__byte_perm(a0[0], a0[1], 0x0062), __byte_perm(a0[2], a0[3], 0x0062), 0x5410);
+        *reinterpret_cast<uint32_t*>(dp + pitch) = __byte_perm(__byte_perm(a1[0], a1[1], 0x0062), __byte_perm(a1[2], a1[3], 0x0062), 0x5410);
+        dp += 2 * pitch;
+    };
+    // four row pairs per trip, the window rotating through P[0..3] by name (no register moves)
+    for (int y = y0; y < y1; y += 8) {
+        vout(P[0], P[1], P[2], P[3]);
+        if (y + 2 >= y1) break;
+        hpair(sp, P[0]); sp += 2 * pitch;
+        vout(P[1], P[2], P[3], P[0]);
+        if (y + 4 >= y1) break;
+        hpair(sp, P[1]); sp += 2 * pitch;
+        vout(P[2], P[3], P[0], P[1]);
+        if (y + 6 >= y1) break;
+        hpair(sp, P[2]); sp += 2 * pitch;
+        vout(P[3], P[0], P[1], P[2]);
+        if (y + 8 >= y1) break;
+        hpair(sp, P[3]); sp += 2 * pitch;
     }
 }
 
@@ -1486,8 +1490,8 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_PYRAMID], s));
     {
         const LevelGeom& g = P.lv[0];
-        dim3 grid((g.pitch / 16 + 127) / 128, g.planeRows, n);
-        k_level0<<<grid, 128, 0, s>>>(P, B, dIn, inStep, inFrameStride);
+        dim3 grid((g.planeRows + L0_ROWS - 1) / L0_ROWS, n);
+        k_level0<<<grid, 16 * L0_ROWS, 0, s>>>(P, B, dIn, inStep, inFrameStride);
         nl++;
     }
     for (int l = 1; l < P.nlevels; l++) {
