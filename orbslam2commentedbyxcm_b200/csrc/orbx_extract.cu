@@ -103,6 +103,7 @@ struct Buffers {
     const short* yofs0;
     const short* yofs1;
     const short2* yw;
+    const int4* yrow;    // k_resize_words row table: {r0 * srcPitch, r1 * srcPitch, b0 | b1 << 16, mirrored frame rows as deltas}
     const FastUnit* fastUnits;  // [totalFastUnits]
     int* errFlag;        // device-side overflow flag
     int frames;
@@ -259,40 +260,37 @@ __global__ void __launch_bounds__(128) k_resize_words(Plan plan, Buffers buf, in
     const uint8_t* S = plane_ptr(buf.pyr, gp, frame) + (long long)PAD_TOP * gp.pitch;  // row 0 of the interior, buffer column 0
     uint8_t* D = plane_ptr(buf.pyr, g, frame);
     const uint32_t spitch = (uint32_t)gp.pitch, dpitch = (uint32_t)g.pitch;
-    uint32_t t0[4], t1[4];
-    int rowInT1 = -1;
-    auto hrow = [&](int r, uint32_t* t) {
-        const uint32_t* R = reinterpret_cast<const uint32_t*>(S + ((uint32_t)r * spitch + colOff));
-        const uint32_t w0 = R[0], w1 = R[1], w2 = R[2];
+    const uint8_t* Sb = S + colOff;
+    uint8_t* Dp = D + ((uint32_t)(PAD_TOP + dy0) * dpitch + bx);
+    const int4* yrow = buf.yrow + g.yTab;
+    // horizontal pass of one source row (byte offset off): T >> 4 for the thread's 4 columns
+    auto hrow = [&](uint32_t off, uint32_t* t) {
+        const uint32_t* R = reinterpret_cast<const uint32_t*>(Sb + off);
+        const uint32_t w0 = __ldg(R), w1 = __ldg(R + 1), w2 = __ldg(R + 2);
         const uint32_t u0 = __funnelshift_r(w0, w1, sh), u1 = __funnelshift_r(w1, w2, sh);
 #pragma unroll
         for (int j = 0; j < 4; j++) t[j] = __dp2a_lo(a[j], __byte_perm(u0, u1, sel[j]), 0u) >> 4;
     };
+    // Both source rows are interpolated for every output row (no row cache: the copies and branches it needs cost as
+    // much as the second horizontal pass).  Vertical pass: p = b * (T >> 4) < 2^27; the two high halves are summed by
+    // one IDP.2A with weights 64 and accumulator 2 * 64, which leaves ((p0 >> 16) + (p1 >> 16) + 2) >> 2 in byte 1.
     for (int dy = dy0; dy < dy1; dy++) {
-        const int r0 = buf.yofs0[g.yTab + dy], r1 = buf.yofs1[g.yTab + dy];
-        const short2 b = buf.yw[g.yTab + dy];
-        if (r0 == rowInT1) {
-#pragma unroll
-            for (int j = 0; j < 4; j++) t0[j] = t1[j];
-        } else {
-            hrow(r0, t0);
-        }
-        if (r1 == r0) {
-#pragma unroll
-            for (int j = 0; j < 4; j++) t1[j] = t0[j];
-        } else {
-            hrow(r1, t1);
-        }
-        rowInT1 = r1;
-        const uint32_t b0 = (uint32_t)b.x << 16, b1 = (uint32_t)b.y << 16;
+        const int4 e = __ldg(yrow + dy);
+        uint32_t t0[4], t1[4];
+        hrow((uint32_t)e.x, t0);
+        hrow((uint32_t)e.y, t1);
+        const uint32_t b0 = (uint32_t)e.z & 0xffffu, b1 = (uint32_t)e.z >> 16;
         uint32_t o[4];
 #pragma unroll
-        for (int j = 0; j < 4; j++) o[j] = (__umulhi(b0, t0[j]) + __umulhi(b1, t1[j]) + 2u) >> 2;  // in [0, 255]
-        const uint32_t v = __byte_perm(__byte_perm(o[0], o[1], 0x0040), __byte_perm(o[2], o[3], 0x0040), 0x5410);
-        *reinterpret_cast<uint32_t*>(D + ((uint32_t)(PAD_TOP + dy) * dpitch + bx)) = v;
-        if (dy >= 1 && dy <= EDGE) *reinterpret_cast<uint32_t*>(D + ((uint32_t)(PAD_TOP - dy) * dpitch + bx)) = v;
-        if (dy >= g.h - 1 - EDGE && dy <= g.h - 2)
-            *reinterpret_cast<uint32_t*>(D + ((uint32_t)(PAD_TOP + 2 * (g.h - 1) - dy) * dpitch + bx)) = v;
+        for (int j = 0; j < 4; j++) o[j] = __dp2a_lo(__byte_perm(b0 * t0[j], b1 * t1[j], 0x7632), 0x4040u, 128u);
+        const uint32_t v = __byte_perm(__byte_perm(o[0], o[1], 0x0051), __byte_perm(o[2], o[3], 0x0051), 0x5410);
+        *reinterpret_cast<uint32_t*>(Dp) = v;
+        if (e.w) {  // this row is also a row of the REFLECT_101 frame (above and / or below the interior)
+            const int up = (short)(e.w & 0xffff), down = e.w >> 16;
+            if (up) *reinterpret_cast<uint32_t*>(Dp + (long long)up * (int)dpitch) = v;
+            if (down) *reinterpret_cast<uint32_t*>(Dp + (long long)down * (int)dpitch) = v;
+        }
+        Dp += dpitch;
     }
 }
 
@@ -1249,7 +1247,7 @@ static void free_arenas(orbx_handle* h)
 }
 
 // Level geometry, cell grids, capacities, resize tables for one image shape.
-struct TabInfo { long long nx, ny, nxw, nyw; std::vector<FastUnit> units; };  // padded lengths of xofs / yofs and true lengths of the weight arrays
+struct TabInfo { long long nx, ny, nxw, nyw, yrowOff; std::vector<FastUnit> units; };  // padded lengths of xofs / yofs and true lengths of the weight arrays
 
 static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<short>& tabs, long long& pyrBytesPerFrame,
                       TabInfo* ti = nullptr)
@@ -1261,6 +1259,7 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
     int fastOff = 0, kpOff = 0, fastRows = 0, fastQ = 0, blurOff = 0;
     // tables: per level >= 1: xofs[w], xw[2w], yofs0[h], yofs1[h], yw[2h] -- stored in 5 separate arrays
     std::vector<short> xofs, xw, y0v, y1v, yw;
+    std::vector<int> yrow;  // 4 ints per destination row, indexed like y0v
     for (int l = 0; l < c.nlevels; l++) {
         LevelGeom& g = P.lv[l];
         g.w = cv_round_f((float)cols * h->invScale[l]);
@@ -1327,7 +1326,15 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
                     f -= s;
                     auto clip = [&](int x) { return x >= 0 ? (x < gp.h ? x : gp.h - 1) : 0; };
                     y0v.push_back((short)clip(s)); y1v.push_back((short)clip(s + 1));
-                    yw.push_back(sat_short((1.f - f) * 2048)); yw.push_back(sat_short(f * 2048));
+                    const short wb0 = sat_short((1.f - f) * 2048), wb1 = sat_short(f * 2048);
+                    yw.push_back(wb0); yw.push_back(wb1);
+                    // destination rows 1..19 and h-20..h-2 are also the REFLECT_101 frame rows -d and 2(h-1)-d
+                    // (as row deltas: low half = upper frame, high half = lower frame, 0 = none)
+                    int dup = 0;
+                    if (d >= 1 && d <= EDGE) dup |= (-2 * d) & 0xffff;
+                    if (d >= g.h - 1 - EDGE && d <= g.h - 2) dup |= (2 * (g.h - 1 - d)) << 16;
+                    yrow.push_back(clip(s) * gp.pitch); yrow.push_back(clip(s + 1) * gp.pitch);
+                    yrow.push_back((int)((uint32_t)(unsigned short)wb0 | ((uint32_t)(unsigned short)wb1 << 16))); yrow.push_back(dup);
                 }
             }
             // k_resize_words eligibility: every aligned group of 4 buffer columns (frame columns map to the reflected
@@ -1361,6 +1368,12 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
     tabs.insert(tabs.end(), y1v.begin(), y1v.end());
     tabs.insert(tabs.end(), xw.begin(), xw.end());
     tabs.insert(tabs.end(), yw.begin(), yw.end());
+    while (tabs.size() & 7) tabs.push_back(0);  // 16-byte alignment for the int4 row table
+    const long long yrowOff = (long long)tabs.size();
+    {
+        const short* yr = reinterpret_cast<const short*>(yrow.data());
+        tabs.insert(tabs.end(), yr, yr + 2 * yrow.size());
+    }
     std::vector<FastUnit> units;
     for (int l = 0; l < c.nlevels; l++) {
         const LevelGeom& g = P.lv[l];
@@ -1381,7 +1394,7 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
     }
     P.totalFastUnits = (int)units.size();
     if (ti) {
-        ti->nx = (long long)xofs.size(); ti->ny = (long long)y0v.size(); ti->nxw = (long long)xw.size(); ti->nyw = (long long)yw.size();
+        ti->nx = (long long)xofs.size(); ti->ny = (long long)y0v.size(); ti->nxw = (long long)xw.size(); ti->nyw = (long long)yw.size(); ti->yrowOff = yrowOff;
         ti->units.swap(units);
     }
     P.pyrFrameStride = pyrBytesPerFrame;
@@ -1440,6 +1453,7 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
     B.yofs1 = h->dTabs + ti.nx + ti.ny;
     B.xw = reinterpret_cast<const short2*>(h->dTabs + ti.nx + 2 * ti.ny);
     B.yw = reinterpret_cast<const short2*>(h->dTabs + ti.nx + 2 * ti.ny + ti.nxw);
+    B.yrow = reinterpret_cast<const int4*>(h->dTabs + ti.yrowOff);
     // quad-tree kernel shared memory
     int nodeCapMax = 0, candCapMax = 0;
     for (int l = 0; l < P.nlevels; l++) { nodeCapMax = std::max(nodeCapMax, P.lv[l].nodeCap); candCapMax = std::max(candCapMax, P.lv[l].candCap); }
