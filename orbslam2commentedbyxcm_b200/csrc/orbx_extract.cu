@@ -68,7 +68,7 @@ struct Plan {
     int nlevels, rows, cols;
     int iniTh, minTh;
     int totalFastUnits, totalBlurUnits;
-    int fastTileBytes, fastQCap;   // k_fast_band shared-memory carve-up
+    int fastTileBytes, fastQCap;   // k_fast_band shared-memory carve-up (fastQCap = capacity of the post-NMS queue)
     int kpCapFrame;          // sum of nodeCap = keypoint capacity per frame
     long long pyrFrameStride;  // not used for addressing (planes are [level][frame]); kept for sizing
     long long candFrame;       // candidates per frame (sum of candCap)
@@ -304,9 +304,11 @@ __global__ void __launch_bounds__(128) k_resize_words(Plan plan, Buffers buf, in
 //   1. SWAR rejection on 4 pixels at a time: a 9-arc contains one pixel of every opposite ring pair, so a corner needs
 //      |I(p)-I(q)| > minTh for q in {N or S} and q in {E or W}  (VABSDIFF4 + a carry trick; ~90 % of pixels stop here);
 //      survivors are compacted into a queue.
-//   2. exact score for queued pixels: the 16 ring differences packed as 8 x s16x2, sliding min/max over windows of 9
-//      as min3(min3) with VIMNMX3.S16x2.
-//   3. NMS for corners only (sparse), per-cell ini/min decision, unordered append to the level's candidate list.
+//   2. exact score for queued pixels: the 16 ring differences packed as 8 x biased u16x2, sliding min/max over windows
+//      of 9 as min3(min3) with VIMNMX3.U16x2.  The queue holds FAST_Q1CAP pixels (shared memory bounds residency); a band
+//      with more survivors than that is scored in rounds of FAST_GIT row sweeps from the masks kept in registers.
+//   3. NMS for corners only (sparse; a dense scan of the score tile after a multi-round pass 2), per-cell ini/min
+//      decision, unordered append to the level's candidate list.
 // The reference's candidate order (cell row-major, then pixel row-major) is carried in `ord` and only matters for
 // response ties inside a quad-tree node.
 // ------------------------------------------------------------------------------------------------------
@@ -315,44 +317,51 @@ constexpr int FAST_P = 160;   // tile pitch in bytes: <= 124 + 6 px band + 15 al
 constexpr int FAST_P4 = FAST_P / 4;
 constexpr int FAST_MAXG = 4;
 
+constexpr int FAST_Q1CAP = 1280;  // pass-1 queue entries; bands with more survivors are scored in rounds of 2 row sweeps (<= 1024)
+constexpr int FAST_GIT = 2;       // row sweeps (4 rows each, 4 px x 32 lanes per row) per round
+
 __device__ __forceinline__ uint32_t swap16(uint32_t v) { return __byte_perm(v, 0, 0x1032); }
 
-// exact arc measure M(p) = max over 9-arcs of max(min d, min -d), d_k = I(p) - I(ring_k)
+// exact arc measure M(p) = max over 9-arcs of max(min d, min -d), d_k = I(p) - I(ring_k).  The differences are kept as
+// biased u16x2 pairs (d_k + 0x8000, d_{k+8} + 0x8000): one 32-bit subtraction makes both (no borrow can cross the
+// halves), and unsigned 16-bit min / max order the biased values like the signed differences.
 __device__ __forceinline__ int fast_measure_packed(const uint8_t* p)
 {
     constexpr int O[16] = {
         3 * FAST_P + 0, 3 * FAST_P + 1, 2 * FAST_P + 2, 1 * FAST_P + 3, 0 * FAST_P + 3, -1 * FAST_P + 3,
         -2 * FAST_P + 2, -3 * FAST_P + 1, -3 * FAST_P + 0, -3 * FAST_P - 1, -2 * FAST_P - 2, -1 * FAST_P - 3,
         0 * FAST_P - 3, 1 * FAST_P - 3, 2 * FAST_P - 2, 3 * FAST_P - 1};
-    const uint32_t cc = (uint32_t)p[0] * 0x10001u;
-    uint32_t dp[10];  // dp[k] = (d[k], d[k+8]) as s16x2
+    const uint32_t cc = (uint32_t)p[0] * 0x10001u + 0x80008000u;
+    uint32_t dp[10];  // dp[k] = (d[k], d[k+8]) biased
 #pragma unroll
-    for (int k = 0; k < 8; k++) dp[k] = __vsub2(cc, (uint32_t)p[O[k]] | ((uint32_t)p[O[k + 8]] << 16));
+    for (int k = 0; k < 8; k++) dp[k] = cc - ((uint32_t)p[O[k]] | ((uint32_t)p[O[k + 8]] << 16));
     dp[8] = swap16(dp[0]);
     dp[9] = swap16(dp[1]);
     uint32_t tn[14], tx[14];  // min / max over 3 consecutive differences, (k, k+8) packed
 #pragma unroll
     for (int k = 0; k < 8; k++) {
-        tn[k] = __vimin3_s16x2(dp[k], dp[k + 1], dp[k + 2]);
-        tx[k] = __vimax3_s16x2(dp[k], dp[k + 1], dp[k + 2]);
+        tn[k] = __vimin3_u16x2(dp[k], dp[k + 1], dp[k + 2]);
+        tx[k] = __vimax3_u16x2(dp[k], dp[k + 1], dp[k + 2]);
     }
 #pragma unroll
     for (int k = 0; k < 6; k++) { tn[8 + k] = swap16(tn[k]); tx[8 + k] = swap16(tx[k]); }
-    uint32_t a = 0x80008000u, b = 0x7fff7fffu;  // running max of window minima / min of window maxima
+    uint32_t wn[8], wx[8];  // min / max over the window of 9 starting at k (and k + 8)
 #pragma unroll
     for (int k = 0; k < 8; k++) {
-        a = __vmaxs2(a, __vimin3_s16x2(tn[k], tn[k + 3], tn[k + 6]));
-        b = __vmins2(b, __vimax3_s16x2(tx[k], tx[k + 3], tx[k + 6]));
+        wn[k] = __vimin3_u16x2(tn[k], tn[k + 3], tn[k + 6]);
+        wx[k] = __vimax3_u16x2(tx[k], tx[k + 3], tx[k + 6]);
     }
-    const int A = max((int)(short)(a & 0xffff), (int)(short)(a >> 16));
-    const int B = min((int)(short)(b & 0xffff), (int)(short)(b >> 16));
+    const uint32_t a = __vimax3_u16x2(__vimax3_u16x2(wn[0], wn[1], wn[2]), __vimax3_u16x2(wn[3], wn[4], wn[5]), __vmaxu2(wn[6], wn[7]));
+    const uint32_t b = __vimin3_u16x2(__vimin3_u16x2(wx[0], wx[1], wx[2]), __vimin3_u16x2(wx[3], wx[4], wx[5]), __vminu2(wx[6], wx[7]));
+    const int A = (int)max(a & 0xffffu, a >> 16) - 0x8000;
+    const int B = (int)min(b & 0xffffu, b >> 16) - 0x8000;
     return max(A, -B);
 }
 
 __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
 {
     extern __shared__ __align__(16) unsigned char fsm[];
-    __shared__ int sQ1, sQ2, sQ3, sCnt, sBase, sPos;
+    __shared__ int sQ1, sQ3, sCnt, sBase, sPos;
     __shared__ int sHasIni[FAST_MAXG];
 
     const int frame = blockIdx.y + buf.frameBase;
@@ -364,47 +373,51 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
 
     uint8_t* tile = fsm;
     uint8_t* sc = fsm + plan.fastTileBytes;
-    unsigned short* q1 = reinterpret_cast<unsigned short*>(fsm + 2 * plan.fastTileBytes);
-    unsigned short* q2 = q1 + plan.fastQCap;
+    unsigned short* q1 = reinterpret_cast<unsigned short*>(fsm + 2 * plan.fastTileBytes);  // FAST_Q1CAP entries
+    unsigned short* q3 = q1 + FAST_Q1CAP;                                                   // plan.fastQCap entries
 
     // stage the band with 16-byte asynchronous copies (16 lanes per row, 8 rows per pass), zero the score tile
-    const uint8_t* interior = interior_ptr(buf.pyr, g, frame);
     const int shift = (PAD_LEFT + iniX) & 15;
-    const int nw16 = (shift + bw + 15) >> 4;  // <= 10
     {
-        const int c16 = threadIdx.x & 15;
+        const int nw16 = (shift + bw + 15) >> 4;  // <= 10
+        const int c16 = threadIdx.x & 15, r0 = threadIdx.x >> 4;
         if (c16 < nw16) {
-            const uint8_t* src = interior + (long long)iniY * g.pitch + (iniX - shift) + 16 * c16;
-            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(tile) + 16 * c16;
-            for (int r = threadIdx.x >> 4; r < rh; r += FAST_T / 16)
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + r * FAST_P), "l"(src + (long long)r * g.pitch) : "memory");
+            const uint8_t* src = interior_ptr(buf.pyr, g, frame) + (long long)(iniY + r0) * g.pitch + (iniX - shift) + 16 * c16;
+            uint32_t dst = (uint32_t)__cvta_generic_to_shared(tile) + r0 * FAST_P + 16 * c16;
+            const long long step = (long long)(FAST_T / 16) * g.pitch;
+            for (int r = r0; r < rh; r += FAST_T / 16) {
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+                src += step;
+                dst += (FAST_T / 16) * FAST_P;
+            }
         }
     }
-    for (int idx = threadIdx.x; idx < rh * (FAST_P / 16); idx += FAST_T) reinterpret_cast<uint4*>(sc)[idx] = make_uint4(0, 0, 0, 0);
+    {
+        uint4* z = reinterpret_cast<uint4*>(sc) + threadIdx.x;
+        for (int n = rh * (FAST_P / 16) - threadIdx.x; n > 0; n -= FAST_T, z += FAST_T) *z = make_uint4(0, 0, 0, 0);
+    }
     if (threadIdx.x < FAST_MAXG) sHasIni[threadIdx.x] = 0;
-    if (threadIdx.x == 0) { sQ1 = 0; sQ2 = 0; sQ3 = 0; sCnt = 0; sPos = 0; }
+    if (threadIdx.x == 0) { sQ1 = 0; sQ3 = 0; sCnt = 0; sPos = 0; }
     asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int minTh = plan.minTh, iniTh = plan.iniTh;
     // ---- pass 1: SWAR rejection, 4 pixels per lane; the survivors of a lane's rows are kept as 4-bit groups of a
-    //      60-bit mask and written to the queue by ONE loop per lane (one divergent region instead of one per row) ----
+    //      60-bit mask (sweep `it` = rows warp + 4 * it) ----
+    const int txFirst = shift + 3, txEnd = shift + 3 + evalW;  // evaluated tile columns [txFirst, txEnd)
+    const int gw = (txFirst >> 2) + lane;                        // ((txEnd-1)>>2) - (txFirst>>2) + 1 <= 32 words
+    constexpr int FAST_RPW = (59 + FAST_T / 32 - 1) / (FAST_T / 32);  // sweeps: eh <= 59
+    static_assert(FAST_RPW <= 16, "survivor nibbles must fit 64 bits");
+    uint32_t mlo = 0, mhi = 0;
     {
-        const int txFirst = shift + 3, txEnd = shift + 3 + evalW;  // evaluated tile columns [txFirst, txEnd)
-        const int gFirst = txFirst >> 2;                             // ((txEnd-1)>>2) - gFirst + 1 <= 32 words
         const uint32_t K = (uint32_t)(0x7f - min(minTh, 0x7f)) * 0x01010101u;
         const bool filter = minTh < 0x80;
-        const uint32_t* t32 = reinterpret_cast<const uint32_t*>(tile);
-        const int gw = gFirst + lane;
         uint32_t vmask = 0;  // bytes of this word that are evaluated pixels
 #pragma unroll
         for (int bb = 0; bb < 4; bb++)
             if (4 * gw + bb >= txFirst && 4 * gw + bb < txEnd) vmask |= 0x80u << (8 * bb);
-        constexpr int FAST_RPW = (59 + FAST_T / 32 - 1) / (FAST_T / 32);  // rows per warp: eh <= 59
-        static_assert(FAST_RPW <= 16, "survivor nibbles must fit 64 bits");
-        uint32_t mlo = 0, mhi = 0;
-        const uint32_t* rowp = t32 + (warp + 3) * FAST_P4 + gw;
+        const uint32_t* rowp = reinterpret_cast<const uint32_t*>(tile) + (warp + 3) * FAST_P4 + gw;
 #pragma unroll
         for (int it = 0; it < FAST_RPW; it++) {
             if (warp + it * (FAST_T / 32) >= eh) break;  // warp-uniform
@@ -423,53 +436,82 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
             const uint32_t nib = (m * 0x00204081u) >> 28;  // bits 7, 15, 23, 31 -> 0..3
             if (it < 8) mlo |= nib << (4 * it); else mhi |= nib << (4 * (it - 8));
         }
+    }
+    // queue entry = tile row << 8 | tile column; bit b of sweep `it` is pixel (warp + 3 + 4 * it, 4 * gw + (b & 3))
+    const uint32_t e0 = ((uint32_t)(warp + 3) << 8) | (uint32_t)(4 * gw);
+    auto push = [&](uint32_t m, uint32_t ebase, int base) {
+        while (m) {
+            const int bit = __ffs(m) - 1;
+            m &= m - 1;
+            q1[base++] = (unsigned short)(ebase + (((uint32_t)bit >> 2) * ((FAST_T / 32) << 8)) + (bit & 3));
+        }
+    };
+    {
         const int cnt = __popc(mlo) + __popc(mhi);
         if (cnt) {
-            int base = atomicAdd(&sQ1, cnt);
-            const uint32_t e0 = ((uint32_t)(warp + 3) << 8) | (uint32_t)(4 * gw);
-#pragma unroll
-            for (int half = 0; half < 2; half++) {
-                uint32_t m = half ? mhi : mlo;
-                const uint32_t eh0 = e0 + (half ? (8u * (FAST_T / 32)) << 8 : 0u);
-                while (m) {
-                    const int bit = __ffs(m) - 1;
-                    m &= m - 1;
-                    q1[base++] = (unsigned short)(eh0 + (((uint32_t)bit >> 2) * ((FAST_T / 32) << 8)) + (bit & 3));
-                }
+            const int base = atomicAdd(&sQ1, cnt);
+            if (base + cnt <= FAST_Q1CAP) {
+                push(mlo, e0, base);
+                push(mhi, e0 + ((8u * (FAST_T / 32)) << 8), base + __popc(mlo));
             }
         }
     }
     __syncthreads();
     // ---- pass 2: exact score of the queued pixels ----
     const int n1 = sQ1;
-    for (int q = threadIdx.x; q < n1; q += FAST_T) {
-        const int e = q1[q];
-        const int ty = e >> 8, tx = e & 0xff;
-        const int mval = fast_measure_packed(tile + ty * FAST_P + tx);
-        if (mval > minTh) {
-            sc[ty * FAST_P + tx] = (uint8_t)(mval - 1);
-            q2[atomicAdd(&sQ2, 1)] = (unsigned short)e;
+    const bool sparse = n1 <= FAST_Q1CAP;  // CTA-uniform
+    auto score = [&](int n) {
+        for (int q = threadIdx.x; q < n; q += FAST_T) {
+            const int e = q1[q];
+            const int idx = (e >> 8) * FAST_P + (e & 0xff);
+            const int mval = fast_measure_packed(tile + idx);
+            if (mval > minTh) sc[idx] = (uint8_t)(mval - 1);
+        }
+    };
+    if (sparse) {
+        score(n1);
+    } else {
+        // too many survivors for the queue (texture / noise everywhere): FAST_GIT sweeps per round
+        for (int it0 = 0; it0 * (FAST_T / 32) < eh; it0 += FAST_GIT) {
+            __syncthreads();
+            if (threadIdx.x == 0) sQ1 = 0;
+            __syncthreads();
+            const uint32_t m = ((it0 < 8 ? mlo >> (4 * it0) : mhi >> (4 * (it0 - 8)))) & ((1u << (4 * FAST_GIT)) - 1u);
+            if (m) push(m, e0 + (((uint32_t)it0 * (FAST_T / 32)) << 8), atomicAdd(&sQ1, __popc(m)));
+            __syncthreads();
+            score(sQ1);
         }
     }
     __syncthreads();
     // ---- pass 3: 3x3 NMS inside the cell, for corners only ----
-    const int n2 = sQ2;
     const int wCell = g.wCell;
-    for (int q = threadIdx.x; q < n2; q += FAST_T) {
-        const int e = q2[q];
-        const int ty = e >> 8, tx = e & 0xff;
+    auto nms = [&](int ty, int tx) {
         const int ex = tx - (shift + 3);
         const int c = (ex >= wCell) + (ex >= 2 * wCell) + (ex >= 3 * wCell);
         const int r = ex - c * wCell;
         const uint8_t* s0 = sc + ty * FAST_P + tx;
         const int s = s0[0];
         const bool hasL = r > 0, hasR = r < wCell - 1;  // neighbours in another cell's region count as 0
-        bool keep = s > 0 && s > s0[-FAST_P] && s > s0[FAST_P];
+        bool keep = s > s0[-FAST_P] && s > s0[FAST_P];
         if (hasL) keep = keep && s > s0[-1] && s > s0[-FAST_P - 1] && s > s0[FAST_P - 1];
         if (hasR) keep = keep && s > s0[1] && s > s0[-FAST_P + 1] && s > s0[FAST_P + 1];
         if (keep) {
-            q1[atomicAdd(&sQ3, 1)] = (unsigned short)e;
+            q3[atomicAdd(&sQ3, 1)] = (unsigned short)((ty << 8) | tx);
             if (s >= iniTh) sHasIni[c] = 1;
+        }
+    };
+    if (sparse) {
+        for (int q = threadIdx.x; q < n1; q += FAST_T) {
+            const int e = q1[q];
+            if (sc[(e >> 8) * FAST_P + (e & 0xff)]) nms(e >> 8, e & 0xff);
+        }
+    } else {
+        const uint32_t* sc32 = reinterpret_cast<const uint32_t*>(sc);
+        for (int idx = threadIdx.x; idx < eh * FAST_P4; idx += FAST_T) {
+            const int ty = idx / FAST_P4 + 3, wx = idx - (ty - 3) * FAST_P4;
+            uint32_t w = sc32[ty * FAST_P4 + wx];
+            for (int bb = 0; w; bb++, w >>= 8)
+                if (w & 0xffu) nms(ty, 4 * wx + bb);
         }
     }
     __syncthreads();
@@ -477,7 +519,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
     const int n3 = sQ3;
     int mine = 0;
     for (int q = threadIdx.x; q < n3; q += FAST_T) {
-        const int e = q1[q];
+        const int e = q3[q];
         const int ty = e >> 8, tx = e & 0xff;
         const int ex = tx - (shift + 3);
         const int c = (ex >= wCell) + (ex >= 2 * wCell) + (ex >= 3 * wCell);
@@ -490,7 +532,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
     if (!mine) return;
     Cand* out = buf.cand + (long long)frame * plan.candFrame + g.candOff;
     for (int q = threadIdx.x; q < n3; q += FAST_T) {
-        const int e = q1[q];
+        const int e = q3[q];
         const int ty = e >> 8, tx = e & 0xff;
         const int ex = tx - (shift + 3), ey = ty - 3;
         const int c = (ex >= wCell) + (ex >= 2 * wCell) + (ex >= 3 * wCell);
@@ -1293,7 +1335,8 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
         g.fastGroups = (g.nCols + g.fastG - 1) / g.fastG;
         g.fastOff = fastOff; fastOff += g.nRows * g.fastGroups;
         fastRows = std::max(fastRows, g.hCell + 6);
-        fastQ = std::max(fastQ, g.hCell * std::min(g.fastG * g.wCell, 124));
+        // worst case after the 3x3 NMS: every other pixel of every other row of the evaluated band
+        fastQ = std::max(fastQ, ((std::min(g.fastG * g.wCell, 124) + 1) / 2 + 1) * ((g.hCell + 1) / 2 + 1));
         g.quota = h->quota[l];
         const int evalW = g.maxBX - minB - 6, evalH = g.maxBY - minB - 6;
         g.candCap = ((evalW + 1) / 2 + 1) * ((evalH + 1) / 2 + 1);
@@ -1478,7 +1521,7 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
     h->octKeySmemCap = keyCap;
     h->octSmem = nodeBytes + 2 * (size_t)keyCap + 16;
     ORBX_CUDA_TRY(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->octSmem));
-    h->fastSmem = 2 * (size_t)P.fastTileBytes + 4 * (size_t)P.fastQCap;
+    h->fastSmem = 2 * (size_t)P.fastTileBytes + 2 * ((size_t)FAST_Q1CAP + (size_t)P.fastQCap);
     ORBX_CUDA_TRY(cudaFuncSetAttribute(k_fast_band, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fastSmem));
     ORBX_CUDA_TRY(cudaMalloc(&h->dKeyNode, sizeof(unsigned short) * (size_t)P.candFrame * cap));
     h->plan = P;

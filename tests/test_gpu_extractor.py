@@ -153,6 +153,13 @@ def test_flat_and_empty_inputs(gpu, oracle_mod):
     ok, od = oracle_mod.Extractor(1000, 1.2, 8, 20, 7).extract(img)
     kps, desc = ex(img)
     assert kps.tobytes() == ok.tobytes() and np.array_equal(desc, od)
+    # uniform noise at full size: nearly every pixel survives the FAST pre-test, so k_fast_band's survivor queue
+    # overflows and the band is scored in rounds (the path typical images never take)
+    img = rng.integers(0, 256, (480, 640)).astype(np.uint8)
+    ok, od = oracle_mod.Extractor(1000, 1.2, 8, 20, 7).extract(img)
+    kps, desc = ex(img)
+    assert len(ok) > 900
+    assert kps.tobytes() == ok.tobytes() and np.array_equal(desc, od)
     ex.close()
 
 
