@@ -1929,20 +1929,34 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
         }
         h->lastFrames = chunk;
         int launches = 0;
+        // ORBX_PIPE_TRACE=1: per-chunk device timeline (ms from the first H2D) on stderr -- a debugging aid
+        static const bool trace = std::getenv("ORBX_PIPE_TRACE") != nullptr;
+        std::vector<cudaEvent_t> tev;
+        auto mark = [&](cudaStream_t st) {
+            if (!trace) return;
+            cudaEvent_t e;
+            cudaEventCreate(&e);
+            cudaEventRecord(e, st);
+            tev.push_back(e);
+        };
         for (int k = 0; k < nchunks; k++) {
             const int f0 = chunkStart[k], nk = chunkStart[k + 1] - f0, b = k & 1;
             uint8_t* dInB = h->dIn + (size_t)b * chunk * frameBytes;
             if (k >= 2) ORBX_CUDA_TRY(cudaStreamWaitEvent(h->streamH2D, h->evInFree[b], 0));
+            mark(h->streamH2D);
             if ((rc = copy_in(h, dInB, imgs + (size_t)f0 * frame_stride, nk, rows, cols, step, frame_stride, h->streamH2D)) != ORBX_OK) return rc;
             ORBX_CUDA_TRY(cudaEventRecord(h->evInReady[b], h->streamH2D));
+            mark(h->streamH2D);
             cudaStream_t cs = b ? h->stream2 : h->stream;  // chunk k computes in arena slot b on compute lane b
             ORBX_CUDA_TRY(cudaStreamWaitEvent(cs, h->evInReady[b], 0));
+            mark(cs);
             int nl = 0;
             rc = launch_cached(h, dInB, (long long)cols, (long long)frameBytes, nk, dKps + (size_t)f0 * devCap,
                                dDesc + (size_t)f0 * devCap * 32, dCounts + f0, devCap, &nl, b, b * chunk);
             if (rc != ORBX_OK) return rc;
             launches += nl;
             ORBX_CUDA_TRY(cudaEventRecord(h->evInFree[b], cs));
+            mark(cs);
             ORBX_CUDA_TRY(cudaStreamWaitEvent(h->streamD2H, h->evInFree[b], 0));
             ORBX_CUDA_TRY(cudaMemcpyAsync(hCnt + (size_t)f0 * sizeof(int), dCounts + f0, sizeof(int) * nk, cudaMemcpyDeviceToHost, h->streamD2H));
             ORBX_CUDA_TRY(cudaMemcpyAsync(hKps + (size_t)f0 * devCap * sizeof(orbx_keypoint), dKps + (size_t)f0 * devCap,
@@ -1950,8 +1964,19 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
             ORBX_CUDA_TRY(cudaMemcpyAsync(hDesc + (size_t)f0 * devCap * 32, dDesc + (size_t)f0 * devCap * 32,
                                           (size_t)32 * nk * devCap, cudaMemcpyDeviceToHost, h->streamD2H));
             ORBX_CUDA_TRY(cudaEventRecord(h->evChunkDone[k], h->streamD2H));
+            mark(h->streamD2H);
         }
         h->lastLaunches = launches;
+        if (trace) {
+            cudaDeviceSynchronize();
+            for (int k = 0; k < nchunks; k++) {
+                float t[5];
+                for (int i = 0; i < 5; i++) cudaEventElapsedTime(&t[i], tev[0], tev[5 * k + i]);
+                fprintf(stderr, "chunk %2d (%3d frames): h2d %.3f-%.3f  kernels %.3f-%.3f  d2h done %.3f\n", k, chunkStart[k + 1] - chunkStart[k],
+                        t[0], t[1], t[2], t[3], t[4]);
+            }
+            for (cudaEvent_t e : tev) cudaEventDestroy(e);
+        }
         if (direct) {
             ORBX_CUDA_TRY(cudaStreamSynchronize(h->streamD2H));
         } else {
