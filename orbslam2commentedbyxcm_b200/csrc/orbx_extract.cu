@@ -656,8 +656,8 @@ __device__ __forceinline__ float fast_atan2_dev(float y, float x)
 // circular patch half-widths umax[|v|] (src/ORBextractor.cc:519-549)
 __device__ __forceinline__ constexpr int umax_of(int av)
 {
-    constexpr int U[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
-    return U[av];
+    // {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3} as nibbles (no local-memory table)
+    return (int)((0x3689ABCDDEEEFFFFull >> (4 * av)) & 15ull);
 }
 
 __global__ void __launch_bounds__(OCT_T) k_octree(Plan plan, Buffers buf, int nodeCapMax, int keySmemCap,
@@ -1127,43 +1127,53 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 5) k_describe(Plan plan, Buff
     uint8_t* P = patch[wid];
     uint32_t* R = raw[wid];
 
-    for (int gidx = blockIdx.x * DESC_WARPS + wid; gidx < total; gidx += gridDim.x * DESC_WARPS) {
-        int level = 0;
-        while (gidx >= cum[level + 1]) level++;
-        const int j = gidx - cum[level];
-        const LevelGeom& g = plan.lv[level];
-        const StagedKp kp = buf.staged[(long long)frame * plan.kpCapFrame + g.kpOff + j];
-        const int cx = (int)kp.x, cy = (int)kp.y;
-        __syncwarp();
-        // ---- stage raw rows cy-15..cy+15 (9 aligned words per row from the word containing cx-16) and the blurred 37x37
-        //      neighbourhood (10 aligned words per row); every load is issued before the first store ----
-        const int shift = (PAD_LEFT + cx - 18) & 3;
-        {
-            const uint8_t* imgR = interior_ptr(buf.pyr, g, frame);
-            const uint8_t* rowR = imgR + (long long)(cy - 15) * g.pitch + (cx - 16 - (cx & 3));
-            const uint8_t* imgB = interior_ptr(buf.blur, g, frame);
-            const uint8_t* rowB = imgB + (long long)(cy - 18) * g.pitch + (cx - 18 - shift);
-            uint32_t tr[9], tb[12];
+    // staging maps: lane -> (word column, first row), rows advance by 3 per load (27 / 30 lanes active)
+    const int rwi = lane % ORI_PW, rrg = lane / ORI_PW;                  // raw: 31 rows x 9 words
+    const int bwi = lane % (DESC_PP / 4), brg = lane / (DESC_PP / 4);    // blurred: 37 rows x 10 words
+    // The patches of keypoint i+1 are loaded into registers while keypoint i is being processed from shared memory
+    // (software pipeline: the global-load latency hides behind the arithmetic of the previous keypoint).
+    uint32_t tr[11], tb[13];
+    int level = 0, nLevel = 0;  // gidx only grows: the level search resumes where it stopped
+    StagedKp nkp;
+    auto fetch = [&](int gi) {
+        while (gi >= cum[nLevel + 1]) nLevel++;
+        const LevelGeom& g = plan.lv[nLevel];
+        nkp = buf.staged[(long long)frame * plan.kpCapFrame + g.kpOff + (gi - cum[nLevel])];
+        const int cx = (int)nkp.x, cy = (int)nkp.y;
+        // raw rows cy-15..cy+15 (9 aligned words per row from the word containing cx-16) and the blurred 37x37
+        // neighbourhood (10 aligned words per row)
+        const long long step3 = 3LL * g.pitch;
+        const uint8_t* pr = interior_ptr(buf.pyr, g, frame) + (long long)(cy - 15 + rrg) * g.pitch + (cx - 16 - (cx & 3)) + 4 * rwi;
+        const uint8_t* pb = interior_ptr(buf.blur, g, frame) + (long long)(cy - 18 + brg) * g.pitch + (cx - 18 - ((PAD_LEFT + cx - 18) & 3)) + 4 * bwi;
 #pragma unroll
-            for (int i = 0; i < 9; i++) {
-                const int idx = lane + 32 * i;
-                const int r = idx / ORI_PW, wi = idx - r * ORI_PW;
-                tr[i] = idx < 31 * ORI_PW ? __ldg(reinterpret_cast<const uint32_t*>(rowR + r * g.pitch) + wi) : 0u;
-            }
-#pragma unroll
-            for (int i = 0; i < 12; i++) {
-                const int idx = lane + 32 * i;
-                const int r = idx / (DESC_PP / 4), wi = idx - r * (DESC_PP / 4);
-                tb[i] = idx < 37 * (DESC_PP / 4) ? __ldg(reinterpret_cast<const uint32_t*>(rowB + r * g.pitch) + wi) : 0u;
-            }
-#pragma unroll
-            for (int i = 0; i < 9; i++)
-                if (lane + 32 * i < 31 * ORI_PW) R[lane + 32 * i] = tr[i];
-#pragma unroll
-            for (int i = 0; i < 12; i++)
-                if (lane + 32 * i < 37 * (DESC_PP / 4)) reinterpret_cast<uint32_t*>(P)[lane + 32 * i] = tb[i];
+        for (int i = 0; i < 11; i++) {
+            tr[i] = (rrg < 3 && rrg + 3 * i < 31) ? __ldg(reinterpret_cast<const uint32_t*>(pr)) : 0u;
+            pr += step3;
         }
+#pragma unroll
+        for (int i = 0; i < 13; i++) {
+            tb[i] = (brg < 3 && brg + 3 * i < 37) ? __ldg(reinterpret_cast<const uint32_t*>(pb)) : 0u;
+            pb += step3;
+        }
+    };
+    const int gstride = gridDim.x * DESC_WARPS;
+    int gidx = blockIdx.x * DESC_WARPS + wid;
+    if (gidx < total) fetch(gidx);
+    for (; gidx < total; gidx += gstride) {
+        const StagedKp kp = nkp;
+        level = nLevel;
+        const LevelGeom& g = plan.lv[level];
+        const int cx = (int)kp.x;
+        const int shift = (PAD_LEFT + cx - 18) & 3;
+        __syncwarp();  // the previous keypoint's reads of R / P are done
+#pragma unroll
+        for (int i = 0; i < 11; i++)
+            if (rrg < 3 && rrg + 3 * i < 31) R[lane + 3 * ORI_PW * i] = tr[i];
+#pragma unroll
+        for (int i = 0; i < 13; i++)
+            if (brg < 3 && brg + 3 * i < 37) reinterpret_cast<uint32_t*>(P)[lane + 3 * (DESC_PP / 4) * i] = tb[i];
         __syncwarp();
+        if (gidx + gstride < total) fetch(gidx + gstride);
         // ---- IC_Angle ----
         int m10 = 0, rs = 0;
         if (lane < 31) {
@@ -1186,19 +1196,19 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 5) k_describe(Plan plan, Buff
         const float factorPI = 0.0174532924f;  // (float)(CV_PI/180.f)
         const SinCosOut sc = sincosf_glibc(__fmul_rn(angle, factorPI));
         const float a = sc.c, b = sc.s;
-        const uint8_t* center = P + 18 * DESC_PP + shift + 18;
         int val = 0;
-        // cvRound = round-half-even: adding 1.5 * 2^23 leaves the rounded integer in the low mantissa bits (|v| < 2^22)
+        // cvRound = round-half-even: adding 1.5 * 2^23 leaves the rounded integer in the low mantissa bits (|v| < 2^22);
+        // the bias 0x4B400000 of both coordinates is folded into the patch base (32-bit wrap-around arithmetic)
         const float RND = 12582912.f;
-        const int RNDI = 0x4B400000;
+        const uint32_t cbase = (uint32_t)(18 * DESC_PP + shift + 18) - (uint32_t)(DESC_PP + 1) * 0x4B400000u;
 #pragma unroll
         for (int k = 0; k < 8; k++) {
             const float4 pt = patF[k * 32 + lane];
-            const int iy0 = __float_as_int(__fadd_rn(__fadd_rn(__fmul_rn(pt.x, b), __fmul_rn(pt.y, a)), RND)) - RNDI;
-            const int ix0 = __float_as_int(__fadd_rn(__fsub_rn(__fmul_rn(pt.x, a), __fmul_rn(pt.y, b)), RND)) - RNDI;
-            const int iy1 = __float_as_int(__fadd_rn(__fadd_rn(__fmul_rn(pt.z, b), __fmul_rn(pt.w, a)), RND)) - RNDI;
-            const int ix1 = __float_as_int(__fadd_rn(__fsub_rn(__fmul_rn(pt.z, a), __fmul_rn(pt.w, b)), RND)) - RNDI;
-            const int t0 = center[iy0 * DESC_PP + ix0], t1 = center[iy1 * DESC_PP + ix1];
+            const uint32_t iy0 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(pt.x, b), __fmul_rn(pt.y, a)), RND));
+            const uint32_t ix0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(pt.x, a), __fmul_rn(pt.y, b)), RND));
+            const uint32_t iy1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(pt.z, b), __fmul_rn(pt.w, a)), RND));
+            const uint32_t ix1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(pt.z, a), __fmul_rn(pt.w, b)), RND));
+            const int t0 = P[iy0 * DESC_PP + (ix0 + cbase)], t1 = P[iy1 * DESC_PP + (ix1 + cbase)];
             val |= (t0 < t1) << k;
         }
         const long long o = (long long)lframe * capacity + gidx;
@@ -1579,7 +1589,11 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
         ORBX_CUDA_TRY(cudaStreamWaitEvent(s, evJoin, 0));
     }
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_DESC], s));
-    k_describe<<<dim3((capacity + 4 * DESC_WARPS - 1) / (4 * DESC_WARPS), n), DESC_WARPS * 32, 0, s>>>(P, B, dKps, dDesc, dCounts, capacity);
+    {
+        // keypoints per warp: the per-CTA constants are amortised over more keypoints when the batch alone fills the GPU
+        const int perWarp = n >= 16 ? 12 : (n >= 4 ? 6 : 2);
+        k_describe<<<dim3((capacity + perWarp * DESC_WARPS - 1) / (perWarp * DESC_WARPS), n), DESC_WARPS * 32, 0, s>>>(P, B, dKps, dDesc, dCounts, capacity);
+    }
     nl++;
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_D2H], s));
     ORBX_CUDA_TRY(cudaGetLastError());
