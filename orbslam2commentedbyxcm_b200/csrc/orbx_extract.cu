@@ -319,6 +319,7 @@ constexpr int FAST_MAXG = 4;
 
 constexpr int FAST_Q1CAP = 1280;  // pass-1 queue entries; bands with more survivors are scored in rounds of 2 row sweeps (<= 1024)
 constexpr int FAST_GIT = 2;       // row sweeps (4 rows each, 4 px x 32 lanes per row) per round
+static_assert(FAST_T == 128, "k_fast_band hard-codes 4 warps (queue quarters, sweeps of 4 rows)");
 
 __device__ __forceinline__ uint32_t swap16(uint32_t v) { return __byte_perm(v, 0, 0x1032); }
 
@@ -362,7 +363,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
 {
     extern __shared__ __align__(16) unsigned char fsm[];
     __shared__ int sQ1, sQ3, sCnt, sBase, sPos;
-    __shared__ int sHasIni[FAST_MAXG];
+    __shared__ int sHasIni[FAST_MAXG], sSeg[FAST_T / 32];
 
     const int frame = blockIdx.y + buf.frameBase;
     const int4 fuw = __ldg(reinterpret_cast<const int4*>(buf.fastUnits) + blockIdx.x);
@@ -457,19 +458,27 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
         }
     }
     __syncthreads();
-    // ---- pass 2: exact score of the queued pixels ----
+    // ---- pass 2: exact score of the queued pixels.  Each warp owns a contiguous quarter of the queue and compacts the
+    //      entries that turn out to be corners in place at the head of its quarter (writes trail the reads) ----
     const int n1 = sQ1;
     const bool sparse = n1 <= FAST_Q1CAP;  // CTA-uniform
-    auto score = [&](int n) {
-        for (int q = threadIdx.x; q < n; q += FAST_T) {
-            const int e = q1[q];
-            const int idx = (e >> 8) * FAST_P + (e & 0xff);
-            const int mval = fast_measure_packed(tile + idx);
-            if (mval > minTh) sc[idx] = (uint8_t)(mval - 1);
-        }
-    };
+    const int per = (((n1 + FAST_T / 32 - 1) / (FAST_T / 32)) + 31) & ~31;
     if (sparse) {
-        score(n1);
+        const int wbase = warp * per, wend = min(wbase + per, n1);
+        int cnt = 0;
+        for (int q0 = wbase; q0 < wend; q0 += 32) {
+            const int q = q0 + lane;
+            const int e = q < wend ? q1[q] : 0;
+            const int idx = (e >> 8) * FAST_P + (e & 0xff);
+            int mval = 0;
+            if (q < wend) mval = fast_measure_packed(tile + idx);
+            const bool corner = mval > minTh;
+            if (corner) sc[idx] = (uint8_t)(mval - 1);
+            const uint32_t bal = __ballot_sync(0xffffffffu, corner);
+            if (corner) q1[wbase + cnt + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)e;
+            cnt += __popc(bal);
+        }
+        if (lane == 0) sSeg[warp] = cnt;
     } else {
         // too many survivors for the queue (texture / noise everywhere): FAST_GIT sweeps per round
         for (int it0 = 0; it0 * (FAST_T / 32) < eh; it0 += FAST_GIT) {
@@ -479,7 +488,13 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
             const uint32_t m = ((it0 < 8 ? mlo >> (4 * it0) : mhi >> (4 * (it0 - 8)))) & ((1u << (4 * FAST_GIT)) - 1u);
             if (m) push(m, e0 + (((uint32_t)it0 * (FAST_T / 32)) << 8), atomicAdd(&sQ1, __popc(m)));
             __syncthreads();
-            score(sQ1);
+            const int n = sQ1;
+            for (int q = threadIdx.x; q < n; q += FAST_T) {
+                const int e = q1[q];
+                const int idx = (e >> 8) * FAST_P + (e & 0xff);
+                const int mval = fast_measure_packed(tile + idx);
+                if (mval > minTh) sc[idx] = (uint8_t)(mval - 1);
+            }
         }
     }
     __syncthreads();
@@ -501,9 +516,11 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
         }
     };
     if (sparse) {
-        for (int q = threadIdx.x; q < n1; q += FAST_T) {
-            const int e = q1[q];
-            if (sc[(e >> 8) * FAST_P + (e & 0xff)]) nms(e >> 8, e & 0xff);
+        const int c0 = sSeg[0], c1 = c0 + sSeg[1], c2 = c1 + sSeg[2], c3 = c2 + sSeg[3];
+        for (int t = threadIdx.x; t < c3; t += FAST_T) {
+            const int w = (t >= c0) + (t >= c1) + (t >= c2);
+            const int e = q1[w * per + t - (w == 0 ? 0 : (w == 1 ? c0 : (w == 2 ? c1 : c2)))];
+            nms(e >> 8, e & 0xff);
         }
     } else {
         const uint32_t* sc32 = reinterpret_cast<const uint32_t*>(sc);
