@@ -400,8 +400,18 @@ def run_ours(args):
     ps = torch.empty_like(pb)
     mstream = torch.cuda.ExternalStream(m.stream, device=dev)
 
-    def bf_step():
-        m.bruteforce_device(dq.data_ptr(), nq, ddb.data_ptr(), per, lo, pb.data_ptr(), pi.data_ptr(), ps.data_ptr())
+    ob, oi, os_ = torch.empty_like(pb), torch.empty_like(pb), torch.empty_like(pb)
+    if dist is not None:
+        # N > 1: the search, the exchange of the per-shard (best, idx, second) triples and the merge are ONE stream of
+        # device work per rank: k_bruteforce on the shard, then k_merge_exchange (P2P stores into every peer's buffer
+        # over NVLink, wait for the peers' triples, deterministic merge) -- no NCCL call on the data path.
+        m.exchange_connect_group(world, rank, nq)
+
+        def bf_step():
+            m.bruteforce_sharded_device(dq.data_ptr(), nq, ddb.data_ptr(), per, lo, ob.data_ptr(), oi.data_ptr(), os_.data_ptr())
+    else:
+        def bf_step():
+            m.bruteforce_device(dq.data_ptr(), nq, ddb.data_ptr(), per, lo, ob.data_ptr(), oi.data_ptr(), os_.data_ptr())
 
     for _ in range(3):
         bf_step()
@@ -415,17 +425,33 @@ def run_ours(args):
     b1.record(mstream)
     m.sync()
     bf_ms = b0.elapsed_time(b1) / bf_reps
+    nccl_ms = None
     if dist is not None:
-        # the only exchange step of the path: all-gather the per-shard (best, idx, second), identical merge on every rank
+        if m.exchange_timed_out():
+            raise RuntimeError("sharded search: a peer never answered")
+        # cross-check + comparison: the same search through NCCL (per-shard search, 3 all-gathers, merge kernel)
         gb = [torch.empty_like(pb) for _ in range(world)]
         gi = [torch.empty_like(pb) for _ in range(world)]
         gs = [torch.empty_like(pb) for _ in range(world)]
-        dist.all_gather(gb, pb); dist.all_gather(gi, pi); dist.all_gather(gs, ps)
-        ob, oi, os_ = torch.empty_like(pb), torch.empty_like(pb), torch.empty_like(pb)
-        torch.cuda.synchronize()
-        m.merge_partials_device(torch.stack(gb).data_ptr(), torch.stack(gi).data_ptr(), torch.stack(gs).data_ptr(), world, nq,
-                                ob.data_ptr(), oi.data_ptr(), os_.data_ptr())
-        m.sync()
+        nb, ni, ns = torch.empty_like(pb), torch.empty_like(pb), torch.empty_like(pb)
+
+        def nccl_step():
+            m.bruteforce_device(dq.data_ptr(), nq, ddb.data_ptr(), per, lo, pb.data_ptr(), pi.data_ptr(), ps.data_ptr())
+            m.sync()
+            dist.all_gather(gb, pb); dist.all_gather(gi, pi); dist.all_gather(gs, ps)
+            sb, si, ss = torch.stack(gb), torch.stack(gi), torch.stack(gs)
+            torch.cuda.synchronize()
+            m.merge_partials_device(sb.data_ptr(), si.data_ptr(), ss.data_ptr(), world, nq, nb.data_ptr(), ni.data_ptr(), ns.data_ptr())
+            m.sync()
+
+        nccl_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(5):
+            nccl_step()
+        nccl_ms = 1e3 * (time.perf_counter() - t0) / 5
+        if not (torch.equal(nb, ob) and torch.equal(ni, oi) and torch.equal(ns, os_)):
+            raise RuntimeError("sharded search: fused exchange and NCCL all-gather + merge disagree")
 
     # ---- max over ranks ----
     t = torch.tensor([ms, e2e_s, bf_ms], dtype=torch.float64, device=dev)
@@ -470,7 +496,11 @@ def run_ours(args):
             "keypoints_per_frame": float(counts.mean()),
             "latency_ms_single_frame_e2e": lat_ms,
             "hamming": {"pairs_per_s": world * nq * per / (bf_ms * 1e-3), "queries": nq, "db_rows_per_gpu": per,
-                        "ms_per_search": bf_ms, "unit": "descriptor pairs/s"},
+                        "ms_per_search": bf_ms, "unit": "descriptor pairs/s",
+                        "exchange": ("none (one shard)" if world == 1 else
+                                     "fused: k_merge_exchange stores the per-query triples into every peer's buffer over NVLink "
+                                     "P2P and merges; checked equal to NCCL all-gather + merge"),
+                        "nccl_allgather_path_ms_per_search_wall": nccl_ms},
         }
         if world == 1 and not args.no_extra:
             line["configs"] = other_configs(pkg, torch, dev, local)

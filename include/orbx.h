@@ -160,6 +160,34 @@ int orbm_bruteforce(orbm_context* m, const uint8_t* q, int nq, const uint8_t* db
 int orbm_merge_partials(orbm_context* m, const int32_t* best, const int32_t* best_idx, const int32_t* second,
                         int nparts, int nq, int32_t* out_best, int32_t* out_idx, int32_t* out_second);
 
+/* ---- Sharded brute-force search with a fused merge + exchange over peer memory (north_star: "local-map matching shards
+ * ... by query set across 2, 4 and 8 GPUs"; replaces the all-gather + orbm_merge_partials pair).
+ * One process (or context) per GPU.  Each rank creates an exchange buffer, publishes its CUDA IPC handle through any
+ * side channel (torch.distributed / MPI / a pipe), and connects to the peers' handles once.  After that a search is
+ * asynchronous device work only: the rank's shard is searched, one kernel merges the chunk partials, stores the
+ * per-query (best, index, second) triple into every peer's buffer with NVLink P2P stores, waits for the peers' triples
+ * in its own buffer and merges them (same deterministic rule as orbm_merge_partials, so the result equals the
+ * unsharded sequential scan on every rank).  All ranks must call orbm_bruteforce_sharded the same number of times with
+ * the same queries.  Pointers of orbm_bruteforce_sharded are DEVICE pointers; call orbm_sync() before reading. */
+#define ORBM_IPC_HANDLE_BYTES 64
+#define ORBM_MAX_WORLD 16
+int orbm_exchange_create(orbm_context* m, int world, int rank, int nq_max, uint8_t* handle_out /* 64 B or NULL */,
+                         void** local_ptr_out /* or NULL */);
+/* handles: world x ORBM_IPC_HANDLE_BYTES, rank order (the entry of this rank is ignored) */
+int orbm_exchange_connect(orbm_context* m, const uint8_t* handles);
+/* same-process variant (several contexts / GPUs in one process): raw device pointers from orbm_exchange_create */
+int orbm_exchange_connect_local(orbm_context* m, void* const* peer_ptrs);
+void orbm_exchange_destroy(orbm_context* m);
+int orbm_bruteforce_sharded(orbm_context* m, const uint8_t* q, int nq, const uint8_t* db_shard, int ndb_shard, int idx_offset,
+                            int32_t* best, int32_t* best_idx, int32_t* second);
+/* The same in two steps, for callers that overlap other work with the exchange (and for single-GPU protocol tests):
+ * phases = 1 searches the shard and publishes the triples to the peers, phases = 2 waits for the peers' triples of the
+ * latest published search and writes the merged result, phases = 3 is orbm_bruteforce_sharded. */
+int orbm_bruteforce_sharded_phases(orbm_context* m, const uint8_t* q, int nq, const uint8_t* db_shard, int ndb_shard,
+                                   int idx_offset, int32_t* best, int32_t* best_idx, int32_t* second, int phases);
+/* 1 if a sharded search gave up waiting for a peer (the results of that call are invalid) */
+int orbm_exchange_timed_out(orbm_context* m);
+
 /* Frame-side inputs of the windowed searches: Frame::mvKeysUn, mvuRight, mDescriptors, mvpMapPoints occupancy,
  * mGrid (src/Frame.cc:351-370) flattened as CSR with cell (ix, iy) at ix*48+iy, and the grid constants. */
 typedef struct orbm_frame_view {

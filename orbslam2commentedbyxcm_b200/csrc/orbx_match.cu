@@ -189,6 +189,86 @@ __global__ void __launch_bounds__(256) k_merge_partials(const int32_t* __restric
 }
 
 // ------------------------------------------------------------------------------------------------------
+// Sharded search, fused merge + exchange over peer memory (NVLink / NVSwitch P2P stores, no NCCL call on the data path).
+// Every rank owns an exchange buffer that all peers have mapped: slots[parity][source rank][query] of one 64-bit word
+//   epoch (14 bits) << 50 | best (9) << 41 | second (9) << 32 | index (32).
+// One warp per query merges the rank's chunk partials, lanes 0..world-1 store the packed triple into the slot of this
+// rank in every peer's buffer (one 64-bit store each: payload and "ready" flag travel in the same word, so no fence or
+// separate signal is needed), then spin on the `world` slots of the query in the local buffer until they carry the
+// current epoch and merge them in the same deterministic way as k_merge_partials.  Slots alternate between two sets by
+// epoch parity: a peer may already be writing call k+1 while this rank still reads call k.  The grid is one CTA per SM
+// (persistent, always co-resident), the spin is bounded by a cycle budget and reports a timeout instead of hanging.
+// ------------------------------------------------------------------------------------------------------
+constexpr int BFX_MAX_WORLD = 16;
+struct BfxPeers { unsigned long long* p[BFX_MAX_WORLD]; };
+
+__global__ void __launch_bounds__(256) k_merge_exchange(const int32_t* __restrict__ pBest, const int32_t* __restrict__ pIdx,
+                                                        const int32_t* __restrict__ pSecond, int nparts, int nq, int nqMax,
+                                                        const __grid_constant__ BfxPeers peers, int rank, int world, uint32_t epoch,
+                                                        long long spinBudget, int* __restrict__ timeoutFlag,
+                                                        int32_t* __restrict__ oBest, int32_t* __restrict__ oIdx,
+                                                        int32_t* __restrict__ oSecond, int phases)
+{
+    // phases: 1 = publish (merge the chunk partials, store to the peers), 2 = collect (wait, merge, write the result),
+    // 3 = both (the normal, fused call)
+    const int lane = threadIdx.x & 31;
+    const int warpsTotal = gridDim.x * (blockDim.x >> 5);
+    const unsigned long long ep = (unsigned long long)(epoch & 0x3fffu);
+    const size_t setOff = (size_t)(epoch & 1u) * world * nqMax;
+    for (int qi = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; qi < nq; qi += warpsTotal) {
+        BfTriple acc = {256, -1, 256};
+        if (phases & 1) {
+            for (int p = lane; p < nparts; p += 32) {
+                const size_t o = (size_t)p * nq + qi;
+                BfTriple t = {pBest[o], pIdx[o], pSecond[o]};
+                acc = bf_merge(acc, t);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                BfTriple t;
+                t.b = __shfl_xor_sync(0xffffffffu, acc.b, o);
+                t.id = __shfl_xor_sync(0xffffffffu, acc.id, o);
+                t.s = __shfl_xor_sync(0xffffffffu, acc.s, o);
+                acc = bf_merge(acc, t);
+            }
+            if (lane < world) {
+                const unsigned long long word = (ep << 50) | ((unsigned long long)(uint32_t)acc.b << 41) |
+                                                ((unsigned long long)(uint32_t)acc.s << 32) | (unsigned long long)(uint32_t)acc.id;
+                // lane p -> peer p: slot of `rank` for this query
+                asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(peers.p[lane] + setOff + (size_t)rank * nqMax + qi), "l"(word) : "memory");
+            }
+        }
+        if (!(phases & 2)) continue;
+        BfTriple mine = {256, -1, 256};
+        if (lane < world) {
+            // lane p <- slot of rank p in the local buffer
+            const unsigned long long* slot = peers.p[rank] + setOff + (size_t)lane * nqMax + qi;
+            unsigned long long v;
+            const long long t0 = clock64();
+            for (;;) {
+                asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(slot) : "memory");
+                if ((v >> 50) == ep) break;
+                if (clock64() - t0 > spinBudget) { *timeoutFlag = 1; v = (ep << 50) | (256ull << 41) | (256ull << 32) | 0xffffffffull; break; }
+                __nanosleep(64);
+            }
+            mine.b = (int)((v >> 41) & 0x1ffu);
+            mine.s = (int)((v >> 32) & 0x1ffu);
+            mine.id = (int)(uint32_t)(v & 0xffffffffull);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            BfTriple t;
+            t.b = __shfl_xor_sync(0xffffffffu, mine.b, o);
+            t.id = __shfl_xor_sync(0xffffffffu, mine.id, o);
+            t.s = __shfl_xor_sync(0xffffffffu, mine.s, o);
+            mine = bf_merge(mine, t);
+        }
+        if (lane == 0) { oBest[qi] = mine.b; oIdx[qi] = mine.id; oSecond[qi] = mine.s; }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
 // two-smallest tracking on packed keys (dist << 20 | visit order) with a payload for the best entry
 // ------------------------------------------------------------------------------------------------------
 struct Top2 {
@@ -1048,6 +1128,15 @@ struct orbm_context {
     size_t partialsBytes = 0;
     void* pinned = nullptr;
     size_t pinnedBytes = 0;
+    // sharded search: exchange buffer mapped by every peer (orbm_exchange_*)
+    unsigned long long* xchg = nullptr;
+    size_t xchgBytes = 0;
+    unsigned long long* xchgPeers[16] = {};
+    bool xchgOpenedIpc[16] = {};
+    bool xchgConnected = false;
+    int world = 0, rank = 0, nqMax = 0;
+    uint32_t epoch = 0;
+    int* xchgTimeout = nullptr;  // mapped pinned host int, written by the kernel when a peer never answered
 };
 
 namespace {
@@ -1114,11 +1203,14 @@ int orbm_create(int device, orbm_context** out)
     return ORBX_OK;
 }
 
+static void exchange_release(orbm_context* m);
+
 void orbm_destroy(orbm_context* m)
 {
     if (!m) return;
     cudaSetDevice(m->device);
     if (m->stream) cudaStreamSynchronize(m->stream);
+    exchange_release(m);
     cudaFree(m->arena); cudaFree(m->partials);
     if (m->pinned) cudaFreeHost(m->pinned);
     if (m->stream) cudaStreamDestroy(m->stream);
@@ -1135,8 +1227,8 @@ int orbm_sync(orbm_context* m)
     return ORBX_OK;
 }
 
-static int bruteforce_device(orbm_context* m, const uint8_t* dq, int nq, const uint8_t* ddb, int ndb, int idxOffset,
-                             int32_t* dBest, int32_t* dIdx, int32_t* dSecond)
+// chunk partials of one database (shard) into m->partials: [best | idx | second][chunk][nq]
+static int bruteforce_partials(orbm_context* m, const uint8_t* dq, int nq, const uint8_t* ddb, int ndb, int idxOffset, int* nChunksOut)
 {
     const int qBlocks = (nq + BF_T * BF_RQ - 1) / (BF_T * BF_RQ);
     // enough chunks to fill the GPU ~4 CTAs per SM, each chunk a multiple of the tile and below 2^22 rows
@@ -1158,6 +1250,20 @@ static int bruteforce_device(orbm_context* m, const uint8_t* dq, int nq, const u
     else if (variant == 3) k_bruteforce<3><<<grid, BF_T, 0, m->stream>>>(dq, nq, ddb, ndb, chunk, idxOffset, pBest, pIdx, pSecond);
     else if (variant == 4) k_bruteforce<4><<<grid, BF_T, 0, m->stream>>>(dq, nq, ddb, ndb, chunk, idxOffset, pBest, pIdx, pSecond);
     else k_bruteforce<2><<<grid, BF_T, 0, m->stream>>>(dq, nq, ddb, ndb, chunk, idxOffset, pBest, pIdx, pSecond);
+    ORBX_CUDA_TRY(cudaGetLastError());
+    *nChunksOut = nChunks;
+    return ORBX_OK;
+}
+
+static int bruteforce_device(orbm_context* m, const uint8_t* dq, int nq, const uint8_t* ddb, int ndb, int idxOffset,
+                             int32_t* dBest, int32_t* dIdx, int32_t* dSecond)
+{
+    int nChunks = 0;
+    int rc = bruteforce_partials(m, dq, nq, ddb, ndb, idxOffset, &nChunks);
+    if (rc != ORBX_OK) return rc;
+    const int32_t* pBest = m->partials;
+    const int32_t* pIdx = pBest + (size_t)nChunks * nq;
+    const int32_t* pSecond = pIdx + (size_t)nChunks * nq;
     k_merge_partials<<<(nq + 7) / 8, 256, 0, m->stream>>>(pBest, pIdx, pSecond, nChunks, nq, dBest, dIdx, dSecond);
     ORBX_CUDA_TRY(cudaGetLastError());
     return ORBX_OK;
@@ -1202,6 +1308,139 @@ int orbm_merge_partials(orbm_context* m, const int32_t* best, const int32_t* bes
     ORBX_CUDA_TRY(cudaGetLastError());
     return ORBX_OK;
 }
+
+// ---- sharded search over peer memory -------------------------------------------------------------------------------
+static void exchange_release(orbm_context* m)
+{
+    for (int r = 0; r < 16; r++) {
+        if (m->xchgOpenedIpc[r] && m->xchgPeers[r]) cudaIpcCloseMemHandle(m->xchgPeers[r]);
+        m->xchgPeers[r] = nullptr;
+        m->xchgOpenedIpc[r] = false;
+    }
+    if (m->xchg) cudaFree(m->xchg);
+    m->xchg = nullptr;
+    m->xchgBytes = 0;
+    if (m->xchgTimeout) cudaFreeHost(m->xchgTimeout);
+    m->xchgTimeout = nullptr;
+    m->xchgConnected = false;
+    m->world = 0;
+}
+
+int orbm_exchange_create(orbm_context* m, int world, int rank, int nq_max, uint8_t* handle_out, void** local_ptr_out)
+{
+    if (!m || world < 1 || world > BFX_MAX_WORLD || rank < 0 || rank >= world || nq_max <= 0) {
+        set_error("orbm_exchange_create: bad argument (world 1..%d)", BFX_MAX_WORLD);
+        return ORBX_ERR_BAD_ARG;
+    }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    exchange_release(m);
+    m->xchgBytes = sizeof(unsigned long long) * 2 * (size_t)world * nq_max;
+    ORBX_CUDA_TRY(cudaMalloc(&m->xchg, m->xchgBytes));
+    ORBX_CUDA_TRY(cudaMemset(m->xchg, 0, m->xchgBytes));  // epoch 0 = "never written"; calls start at epoch 1
+    ORBX_CUDA_TRY(cudaHostAlloc(&m->xchgTimeout, sizeof(int), cudaHostAllocMapped));
+    *m->xchgTimeout = 0;
+    m->world = world; m->rank = rank; m->nqMax = nq_max; m->epoch = 0;
+    m->xchgPeers[rank] = m->xchg;
+    if (handle_out) {
+        cudaIpcMemHandle_t hnd;
+        static_assert(sizeof(hnd) == ORBM_IPC_HANDLE_BYTES, "handle size");
+        ORBX_CUDA_TRY(cudaIpcGetMemHandle(&hnd, m->xchg));
+        memcpy(handle_out, &hnd, sizeof hnd);
+    }
+    if (local_ptr_out) *local_ptr_out = m->xchg;
+    m->xchgConnected = world == 1;
+    return ORBX_OK;
+}
+
+int orbm_exchange_connect(orbm_context* m, const uint8_t* handles)
+{
+    if (!m || !m->xchg || !handles) { set_error("orbm_exchange_connect: create the exchange first"); return ORBX_ERR_BAD_ARG; }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    for (int r = 0; r < m->world; r++) {
+        if (r == m->rank) continue;
+        cudaIpcMemHandle_t hnd;
+        memcpy(&hnd, handles + (size_t)r * ORBM_IPC_HANDLE_BYTES, sizeof hnd);
+        void* p = nullptr;
+        ORBX_CUDA_TRY(cudaIpcOpenMemHandle(&p, hnd, cudaIpcMemLazyEnablePeerAccess));
+        m->xchgPeers[r] = (unsigned long long*)p;
+        m->xchgOpenedIpc[r] = true;
+    }
+    m->xchgConnected = true;
+    return ORBX_OK;
+}
+
+int orbm_exchange_connect_local(orbm_context* m, void* const* peer_ptrs)
+{
+    if (!m || !m->xchg || !peer_ptrs) { set_error("orbm_exchange_connect_local: create the exchange first"); return ORBX_ERR_BAD_ARG; }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    for (int r = 0; r < m->world; r++) {
+        if (r == m->rank) continue;
+        if (!peer_ptrs[r]) { set_error("orbm_exchange_connect_local: null pointer for rank %d", r); return ORBX_ERR_BAD_ARG; }
+        cudaPointerAttributes a;
+        ORBX_CUDA_TRY(cudaPointerGetAttributes(&a, peer_ptrs[r]));
+        if (a.type == cudaMemoryTypeDevice && a.device != m->device) {
+            cudaError_t e = cudaDeviceEnablePeerAccess(a.device, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+            else if (e != cudaSuccess) { set_error("peer access %d -> %d: %s", m->device, a.device, cudaGetErrorString(e)); return ORBX_ERR_CUDA; }
+        }
+        m->xchgPeers[r] = (unsigned long long*)peer_ptrs[r];
+    }
+    m->xchgConnected = true;
+    return ORBX_OK;
+}
+
+void orbm_exchange_destroy(orbm_context* m)
+{
+    if (!m) return;
+    cudaSetDevice(m->device);
+    if (m->stream) cudaStreamSynchronize(m->stream);
+    exchange_release(m);
+}
+
+int orbm_bruteforce_sharded(orbm_context* m, const uint8_t* q, int nq, const uint8_t* db, int ndb, int idx_offset,
+                            int32_t* best, int32_t* best_idx, int32_t* second)
+{
+    return orbm_bruteforce_sharded_phases(m, q, nq, db, ndb, idx_offset, best, best_idx, second, 3);
+}
+
+int orbm_bruteforce_sharded_phases(orbm_context* m, const uint8_t* q, int nq, const uint8_t* db, int ndb, int idx_offset,
+                                   int32_t* best, int32_t* best_idx, int32_t* second, int phases)
+{
+    const bool pub = phases & 1, col = phases & 2;
+    if (!m || nq <= 0 || !(pub || col) || (pub && (!q || ndb < 0 || (ndb > 0 && !db))) || (col && (!best || !best_idx || !second))) {
+        set_error("orbm_bruteforce_sharded: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    if (!m->xchg || !m->xchgConnected) { set_error("orbm_bruteforce_sharded: exchange not created / connected"); return ORBX_ERR_BAD_ARG; }
+    if (nq > m->nqMax) { set_error("orbm_bruteforce_sharded: nq %d > nq_max %d of the exchange", nq, m->nqMax); return ORBX_ERR_CAPACITY; }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    if (*m->xchgTimeout) { set_error("orbm_bruteforce_sharded: an earlier call timed out waiting for a peer"); return ORBX_ERR_CUDA; }
+    int nChunks = 0;
+    if (pub) {
+        int rc = bruteforce_partials(m, q, nq, db, ndb, idx_offset, &nChunks);
+        if (rc != ORBX_OK) return rc;
+        m->epoch++;
+    } else if (m->epoch == 0) {
+        set_error("orbm_bruteforce_sharded: collect without a preceding publish");
+        return ORBX_ERR_BAD_ARG;
+    }
+    const int32_t* pBest = m->partials;
+    const int32_t* pIdx = pBest + (size_t)nChunks * nq;
+    const int32_t* pSecond = pIdx + (size_t)nChunks * nq;
+    BfxPeers peers;
+    for (int r = 0; r < BFX_MAX_WORLD; r++) peers.p[r] = r < m->world ? m->xchgPeers[r] : nullptr;
+    int* dTimeout = nullptr;
+    ORBX_CUDA_TRY(cudaHostGetDevicePointer(&dTimeout, m->xchgTimeout, 0));
+    static const long long budget = [] { const char* e = std::getenv("ORBX_EXCHANGE_SPIN_CYCLES"); return e ? std::atoll(e) : 20000000000LL; }();
+    const int grid = std::max(1, std::min(m->numSMs, (nq + 7) / 8));
+    k_merge_exchange<<<grid, 256, 0, m->stream>>>(pBest, pIdx, pSecond, nChunks, nq, m->nqMax, peers, m->rank, m->world, m->epoch, budget,
+                                                  dTimeout, best, best_idx, second, phases);
+    ORBX_CUDA_TRY(cudaGetLastError());
+    return ORBX_OK;
+}
+
+int orbm_exchange_timed_out(orbm_context* m) { return m && m->xchgTimeout ? *m->xchgTimeout : 0; }
 
 int orbm_search_window(orbm_context* m, const orbm_frame_view* f, const float* f_angle, const orbm_window_query_view* q,
                        int max_dist, int ratio_mode, float nnratio, int check_orientation, int32_t* out_match, int* nmatches)

@@ -97,6 +97,50 @@ class ORBmatcher:
         check(self._L.orbm_merge_partials(self._m, d_best, d_idx, d_second, nparts, nq, o_best, o_idx, o_second),
               "orbm_merge_partials")
 
+    # ---- sharded brute force with the fused merge + exchange over peer memory (include/orbx.h) ----
+    def exchange_create(self, world, rank, nq_max):
+        """Allocates this rank's exchange buffer; returns (ipc_handle_bytes, local_device_pointer)."""
+        import ctypes
+
+        handle = (ctypes.c_uint8 * 64)()
+        ptr = ctypes.c_void_p()
+        check(self._L.orbm_exchange_create(self._m, world, rank, nq_max, ctypes.addressof(handle), ctypes.addressof(ptr)),
+              "orbm_exchange_create")
+        return bytes(handle), ptr.value
+
+    def exchange_connect(self, handles):
+        """handles: list of `world` 64-byte IPC handles in rank order (other processes on the same node)."""
+        blob = b"".join(handles)
+        buf = np.frombuffer(blob, np.uint8).copy()
+        check(self._L.orbm_exchange_connect(self._m, buf.ctypes.data), "orbm_exchange_connect")
+
+    def exchange_connect_local(self, ptrs):
+        """ptrs: list of `world` device pointers (contexts of the same process)."""
+        arr = np.asarray([p or 0 for p in ptrs], np.uint64)
+        check(self._L.orbm_exchange_connect_local(self._m, arr.ctypes.data), "orbm_exchange_connect_local")
+
+    def exchange_connect_group(self, world, rank, nq_max, group=None):
+        """Convenience for one process per GPU under torch.distributed: create, all-gather the handles, connect."""
+        import torch.distributed as dist
+
+        handle, _ = self.exchange_create(world, rank, nq_max)
+        handles = [None] * world
+        dist.all_gather_object(handles, handle, group=group)
+        if world > 1:
+            self.exchange_connect(handles)
+
+    def exchange_destroy(self):
+        self._L.orbm_exchange_destroy(self._m)
+
+    def bruteforce_sharded_device(self, dq, nq, ddb, ndb, idx_offset, d_best, d_idx, d_second, phases=3):
+        """Asynchronous on the context's stream; every rank ends up with the merged result of all shards.
+        phases: 3 = fused call, 1 = search + publish only, 2 = collect only (see include/orbx.h)."""
+        check(self._L.orbm_bruteforce_sharded_phases(self._m, dq, nq, ddb, ndb, idx_offset, d_best, d_idx, d_second, phases),
+              "orbm_bruteforce_sharded")
+
+    def exchange_timed_out(self):
+        return bool(self._L.orbm_exchange_timed_out(self._m))
+
     # ---- SearchByProjection(Frame&, vector<MapPoint*>&, th) ----
     def SearchByProjection(self, frame, mps, th=3.0):
         keep = []
