@@ -580,7 +580,9 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
 // Keys never move: each key carries the list position of its node, so node sizes are atomics and the final
 // "max response, first in candidate order" pick is one atomicMax on (response << 24 | ~ord).
 // ------------------------------------------------------------------------------------------------------
-constexpr int OCT_T = 512;
+// Threads per (level, frame) CTA = template parameter OCT_T.  The kernel is barrier-latency bound: for batches, many small
+// CTAs per SM (128 threads, 8 resident) give the best throughput (0.145 -> 0.092 ms per 256 frames against two CTAs of 512);
+// a single frame is fastest with 512 threads per level.
 
 struct OctSmem {
     short4* geoA; short4* geoB;       // node rectangles (ulx, uly, brx, bry), list order, double buffered
@@ -609,6 +611,7 @@ __device__ __forceinline__ int warp_incl_scan(int v)
 }
 
 // in-place exclusive scan of data[0..n); returns the total.  All threads of the CTA must call it.
+template <int OCT_T>
 __device__ int block_exscan(int* data, int n, int* warpSums)
 {
     const int ipt = (n + OCT_T - 1) / OCT_T;
@@ -677,6 +680,7 @@ __device__ __forceinline__ constexpr int umax_of(int av)
     return (int)((0x3689ABCDDEEEFFFFull >> (4 * av)) & 15ull);
 }
 
+template <int OCT_T>
 __global__ void __launch_bounds__(OCT_T) k_octree(Plan plan, Buffers buf, int nodeCapMax, int keySmemCap,
                                                   unsigned short* keyNodeGlobal, long long keyNodeFrameStride)
 {
@@ -751,7 +755,7 @@ __global__ void __launch_bounds__(OCT_T) k_octree(Plan plan, Buffers buf, int no
     // drop empty roots, keep order
     for (int i = tid; i < nIni; i += OCT_T) S.scanA[i] = S.cntB[i] > 0;
     __syncthreads();
-    int n = block_exscan(S.scanA, nIni, warpSums);
+    int n = block_exscan<OCT_T>(S.scanA, nIni, warpSums);
     for (int i = tid; i < nIni; i += OCT_T)
         if (S.cntB[i] > 0) { S.geoA[S.scanA[i]] = S.geoB[i]; S.cntA[S.scanA[i]] = S.cntB[i]; S.nodePos[i] = (unsigned short)S.scanA[i]; }
     __syncthreads();
@@ -787,8 +791,8 @@ __global__ void __launch_bounds__(OCT_T) k_octree(Plan plan, Buffers buf, int no
             S.scanB[i] = cnt[i] > 1 ? 0 : 1;
         }
         __syncthreads();
-        const int totA = block_exscan(S.scanA, n, warpSums);
-        const int totB = block_exscan(S.scanB, n, warpSums);
+        const int totA = block_exscan<OCT_T>(S.scanA, n, warpSums);
+        const int totB = block_exscan<OCT_T>(S.scanB, n, warpSums);
         const int C = totA & 0xffff, nToExpand = totA >> 16;
         const int nNew = C + totB;
         // (capacity: nNew <= max(N, 4*nIni) <= nodeCap by construction)
@@ -876,7 +880,7 @@ __global__ void __launch_bounds__(OCT_T) k_octree(Plan plan, Buffers buf, int no
                 }
                 if (tid == 0) sCut = nV - 1;
                 __syncthreads();
-                block_exscan(S.scanA, nV, warpSums);
+                block_exscan<OCT_T>(S.scanA, nV, warpSums);
                 // inclusive gain after processing p: (excl[p] + nch_p) - (p + 1)
                 for (int p = tid; p < nV; p += OCT_T) {
                     const int s = S.slotOfProc[p];
@@ -900,7 +904,7 @@ __global__ void __launch_bounds__(OCT_T) k_octree(Plan plan, Buffers buf, int no
                 }
                 __syncthreads();
                 const int Ctot = sCtot;
-                const int keepOld = block_exscan(S.scanB, n, warpSums);
+                const int keepOld = block_exscan<OCT_T>(S.scanB, n, warpSums);
                 const int nNew2 = Ctot + keepOld;
                 // new expandable list (creation order) needs its own prefix over processing ranks
                 for (int p = tid; p < nV; p += OCT_T) {
@@ -913,7 +917,7 @@ __global__ void __launch_bounds__(OCT_T) k_octree(Plan plan, Buffers buf, int no
                     S.winner[p] = nex;  // scratch
                 }
                 __syncthreads();
-                const int nVnew = block_exscan(S.winner, nV, warpSums);
+                const int nVnew = block_exscan<OCT_T>(S.winner, nV, warpSums);
                 for (int p = tid; p <= cut; p += OCT_T) {
                     const int s = S.slotOfProc[p];
                     const int i = V[s];
@@ -1286,9 +1290,10 @@ struct orbx_handle {
     short* dTabs = nullptr;
     unsigned short* dKeyNode = nullptr;
     FastUnit* dFastUnits = nullptr;
-    int octNodeCap = 0, octKeySmemCap = 0;
+    int octNodeCap = 0;
+    int octKeySmemCap[3] = {0, 0, 0};  // per k_octree variant: 128, 256, 512 threads
     size_t fastSmem = 0;
-    size_t octSmem = 0;
+    size_t octSmem[3] = {0, 0, 0};
     int lastFrames = 0;
     int plainRuns = 0;           // batches enqueued without a graph since the plan was (re)built
     bool profiling = false;
@@ -1540,14 +1545,23 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
         set_error("quad-tree node arrays (%zu B) exceed shared memory (%d B)", nodeBytes, devSmem);
         return ORBX_ERR_BAD_ARG;
     }
-    // keys in shared memory when they fit in what is left, capped so that several CTAs stay resident
-    size_t keyBudget = std::min<size_t>((size_t)devSmem - nodeBytes - 1024, 64 * 1024);
-    int keyCap = (int)std::min<size_t>(keyBudget / 2, (size_t)candCapMax);
-    keyCap &= ~7;
+    // keys in shared memory when they fit in what is left, capped so that 1024 threads' worth of CTAs stay resident per SM
+    // (the register file allows about that many at 58 registers per thread)
     h->octNodeCap = nodeCapMax;
-    h->octKeySmemCap = keyCap;
-    h->octSmem = nodeBytes + 2 * (size_t)keyCap + 16;
-    ORBX_CUDA_TRY(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->octSmem));
+    for (int v = 0; v < 3; v++) {
+        const int T = 128 << v;
+        const size_t ctasPerSM = 1024 / T;
+        const size_t perCta = (size_t)(228 * 1024) / ctasPerSM - 1024;
+        size_t keyBudget = perCta > nodeBytes + 4096 ? perCta - nodeBytes - 1024 : 4096;
+        keyBudget = std::min<size_t>(std::min<size_t>(keyBudget, (size_t)devSmem - nodeBytes - 1024), 64 * 1024);
+        int keyCap = (int)std::min<size_t>(keyBudget / 2, (size_t)candCapMax);
+        keyCap &= ~7;
+        h->octKeySmemCap[v] = keyCap;
+        h->octSmem[v] = nodeBytes + 2 * (size_t)keyCap + 16;
+    }
+    ORBX_CUDA_TRY(cudaFuncSetAttribute(k_octree<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->octSmem[0]));
+    ORBX_CUDA_TRY(cudaFuncSetAttribute(k_octree<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->octSmem[1]));
+    ORBX_CUDA_TRY(cudaFuncSetAttribute(k_octree<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->octSmem[2]));
     h->fastSmem = 2 * (size_t)P.fastTileBytes + 2 * ((size_t)FAST_Q1CAP + (size_t)P.fastQCap);
     ORBX_CUDA_TRY(cudaFuncSetAttribute(k_fast_band, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fastSmem));
     ORBX_CUDA_TRY(cudaMalloc(&h->dKeyNode, sizeof(unsigned short) * (size_t)P.candFrame * cap));
@@ -1596,7 +1610,10 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
     k_fast_band<<<dim3(P.totalFastUnits, n), FAST_T, h->fastSmem, s>>>(P, B);
     nl++;
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_OCTREE], s));
-    k_octree<<<dim3(P.nlevels, n), OCT_T, h->octSmem, s>>>(P, B, h->octNodeCap, h->octKeySmemCap, h->dKeyNode, P.candFrame);
+    // batches: many small CTAs per SM (throughput); a few frames: more threads per level (latency)
+    if (n >= 16) k_octree<128><<<dim3(P.nlevels, n), 128, h->octSmem[0], s>>>(P, B, h->octNodeCap, h->octKeySmemCap[0], h->dKeyNode, P.candFrame);
+    else if (n >= 4) k_octree<256><<<dim3(P.nlevels, n), 256, h->octSmem[1], s>>>(P, B, h->octNodeCap, h->octKeySmemCap[1], h->dKeyNode, P.candFrame);
+    else k_octree<512><<<dim3(P.nlevels, n), 512, h->octSmem[2], s>>>(P, B, h->octNodeCap, h->octKeySmemCap[2], h->dKeyNode, P.candFrame);
     nl++;
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_BLUR], s));
     k_blur<<<dim3(P.totalBlurUnits, n), 128, 0, sb>>>(P, B);
