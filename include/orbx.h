@@ -383,6 +383,21 @@ int orbm_bow_transform(orbm_context* m, const orbm_vocab* v, const uint8_t* desc
 int orbm_distinctive_descriptors(orbm_context* m, int n_sets, const int32_t* set_start, const uint8_t* desc,
                                  int32_t* best_idx);
 
+/* Frame preparation between extraction and matching ("next" row).  mem_kind 0 = HOST pointers
+ * (synchronous), 1 = DEVICE pointers (asynchronous on the context's stream), as in orbm_bruteforce.
+ *
+ * orbm_undistort_keypoints replaces Frame::UndistortKeyPoints (src/Frame.cc:586-628): copies the coordinates when
+ * dist[0] == 0 (:589-592), else cv::undistortPoints(pts, K, dist, R = I, P = K) -- 5 iterations in double, result
+ * narrowed to float; `dist` = (k1, k2, p1, p2[, k3[, k4, k5, k6[, s1..s4]]]) is always a HOST array (mDistCoef).
+ *
+ * orbm_assign_grid replaces Frame::AssignFeaturesToGrid + PosInGrid (:351-370, :558-567): the 64 x 48 mGrid as CSR
+ * (cell (ix, iy) at ix * 48 + iy; cell_start has 64*48+1 entries, cell_items n), indices ascending inside a cell --
+ * the layout orbm_frame_view takes. */
+int orbm_undistort_keypoints(orbm_context* m, const float* x, const float* y, int n, float fx, float fy, float cx, float cy,
+                             const float* dist, int ndist, float* xu, float* yu, int mem_kind);
+int orbm_assign_grid(orbm_context* m, const float* x, const float* y, int n, float min_x, float min_y, float grid_w_inv,
+                     float grid_h_inv, int32_t* cell_start, int32_t* cell_items, int mem_kind);
+
 #ifdef __cplusplus
 }
 #endif

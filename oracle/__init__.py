@@ -301,6 +301,22 @@ def assign_grid(kx, ky, min_x, min_y, w_inv, h_inv):
     return start, items[: start[-1]].copy()
 
 
+def undistort_points(x, y, fx, fy, cx, cy, dist):
+    """Frame::UndistortKeyPoints (src/Frame.cc:586-628) = cv::undistortPoints(pts, K, dist, R=I, P=K), restated."""
+    L = lib()
+    x = np.ascontiguousarray(x, np.float32)
+    y = np.ascontiguousarray(y, np.float32)
+    dist = np.ascontiguousarray(dist, np.float32)
+    ox, oy = np.empty_like(x), np.empty_like(y)
+    L.orbo_undistort_points.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_float,
+                                        ctypes.c_float, ctypes.c_float, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
+                                        ctypes.c_void_p]
+    L.orbo_undistort_points.restype = None
+    L.orbo_undistort_points(x.ctypes.data, y.ctypes.data, len(x), fx, fy, cx, cy, dist.ctypes.data, len(dist),
+                            ox.ctypes.data, oy.ctypes.data)
+    return ox, oy
+
+
 def search_by_projection(frame, mps, th, nnratio, kind="strict"):
     """frame / mps: dicts of numpy arrays (see orbslam2commentedbyxcm_b200.matcher for the field names)."""
     L = lib(kind)

@@ -92,6 +92,41 @@ void orbo_assign_grid(const float* kx, const float* ky, int n, float minX, float
     cell_start[GRID_COLS * GRID_ROWS] = off;
 }
 
+// Frame::UndistortKeyPoints (src/Frame.cc:586-628): mvKeysUn = mvKeys when mDistCoef(0) == 0, else
+// cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK).  OpenCV is not vendored by the reference; this restates
+// cvUndistortPointsInternal of OpenCV 4.x for that call (R = identity, P = K, default criteria = 5 iterations, no
+// tilt terms): everything in double, K and the coefficients widened from float, result narrowed to float.
+// Pinned bit-for-bit against cv2 4.13 (tests/test_oracle_primitives.py, tests/golden/undistort_cv2.npz).
+void orbo_undistort_points(const float* px, const float* py, int n, float fxf, float fyf, float cxf, float cyf,
+                           const float* dist, int ndist, float* ox, float* oy)
+{
+    if (ndist <= 0 || dist[0] == 0.0f) {  // src/Frame.cc:589-592
+        for (int i = 0; i < n; i++) { ox[i] = px[i]; oy[i] = py[i]; }
+        return;
+    }
+    double k[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // k1 k2 p1 p2 k3 k4 k5 k6 s1 s2 s3 s4
+    for (int i = 0; i < ndist && i < 12; i++) k[i] = (double)dist[i];
+    const double fx = fxf, fy = fyf, cx = cxf, cy = cyf;
+    const double ifx = 1. / fx, ify = 1. / fy;
+    for (int i = 0; i < n; i++) {
+        const double u = px[i], v = py[i];
+        double x = (u - cx) * ifx, y = (v - cy) * ify;
+        const double x0 = x, y0 = y;
+        for (int j = 0; j < 5; j++) {
+            const double r2 = x * x + y * y;
+            const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+            if (icdist < 0) { x = (u - cx) * ifx; y = (v - cy) * ify; break; }
+            const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+            const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+            x = (x0 - deltaX) * icdist;
+            y = (y0 - deltaY) * icdist;
+        }
+        // P * R = K: xx = fx*x + 0*y + cx, yy = 0*x + fy*y + cy, ww = 1 / (0*x + 0*y + 1)
+        ox[i] = (float)((fx * x + cx) * 1.0);
+        oy[i] = (float)((fy * y + cy) * 1.0);
+    }
+}
+
 // SearchByProjection(Frame&, vector<MapPoint*>&, th).  out_match[idx] = index of the map point written into
 // F.mvpMapPoints[idx] by this call (the last writer), or -1 when untouched.  Returns nmatches.
 int orbo_search_by_projection(

@@ -84,6 +84,8 @@ SIGNATURES = {
     "orbm_sync": (_i, [_vp]),
     "orbm_bruteforce": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _i]),
     "orbm_merge_partials": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]),
+    "orbm_undistort_keypoints": (_i, [_vp, _vp, _vp, _i, _f, _f, _f, _f, _vp, _i, _vp, _vp, _i]),
+    "orbm_assign_grid": (_i, [_vp, _vp, _vp, _i, _f, _f, _f, _f, _vp, _vp, _i]),
     "orbm_exchange_create": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "orbm_exchange_connect": (_i, [_vp, _vp]),
     "orbm_exchange_connect_local": (_i, [_vp, _vp]),

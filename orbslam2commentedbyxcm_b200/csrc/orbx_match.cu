@@ -189,6 +189,119 @@ __global__ void __launch_bounds__(256) k_merge_partials(const int32_t* __restric
 }
 
 // ------------------------------------------------------------------------------------------------------
+// Frame::UndistortKeyPoints (src/Frame.cc:586-628) = cv::undistortPoints(pts, K, dist, R = I, P = K): 5 fixed-point
+// iterations of the inverse Brown model in double, one thread per keypoint; every operation is an explicitly rounded
+// intrinsic (no FMA contraction) so that the result is the CPU's, bit for bit (oracle: orbo_undistort_points).
+// ------------------------------------------------------------------------------------------------------
+struct UndistortCam { double fx, fy, cx, cy, k[12]; };
+
+__global__ void __launch_bounds__(128) k_undistort(const float* __restrict__ px, const float* __restrict__ py, int n,
+                                                   UndistortCam c, float* __restrict__ ox, float* __restrict__ oy)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double* k = c.k;
+    const double ifx = __ddiv_rn(1.0, c.fx), ify = __ddiv_rn(1.0, c.fy);
+    const double u = (double)px[i], v = (double)py[i];
+    double x = __dmul_rn(__dsub_rn(u, c.cx), ifx), y = __dmul_rn(__dsub_rn(v, c.cy), ify);
+    const double x0 = x, y0 = y;
+#define M_(a, b) __dmul_rn(a, b)
+#define A_(a, b) __dadd_rn(a, b)
+    for (int j = 0; j < 5; j++) {
+        const double r2 = A_(M_(x, x), M_(y, y));
+        const double num = A_(1.0, M_(A_(M_(A_(M_(k[7], r2), k[6]), r2), k[5]), r2));
+        const double den = A_(1.0, M_(A_(M_(A_(M_(k[4], r2), k[1]), r2), k[0]), r2));
+        const double icdist = __ddiv_rn(num, den);
+        if (icdist < 0) { x = x0; y = y0; break; }
+        // 2*k2*x*y + k3*(r2 + 2*x*x) + k8*r2 + k9*r2*r2, left to right as the C++ expression evaluates
+        const double deltaX = A_(A_(A_(M_(M_(M_(2.0, k[2]), x), y), M_(k[3], A_(r2, M_(M_(2.0, x), x)))), M_(k[8], r2)), M_(M_(k[9], r2), r2));
+        const double deltaY = A_(A_(A_(M_(k[2], A_(r2, M_(M_(2.0, y), y))), M_(M_(M_(2.0, k[3]), x), y)), M_(k[10], r2)), M_(M_(k[11], r2), r2));
+        x = M_(__dsub_rn(x0, deltaX), icdist);
+        y = M_(__dsub_rn(y0, deltaY), icdist);
+    }
+    ox[i] = (float)A_(M_(c.fx, x), c.cx);
+    oy[i] = (float)A_(M_(c.fy, y), c.cy);
+#undef M_
+#undef A_
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Frame::AssignFeaturesToGrid / PosInGrid (src/Frame.cc:351-370, :558-567): 64 x 48 grid as CSR, cell (ix, iy) at
+// ix * 48 + iy, keypoint indices ascending inside a cell (the reference pushes them in index order).  One CTA: cell
+// counts by shared-memory atomics, exclusive scan, scatter in arbitrary order, then every cell's few entries are put
+// in ascending order by one thread.
+// ------------------------------------------------------------------------------------------------------
+constexpr int GRID_CELLS = 64 * 48;
+
+__global__ void __launch_bounds__(1024) k_assign_grid(const float* __restrict__ kx, const float* __restrict__ ky, int n, float minX,
+                                                      float minY, float wInv, float hInv, int32_t* __restrict__ cellStart,
+                                                      int32_t* __restrict__ cellItems)
+{
+    __shared__ int cnt[GRID_CELLS];
+    __shared__ int fill[GRID_CELLS];
+    __shared__ int wsum[33];
+    const int tid = threadIdx.x;
+    for (int c = tid; c < GRID_CELLS; c += 1024) cnt[c] = 0;
+    __syncthreads();
+    auto cell_of = [&](int i) {
+        // posX = round((x - mnMinX) * mfGridElementWidthInv): float arithmetic, round half away from zero
+        const int gx = (int)roundf(__fmul_rn(__fsub_rn(kx[i], minX), wInv));
+        const int gy = (int)roundf(__fmul_rn(__fsub_rn(ky[i], minY), hInv));
+        return (gx < 0 || gx >= 64 || gy < 0 || gy >= 48) ? -1 : gx * 48 + gy;
+    };
+    for (int i = tid; i < n; i += 1024) {
+        const int c = cell_of(i);
+        if (c >= 0) atomicAdd(&cnt[c], 1);
+    }
+    __syncthreads();
+    // exclusive scan of 3072 counts: 3 per thread
+    int v[3], sum = 0;
+#pragma unroll
+    for (int j = 0; j < 3; j++) { v[j] = cnt[3 * tid + j]; sum += v[j]; }
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((tid & 31) >= o) incl += t;
+    }
+    if ((tid & 31) == 31) wsum[tid >> 5] = incl;
+    __syncthreads();
+    if (tid < 32) {
+        const int w = wsum[tid];
+        int wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, wi, o);
+            if (tid >= o) wi += t;
+        }
+        wsum[tid] = wi - w;
+        if (tid == 31) wsum[32] = wi;
+    }
+    __syncthreads();
+    int run = wsum[tid >> 5] + incl - sum;
+#pragma unroll
+    for (int j = 0; j < 3; j++) { fill[3 * tid + j] = run; cellStart[3 * tid + j] = run; run += v[j]; }
+    if (tid == 0) cellStart[GRID_CELLS] = wsum[32];
+    __syncthreads();
+    for (int i = tid; i < n; i += 1024) {
+        const int c = cell_of(i);
+        if (c >= 0) cellItems[atomicAdd(&fill[c], 1)] = i;
+    }
+    __syncthreads();
+    for (int c = tid; c < GRID_CELLS; c += 1024) {
+        const int m = cnt[c];
+        if (m < 2) continue;
+        int32_t* a = cellItems + (fill[c] - m);
+        for (int p = 1; p < m; p++) {  // insertion sort: a cell holds a handful of keypoints
+            const int key = a[p];
+            int q = p - 1;
+            while (q >= 0 && a[q] > key) { a[q + 1] = a[q]; q--; }
+            a[q + 1] = key;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
 // Sharded search, fused merge + exchange over peer memory (NVLink / NVSwitch P2P stores, no NCCL call on the data path).
 // Every rank owns an exchange buffer that all peers have mapped: slots[parity][source rank][query] of one 64-bit word
 //   epoch (14 bits) << 50 | best (9) << 41 | second (9) << 32 | index (32).
@@ -1306,6 +1419,83 @@ int orbm_merge_partials(orbm_context* m, const int32_t* best, const int32_t* bes
     ORBX_CUDA_TRY(cudaSetDevice(m->device));
     k_merge_partials<<<(nq + 7) / 8, 256, 0, m->stream>>>(best, best_idx, second, nparts, nq, out_best, out_idx, out_second);
     ORBX_CUDA_TRY(cudaGetLastError());
+    return ORBX_OK;
+}
+
+// ---- frame preparation between extraction and matching ("next" row) -------------------------------
+int orbm_undistort_keypoints(orbm_context* m, const float* x, const float* y, int n, float fx, float fy, float cx, float cy,
+                             const float* dist, int ndist, float* xu, float* yu, int mem_kind)
+{
+    if (!m || n < 0 || (n > 0 && (!x || !y || !xu || !yu)) || ndist < 0 || ndist > 12 || (ndist > 0 && !dist) || fx == 0.f || fy == 0.f) {
+        set_error("orbm_undistort_keypoints: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    if (n == 0) return ORBX_OK;
+    UndistortCam c;
+    c.fx = fx; c.fy = fy; c.cx = cx; c.cy = cy;
+    for (int i = 0; i < 12; i++) c.k[i] = i < ndist ? (double)dist[i] : 0.0;   // dist is a HOST array in both modes
+    const bool identity = ndist == 0 || dist[0] == 0.0f;                        // src/Frame.cc:589-592: mvKeysUn = mvKeys
+    const size_t bytes = sizeof(float) * (size_t)n;
+    if (mem_kind == 1) {
+        if (identity) {
+            if (xu != x) ORBX_CUDA_TRY(cudaMemcpyAsync(xu, x, bytes, cudaMemcpyDeviceToDevice, m->stream));
+            if (yu != y) ORBX_CUDA_TRY(cudaMemcpyAsync(yu, y, bytes, cudaMemcpyDeviceToDevice, m->stream));
+        } else {
+            k_undistort<<<(n + 127) / 128, 128, 0, m->stream>>>(x, y, n, c, xu, yu);
+            ORBX_CUDA_TRY(cudaGetLastError());
+        }
+        return ORBX_OK;
+    }
+    if (identity) {
+        if (xu != x) memcpy(xu, x, bytes);
+        if (yu != y) memcpy(yu, y, bytes);
+        return ORBX_OK;
+    }
+    Carver cv;
+    const size_t oxi = cv.take(bytes), oyi = cv.take(bytes), oxo = cv.take(bytes), oyo = cv.take(bytes);
+    int rc = ensure_arena(m, cv.off);
+    if (rc != ORBX_OK) return rc;
+    char* A = m->arena;
+    ORBX_CUDA_TRY(cudaMemcpyAsync(A + oxi, x, bytes, cudaMemcpyHostToDevice, m->stream));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(A + oyi, y, bytes, cudaMemcpyHostToDevice, m->stream));
+    k_undistort<<<(n + 127) / 128, 128, 0, m->stream>>>((float*)(A + oxi), (float*)(A + oyi), n, c, (float*)(A + oxo), (float*)(A + oyo));
+    ORBX_CUDA_TRY(cudaGetLastError());
+    ORBX_CUDA_TRY(cudaMemcpyAsync(xu, A + oxo, bytes, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaMemcpyAsync(yu, A + oyo, bytes, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    return ORBX_OK;
+}
+
+int orbm_assign_grid(orbm_context* m, const float* x, const float* y, int n, float min_x, float min_y, float grid_w_inv,
+                     float grid_h_inv, int32_t* cell_start, int32_t* cell_items, int mem_kind)
+{
+    if (!m || n < 0 || (n > 0 && (!x || !y || !cell_items)) || !cell_start) {
+        set_error("orbm_assign_grid: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    if (mem_kind == 1) {
+        k_assign_grid<<<1, 1024, 0, m->stream>>>(x, y, n, min_x, min_y, grid_w_inv, grid_h_inv, cell_start, cell_items);
+        ORBX_CUDA_TRY(cudaGetLastError());
+        return ORBX_OK;
+    }
+    Carver cv;
+    const size_t bytes = sizeof(float) * (size_t)std::max(n, 1);
+    const size_t ox = cv.take(bytes), oy = cv.take(bytes), os = cv.take(4 * (GRID_CELLS + 1)), oi = cv.take(bytes);
+    int rc = ensure_arena(m, cv.off);
+    if (rc != ORBX_OK) return rc;
+    char* A = m->arena;
+    if (n) {
+        ORBX_CUDA_TRY(cudaMemcpyAsync(A + ox, x, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice, m->stream));
+        ORBX_CUDA_TRY(cudaMemcpyAsync(A + oy, y, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice, m->stream));
+    }
+    k_assign_grid<<<1, 1024, 0, m->stream>>>((float*)(A + ox), (float*)(A + oy), n, min_x, min_y, grid_w_inv, grid_h_inv,
+                                             (int32_t*)(A + os), (int32_t*)(A + oi));
+    ORBX_CUDA_TRY(cudaGetLastError());
+    ORBX_CUDA_TRY(cudaMemcpyAsync(cell_start, A + os, 4 * (GRID_CELLS + 1), cudaMemcpyDeviceToHost, m->stream));
+    if (n) ORBX_CUDA_TRY(cudaMemcpyAsync(cell_items, A + oi, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
     return ORBX_OK;
 }
 

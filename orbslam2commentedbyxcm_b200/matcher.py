@@ -97,6 +97,35 @@ class ORBmatcher:
         check(self._L.orbm_merge_partials(self._m, d_best, d_idx, d_second, nparts, nq, o_best, o_idx, o_second),
               "orbm_merge_partials")
 
+    # ---- frame preparation: Frame::UndistortKeyPoints / AssignFeaturesToGrid on the device ----
+    def UndistortKeyPoints(self, x, y, fx, fy, cx, cy, dist):
+        """mvKeysUn coordinates from mvKeys (src/Frame.cc:586-628); numpy in / out."""
+        x = np.ascontiguousarray(x, np.float32)
+        y = np.ascontiguousarray(y, np.float32)
+        dist = np.ascontiguousarray(dist, np.float32)
+        xu, yu = np.empty_like(x), np.empty_like(y)
+        check(self._L.orbm_undistort_keypoints(self._m, _p(x), _p(y), len(x), fx, fy, cx, cy, _p(dist), len(dist), _p(xu), _p(yu), 0),
+              "orbm_undistort_keypoints")
+        return xu, yu
+
+    def AssignFeaturesToGrid(self, x, y, min_x, min_y, w_inv, h_inv):
+        """mGrid as CSR (cell_start[64*48+1], cell_items) from undistorted keypoints (src/Frame.cc:351-370)."""
+        x = np.ascontiguousarray(x, np.float32)
+        y = np.ascontiguousarray(y, np.float32)
+        start = np.zeros(64 * 48 + 1, np.int32)
+        items = np.zeros(max(len(x), 1), np.int32)
+        check(self._L.orbm_assign_grid(self._m, _p(x), _p(y), len(x), min_x, min_y, w_inv, h_inv, _p(start), _p(items), 0),
+              "orbm_assign_grid")
+        return start, items[: start[-1]].copy()
+
+    def undistort_device(self, dx, dy, n, fx, fy, cx, cy, dist, dxu, dyu):
+        dist = np.ascontiguousarray(dist, np.float32)
+        check(self._L.orbm_undistort_keypoints(self._m, dx, dy, n, fx, fy, cx, cy, _p(dist), len(dist), dxu, dyu, 1),
+              "orbm_undistort_keypoints")
+
+    def assign_grid_device(self, dx, dy, n, min_x, min_y, w_inv, h_inv, d_start, d_items):
+        check(self._L.orbm_assign_grid(self._m, dx, dy, n, min_x, min_y, w_inv, h_inv, d_start, d_items, 1), "orbm_assign_grid")
+
     # ---- sharded brute force with the fused merge + exchange over peer memory (include/orbx.h) ----
     def exchange_create(self, world, rank, nq_max):
         """Allocates this rank's exchange buffer; returns (ipc_handle_bytes, local_device_pointer)."""

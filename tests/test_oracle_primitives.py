@@ -56,6 +56,20 @@ def test_golden_primitives(oracle_mod, golden_dir):
     assert np.array_equal(got.view(np.uint32), g["atan_deg"].view(np.uint32))
 
 
+def test_golden_undistort(oracle_mod, golden_dir):
+    """Frame::UndistortKeyPoints = cv::undistortPoints(pts, K, dist, R=I, P=K): restatement vs cv2 4.13 fixtures, bit for bit"""
+    g = np.load(os.path.join(golden_dir, "undistort_cv2.npz"))
+    ncases = sum(1 for k in g.files if k.startswith("cam"))
+    assert ncases >= 4
+    for c in range(ncases):
+        fx, fy, cx, cy = (float(v) for v in g["cam%d" % c])
+        d = g["dist%d" % c]
+        pts, ref = g["pts%d" % c], g["res%d" % c]
+        ox, oy = oracle_mod.undistort_points(pts[:, 0], pts[:, 1], fx, fy, cx, cy, np.array(d, np.float32))
+        assert np.array_equal(ox.view(np.uint32), ref[:, 0].view(np.uint32)), "case %d x" % c
+        assert np.array_equal(oy.view(np.uint32), ref[:, 1].view(np.uint32)), "case %d y" % c
+
+
 def test_golden_sincosf(oracle_mod, golden_dir):
     """restated glibc sincosf == host libm fixture (and == the libm of the machine running the test)."""
     L = oracle_mod.lib()
@@ -154,6 +168,21 @@ def test_fast_vs_cv2(oracle_mod):
 
 
 @pytest.mark.skipif(cv2 is None, reason="cv2 not importable")
+def test_undistort_vs_cv2(oracle_mod):
+    rng = np.random.default_rng(21)
+    for trial in range(6):
+        fx, fy = 400 + 300 * rng.random(2)
+        cx, cy = 320 + 40 * rng.standard_normal(), 240 + 30 * rng.standard_normal()
+        d = np.array([0.3 * rng.standard_normal(), rng.standard_normal(), 0.01 * rng.standard_normal(),
+                      0.01 * rng.standard_normal(), rng.standard_normal()][: 4 + trial % 2], np.float32)
+        K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], np.float32)
+        pts = (rng.random((5000, 1, 2)) * [640, 480]).astype(np.float32)
+        ref = cv2.undistortPoints(pts, K, d, None, K).reshape(-1, 2)
+        ox, oy = oracle_mod.undistort_points(pts[:, 0, 0], pts[:, 0, 1], float(K[0, 0]), float(K[1, 1]), float(K[0, 2]), float(K[1, 2]), d)
+        assert np.array_equal(ox.view(np.uint32), ref[:, 0].view(np.uint32))
+        assert np.array_equal(oy.view(np.uint32), ref[:, 1].view(np.uint32))
+
+
 def test_atan2_vs_cv2(oracle_mod):
     L = oracle_mod.lib()
     rng = np.random.default_rng(3)

@@ -82,8 +82,39 @@ def extract():
         print(name, len(kps))
 
 
+UNDISTORT_CASES = [  # (fx, fy, cx, cy, (k1, k2, p1, p2, k3)) : TUM1, TUM2, TUM3-like (no distortion) and a 4-coefficient camera
+    (517.306408, 516.469215, 318.643040, 255.313989, (0.262383, -0.953104, -0.005358, 0.002628, 1.163314)),
+    (520.908620, 521.007327, 325.141442, 249.701764, (0.231222, -0.784899, -0.003257, -0.000105, 0.917205)),
+    (535.4, 539.2, 320.1, 247.6, (0.0, 0.0, 0.0, 0.0, 0.0)),
+    (458.654, 457.296, 367.215, 248.375, (-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05)),
+]
+
+
+def undistort():
+    """cv2.undistortPoints(pts, K, dist, None, K) -- the call of Frame::UndistortKeyPoints (src/Frame.cc:608-614)."""
+    import cv2
+
+    rng = np.random.Generator(np.random.PCG64(11))
+    out = {}
+    for c, (fx, fy, cx, cy, d) in enumerate(UNDISTORT_CASES):
+        K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], np.float32)
+        D = np.array(d, np.float32)
+        pts = (rng.random((3000, 1, 2)) * [752, 480]).astype(np.float32)
+        pts[:4, 0] = [[0, 0], [751, 479], [cx, cy], [19.5, 460.25]]
+        if D[0] == 0:
+            res = pts.reshape(-1, 2).copy()      # the reference skips the call (src/Frame.cc:589-592)
+        else:
+            res = cv2.undistortPoints(pts, K, D, None, K).reshape(-1, 2)
+        out["pts%d" % c] = pts.reshape(-1, 2)
+        out["res%d" % c] = res
+        out["cam%d" % c] = np.array([fx, fy, cx, cy], np.float32)
+        out["dist%d" % c] = D
+    np.savez_compressed(os.path.join(G, "undistort_cv2.npz"), **out)
+
+
 if __name__ == "__main__":
     prim()
+    undistort()
     sincos()
     extract()
     print(sorted(os.listdir(G)))
