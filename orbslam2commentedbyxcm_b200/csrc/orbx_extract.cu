@@ -1268,7 +1268,8 @@ struct orbx_handle {
     std::vector<float> scale, invScale, sigma2, invSigma2;
     std::vector<int> quota;
     cudaStream_t stream = nullptr, streamBlur = nullptr, streamH2D = nullptr, streamD2H = nullptr;
-    cudaEvent_t evInReady[2] = {}, evInFree[2] = {};
+    static constexpr int PIPE_IN_SLOTS = 4;  // input staging slots of the pipelined host path (H2D runs ahead of the kernels)
+    cudaEvent_t evInReady[PIPE_IN_SLOTS] = {}, evInFree[PIPE_IN_SLOTS] = {};
     cudaStream_t stream2 = nullptr, streamBlur2 = nullptr;   // second compute lane of the pipelined host path
     cudaEvent_t evFork2 = nullptr, evJoin2 = nullptr;
     std::vector<cudaEvent_t> evChunkDone;
@@ -1745,7 +1746,7 @@ int orbx_create(const orbx_config* cfg, int device, orbx_handle** out)
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->streamBlur, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->streamH2D, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->streamD2H, cudaStreamNonBlocking);
-    for (int i = 0; i < 2 && e == cudaSuccess; i++) {
+    for (int i = 0; i < orbx_handle::PIPE_IN_SLOTS && e == cudaSuccess; i++) {
         e = cudaEventCreateWithFlags(&h->evInReady[i], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->evInFree[i], cudaEventDisableTiming);
     }
@@ -1783,7 +1784,7 @@ void orbx_destroy(orbx_handle* h)
     if (h->streamBlur) cudaStreamDestroy(h->streamBlur);
     if (h->streamH2D) cudaStreamDestroy(h->streamH2D);
     if (h->streamD2H) cudaStreamDestroy(h->streamD2H);
-    for (int i = 0; i < 2; i++) { if (h->evInReady[i]) cudaEventDestroy(h->evInReady[i]); if (h->evInFree[i]) cudaEventDestroy(h->evInFree[i]); }
+    for (int i = 0; i < orbx_handle::PIPE_IN_SLOTS; i++) { if (h->evInReady[i]) cudaEventDestroy(h->evInReady[i]); if (h->evInFree[i]) cudaEventDestroy(h->evInFree[i]); }
     for (auto& ev : h->evChunkDone) cudaEventDestroy(ev);
     if (h->stream2) { cudaStreamSynchronize(h->stream2); cudaStreamDestroy(h->stream2); }
     if (h->streamBlur2) cudaStreamDestroy(h->streamBlur2);
@@ -1900,7 +1901,7 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
     const int devCap = h->plan.kpCapFrame;
     // device staging for input (double buffered when pipelined) and packed output [counts | kps | desc]
     const size_t frameBytes = (size_t)rows * cols;
-    const size_t inBytes = frameBytes * chunk * (piped ? 2 : 1);
+    const size_t inBytes = frameBytes * chunk * (piped ? orbx_handle::PIPE_IN_SLOTS : 1);
     if (inBytes > h->dInBytes) {
         std::lock_guard<std::mutex> setupLock(g_setupMutex);
         ORBX_CUDA_TRY(cudaDeviceSynchronize());
@@ -1989,28 +1990,34 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
         };
         for (int k = 0; k < nchunks; k++) {
             const int f0 = chunkStart[k], nk = chunkStart[k + 1] - f0, b = k & 1;
-            uint8_t* dInB = h->dIn + (size_t)b * chunk * frameBytes;
-            if (k >= 2) ORBX_CUDA_TRY(cudaStreamWaitEvent(h->streamH2D, h->evInFree[b], 0));
+            // the input staging buffer has more slots than the arena: only k_level0 reads it, so the H2D engine may run
+            // several chunks ahead of the kernels instead of waiting for chunk k-2 to finish
+            const int ib = k % orbx_handle::PIPE_IN_SLOTS;
+            uint8_t* dInB = h->dIn + (size_t)ib * chunk * frameBytes;
+            if (k >= orbx_handle::PIPE_IN_SLOTS) ORBX_CUDA_TRY(cudaStreamWaitEvent(h->streamH2D, h->evInFree[ib], 0));
             mark(h->streamH2D);
             if ((rc = copy_in(h, dInB, imgs + (size_t)f0 * frame_stride, nk, rows, cols, step, frame_stride, h->streamH2D)) != ORBX_OK) return rc;
-            ORBX_CUDA_TRY(cudaEventRecord(h->evInReady[b], h->streamH2D));
+            ORBX_CUDA_TRY(cudaEventRecord(h->evInReady[ib], h->streamH2D));
             mark(h->streamH2D);
             cudaStream_t cs = b ? h->stream2 : h->stream;  // chunk k computes in arena slot b on compute lane b
-            ORBX_CUDA_TRY(cudaStreamWaitEvent(cs, h->evInReady[b], 0));
+            ORBX_CUDA_TRY(cudaStreamWaitEvent(cs, h->evInReady[ib], 0));
             mark(cs);
             int nl = 0;
             rc = launch_cached(h, dInB, (long long)cols, (long long)frameBytes, nk, dKps + (size_t)f0 * devCap,
                                dDesc + (size_t)f0 * devCap * 32, dCounts + f0, devCap, &nl, b, b * chunk);
             if (rc != ORBX_OK) return rc;
             launches += nl;
-            ORBX_CUDA_TRY(cudaEventRecord(h->evInFree[b], cs));
+            ORBX_CUDA_TRY(cudaEventRecord(h->evInFree[ib], cs));
             mark(cs);
-            ORBX_CUDA_TRY(cudaStreamWaitEvent(h->streamD2H, h->evInFree[b], 0));
+            ORBX_CUDA_TRY(cudaStreamWaitEvent(h->streamD2H, h->evInFree[ib], 0));
+            static const bool dbgNoD2H = std::getenv("ORBX_PIPE_NO_D2H") != nullptr;  // timeline experiments only
+            if (!dbgNoD2H) {
             ORBX_CUDA_TRY(cudaMemcpyAsync(hCnt + (size_t)f0 * sizeof(int), dCounts + f0, sizeof(int) * nk, cudaMemcpyDeviceToHost, h->streamD2H));
             ORBX_CUDA_TRY(cudaMemcpyAsync(hKps + (size_t)f0 * devCap * sizeof(orbx_keypoint), dKps + (size_t)f0 * devCap,
                                           sizeof(orbx_keypoint) * (size_t)nk * devCap, cudaMemcpyDeviceToHost, h->streamD2H));
             ORBX_CUDA_TRY(cudaMemcpyAsync(hDesc + (size_t)f0 * devCap * 32, dDesc + (size_t)f0 * devCap * 32,
                                           (size_t)32 * nk * devCap, cudaMemcpyDeviceToHost, h->streamD2H));
+            }
             ORBX_CUDA_TRY(cudaEventRecord(h->evChunkDone[k], h->streamD2H));
             mark(h->streamD2H);
         }
