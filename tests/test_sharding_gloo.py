@@ -79,6 +79,72 @@ def test_sharded_bruteforce_protocol_world2(tmp_path, oracle_mod):
     assert ri[0] == 7 and rb[0] == 0 and rs[0] == 0
 
 
+def _exchange_worker(rank, world, port, ndb, nq, calls, out_dir):
+    """the fused-exchange protocol on CPU: every rank owns a slot buffer [2][world][nq_max]; per call each rank 'stores'
+    its packed triples into slot set (epoch & 1) of every peer (emulated with an all-gather of the words), a reader
+    accepts a slot only when it carries the current epoch, then merges in rank order."""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import oracle
+
+    nq_max = nq + 3
+    slots = np.zeros(2 * world * nq_max, np.uint64)  # epoch 0 = never written
+    results = []
+    for call in range(1, calls + 1):
+        db = synth.gen_descriptors(ndb, seed=3 + call)
+        q, _ = synth.gen_queries(db, nq, seed=4 + call)
+        lo, hi = sharding.db_shard(ndb, rank, world)
+        b, i, s = oracle.bruteforce(q, db[lo:hi], threads=2)
+        i = np.where(i >= 0, i + lo, i).astype(np.int32)
+        words = torch.from_numpy(sharding.pack_exchange_word(call, b, s, i).view(np.int64).copy())
+        gathered = [torch.empty_like(words) for _ in range(world)]
+        dist.all_gather(gathered, words)
+        stale = slots.copy()
+        for src in range(world):
+            o = sharding.exchange_slot_offset(call, src, world, nq_max)
+            slots[o:o + nq] = gathered[src].numpy().view(np.uint64)
+        parts = []
+        for src in range(world):
+            o = sharding.exchange_slot_offset(call, src, world, nq_max)
+            ep_old = sharding.unpack_exchange_word(stale[o:o + nq])[0]
+            assert (ep_old != (call & 0x3FFF)).all()        # what was there before (call - 2 or never written) is not mistaken for ready
+            ep, pb, ps, pi = sharding.unpack_exchange_word(slots[o:o + nq])
+            assert (ep == (call & 0x3FFF)).all()
+            parts.append((pb, pi, ps))
+        ob, oi, os_ = merge_partials_model(*(np.stack([p[k] for p in parts]).astype(np.int32) for k in range(3)))
+        results.append((ob, oi, os_))
+    np.savez(os.path.join(out_dir, "xrank%d.npz" % rank), **{"c%d_%s" % (c, n): v for c, r in enumerate(results) for n, v in zip("bis", r)})
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_fused_exchange_protocol_world2(tmp_path, oracle_mod):
+    ndb, nq, world, calls = 2000, 40, 2, 3
+    mp.spawn(_exchange_worker, args=(world, _free_port(), ndb, nq, calls, str(tmp_path)), nprocs=world, join=True)
+    for call in range(1, calls + 1):
+        db = synth.gen_descriptors(ndb, seed=3 + call)
+        q, _ = synth.gen_queries(db, nq, seed=4 + call)
+        rb, ri, rs = oracle_mod.bruteforce(q, db)
+        for r in range(world):
+            g = np.load(os.path.join(str(tmp_path), "xrank%d.npz" % r))
+            assert np.array_equal(g["c%d_b" % (call - 1)], rb) and np.array_equal(g["c%d_i" % (call - 1)], ri)
+            assert np.array_equal(g["c%d_s" % (call - 1)], rs)
+
+
+def test_exchange_word_round_trip():
+    rng = np.random.default_rng(1)
+    b = rng.integers(0, 257, 1000).astype(np.int32)
+    s = rng.integers(0, 257, 1000).astype(np.int32)
+    i = rng.integers(-1, 2**31 - 1, 1000).astype(np.int32)
+    i[:10] = -1
+    for epoch in (1, 2, 16383, 16384, 16385, 40000):
+        e, ub, us, ui = sharding.unpack_exchange_word(sharding.pack_exchange_word(epoch, b, s, i))
+        assert (e == (epoch & 0x3FFF)).all() and np.array_equal(ub, b) and np.array_equal(us, s) and np.array_equal(ui, i)
+    assert sharding.exchange_slot_offset(5, 1, 4, 100) != sharding.exchange_slot_offset(6, 1, 4, 100)
+    assert sharding.exchange_slot_offset(5, 1, 4, 100) == sharding.exchange_slot_offset(7, 1, 4, 100)
+
+
 def test_shard_plans():
     for n, w in [(10, 3), (4096, 8), (7, 8), (1_000_000, 8)]:
         ranges = [sharding.db_shard(n, r, w) for r in range(w)]
