@@ -1092,8 +1092,10 @@ __global__ void __launch_bounds__(128) k_blur(Plan plan, Buffers buf)
 // Also finalises the keypoint record (level-0 coordinates, size, octave) and the per-frame count.
 // ------------------------------------------------------------------------------------------------------
 constexpr int DESC_WARPS = 4;
-constexpr int DESC_PP = 40;   // blurred patch pitch: 37 + up to 3 alignment bytes
-constexpr int ORI_PW = 9;     // raw patch pitch in words (odd: lanes reading different rows hit different banks)
+constexpr int DESC_PP = 64;   // blurred patch pitch in bytes: 37 columns at any 16-byte alignment span <= 15 + 37 = 52 bytes
+constexpr int ORI_PB = 48;    // raw patch pitch in bytes: 31 columns at any 16-byte alignment span <= 15 + 31 = 46 bytes
+constexpr int DESC_PBYTES = 37 * DESC_PP, ORI_BYTES = 31 * ORI_PB;
+constexpr int DESC_STAGE = DESC_PBYTES + ORI_BYTES;  // one staging buffer: blurred patch, then raw disc rows
 
 __device__ __forceinline__ int dp4a_u8s8(uint32_t a, uint32_t b, int c)
 {
@@ -1102,11 +1104,26 @@ __device__ __forceinline__ int dp4a_u8s8(uint32_t a, uint32_t b, int c)
     return d;
 }
 
-__global__ void __launch_bounds__(DESC_WARPS * 32, 5) k_describe(Plan plan, Buffers buf, orbx_keypoint* outKps,
+// IC_Angle moments of one disc row held as 12 words starting at a 16-byte boundary; W4 = word offset of column cx-16
+// (warp-uniform, so the switch in the caller does not diverge), sh8 = bit offset inside that word.
+template <int W4>
+__device__ __forceinline__ void ori_row(const uint4 q0, const uint4 q1, const uint4 q2, int sh8, const uint32_t (&wU)[8],
+                                        const uint32_t (&wOne)[8], int& m10, int& rs)
+{
+    const uint32_t w[12] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w};
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const uint32_t px = __funnelshift_r(w[W4 + k], w[W4 + k + 1], sh8);  // columns 4k-16 .. 4k-13 relative to cx
+        m10 = dp4a_u8s8(px, wU[k], m10);
+        rs = (int)__dp4a(px, wOne[k], (uint32_t)rs);
+    }
+}
+
+__global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buffers buf, orbx_keypoint* outKps,
                                                                uint8_t* outDesc, int* outCounts, int capacity)
 {
-    __shared__ __align__(16) uint8_t patch[DESC_WARPS][37 * DESC_PP];
-    __shared__ __align__(16) uint32_t raw[DESC_WARPS][31 * ORI_PW + 1];
+    // two staging buffers per warp: keypoint i is processed from one while cp.async fills the other for keypoint i+1
+    __shared__ __align__(16) uint8_t stage[DESC_WARPS][2][DESC_STAGE];
     const int lframe = blockIdx.y, frame = lframe + buf.frameBase;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     __shared__ int cum[ORBX_MAX_LEVELS + 1];
@@ -1145,69 +1162,82 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 5) k_describe(Plan plan, Buff
         patF[i] = make_float4((float)pp[0], (float)pp[1], (float)pp[2], (float)pp[3]);
     }
     __syncthreads();
-    uint8_t* P = patch[wid];
-    uint32_t* R = raw[wid];
+    const uint32_t stage0 = (uint32_t)__cvta_generic_to_shared(&stage[wid][0][0]);
 
-    // staging maps: lane -> (word column, first row), rows advance by 3 per load (27 / 30 lanes active)
-    const int rwi = lane % ORI_PW, rrg = lane / ORI_PW;                  // raw: 31 rows x 9 words
-    const int bwi = lane % (DESC_PP / 4), brg = lane / (DESC_PP / 4);    // blurred: 37 rows x 10 words
-    // The patches of keypoint i+1 are loaded into registers while keypoint i is being processed from shared memory
-    // (software pipeline: the global-load latency hides behind the arithmetic of the previous keypoint).
-    uint32_t tr[11], tb[13];
-    int level = 0, nLevel = 0;  // gidx only grows: the level search resumes where it stopped
-    StagedKp nkp;
-    auto fetch = [&](int gi) {
+    // staging maps: a lane copies 16-byte segments; blurred = 37 rows x 4 segments (lane -> segment lane & 3, rows
+    // (lane >> 2) + 8 i), raw = 31 rows x 3 segments (lanes 0..29 -> segment lane % 3, rows lane / 3 + 10 i).  Segments
+    // that the keypoint's alignment leaves unused are not fetched.
+    const int bseg = lane & 3, brow = lane >> 2;
+    const int rseg = lane % 3, rrow = lane / 3;
+    // Three keypoints are in flight per warp: i is processed from shared memory, the patches of i+1 are being copied, and
+    // the 16-byte record of i+2 is being loaded (the copy addresses of a keypoint depend on its record, so loading the
+    // record one iteration earlier keeps that global-load latency off the warp's critical path).
+    int nLevel = 0;  // gidx only grows: the level search resumes where it stopped
+    auto load_record = [&](int gi, StagedKp& rec, int& lev) {
         while (gi >= cum[nLevel + 1]) nLevel++;
-        const LevelGeom& g = plan.lv[nLevel];
-        nkp = buf.staged[(long long)frame * plan.kpCapFrame + g.kpOff + (gi - cum[nLevel])];
-        const int cx = (int)nkp.x, cy = (int)nkp.y;
-        // raw rows cy-15..cy+15 (9 aligned words per row from the word containing cx-16) and the blurred 37x37
-        // neighbourhood (10 aligned words per row)
-        const long long step3 = 3LL * g.pitch;
-        const uint8_t* pr = interior_ptr(buf.pyr, g, frame) + (long long)(cy - 15 + rrg) * g.pitch + (cx - 16 - (cx & 3)) + 4 * rwi;
-        const uint8_t* pb = interior_ptr(buf.blur, g, frame) + (long long)(cy - 18 + brg) * g.pitch + (cx - 18 - ((PAD_LEFT + cx - 18) & 3)) + 4 * bwi;
+        lev = nLevel;
+        rec = buf.staged[(long long)frame * plan.kpCapFrame + plan.lv[nLevel].kpOff + (gi - cum[nLevel])];
+    };
+    auto fetch = [&](const StagedKp& rec, int lev, int slot) {
+        const LevelGeom& g = plan.lv[lev];
+        const int cx = (int)rec.x, cy = (int)rec.y;
+        const int pitch = g.pitch;
+        // interior column 0 is 32-byte aligned in both arenas, so the alignment of a column is that of its index
+        const int bsh = (cx - 18) & 15, rsh = (cx - 16) & 15;
+        const uint32_t sb = stage0 + slot * DESC_STAGE;
+        if (bseg * 16 < bsh + 37) {
+            const uint8_t* pb = interior_ptr(buf.blur, g, frame) + (long long)(cy - 18 + brow) * pitch + (cx - 18 - bsh) + 16 * bseg;
+            uint32_t dst = sb + brow * DESC_PP + 16 * bseg;
 #pragma unroll
-        for (int i = 0; i < 11; i++) {
-            tr[i] = (rrg < 3 && rrg + 3 * i < 31) ? __ldg(reinterpret_cast<const uint32_t*>(pr)) : 0u;
-            pr += step3;
+            for (int i = 0; i < 5; i++) {
+                if (brow + 8 * i < 37)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 8 * i * DESC_PP), "l"(pb + (long long)(8 * i) * pitch) : "memory");
+            }
         }
+        if (lane < 30 && rseg * 16 < rsh + 32) {
+            const uint8_t* pr = interior_ptr(buf.pyr, g, frame) + (long long)(cy - 15 + rrow) * pitch + (cx - 16 - rsh) + 16 * rseg;
+            uint32_t dst = sb + DESC_PBYTES + rrow * ORI_PB + 16 * rseg;
 #pragma unroll
-        for (int i = 0; i < 13; i++) {
-            tb[i] = (brg < 3 && brg + 3 * i < 37) ? __ldg(reinterpret_cast<const uint32_t*>(pb)) : 0u;
-            pb += step3;
+            for (int i = 0; i < 4; i++) {
+                if (rrow + 10 * i < 31)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 10 * i * ORI_PB), "l"(pr + (long long)(10 * i) * pitch) : "memory");
+            }
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
     };
     const int gstride = gridDim.x * DESC_WARPS;
     int gidx = blockIdx.x * DESC_WARPS + wid;
-    if (gidx < total) fetch(gidx);
-    for (; gidx < total; gidx += gstride) {
-        const StagedKp kp = nkp;
-        level = nLevel;
+    int slot = 0;
+    StagedKp kp, kpN, kpNN;
+    int level = 0, levelN = 0, levelNN = 0;
+    kp.x = kp.y = kp.angle = kp.response = 0.f;
+    kpN = kp; kpNN = kp;
+    if (gidx < total) {
+        load_record(gidx, kp, level);
+        fetch(kp, level, 0);
+        if (gidx + gstride < total) load_record(gidx + gstride, kpN, levelN);
+    }
+    for (; gidx < total; gidx += gstride, slot ^= 1) {
         const LevelGeom& g = plan.lv[level];
         const int cx = (int)kp.x;
-        const int shift = (PAD_LEFT + cx - 18) & 3;
-        __syncwarp();  // the previous keypoint's reads of R / P are done
-#pragma unroll
-        for (int i = 0; i < 11; i++)
-            if (rrg < 3 && rrg + 3 * i < 31) R[lane + 3 * ORI_PW * i] = tr[i];
-#pragma unroll
-        for (int i = 0; i < 13; i++)
-            if (brg < 3 && brg + 3 * i < 37) reinterpret_cast<uint32_t*>(P)[lane + 3 * (DESC_PP / 4) * i] = tb[i];
-        __syncwarp();
-        if (gidx + gstride < total) fetch(gidx + gstride);
+        const uint8_t* P = &stage[wid][slot][0];
+        const uint8_t* R = P + DESC_PBYTES;
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        __syncwarp();  // this keypoint's patches have landed (all lanes); the previous keypoint's reads of the other buffer are done
+        if (gidx + gstride < total) fetch(kpN, levelN, slot ^ 1);
+        if (gidx + 2 * gstride < total) load_record(gidx + 2 * gstride, kpNN, levelNN);
         // ---- IC_Angle ----
         int m10 = 0, rs = 0;
         if (lane < 31) {
-            const int sh8 = 8 * (cx & 3);
-            const uint32_t* rw = R + lane * ORI_PW;
-            uint32_t w0 = rw[0];
-#pragma unroll
-            for (int k = 0; k < 8; k++) {
-                const uint32_t w1 = rw[k + 1];
-                const uint32_t px = __funnelshift_r(w0, w1, sh8);  // columns 4k-16 .. 4k-13 relative to cx
-                m10 = dp4a_u8s8(px, wU[k], m10);
-                rs = (int)__dp4a(px, wOne[k], (uint32_t)rs);
-                w0 = w1;
+            const int rsh = (cx - 16) & 15;
+            const int sh8 = 8 * (rsh & 3);
+            const uint4* rq = reinterpret_cast<const uint4*>(R + lane * ORI_PB);
+            const uint4 q0 = rq[0], q1 = rq[1], q2 = rq[2];
+            switch (rsh >> 2) {  // warp-uniform
+            case 0: ori_row<0>(q0, q1, q2, sh8, wU, wOne, m10, rs); break;
+            case 1: ori_row<1>(q0, q1, q2, sh8, wU, wOne, m10, rs); break;
+            case 2: ori_row<2>(q0, q1, q2, sh8, wU, wOne, m10, rs); break;
+            default: ori_row<3>(q0, q1, q2, sh8, wU, wOne, m10, rs); break;
             }
         }
         m10 = __reduce_add_sync(0xffffffffu, m10);
@@ -1221,7 +1251,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 5) k_describe(Plan plan, Buff
         // cvRound = round-half-even: adding 1.5 * 2^23 leaves the rounded integer in the low mantissa bits (|v| < 2^22);
         // the bias 0x4B400000 of both coordinates is folded into the patch base (32-bit wrap-around arithmetic)
         const float RND = 12582912.f;
-        const uint32_t cbase = (uint32_t)(18 * DESC_PP + shift + 18) - (uint32_t)(DESC_PP + 1) * 0x4B400000u;
+        const uint32_t cbase = (uint32_t)(18 * DESC_PP + ((cx - 18) & 15) + 18) - (uint32_t)(DESC_PP + 1) * 0x4B400000u;
 #pragma unroll
         for (int k = 0; k < 8; k++) {
             const float4 pt = patF[k * 32 + lane];
@@ -1244,6 +1274,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 5) k_describe(Plan plan, Buff
             r.octave = level;
             outKps[o] = r;
         }
+        kp = kpN; level = levelN;
+        kpN = kpNN; levelN = levelNN;
     }
 }
 
@@ -1611,9 +1643,11 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
     k_fast_band<<<dim3(P.totalFastUnits, n), FAST_T, h->fastSmem, s>>>(P, B);
     nl++;
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_OCTREE], s));
-    // batches: many small CTAs per SM (throughput); a few frames: more threads per level (latency)
-    if (n >= 16) k_octree<128><<<dim3(P.nlevels, n), 128, h->octSmem[0], s>>>(P, B, h->octNodeCap, h->octKeySmemCap[0], h->dKeyNode, P.candFrame);
-    else if (n >= 4) k_octree<256><<<dim3(P.nlevels, n), 256, h->octSmem[1], s>>>(P, B, h->octNodeCap, h->octKeySmemCap[1], h->dKeyNode, P.candFrame);
+    // large batches: many small CTAs per SM (throughput); up to a few dozen frames: more threads per level (latency)
+    static const int octForce = [] { const char* e = std::getenv("ORBX_OCT_T"); return e ? std::atoi(e) : 0; }();  // experiments only
+    const int octT = octForce ? octForce : (n >= 112 ? 128 : (n >= 48 ? 256 : 512));  // measured: tools/sweep_octree.sh, profiles/r1h_sweep_octree.txt
+    if (octT == 128) k_octree<128><<<dim3(P.nlevels, n), 128, h->octSmem[0], s>>>(P, B, h->octNodeCap, h->octKeySmemCap[0], h->dKeyNode, P.candFrame);
+    else if (octT == 256) k_octree<256><<<dim3(P.nlevels, n), 256, h->octSmem[1], s>>>(P, B, h->octNodeCap, h->octKeySmemCap[1], h->dKeyNode, P.candFrame);
     else k_octree<512><<<dim3(P.nlevels, n), 512, h->octSmem[2], s>>>(P, B, h->octNodeCap, h->octKeySmemCap[2], h->dKeyNode, P.candFrame);
     nl++;
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_BLUR], s));
