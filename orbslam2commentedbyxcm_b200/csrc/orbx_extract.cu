@@ -1001,14 +1001,19 @@ __global__ void __launch_bounds__(OCT_T) k_octree(Plan plan, Buffers buf, int no
 //   vertical pass on row pairs packed as u16x2 with IDP.2A (two taps per instruction, 32-bit accumulate); the
 //   rounding constant is the accumulator's initial value.
 // ------------------------------------------------------------------------------------------------------
-constexpr int BLUR_ROWS = 32;  // output rows per thread (even)
+constexpr int BLUR_ROWS = 32;  // output rows per thread (even; 64 measured no faster: the kernel is latency-, not issue-bound)
 
-__device__ __forceinline__ void blur_hrow(const uint8_t* row, uint32_t h[4])
+// the three words (columns x-4 .. x+7) a thread needs from one source row; row points at the thread's first column
+__device__ __forceinline__ void blur_ldrow(const uint8_t* row, uint32_t (&n)[3])
 {
-    // row points at the thread's first column (4-byte aligned)
-    const uint32_t L = __ldg(reinterpret_cast<const uint32_t*>(row) - 1);
-    const uint32_t C = __ldg(reinterpret_cast<const uint32_t*>(row));
-    const uint32_t R = __ldg(reinterpret_cast<const uint32_t*>(row) + 1);
+    n[0] = __ldg(reinterpret_cast<const uint32_t*>(row) - 1);
+    n[1] = __ldg(reinterpret_cast<const uint32_t*>(row));
+    n[2] = __ldg(reinterpret_cast<const uint32_t*>(row) + 1);
+}
+
+__device__ __forceinline__ void blur_hrow(const uint32_t (&n)[3], uint32_t h[4])
+{
+    const uint32_t L = n[0], C = n[1], R = n[2];
     constexpr uint32_t TLO = 0x38302212u;  // taps 18,34,48,56 for bytes x-3..x
     constexpr uint32_t THI = 0x00122230u;  // taps 48,34,18,0  for bytes x+1..x+4
     h[0] = __dp4a(__funnelshift_r(C, R, 8), THI, __dp4a(__funnelshift_r(L, C, 8), TLO, 0u));
@@ -1035,16 +1040,27 @@ __global__ void __launch_bounds__(128) k_blur(Plan plan, Buffers buf)
     const long long pitch = g.pitch;
     // window of 8 rows (y-3 .. y+4) as 4 vertical pairs per column: P[k][j] = h(y-3+2k, j) | h(y-2+2k, j) << 16
     uint32_t P[4][4];
-    auto hpair = [&](const uint8_t* row, uint32_t (&Q)[4]) {  // rows `row` and `row + pitch`
+    // the source words of a row pair are loaded two steps before they are used (buffers A and B alternate), so that their
+    // latency hides behind the arithmetic of the steps in between
+    uint32_t A0[3], A1[3], B0[3], B1[3];
+    auto ldpair = [&](const uint8_t* row, uint32_t (&n0)[3], uint32_t (&n1)[3]) {  // rows `row` and `row + pitch`
+        blur_ldrow(row, n0);
+        blur_ldrow(row + pitch, n1);
+    };
+    auto hpair = [&](const uint32_t (&n0)[3], const uint32_t (&n1)[3], uint32_t (&Q)[4]) {
         uint32_t ha[4], hb[4];
-        blur_hrow(row, ha);
-        blur_hrow(row + pitch, hb);
+        blur_hrow(n0, ha);
+        blur_hrow(n1, hb);
 #pragma unroll
         for (int j = 0; j < 4; j++) Q[j] = __byte_perm(ha[j], hb[j], 0x5410);
     };
     const uint8_t* sp = src + (long long)(y0 - 3) * pitch;
-#pragma unroll
-    for (int k = 0; k < 4; k++) { hpair(sp, P[k]); sp += 2 * pitch; }   // sp -> row y0 + 5
+    ldpair(sp, A0, A1); sp += 2 * pitch;
+    ldpair(sp, B0, B1); sp += 2 * pitch;
+    hpair(A0, A1, P[0]); ldpair(sp, A0, A1); sp += 2 * pitch;
+    hpair(B0, B1, P[1]); ldpair(sp, B0, B1); sp += 2 * pitch;
+    hpair(A0, A1, P[2]); ldpair(sp, A0, A1); sp += 2 * pitch;
+    hpair(B0, B1, P[3]); ldpair(sp, B0, B1); sp += 2 * pitch;   // A = rows y0+5/6, B = rows y0+7/8, sp -> row y0 + 9
     uint8_t* dp = dst + (long long)y0 * pitch;
     constexpr uint32_t TA = 0x12002212u;  // lo pair taps (18,34): row y   | hi pair taps (0,18):  row y+1
     constexpr uint32_t TB = 0x30223830u;  // (48,56) | (34,48)
@@ -1064,19 +1080,20 @@ __global__ void __launch_bounds__(128) k_blur(Plan plan, Buffers buf)
         dp += 2 * pitch;
     };
     // four row pairs per trip, the window rotating through P[0..3] by name (no register moves)
+    // (the last two pairs loaded are not used: at most rows y1 + 4 .. y1 + 7, inside the 19-row frame)
     for (int y = y0; y < y1; y += 8) {
         vout(P[0], P[1], P[2], P[3]);
         if (y + 2 >= y1) break;
-        hpair(sp, P[0]); sp += 2 * pitch;
+        hpair(A0, A1, P[0]); ldpair(sp, A0, A1); sp += 2 * pitch;
         vout(P[1], P[2], P[3], P[0]);
         if (y + 4 >= y1) break;
-        hpair(sp, P[1]); sp += 2 * pitch;
+        hpair(B0, B1, P[1]); ldpair(sp, B0, B1); sp += 2 * pitch;
         vout(P[2], P[3], P[0], P[1]);
         if (y + 6 >= y1) break;
-        hpair(sp, P[2]); sp += 2 * pitch;
+        hpair(A0, A1, P[2]); ldpair(sp, A0, A1); sp += 2 * pitch;
         vout(P[3], P[0], P[1], P[2]);
         if (y + 8 >= y1) break;
-        hpair(sp, P[3]); sp += 2 * pitch;
+        hpair(B0, B1, P[3]); ldpair(sp, B0, B1); sp += 2 * pitch;
     }
 }
 
