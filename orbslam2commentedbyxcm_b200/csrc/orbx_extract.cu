@@ -404,16 +404,27 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int minTh = plan.minTh, iniTh = plan.iniTh;
-    // ---- pass 1: SWAR rejection, 4 pixels per lane; the survivors of a lane's rows are kept as 4-bit groups of a
-    //      60-bit mask (sweep `it` = rows warp + 4 * it) ----
+    const int wCell = g.wCell;
     const int txFirst = shift + 3, txEnd = shift + 3 + evalW;  // evaluated tile columns [txFirst, txEnd)
     const int gw = (txFirst >> 2) + lane;                        // ((txEnd-1)>>2) - (txFirst>>2) + 1 <= 32 words
+    const int ncells = min(FAST_MAXG, (evalW - 1) / wCell + 1);
     constexpr int FAST_RPW = (59 + FAST_T / 32 - 1) / (FAST_T / 32);  // sweeps: eh <= 59
     static_assert(FAST_RPW <= 16, "survivor nibbles must fit 64 bits");
-    uint32_t mlo = 0, mhi = 0;
+    // queue entry = tile row << 8 | tile column; bit b of sweep `it` is pixel (warp + 3 + 4 * it, 4 * gw + (b & 3))
+    const uint32_t e0 = ((uint32_t)(warp + 3) << 8) | (uint32_t)(4 * gw);
+    auto push = [&](uint32_t m, uint32_t ebase, int base) {
+        while (m) {
+            const int bit = __ffs(m) - 1;
+            m &= m - 1;
+            q1[base++] = (unsigned short)(ebase + (((uint32_t)bit >> 2) * ((FAST_T / 32) << 8)) + (bit & 3));
+        }
+    };
+    // ---- pass 1: SWAR rejection, 4 pixels per lane, at both thresholds; the survivors of a lane's rows are kept as 4-bit
+    //      groups of a 60-bit mask per threshold (sweep `it` = rows warp + 4 * it) ----
+    uint32_t iniLo = 0, iniHi = 0, minLo = 0, minHi = 0;
     {
-        const uint32_t K = (uint32_t)(0x7f - min(minTh, 0x7f)) * 0x01010101u;
-        const bool filter = minTh < 0x80;
+        const uint32_t Ki = (uint32_t)(0x7f - min(iniTh, 0x7f)) * 0x01010101u, Km = (uint32_t)(0x7f - min(minTh, 0x7f)) * 0x01010101u;
+        const bool filterIni = iniTh < 0x80, filterMin = minTh < 0x80;
         uint32_t vmask = 0;  // bytes of this word that are evaluated pixels
 #pragma unroll
         for (int bb = 0; bb < 4; bb++)
@@ -426,27 +437,36 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
             const uint32_t C = cp[0], Lw = cp[-1], Rw = cp[1], N = cp[-3 * FAST_P4], S = cp[3 * FAST_P4];
             const uint32_t W4 = __byte_perm(Lw, C, 0x4321);  // pixels x-3 .. x
             const uint32_t E4 = __byte_perm(C, Rw, 0x6543);  // pixels x+3 .. x+6
-            uint32_t m = vmask;
-            if (filter) {
-                const uint32_t an = __vabsdiffu4(C, N), as = __vabsdiffu4(C, S), aw = __vabsdiffu4(C, W4), ae = __vabsdiffu4(C, E4);
-                // bit 7 of each byte: |d| > minTh
-                const uint32_t gn = ((an & 0x7f7f7f7fu) + K) | an, gs = ((as & 0x7f7f7f7fu) + K) | as;
-                const uint32_t gww = ((aw & 0x7f7f7f7fu) + K) | aw, ge = ((ae & 0x7f7f7f7fu) + K) | ae;
-                m = (gn | gs) & (gww | ge) & vmask;
-            }
-            const uint32_t nib = (m * 0x00204081u) >> 28;  // bits 7, 15, 23, 31 -> 0..3
-            if (it < 8) mlo |= nib << (4 * it); else mhi |= nib << (4 * (it - 8));
+            const uint32_t an = __vabsdiffu4(C, N), as = __vabsdiffu4(C, S), aw = __vabsdiffu4(C, W4), ae = __vabsdiffu4(C, E4);
+            const uint32_t ln = an & 0x7f7f7f7fu, ls = as & 0x7f7f7f7fu, lw = aw & 0x7f7f7f7fu, le = ae & 0x7f7f7f7fu;
+            // bit 7 of each byte: |d| > threshold
+            uint32_t mi = vmask, mm = vmask;
+            if (filterIni) mi = (((ln + Ki) | an) | ((ls + Ki) | as)) & (((lw + Ki) | aw) | ((le + Ki) | ae)) & vmask;
+            if (filterMin) mm = (((ln + Km) | an) | ((ls + Km) | as)) & (((lw + Km) | aw) | ((le + Km) | ae)) & vmask;
+            const uint32_t ni = (mi * 0x00204081u) >> 28, nm = (mm * 0x00204081u) >> 28;  // bits 7, 15, 23, 31 -> 0..3
+            if (it < 8) { iniLo |= ni << (4 * it); minLo |= nm << (4 * it); }
+            else { iniHi |= ni << (4 * (it - 8)); minHi |= nm << (4 * (it - 8)); }
         }
     }
-    // queue entry = tile row << 8 | tile column; bit b of sweep `it` is pixel (warp + 3 + 4 * it, 4 * gw + (b & 3))
-    const uint32_t e0 = ((uint32_t)(warp + 3) << 8) | (uint32_t)(4 * gw);
-    auto push = [&](uint32_t m, uint32_t ebase, int base) {
-        while (m) {
-            const int bit = __ffs(m) - 1;
-            m &= m - 1;
-            q1[base++] = (unsigned short)(ebase + (((uint32_t)bit >> 2) * ((FAST_T / 32) << 8)) + (bit & 3));
+    // Two phases, as the reference calls cv::FAST twice: phase 0 scores the corners at iniTh (NMS among them is exact: a
+    // kept pixel beats every neighbour below iniTh anyway); phase 1 repeats passes 2 and 3 at minTh for the cells that kept
+    // nothing, restricted to their columns.  The pixels with minTh <= S < iniTh of textured cells (the majority of what
+    // a minTh filter lets through) are never scored.
+    uint32_t retry = 0;  // phase 1: bit c = cell c of the band kept nothing at iniTh
+#pragma unroll 1
+    for (int phase = 0; phase < 2; phase++) {
+    const int th = phase ? minTh : iniTh;
+    uint32_t mlo = iniLo, mhi = iniHi;
+    if (phase) {
+        uint32_t nibOK = 0;  // pixels of this lane's word that lie in a cell to retry
+#pragma unroll
+        for (int bb = 0; bb < 4; bb++) {
+            const int ex = 4 * gw + bb - txFirst;
+            nibOK |= ((retry >> ((ex >= wCell) + (ex >= 2 * wCell) + (ex >= 3 * wCell))) & 1u) << bb;
         }
-    };
+        mlo = minLo & (nibOK * 0x11111111u);
+        mhi = minHi & (nibOK * 0x11111111u);
+    }
     {
         const int cnt = __popc(mlo) + __popc(mhi);
         if (cnt) {
@@ -472,7 +492,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
             const int idx = (e >> 8) * FAST_P + (e & 0xff);
             int mval = 0;
             if (q < wend) mval = fast_measure_packed(tile + idx);
-            const bool corner = mval > minTh;
+            const bool corner = mval > th;
             if (corner) sc[idx] = (uint8_t)(mval - 1);
             const uint32_t bal = __ballot_sync(0xffffffffu, corner);
             if (corner) q1[wbase + cnt + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)e;
@@ -493,16 +513,16 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
                 const int e = q1[q];
                 const int idx = (e >> 8) * FAST_P + (e & 0xff);
                 const int mval = fast_measure_packed(tile + idx);
-                if (mval > minTh) sc[idx] = (uint8_t)(mval - 1);
+                if (mval > th) sc[idx] = (uint8_t)(mval - 1);
             }
         }
     }
     __syncthreads();
     // ---- pass 3: 3x3 NMS inside the cell, for corners only ----
-    const int wCell = g.wCell;
     auto nms = [&](int ty, int tx) {
         const int ex = tx - (shift + 3);
         const int c = (ex >= wCell) + (ex >= 2 * wCell) + (ex >= 3 * wCell);
+        if (phase && !((retry >> c) & 1u)) return;  // (dense scan only) this cell was finished in phase 0
         const int r = ex - c * wCell;
         const uint8_t* s0 = sc + ty * FAST_P + tx;
         const int s = s0[0];
@@ -532,6 +552,14 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
         }
     }
     __syncthreads();
+    if (phase || minTh >= iniTh) break;  // (a retry at minTh >= iniTh can only find a subset of nothing)
+    retry = 0;
+    for (int c = 0; c < ncells; c++) retry |= (sHasIni[c] ? 0u : 1u) << c;
+    if (!retry) break;  // CTA-uniform
+    __syncthreads();    // sHasIni / sQ1 / sSeg have been read by everyone
+    if (threadIdx.x == 0) sQ1 = 0;
+    __syncthreads();
+    }
     // ---- pass 4: per-cell threshold, count, reserve, write ----
     const int n3 = sQ3;
     int mine = 0;
