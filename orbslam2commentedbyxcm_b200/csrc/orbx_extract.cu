@@ -362,7 +362,7 @@ __device__ __forceinline__ int fast_measure_packed(const uint8_t* p)
 __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
 {
     extern __shared__ __align__(16) unsigned char fsm[];
-    __shared__ int sQ1, sQ3, sCnt, sBase, sPos;
+    __shared__ int sQ1[2], sQ3, sCnt, sBase, sPos;  // sQ1: one survivor counter per phase (no reset barrier between them)
     __shared__ int sHasIni[FAST_MAXG], sSeg[FAST_T / 32];
 
     const int frame = blockIdx.y + buf.frameBase;
@@ -398,7 +398,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
         for (int n = rh * (FAST_P / 16) - threadIdx.x; n > 0; n -= FAST_T, z += FAST_T) *z = make_uint4(0, 0, 0, 0);
     }
     if (threadIdx.x < FAST_MAXG) sHasIni[threadIdx.x] = 0;
-    if (threadIdx.x == 0) { sQ1 = 0; sQ3 = 0; sCnt = 0; sPos = 0; }
+    if (threadIdx.x == 0) { sQ1[0] = 0; sQ1[1] = 0; sQ3 = 0; sCnt = 0; sPos = 0; }
     asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
 
@@ -470,7 +470,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
     {
         const int cnt = __popc(mlo) + __popc(mhi);
         if (cnt) {
-            const int base = atomicAdd(&sQ1, cnt);
+            const int base = atomicAdd(&sQ1[phase], cnt);
             if (base + cnt <= FAST_Q1CAP) {
                 push(mlo, e0, base);
                 push(mhi, e0 + ((8u * (FAST_T / 32)) << 8), base + __popc(mlo));
@@ -480,7 +480,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
     __syncthreads();
     // ---- pass 2: exact score of the queued pixels.  Each warp owns a contiguous quarter of the queue and compacts the
     //      entries that turn out to be corners in place at the head of its quarter (writes trail the reads) ----
-    const int n1 = sQ1;
+    const int n1 = sQ1[phase];
     const bool sparse = n1 <= FAST_Q1CAP;  // CTA-uniform
     const int per = (((n1 + FAST_T / 32 - 1) / (FAST_T / 32)) + 31) & ~31;
     if (sparse) {
@@ -503,12 +503,12 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
         // too many survivors for the queue (texture / noise everywhere): FAST_GIT sweeps per round
         for (int it0 = 0; it0 * (FAST_T / 32) < eh; it0 += FAST_GIT) {
             __syncthreads();
-            if (threadIdx.x == 0) sQ1 = 0;
+            if (threadIdx.x == 0) sQ1[phase] = 0;
             __syncthreads();
             const uint32_t m = ((it0 < 8 ? mlo >> (4 * it0) : mhi >> (4 * (it0 - 8)))) & ((1u << (4 * FAST_GIT)) - 1u);
-            if (m) push(m, e0 + (((uint32_t)it0 * (FAST_T / 32)) << 8), atomicAdd(&sQ1, __popc(m)));
+            if (m) push(m, e0 + (((uint32_t)it0 * (FAST_T / 32)) << 8), atomicAdd(&sQ1[phase], __popc(m)));
             __syncthreads();
-            const int n = sQ1;
+            const int n = sQ1[phase];
             for (int q = threadIdx.x; q < n; q += FAST_T) {
                 const int e = q1[q];
                 const int idx = (e >> 8) * FAST_P + (e & 0xff);
@@ -555,10 +555,8 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
     if (phase || minTh >= iniTh) break;  // (a retry at minTh >= iniTh can only find a subset of nothing)
     retry = 0;
     for (int c = 0; c < ncells; c++) retry |= (sHasIni[c] ? 0u : 1u) << c;
-    if (!retry) break;  // CTA-uniform
-    __syncthreads();    // sHasIni / sQ1 / sSeg have been read by everyone
-    if (threadIdx.x == 0) sQ1 = 0;
-    __syncthreads();
+    if (!retry) break;  // CTA-uniform.  No barrier here: phase 1 writes q1 / sSeg / sHasIni only after its own barriers,
+                        // which every thread reaches after it has read them above
     }
     // ---- pass 4: per-cell threshold, count, reserve, write ----
     const int n3 = sQ3;
