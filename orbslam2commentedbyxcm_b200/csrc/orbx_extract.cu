@@ -301,14 +301,19 @@ __global__ void __launch_bounds__(128) k_resize_words(Plan plan, Buffers buf, in
 //   3x3 NMS inside each cell's evaluated region only (cv::FAST is run on the cell ROI);
 //   cell output = NMS survivors with S >= ini if there is one, else survivors with S >= min.
 // Passes (all through shared memory):
-//   1. SWAR rejection on 4 pixels at a time: a 9-arc contains one pixel of every opposite ring pair, so a corner needs
-//      |I(p)-I(q)| > minTh for q in {N or S} and q in {E or W}  (VABSDIFF4 + a carry trick; ~90 % of pixels stop here);
-//      survivors are compacted into a queue.
-//   2. exact score for queued pixels: the 16 ring differences packed as 8 x biased u16x2, sliding min/max over windows
-//      of 9 as min3(min3) with VIMNMX3.U16x2.  The queue holds FAST_Q1CAP pixels (shared memory bounds residency); a band
-//      with more survivors than that is scored in rounds of FAST_GIT row sweeps from the masks kept in registers.
-//   3. NMS for corners only (sparse; a dense scan of the score tile after a multi-round pass 2), per-cell ini/min
-//      decision, unordered append to the level's candidate list.
+//   1. SWAR rejection on 4 pixels at a time, at both thresholds in one sweep: a 9-arc contains one pixel of every opposite
+//      ring pair, so a corner at t needs |I(p)-I(q)| > t for q in {N or S} and q in {E or W}  (VABSDIFF4 + a carry trick);
+//      the survivors of each threshold are kept as nibble masks in registers.
+//   Then two phases, as the reference calls cv::FAST twice per cell: phase 0 at iniTh, phase 1 at minTh for the columns of
+//   the cells that kept nothing at iniTh (NMS at iniTh is exact on its own: a kept pixel beats every neighbour below
+//   iniTh anyway).  Per phase:
+//   2. the phase's survivors are compacted into a queue and scored exactly: the 16 ring differences packed as 8 x biased
+//      u16x2, sliding min/max over windows of 9 as min3(min3) with VIMNMX3.U16x2.  The queue holds FAST_Q1CAP pixels
+//      (shared memory bounds residency); a band with more survivors than that is scored in rounds of FAST_GIT row sweeps
+//      from the masks.
+//   3. NMS for corners only (sparse; a dense scan of the score tile after a multi-round pass 2), per-cell record of
+//      "kept a corner >= iniTh".
+//   4. per-cell ini/min decision, unordered append to the level's candidate list.
 // The reference's candidate order (cell row-major, then pixel row-major) is carried in `ord` and only matters for
 // response ties inside a quad-tree node.
 // ------------------------------------------------------------------------------------------------------
