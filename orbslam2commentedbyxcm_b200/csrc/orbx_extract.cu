@@ -1267,8 +1267,11 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
     }
     for (; gidx < total; gidx += gstride, slot ^= 1) {
         const LevelGeom& g = plan.lv[level];
-        const int cx = (int)kp.x;
-        const uint8_t* P = &stage[wid][slot][0];
+        // cx and the warp index are the same in every lane; taking them through REDUX tells the compiler so, which keeps the
+        // patch base + alignment offset in a uniform register (shared-memory loads then address [R + UR])
+        const int cx = __reduce_min_sync(0xffffffffu, (int)kp.x);
+        const int widu = __reduce_min_sync(0xffffffffu, wid);
+        const uint8_t* P = &stage[widu][slot][0];
         const uint8_t* R = P + DESC_PBYTES;
         asm volatile("cp.async.wait_all;" ::: "memory");
         __syncwarp();  // this keypoint's patches have landed (all lanes); the previous keypoint's reads of the other buffer are done
@@ -1299,7 +1302,14 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
         // cvRound = round-half-even: adding 1.5 * 2^23 leaves the rounded integer in the low mantissa bits (|v| < 2^22);
         // the bias 0x4B400000 of both coordinates is folded into the patch base (32-bit wrap-around arithmetic)
         const float RND = 12582912.f;
-        const uint32_t cbase = (uint32_t)(18 * DESC_PP + ((cx - 18) & 15) + 18) - (uint32_t)(DESC_PP + 1) * 0x4B400000u;
+        // (the shared-memory address of the patch is folded in as well: one 32-bit base, two instructions per sample address)
+        const uint32_t cbase = (uint32_t)__cvta_generic_to_shared(P) + (uint32_t)(18 * DESC_PP + ((cx - 18) & 15) + 18) -
+                               (uint32_t)(DESC_PP + 1) * 0x4B400000u;
+        auto sample = [](uint32_t addr) {
+            uint32_t v;
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+            return (int)v;
+        };
 #pragma unroll
         for (int k = 0; k < 8; k++) {
             const float4 pt = patF[k * 32 + lane];
@@ -1307,7 +1317,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
             const uint32_t ix0 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(pt.x, a), __fmul_rn(pt.y, b)), RND));
             const uint32_t iy1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(pt.z, b), __fmul_rn(pt.w, a)), RND));
             const uint32_t ix1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(pt.z, a), __fmul_rn(pt.w, b)), RND));
-            const int t0 = P[iy0 * DESC_PP + (ix0 + cbase)], t1 = P[iy1 * DESC_PP + (ix1 + cbase)];
+            const int t0 = sample(iy0 * DESC_PP + (ix0 + cbase)), t1 = sample(iy1 * DESC_PP + (ix1 + cbase));
             val |= (t0 < t1) << k;
         }
         const long long o = (long long)lframe * capacity + gidx;
@@ -1684,12 +1694,20 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
         nl++;
     }
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_FAST], s));
-    if (!profile) {
+    // The blur runs on its own branch of the graph.  A few frames: beside FAST (both grids fit the GPU at once, lowest
+    // latency).  Batches: beside the quad-tree, whose barrier-bound CTAs leave most issue slots free (measured +2 % per
+    // step against FAST || blur, where both kernels compete for the same issue slots).
+    const bool blurAfterFast = n >= 16;
+    if (!profile && !blurAfterFast) {
         ORBX_CUDA_TRY(cudaEventRecord(evFork, s));
         ORBX_CUDA_TRY(cudaStreamWaitEvent(sb, evFork, 0));
     }
     k_fast_band<<<dim3(P.totalFastUnits, n), FAST_T, h->fastSmem, s>>>(P, B);
     nl++;
+    if (!profile && blurAfterFast) {
+        ORBX_CUDA_TRY(cudaEventRecord(evFork, s));
+        ORBX_CUDA_TRY(cudaStreamWaitEvent(sb, evFork, 0));
+    }
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_OCTREE], s));
     // large batches: many small CTAs per SM (throughput); up to a few dozen frames: more threads per level (latency)
     static const int octForce = [] { const char* e = std::getenv("ORBX_OCT_T"); return e ? std::atoi(e) : 0; }();  // experiments only
