@@ -591,6 +591,12 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the C2 / C3 side measurements")
     args = ap.parse_args()
+    # stdout carries exactly one JSON line: anything a library writes to file descriptor 1 (NCCL prints its version
+    # there on some boxes) goes to stderr instead
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(json_fd, "w")
     if args.impl == "reference":
         run_reference(args)
     else:
