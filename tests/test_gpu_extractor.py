@@ -163,6 +163,39 @@ def test_flat_and_empty_inputs(gpu, oracle_mod):
     ex.close()
 
 
+def test_fast_two_phase_paths(gpu, oracle_mod):
+    """k_fast_band scores at iniTh first and repeats at minTh only for the cells that kept nothing.  Cases built to hit
+    every branch of that: cells whose iniTh corners are all NMS ties (2x2 blocks: four equal scores, none kept, so the
+    cell is retried although it has pixels above iniTh), cells with only minTh-level corners (low contrast), cells with
+    both kinds side by side in one band, low-amplitude noise (dense survivors at minTh, none at iniTh: the retry
+    overflows the survivor queue), and thresholds where the retry cannot add anything (minTh >= iniTh) or where the
+    byte-wise pre-test is off (>= 128)."""
+    rng = np.random.default_rng(11)
+    H, W = 240, 320
+    imgs = []
+    a = np.full((H, W), 60, np.uint8)          # 2x2 bright blocks on a grid that puts some cells' only corners in ties
+    for y in range(24, H - 24, 17):
+        for x in range(24, W - 24, 23):
+            a[y:y + 2, x:x + 2] = 160
+    imgs.append(a)
+    b = np.full((H, W), 100, np.uint8)         # left half: low-contrast dots (minTh only); right half: strong dots
+    for y in range(22, H - 22, 11):
+        for x in range(22, W - 22, 13):
+            b[y, x] = 100 + (12 if x < W // 2 else 90)
+    imgs.append(b)
+    c = (100 + rng.integers(-9, 10, (H, W))).astype(np.uint8)   # noise of amplitude 9: nothing reaches iniTh
+    c[60:180, 100:220] = (100 + rng.integers(-40, 41, (120, 120))).astype(np.uint8)  # a textured island
+    imgs.append(c)
+    for cfg in [(500, 1.2, 8, 20, 7), (500, 1.2, 4, 7, 20), (500, 1.2, 4, 12, 12), (300, 1.2, 3, 130, 7), (300, 1.2, 3, 20, 128)]:
+        ex = gpu.ORBextractor(*cfg)
+        orc = oracle_mod.Extractor(*cfg)
+        for i, img in enumerate(imgs):
+            ok, od = orc.extract(img)
+            kps, desc = ex(img)
+            assert kps.tobytes() == ok.tobytes() and np.array_equal(desc, od), (cfg, i, len(kps), len(ok))
+        ex.close()
+
+
 def test_too_small_image_is_an_error_not_a_crash(gpu):
     ex = gpu.ORBextractor(1000, 1.2, 8, 20, 7)
     with pytest.raises(gpu.OrbxError):
