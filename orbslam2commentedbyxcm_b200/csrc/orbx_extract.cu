@@ -412,7 +412,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
     const int wCell = g.wCell;
     const int txFirst = shift + 3, txEnd = shift + 3 + evalW;  // evaluated tile columns [txFirst, txEnd)
     const int gw = (txFirst >> 2) + lane;                        // ((txEnd-1)>>2) - (txFirst>>2) + 1 <= 32 words
-    const int ncells = min(FAST_MAXG, (evalW - 1) / wCell + 1);
+    const int ncells = 1 + (evalW - 1 >= wCell) + (evalW - 1 >= 2 * wCell) + (evalW - 1 >= 3 * wCell);  // = min(4, (evalW-1)/wCell + 1), no division
     constexpr int FAST_RPW = (59 + FAST_T / 32 - 1) / (FAST_T / 32);  // sweeps: eh <= 59
     static_assert(FAST_RPW <= 16, "survivor nibbles must fit 64 bits");
     // queue entry = tile row << 8 | tile column; bit b of sweep `it` is pixel (warp + 3 + 4 * it, 4 * gw + (b & 3))
