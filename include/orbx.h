@@ -116,7 +116,7 @@ int orbx_get_pyramid_level(orbx_handle* h, int frame, int level, uint8_t* dst, s
 #define ORBX_STAGE_H2D 0
 #define ORBX_STAGE_PYRAMID 1
 #define ORBX_STAGE_FAST 2
-#define ORBX_STAGE_OCTREE 3 /* quad-tree distribution + IC_Angle */
+#define ORBX_STAGE_OCTREE 3 /* quad-tree distribution (IC_Angle is part of ORBX_STAGE_DESC: k_describe) */
 #define ORBX_STAGE_BLUR 4
 #define ORBX_STAGE_DESC 5
 #define ORBX_STAGE_D2H 6
@@ -132,6 +132,20 @@ int orbx_set_use_graph(orbx_handle* h, int on);
  * in level pixel coordinates, unordered; the blurred interior of one level (rows_l x cols_l, tight). */
 int orbx_debug_get_candidates(orbx_handle* h, int frame, int level, int* xyr, int cap, int* n);
 int orbx_debug_get_blurred(orbx_handle* h, int frame, int level, uint8_t* dst);
+
+/* Domain sweeps of the two transcendental device functions behind IC_Angle and the steered descriptor (parity tests):
+ * the device cosf/sinf restatement of glibc (src/ORBextractor.cc:109,123-125: angle = deg * factorPI) over the float bit
+ * patterns first_bits .. first_bits + count - 1 of `deg`, and the device cv::fastAtan2 (src/ORBextractor.cc:105) over
+ * generated integer moment pairs (mode 0: pair i = (i / 10001 - 5000, i % 10001 - 5000), the dense grid [-5000, 5000]^2;
+ * mode k >= 1: two signed 22-bit values from splitmix64(i + k * 0x9E3779B97F4A7C15)).  The *_checksum forms fold every
+ * `chunk` consecutive values into sum_i bits(value_i) * (2 i + 1) mod 2^64 (i = index inside the chunk), one word per
+ * chunk, so all 1 135 869 953 angles can be compared with the CPU oracle without moving them; the plain forms return
+ * the values (n <= 2^24 is sensible). */
+int orbx_debug_sincosf_checksum(int device, uint32_t first_bits, uint64_t count, uint64_t chunk, uint64_t* sum_sin,
+                                uint64_t* sum_cos);
+int orbx_debug_sincosf(int device, uint32_t first_bits, int n, float* out_sin, float* out_cos);
+int orbx_debug_fast_atan2_checksum(int device, int mode, uint64_t first, uint64_t count, uint64_t chunk, uint64_t* sum);
+int orbx_debug_fast_atan2(int device, int mode, uint64_t first, int n, float* out);
 
 /* ---- matcher -------------------------------------------------------------------------------------- */
 

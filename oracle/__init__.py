@@ -67,6 +67,8 @@ def _bind_ref(L):
     _bind_extractor(L, "orbref_")
     L.orbref_extract_batch.restype = _c.c_long
     L.orbref_extract_batch.argtypes = [_i, _f, _i, _i, _i, _vp, _i, _i, _i, _i, _vp]
+    L.orbref_extract_batch_full.restype = _c.c_long
+    L.orbref_extract_batch_full.argtypes = [_i, _f, _i, _i, _i, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp]
 
 
 def lib(kind="strict"):
@@ -123,6 +125,11 @@ def _bind_all(L):
     L.orbo_fast9_16_simple.argtypes = [_vp, _i, _i, _sz, _i, _i, _vp, _i]
     L.orbo_gaussian_blur_7x7_s2.argtypes = [_vp, _i, _i, _sz, _vp, _sz]
     L.orbo_fast_atan2.argtypes = [_vp, _vp, _vp, _i]
+    _u64 = _c.c_uint64
+    L.orbo_sincosf_checksum.argtypes = [_c.c_uint32, _u64, _u64, _vp, _vp, _i]
+    L.orbo_fast_atan2_checksum.argtypes = [_i, _u64, _u64, _u64, _vp, _i]
+    L.orbo_sweep_sincosf_values.argtypes = [_c.c_uint32, _i, _vp, _vp]
+    L.orbo_sweep_fast_atan2_values.argtypes = [_i, _u64, _i, _vp]
     L.orbo_cv_round_f.restype = _i
     L.orbo_cv_round_f.argtypes = [_f]
     # matcher
@@ -277,6 +284,22 @@ def extract_batch(imgs, nfeatures, scale_factor, nlevels, ini_th, min_th, thread
     fn = L.orbref_extract_batch if kind.startswith("ref") else L.orbo_extract_batch
     tot = fn(nfeatures, scale_factor, nlevels, ini_th, min_th, imgs.ctypes.data, n, rows, cols, threads, counts.ctypes.data)
     return tot, counts
+
+
+def ref_extract_batch_full(imgs, nfeatures, scale_factor, nlevels, ini_th, min_th, cap, threads=0, kind="ref_fast"):
+    """The reference's own ORBextractor.cc (oracle/_ref) over a batch, frame-parallel: (kps[n, cap] KP_DTYPE,
+    desc[n, cap, 32] u8, counts[n]).  Returns None when oracle/_ref is not built."""
+    L = lib(kind)
+    if L is None:
+        return None
+    imgs = np.ascontiguousarray(imgs, np.uint8)
+    n, rows, cols = imgs.shape
+    kps = np.zeros((n, cap), KP_DTYPE)
+    desc = np.zeros((n, cap, 32), np.uint8)
+    counts = np.zeros(n, np.int32)
+    L.orbref_extract_batch_full(nfeatures, scale_factor, nlevels, ini_th, min_th, imgs.ctypes.data, n, rows, cols,
+                                threads or (os.cpu_count() or 1), cap, kps.ctypes.data, desc.ctypes.data, counts.ctypes.data)
+    return kps, desc, counts
 
 
 def bruteforce(q, db, threads=1, kind="strict"):
@@ -494,3 +517,33 @@ def search_for_triangulation(kf1, kf2, F12, ex, ey, scale_factors2, level_sigma2
         _ptr(kf2["has_mp"]), len(kf2["node_id"]), _ptr(kf2["node_id"]), _ptr(kf2["node_start"]), _ptr(kf2["node_feat"]),
         F.ctypes.data, float(ex), float(ey), sf.ctypes.data, sg.ctypes.data, int(only_stereo), int(check_orientation), out.ctypes.data)
     return n, out[:n1]
+
+
+def sincosf_checksum(first_bits, count, chunk, threads=0, kind="fast"):
+    """Checker side of orbx_debug_sincosf_checksum: per-chunk position-weighted checksums of glibc sinf / cosf of
+    deg * factorPI over the float bit patterns first_bits .. first_bits + count - 1."""
+    n = (count + chunk - 1) // chunk
+    a = np.zeros(n, np.uint64)
+    b = np.zeros(n, np.uint64)
+    lib(kind).orbo_sincosf_checksum(first_bits, count, chunk, _ptr(a), _ptr(b), threads or (os.cpu_count() or 1))
+    return a, b
+
+
+def fast_atan2_checksum(mode, first, count, chunk, threads=0, kind="fast"):
+    n = (count + chunk - 1) // chunk
+    a = np.zeros(n, np.uint64)
+    lib(kind).orbo_fast_atan2_checksum(mode, first, count, chunk, _ptr(a), threads or (os.cpu_count() or 1))
+    return a
+
+
+def sweep_sincosf_values(first_bits, n, kind="strict"):
+    s = np.zeros(n, np.float32)
+    c = np.zeros(n, np.float32)
+    lib(kind).orbo_sweep_sincosf_values(first_bits, n, _ptr(s), _ptr(c))
+    return s, c
+
+
+def sweep_fast_atan2_values(mode, first, n, kind="strict"):
+    a = np.zeros(n, np.float32)
+    lib(kind).orbo_sweep_fast_atan2_values(mode, first, n, _ptr(a))
+    return a

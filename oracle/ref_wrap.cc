@@ -113,4 +113,38 @@ long orbref_extract_batch(int nfeatures, float scaleFactor, int nlevels, int ini
     return s;
 }
 
+// Same frame-parallel batch, returning everything: keypoint records and descriptor rows of frame i go to
+// out_kps[i * cap ..] / out_desc[(i * cap ..) * 32] (at most cap per frame, out_counts[i] = the true count).  Used by the
+// bulk GPU parity sweep and by bench.py's parity hash of the timed batch.
+long orbref_extract_batch_full(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh, const uint8_t* imgs,
+                               int n, int rows, int cols, int threads, int cap, RefKp* out_kps, uint8_t* out_desc,
+                               int* out_counts)
+{
+    if (threads < 1) threads = 1;
+    std::vector<long> tot(threads, 0);
+    std::vector<std::thread> th;
+    for (int t = 0; t < threads; t++)
+        th.emplace_back([&, t]() {
+            ORB_SLAM2::ORBextractor ex(nfeatures, scaleFactor, nlevels, iniTh, minTh);
+            std::vector<cv::KeyPoint> kps;
+            for (int i = t; i < n; i += threads) {
+                cv::Mat im(rows, cols, CV_8UC1, (void*)(imgs + (size_t)i * rows * cols), (size_t)cols);
+                cv::Mat mask, desc;
+                ex(im, mask, kps, desc);
+                out_counts[i] = (int)kps.size();
+                tot[t] += (long)kps.size();
+                const int k = std::min((int)kps.size(), cap);
+                for (int j = 0; j < k; j++) {
+                    const cv::KeyPoint& kp = kps[j];
+                    out_kps[(size_t)i * cap + j] = RefKp{kp.pt.x, kp.pt.y, kp.size, kp.angle, kp.response, kp.octave};
+                    std::memcpy(out_desc + ((size_t)i * cap + j) * 32, desc.ptr(j), 32);
+                }
+            }
+        });
+    for (auto& x : th) x.join();
+    long s = 0;
+    for (long v : tot) s += v;
+    return s;
+}
+
 }  // extern "C"

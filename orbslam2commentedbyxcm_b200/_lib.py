@@ -77,6 +77,10 @@ SIGNATURES = {
     "orbx_set_use_graph": (_i, [_vp, _i]),
     "orbx_debug_get_candidates": (_i, [_vp, _i, _i, _vp, _i, _vp]),
     "orbx_debug_get_blurred": (_i, [_vp, _i, _i, _vp]),
+    "orbx_debug_sincosf_checksum": (_i, [_i, C.c_uint32, C.c_uint64, C.c_uint64, _vp, _vp]),
+    "orbx_debug_sincosf": (_i, [_i, C.c_uint32, _i, _vp, _vp]),
+    "orbx_debug_fast_atan2_checksum": (_i, [_i, _i, C.c_uint64, C.c_uint64, C.c_uint64, _vp]),
+    "orbx_debug_fast_atan2": (_i, [_i, _i, C.c_uint64, _i, _vp]),
     "orbm_descriptor_distance": (_i, [_vp, _vp]),
     "orbm_create": (_i, [_i, C.POINTER(_vp)]),
     "orbm_destroy": (None, [_vp]),

@@ -1802,6 +1802,112 @@ int pyramid_view(orbx_handle* h, int frame, PyramidView* out)
 }
 }  // namespace orbx
 
+// ------------------------------------------------------------------------------------------------------
+// Domain sweeps of the two transcendental device functions the descriptor path depends on (parity tests only):
+// every launch folds a contiguous index range into one position-weighted 64-bit checksum per chunk, so that a test can
+// compare ALL 1 135 869 953 float angles deg in [0, 360] (cosf/sinf of deg * factorPI, src/ORBextractor.cc:109,123-125)
+// and >= 1e8 integer moment pairs (cv::fastAtan2((float)m01, (float)m10), :105) against the CPU oracle without moving
+// the values.  checksum = sum_i bits(value_i) * (2 * i + 1) mod 2^64, i = index inside the chunk.
+// ------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void dbg_atan2_pair(int mode, unsigned long long i, int& y, int& x)
+{
+    if (mode == 0) {  // dense grid [-H, H]^2, H = 5000, row-major
+        const unsigned W = 10001u;
+        y = (int)(i / W) - 5000;
+        x = (int)(i % W) - 5000;
+    } else {          // splitmix64(i) -> two signed 22-bit moments (|m| < 2^21 covers the 31x31 disc of u8 pixels)
+        unsigned long long z = i + 0x9E3779B97F4A7C15ull * (unsigned long long)mode;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        z ^= z >> 31;
+        y = (int)(z & 0x3fffffu) - 0x200000;
+        x = (int)((z >> 32) & 0x3fffffu) - 0x200000;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_dbg_sweep(int what, int mode, unsigned long long first, unsigned long long total,
+                                                    unsigned long long chunk, unsigned long long* sumA,
+                                                    unsigned long long* sumB)
+{
+    const unsigned long long c = blockIdx.x;
+    const unsigned long long lo = c * chunk, hi = min(lo + chunk, total);
+    unsigned long long a = 0, b = 0;
+    const float factorPI = 0.0174532924f;
+    for (unsigned long long i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+        const unsigned long long w = 2ull * (i - lo) + 1ull;
+        if (what == 0) {
+            const float deg = __uint_as_float((uint32_t)(first + i));
+            const SinCosOut sc = sincosf_glibc(__fmul_rn(deg, factorPI));
+            a += (unsigned long long)__float_as_uint(sc.s) * w;
+            b += (unsigned long long)__float_as_uint(sc.c) * w;
+        } else {
+            int y, x;
+            dbg_atan2_pair(mode, first + i, y, x);
+            a += (unsigned long long)__float_as_uint(fast_atan2_dev((float)y, (float)x)) * w;
+        }
+    }
+    __shared__ unsigned long long sa[256], sb[256];
+    sa[threadIdx.x] = a; sb[threadIdx.x] = b;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if ((int)threadIdx.x < s) { sa[threadIdx.x] += sa[threadIdx.x + s]; sb[threadIdx.x] += sb[threadIdx.x + s]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { sumA[c] = sa[0]; if (sumB) sumB[c] = sb[0]; }
+}
+
+__global__ void k_dbg_values(int what, int mode, unsigned long long first, int n, float* outA, float* outB)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (what == 0) {
+        const float deg = __uint_as_float((uint32_t)(first + i));
+        const SinCosOut sc = sincosf_glibc(__fmul_rn(deg, 0.0174532924f));
+        outA[i] = sc.s; outB[i] = sc.c;
+    } else {
+        int y, x;
+        dbg_atan2_pair(mode, first + i, y, x);
+        outA[i] = fast_atan2_dev((float)y, (float)x);
+    }
+}
+
+static int dbg_sweep(int device, int what, int mode, unsigned long long first, unsigned long long total,
+                     unsigned long long chunk, unsigned long long* sumA, unsigned long long* sumB)
+{
+    if (!sumA || chunk == 0 || (what == 0 && !sumB)) { set_error("orbx_debug sweep: bad argument"); return ORBX_ERR_BAD_ARG; }
+    const unsigned long long nchunks = (total + chunk - 1) / chunk;
+    if (nchunks == 0) return ORBX_OK;
+    if (nchunks > 0x7fffffffull) { set_error("orbx_debug sweep: too many chunks"); return ORBX_ERR_BAD_ARG; }
+    ORBX_CUDA_TRY(cudaSetDevice(device));
+    unsigned long long *dA = nullptr, *dB = nullptr;
+    ORBX_CUDA_TRY(cudaMalloc(&dA, nchunks * 8));
+    ORBX_CUDA_TRY(cudaMalloc(&dB, nchunks * 8));
+    k_dbg_sweep<<<(unsigned)nchunks, 256>>>(what, mode, first, total, chunk, dA, what == 0 ? dB : nullptr);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = cudaMemcpy(sumA, dA, nchunks * 8, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && what == 0) e = cudaMemcpy(sumB, dB, nchunks * 8, cudaMemcpyDeviceToHost);
+    cudaFree(dA); cudaFree(dB);
+    ORBX_CUDA_TRY(e);
+    return ORBX_OK;
+}
+
+static int dbg_values(int device, int what, int mode, unsigned long long first, int n, float* outA, float* outB)
+{
+    if (n < 0 || !outA || (what == 0 && !outB)) { set_error("orbx_debug values: bad argument"); return ORBX_ERR_BAD_ARG; }
+    if (n == 0) return ORBX_OK;
+    ORBX_CUDA_TRY(cudaSetDevice(device));
+    float *dA = nullptr, *dB = nullptr;
+    ORBX_CUDA_TRY(cudaMalloc(&dA, (size_t)n * 4));
+    ORBX_CUDA_TRY(cudaMalloc(&dB, (size_t)n * 4));
+    k_dbg_values<<<(n + 255) / 256, 256>>>(what, mode, first, n, dA, dB);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = cudaMemcpy(outA, dA, (size_t)n * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && what == 0) e = cudaMemcpy(outB, dB, (size_t)n * 4, cudaMemcpyDeviceToHost);
+    cudaFree(dA); cudaFree(dB);
+    ORBX_CUDA_TRY(e);
+    return ORBX_OK;
+}
+
 extern "C" {
 
 const char* orbx_last_error(void) { return last_error().c_str(); }
@@ -2240,6 +2346,24 @@ int orbx_debug_get_blurred(orbx_handle* h, int frame, int level, uint8_t* dst)
     ORBX_CUDA_TRY(cudaMemcpy2DAsync(dst, g.w, src, g.pitch, g.w, g.h, cudaMemcpyDeviceToHost, h->stream));
     ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
     return ORBX_OK;
+}
+
+int orbx_debug_sincosf_checksum(int device, uint32_t first_bits, uint64_t count, uint64_t chunk, uint64_t* sum_sin,
+                                uint64_t* sum_cos)
+{
+    return dbg_sweep(device, 0, 0, first_bits, count, chunk, (unsigned long long*)sum_sin, (unsigned long long*)sum_cos);
+}
+int orbx_debug_sincosf(int device, uint32_t first_bits, int n, float* out_sin, float* out_cos)
+{
+    return dbg_values(device, 0, 0, first_bits, n, out_sin, out_cos);
+}
+int orbx_debug_fast_atan2_checksum(int device, int mode, uint64_t first, uint64_t count, uint64_t chunk, uint64_t* sum)
+{
+    return dbg_sweep(device, 1, mode, first, count, chunk, (unsigned long long*)sum, nullptr);
+}
+int orbx_debug_fast_atan2(int device, int mode, uint64_t first, int n, float* out)
+{
+    return dbg_values(device, 1, mode, first, n, out, nullptr);
 }
 
 }  // extern "C"
