@@ -279,7 +279,10 @@ int orbm_stereo_rows(orbm_context* m, int nl, const float* lx, const float* ly, 
 
 /* Replaces the WHOLE of Frame::ComputeStereoMatches (src/Frame.cc:673-885): coarse row search, SAD refinement on the
  * pyramid levels (11x11 window, 11 shifts, sub-pixel parabola fit, :767-866) and removal of matches whose SAD is >=
- * 2.1 x median (:868-884, executed once after the loop as in upstream ORB-SLAM2).  The level images are read straight
+ * 2.1 x median (:868-884).  In this reference that block sits INSIDE the per-keypoint loop, so a match is tested against
+ * the running median after its own insertion and after every later one; that is the default (bit-identical to the
+ * reference's Frame constructor, tests/test_oracle_matcher.py).  orbm_set_stereo_outlier_mode(m, 1) selects the upstream
+ * ORB-SLAM2 placement instead (one test against the final median after the loop).  The level images are read straight
  * from the device arenas of the two extractor handles (frame indices refer to their last extracted batch), so
  * mvImagePyramid never has to be downloaded.  Keypoint arrays are HOST pointers.  mb = baseline in metres (mbf / fx):
  * minZ = mb, maxD = mbf / minZ.  u_right / depth: nl entries, -1 where unmatched (mvuRight, mvDepth). */
@@ -287,6 +290,7 @@ int orbm_stereo_match(orbm_context* m, orbx_handle* ex_left, int frame_left, orb
                       int nl, const float* lx, const float* ly, const int32_t* loct, const uint8_t* ldesc, int nr,
                       const float* rx, const float* ry, const int32_t* roct, const uint8_t* rdesc, float mbf, float mb,
                       float* u_right, float* depth, int* n_matched);
+int orbm_set_stereo_outlier_mode(orbm_context* m, int mode /* 0 = as this reference (default), 1 = upstream */);
 
 /* DBoW2::FeatureVector (std::map<NodeId, vector<unsigned>>) flattened as CSR with ascending node ids. */
 typedef struct orbm_featvec_view {

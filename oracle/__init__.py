@@ -147,7 +147,7 @@ def _bind_all(L):
     L.orbo_get_level_ptr.restype = _vp
     L.orbo_get_level_ptr.argtypes = [_vp, _i, _vp]
     L.orbo_stereo_match.restype = _i
-    L.orbo_stereo_match.argtypes = [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _f, _vp, _vp]
+    L.orbo_stereo_match.argtypes = [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _f, _i, _vp, _vp]
     L.orbo_search_window.restype = _i
     L.orbo_search_window.argtypes = ([_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _vp]
                                      + [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp] + [_i, _i, _f, _i, _vp])
@@ -384,8 +384,10 @@ def search_by_bow(kf, fr, nnratio, check_orientation):
     return n, out
 
 
-def stereo_match(exL, exR, left, right, n_rows, mbf, mb):
-    """Full ComputeStereoMatches on two oracle Extractor objects that have just extracted the left / right image."""
+def stereo_match(exL, exR, left, right, n_rows, mbf, mb, upstream_outliers=False):
+    """Full ComputeStereoMatches on two oracle Extractor objects that have just extracted the left / right image.
+    upstream_outliers=False: the SAD outlier block inside the keypoint loop as in this reference (src/Frame.cc:868-884);
+    True: once after the loop as in upstream ORB-SLAM2."""
     L = lib()
     nl, nlev = len(left["x"]), exL.nlevels
     sf = exL.scale_factors()
@@ -407,7 +409,7 @@ def stereo_match(exL, exR, left, right, n_rows, mbf, mb):
         nl, _ptr(left["x"]), _ptr(left["y"]), _ptr(left["octave"]), _ptr(left["desc"]),
         len(right["x"]), _ptr(right["x"]), _ptr(right["y"]), _ptr(right["octave"]), _ptr(right["desc"]),
         nlev, sf.ctypes.data, inv.ctypes.data, lp, rp, ls.ctypes.data, rs.ctypes.data, rc.ctypes.data,
-        n_rows, mbf, mb, ur.ctypes.data, dp.ctypes.data)
+        n_rows, mbf, mb, 1 if upstream_outliers else 0, ur.ctypes.data, dp.ctypes.data)
     return n, ur[:nl], dp[:nl]
 
 

@@ -341,4 +341,35 @@ static inline float fast_atan2(float y, float x)
     return a;
 }
 
+// cv::undistortPoints(src, dst, K, distCoef, R = Mat(), P = K) as called by Frame::UndistortKeyPoints /
+// ComputeImageBounds (src/Frame.cc:586-660): cvUndistortPointsInternal of OpenCV 4.x for that call (R = identity,
+// P = K, default criteria = 5 iterations, no tilt terms); everything in double, K and the coefficients widened from
+// float, result narrowed to float.  Pinned bit-for-bit against cv2 4.13 (tests/test_oracle_primitives.py,
+// tests/golden/undistort_cv2.npz).
+inline void undistort_points(const float* px, const float* py, int n, float fxf, float fyf, float cxf, float cyf,
+                             const float* dist, int ndist, float* ox, float* oy)
+{
+    double k[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // k1 k2 p1 p2 k3 k4 k5 k6 s1 s2 s3 s4
+    for (int i = 0; i < ndist && i < 12; i++) k[i] = (double)dist[i];
+    const double fx = fxf, fy = fyf, cx = cxf, cy = cyf;
+    const double ifx = 1. / fx, ify = 1. / fy;
+    for (int i = 0; i < n; i++) {
+        const double u = px[i], v = py[i];
+        double x = (u - cx) * ifx, y = (v - cy) * ify;
+        const double x0 = x, y0 = y;
+        for (int j = 0; j < 5; j++) {
+            const double r2 = x * x + y * y;
+            const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+            if (icdist < 0) { x = (u - cx) * ifx; y = (v - cy) * ify; break; }
+            const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+            const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+            x = (x0 - deltaX) * icdist;
+            y = (y0 - deltaY) * icdist;
+        }
+        // P * R = K: xx = fx*x + 0*y + cx, yy = 0*x + fy*y + cy, ww = 1 / (0*x + 0*y + 1)
+        ox[i] = (float)((fx * x + cx) * 1.0);
+        oy[i] = (float)((fy * y + cy) * 1.0);
+    }
+}
+
 }  // namespace orbo

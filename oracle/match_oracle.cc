@@ -22,6 +22,7 @@
 #include <vector>
 #include <algorithm>
 #include <thread>
+#include "cvprim.h"
 
 namespace {
 
@@ -104,27 +105,7 @@ void orbo_undistort_points(const float* px, const float* py, int n, float fxf, f
         for (int i = 0; i < n; i++) { ox[i] = px[i]; oy[i] = py[i]; }
         return;
     }
-    double k[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // k1 k2 p1 p2 k3 k4 k5 k6 s1 s2 s3 s4
-    for (int i = 0; i < ndist && i < 12; i++) k[i] = (double)dist[i];
-    const double fx = fxf, fy = fyf, cx = cxf, cy = cyf;
-    const double ifx = 1. / fx, ify = 1. / fy;
-    for (int i = 0; i < n; i++) {
-        const double u = px[i], v = py[i];
-        double x = (u - cx) * ifx, y = (v - cy) * ify;
-        const double x0 = x, y0 = y;
-        for (int j = 0; j < 5; j++) {
-            const double r2 = x * x + y * y;
-            const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
-            if (icdist < 0) { x = (u - cx) * ifx; y = (v - cy) * ify; break; }
-            const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
-            const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
-            x = (x0 - deltaX) * icdist;
-            y = (y0 - deltaY) * icdist;
-        }
-        // P * R = K: xx = fx*x + 0*y + cx, yy = 0*x + fy*y + cy, ww = 1 / (0*x + 0*y + 1)
-        ox[i] = (float)((fx * x + cx) * 1.0);
-        oy[i] = (float)((fy * y + cy) * 1.0);
-    }
+    orbo::undistort_points(px, py, n, fxf, fyf, cxf, cyf, dist, ndist, ox, oy);
 }
 
 // SearchByProjection(Frame&, vector<MapPoint*>&, th).  out_match[idx] = index of the map point written into
@@ -316,8 +297,11 @@ int orbo_search_by_bow(
 // ---------------------------------------------------------------------------------------------------------------------
 // Full Frame::ComputeStereoMatches (src/Frame.cc:673-885): coarse row search (orbo_stereo_rows above) + SAD refinement
 // on the pyramid levels with sub-pixel parabola fit (:767-866) + removal of matches whose SAD distance is >= 2.1 x median
-// (:868-884).  Decision D7: the fork executes the outlier block INSIDE the per-keypoint loop (indexing an empty vector on
-// the first iterations); the oracle follows upstream ORB-SLAM2 and runs it once after the loop.  Decision D5: minZ = mb.
+// (:868-884).  Decision D7: this reference executes the outlier block INSIDE the per-keypoint loop (upstream ORB-SLAM2 has
+// it after the loop); outlier_mode 0 reproduces that placement and is what the compiled reference is compared with
+// (tests/test_oracle_matcher.py): the block runs at the end of every iteration that reaches it, reads element 0 of a
+// still-empty vector before the first match (never used: its loop does not run) and rejects against the running median.
+// outlier_mode 1 = upstream placement, kept for callers that link against upstream semantics.  Decision D5: minZ = mb.
 // Level planes are given as pointers to the interior pixel (0,0) of the padded pyramid planes.
 // ---------------------------------------------------------------------------------------------------------------------
 extern "C" int orbo_stereo_match(
@@ -325,7 +309,7 @@ extern "C" int orbo_stereo_match(
     int nr, const float* rx, const float* ry, const int32_t* roct, const uint8_t* rdesc,
     int nlevels, const float* scaleFactors, const float* invScaleFactors,
     const uint8_t* const* lplane, const uint8_t* const* rplane, const int32_t* lstep, const int32_t* rstep, const int32_t* rcols,
-    int nRows, float mbf, float mb, float* uRight, float* depth)
+    int nRows, float mbf, float mb, int outlier_mode, float* uRight, float* depth)
 {
     (void)nlevels;
     const float minZ = mb, minD = 0, maxD = mbf / minZ;
@@ -376,8 +360,18 @@ extern "C" int orbo_stereo_match(
             uRight[iL] = bestuR;
             vDistIdx.push_back(std::pair<int, int>(bestDist, iL));
         }
+        if (outlier_mode == 0 && !vDistIdx.empty()) {  // src/Frame.cc:868-884, inside the loop
+            std::sort(vDistIdx.begin(), vDistIdx.end());
+            const float median = vDistIdx[vDistIdx.size() / 2].first;
+            const float thDist = 1.5f * 1.4f * median;
+            for (int i = (int)vDistIdx.size() - 1; i >= 0; i--) {
+                if (vDistIdx[i].first < thDist) break;
+                uRight[vDistIdx[i].second] = -1;
+                depth[vDistIdx[i].second] = -1;
+            }
+        }
     }
-    if (!vDistIdx.empty()) {
+    if (outlier_mode == 1 && !vDistIdx.empty()) {
         std::sort(vDistIdx.begin(), vDistIdx.end());
         const float median = vDistIdx[vDistIdx.size() / 2].first;
         const float thDist = 1.5f * 1.4f * median;

@@ -1,0 +1,742 @@
+// oracle/matchref_wrap.cc -- TEST INFRASTRUCTURE.
+//
+// C entry points around the reference's OWN matcher-side code, compiled UNMODIFIED from /root/reference (oracle/Makefile,
+// target `ref` -> oracle/_ref/libmatchref.so): src/ORBmatcher.cc, src/Frame.cc, src/KeyFrame.cc, src/MapPoint.cc,
+// src/Map.cc, src/KeyFrameDatabase.cc, src/ORBextractor.cc and the vendored Thirdparty/DBoW2 sources, against the mini-cv
+// shim (oracle/shim).  The only reference header that is replaced is include/Converter.h (Eigen + g2o, absent here): the
+// two call sites use one function of it, Converter::toDescriptorVector, defined below.
+//
+// Every entry point takes flat arrays, builds REAL ORB_SLAM2::Frame / KeyFrame / MapPoint / Map objects from them
+// (compiled with -fno-access-control so that protected members can be filled in directly), calls the reference member
+// function and flattens what it wrote.  It pins oracle/match_oracle.cc (tests/test_oracle_matcher.py) and generates the
+// golden fixtures the GPU tests consume (tools/make_golden.py).
+//
+// Pose arithmetic.  The GPU path and the oracle take map points AFTER projection (u, v, ur, radius, level range); the
+// reference projects inside its functions with cv::Mat float arithmetic (un-vendored OpenCV gemm).  The harness keeps that
+// arithmetic EXACT so that it cannot depend on the gemm flavour: camera intrinsics fx = fy = 1, cx = cy = 0, every pose the
+// identity (or a pure translation where a function needs one), and a point that must project to (u, v) with inverse depth
+// invz (a power of two) sits at (u / invz, v / invz, 1 / invz): fx * (u z) * (1 / z) + 0 == u bit for bit, ur = u - mbf *
+// invz is one multiplication by a power of two and one subtraction.  The predicted pyramid level L is steered through
+// MapPoint::mfMaxDistance = dist * scale^(L - 0.5), so ceil(log(max / dist) / log(scale)) == L with a wide margin.
+#include "ORBmatcher.h"
+#include "Frame.h"
+#include "KeyFrame.h"
+#include "MapPoint.h"
+#include "Map.h"
+#include "ORBVocabulary.h"
+#include "Converter.h"
+#include <cstdint>
+#include <cstring>
+#include <cstddef>
+#include <cmath>
+#include <map>
+#include <new>
+#include <vector>
+
+using namespace ORB_SLAM2;
+
+// src/Converter.cc:29-40 restated: one 1 x 32 row per descriptor
+std::vector<cv::Mat> Converter::toDescriptorVector(const cv::Mat& Descriptors)
+{
+    std::vector<cv::Mat> v;
+    v.reserve(Descriptors.rows);
+    for (int j = 0; j < Descriptors.rows; j++) v.push_back(Descriptors.row(j));
+    return v;
+}
+
+extern "C" {
+
+struct orbr_frame_in {
+    int32_t n;
+    const float* x;
+    const float* y;
+    const int32_t* octave;
+    const float* angle;          // may be NULL (0)
+    const float* u_right;        // may be NULL (all -1)
+    const uint8_t* desc;         // n x 32
+    const uint8_t* occupied;     // may be NULL; 1 = the keypoint holds a map point with Observations() > 0
+    float min_x, min_y, max_x, max_y, w_inv, h_inv;
+    const float* scale_factors;
+    int32_t nlevels;
+    float mbf;
+    int32_t n_nodes;             // optional FeatureVector in CSR form
+    const int32_t* node_id;
+    const int32_t* node_start;
+    const int32_t* node_feat;
+    const uint8_t* has_mp;       // may be NULL; key frames: feature has a good map point
+};
+
+struct orbr_query_in {
+    int32_t n;
+    const float* x;              // projection (u, v)
+    const float* y;
+    const float* invz;           // may be NULL (1); powers of two
+    const int32_t* level;        // predicted level / octave of the source keypoint
+    const float* angle;          // may be NULL
+    const uint8_t* valid;        // may be NULL (all valid)
+    const uint8_t* blocks;       // may be NULL (all): Observations() > 0
+    const uint8_t* desc;         // n x 32
+};
+
+}  // extern "C"
+
+namespace {
+
+struct World {
+    Map map;
+    std::vector<Frame*> frames;
+    std::vector<KeyFrame*> kfs;
+    std::vector<MapPoint*> mps;
+    KeyFrame* seed = nullptr;
+    ~World()
+    {
+        for (auto* p : mps) delete p;
+        for (auto* p : kfs) delete p;
+        for (auto* p : frames) delete p;
+    }
+};
+
+cv::Mat eye4()
+{
+    cv::Mat T = cv::Mat::eye(4, 4, CV_32F);
+    return T;
+}
+
+void set_camera(const orbr_frame_in& f)
+{
+    Frame::fx = 1.f; Frame::fy = 1.f; Frame::cx = 0.f; Frame::cy = 0.f; Frame::invfx = 1.f; Frame::invfy = 1.f;
+    Frame::mnMinX = f.min_x; Frame::mnMinY = f.min_y; Frame::mnMaxX = f.max_x; Frame::mnMaxY = f.max_y;
+    Frame::mfGridElementWidthInv = f.w_inv;
+    Frame::mfGridElementHeightInv = f.h_inv;
+    Frame::mbInitialComputations = false;
+}
+
+// A Frame as Tracking would hold it after construction, filled from flat arrays; the grid comes from the reference's own
+// Frame::AssignFeaturesToGrid.
+Frame* build_frame(World& w, const orbr_frame_in& f)
+{
+    set_camera(f);
+    Frame* F = new Frame();
+    w.frames.push_back(F);
+    F->mpORBvocabulary = nullptr;
+    F->mpORBextractorLeft = F->mpORBextractorRight = nullptr;
+    F->mTimeStamp = 0;
+    F->mK = cv::Mat::eye(3, 3, CV_32F);
+    F->mDistCoef = cv::Mat::zeros(4, 1, CV_32F);
+    F->mbf = f.mbf;
+    F->mb = f.mbf / Frame::fx;
+    F->mThDepth = 1e9f;
+    F->N = f.n;
+    F->mvKeys.resize(f.n);
+    for (int i = 0; i < f.n; i++) {
+        const int oct = f.octave ? f.octave[i] : 0;
+        F->mvKeys[i] = cv::KeyPoint(f.x[i], f.y[i], 31.f * f.scale_factors[oct], f.angle ? f.angle[i] : 0.f, 0.f, oct);
+    }
+    F->mvKeysUn = F->mvKeys;
+    F->mvuRight.assign(f.n, -1.f);
+    F->mvDepth.assign(f.n, -1.f);
+    if (f.u_right)
+        for (int i = 0; i < f.n; i++) {
+            F->mvuRight[i] = f.u_right[i];
+            if (f.u_right[i] >= 0) F->mvDepth[i] = 1.f;
+        }
+    F->mDescriptors = cv::Mat(f.n, 32, CV_8U);
+    if (f.n) std::memcpy(F->mDescriptors.data, f.desc, (size_t)f.n * 32);
+    F->mvpMapPoints.assign(f.n, (MapPoint*)nullptr);
+    F->mvbOutlier.assign(f.n, false);
+    F->mnId = Frame::nNextId++;
+    F->mpReferenceKF = nullptr;
+    F->mnScaleLevels = f.nlevels;
+    F->mfScaleFactor = f.nlevels > 1 ? f.scale_factors[1] : 1.2f;
+    F->mfLogScaleFactor = log(F->mfScaleFactor);
+    F->mvScaleFactors.assign(f.scale_factors, f.scale_factors + f.nlevels);
+    F->mvInvScaleFactors.resize(f.nlevels);
+    F->mvLevelSigma2.resize(f.nlevels);
+    F->mvInvLevelSigma2.resize(f.nlevels);
+    for (int i = 0; i < f.nlevels; i++) {  // as src/ORBextractor.cc:455-474
+        F->mvLevelSigma2[i] = f.scale_factors[i] * f.scale_factors[i];
+        F->mvInvScaleFactors[i] = 1.0f / f.scale_factors[i];
+        F->mvInvLevelSigma2[i] = 1.0f / F->mvLevelSigma2[i];
+    }
+    if (f.n_nodes > 0)
+        for (int a = 0; a < f.n_nodes; a++)
+            for (int k = f.node_start[a]; k < f.node_start[a + 1]; k++) F->mFeatVec.addFeature(f.node_id[a], f.node_feat[k]);
+    F->AssignFeaturesToGrid();
+    F->SetPose(eye4());
+    return F;
+}
+
+KeyFrame* build_kf(World& w, Frame* F)
+{
+    KeyFrame* kf = new KeyFrame(*F, &w.map, nullptr);
+    w.kfs.push_back(kf);
+    return kf;
+}
+
+void ensure_seed(World& w, const orbr_frame_in& like)
+{
+    if (w.seed) return;
+    static const float x0 = 1.f, y0 = 1.f;
+    static const int32_t o0 = 0;
+    static const uint8_t d0[32] = {0};
+    orbr_frame_in s = like;
+    s.n = 1; s.x = &x0; s.y = &y0; s.octave = &o0; s.angle = nullptr; s.u_right = nullptr; s.desc = d0; s.occupied = nullptr;
+    s.n_nodes = 0; s.has_mp = nullptr;
+    w.seed = build_kf(w, build_frame(w, s));
+}
+
+// A map point at camera coordinates of the identity pose such that it projects to (u, v) with inverse depth invz and is
+// predicted at pyramid level `level` (see the header comment).
+MapPoint* new_mp(World& w, float u, float v, float invz, int level, const uint8_t* desc, int nObs, bool bad, float scaleFactor)
+{
+    const float z = 1.0f / invz;
+    cv::Mat P(3, 1, CV_32F);
+    P.at<float>(0) = u * z; P.at<float>(1) = v * z; P.at<float>(2) = z;
+    MapPoint* mp = new MapPoint(P, w.seed, &w.map);
+    w.mps.push_back(mp);
+    const double dist = cv::norm(P);
+    cv::Mat nrm(3, 1, CV_32F);
+    for (int i = 0; i < 3; i++) nrm.at<float>(i) = (float)(P.at<float>(i) / dist);
+    mp->mNormalVector = nrm;
+    mp->mfMinDistance = 0.f;
+    mp->mfMaxDistance = (float)(dist * std::pow((double)scaleFactor, (double)level - 0.5));
+    mp->mDescriptor = cv::Mat(1, 32, CV_8U);
+    if (desc) std::memcpy(mp->mDescriptor.data, desc, 32); else std::memset(mp->mDescriptor.data, 0, 32);
+    mp->nObs = nObs;
+    mp->mbBad = bad;
+    return mp;
+}
+
+MapPoint* dummy_mp(World& w, int nObs)
+{
+    return new_mp(w, 0.f, 0.f, 1.f, 0, nullptr, nObs, false, 1.2f);
+}
+
+void occupy(World& w, Frame* F, const uint8_t* occupied, int nObs = 1)
+{
+    if (!occupied) return;
+    for (int i = 0; i < F->N; i++)
+        if (occupied[i]) F->mvpMapPoints[i] = dummy_mp(w, nObs);
+}
+
+inline float q_invz(const orbr_query_in& q, int i) { return q.invz ? q.invz[i] : 1.f; }
+inline bool q_valid(const orbr_query_in& q, int i) { return !q.valid || q.valid[i]; }
+inline bool q_blocks(const orbr_query_in& q, int i) { return !q.blocks || q.blocks[i]; }
+
+void kf_set_mappoints(World& w, KeyFrame* kf, const uint8_t* has_mp)
+{
+    // features without a good map point alternate between NULL and a bad one, so both skip paths run
+    for (int i = 0; i < kf->N; i++) {
+        if (!has_mp || has_mp[i]) kf->mvpMapPoints[i] = dummy_mp(w, 1);
+        else kf->mvpMapPoints[i] = (i & 1) ? new_mp(w, 0, 0, 1, 0, nullptr, 1, true, 1.2f) : nullptr;
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+// ---- Frame::AssignFeaturesToGrid / PosInGrid (src/Frame.cc:351-370, 558-567) ----
+void orbr_assign_grid(const orbr_frame_in* f, int32_t* cell_start /*64*48+1*/, int32_t* cell_items /*n*/)
+{
+    World w;
+    Frame* F = build_frame(w, *f);
+    int off = 0;
+    for (int ix = 0; ix < FRAME_GRID_COLS; ix++)
+        for (int iy = 0; iy < FRAME_GRID_ROWS; iy++) {
+            cell_start[ix * FRAME_GRID_ROWS + iy] = off;
+            for (size_t v : F->mGrid[ix][iy]) cell_items[off++] = (int32_t)v;
+        }
+    cell_start[FRAME_GRID_COLS * FRAME_GRID_ROWS] = off;
+}
+
+// ---- Frame::GetFeaturesInArea (src/Frame.cc:488-548) and KeyFrame::GetFeaturesInArea (src/KeyFrame.cc:623-658) ----
+int orbr_features_in_area(const orbr_frame_in* f, int use_keyframe, float x, float y, float r, int minLevel, int maxLevel,
+                          int32_t* out)
+{
+    World w;
+    Frame* F = build_frame(w, *f);
+    std::vector<size_t> v;
+    if (use_keyframe) v = build_kf(w, F)->GetFeaturesInArea(x, y, r);
+    else v = F->GetFeaturesInArea(x, y, r, minLevel, maxLevel);
+    for (size_t i = 0; i < v.size(); i++) out[i] = (int32_t)v[i];
+    return (int)v.size();
+}
+
+// ---- ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1983-2003) ----
+int orbr_descriptor_distance(const uint8_t* a, const uint8_t* b)
+{
+    cv::Mat A(1, 32, CV_8U, (void*)a), B(1, 32, CV_8U, (void*)b);
+    return ORBmatcher::DescriptorDistance(A, B);
+}
+
+// ---- ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th) (src/ORBmatcher.cc:61-173) ----
+// Same arguments as orbo_search_by_projection after the frame: map points carry the fields Frame::isInFrustum would have
+// written.  pvalid = 0 alternates between mbTrackInView = false and isBad().
+int orbr_search_by_projection(const orbr_frame_in* f, int nmp, const float* px, const float* py, const float* pxr,
+                              const int32_t* plevel, const float* pviewcos, const uint8_t* pvalid, const uint8_t* pobs,
+                              const uint8_t* pdesc, float th, float nnratio, int32_t* out_match)
+{
+    World w;
+    ensure_seed(w, *f);
+    Frame* F = build_frame(w, *f);
+    occupy(w, F, f->occupied);
+    std::vector<MapPoint*> v(nmp);
+    std::map<MapPoint*, int> index;
+    for (int m = 0; m < nmp; m++) {
+        const bool valid = pvalid[m] != 0;
+        MapPoint* mp = new_mp(w, px[m], py[m], 1.f, plevel[m], pdesc + 32 * (size_t)m, pobs[m] ? 1 : 0, !valid && (m & 1), F->mfScaleFactor);
+        mp->mbTrackInView = valid || (m & 1);
+        mp->mTrackProjX = px[m]; mp->mTrackProjY = py[m]; mp->mTrackProjXR = pxr[m];
+        mp->mnTrackScaleLevel = plevel[m];
+        mp->mTrackViewCos = pviewcos[m];
+        v[m] = mp;
+        index[mp] = m;
+    }
+    ORBmatcher matcher(nnratio, true);
+    const int n = matcher.SearchByProjection(*F, v, th);
+    for (int i = 0; i < F->N; i++) {
+        auto it = index.find(F->mvpMapPoints[i]);
+        out_match[i] = it == index.end() ? -1 : it->second;
+    }
+    return n;
+}
+
+// ---- ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&) (src/ORBmatcher.cc:228-392) ----
+int orbr_search_by_bow(const orbr_frame_in* kfIn, const orbr_frame_in* fIn, float nnratio, int checkOrientation,
+                       int32_t* out_match)
+{
+    World w;
+    ensure_seed(w, *kfIn);
+    KeyFrame* kf = build_kf(w, build_frame(w, *kfIn));
+    kf_set_mappoints(w, kf, kfIn->has_mp);
+    Frame* F = build_frame(w, *fIn);
+    std::map<MapPoint*, int> index;
+    for (int i = 0; i < kf->N; i++)
+        if (kf->mvpMapPoints[i]) index[kf->mvpMapPoints[i]] = i;
+    std::vector<MapPoint*> matches;
+    ORBmatcher matcher(nnratio, checkOrientation != 0);
+    const int n = matcher.SearchByBoW(kf, *F, matches);
+    for (int i = 0; i < F->N; i++) out_match[i] = matches[i] ? index[matches[i]] : -1;
+    return n;
+}
+
+// ---- ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vector<MapPoint*>&) (src/ORBmatcher.cc:696-850) ----
+int orbr_search_by_bow_kf(const orbr_frame_in* in1, const orbr_frame_in* in2, float nnratio, int checkOrientation, int32_t* out12)
+{
+    World w;
+    ensure_seed(w, *in1);
+    KeyFrame* kf1 = build_kf(w, build_frame(w, *in1));
+    KeyFrame* kf2 = build_kf(w, build_frame(w, *in2));
+    kf_set_mappoints(w, kf1, in1->has_mp);
+    kf_set_mappoints(w, kf2, in2->has_mp);
+    std::map<MapPoint*, int> index2;
+    for (int i = 0; i < kf2->N; i++)
+        if (kf2->mvpMapPoints[i]) index2[kf2->mvpMapPoints[i]] = i;
+    std::vector<MapPoint*> matches;
+    ORBmatcher matcher(nnratio, checkOrientation != 0);
+    const int n = matcher.SearchByBoW(kf1, kf2, matches);
+    for (int i = 0; i < kf1->N; i++) out12[i] = matches[i] ? index2[matches[i]] : -1;
+    return n;
+}
+
+// ---- ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:539-683) ----
+// F1 is given as a frame whose (x, y) are irrelevant to the search; prevx / prevy = vbPrevMatched.
+int orbr_search_for_initialization(const orbr_frame_in* in1, const float* prevx, const float* prevy, const orbr_frame_in* in2,
+                                   int windowSize, float nnratio, int checkOrientation, int32_t* out12, float* prev_out_xy)
+{
+    World w;
+    Frame* F1 = build_frame(w, *in1);
+    Frame* F2 = build_frame(w, *in2);
+    std::vector<cv::Point2f> prev(in1->n);
+    for (int i = 0; i < in1->n; i++) prev[i] = cv::Point2f(prevx[i], prevy[i]);
+    std::vector<int> m12;
+    ORBmatcher matcher(nnratio, checkOrientation != 0);
+    const int n = matcher.SearchForInitialization(*F1, *F2, prev, m12, windowSize);
+    for (int i = 0; i < in1->n; i++) {
+        out12[i] = m12[i];
+        if (prev_out_xy) { prev_out_xy[2 * i] = prev[i].x; prev_out_xy[2 * i + 1] = prev[i].y; }
+    }
+    return n;
+}
+
+// ---- ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:850-1056) + CheckDistEpipolarLine (:186-213) ----
+// KF2 sits at the identity, KF1's camera centre at (ex, ey, 1), so the epipole the reference computes is exactly (ex, ey).
+int orbr_search_for_triangulation(const orbr_frame_in* in1, const orbr_frame_in* in2, const float* F12, float ex, float ey,
+                                  int onlyStereo, int checkOrientation, float nnratio, int32_t* out12)
+{
+    World w;
+    ensure_seed(w, *in1);
+    Frame* F1 = build_frame(w, *in1);
+    cv::Mat T1 = eye4();
+    T1.at<float>(0, 3) = -ex; T1.at<float>(1, 3) = -ey; T1.at<float>(2, 3) = -1.f;
+    F1->SetPose(T1);
+    KeyFrame* kf1 = build_kf(w, F1);
+    KeyFrame* kf2 = build_kf(w, build_frame(w, *in2));
+    for (int i = 0; i < kf1->N; i++) kf1->mvpMapPoints[i] = (in1->has_mp && in1->has_mp[i]) ? dummy_mp(w, 1) : nullptr;
+    for (int i = 0; i < kf2->N; i++) kf2->mvpMapPoints[i] = (in2->has_mp && in2->has_mp[i]) ? dummy_mp(w, 1) : nullptr;
+    cv::Mat F(3, 3, CV_32F);
+    for (int i = 0; i < 9; i++) F.at<float>(i / 3, i % 3) = F12[i];
+    std::vector<std::pair<size_t, size_t>> pairs;
+    ORBmatcher matcher(nnratio, checkOrientation != 0);
+    const int n = matcher.SearchForTriangulation(kf1, kf2, F, pairs, onlyStereo != 0);
+    for (int i = 0; i < kf1->N; i++) out12[i] = -1;
+    for (auto& p : pairs) out12[p.first] = (int32_t)p.second;
+    return n;
+}
+
+// ---- ORBmatcher::SearchByProjection(Frame& Cur, const Frame& Last, th, bMono) (src/ORBmatcher.cc:1620-1789) ----
+// Query i = feature i of the last frame with its map point.  motion: 0 = neither (levels [oct-1, oct+1]), 1 = forward
+// (tlc.z > mb), 2 = backward.  out_match[idx] = query index held by Cur.mvpMapPoints[idx] after the call, else -1.
+int orbr_search_by_projection_last(const orbr_frame_in* cur, const orbr_query_in* q, float th, int motion, int bMono,
+                                   float nnratio, int checkOrientation, int32_t* out_match)
+{
+    World w;
+    ensure_seed(w, *cur);
+    Frame* C = build_frame(w, *cur);
+    occupy(w, C, cur->occupied);
+    // the last frame: one keypoint per query
+    std::vector<float> zx(q->n, 0.f);
+    orbr_frame_in lastIn = *cur;
+    lastIn.n = q->n; lastIn.x = zx.data(); lastIn.y = zx.data(); lastIn.octave = q->level; lastIn.angle = q->angle;
+    lastIn.u_right = nullptr; lastIn.desc = q->desc; lastIn.occupied = nullptr; lastIn.n_nodes = 0; lastIn.has_mp = nullptr;
+    Frame* Lf = build_frame(w, lastIn);
+    cv::Mat Tl = eye4();
+    Tl.at<float>(2, 3) = motion == 1 ? 2.f * C->mb + 1.f : motion == 2 ? -(2.f * C->mb + 1.f) : 0.f;
+    Lf->SetPose(Tl);
+    std::map<MapPoint*, int> index;
+    for (int i = 0; i < q->n; i++) {
+        if (!q_valid(*q, i)) {  // alternate: no map point / outlier flag
+            if (i & 1) { Lf->mvpMapPoints[i] = dummy_mp(w, 1); Lf->mvbOutlier[i] = true; }
+            continue;
+        }
+        MapPoint* mp = new_mp(w, q->x[i], q->y[i], q_invz(*q, i), q->level[i], q->desc + 32 * (size_t)i, q_blocks(*q, i) ? 1 : 0,
+                              false, C->mfScaleFactor);
+        Lf->mvpMapPoints[i] = mp;
+        index[mp] = i;
+    }
+    ORBmatcher matcher(nnratio, checkOrientation != 0);
+    const int n = matcher.SearchByProjection(*C, *Lf, th, bMono != 0);
+    for (int i = 0; i < C->N; i++) {
+        auto it = index.find(C->mvpMapPoints[i]);
+        out_match[i] = it == index.end() ? -1 : it->second;
+    }
+    return n;
+}
+
+// ---- ORBmatcher::SearchByProjection(Frame& Cur, KeyFrame*, const set<MapPoint*>& sAlreadyFound, th, ORBdist)
+//      (src/ORBmatcher.cc:1792-1924) ----
+// Query i = feature i of the key frame with its map point; valid = 0 rotates over NULL / bad / already found.
+int orbr_search_by_projection_kf(const orbr_frame_in* cur, const orbr_query_in* q, float th, int ORBdist, float nnratio,
+                                 int checkOrientation, int32_t* out_match)
+{
+    World w;
+    ensure_seed(w, *cur);
+    Frame* C = build_frame(w, *cur);
+    occupy(w, C, cur->occupied, 0);  // any non-NULL entry blocks here, observations or not
+    std::vector<float> zx(q->n, 0.f);
+    orbr_frame_in kfIn = *cur;
+    kfIn.n = q->n; kfIn.x = zx.data(); kfIn.y = zx.data(); kfIn.octave = q->level; kfIn.angle = q->angle;
+    kfIn.u_right = nullptr; kfIn.desc = q->desc; kfIn.occupied = nullptr; kfIn.n_nodes = 0; kfIn.has_mp = nullptr;
+    KeyFrame* kf = build_kf(w, build_frame(w, kfIn));
+    std::map<MapPoint*, int> index;
+    std::set<MapPoint*> found;
+    for (int i = 0; i < q->n; i++) {
+        const bool valid = q_valid(*q, i);
+        if (!valid && i % 3 == 0) continue;
+        MapPoint* mp = new_mp(w, q->x[i], q->y[i], q_invz(*q, i), q->level[i], q->desc + 32 * (size_t)i, 1, !valid && i % 3 == 1,
+                              C->mfScaleFactor);
+        if (!valid && i % 3 == 2) found.insert(mp);
+        kf->mvpMapPoints[i] = mp;
+        index[mp] = i;
+    }
+    ORBmatcher matcher(nnratio, checkOrientation != 0);
+    const int n = matcher.SearchByProjection(*C, kf, found, th, ORBdist);
+    for (int i = 0; i < C->N; i++) {
+        auto it = index.find(C->mvpMapPoints[i]);
+        out_match[i] = it == index.end() ? -1 : it->second;
+    }
+    return n;
+}
+
+// ---- ORBmatcher::SearchByProjection(KeyFrame*, cv::Mat Scw, vpPoints, vpMatched, th) (src/ORBmatcher.cc:398-520) ----
+// Scw = identity; occupied = vpMatched[idx] != NULL on entry.  out_match[idx] = query index written into vpMatched.
+int orbr_search_by_projection_scw(const orbr_frame_in* kfIn, const orbr_query_in* q, int th, int32_t* out_match)
+{
+    World w;
+    ensure_seed(w, *kfIn);
+    KeyFrame* kf = build_kf(w, build_frame(w, *kfIn));
+    std::vector<MapPoint*> matched(kf->N, (MapPoint*)nullptr);
+    if (kfIn->occupied)
+        for (int i = 0; i < kf->N; i++)
+            if (kfIn->occupied[i]) matched[i] = dummy_mp(w, 1);
+    std::vector<MapPoint*> pts(q->n);
+    std::map<MapPoint*, int> index;
+    for (int i = 0; i < q->n; i++) {
+        pts[i] = new_mp(w, q->x[i], q->y[i], q_invz(*q, i), q->level[i], q->desc + 32 * (size_t)i, 1, !q_valid(*q, i), kf->mfScaleFactor);
+        index[pts[i]] = i;
+    }
+    ORBmatcher matcher(0.75f, true);
+    const int n = matcher.SearchByProjection(kf, eye4(), pts, matched, th);
+    for (int i = 0; i < kf->N; i++) {
+        auto it = index.find(matched[i]);
+        out_match[i] = it == index.end() ? -1 : it->second;
+    }
+    return n;
+}
+
+// ---- ORBmatcher::Fuse(KeyFrame*, const vector<MapPoint*>&, th) (src/ORBmatcher.cc:1067-1222) ----
+// The key frame starts without map points.  best_idx[i] = the key-frame feature query i was fused into: either the point
+// was added there, or it was replaced by the point already sitting there (MapPoint::Replace), else -1.
+int orbr_fuse(const orbr_frame_in* kfIn, const orbr_query_in* q, float th, int32_t* best_idx)
+{
+    World w;
+    ensure_seed(w, *kfIn);
+    KeyFrame* kf = build_kf(w, build_frame(w, *kfIn));
+    std::vector<MapPoint*> pts(q->n);
+    for (int i = 0; i < q->n; i++) {
+        if (!q_valid(*q, i) && (i & 1)) { pts[i] = nullptr; continue; }
+        pts[i] = new_mp(w, q->x[i], q->y[i], q_invz(*q, i), q->level[i], q->desc + 32 * (size_t)i, 0, !q_valid(*q, i), kf->mfScaleFactor);
+    }
+    ORBmatcher matcher(0.6f, true);
+    const int n = matcher.Fuse(kf, pts, th);
+    for (int i = 0; i < q->n; i++) {
+        best_idx[i] = -1;
+        MapPoint* mp = pts[i];
+        if (!mp || !q_valid(*q, i)) continue;
+        int idx = mp->GetIndexInKeyFrame(kf);
+        if (idx < 0 && mp->GetReplaced()) idx = mp->GetReplaced()->GetIndexInKeyFrame(kf);
+        best_idx[i] = idx;
+    }
+    return n;
+}
+
+// ---- ORBmatcher::Fuse(KeyFrame*, cv::Mat Scw, vpPoints, th, vpReplacePoint) (src/ORBmatcher.cc:1225-1357) ----
+int orbr_fuse_scw(const orbr_frame_in* kfIn, const orbr_query_in* q, float th, int32_t* best_idx)
+{
+    World w;
+    ensure_seed(w, *kfIn);
+    KeyFrame* kf = build_kf(w, build_frame(w, *kfIn));
+    std::vector<MapPoint*> pts(q->n);
+    for (int i = 0; i < q->n; i++)
+        pts[i] = new_mp(w, q->x[i], q->y[i], q_invz(*q, i), q->level[i], q->desc + 32 * (size_t)i, 0, !q_valid(*q, i), kf->mfScaleFactor);
+    std::vector<MapPoint*> repl(q->n, (MapPoint*)nullptr);
+    ORBmatcher matcher(0.6f, true);
+    const int n = matcher.Fuse(kf, eye4(), pts, th, repl);
+    for (int i = 0; i < q->n; i++) {
+        best_idx[i] = -1;
+        if (!q_valid(*q, i)) continue;
+        int idx = pts[i]->GetIndexInKeyFrame(kf);
+        if (idx < 0 && repl[i]) idx = repl[i]->GetIndexInKeyFrame(kf);
+        best_idx[i] = idx;
+    }
+    return n;
+}
+
+// ---- ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1361-1602) with s12 = 1, R12 = I, t12 = 0 ----
+// q1in2: feature i of KF1 with its map point projected into KF2; q2in1: the reverse.  out12[i1] = idx2 or -1.
+int orbr_search_by_sim3(const orbr_frame_in* in1, const orbr_query_in* q2in1, const orbr_frame_in* in2, const orbr_query_in* q1in2,
+                        float th, int32_t* out12)
+{
+    World w;
+    ensure_seed(w, *in1);
+    KeyFrame* kf1 = build_kf(w, build_frame(w, *in1));
+    KeyFrame* kf2 = build_kf(w, build_frame(w, *in2));
+    std::map<MapPoint*, int> index2;
+    for (int i = 0; i < kf1->N; i++) {
+        const bool valid = q_valid(*q1in2, i);
+        if (!valid && (i & 1)) { kf1->mvpMapPoints[i] = nullptr; continue; }
+        kf1->mvpMapPoints[i] = new_mp(w, q1in2->x[i], q1in2->y[i], q_invz(*q1in2, i), q1in2->level[i], q1in2->desc + 32 * (size_t)i, 1,
+                                      !valid, kf1->mfScaleFactor);
+    }
+    for (int i = 0; i < kf2->N; i++) {
+        const bool valid = q_valid(*q2in1, i);
+        if (!valid && (i & 1)) { kf2->mvpMapPoints[i] = nullptr; continue; }
+        kf2->mvpMapPoints[i] = new_mp(w, q2in1->x[i], q2in1->y[i], q_invz(*q2in1, i), q2in1->level[i], q2in1->desc + 32 * (size_t)i, 1,
+                                      !valid, kf2->mfScaleFactor);
+        index2[kf2->mvpMapPoints[i]] = i;
+    }
+    std::vector<MapPoint*> m12(kf1->N, (MapPoint*)nullptr);
+    cv::Mat R12 = cv::Mat::eye(3, 3, CV_32F);
+    cv::Mat t12 = cv::Mat::zeros(3, 1, CV_32F);
+    ORBmatcher matcher(0.75f, true);
+    const int n = matcher.SearchBySim3(kf1, kf2, m12, 1.0f, R12, t12, th);
+    for (int i = 0; i < kf1->N; i++) out12[i] = m12[i] ? index2[m12[i]] : -1;
+    return n;
+}
+
+// ---- MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:295-360), batched ----
+// Observations live in a std::map keyed by KeyFrame POINTER, so the reference visits them in heap-address order; the
+// harness sorts its key frames by address and hands descriptor j of a set to the j-th of them, which makes "first minimum
+// wins" refer to the caller's order.  out_desc = the chosen descriptor per set (32 bytes; untouched for empty sets).
+void orbr_distinctive_descriptors(int n_sets, const int32_t* set_start, const uint8_t* desc, uint8_t* out_desc,
+                                  const orbr_frame_in* like)
+{
+    World w;
+    ensure_seed(w, *like);
+    int maxObs = 0;
+    for (int s = 0; s < n_sets; s++) maxObs = std::max(maxObs, set_start[s + 1] - set_start[s]);
+    // one key frame per observation slot, every one with n_sets features
+    std::vector<float> zx(n_sets, 1.f);
+    std::vector<int32_t> zo(n_sets, 0);
+    std::vector<KeyFrame*> slot;
+    std::vector<std::vector<uint8_t>> slotDesc(maxObs, std::vector<uint8_t>((size_t)n_sets * 32, 0));
+    for (int s = 0; s < n_sets; s++)
+        for (int j = 0; j < set_start[s + 1] - set_start[s]; j++)
+            std::memcpy(&slotDesc[j][(size_t)s * 32], desc + 32 * (size_t)(set_start[s] + j), 32);
+    std::vector<Frame*> fr;
+    for (int j = 0; j < maxObs; j++) {
+        orbr_frame_in in = *like;
+        in.n = n_sets; in.x = zx.data(); in.y = zx.data(); in.octave = zo.data(); in.angle = nullptr; in.u_right = nullptr;
+        in.desc = slotDesc[j].data(); in.occupied = nullptr; in.n_nodes = 0; in.has_mp = nullptr;
+        slot.push_back(build_kf(w, build_frame(w, in)));
+    }
+    // address order = observation order; descriptors must follow it
+    std::vector<KeyFrame*> sorted = slot;
+    std::sort(sorted.begin(), sorted.end());
+    for (int j = 0; j < maxObs; j++)
+        std::memcpy(const_cast<cv::Mat&>(sorted[j]->mDescriptors).data, slotDesc[j].data(), (size_t)n_sets * 32);
+    for (int s = 0; s < n_sets; s++) {
+        const int N = set_start[s + 1] - set_start[s];
+        if (N <= 0) continue;
+        MapPoint* mp = new_mp(w, 0, 0, 1, 0, nullptr, 0, false, 1.2f);
+        for (int j = 0; j < N; j++) mp->AddObservation(sorted[j], s);
+        mp->ComputeDistinctiveDescriptors();
+        cv::Mat d = mp->GetDescriptor();
+        std::memcpy(out_desc + 32 * (size_t)s, d.data, 32);
+    }
+}
+
+// ---- DBoW2 vocabulary: loadFromTextFile (TemplatedVocabulary.h:1338-1420) + transform (:1127-1259) ----
+void* orbr_vocab_load(const char* path)
+{
+    ORBVocabulary* v = new ORBVocabulary();
+    if (!v->loadFromTextFile(path)) { delete v; return nullptr; }
+    return v;
+}
+void orbr_vocab_free(void* p) { delete (ORBVocabulary*)p; }
+
+void orbr_bow_transform(void* voc, const uint8_t* desc, int n, int levelsup, int32_t* out_word, int32_t* out_node,
+                        double* out_weight)
+{
+    ORBVocabulary* v = (ORBVocabulary*)voc;
+    for (int i = 0; i < n; i++) {
+        cv::Mat d(1, 32, CV_8U, (void*)(desc + 32 * (size_t)i));
+        DBoW2::WordId wid = 0; DBoW2::WordValue wt = 0; DBoW2::NodeId nid = 0;
+        v->transform(d, wid, wt, &nid, levelsup);
+        out_word[i] = (int32_t)wid; out_node[i] = (int32_t)nid; out_weight[i] = wt;
+    }
+}
+
+// Frame::ComputeBoW (src/Frame.cc:572-581): the folded BowVector (id ascending, value) and FeatureVector (CSR).
+// Returns the number of BowVector entries; fv_* may be NULL to query sizes (n_fv_nodes written).
+int orbr_compute_bow(void* voc, const uint8_t* desc, int n, int32_t* bow_id, double* bow_val, int* n_fv_nodes,
+                     int32_t* fv_node_id, int32_t* fv_node_start, int32_t* fv_node_feat)
+{
+    World w;
+    Frame* F = new Frame();
+    w.frames.push_back(F);
+    F->mpORBvocabulary = (ORBVocabulary*)voc;
+    F->mDescriptors = cv::Mat(n, 32, CV_8U);
+    if (n) std::memcpy(F->mDescriptors.data, desc, (size_t)n * 32);
+    F->ComputeBoW();
+    int k = 0;
+    for (auto& e : F->mBowVec) {
+        if (bow_id) { bow_id[k] = (int32_t)e.first; bow_val[k] = e.second; }
+        k++;
+    }
+    if (n_fv_nodes) *n_fv_nodes = (int)F->mFeatVec.size();
+    if (fv_node_id) {
+        int a = 0, off = 0;
+        for (auto& e : F->mFeatVec) {
+            fv_node_id[a] = (int32_t)e.first;
+            fv_node_start[a] = off;
+            for (unsigned f : e.second) fv_node_feat[off++] = (int32_t)f;
+            a++;
+        }
+        fv_node_start[a] = off;
+    }
+    return k;
+}
+
+// ---- the whole stereo Frame constructor (src/Frame.cc:91-150): extraction L/R on two threads, UndistortKeyPoints,
+//      ComputeStereoMatches (:673-885), AssignFeaturesToGrid ----
+// `mb` is read by ComputeStereoMatches BEFORE the constructor assigns it (src/Frame.cc:715 vs :174, SURVEY decision D5);
+// the harness constructs the Frame in storage whose `mb` bytes already hold the intended value mbf / fx, which the
+// constructor leaves alone until the late assignment of the same value.
+struct StereoOut { Frame* F; ORBextractor *exL, *exR; };
+
+void* orbr_stereo_frame(const uint8_t* left, const uint8_t* right, int rows, int cols, int nfeatures, float scaleFactor,
+                        int nlevels, int iniTh, int minTh, float fx, float fy, float cx, float cy, const float* dist4,
+                        float mbf)
+{
+    StereoOut* o = new StereoOut;
+    o->exL = new ORBextractor(nfeatures, scaleFactor, nlevels, iniTh, minTh);
+    o->exR = new ORBextractor(nfeatures, scaleFactor, nlevels, iniTh, minTh);
+    cv::Mat K = cv::Mat::eye(3, 3, CV_32F);
+    K.at<float>(0, 0) = fx; K.at<float>(1, 1) = fy; K.at<float>(0, 2) = cx; K.at<float>(1, 2) = cy;
+    cv::Mat D(4, 1, CV_32F);
+    for (int i = 0; i < 4; i++) D.at<float>(i) = dist4 ? dist4[i] : 0.f;
+    cv::Mat imL(rows, cols, CV_8UC1, (void*)left, (size_t)cols), imR(rows, cols, CV_8UC1, (void*)right, (size_t)cols);
+    Frame::mbInitialComputations = true;
+    void* mem = ::operator new(sizeof(Frame));
+    std::memset(mem, 0, sizeof(Frame));
+    const float mb = mbf / fx;
+    std::memcpy((char*)mem + offsetof(Frame, mb), &mb, sizeof(float));
+    o->F = new (mem) Frame(imL, imR, 0.0, o->exL, o->exR, nullptr, K, D, mbf, 40.f * mb);
+    return o;
+}
+int orbr_stereo_n(void* p, int right) { StereoOut* o = (StereoOut*)p; return right ? (int)o->F->mvKeysRight.size() : o->F->N; }
+void orbr_stereo_get(void* p, float* uRight, float* depth, float* keys_xy, float* keysun_xy, int32_t* cell_start, int32_t* cell_items,
+                     float* bounds4)
+{
+    Frame* F = ((StereoOut*)p)->F;
+    for (int i = 0; i < F->N; i++) {
+        if (uRight) uRight[i] = F->mvuRight[i];
+        if (depth) depth[i] = F->mvDepth[i];
+        if (keys_xy) { keys_xy[2 * i] = F->mvKeys[i].pt.x; keys_xy[2 * i + 1] = F->mvKeys[i].pt.y; }
+        if (keysun_xy) { keysun_xy[2 * i] = F->mvKeysUn[i].pt.x; keysun_xy[2 * i + 1] = F->mvKeysUn[i].pt.y; }
+    }
+    if (cell_start) {
+        int off = 0;
+        for (int ix = 0; ix < FRAME_GRID_COLS; ix++)
+            for (int iy = 0; iy < FRAME_GRID_ROWS; iy++) {
+                cell_start[ix * FRAME_GRID_ROWS + iy] = off;
+                for (size_t v : F->mGrid[ix][iy]) cell_items[off++] = (int32_t)v;
+            }
+        cell_start[FRAME_GRID_COLS * FRAME_GRID_ROWS] = off;
+    }
+    if (bounds4) {
+        bounds4[0] = Frame::mnMinX; bounds4[1] = Frame::mnMinY; bounds4[2] = Frame::mnMaxX; bounds4[3] = Frame::mnMaxY;
+    }
+}
+void orbr_stereo_free(void* p)
+{
+    StereoOut* o = (StereoOut*)p;
+    o->F->~Frame();
+    ::operator delete((void*)o->F);
+    delete o->exL; delete o->exR;
+    delete o;
+}
+
+// ---- the monocular Frame constructor (src/Frame.cc:213-265): extraction, UndistortKeyPoints (:586-628),
+//      ComputeImageBounds (:633-664), AssignFeaturesToGrid ----
+void* orbr_mono_frame(const uint8_t* img, int rows, int cols, int nfeatures, float scaleFactor, int nlevels, int iniTh,
+                      int minTh, float fx, float fy, float cx, float cy, const float* dist, int ndist, float mbf)
+{
+    StereoOut* o = new StereoOut;
+    o->exL = new ORBextractor(nfeatures, scaleFactor, nlevels, iniTh, minTh);
+    o->exR = nullptr;
+    cv::Mat K = cv::Mat::eye(3, 3, CV_32F);
+    K.at<float>(0, 0) = fx; K.at<float>(1, 1) = fy; K.at<float>(0, 2) = cx; K.at<float>(1, 2) = cy;
+    cv::Mat D(ndist > 0 ? ndist : 4, 1, CV_32F);
+    for (int i = 0; i < D.rows; i++) D.at<float>(i) = (dist && i < ndist) ? dist[i] : 0.f;
+    cv::Mat im(rows, cols, CV_8UC1, (void*)img, (size_t)cols);
+    Frame::mbInitialComputations = true;
+    void* mem = ::operator new(sizeof(Frame));
+    std::memset(mem, 0, sizeof(Frame));
+    o->F = new (mem) Frame(im, 0.0, o->exL, nullptr, K, D, mbf, 40.f);
+    return o;
+}
+
+}  // extern "C"

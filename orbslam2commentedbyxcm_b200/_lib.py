@@ -106,6 +106,7 @@ SIGNATURES = {
     "orbm_search_for_triangulation": (_i, [_vp, C.POINTER(KFView), C.POINTER(KFView), _vp, _f, _f, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "orbm_stereo_rows": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _f, _f, _vp, _vp]),
     "orbm_stereo_match": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp]),
+    "orbm_set_stereo_outlier_mode": (_i, [_vp, _i]),
     "orbm_search_by_bow_kf": (_i, [_vp, _i, _vp, _vp, _vp, C.POINTER(FeatVecView), _i, _vp, _vp, _vp, C.POINTER(FeatVecView), _f, _i, _vp, _vp]),
     "orbm_vocab_create": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, C.POINTER(_vp)]),
     "orbm_vocab_destroy": (None, [_vp]),

@@ -702,35 +702,87 @@ __global__ void __launch_bounds__(256) k_stereo_refine(int nl, const float* __re
     if (lane == 0) { uRight[iL] = outU; depth[iL] = outD; sad[iL] = outS; }
 }
 
-// Outlier removal (src/Frame.cc:868-884, upstream placement): sort accepted (SAD, iL), median = element size/2,
-// reject every match with SAD >= 1.5f * 1.4f * median.  Rank by counting (n <= a few thousand).
-__global__ void __launch_bounds__(1024) k_stereo_outliers(int nl, const int32_t* __restrict__ sad, float* uRight, float* depth)
+// Outlier removal (src/Frame.cc:868-884).  In THIS reference the sort / median / reject block sits INSIDE the
+// per-keypoint loop (upstream ORB-SLAM2 has it after the loop): after every accepted match the running list of (SAD, iL)
+// pairs is sorted, median = element size/2, and every match so far with SAD >= 1.5f * 1.4f * median is rejected for good.
+// A match inserted as the (i+1)-th is therefore rejected iff SAD_i >= min over t > i of thDist_t, where thDist_t comes from
+// the median of the first t accepted matches (the block is idempotent on iterations that add nothing, and a no-op while
+// the list is empty: its loop does not run, the out-of-range read of element 0 is never used).
+//   k_stereo_medians: every CTA compacts the accepted SADs (iL order) into shared memory; warp per prefix length t finds
+//                     the median VALUE by bisection on the value (counting entries <= v across the lanes, 17 steps).
+//   k_stereo_reject:  suffix minimum of thDist (one CTA), then the per-match test.  mode 1 = upstream placement: every
+//                     match is tested against thDist of the full list only.
+__global__ void __launch_bounds__(256) k_stereo_medians(int nl, const int32_t* __restrict__ sad, float* __restrict__ thDist,
+                                                        int32_t* __restrict__ entryIdx, int32_t* __restrict__ nEntries)
 {
-    __shared__ int sN, sMedian;
-    if (threadIdx.x == 0) { sN = 0; sMedian = -1; }
+    extern __shared__ int32_t sE[];  // compacted SADs, nl ints
+    __shared__ int sWarpCnt[8], sBase;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) sBase = 0;
     __syncthreads();
-    int mine = 0;
-    for (int i = threadIdx.x; i < nl; i += blockDim.x) mine += sad[i] >= 0;
-    if (mine) atomicAdd(&sN, mine);
-    __syncthreads();
-    const int n = sN;
-    if (n == 0) return;
-    const int target = n / 2;
-    for (int i = threadIdx.x; i < nl; i += blockDim.x) {
-        const int d = sad[i];
-        if (d < 0) continue;
-        int rank = 0;
-        for (int j = 0; j < nl; j++) {
-            const int e = sad[j];
-            rank += (e >= 0) && (e < d || (e == d && j < i));
+    for (int i0 = 0; i0 < nl; i0 += 256) {
+        const int i = i0 + threadIdx.x;
+        const int d = i < nl ? sad[i] : -1;
+        const unsigned bal = __ballot_sync(0xffffffffu, d >= 0);
+        if (lane == 0) sWarpCnt[warp] = __popc(bal);
+        __syncthreads();
+        int off = sBase;
+        for (int w = 0; w < warp; w++) off += sWarpCnt[w];
+        if (d >= 0) {
+            const int pos = off + __popc(bal & ((1u << lane) - 1u));
+            sE[pos] = d;
+            if (blockIdx.x == 0) entryIdx[pos] = i;
         }
-        if (rank == target) sMedian = d;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int tot = 0;
+            for (int w = 0; w < 8; w++) tot += sWarpCnt[w];
+            sBase += tot;
+        }
+        __syncthreads();
     }
+    const int n = sBase;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *nEntries = n;
+    const int t = blockIdx.x * 8 + warp + 1;  // prefix length
+    if (t > n) return;
+    const int target = t / 2 + 1;             // smallest v with #(e <= v) >= target is element t/2 of the sorted prefix
+    int lo = 0, hi = 1 << 17;                 // SAD <= 121 * 510 < 2^16
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        int c = 0;
+        for (int j = lane; j < t; j += 32) c += sE[j] <= mid;
+        c = __reduce_add_sync(0xffffffffu, c);
+        if (c >= target) hi = mid; else lo = mid + 1;
+    }
+    if (lane == 0) thDist[t - 1] = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)lo);
+}
+
+__global__ void __launch_bounds__(1024) k_stereo_reject(const int32_t* __restrict__ sad, const float* __restrict__ thDist,
+                                                        const int32_t* __restrict__ entryIdx, const int32_t* __restrict__ nEntries,
+                                                        int mode, float* uRight, float* depth)
+{
+    __shared__ float sMin[1024];
+    const int n = *nEntries;
+    if (n == 0) return;
+    const int per = (n + 1023) / 1024;
+    const int b = threadIdx.x * per, e = min(b + per, n);
+    float m = 3.0e38f;
+    for (int i = e - 1; i >= b; i--) m = fminf(m, thDist[i]);
+    sMin[threadIdx.x] = m;
     __syncthreads();
-    const float thDist = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)sMedian);
-    for (int i = threadIdx.x; i < nl; i += blockDim.x) {
-        const int d = sad[i];
-        if (d >= 0 && !((float)d < thDist)) { uRight[i] = -1.0f; depth[i] = -1.0f; }
+    for (int s = 1; s < 1024; s <<= 1) {   // inclusive suffix minimum over the chunk minima
+        const float o = threadIdx.x + s < 1024 ? sMin[threadIdx.x + s] : 3.0e38f;
+        __syncthreads();
+        sMin[threadIdx.x] = fminf(sMin[threadIdx.x], o);
+        __syncthreads();
+    }
+    float run = threadIdx.x + 1 < 1024 ? sMin[threadIdx.x + 1] : 3.0e38f;  // minimum over the later chunks
+    const float last = thDist[n - 1];
+    for (int i = e - 1; i >= b; i--) {
+        run = fminf(run, thDist[i]);       // min over t > i of thDist_t (thDist[i] belongs to prefix length i + 1)
+        const int iL = entryIdx[i];
+        const float th = mode == 1 ? last : run;
+        if (!((float)sad[iL] < th)) { uRight[iL] = -1.0f; depth[iL] = -1.0f; }
     }
 }
 
@@ -1250,6 +1302,7 @@ struct orbm_context {
     int world = 0, rank = 0, nqMax = 0;
     uint32_t epoch = 0;
     int* xchgTimeout = nullptr;  // mapped pinned host int, written by the kernel when a peer never answered
+    int stereoOutlierMode = 0;   // 0 = this reference (block inside the keypoint loop), 1 = upstream ORB-SLAM2 (after the loop)
 };
 
 namespace {
@@ -1816,6 +1869,16 @@ int orbm_search_by_bow(orbm_context* m, int nkf, const uint8_t* kf_desc, const f
     return ORBX_OK;
 }
 
+int orbm_set_stereo_outlier_mode(orbm_context* m, int mode)
+{
+    if (!m || (mode != 0 && mode != 1)) {
+        set_error("orbm_set_stereo_outlier_mode: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    m->stereoOutlierMode = mode;
+    return ORBX_OK;
+}
+
 int orbm_stereo_match(orbm_context* m, orbx_handle* ex_left, int frame_left, orbx_handle* ex_right, int frame_right, int nl,
                       const float* lx, const float* ly, const int32_t* loct, const uint8_t* ldesc, int nr, const float* rx,
                       const float* ry, const int32_t* roct, const uint8_t* rdesc, float mbf, float mb, float* u_right,
@@ -1853,7 +1916,11 @@ int orbm_stereo_match(orbm_context* m, orbx_handle* ex_left, int frame_left, orb
     const size_t oRx = c.take(4 * (size_t)nrA), oRy = c.take(4 * (size_t)nrA), oRo = c.take(4 * (size_t)nrA), oRd = c.take(32 * (size_t)nrA),
                  oSf = c.take(4 * (size_t)ORBX_MAX_LEVELS);
     const size_t oBr = c.take(4 * (size_t)nl), oBd = c.take(4 * (size_t)nl), oU = c.take(4 * (size_t)nl), oD = c.take(4 * (size_t)nl),
-                 oS = c.take(4 * (size_t)nl);
+                 oS = c.take(4 * (size_t)nl), oTh = c.take(4 * (size_t)nl), oEi = c.take(4 * (size_t)nl), oNe = c.take(16);
+    if (4 * (size_t)nl > 200 * 1024) {
+        set_error("orbm_stereo_match: more than 51200 left keypoints");
+        return ORBX_ERR_BAD_ARG;
+    }
     rc = ensure_arena(m, c.off);
     if (rc != ORBX_OK) return rc;
     char* A = m->arena;
@@ -1869,7 +1936,12 @@ int orbm_stereo_match(orbm_context* m, orbx_handle* ex_left, int frame_left, orb
     k_stereo_refine<<<(nl + 7) / 8, 256, 0, m->stream>>>(nl, (float*)(A + oLx), (float*)(A + oLy), (int32_t*)(A + oLo),
                                                         (float*)(A + oRx), (int32_t*)(A + oBr), pl, pr, mbf, minD, maxD,
                                                         (float*)(A + oU), (float*)(A + oD), (int32_t*)(A + oS));
-    k_stereo_outliers<<<1, 1024, 0, m->stream>>>(nl, (int32_t*)(A + oS), (float*)(A + oU), (float*)(A + oD));
+    if (4 * (size_t)nl > 48 * 1024)
+        ORBX_CUDA_TRY(cudaFuncSetAttribute(k_stereo_medians, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    k_stereo_medians<<<(nl + 7) / 8, 256, 4 * (size_t)nl, m->stream>>>(nl, (int32_t*)(A + oS), (float*)(A + oTh), (int32_t*)(A + oEi),
+                                                                      (int32_t*)(A + oNe));
+    k_stereo_reject<<<1, 1024, 0, m->stream>>>((int32_t*)(A + oS), (float*)(A + oTh), (int32_t*)(A + oEi), (int32_t*)(A + oNe),
+                                              m->stereoOutlierMode, (float*)(A + oU), (float*)(A + oD));
     ORBX_CUDA_TRY(cudaGetLastError());
     ORBX_CUDA_TRY(cudaMemcpyAsync(u_right, A + oU, 4 * (size_t)nl, cudaMemcpyDeviceToHost, m->stream));
     ORBX_CUDA_TRY(cudaMemcpyAsync(depth, A + oD, 4 * (size_t)nl, cudaMemcpyDeviceToHost, m->stream));

@@ -262,10 +262,12 @@ class ORBmatcher:
         return best_r[:nl], best_d[:nl]
 
     # ---- Frame::ComputeStereoMatches, complete (coarse search + SAD refinement + outlier removal) ----
-    def ComputeStereoMatches(self, ex_left, ex_right, left, right, mbf, mb, frame_left=0, frame_right=0):
+    def ComputeStereoMatches(self, ex_left, ex_right, left, right, mbf, mb, frame_left=0, frame_right=0, upstream_outliers=False):
         """ex_left / ex_right: ORBextractor objects that have just extracted the left / right image (their device
-        pyramids are read in place).  Returns (mvuRight, mvDepth)."""
+        pyramids are read in place).  Returns (mvuRight, mvDepth).  upstream_outliers=True runs the SAD outlier block once
+        after the loop (upstream ORB-SLAM2) instead of inside it (this reference, src/Frame.cc:868-884)."""
         keep = []
+        check(self._L.orbm_set_stereo_outlier_mode(self._m, 1 if upstream_outliers else 0), "orbm_set_stereo_outlier_mode")
 
         def arr(v, dt):
             a = np.ascontiguousarray(v, dt)
