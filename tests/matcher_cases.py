@@ -331,3 +331,85 @@ UNDISTORT_CAMS = [
     ("euroc", 1, dict(fx=458.654, fy=457.296, cx=367.215, cy=248.375), [-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05]),
     ("kitti", 2, dict(fx=718.856, fy=718.856, cx=607.19, cy=185.2), [0.0, 0.0, 0.0, 0.0]),
 ]
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# one pass over every case: the same keys from the compiled reference (tools/make_golden.py -> tests/golden/
+# matcher_ref.npz, tests/test_oracle_matcher.py::test_golden_is_current) and from the CUDA path (tests/test_gpu_matcher_ref.py)
+# ------------------------------------------------------------------------------------------------------------------
+def _norm(out):
+    return np.where(out == -2, -1, out).astype(np.int32)
+
+
+def reference_outputs(oracle_mod, R):
+    """name -> int32/float32 array, produced by oracle/_ref/libmatchref.so (the reference's own code)."""
+    out = {}
+    for c in SBP_CASES:
+        frame, mps = sbp_case(oracle_mod, *c)
+        n, m = R.search_by_projection(frame, mps, c[3], 0.8)
+        out["sbp_%s_%d" % (c[0], c[1])] = np.concatenate([[n], m]).astype(np.int32)
+    frame, mps = sbp_chain_case(oracle_mod)
+    n, m = R.search_by_projection(frame, mps, 15.0, 0.8)
+    out["sbp_chain"] = np.concatenate([[n], m]).astype(np.int32)
+    for seed, ori in BOW_CASES:
+        kf, fr = bow_case(oracle_mod, seed)
+        n, m = R.search_by_bow(kf, fr, 0.7, ori)
+        out["bow_%d" % seed] = np.concatenate([[n], m]).astype(np.int32)
+        kf1, kf2 = bow_case(oracle_mod, seed, kfkf=True)
+        n, m = R.search_by_bow_kf(kf1, kf2, 0.8, ori)
+        out["bowkf_%d" % seed] = np.concatenate([[n], m]).astype(np.int32)
+    for shape_name, seed, ori, window in INIT_CASES:
+        f1, f2, prev = init_case(oracle_mod, shape_name, seed)
+        n, m, newprev = R.search_for_initialization(f1, f2, prev, window, 0.9, ori)
+        out["init_%s_%d" % (shape_name, seed)] = np.concatenate([[n], m]).astype(np.int32)
+        out["init_prev_%s_%d" % (shape_name, seed)] = newprev.astype(np.float32)
+    for seed, ori, only_stereo, stereo_p in TRIANG_CASES:
+        kf1, kf2, F12, ex, ey, sf, sigma2 = triang_case(oracle_mod, seed, stereo_p)
+        n, m = R.search_for_triangulation(kf1, kf2, F12, ex, ey, only_stereo, ori)
+        out["triang_%d" % seed] = np.concatenate([[n], m]).astype(np.int32)
+    for shape_name, seed, mode, ori, max_dist in WINDOW_CASES:
+        frame, q = window_case(oracle_mod, shape_name, seed, mode)
+        if mode == "kf":
+            n, m = R.search_by_projection_kf(frame, q, q["th"], max_dist, 0.9, ori)
+        else:
+            n, m = R.search_by_projection_last(frame, q, q["th"], {"band": 0, "forward": 1, "backward": 2}[mode], False, 0.9, ori, mbf=MBF)
+        out["window_%s_%d_%s" % (shape_name, seed, mode)] = np.concatenate([[n], m]).astype(np.int32)
+    for shape_name, seed in SCW_CASES:
+        frame, q = scw_case(oracle_mod, shape_name, seed)
+        n, m = R.search_by_projection_scw(frame, q, int(q["th"]))
+        out["scw_%s_%d" % (shape_name, seed)] = np.concatenate([[n], m]).astype(np.int32)
+    for shape_name, seed, gate, stereo in FUSE_CASES:
+        frame, q, inv_sigma2 = fuse_case(oracle_mod, shape_name, seed, stereo)
+        n, bi = R.fuse(frame, q, q["th"], mbf=MBF, scw=(gate == 0))
+        out["fuse_%s_%d" % (shape_name, seed)] = np.concatenate([[n], bi]).astype(np.int32)
+    for shape_name, seed in SIM3_CASES:
+        kf1, q21, kf2, q12 = sim3_case(oracle_mod, shape_name, seed)
+        n, m = R.search_by_sim3(kf1, q21, kf2, q12, 7.5)
+        out["sim3_%s_%d" % (shape_name, seed)] = np.concatenate([[n], m]).astype(np.int32)
+    start, desc = distinctive_case()
+    out["distinctive"] = R.distinctive_descriptors(start, desc)
+    for k, L, levelsup in VOCAB_CASES:
+        vocab, desc = vocab_case(k, L)
+        voc = R.Vocabulary(vocab)
+        w, nd, wt = voc.transform_features(desc, levelsup)
+        out["vocab_%d_%d_word" % (k, L)] = w.astype(np.int32)
+        out["vocab_%d_%d_node" % (k, L)] = nd.astype(np.int32)
+        out["vocab_%d_%d_weight" % (k, L)] = wt.astype(np.float64)
+        voc.close()
+    cfg = synth.PRESETS["euroc"]
+    cam = STEREO_CAM
+    for seed in STEREO_SEEDS:
+        left, right = stereo_case(seed)
+        ref = R.stereo_frame(left, right, cfg, cam["fx"], cam["fy"], cam["cx"], cam["cy"], cam["bf"])
+        out["stereo_%d_uright" % seed] = ref.u_right.astype(np.float32)
+        out["stereo_%d_depth" % seed] = ref.depth.astype(np.float32)
+        out["stereo_%d_cell_start" % seed] = ref.cell_start
+        out["stereo_%d_cell_items" % seed] = ref.cell_items.astype(np.int32)
+    for shape_name, seed, camd, dist in UNDISTORT_CAMS:
+        img = synth.gen_frame(synth.SHAPES[shape_name], seed)
+        ref = R.mono_frame(img, synth.PRESETS[shape_name], camd["fx"], camd["fy"], camd["cx"], camd["cy"], dist)
+        out["mono_%s_keys_un" % shape_name] = ref.keys_un.astype(np.float32)
+        out["mono_%s_bounds" % shape_name] = ref.bounds
+        out["mono_%s_cell_start" % shape_name] = ref.cell_start
+        out["mono_%s_cell_items" % shape_name] = ref.cell_items.astype(np.int32)
+    return out

@@ -1,0 +1,194 @@
+"""GPU parity of the whole matcher side against the REFERENCE'S OWN code: the CUDA path (through the C-ABI) must return
+what src/ORBmatcher.cc / src/Frame.cc / src/MapPoint.cc / DBoW2, compiled unmodified (oracle/_ref/libmatchref.so), returned
+for the same seeded inputs.  The reference's outputs are frozen in tests/golden/matcher_ref.npz (tools/make_golden.py
+matcher; tests/test_oracle_matcher.py::test_golden_is_current keeps the file honest wherever the library exists); the
+inputs are regenerated from seeds by tests/matcher_cases.py.  Bit-exact: match indices, counts, float bits of mvuRight /
+mvDepth / undistorted keypoints, grid CSR, vocabulary words / nodes / weights."""
+import os
+
+import numpy as np
+import pytest
+
+import matcher_cases as mc
+from orbslam2commentedbyxcm_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def gpu():
+    import orbslam2commentedbyxcm_b200 as pkg
+    return pkg
+
+
+@pytest.fixture(scope="module")
+def gold(golden_dir):
+    return np.load(os.path.join(golden_dir, "matcher_ref.npz"))
+
+
+def _packed(n, m):
+    return np.concatenate([[n], mc._norm(np.asarray(m))]).astype(np.int32)
+
+
+@pytest.mark.parametrize("c", mc.SBP_CASES, ids=lambda c: "%s-%d" % (c[0], c[1]))
+def test_search_by_projection(gpu, oracle_mod, gold, c):
+    frame, mps = mc.sbp_case(oracle_mod, *c)
+    m = gpu.ORBmatcher(0.8, True)
+    n, out = m.SearchByProjection(frame, mps, c[3])
+    assert np.array_equal(_packed(n, out), gold["sbp_%s_%d" % (c[0], c[1])])
+    m.close()
+
+
+def test_search_by_projection_claim_chain(gpu, oracle_mod, gold):
+    frame, mps = mc.sbp_chain_case(oracle_mod)
+    m = gpu.ORBmatcher(0.8, True)
+    n, out = m.SearchByProjection(frame, mps, 15.0)
+    assert np.array_equal(_packed(n, out), gold["sbp_chain"])
+    m.close()
+
+
+@pytest.mark.parametrize("seed,ori", mc.BOW_CASES)
+def test_search_by_bow(gpu, oracle_mod, gold, seed, ori):
+    kf, fr = mc.bow_case(oracle_mod, seed)
+    m = gpu.ORBmatcher(0.7, ori)
+    n, out = m.SearchByBoW(kf, fr)
+    assert np.array_equal(_packed(n, out), gold["bow_%d" % seed])
+    m.close()
+    kf1, kf2 = mc.bow_case(oracle_mod, seed, kfkf=True)
+    m = gpu.ORBmatcher(0.8, ori)
+    n, out = m.SearchByBoWKF(kf1, kf2)
+    assert np.array_equal(_packed(n, out), gold["bowkf_%d" % seed])
+    m.close()
+
+
+@pytest.mark.parametrize("shape_name,seed,ori,window", mc.INIT_CASES)
+def test_search_for_initialization(gpu, oracle_mod, gold, shape_name, seed, ori, window):
+    f1, f2, prev = mc.init_case(oracle_mod, shape_name, seed)
+    m = gpu.ORBmatcher(0.9, ori)
+    n, out, new_prev = m.SearchForInitialization(f1, f2, prev, window)
+    assert np.array_equal(_packed(n, out), gold["init_%s_%d" % (shape_name, seed)])
+    assert np.array_equal(np.asarray(new_prev, np.float32).view(np.uint32), gold["init_prev_%s_%d" % (shape_name, seed)].view(np.uint32))
+    m.close()
+
+
+@pytest.mark.parametrize("seed,ori,only_stereo,stereo_p", mc.TRIANG_CASES)
+def test_search_for_triangulation(gpu, oracle_mod, gold, seed, ori, only_stereo, stereo_p):
+    kf1, kf2, F12, ex, ey, sf, sigma2 = mc.triang_case(oracle_mod, seed, stereo_p)
+    m = gpu.ORBmatcher(0.6, ori)
+    n, out = m.SearchForTriangulation(kf1, kf2, F12, ex, ey, sf, sigma2, only_stereo)
+    assert np.array_equal(_packed(n, out), gold["triang_%d" % seed])
+    m.close()
+
+
+@pytest.mark.parametrize("shape_name,seed,mode,ori,max_dist", mc.WINDOW_CASES)
+def test_search_by_projection_last_frame_and_keyframe(gpu, oracle_mod, gold, shape_name, seed, mode, ori, max_dist):
+    frame, q = mc.window_case(oracle_mod, shape_name, seed, mode)
+    m = gpu.ORBmatcher(0.9, ori)
+    n, out = m.SearchWindow(frame, q, max_dist, 0)
+    assert np.array_equal(_packed(n, out), gold["window_%s_%d_%s" % (shape_name, seed, mode)])
+    m.close()
+
+
+@pytest.mark.parametrize("shape_name,seed", mc.SCW_CASES)
+def test_search_by_projection_kf_scw(gpu, oracle_mod, gold, shape_name, seed):
+    frame, q = mc.scw_case(oracle_mod, shape_name, seed)
+    m = gpu.ORBmatcher(0.75, False)
+    n, out = m.SearchWindow(frame, q, 50, 0)
+    assert np.array_equal(_packed(n, out), gold["scw_%s_%d" % (shape_name, seed)])
+    m.close()
+
+
+@pytest.mark.parametrize("shape_name,seed,gate,stereo", mc.FUSE_CASES)
+def test_fuse(gpu, oracle_mod, gold, shape_name, seed, gate, stereo):
+    frame, q, inv_sigma2 = mc.fuse_case(oracle_mod, shape_name, seed, stereo)
+    m = gpu.ORBmatcher()
+    bi, bd = m.FuseSearch(frame, q, gate=gate, inv_level_sigma2=inv_sigma2)
+    assert np.array_equal(_packed(int((bi >= 0).sum()), bi), gold["fuse_%s_%d" % (shape_name, seed)])
+    m.close()
+
+
+@pytest.mark.parametrize("shape_name,seed", mc.SIM3_CASES)
+def test_search_by_sim3(gpu, oracle_mod, gold, shape_name, seed):
+    kf1, q21, kf2, q12 = mc.sim3_case(oracle_mod, shape_name, seed)
+    m = gpu.ORBmatcher()
+    n, out = m.SearchBySim3(kf1, q21, kf2, q12)
+    assert np.array_equal(_packed(n, out), gold["sim3_%s_%d" % (shape_name, seed)])
+    m.close()
+
+
+def test_distinctive_descriptors(gpu, gold):
+    start, desc = mc.distinctive_case()
+    m = gpu.ORBmatcher()
+    idx = m.ComputeDistinctiveDescriptors(start, desc)
+    ref = gold["distinctive"]
+    for s in range(len(start) - 1):
+        if start[s + 1] > start[s]:
+            assert np.array_equal(desc[start[s] + idx[s]], ref[s]), s
+    m.close()
+
+
+@pytest.mark.parametrize("k,L,levelsup", mc.VOCAB_CASES)
+def test_vocabulary_transform(gpu, gold, k, L, levelsup):
+    from orbslam2commentedbyxcm_b200 import vocabulary
+
+    vocab, desc = mc.vocab_case(k, L)
+    m = gpu.ORBmatcher()
+    voc = vocabulary.ORBVocabulary(vocab, m)
+    w, nd, wt = voc.transform_features(desc, levelsup)
+    assert np.array_equal(w, gold["vocab_%d_%d_word" % (k, L)]) and np.array_equal(nd, gold["vocab_%d_%d_node" % (k, L)])
+    assert np.array_equal(wt.view(np.uint64), gold["vocab_%d_%d_weight" % (k, L)].view(np.uint64))
+    voc.close(); m.close()
+
+
+@pytest.mark.parametrize("seed", mc.STEREO_SEEDS)
+def test_stereo_frame(gpu, gold, seed):
+    """extraction L/R + ComputeStereoMatches (in-loop outlier block of this reference) + grid, end to end on the GPU,
+    against the reference's stereo Frame constructor."""
+    left, right = mc.stereo_case(seed)
+    cam, cfg = mc.STEREO_CAM, synth.PRESETS["euroc"]
+    gL, gR = gpu.ORBextractor(*cfg), gpu.ORBextractor(*cfg)
+    kl, dl = gL(left)
+    kr, dr = gR(right)
+    Lv = dict(x=kl["x"].copy(), y=kl["y"].copy(), octave=kl["octave"].astype(np.int32), desc=dl)
+    Rv = dict(x=kr["x"].copy(), y=kr["y"].copy(), octave=kr["octave"].astype(np.int32), desc=dr)
+    mb = float(np.float32(cam["bf"]) / np.float32(cam["fx"]))
+    m = gpu.ORBmatcher()
+    ur, dp = m.ComputeStereoMatches(gL, gR, Lv, Rv, cam["bf"], mb)
+    assert np.array_equal(ur.view(np.uint32), gold["stereo_%d_uright" % seed].view(np.uint32))
+    assert np.array_equal(dp.view(np.uint32), gold["stereo_%d_depth" % seed].view(np.uint32))
+    # upstream placement of the outlier block keeps a superset of the matches, with identical values
+    ur2, dp2 = m.ComputeStereoMatches(gL, gR, Lv, Rv, cam["bf"], mb, upstream_outliers=True)
+    keep = ur >= 0
+    assert np.array_equal(ur2[keep], ur[keep]) and (ur2 >= 0).sum() > keep.sum()
+    rows, cols = synth.SHAPES["euroc"]
+    w_inv = float(np.float32(64.0) / np.float32(cols))
+    h_inv = float(np.float32(48.0) / np.float32(rows))
+    cs, ci = m.AssignFeaturesToGrid(kl["x"], kl["y"], 0.0, 0.0, w_inv, h_inv)
+    assert np.array_equal(cs, gold["stereo_%d_cell_start" % seed]) and np.array_equal(ci, gold["stereo_%d_cell_items" % seed])
+    m.close(); gL.close(); gR.close()
+
+
+@pytest.mark.parametrize("shape_name,seed,cam,dist", mc.UNDISTORT_CAMS, ids=lambda v: v if isinstance(v, str) else None)
+def test_mono_frame(gpu, gold, shape_name, seed, cam, dist):
+    """extraction + UndistortKeyPoints + ComputeImageBounds + AssignFeaturesToGrid against the reference's monocular
+    Frame constructor."""
+    img = synth.gen_frame(synth.SHAPES[shape_name], seed)
+    ex = gpu.ORBextractor(*synth.PRESETS[shape_name])
+    kps, desc = ex(img)
+    m = gpu.ORBmatcher()
+    ux, uy = m.UndistortKeyPoints(kps["x"], kps["y"], cam["fx"], cam["fy"], cam["cx"], cam["cy"], dist)
+    ref = gold["mono_%s_keys_un" % shape_name]
+    assert np.array_equal(ux.view(np.uint32), ref[:, 0].view(np.uint32)) and np.array_equal(uy.view(np.uint32), ref[:, 1].view(np.uint32))
+    rows, cols = synth.SHAPES[shape_name]
+    if dist[0] != 0.0:
+        cx_, cy_ = m.UndistortKeyPoints(np.array([0, cols, 0, cols], np.float32), np.array([0, 0, rows, rows], np.float32),
+                                        cam["fx"], cam["fy"], cam["cx"], cam["cy"], dist)
+        bounds = np.array([min(cx_[0], cx_[2]), min(cy_[0], cy_[1]), max(cx_[1], cx_[3]), max(cy_[2], cy_[3])], np.float32)
+    else:
+        bounds = np.array([0, 0, cols, rows], np.float32)
+    assert np.array_equal(bounds, gold["mono_%s_bounds" % shape_name])
+    w_inv = np.float32(64.0) / (bounds[2] - bounds[0])
+    h_inv = np.float32(48.0) / (bounds[3] - bounds[1])
+    cs, ci = m.AssignFeaturesToGrid(ux, uy, float(bounds[0]), float(bounds[1]), float(w_inv), float(h_inv))
+    assert np.array_equal(cs, gold["mono_%s_cell_start" % shape_name]) and np.array_equal(ci, gold["mono_%s_cell_items" % shape_name])
+    m.close(); ex.close()

@@ -251,3 +251,16 @@ def test_mono_frame_constructor_undistort_bounds_grid(oracle_mod, shape_name, se
     h_inv = np.float32(48.0) / (bounds[3] - bounds[1])
     cs, ci = oracle_mod.assign_grid(ux, uy, float(bounds[0]), float(bounds[1]), float(w_inv), float(h_inv))
     assert np.array_equal(cs, ref.cell_start) and np.array_equal(ci, ref.cell_items)
+
+
+def test_golden_is_current(oracle_mod, golden_dir):
+    """tests/golden/matcher_ref.npz (consumed by the -m gpu tests) equals what the compiled reference returns now."""
+    import os
+
+    gold = np.load(os.path.join(golden_dir, "matcher_ref.npz"))
+    live = mc.reference_outputs(oracle_mod, R)
+    assert sorted(gold.files) == sorted(live)
+    for k, v in live.items():
+        g = gold[k]
+        assert g.dtype == v.dtype and g.shape == v.shape, k
+        assert g.tobytes() == v.tobytes(), k

@@ -112,9 +112,27 @@ def undistort():
     np.savez_compressed(os.path.join(G, "undistort_cv2.npz"), **out)
 
 
+def matcher():
+    """tests/golden/matcher_ref.npz: what the REFERENCE'S OWN matcher-side code (oracle/_ref/libmatchref.so: ORBmatcher.cc,
+    Frame.cc, KeyFrame.cc, MapPoint.cc, DBoW2 compiled unmodified) returns on every case of tests/matcher_cases.py.  The
+    GPU tests compare the CUDA path with these arrays (tests/test_gpu_matcher_ref.py); the inputs are regenerated from
+    seeds on both sides."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import matcher_cases as mc
+    from oracle import matchref as R
+
+    out = mc.reference_outputs(oracle, R)
+    np.savez_compressed(os.path.join(G, "matcher_ref.npz"), **out)
+    print("matcher_ref.npz: %d arrays" % len(out))
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "matcher":
+        matcher()
+        sys.exit(0)
     prim()
     undistort()
     sincos()
+    matcher()
     extract()
     print(sorted(os.listdir(G)))
