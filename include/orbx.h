@@ -174,6 +174,18 @@ int orbm_bruteforce(orbm_context* m, const uint8_t* q, int nq, const uint8_t* db
 int orbm_merge_partials(orbm_context* m, const int32_t* best, const int32_t* best_idx, const int32_t* second,
                         int nparts, int nq, int32_t* out_best, int32_t* out_idx, int32_t* out_second);
 
+/* ---- Brute force on the tensor cores (sm_100a: tcgen05.mma kind::i8, TMEM accumulators, TMA operand tiles).  The same
+ * result as orbm_bruteforce, bit for bit: with descriptors expanded to +-1 bytes the dot product is 256 - 2 x Hamming
+ * distance (src/ORBmatcher.cc:1983-2003), an exact integer, so query tile x database tile distances are an int8 GEMM and
+ * the best / second selection runs as its epilogue.  orbm_db_create expands a database (mem_kind 0 = host pointer, 1 =
+ * device pointer; 256 bytes per row of device memory) once; searches against it are orbm_bruteforce_db (mem_kind as in
+ * orbm_bruteforce) and, for a shard of a distributed map, orbm_bruteforce_sharded_db (DEVICE pointers). */
+typedef struct orbm_db orbm_db;
+int orbm_db_create(orbm_context* m, const uint8_t* db, int ndb, int mem_kind, orbm_db** out);
+void orbm_db_destroy(orbm_db* db);
+int orbm_bruteforce_db(orbm_context* m, const orbm_db* db, const uint8_t* q, int nq, int idx_offset, int32_t* best,
+                       int32_t* best_idx, int32_t* second, int mem_kind);
+
 /* ---- Sharded brute-force search with a fused merge + exchange over peer memory (north_star: "local-map matching shards
  * ... by query set across 2, 4 and 8 GPUs"; replaces the all-gather + orbm_merge_partials pair).
  * One process (or context) per GPU.  Each rank creates an exchange buffer, publishes its CUDA IPC handle through any
@@ -199,6 +211,9 @@ int orbm_bruteforce_sharded(orbm_context* m, const uint8_t* q, int nq, const uin
  * latest published search and writes the merged result, phases = 3 is orbm_bruteforce_sharded. */
 int orbm_bruteforce_sharded_phases(orbm_context* m, const uint8_t* q, int nq, const uint8_t* db_shard, int ndb_shard,
                                    int idx_offset, int32_t* best, int32_t* best_idx, int32_t* second, int phases);
+/* orbm_bruteforce_sharded with the shard prepared by orbm_db_create (tensor-core search of the shard, same exchange). */
+int orbm_bruteforce_sharded_db(orbm_context* m, const orbm_db* db_shard, const uint8_t* q, int nq, int idx_offset, int32_t* best,
+                               int32_t* best_idx, int32_t* second);
 /* 1 if a sharded search gave up waiting for a peer (the results of that call are invalid) */
 int orbm_exchange_timed_out(orbm_context* m);
 

@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "liborbx.so")
 SOURCES = ["orbx_extract.cu", "orbx_match.cu"]
-DEPS = SOURCES + ["orbx_common.cuh", "sincosf_dev.cuh", "orb_pattern.inc", os.path.join("..", "..", "include", "orbx.h")]
+DEPS = SOURCES + ["orbx_common.cuh", "orbx_match_tc.cuh", "sincosf_dev.cuh", "orb_pattern.inc", os.path.join("..", "..", "include", "orbx.h")]
 
 NVCC_FLAGS = [
     "-O3", "-std=c++17",

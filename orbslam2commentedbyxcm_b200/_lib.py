@@ -87,6 +87,10 @@ SIGNATURES = {
     "orbm_stream": (_vp, [_vp]),
     "orbm_sync": (_i, [_vp]),
     "orbm_bruteforce": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _i]),
+    "orbm_db_create": (_i, [_vp, _vp, _i, _i, C.POINTER(_vp)]),
+    "orbm_db_destroy": (None, [_vp]),
+    "orbm_bruteforce_db": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _i]),
+    "orbm_bruteforce_sharded_db": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp]),
     "orbm_merge_partials": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]),
     "orbm_undistort_keypoints": (_i, [_vp, _vp, _vp, _i, _f, _f, _f, _f, _vp, _i, _vp, _vp, _i]),
     "orbm_assign_grid": (_i, [_vp, _vp, _vp, _i, _f, _f, _f, _f, _vp, _vp, _i]),

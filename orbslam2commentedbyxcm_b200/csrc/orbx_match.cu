@@ -1302,6 +1302,9 @@ struct orbm_context {
     int world = 0, rank = 0, nqMax = 0;
     uint32_t epoch = 0;
     int* xchgTimeout = nullptr;  // mapped pinned host int, written by the kernel when a peer never answered
+    // tensor-core search: +-1 expansion of the queries of the current call
+    int8_t* qExp = nullptr;
+    size_t qExpBytes = 0;
     int stereoOutlierMode = 0;   // 0 = this reference (block inside the keypoint loop), 1 = upstream ORB-SLAM2 (after the loop)
 };
 
@@ -1334,6 +1337,61 @@ int ensure_partials(orbm_context* m, size_t bytes)
 template <typename T> int up(orbm_context* m, T* dst, const T* src, size_t n)
 {
     if (n) ORBX_CUDA_TRY(cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyHostToDevice, m->stream));
+    return ORBX_OK;
+}
+
+}  // namespace
+
+#include "orbx_match_tc.cuh"
+
+// A database prepared for the tensor-core search: the +-1 byte expansion (256 B per row, rows padded to a multiple of 256
+// with zeros) and its TMA descriptor.
+struct orbm_db {
+    int device = 0;
+    int ndb = 0;
+    long long rowsPad = 0;
+    int8_t* exp = nullptr;
+    CUtensorMap map;
+};
+
+namespace {
+
+// chunk partials of one prepared database into m->partials, same layout as bruteforce_partials
+int bruteforce_partials_tc(orbm_context* m, const orbm_db* d, const uint8_t* dq, int nq, int idxOffset, int* nChunksOut)
+{
+    const int qTiles = (nq + tc::BM - 1) / tc::BM;
+    const long long nqPad = (long long)qTiles * tc::BM;
+    if ((size_t)nqPad * 256 > m->qExpBytes) {
+        ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+        cudaFree(m->qExp); m->qExp = nullptr; m->qExpBytes = 0;
+        ORBX_CUDA_TRY(cudaMalloc(&m->qExp, (size_t)nqPad * 256));
+        m->qExpBytes = (size_t)nqPad * 256;
+    }
+    tc::k_expand_pm1<<<(unsigned)((nqPad * 32 + 255) / 256), 256, 0, m->stream>>>(dq, nq, nqPad, m->qExp);
+    CUtensorMap mapA;
+    int rc = tc::make_map(&mapA, m->qExp, nqPad, tc::BM);
+    if (rc != ORBX_OK) return rc;
+    // one CTA per SM: (query tiles) x (database chunks); chunks are multiples of the 256-row tile
+    const int target = std::max(1, m->numSMs / qTiles);
+    long long chunk = (d->ndb + target - 1) / target;
+    chunk = std::max<long long>(tc::BN, (chunk + tc::BN - 1) / tc::BN * tc::BN);
+    chunk = std::min<long long>(chunk, 1 << 21);
+    const int nChunks = (int)std::max<long long>(1, (d->ndb + chunk - 1) / chunk);
+    const size_t pBytes = sizeof(int32_t) * 3 * (size_t)nChunks * nq;
+    rc = ensure_partials(m, pBytes);
+    if (rc != ORBX_OK) return rc;
+    int32_t* pBest = m->partials;
+    int32_t* pIdx = pBest + (size_t)nChunks * nq;
+    int32_t* pSecond = pIdx + (size_t)nChunks * nq;
+    static bool attr = false;
+    if (!attr) {
+        ORBX_CUDA_TRY(cudaFuncSetAttribute(tc::k_bruteforce_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+        attr = true;
+    }
+    tc::k_bruteforce_tc<<<dim3(nChunks, qTiles), tc::THREADS, tc::SMEM_BYTES, m->stream>>>(mapA, d->map, nq, d->ndb, (int)chunk, idxOffset,
+                                                                                       pBest, pIdx, pSecond);
+    ORBX_CUDA_TRY(cudaGetLastError());
+    *nChunksOut = nChunks;
     return ORBX_OK;
 }
 
@@ -1377,7 +1435,7 @@ void orbm_destroy(orbm_context* m)
     cudaSetDevice(m->device);
     if (m->stream) cudaStreamSynchronize(m->stream);
     exchange_release(m);
-    cudaFree(m->arena); cudaFree(m->partials);
+    cudaFree(m->arena); cudaFree(m->partials); cudaFree(m->qExp);
     if (m->pinned) cudaFreeHost(m->pinned);
     if (m->stream) cudaStreamDestroy(m->stream);
     delete m;
@@ -1472,6 +1530,92 @@ int orbm_merge_partials(orbm_context* m, const int32_t* best, const int32_t* bes
     ORBX_CUDA_TRY(cudaSetDevice(m->device));
     k_merge_partials<<<(nq + 7) / 8, 256, 0, m->stream>>>(best, best_idx, second, nparts, nq, out_best, out_idx, out_second);
     ORBX_CUDA_TRY(cudaGetLastError());
+    return ORBX_OK;
+}
+
+// ---- tensor-core brute force on a prepared database (see orbx_match_tc.cuh) ----
+int orbm_db_create(orbm_context* m, const uint8_t* db, int ndb, int mem_kind, orbm_db** out)
+{
+    if (!m || !db || ndb <= 0 || !out || (mem_kind != 0 && mem_kind != 1)) {
+        set_error("orbm_db_create: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    cudaDeviceProp prop;
+    ORBX_CUDA_TRY(cudaGetDeviceProperties(&prop, m->device));
+    if (prop.major != 10) {
+        set_error("orbm_db_create: the tensor-core search needs an sm_100 device (tcgen05), found sm_%d%d", prop.major, prop.minor);
+        return ORBX_ERR_NO_DEVICE;
+    }
+    orbm_db* d = new orbm_db;
+    d->device = m->device;
+    d->ndb = ndb;
+    d->rowsPad = ((long long)ndb + tc::BN - 1) / tc::BN * tc::BN;
+    cudaError_t e = cudaMalloc(&d->exp, (size_t)d->rowsPad * 256);
+    if (e != cudaSuccess) { delete d; set_error("orbm_db_create: %s", cudaGetErrorString(e)); return ORBX_ERR_CUDA; }
+    const uint8_t* src = db;
+    uint8_t* tmp = nullptr;
+    if (mem_kind == 0) {
+        e = cudaMalloc(&tmp, 32 * (size_t)ndb);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(tmp, db, 32 * (size_t)ndb, cudaMemcpyHostToDevice, m->stream);
+        if (e != cudaSuccess) { cudaFree(tmp); cudaFree(d->exp); delete d; set_error("orbm_db_create: %s", cudaGetErrorString(e)); return ORBX_ERR_CUDA; }
+        src = tmp;
+    }
+    tc::k_expand_pm1<<<(unsigned)((d->rowsPad * 32 + 255) / 256), 256, 0, m->stream>>>(src, ndb, d->rowsPad, d->exp);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
+    cudaFree(tmp);
+    int rc = e == cudaSuccess ? tc::make_map(&d->map, d->exp, d->rowsPad, tc::BN) : ORBX_ERR_CUDA;
+    if (e != cudaSuccess) set_error("orbm_db_create: %s", cudaGetErrorString(e));
+    if (rc != ORBX_OK) { cudaFree(d->exp); delete d; return rc; }
+    *out = d;
+    return ORBX_OK;
+}
+
+void orbm_db_destroy(orbm_db* d)
+{
+    if (!d) return;
+    cudaSetDevice(d->device);
+    cudaFree(d->exp);
+    delete d;
+}
+
+int orbm_bruteforce_db(orbm_context* m, const orbm_db* d, const uint8_t* q, int nq, int idx_offset, int32_t* best, int32_t* best_idx,
+                       int32_t* second, int mem_kind)
+{
+    if (!m || !d || !q || nq <= 0 || !best || !best_idx || !second || d->device != m->device) {
+        set_error("orbm_bruteforce_db: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    const uint8_t* dq = q;
+    int32_t *dB = best, *dI = best_idx, *dS = second;
+    char* A = nullptr;
+    size_t ob = 0, oi = 0, os = 0;
+    if (mem_kind != 1) {
+        Carver c;
+        const size_t oq = c.take(32 * (size_t)nq);
+        ob = c.take(4 * (size_t)nq); oi = c.take(4 * (size_t)nq); os = c.take(4 * (size_t)nq);
+        int rc = ensure_arena(m, c.off);
+        if (rc != ORBX_OK) return rc;
+        A = m->arena;
+        ORBX_CUDA_TRY(cudaMemcpyAsync(A + oq, q, 32 * (size_t)nq, cudaMemcpyHostToDevice, m->stream));
+        dq = (uint8_t*)(A + oq); dB = (int32_t*)(A + ob); dI = (int32_t*)(A + oi); dS = (int32_t*)(A + os);
+    }
+    int nChunks = 0;
+    int rc = bruteforce_partials_tc(m, d, dq, nq, idx_offset, &nChunks);
+    if (rc != ORBX_OK) return rc;
+    const int32_t* pBest = m->partials;
+    const int32_t* pIdx = pBest + (size_t)nChunks * nq;
+    const int32_t* pSecond = pIdx + (size_t)nChunks * nq;
+    k_merge_partials<<<(nq + 7) / 8, 256, 0, m->stream>>>(pBest, pIdx, pSecond, nChunks, nq, dB, dI, dS);
+    ORBX_CUDA_TRY(cudaGetLastError());
+    if (mem_kind != 1) {
+        ORBX_CUDA_TRY(cudaMemcpyAsync(best, A + ob, 4 * (size_t)nq, cudaMemcpyDeviceToHost, m->stream));
+        ORBX_CUDA_TRY(cudaMemcpyAsync(best_idx, A + oi, 4 * (size_t)nq, cudaMemcpyDeviceToHost, m->stream));
+        ORBX_CUDA_TRY(cudaMemcpyAsync(second, A + os, 4 * (size_t)nq, cudaMemcpyDeviceToHost, m->stream));
+        ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    }
     return ORBX_OK;
 }
 
@@ -1647,11 +1791,27 @@ int orbm_bruteforce_sharded(orbm_context* m, const uint8_t* q, int nq, const uin
     return orbm_bruteforce_sharded_phases(m, q, nq, db, ndb, idx_offset, best, best_idx, second, 3);
 }
 
+static int sharded_impl(orbm_context* m, const uint8_t* q, int nq, const uint8_t* db, int ndb, const orbm_db* prepared, int idx_offset,
+                        int32_t* best, int32_t* best_idx, int32_t* second, int phases);
+
 int orbm_bruteforce_sharded_phases(orbm_context* m, const uint8_t* q, int nq, const uint8_t* db, int ndb, int idx_offset,
                                    int32_t* best, int32_t* best_idx, int32_t* second, int phases)
 {
+    return sharded_impl(m, q, nq, db, ndb, nullptr, idx_offset, best, best_idx, second, phases);
+}
+
+int orbm_bruteforce_sharded_db(orbm_context* m, const orbm_db* db_shard, const uint8_t* q, int nq, int idx_offset, int32_t* best,
+                               int32_t* best_idx, int32_t* second)
+{
+    if (!db_shard || !m || db_shard->device != m->device) { set_error("orbm_bruteforce_sharded_db: bad argument"); return ORBX_ERR_BAD_ARG; }
+    return sharded_impl(m, q, nq, nullptr, db_shard->ndb, db_shard, idx_offset, best, best_idx, second, 3);
+}
+
+static int sharded_impl(orbm_context* m, const uint8_t* q, int nq, const uint8_t* db, int ndb, const orbm_db* prepared, int idx_offset,
+                        int32_t* best, int32_t* best_idx, int32_t* second, int phases)
+{
     const bool pub = phases & 1, col = phases & 2;
-    if (!m || nq <= 0 || !(pub || col) || (pub && (!q || ndb < 0 || (ndb > 0 && !db))) || (col && (!best || !best_idx || !second))) {
+    if (!m || nq <= 0 || !(pub || col) || (pub && (!q || ndb < 0 || (ndb > 0 && !db && !prepared))) || (col && (!best || !best_idx || !second))) {
         set_error("orbm_bruteforce_sharded: bad argument");
         return ORBX_ERR_BAD_ARG;
     }
@@ -1661,7 +1821,8 @@ int orbm_bruteforce_sharded_phases(orbm_context* m, const uint8_t* q, int nq, co
     if (*m->xchgTimeout) { set_error("orbm_bruteforce_sharded: an earlier call timed out waiting for a peer"); return ORBX_ERR_CUDA; }
     int nChunks = 0;
     if (pub) {
-        int rc = bruteforce_partials(m, q, nq, db, ndb, idx_offset, &nChunks);
+        int rc = prepared ? bruteforce_partials_tc(m, prepared, q, nq, idx_offset, &nChunks)
+                          : bruteforce_partials(m, q, nq, db, ndb, idx_offset, &nChunks);
         if (rc != ORBX_OK) return rc;
         m->epoch++;
     } else if (m->epoch == 0) {

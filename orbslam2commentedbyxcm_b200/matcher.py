@@ -42,6 +42,24 @@ def frame_grid(x, y, min_x, min_y, w_inv, h_inv):
     return start, items
 
 
+class PreparedDatabase:
+    """orbm_db handle: a database expanded to +-1 bytes with its TMA descriptor (see csrc/orbx_match_tc.cuh)."""
+
+    def __init__(self, L, h, n):
+        self._L, self._h, self.n = L, h, n
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.orbm_db_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class ORBmatcher:
     TH_LOW = 50
     TH_HIGH = 100
@@ -92,6 +110,33 @@ class ORBmatcher:
 
     def bruteforce_device(self, dq, nq, ddb, ndb, idx_offset, d_best, d_idx, d_second):
         check(self._L.orbm_bruteforce(self._m, dq, nq, ddb, ndb, idx_offset, d_best, d_idx, d_second, 1), "orbm_bruteforce")
+
+    # ---- brute force on the tensor cores (tcgen05 int8 GEMM + best / second epilogue), database prepared once ----
+    def PrepareDatabase(self, db=None, d_db=None, ndb=None):
+        """Expands a descriptor database for the tensor-core search.  db: (n, 32) uint8 host array, or d_db / ndb: raw device
+        pointer and row count.  Returns a PreparedDatabase (close() frees the 256 B / row expansion)."""
+        h = C.c_void_p()
+        if db is not None:
+            db = np.ascontiguousarray(db, np.uint8)
+            check(self._L.orbm_db_create(self._m, db.ctypes.data, len(db), 0, C.byref(h)), "orbm_db_create")
+            return PreparedDatabase(self._L, h, len(db))
+        check(self._L.orbm_db_create(self._m, d_db, int(ndb), 1, C.byref(h)), "orbm_db_create")
+        return PreparedDatabase(self._L, h, int(ndb))
+
+    def BruteForceTC(self, q, prepared, idx_offset=0):
+        q = np.ascontiguousarray(q, np.uint8)
+        nq = len(q)
+        best, idx, second = (np.zeros(nq, np.int32) for _ in range(3))
+        check(self._L.orbm_bruteforce_db(self._m, prepared._h, q.ctypes.data, nq, idx_offset, best.ctypes.data, idx.ctypes.data,
+                                         second.ctypes.data, 0), "orbm_bruteforce_db")
+        return best, idx, second
+
+    def bruteforce_tc_device(self, prepared, dq, nq, idx_offset, d_best, d_idx, d_second):
+        check(self._L.orbm_bruteforce_db(self._m, prepared._h, dq, nq, idx_offset, d_best, d_idx, d_second, 1), "orbm_bruteforce_db")
+
+    def bruteforce_sharded_tc_device(self, prepared, dq, nq, idx_offset, d_best, d_idx, d_second):
+        check(self._L.orbm_bruteforce_sharded_db(self._m, prepared._h, dq, nq, idx_offset, d_best, d_idx, d_second),
+              "orbm_bruteforce_sharded_db")
 
     def merge_partials_device(self, d_best, d_idx, d_second, nparts, nq, o_best, o_idx, o_second):
         check(self._L.orbm_merge_partials(self._m, d_best, d_idx, d_second, nparts, nq, o_best, o_idx, o_second),
