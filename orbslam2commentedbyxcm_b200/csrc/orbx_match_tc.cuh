@@ -14,9 +14,9 @@
 //   warp 1      allocates TMEM (512 columns = two 128 x 256 int32 accumulators); one lane issues the MMAs: per stage four K=32
 //               steps, tcgen05.commit releases the stage, after the second K half another commit hands the accumulator over
 //   warps 2..9  epilogue: warp w reads TMEM lanes 32 (w % 4) .. +31 (its rows = queries), warps 2..5 columns 0..127 and
-//               warps 6..9 columns 128..255 of the accumulator (tcgen05.ld 32x32b.x32); per element
-//               key = -dot * 2^21 + column (one IMAD), second = min(second, max(key, best)), best = min(best, key) in two
-//               independent accumulator pairs; keys are rebased to chunk rows once per tile
+//               warps 6..9 columns 128..255 of the accumulator (tcgen05.ld 32x32b.x32); two columns per instruction:
+//               16-bit keys hamming << 7 | column packed by two IMADs, second = min(second, max(key, best)), best =
+//               min(best, key) as three VIMNMX.U16x2; keys are rebased to chunk rows once per tile
 // Partials are written in k_bruteforce's format, so k_merge_partials / k_merge_exchange are shared.
 #pragma once
 #include <cuda.h>
@@ -158,6 +158,37 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], int colBase, 
     }
 }
 
+// Packed epilogue: two columns per instruction.  key16 = hamming << 7 | column (7 bits, column inside the warp's 128) =
+// 16384 - 64 dot + column fits 16 bits (hamming <= 256), so a pair of columns is two IMADs (the second one shifts its key into
+// the upper half) and the best / second update is three VIMNMX.U16x2 for both.  The two halves of the word are independent
+// (best, second) pairs, folded into chunk-relative 32-bit keys once per tile.
+struct EpiAcc16 {
+    uint32_t b, s;
+};
+
+template <bool MASKED>
+__device__ __forceinline__ void epi_chunk16(const uint32_t (&v)[32], int colBase, int nvalidCols, EpiAcc16& a)
+{
+#pragma unroll
+    for (int j = 0; j < 32; j += 2) {
+        const uint32_t c = (uint32_t)(16384 + colBase + j) | ((uint32_t)(16384 + colBase + j + 1) << 16);
+        const uint32_t t = (uint32_t)((int)v[j] * -64) + c;
+        uint32_t p = (uint32_t)((int)v[j + 1] * -(64 << 16)) + t;
+        if (MASKED) {
+            if (colBase + j >= nvalidCols) p |= 0x0000ffffu;
+            if (colBase + j + 1 >= nvalidCols) p |= 0xffff0000u;
+        }
+        a.s = __vminu2(a.s, __vmaxu2(p, a.b));
+        a.b = __vminu2(a.b, p);
+    }
+}
+
+// 16-bit tile key -> chunk-relative 32-bit key (0xffff = nothing seen)
+__device__ __forceinline__ int key16_to_32(uint32_t k, int rowBase)
+{
+    return k == 0xffffu ? 0x7fffffff : (int)(((k >> 7) << 22) | (uint32_t)(rowBase + (int)(k & 127u)));
+}
+
 __global__ void __launch_bounds__(THREADS, 1)
 k_bruteforce_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, int nq, int ndb, int chunkRows,
                 int idxOffset, int32_t* __restrict__ pBest, int32_t* __restrict__ pIdx, int32_t* __restrict__ pSecond)
@@ -247,40 +278,42 @@ k_bruteforce_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
             tc_fence_after();
             const uint32_t taddr = tmemBase + ((uint32_t)(lg * 32) << 16) + (uint32_t)(b * BN + half * 128);
             const int nvalid = (c1 - c0) - t * BN - half * 128;  // valid columns of this warp's 128
-            EpiAcc a = {KEY_SENTINEL, KEY_SENTINEL, KEY_SENTINEL, KEY_SENTINEL};
+            EpiAcc16 a = {0xffffffffu, 0xffffffffu};
             uint32_t v0[32], v1[32];
             tmem_ld32(taddr, v0);
             tmem_ld_wait(v0);
             tmem_ld32(taddr + 32, v1);
             if (nvalid >= 128) {
-                epi_chunk<false>(v0, 0, 128, a);
+                epi_chunk16<false>(v0, 0, 128, a);
                 tmem_ld_wait(v1);
                 tmem_ld32(taddr + 64, v0);
-                epi_chunk<false>(v1, 32, 128, a);
+                epi_chunk16<false>(v1, 32, 128, a);
                 tmem_ld_wait(v0);
                 tmem_ld32(taddr + 96, v1);
-                epi_chunk<false>(v0, 64, 128, a);
+                epi_chunk16<false>(v0, 64, 128, a);
                 tmem_ld_wait(v1);
-                epi_chunk<false>(v1, 96, 128, a);
+                epi_chunk16<false>(v1, 96, 128, a);
             } else {
-                epi_chunk<true>(v0, 0, nvalid, a);
+                epi_chunk16<true>(v0, 0, nvalid, a);
                 tmem_ld_wait(v1);
                 tmem_ld32(taddr + 64, v0);
-                epi_chunk<true>(v1, 32, nvalid, a);
+                epi_chunk16<true>(v1, 32, nvalid, a);
                 tmem_ld_wait(v0);
                 tmem_ld32(taddr + 96, v1);
-                epi_chunk<true>(v0, 64, nvalid, a);
+                epi_chunk16<true>(v0, 64, nvalid, a);
                 tmem_ld_wait(v1);
-                epi_chunk<true>(v1, 96, nvalid, a);
+                epi_chunk16<true>(v1, 96, nvalid, a);
             }
             // all TMEM reads of this warp are complete: hand the accumulator back
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(barTmemEmpty + 8 * b);
-            // fold the tile into the running pair
-            const int off = (256 << 21) + t * BN + half * 128;
-            const int tb = min(a.b0, a.b1) + off;
-            const int ts = min(max(a.b0, a.b1), min(a.s0, a.s1)) + off;
+            // fold the tile (two independent 16-bit pairs) into the running chunk-relative pair
+            const int rowBase = t * BN + half * 128;
+            const int b0 = key16_to_32(a.b & 0xffffu, rowBase), b1 = key16_to_32(a.b >> 16, rowBase);
+            const int s0 = key16_to_32(a.s & 0xffffu, rowBase), s1 = key16_to_32(a.s >> 16, rowBase);
+            const int tb = min(b0, b1);
+            const int ts = min(max(b0, b1), min(s0, s1));
             S = min(min(S, ts), max(B, tb));
             B = min(B, tb);
         }
