@@ -4,7 +4,8 @@
   python bench.py --gpus N --steps K --warmup W            our CUDA path (one rank per GPU; torchrun for N > 1)
   python bench.py --impl reference --gpus N --steps K ...  the reference's own CPU ORBextractor on the host cores
 
-A "step" = one pass of the extractor over a batch of synthetic frames (BATCH frames per GPU, weak scaling).
+A "step" = INNER passes of the extractor over a BATCH-frame buffer of synthetic frames (INNER x BATCH frames per GPU, weak
+scaling), so that the K timed steps cover >= 0.5 s.
   value : frames/s with the frames already resident in HBM (device in, device out, CUDA events on the handle's stream)
   e2e   : frames/s through the C-ABI host entry point orbx_extract_batch (pinned host input, H2D + kernels + D2H +
           the copy into caller arrays inside the timed region)
@@ -29,7 +30,14 @@ if ROOT not in sys.path:
 from orbslam2commentedbyxcm_b200 import sharding, synth  # noqa: E402
 
 WORKLOAD = "tum"  # BASELINE.json metric: "ORB extract frames/s @640x480 1k feats"
-BATCH = 256       # frames per GPU per step
+WORKLOAD_NAME = "C1 TUM 640x480, 1000 feats, scale 1.2, 8 levels, FAST 20/7"
+# identical in both arms' JSON lines (the driver compares them); what one step holds is in "step_detail"
+CONFIG = {"workload": WORKLOAD_NAME, "parallelism": "frames sharded by rank, no data-path collective",
+          "l2": "inputs larger than L2: every pass streams a frame buffer + pyramid of more than 126 MB"}
+BATCH = 256       # frames per GPU per pass (one device buffer, larger than L2 with its pyramid)
+INNER = 32        # passes per step: a step is INNER x BATCH frames per GPU, so 20 steps time >= 0.5 s
+E2E_INNER = 16    # host calls (BATCH frames each) per end-to-end step
+C4_JOBS = 16      # repetitions of the 4096-frame config-4 job inside its timed region
 N_DISTINCT = 32   # distinct synthetic frames (seeds 0..31), tiled to BATCH
 
 
@@ -162,20 +170,55 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_peaks_all():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p))
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}
+
+
 def measured_traffic(stage, frames):
-    """DRAM bytes per launch of a stage from the committed ncu capture (profiles/r1_traffic.json), or None."""
-    p = os.path.join(ROOT, "profiles", "r1_traffic.json")
-    try:
-        d = json.load(open(p))
-        return int(d["bytes_per_frame"][stage] * frames)
-    except Exception:
-        return None
+    """(DRAM bytes per launch of a stage, source): NOT measured by this run -- dram__bytes_read + dram__bytes_write of a committed
+    `ncu --set full` capture (per frame, 64-frame launch) scaled to this launch's frame count; (None, why) without one."""
+    for name in ("r2_traffic.json", "r1_traffic.json"):
+        p = os.path.join(ROOT, "profiles", name)
+        try:
+            d = json.load(open(p))
+            return int(d["bytes_per_frame"][stage] * frames), "ncu capture profiles/%s, extrapolated per frame (not measured live)" % name
+        except Exception:
+            continue
+    return None, "no ncu capture committed"
 
 
 def make_frames(shape, n_distinct, batch):
     base = np.stack([synth.gen_frame(shape, s) for s in range(n_distinct)])
     reps = (batch + n_distinct - 1) // n_distinct
     return np.concatenate([base] * reps)[:batch].copy()
+
+
+def output_digest(kps, desc, counts, n):
+    """sha256 over (count, keypoint records, descriptor rows) of the first n frames: the same bytes from the CUDA path and
+    from the reference arm mean identical keypoints (coordinates, octave, angle bits, response, order) and descriptors."""
+    import hashlib
+
+    h = hashlib.sha256()
+    for i in range(n):
+        c = int(counts[i])
+        h.update(np.int32(c).tobytes())
+        h.update(np.ascontiguousarray(kps[i, :c]).tobytes())
+        h.update(np.ascontiguousarray(desc[i, :c]).tobytes())
+    return h.hexdigest()
+
+
+def reference_digest(frames, cfg, cap):
+    """digest of the reference's own ORBextractor.cc (oracle/_ref) on `frames`, or (None, why)."""
+    import oracle
+
+    ref = oracle.ref_extract_batch_full(frames, *cfg, cap=cap, threads=host_threads())
+    if ref is None:
+        return None, "oracle/_ref/liborbref_fast.so not present"
+    rk, rd, rc = ref
+    return output_digest(rk, rd, rc, len(frames)), "reference src/ORBextractor.cc (oracle/_ref/liborbref_fast.so)"
 
 
 def host_threads():
@@ -209,17 +252,21 @@ def run_reference(args):
         total_kp += tot
     dt = time.perf_counter() - t0
     fps = sample * args.steps / dt
+    distinct = make_frames(shape, N_DISTINCT, N_DISTINCT)
+    digest, digest_src = (reference_digest(distinct, cfg, 2 * cfg[0]) if kind == "ref_fast" else (None, "oracle port only"))
     line = {
         "impl": "reference", "metric": "orb_extract_frames_per_s_640x480_1000feat", "value": fps, "unit": "frames/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "C1 TUM 640x480, 1000 feats, scale 1.2, 8 levels, FAST 20/7; %d-frame sample per step" % sample},
+        "config": dict(CONFIG),
+        "step_detail": {"step": "%d-frame sample of the workload per step, frame-parallel on %d host threads" % (sample, threads)},
         "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads,
                          "kind": "reference" if kind == "ref_fast" else "port",
                          "sample": "%d frames x %d steps, %d host threads, %s" % (sample, args.steps, threads,
                                    "reference src/ORBextractor.cc + mini-cv shim (-O3 x86-64-v3)" if kind == "ref_fast" else "oracle port (-O3 x86-64-v3)")},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "keypoints_per_frame": total_kp / (sample * args.steps),
+        "output_sha256": {"frames": N_DISTINCT, "digest": digest, "of": digest_src},
     }
     print(json.dumps(line))
 
@@ -308,20 +355,6 @@ def other_configs(pkg, torch, dev, local):
         t0 = time.perf_counter()
         nm, _o = mt2.SearchByProjection(frame, mps, 3.0)
         ts.append(time.perf_counter() - t0)
-    # ---- C4: 4096 KITTI-shaped frames through the host C-ABI (8 calls of 512 frames from one pinned buffer) ----
-    big = torch.from_numpy(np.concatenate([frames] * 8)).pin_memory()   # 512 frames
-    bout = ex.alloc_outputs(512, rows, cols, pinned=True)
-    t_w = time.perf_counter()
-    while time.perf_counter() - t_w < 0.3:   # host path warm-up by time (see the e2e section of run_ours)
-        ex.extract_batch(big.numpy(), out=bout)
-    t0 = time.perf_counter()
-    for _ in range(8):
-        ex.extract_batch(big.numpy(), out=bout)
-    c4_s = time.perf_counter() - t0
-    out["C4_batched_4096x1241x376_2000"] = {
-        "frames_per_s_e2e": 4096 / c4_s, "seconds_for_4096_frames": c4_s,
-        "note": "pinned host in / pinned host out, 8 x 512-frame calls (8 distinct seeded frames tiled), H2D | kernels | D2H pipelined"}
-    del big, bout
     out["C3_kitti_1241x376_2000"] = {
         "extract_frames_per_s_device_resident": fps, "frames_per_step": Bk, "keypoints_per_frame": n,
         "search_by_projection_ms_e2e": 1e3 * float(np.median(ts)), "map_points": nmp, "matches": int(nm),
@@ -331,6 +364,40 @@ def other_configs(pkg, torch, dev, local):
 
 
 # ------------------------------------------------------------------------------------------------------------------
+def c4_leg(pkg, torch, dev, local, rank, world, barrier):
+    """BASELINE.json config 4: re-extraction of 4096 synthetic 1241x376 frames, 2000 features, sharded by frame across the
+    ranks (strong scaling: 4096 / N frames per rank, no data-path collective), through the reference-facing host call
+    orbx_extract_batch with pinned host input and output.  Returns (seconds, frames of this rank, keypoints per frame)."""
+    shape, cfg = synth.SHAPES["kitti"], synth.PRESETS["kitti"]
+    rows, cols = shape
+    total = 4096
+    mine = len(sharding.frame_shard(total, rank, world))
+    call = min(512, mine)
+    ncalls = (mine + call - 1) // call
+    frames = make_frames(shape, 8, call)
+    ex = pkg.ORBextractor(*cfg, device=local)
+    big = torch.from_numpy(frames).pin_memory()
+    bout = ex.alloc_outputs(call, rows, cols, pinned=True)
+    t_w = time.perf_counter()
+    while time.perf_counter() - t_w < 0.3:   # host path warm-up by time (see the e2e section of run_ours)
+        ex.extract_batch(big.numpy(), out=bout)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(C4_JOBS):       # the 4096-frame job repeated so that the timed region is >= 0.5 s
+        done = 0
+        for i in range(ncalls):
+            n = min(call, mine - done)
+            ex.extract_batch(big.numpy()[:n], out=(bout[0][:n], bout[1][:n], bout[2][:n]))
+            done += n
+    torch.cuda.synchronize()
+    dt = (time.perf_counter() - t0) / C4_JOBS
+    barrier()
+    kp = float(bout[2][: min(call, mine)].mean())
+    ex.close()
+    del big, bout
+    return dt, mine, kp
+
+
 def bind_to_gpu_numa_node(index):
     """One process per GPU: pin the process to the CPUs next to its GPU (NVML's ideal affinity) before the page-locked host
     buffers are allocated, so that first touch places them on the GPU's NUMA node.  Matters when eight ranks stream frames
@@ -383,8 +450,12 @@ def run_ours(args):
     d_counts = torch.empty(B, dtype=torch.int32, device=dev)
     torch.cuda.synchronize()
 
-    def step_device():
+    def pass_device():
         ex.extract_batch_device(d_imgs.data_ptr(), B, rows, cols, d_kps.data_ptr(), d_desc.data_ptr(), d_counts.data_ptr(), cap)
+
+    def step_device():
+        for _ in range(args.inner):
+            pass_device()
 
     def barrier():
         if dist is not None:
@@ -406,15 +477,28 @@ def run_ours(args):
     ex.sync()
     barrier()
     ms = e0.elapsed_time(e1)
-    launches = ex.last_launch_count() * args.steps
+    launches = ex.last_launch_count() * args.steps * args.inner
     counts = d_counts.cpu().numpy()
+    # parity of the timed batch: digest of the device-resident outputs of the N_DISTINCT distinct frames (rank 0 holds them
+    # unrotated) against the reference's own extractor on the same frames
+    parity = None
+    if rank == 0:
+        nd = min(N_DISTINCT, B)
+        kps_h = d_kps[:nd].cpu().numpy().view(pkg.KP_DTYPE).reshape(nd, cap)
+        desc_h = d_desc[:nd].cpu().numpy()
+        ours_digest = output_digest(kps_h, desc_h, counts, nd)
+        ref_digest, ref_src = reference_digest(frames[:nd], cfg, cap)
+        parity = {"frames": nd, "digest": ours_digest, "reference_digest": ref_digest, "reference": ref_src,
+                  "equal": (ours_digest == ref_digest) if ref_digest else None}
+        if ref_digest and ours_digest != ref_digest:
+            raise RuntimeError("bench: the timed batch's keypoints / descriptors differ from the reference extractor")
 
     # ---- per-stage timing (CUDA events between stages on the handle's stream; serialised, no graph) ----
     ex.set_profiling(True)
     stage_ms = {}
     reps = max(3, min(args.steps, 10))
     for i in range(reps + 1):
-        step_device()
+        pass_device()
         ex.sync()
         if i == 0:
             continue
@@ -435,12 +519,17 @@ def run_ours(args):
         n_w += 1
     barrier()
     t0 = time.perf_counter()
-    for _ in range(e2e_steps):
+    for _ in range(e2e_steps * args.e2e_inner):
         ex.extract_batch(h_imgs.numpy(), out=out)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     barrier()
     clocks = sampler.stop() if rank == 0 else None
+    if rank == 0 and parity is not None:
+        nd = parity["frames"]
+        parity["e2e_digest_equal"] = output_digest(out[0], out[1], out[2], nd) == parity["digest"]
+        if not parity["e2e_digest_equal"]:
+            raise RuntimeError("bench: the host-path outputs differ from the device-resident outputs")
 
     # ---- single-frame latency through the host C-ABI ----
     one = frames[:1].copy()
@@ -454,7 +543,9 @@ def run_ours(args):
         lat.append(time.perf_counter() - t)
     lat_ms = 1e3 * float(np.median(lat))
 
-    # ---- brute-force Hamming (config 5 shape: 2000 queries x 1M map descriptors, sharded by rank) ----
+    # ---- brute-force Hamming (config 5: 2000 queries x 1M map descriptors, the map sharded by rank) ----
+    # default path = tensor cores (tcgen05 int8 GEMM on +-1 expanded descriptors + best / second epilogue, the shard expanded
+    # once by orbm_db_create); the integer-pipe kernel (LOP3 + POPC) is timed beside it and both must agree bit for bit
     m = pkg.ORBmatcher(0.6, True, device=local)
     ndb_total, nq = 1_000_000, 2000
     lo, hi = sharding.db_shard(ndb_total, rank, world)
@@ -467,65 +558,85 @@ def run_ours(args):
     pi = torch.empty_like(pb)
     ps = torch.empty_like(pb)
     mstream = torch.cuda.ExternalStream(m.stream, device=dev)
+    b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    b0.record(mstream)
+    prep = m.PrepareDatabase(d_db=ddb.data_ptr(), ndb=per)
+    b1.record(mstream)
+    m.sync()
+    expand_ms = b0.elapsed_time(b1)
 
     ob, oi, os_ = torch.empty_like(pb), torch.empty_like(pb), torch.empty_like(pb)
+    ib, ii, is_ = torch.empty_like(pb), torch.empty_like(pb), torch.empty_like(pb)
     if dist is not None:
         # N > 1: the search, the exchange of the per-shard (best, idx, second) triples and the merge are ONE stream of
-        # device work per rank: k_bruteforce on the shard, then k_merge_exchange (P2P stores into every peer's buffer
-        # over NVLink, wait for the peers' triples, deterministic merge) -- no NCCL call on the data path.
+        # device work per rank: the shard search, then k_merge_exchange (P2P stores into every peer's buffer over NVLink,
+        # wait for the peers' triples, deterministic merge) -- no NCCL call on the data path.
         m.exchange_connect_group(world, rank, nq)
 
         def bf_step():
-            m.bruteforce_sharded_device(dq.data_ptr(), nq, ddb.data_ptr(), per, lo, ob.data_ptr(), oi.data_ptr(), os_.data_ptr())
+            m.bruteforce_sharded_tc_device(prep, dq.data_ptr(), nq, lo, ob.data_ptr(), oi.data_ptr(), os_.data_ptr())
+
+        def bf_int_step():
+            m.bruteforce_sharded_device(dq.data_ptr(), nq, ddb.data_ptr(), per, lo, ib.data_ptr(), ii.data_ptr(), is_.data_ptr())
     else:
         def bf_step():
-            m.bruteforce_device(dq.data_ptr(), nq, ddb.data_ptr(), per, lo, ob.data_ptr(), oi.data_ptr(), os_.data_ptr())
+            m.bruteforce_tc_device(prep, dq.data_ptr(), nq, lo, ob.data_ptr(), oi.data_ptr(), os_.data_ptr())
 
-    for _ in range(3):
-        bf_step()
-    m.sync()
-    barrier()
-    b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    bf_reps = 20
-    b0.record(mstream)
-    for _ in range(bf_reps):
-        bf_step()
-    b1.record(mstream)
-    m.sync()
-    bf_ms = b0.elapsed_time(b1) / bf_reps
+        def bf_int_step():
+            m.bruteforce_device(dq.data_ptr(), nq, ddb.data_ptr(), per, lo, ib.data_ptr(), ii.data_ptr(), is_.data_ptr())
+
+    def timed(fn, reps):
+        for _ in range(3):
+            fn()
+        m.sync()
+        barrier()
+        b0.record(mstream)
+        for _ in range(reps):
+            fn()
+        b1.record(mstream)
+        m.sync()
+        barrier()
+        return b0.elapsed_time(b1) / reps
+
+    bf_ms = timed(bf_step, 1500 if world == 1 else 3000)      # >= 0.5 s of searches at every N
+    bf_int_ms = timed(bf_int_step, 150)
+    if not (torch.equal(ib, ob) and torch.equal(ii, oi) and torch.equal(is_, os_)):
+        raise RuntimeError("brute force: tensor-core and integer-pipe kernels disagree")
     nccl_ms = None
     if dist is not None:
         if m.exchange_timed_out():
             raise RuntimeError("sharded search: a peer never answered")
-        # cross-check + comparison: the same search through NCCL (per-shard search, 3 all-gathers, merge kernel)
-        gb = [torch.empty_like(pb) for _ in range(world)]
-        gi = [torch.empty_like(pb) for _ in range(world)]
-        gs = [torch.empty_like(pb) for _ in range(world)]
+        # like-for-like baseline: the same shard search, then ONE all-gather of the packed (best, idx, second) triples and the
+        # merge kernel, all enqueued on the matcher's stream, CUDA-event timed, no host synchronisation inside
+        packed = torch.empty((3, nq), dtype=torch.int32, device=dev)
+        gathered = torch.empty((world, 3, nq), dtype=torch.int32, device=dev)
         nb, ni, ns = torch.empty_like(pb), torch.empty_like(pb), torch.empty_like(pb)
 
         def nccl_step():
-            m.bruteforce_device(dq.data_ptr(), nq, ddb.data_ptr(), per, lo, pb.data_ptr(), pi.data_ptr(), ps.data_ptr())
-            m.sync()
-            dist.all_gather(gb, pb); dist.all_gather(gi, pi); dist.all_gather(gs, ps)
-            sb, si, ss = torch.stack(gb), torch.stack(gi), torch.stack(gs)
-            torch.cuda.synchronize()
-            m.merge_partials_device(sb.data_ptr(), si.data_ptr(), ss.data_ptr(), world, nq, nb.data_ptr(), ni.data_ptr(), ns.data_ptr())
-            m.sync()
+            m.bruteforce_tc_device(prep, dq.data_ptr(), nq, lo, packed[0].data_ptr(), packed[1].data_ptr(), packed[2].data_ptr())
+            with torch.cuda.stream(mstream):
+                dist.all_gather_into_tensor(gathered, packed)
+                parts = gathered.permute(1, 0, 2).contiguous()     # [3][world][nq]: the layout orbm_merge_partials reads
+            m.merge_partials_device(parts[0].data_ptr(), parts[1].data_ptr(), parts[2].data_ptr(), world, nq, nb.data_ptr(),
+                                    ni.data_ptr(), ns.data_ptr())
 
-        nccl_step()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(5):
-            nccl_step()
-        nccl_ms = 1e3 * (time.perf_counter() - t0) / 5
+        nccl_ms = timed(nccl_step, 1000)
+        torch.cuda.synchronize()
         if not (torch.equal(nb, ob) and torch.equal(ni, oi) and torch.equal(ns, os_)):
             raise RuntimeError("sharded search: fused exchange and NCCL all-gather + merge disagree")
 
+    # ---- config 4 (strong scaling over the ranks) ----
+    c4_s, c4_frames, c4_kp = (None, 0, None)
+    if not args.no_extra:
+        c4_s, c4_frames, c4_kp = c4_leg(pkg, torch, dev, local, rank, world, barrier)
+
     # ---- max over ranks ----
-    t = torch.tensor([ms, e2e_s, bf_ms], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms, e2e_s, bf_ms, bf_int_ms, nccl_ms or 0.0, c4_s or 0.0], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, e2e_s, bf_ms = t.tolist()
+    ms, e2e_s, bf_ms, bf_int_ms, nccl_ms_max, c4_s = t.tolist()
+    if nccl_ms is not None:
+        nccl_ms = nccl_ms_max
 
     if rank == 0:
         peak, peak_src = measured_peaks()
@@ -536,42 +647,77 @@ def run_ours(args):
             gbs = ab[k] * B / (t_ms * 1e-3) / 1e9 if t_ms > 0 else 0.0
             stages[k] = {"ms": t_ms, "algo_bytes_per_frame": ab[k], "GB_per_s": gbs, "frac_of_hbm_peak": gbs / peak}
         dom = max(("pyramid", "fast", "octree", "blur", "desc"), key=lambda k: stage_ms.get(k, 0.0))
-        fps = world * B * args.steps / (ms * 1e-3)
-        e2e_fps = world * B * e2e_steps / e2e_s
+        frames_step = B * args.inner
+        fps = world * frames_step * args.steps / (ms * 1e-3)
+        e2e_fps = world * B * args.e2e_inner * e2e_steps / e2e_s
         d2h = out[0].nbytes + out[1].nbytes + out[2].nbytes
+        traffic, traffic_src = measured_traffic(dom, B)
+        five = sum(ab[k] for k in ("pyramid", "fast", "blur", "desc"))   # pyramid + FAST + blur + orientation + descriptor
+        peaks = measured_peaks_all()
+        # tensor roof of the int8 search: int8 dense = 2 x bf16 dense on B200 (4.5 vs 2.25 PFLOP/s nominal); the measured
+        # denominator is 2 x the driver's measured cuBLAS bf16 burst figure
+        tc_ops = 2.0 * ((nq + 127) // 128 * 128) * per * 256
+        tc_tops = world * tc_ops / (bf_ms * 1e-3) / 1e12
+        int8_peak = 2.0 * peaks["bf16_tflops"]
+        # integer-pipe roof of the POPC kernel (profiles/r1_bruteforce_variants.md): 6 POPC per pair, 16 POPC lanes / clk / SM
+        popc_roof = 148 * 16 * (clocks["sm_mhz"] or 1965.0) * 1e6 / 6.0 if clocks else None
         line = {
             "metric": "orb_extract_frames_per_s_640x480_1000feat", "value": fps, "unit": "frames/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {
-                "workload": "C1 TUM 640x480, 1000 feats, scale 1.2, 8 levels, FAST 20/7; %d frames per GPU per step "
-                            "(%d distinct seeded frames tiled)" % (B, N_DISTINCT),
-                "frames_per_gpu_per_step": B, "parallelism": "frames sharded by rank, no data-path collective",
-                "l2": "working set per step (%d MB of frames + pyramid + blurred planes) exceeds the 126 MB L2" %
-                      (B * (rows * cols + 2 * 1.2e6) / 1e6),
-            },
-            "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": int(frames.nbytes),
-                    "d2h_bytes_per_step": int(d2h), "steps": e2e_steps},
+            "config": dict(CONFIG),
+            "step_detail": {
+                "step": "%d frames per GPU per step = %d passes over a %d-frame device buffer (%d distinct seeded frames tiled)"
+                        % (frames_step, args.inner, B, N_DISTINCT),
+                "frames_per_gpu_per_step": frames_step,
+                "l2": "working set per pass (%d MB of frames + pyramid + blurred planes) exceeds the 126 MB L2" %
+                      (B * (rows * cols + 2 * 1.2e6) / 1e6)},
+            "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": int(frames.nbytes) * args.e2e_inner,
+                    "d2h_bytes_per_step": int(d2h) * args.e2e_inner, "steps": e2e_steps,
+                    "calls_per_step": args.e2e_inner, "frames_per_call": B, "timed_region_s": e2e_s},
             "gpu_launches": launches,
             "clocks": clocks,
+            "parity_checked": bool(parity and parity["equal"]),
+            "parity": parity,
             "roofline": {
                 "kernel": dom, "bound": "hbm", "achieved": stages[dom]["GB_per_s"], "peak": peak, "unit": "GB/s",
-                "frac": stages[dom]["frac_of_hbm_peak"], "traffic": measured_traffic(dom, B), "peak_source": peak_src,
+                "frac": stages[dom]["frac_of_hbm_peak"], "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": ab[dom] * B,
-                "whole_step_GB_per_s": sum(ab.values()) * B * args.steps / (ms * 1e-3) / 1e9,
+                "whole_step_GB_per_s": five * frames_step * args.steps / (ms * 1e-3) / 1e9,
             },
             "stages": stages,
             "keypoints_per_frame": float(counts.mean()),
             "latency_ms_single_frame_e2e": lat_ms,
-            "hamming": {"pairs_per_s": world * nq * per / (bf_ms * 1e-3), "queries": nq, "db_rows_per_gpu": per,
-                        "ms_per_search": bf_ms, "unit": "descriptor pairs/s",
-                        "exchange": ("none (one shard)" if world == 1 else
-                                     "fused: k_merge_exchange stores the per-query triples into every peer's buffer over NVLink "
-                                     "P2P and merges; checked equal to NCCL all-gather + merge"),
-                        "nccl_allgather_path_ms_per_search_wall": nccl_ms},
+            "hamming": {
+                "pairs_per_s": world * nq * per / (bf_ms * 1e-3), "queries": nq, "db_rows_per_gpu": per,
+                "ms_per_search": bf_ms, "unit": "descriptor pairs/s",
+                "kernel": "k_bruteforce_tc (tcgen05.mma kind::i8, TMA, TMEM; shard expanded once in %.2f ms)" % expand_ms,
+                "roofline": {"bound": "tensor", "achieved": tc_tops / world, "peak": int8_peak, "unit": "TOP/s (int8, per GPU)",
+                             "frac": tc_tops / world / int8_peak,
+                             "peak_source": "2 x measured bf16 dense (MEASURED_PEAKS.json bf16_tflops); nominal int8 4500"},
+                "integer_pipe_kernel": {
+                    "ms_per_search": bf_int_ms, "pairs_per_s": world * nq * per / (bf_int_ms * 1e-3),
+                    "roofline": {"bound": "int-pipe", "achieved": nq * per / (bf_int_ms * 1e-3), "peak": popc_roof,
+                                 "unit": "pairs/s per GPU", "frac": (nq * per / (bf_int_ms * 1e-3) / popc_roof) if popc_roof else None,
+                                 "peak_source": "148 SMs x 16 POPC / clk x SM clock under load / 6 POPC per pair"}},
+                "results_equal": True,
+                "exchange": ("none (one shard)" if world == 1 else
+                             "fused: k_merge_exchange stores the per-query triples into every peer's buffer over NVLink "
+                             "P2P and merges; checked equal to NCCL all-gather + merge"),
+                "nccl_allgather_path_ms_per_search": nccl_ms,
+                "nccl_allgather_path": None if nccl_ms is None else
+                    "same shard search + ONE all_gather_into_tensor of the packed triples + merge kernel on the matcher stream, "
+                    "CUDA-event timed, no host synchronisation"},
         }
+        if c4_s:
+            line.setdefault("configs", {})["C4_batched_4096x1241x376_2000"] = {
+                "frames_per_s_e2e": 4096 / c4_s, "seconds_for_4096_frames": c4_s, "jobs_timed": C4_JOBS,
+                "timed_region_s": c4_s * C4_JOBS, "frames_per_rank": c4_frames,
+                "keypoints_per_frame": c4_kp, "scaling": "strong (4096 frames sharded by frame over %d rank(s))" % world,
+                "note": "pinned host in / pinned host out through orbx_extract_batch, calls of <= 512 frames (8 distinct seeded "
+                        "frames tiled), H2D | kernels | D2H pipelined; max over ranks"}
         if world == 1 and not args.no_extra:
-            line["configs"] = other_configs(pkg, torch, dev, local)
+            line.setdefault("configs", {}).update(other_configs(pkg, torch, dev, local))
         # CPU baseline on rank 0 at N = 1 only (bounded sample)
         if world == 1 and not args.no_cpu_baseline:
             import oracle
@@ -581,7 +727,7 @@ def run_ours(args):
             sample = max(4 * threads, 16)
             oracle.extract_batch(frames[:threads], *cfg, threads=threads, kind=kind)
             reps_cpu, t_cpu = 0, 0.0
-            while t_cpu < 10.0 and reps_cpu < 50:
+            while t_cpu < 10.0 and reps_cpu < 1000:
                 t0 = time.perf_counter()
                 oracle.extract_batch(frames[:sample], *cfg, threads=threads, kind=kind)
                 t_cpu += time.perf_counter() - t0
@@ -607,6 +753,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--inner", type=int, default=INNER, help="passes over the device buffer per timed step")
+    ap.add_argument("--e2e-inner", type=int, default=E2E_INNER, help="host calls per end-to-end step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the C2 / C3 side measurements")
     args = ap.parse_args()

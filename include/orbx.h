@@ -96,7 +96,9 @@ int orbx_extract(orbx_handle* h, const uint8_t* img, int rows, int cols, size_t 
 
 /* Same computation with DEVICE-resident inputs and outputs, asynchronous on the handle's stream (no copy, no
  * host synchronisation): d_imgs are tight or pitched device frames, d_kps/d_desc/d_counts device buffers laid
- * out as in orbx_extract_batch.  Use orbx_sync() (or your own event on orbx_stream()) before reading results. */
+ * out as in orbx_extract_batch.  Use orbx_sync() (or your own event on orbx_stream()) before reading results.
+ * capacity below orbx_max_keypoints() is accepted; a frame with more keypoints than capacity is truncated to it AND
+ * reported: the next orbx_sync() returns ORBX_ERR_CAPACITY. */
 int orbx_extract_batch_device(orbx_handle* h, const uint8_t* d_imgs, int n, int rows, int cols, size_t step,
                               size_t frame_stride, orbx_keypoint* d_kps, uint8_t* d_desc, int capacity,
                               int* d_counts);
@@ -107,7 +109,12 @@ void* orbx_stream(orbx_handle* h);
 /* Replaces the public member mvImagePyramid (include/ORBextractor.h:162) of the LAST extracted batch:
  * copies level `level` of frame `frame` INCLUDING its 19-px REFLECT_101 frame into dst
  * ((rows_l + 38) rows of (cols_l + 38) bytes, dst_step bytes apart), so that an ROI at (19,19) of dst behaves
- * like the reference's Mat (adjustROI by <= 19 stays valid, src/Frame.cc:782-831). */
+ * like the reference's Mat (adjustROI by <= 19 stays valid, src/Frame.cc:782-831).
+ * Residency: `frame` indexes the last batch.  After orbx_extract_batch_device and after host batches of up to 48
+ * frames every frame of the batch is resident.  A larger host batch is pipelined through two arena slots and only
+ * the frames of its last two chunks (at most the last 64 frames) stay resident; asking for an earlier frame -- here,
+ * in orbm_stereo_match (which reads the pyramids through the handle) or in the orbx_debug_* getters -- returns
+ * ORBX_ERR_BAD_ARG ("no longer resident"), never another frame's data. */
 int orbx_get_level_size(orbx_handle* h, int level, int* rows_l, int* cols_l);
 int orbx_get_pyramid_level(orbx_handle* h, int frame, int level, uint8_t* dst, size_t dst_step);
 
@@ -194,7 +201,9 @@ int orbm_bruteforce_db(orbm_context* m, const orbm_db* db, const uint8_t* q, int
  * per-query (best, index, second) triple into every peer's buffer with NVLink P2P stores, waits for the peers' triples
  * in its own buffer and merges them (same deterministic rule as orbm_merge_partials, so the result equals the
  * unsharded sequential scan on every rank).  All ranks must call orbm_bruteforce_sharded the same number of times with
- * the same queries.  Pointers of orbm_bruteforce_sharded are DEVICE pointers; call orbm_sync() before reading. */
+ * the same queries; nq may differ from call to call (any value up to nq_max): the slot freshness tag wraps every 16384
+ * calls, and each call rewrites a rotating window of unused slots so that an old tag can never pass for the current one.
+ * Pointers of orbm_bruteforce_sharded are DEVICE pointers; call orbm_sync() before reading. */
 #define ORBM_IPC_HANDLE_BYTES 64
 #define ORBM_MAX_WORLD 16
 int orbm_exchange_create(orbm_context* m, int world, int rank, int nq_max, uint8_t* handle_out /* 64 B or NULL */,
@@ -216,6 +225,9 @@ int orbm_bruteforce_sharded_db(orbm_context* m, const orbm_db* db_shard, const u
                                int32_t* best_idx, int32_t* second);
 /* 1 if a sharded search gave up waiting for a peer (the results of that call are invalid) */
 int orbm_exchange_timed_out(orbm_context* m);
+/* test hook: copies the first nwords 64-bit slot words (tag << 50 | best << 41 | second << 32 | index; layout
+ * [parity][source rank][nq_max]) of this rank's exchange buffer to the host, and the number of searches published so far */
+int orbm_debug_exchange_snapshot(orbm_context* m, uint64_t* words, size_t nwords, uint32_t* epoch);
 
 /* Frame-side inputs of the windowed searches: Frame::mvKeysUn, mvuRight, mDescriptors, mvpMapPoints occupancy,
  * mGrid (src/Frame.cc:351-370) flattened as CSR with cell (ix, iy) at ix*48+iy, and the grid constants. */

@@ -101,6 +101,7 @@ SIGNATURES = {
     "orbm_bruteforce_sharded": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp]),
     "orbm_bruteforce_sharded_phases": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _i]),
     "orbm_exchange_timed_out": (_i, [_vp]),
+    "orbm_debug_exchange_snapshot": (_i, [_vp, _vp, C.c_size_t, _vp]),
     "orbm_search_by_projection": (_i, [_vp, C.POINTER(FrameView), C.POINTER(MapPointView), _f, _f, _vp, _vp]),
     "orbm_search_window": (_i, [_vp, C.POINTER(FrameView), _vp, C.POINTER(WindowQueryView), _i, _i, _f, _i, _vp, _vp]),
     "orbm_search_best": (_i, [_vp, C.POINTER(FrameView), C.POINTER(WindowQueryView), _i, _vp, _i, _vp, _vp]),

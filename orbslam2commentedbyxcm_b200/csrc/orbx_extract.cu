@@ -536,7 +536,9 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
         if (hasL) keep = keep && s > s0[-1] && s > s0[-FAST_P - 1] && s > s0[FAST_P - 1];
         if (hasR) keep = keep && s > s0[1] && s > s0[-FAST_P + 1] && s > s0[FAST_P + 1];
         if (keep) {
-            q3[atomicAdd(&sQ3, 1)] = (unsigned short)((ty << 8) | tx);
+            const int p3 = atomicAdd(&sQ3, 1);
+            if (p3 < plan.fastQCap) q3[p3] = (unsigned short)((ty << 8) | tx);
+            else *reinterpret_cast<volatile int*>(buf.errFlag) = 1;  // cannot happen by the arithmetic of fastQCap; never write past the queue
             if (s >= iniTh) sHasIni[c] = 1;
         }
     };
@@ -564,7 +566,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
                         // which every thread reaches after it has read them above
     }
     // ---- pass 4: per-cell threshold, count, reserve, write ----
-    const int n3 = sQ3;
+    const int n3 = min(sQ3, plan.fastQCap);
     int mine = 0;
     for (int q = threadIdx.x; q < n3; q += FAST_T) {
         const int e = q3[q];
@@ -1183,7 +1185,11 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
     }
     __syncthreads();  // cum and patF (filled below, before the first use after another barrier)
     const int total = min(cum[plan.nlevels], capacity);
-    if (blockIdx.x == 0 && threadIdx.x == 0) outCounts[lframe] = total;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        outCounts[lframe] = total;
+        // a caller's capacity below the frame's keypoint count truncates the output: report it instead of hiding it
+        if (cum[plan.nlevels] > capacity) *reinterpret_cast<volatile int*>(buf.errFlag) = 1;
+    }
 
     // per-lane constants of the orientation pass: row v = lane - 15, columns u = 4k + b - 16
     const int v = lane - 15;
@@ -1361,7 +1367,7 @@ struct orbx_handle {
     static constexpr int PIPE_IN_SLOTS = 4;  // input staging slots of the pipelined host path (H2D runs ahead of the kernels)
     cudaEvent_t evInReady[PIPE_IN_SLOTS] = {}, evInFree[PIPE_IN_SLOTS] = {};
     cudaStream_t stream2 = nullptr, streamBlur2 = nullptr;   // second compute lane of the pipelined host path
-    cudaEvent_t evFork2 = nullptr, evJoin2 = nullptr;
+    cudaEvent_t evFork2 = nullptr, evJoin2 = nullptr, evEntry = nullptr;
     std::vector<cudaEvent_t> evChunkDone;
     int* hErrFlag = nullptr;   // mapped pinned host word written by kernels on candidate overflow
     int* dErrFlag = nullptr;
@@ -1385,7 +1391,16 @@ struct orbx_handle {
     int octKeySmemCap[3] = {0, 0, 0};  // per k_octree variant: 128, 256, 512 threads
     size_t fastSmem = 0;
     size_t octSmem[3] = {0, 0, 0};
-    int lastFrames = 0;
+    int lastFrames = 0;          // frames of the last batch
+    // which frames of the last batch are still in the arena: the pipelined host path keeps only its last two chunks
+    struct Resident { int first, count, arenaFirst; };
+    Resident resident[2] = {{0, 0, 0}, {0, 0, 0}};
+    int arena_frame(int frame) const   // arena index of batch frame `frame`, -1 when it has been overwritten
+    {
+        for (const Resident& r : resident)
+            if (frame >= r.first && frame < r.first + r.count) return r.arenaFirst + (frame - r.first);
+        return -1;
+    }
     int plainRuns = 0;           // batches enqueued without a graph since the plan was (re)built
     bool profiling = false;
     bool useGraph = true;
@@ -1458,11 +1473,18 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
         g.fastGroups = (g.nCols + g.fastG - 1) / g.fastG;
         g.fastOff = fastOff; fastOff += g.nRows * g.fastGroups;
         fastRows = std::max(fastRows, g.hCell + 6);
-        // worst case after the 3x3 NMS: every other pixel of every other row of the evaluated band
+        // worst case after the 3x3 NMS, which runs per cell (neighbours across a cell border both survive): every other pixel
+        // of every other row of each of the band's cells
         fastQ = std::max(fastQ, ((std::min(g.fastG * g.wCell, 124) + 1) / 2 + 1) * ((g.hCell + 1) / 2 + 1));
+        fastQ = std::max(fastQ, g.fastG * ((g.wCell + 1) / 2) * ((g.hCell + 1) / 2));
         g.quota = h->quota[l];
+        // capacity of the level's candidate list = the per-cell NMS worst case summed over the cell grid (the last row and
+        // column of cells are clipped at maxBX - 3 / maxBY - 3)
         const int evalW = g.maxBX - minB - 6, evalH = g.maxBY - minB - 6;
-        g.candCap = ((evalW + 1) / 2 + 1) * ((evalH + 1) / 2 + 1);
+        int capX = 0, capY = 0;
+        for (int j = 0; j < g.nCols; j++) capX += (std::max(0, std::min(g.wCell, evalW - j * g.wCell)) + 1) / 2;
+        for (int i = 0; i < g.nRows; i++) capY += (std::max(0, std::min(g.hCell, evalH - i * g.hCell)) + 1) / 2;
+        g.candCap = std::max(capX * capY, ((evalW + 1) / 2 + 1) * ((evalH + 1) / 2 + 1));
         g.candOff = candOff; candOff += g.candCap;
         g.nodeCap = std::max(g.quota + 3, 4 * g.nIni) + 1;
         g.kpOff = kpOff; kpOff += g.nodeCap;
@@ -1587,11 +1609,30 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
     TabInfo ti;
     int rc = build_plan(h, rows, cols, P, tabs, pyrPerFrame, &ti);
     if (rc != ORBX_OK) return rc;
+    // quad-tree kernel shared memory (validated before the old arenas are released)
+    int nodeCapMax = 0, candCapMax = 0;
+    for (int l = 0; l < P.nlevels; l++) { nodeCapMax = std::max(nodeCapMax, P.lv[l].nodeCap); candCapMax = std::max(candCapMax, P.lv[l].candCap); }
+    nodeCapMax = align_up(nodeCapMax, 8);
+    if (nodeCapMax > 16000) {
+        set_error("per-level feature quota %d exceeds the quad-tree kernel's node capacity", nodeCapMax);
+        return ORBX_ERR_BAD_ARG;
+    }
+    const size_t perNode = 8 + 8 + 4 + 4 + 16 + 4 + 4 + 4 + 4 + 8 + 2 + 2 + 2 + 2 + 2 + 2;
+    const size_t nodeBytes = perNode * nodeCapMax + 16 * 16;
+    int devSmem = 0;
+    ORBX_CUDA_TRY(cudaDeviceGetAttribute(&devSmem, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
+    if (nodeBytes + 1024 > (size_t)devSmem) {
+        set_error("quad-tree node arrays (%zu B) exceed shared memory (%d B)", nodeBytes, devSmem);
+        return ORBX_ERR_BAD_ARG;
+    }
     const int cap = std::max(frames, (h->havePlan && h->plan.rows == rows && h->plan.cols == cols) ? h->frameCap : 0);
     free_arenas(h);
     // layout [level][frame]: level l starts at cap * (sum of planeBytes of lower levels)
     for (int l = 0; l < P.nlevels; l++) P.lv[l].planeOff *= cap;
-    Buffers B = {};
+    // allocate straight into the handle: a failure below leaves the partial set where free_arenas() (next plan / destroy)
+    // releases it, and havePlan stays false
+    Buffers& B = h->buf;
+    B = Buffers{};
     B.frames = cap;
     const size_t pyrBytes = (size_t)pyrPerFrame * cap + 256;
     ORBX_CUDA_TRY(cudaMalloc(&B.pyr, pyrBytes));
@@ -1620,22 +1661,6 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
     B.xw = reinterpret_cast<const short2*>(h->dTabs + ti.nx + 2 * ti.ny);
     B.yw = reinterpret_cast<const short2*>(h->dTabs + ti.nx + 2 * ti.ny + ti.nxw);
     B.yrow = reinterpret_cast<const int4*>(h->dTabs + ti.yrowOff);
-    // quad-tree kernel shared memory
-    int nodeCapMax = 0, candCapMax = 0;
-    for (int l = 0; l < P.nlevels; l++) { nodeCapMax = std::max(nodeCapMax, P.lv[l].nodeCap); candCapMax = std::max(candCapMax, P.lv[l].candCap); }
-    nodeCapMax = align_up(nodeCapMax, 8);
-    if (nodeCapMax > 16000) {
-        set_error("per-level feature quota %d exceeds the quad-tree kernel's node capacity", nodeCapMax);
-        return ORBX_ERR_BAD_ARG;
-    }
-    const size_t perNode = 8 + 8 + 4 + 4 + 16 + 4 + 4 + 4 + 4 + 8 + 2 + 2 + 2 + 2 + 2 + 2;
-    const size_t nodeBytes = perNode * nodeCapMax + 16 * 16;
-    int devSmem = 0;
-    ORBX_CUDA_TRY(cudaDeviceGetAttribute(&devSmem, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
-    if (nodeBytes + 1024 > (size_t)devSmem) {
-        set_error("quad-tree node arrays (%zu B) exceed shared memory (%d B)", nodeBytes, devSmem);
-        return ORBX_ERR_BAD_ARG;
-    }
     // keys in shared memory when they fit in what is left, capped so that 1024 threads' worth of CTAs stay resident per SM
     // (the register file allows about that many at 58 registers per thread)
     h->octNodeCap = nodeCapMax;
@@ -1657,7 +1682,6 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
     ORBX_CUDA_TRY(cudaFuncSetAttribute(k_fast_band, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fastSmem));
     ORBX_CUDA_TRY(cudaMalloc(&h->dKeyNode, sizeof(unsigned short) * (size_t)P.candFrame * cap));
     h->plan = P;
-    h->buf = B;
     h->frameCap = cap;
     h->havePlan = true;
     return ORBX_OK;
@@ -1789,6 +1813,9 @@ namespace orbx {
 int pyramid_view(orbx_handle* h, int frame, PyramidView* out)
 {
     if (!h || !out || !h->havePlan || frame < 0 || frame >= h->lastFrames) { set_error("pyramid_view: nothing extracted / bad frame"); return ORBX_ERR_BAD_ARG; }
+    const int batchFrame = frame;
+    frame = h->arena_frame(batchFrame);
+    if (frame < 0) { set_error("pyramid_view: frame %d of the last batch is no longer resident (pipelined host batch keeps its last two chunks)", batchFrame); return ORBX_ERR_BAD_ARG; }
     out->nlevels = h->cfg.nlevels;
     out->device = h->device;
     for (int l = 0; l < h->cfg.nlevels; l++) {
@@ -1960,6 +1987,7 @@ int orbx_create(const orbx_config* cfg, int device, orbx_handle** out)
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->streamBlur2, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->evFork2, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->evJoin2, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->evEntry, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaHostAlloc((void**)&h->hErrFlag, sizeof(int), cudaHostAllocMapped);
     if (e == cudaSuccess) { *h->hErrFlag = 0; e = cudaHostGetDevicePointer((void**)&h->dErrFlag, h->hErrFlag, 0); }
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->evFork, cudaEventDisableTiming);
@@ -1992,6 +2020,7 @@ void orbx_destroy(orbx_handle* h)
     if (h->streamD2H) cudaStreamDestroy(h->streamD2H);
     for (int i = 0; i < orbx_handle::PIPE_IN_SLOTS; i++) { if (h->evInReady[i]) cudaEventDestroy(h->evInReady[i]); if (h->evInFree[i]) cudaEventDestroy(h->evInFree[i]); }
     for (auto& ev : h->evChunkDone) cudaEventDestroy(ev);
+    if (h->evEntry) cudaEventDestroy(h->evEntry);
     if (h->stream2) { cudaStreamSynchronize(h->stream2); cudaStreamDestroy(h->stream2); }
     if (h->streamBlur2) cudaStreamDestroy(h->streamBlur2);
     if (h->evFork2) cudaEventDestroy(h->evFork2);
@@ -2029,7 +2058,7 @@ int orbx_sync(orbx_handle* h)
     if (!h) { set_error("null handle"); return ORBX_ERR_BAD_ARG; }
     ORBX_CUDA_TRY(cudaSetDevice(h->device));
     ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
-    if (*h->hErrFlag) { *h->hErrFlag = 0; set_error("candidate list overflow on device"); return ORBX_ERR_CAPACITY; }
+    if (*h->hErrFlag) { *h->hErrFlag = 0; set_error("device reported an overflow: candidate list full, or more keypoints than the output capacity"); return ORBX_ERR_CAPACITY; }
     return ORBX_OK;
 }
 
@@ -2046,6 +2075,8 @@ int orbx_extract_batch_device(orbx_handle* h, const uint8_t* d_imgs, int n, int 
     int rc = ensure_plan(h, rows, cols, n);
     if (rc != ORBX_OK) return rc;
     h->lastFrames = n;
+    h->resident[0] = {0, n, 0};
+    h->resident[1] = {0, 0, 0};
     if (h->profiling) {
         rc = enqueue(h, d_imgs, (long long)step, (long long)frame_stride, n, d_kps, d_desc, d_counts, capacity, h->profiling, &h->lastLaunches);
         if (rc != ORBX_OK) return rc;
@@ -2182,7 +2213,8 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
             ORBX_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
             h->evChunkDone.push_back(e);
         }
-        h->lastFrames = chunk;
+        h->lastFrames = n;
+        h->resident[0] = h->resident[1] = {0, 0, 0};
         int launches = 0;
         // ORBX_PIPE_TRACE=1: per-chunk device timeline (ms from the first H2D) on stderr -- a debugging aid
         static const bool trace = std::getenv("ORBX_PIPE_TRACE") != nullptr;
@@ -2194,6 +2226,17 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
             cudaEventRecord(e, st);
             tev.push_back(e);
         };
+        // an error in the middle of the pipeline must not leave copies into the caller's buffers in flight
+        auto drain = [&](int code) {
+            cudaStreamSynchronize(h->streamH2D); cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->stream2);
+            cudaStreamSynchronize(h->streamD2H);
+            return code;
+        };
+        // work a caller enqueued on h->stream (orbx_extract_batch_device is asynchronous) may still use the arena and dIn:
+        // the other three lanes start behind it
+        ORBX_CUDA_TRY(cudaEventRecord(h->evEntry, h->stream));
+        ORBX_CUDA_TRY(cudaStreamWaitEvent(h->streamH2D, h->evEntry, 0));
+        ORBX_CUDA_TRY(cudaStreamWaitEvent(h->stream2, h->evEntry, 0));
         for (int k = 0; k < nchunks; k++) {
             const int f0 = chunkStart[k], nk = chunkStart[k + 1] - f0, b = k & 1;
             // the input staging buffer has more slots than the arena: only k_level0 reads it, so the H2D engine may run
@@ -2202,7 +2245,7 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
             uint8_t* dInB = h->dIn + (size_t)ib * chunk * frameBytes;
             if (k >= orbx_handle::PIPE_IN_SLOTS) ORBX_CUDA_TRY(cudaStreamWaitEvent(h->streamH2D, h->evInFree[ib], 0));
             mark(h->streamH2D);
-            if ((rc = copy_in(h, dInB, imgs + (size_t)f0 * frame_stride, nk, rows, cols, step, frame_stride, h->streamH2D)) != ORBX_OK) return rc;
+            if ((rc = copy_in(h, dInB, imgs + (size_t)f0 * frame_stride, nk, rows, cols, step, frame_stride, h->streamH2D)) != ORBX_OK) return drain(rc);
             ORBX_CUDA_TRY(cudaEventRecord(h->evInReady[ib], h->streamH2D));
             mark(h->streamH2D);
             cudaStream_t cs = b ? h->stream2 : h->stream;  // chunk k computes in arena slot b on compute lane b
@@ -2211,8 +2254,9 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
             int nl = 0;
             rc = launch_cached(h, dInB, (long long)cols, (long long)frameBytes, nk, dKps + (size_t)f0 * devCap,
                                dDesc + (size_t)f0 * devCap * 32, dCounts + f0, devCap, &nl, b, b * chunk);
-            if (rc != ORBX_OK) return rc;
+            if (rc != ORBX_OK) return drain(rc);
             launches += nl;
+            h->resident[b] = {f0, nk, b * chunk};
             ORBX_CUDA_TRY(cudaEventRecord(h->evInFree[ib], cs));
             mark(cs);
             ORBX_CUDA_TRY(cudaStreamWaitEvent(h->streamD2H, h->evInFree[ib], 0));
@@ -2249,7 +2293,7 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int rows, int
         ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
         ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream2));
     }
-    if (*h->hErrFlag) { set_error("candidate list overflow on device"); return ORBX_ERR_CAPACITY; }
+    if (*h->hErrFlag) { set_error("device reported an overflow: candidate list full, or more keypoints than the output capacity"); return ORBX_ERR_CAPACITY; }
     return ORBX_OK;
 }
 
@@ -2272,6 +2316,14 @@ int orbx_get_pyramid_level(orbx_handle* h, int frame, int level, uint8_t* dst, s
     if (!h || !h->havePlan || !dst || level < 0 || level >= h->cfg.nlevels || frame < 0 || frame >= h->lastFrames) {
         set_error("orbx_get_pyramid_level: bad argument");
         return ORBX_ERR_BAD_ARG;
+    }
+    {
+        const int batchFrame = frame;
+        frame = h->arena_frame(batchFrame);
+        if (frame < 0) {
+            set_error("orbx_get_pyramid_level: frame %d of the last batch is no longer resident (a pipelined host batch keeps its last two chunks)", batchFrame);
+            return ORBX_ERR_BAD_ARG;
+        }
     }
     const LevelGeom& g = h->plan.lv[level];
     if (dst_step < (size_t)(g.w + 2 * EDGE)) { set_error("dst_step too small"); return ORBX_ERR_CAPACITY; }
@@ -2316,6 +2368,14 @@ int orbx_debug_get_candidates(orbx_handle* h, int frame, int level, int* xyr, in
         set_error("orbx_debug_get_candidates: bad argument");
         return ORBX_ERR_BAD_ARG;
     }
+    {
+        const int batchFrame = frame;
+        frame = h->arena_frame(batchFrame);
+        if (frame < 0) {
+            set_error("orbx_debug_get_candidates: frame %d of the last batch is no longer resident (a pipelined host batch keeps its last two chunks)", batchFrame);
+            return ORBX_ERR_BAD_ARG;
+        }
+    }
     ORBX_CUDA_TRY(cudaSetDevice(h->device));
     ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
     int m = 0;
@@ -2339,6 +2399,14 @@ int orbx_debug_get_blurred(orbx_handle* h, int frame, int level, uint8_t* dst)
     if (!h || !h->havePlan || !dst || level < 0 || level >= h->cfg.nlevels || frame < 0 || frame >= h->lastFrames) {
         set_error("orbx_debug_get_blurred: bad argument");
         return ORBX_ERR_BAD_ARG;
+    }
+    {
+        const int batchFrame = frame;
+        frame = h->arena_frame(batchFrame);
+        if (frame < 0) {
+            set_error("orbx_debug_get_blurred: frame %d of the last batch is no longer resident (a pipelined host batch keeps its last two chunks)", batchFrame);
+            return ORBX_ERR_BAD_ARG;
+        }
     }
     const LevelGeom& g = h->plan.lv[level];
     ORBX_CUDA_TRY(cudaSetDevice(h->device));

@@ -309,7 +309,12 @@ __global__ void __launch_bounds__(1024) k_assign_grid(const float* __restrict__ 
 // rank in every peer's buffer (one 64-bit store each: payload and "ready" flag travel in the same word, so no fence or
 // separate signal is needed), then spin on the `world` slots of the query in the local buffer until they carry the
 // current epoch and merge them in the same deterministic way as k_merge_partials.  Slots alternate between two sets by
-// epoch parity: a peer may already be writing call k+1 while this rank still reads call k.  The grid is one CTA per SM
+// epoch parity: a peer may already be writing call k+1 while this rank still reads call k.
+// The 14-bit tag wraps every 16384 calls and nq may differ from call to call, so a slot that recent calls did not use
+// (query index >= their nq) could still carry a tag that becomes current again.  Every publish therefore also rewrites a
+// rotating window of BFX scrub slots of its set with (current tag, empty triple): each slot of a set is rewritten at
+// least once per 2048 calls of that parity, so the tag found in a slot is never more than 4096 epochs old and cannot
+// alias the current one (slots below nq carry the real triple of this call instead).  The grid is one CTA per SM
 // (persistent, always co-resident), the spin is bounded by a cycle budget and reports a timeout instead of hanging.
 // ------------------------------------------------------------------------------------------------------
 constexpr int BFX_MAX_WORLD = 16;
@@ -320,7 +325,7 @@ __global__ void __launch_bounds__(256) k_merge_exchange(const int32_t* __restric
                                                         const __grid_constant__ BfxPeers peers, int rank, int world, uint32_t epoch,
                                                         long long spinBudget, int* __restrict__ timeoutFlag,
                                                         int32_t* __restrict__ oBest, int32_t* __restrict__ oIdx,
-                                                        int32_t* __restrict__ oSecond, int phases)
+                                                        int32_t* __restrict__ oSecond, int phases, int scrubFirst, int scrubCount)
 {
     // phases: 1 = publish (merge the chunk partials, store to the peers), 2 = collect (wait, merge, write the result),
     // 3 = both (the normal, fused call)
@@ -328,6 +333,16 @@ __global__ void __launch_bounds__(256) k_merge_exchange(const int32_t* __restric
     const int warpsTotal = gridDim.x * (blockDim.x >> 5);
     const unsigned long long ep = (unsigned long long)(epoch & 0x3fffu);
     const size_t setOff = (size_t)(epoch & 1u) * world * nqMax;
+    if ((phases & 1) && ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) == warpsTotal - 1 && lane < world) {
+        // tag scrub (see above): unused slots of this call's set get the current tag with an empty triple
+        const unsigned long long empty = (ep << 50) | (256ull << 41) | (256ull << 32) | 0xffffffffull;
+        for (int k = 0; k < scrubCount; k++) {
+            int sl = scrubFirst + k;
+            if (sl >= nqMax) sl -= nqMax;
+            if (sl >= nq)
+                asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(peers.p[lane] + setOff + (size_t)rank * nqMax + sl), "l"(empty) : "memory");
+        }
+    }
     for (int qi = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; qi < nq; qi += warpsTotal) {
         BfTriple acc = {256, -1, 256};
         if (phases & 1) {
@@ -1838,13 +1853,27 @@ static int sharded_impl(orbm_context* m, const uint8_t* q, int nq, const uint8_t
     ORBX_CUDA_TRY(cudaHostGetDevicePointer(&dTimeout, m->xchgTimeout, 0));
     static const long long budget = [] { const char* e = std::getenv("ORBX_EXCHANGE_SPIN_CYCLES"); return e ? std::atoll(e) : 20000000000LL; }();
     const int grid = std::max(1, std::min(m->numSMs, (nq + 7) / 8));
+    // tag scrub window of this call: W slots starting at (calls of this parity so far) * W, so that a set's nq_max slots
+    // are covered once per <= 2048 calls of its parity (the tag wraps after 8192 of them)
+    const int scrubW = std::min(m->nqMax, (m->nqMax + 2047) / 2048);
+    const int scrubFirst = (int)(((unsigned long long)(m->epoch >> 1) * (unsigned)scrubW) % (unsigned)m->nqMax);
     k_merge_exchange<<<grid, 256, 0, m->stream>>>(pBest, pIdx, pSecond, nChunks, nq, m->nqMax, peers, m->rank, m->world, m->epoch, budget,
-                                                  dTimeout, best, best_idx, second, phases);
+                                                  dTimeout, best, best_idx, second, phases, scrubFirst, pub ? scrubW : 0);
     ORBX_CUDA_TRY(cudaGetLastError());
     return ORBX_OK;
 }
 
 int orbm_exchange_timed_out(orbm_context* m) { return m && m->xchgTimeout ? *m->xchgTimeout : 0; }
+
+int orbm_debug_exchange_snapshot(orbm_context* m, uint64_t* words, size_t nwords, uint32_t* epoch)
+{
+    if (!m || !m->xchg || !words || nwords * 8 > m->xchgBytes) { set_error("orbm_debug_exchange_snapshot: bad argument"); return ORBX_ERR_BAD_ARG; }
+    ORBX_CUDA_TRY(cudaSetDevice(m->device));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    ORBX_CUDA_TRY(cudaMemcpy(words, m->xchg, nwords * 8, cudaMemcpyDeviceToHost));
+    if (epoch) *epoch = m->epoch;
+    return ORBX_OK;
+}
 
 int orbm_search_window(orbm_context* m, const orbm_frame_view* f, const float* f_angle, const orbm_window_query_view* q,
                        int max_dist, int ratio_mode, float nnratio, int check_orientation, int32_t* out_match, int* nmatches)

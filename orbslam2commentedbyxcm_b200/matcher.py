@@ -215,6 +215,13 @@ class ORBmatcher:
     def exchange_timed_out(self):
         return bool(self._L.orbm_exchange_timed_out(self._m))
 
+    def debug_exchange_snapshot(self, world, nq_max):
+        """(slot words [2, world, nq_max] uint64, searches published so far) of this rank's exchange buffer (test hook)."""
+        words = np.zeros((2, world, nq_max), np.uint64)
+        ep = C.c_uint32()
+        check(self._L.orbm_debug_exchange_snapshot(self._m, words.ctypes.data, words.size, C.byref(ep)), "orbm_debug_exchange_snapshot")
+        return words, ep.value
+
     # ---- SearchByProjection(Frame&, vector<MapPoint*>&, th) ----
     def SearchByProjection(self, frame, mps, th=3.0):
         keep = []

@@ -318,3 +318,84 @@ def test_pinned_outputs_and_chunked_pipeline(gpu, oracle_mod):
                 assert counts[i] == len(ok), (pinned, rep, i)
                 assert kps[i, : counts[i]].tobytes() == ok.tobytes() and np.array_equal(desc[i, : counts[i]], od), (pinned, rep, i)
     ex.close()
+
+
+def test_getters_after_pipelined_batch_track_resident_frames(gpu, oracle_mod):
+    """a host batch of more than 48 frames is pipelined through two arena slots; the pyramid / debug
+    getters must translate batch frame -> arena frame for the chunks still resident and refuse the others."""
+    shape, cfg = (120, 160), (300, 1.2, 4, 20, 7)
+    n = 64
+    frames = np.stack([synth.gen_frame(shape, 100 + s) for s in range(n)])
+    ex = gpu.ORBextractor(*cfg)
+    ex.extract_batch(frames)
+    resident, gone = [], []
+    for f in range(n):
+        try:
+            lvl = ex.pyramid_level_padded(1, frame=f)
+        except gpu.OrbxError as e:
+            assert "no longer resident" in str(e)
+            gone.append(f)
+            continue
+        resident.append(f)
+        o = oracle_mod.Extractor(*cfg)
+        o.extract(frames[f])
+        assert np.array_equal(lvl, o.pyramid(1)), "pyramid of batch frame %d" % f
+        ob = o.blurred(1)
+        if ob is not None:
+            assert np.array_equal(ex.debug_blurred(1, frame=f), ob), "blurred plane of batch frame %d" % f
+        assert np.array_equal(_sorted_rows(ex.debug_candidates(1, frame=f)), _sorted_rows(o.candidates(1)))
+    # chunk schedule 8, 24, 32: the last two chunks are frames 8..63
+    assert resident == list(range(8, 64)) and gone == list(range(8))
+    with pytest.raises(gpu.OrbxError):
+        ex.pyramid_level_padded(0, frame=n)
+    # a small batch afterwards: everything resident again
+    ex.extract_batch(frames[:5])
+    for f in range(5):
+        o = oracle_mod.Extractor(*cfg)
+        o.extract(frames[f])
+        assert np.array_equal(ex.pyramid_level_padded(0, frame=f), o.pyramid(0))
+    ex.close()
+
+
+def test_checkerboard_of_corners_fits_the_candidate_lists(gpu, oracle_mod):
+    """the 3x3 NMS runs per cell, so the candidate capacity is the per-cell bound summed over the grid.
+    Dense isolated corners (a bright dot every other pixel of every other row) must not overflow it."""
+    shape = (240, 320)
+    img = np.full(shape, 40, np.uint8)
+    img[::2, ::2] = 220
+    cfg = (1000, 1.2, 4, 20, 7)
+    o = oracle_mod.Extractor(*cfg)
+    okps, odesc = o.extract(img)
+    ex = gpu.ORBextractor(*cfg)
+    kps, desc = ex(img)
+    assert len(kps) == len(okps)
+    assert np.array_equal(desc, odesc)
+    for l in range(cfg[2]):
+        assert np.array_equal(_sorted_rows(ex.debug_candidates(l)), _sorted_rows(o.candidates(l))), "candidates level %d" % l
+    ex.close()
+
+
+def test_device_api_reports_truncation(gpu):
+    """the device entry point accepts a capacity below orbx_max_keypoints(); a frame with more keypoints
+    is cut to it and the next orbx_sync() says so."""
+    import torch
+
+    shape, cfg = synth.SHAPES["tum"], synth.PRESETS["tum"]
+    img = synth.gen_frame(shape, 3)
+    ex = gpu.ORBextractor(*cfg)
+    full, _ = ex(img)
+    assert len(full) > 200
+    dev = torch.device("cuda", 0)
+    d_img = torch.from_numpy(img[None].copy()).to(dev)
+    cap = 200
+    d_kps = torch.zeros((1, cap, 6), dtype=torch.float32, device=dev)
+    d_desc = torch.zeros((1, cap, 32), dtype=torch.uint8, device=dev)
+    d_cnt = torch.zeros(1, dtype=torch.int32, device=dev)
+    ex.extract_batch_device(d_img.data_ptr(), 1, shape[0], shape[1], d_kps.data_ptr(), d_desc.data_ptr(), d_cnt.data_ptr(), cap)
+    with pytest.raises(gpu.OrbxError):
+        ex.sync()
+    assert int(d_cnt.cpu()[0]) == cap
+    got = d_kps[0].cpu().numpy().view(gpu.KP_DTYPE).reshape(cap)
+    assert np.array_equal(got, full[:cap])
+    ex.sync()   # the flag is cleared by the report
+    ex.close()

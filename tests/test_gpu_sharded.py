@@ -157,3 +157,62 @@ def test_sharded_across_gpus_ipc(gpu, oracle_mod):
     ret = mgr.dict()
     mp.spawn(_worker, args=(world, _free_port(), q, db, expect, ret), nprocs=world, join=True)
     assert all(ret.get(r) for r in range(world)), dict(ret)
+
+
+def test_tag_wrap_with_varying_nq(gpu, oracle_mod):
+    """the 14-bit slot tag wraps every 16384 searches and nq may change from call to call.  Drive more
+    than 16384 searches with nq varying between 1 and nq_max over two local contexts and check, across the wrap,
+    (a) the results, and (b) the invariant that makes stale slots harmless: before search e, no slot of set e & 1 already
+    carries tag e & 0x3fff (without the scrub window the slot nq_max - 1, last written 16384 searches earlier, does)."""
+    import torch
+
+    dev = torch.device("cuda:0")
+    world, nq_max, ndb = 2, 48, 512
+    db = synth.gen_descriptors(ndb, seed=31)
+    q, _ = synth.gen_queries(db, nq_max, seed=32)
+    ob, oi, os_ = oracle_mod.bruteforce(q, db, threads=1)
+    ms = [gpu.ORBmatcher(0.6, True, device=0) for _ in range(world)]
+    ptrs = [m.exchange_create(world, r, nq_max)[1] for r, m in enumerate(ms)]
+    for m in ms:
+        m.exchange_connect_local(ptrs)
+    dq = torch.from_numpy(q).to(dev)
+    ddb = torch.from_numpy(db).to(dev)
+    bounds = [sharding.db_shard(ndb, r, world) for r in range(world)]
+    outs = [[torch.empty(nq_max, dtype=torch.int32, device=dev) for _ in range(3)] for _ in range(world)]
+
+    def search(nq):
+        for phase in (1, 2):
+            for r in range(world):
+                lo, hi = bounds[r]
+                ms[r].bruteforce_sharded_device(dq.data_ptr(), nq, ddb.data_ptr() + 32 * lo, hi - lo, lo,
+                                                *[t.data_ptr() for t in outs[r]], phases=phase)
+
+    def check_invariant():
+        for m in ms:
+            words, done = m.debug_exchange_snapshot(world, nq_max)
+            nxt = done + 1
+            tags = (words[nxt & 1] >> np.uint64(50)).astype(np.int64)
+            assert not np.any(tags == (nxt & 0x3fff)), "a slot already carries the tag of search %d" % nxt
+
+    def check_result(nq):
+        torch.cuda.synchronize()
+        for r in range(world):
+            assert not ms[r].exchange_timed_out()
+            b, i, s = (t.cpu().numpy()[:nq] for t in outs[r])
+            assert np.array_equal(b, ob[:nq]) and np.array_equal(i, oi[:nq]) and np.array_equal(s, os_[:nq])
+
+    total = 2 * 16384 + 40
+    probe = {1, 2, 3, 4, 16383, 16384, 16385, 16386, 16387, 2 * 16384, 2 * 16384 + 1, 2 * 16384 + 2, 2 * 16384 + 3}
+    for e in range(1, total + 1):
+        # full-width searches at 1, 2 and exactly one and two wraps later; tiny ones in between (with a few odd sizes)
+        if e in (1, 2, 16385, 16386, 2 * 16384 + 1, 2 * 16384 + 2):
+            nq = nq_max
+        else:
+            nq = 1 + (e * 7) % 5
+        if e in probe or e % 4099 == 0:
+            check_invariant()
+        search(nq)
+        if e in probe or e % 4099 == 0:
+            check_result(nq)
+    for m in ms:
+        m.close()
