@@ -383,14 +383,15 @@ def c4_leg(pkg, torch, dev, local, rank, world, barrier):
         ex.extract_batch(big.numpy(), out=bout)
     barrier()
     t0 = time.perf_counter()
-    for _ in range(C4_JOBS):       # the 4096-frame job repeated so that the timed region is >= 0.5 s
+    jobs = C4_JOBS * world         # the 4096-frame job repeated so that the timed region is >= 0.5 s at every N
+    for _ in range(jobs):
         done = 0
         for i in range(ncalls):
             n = min(call, mine - done)
             ex.extract_batch(big.numpy()[:n], out=(bout[0][:n], bout[1][:n], bout[2][:n]))
             done += n
     torch.cuda.synchronize()
-    dt = (time.perf_counter() - t0) / C4_JOBS
+    dt = (time.perf_counter() - t0) / jobs
     barrier()
     kp = float(bout[2][: min(call, mine)].mean())
     ex.close()
@@ -559,6 +560,7 @@ def run_ours(args):
     ps = torch.empty_like(pb)
     mstream = torch.cuda.ExternalStream(m.stream, device=dev)
     b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    m.PrepareDatabase(d_db=ddb.data_ptr(), ndb=per).close()   # first call: module load, tensor-map entry point
     b0.record(mstream)
     prep = m.PrepareDatabase(d_db=ddb.data_ptr(), ndb=per)
     b1.record(mstream)
@@ -711,8 +713,8 @@ def run_ours(args):
         }
         if c4_s:
             line.setdefault("configs", {})["C4_batched_4096x1241x376_2000"] = {
-                "frames_per_s_e2e": 4096 / c4_s, "seconds_for_4096_frames": c4_s, "jobs_timed": C4_JOBS,
-                "timed_region_s": c4_s * C4_JOBS, "frames_per_rank": c4_frames,
+                "frames_per_s_e2e": 4096 / c4_s, "seconds_for_4096_frames": c4_s, "jobs_timed": C4_JOBS * world,
+                "timed_region_s": c4_s * C4_JOBS * world, "frames_per_rank": c4_frames,
                 "keypoints_per_frame": c4_kp, "scaling": "strong (4096 frames sharded by frame over %d rank(s))" % world,
                 "note": "pinned host in / pinned host out through orbx_extract_batch, calls of <= 512 frames (8 distinct seeded "
                         "frames tiled), H2D | kernels | D2H pipelined; max over ranks"}
