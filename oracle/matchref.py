@@ -16,8 +16,21 @@ import tempfile
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_PATH = os.path.join(_HERE, "_ref", "libmatchref.so")
+_PATHS = {"ref": os.path.join(_HERE, "_ref", "libmatchref.so"),     # the reference's ORBmatcher.cc / ORBextractor.cc
+          "gpu": os.path.join(_HERE, "_ref", "libmatchgpu.so")}     # the product's host/ORBmatcher_gpu.cc / ORBextractor.cc instead
+_PATH = _PATHS["ref"]
 _lib = None
+_libs = {}
+
+
+def use(variant):
+    """Select which build of the object-level harness the functions below call: "ref" (default) or "gpu" (the product's C++
+    drop-in layer linked with the reference's own Frame / KeyFrame / MapPoint / Map / DBoW2; needs a CUDA device)."""
+    global _PATH, _lib
+    _PATH = _PATHS[variant]
+    _lib = _libs.get(variant)
+    return available()
+
 
 _vp, _i, _f = C.c_void_p, C.c_int, C.c_float
 
@@ -45,7 +58,7 @@ def lib():
     global _lib
     if _lib is None:
         if not available():
-            raise RuntimeError("oracle/_ref/libmatchref.so is not built (make -C oracle ref; needs /root/reference)")
+            raise RuntimeError("%s is not built (make -C oracle ref; needs /root/reference)" % _PATH)
         L = C.CDLL(_PATH)
         P = C.POINTER
         L.orbr_assign_grid.argtypes = [P(FrameIn), _vp, _vp]
@@ -91,6 +104,7 @@ def lib():
         L.orbr_stereo_get.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
         L.orbr_stereo_free.argtypes = [_vp]
         _lib = L
+        _libs[[k for k, v in _PATHS.items() if v == _PATH][0]] = L
     return _lib
 
 

@@ -35,6 +35,21 @@
 
 using namespace ORB_SLAM2;
 
+#ifdef ORBR_GPU_ADAPTER
+// Built as oracle/_ref/libmatchgpu.so: ORBmatcher and ORBextractor are the PRODUCT's drop-in definitions
+// (orbslam2commentedbyxcm_b200/host/ORBmatcher_gpu.cc, host/ORBextractor.cc over liborbx.so) instead of the reference's
+// src/ORBmatcher.cc / src/ORBextractor.cc; every other class is still the reference's own source.  The entry points below
+// are the same, so one test body drives either library.
+namespace orbx_adapter {
+int ComputeStereoMatches(ORB_SLAM2::ORBextractor* pLeft, ORB_SLAM2::ORBextractor* pRight, const std::vector<cv::KeyPoint>& vKeysLeft,
+                         const cv::Mat& descLeft, const std::vector<cv::KeyPoint>& vKeysRight, const cv::Mat& descRight, float mbf,
+                         float mb, std::vector<float>& vuRight, std::vector<float>& vDepth);
+}
+extern "C" int orbr_is_gpu_adapter() { return 1; }
+#else
+extern "C" int orbr_is_gpu_adapter() { return 0; }
+#endif
+
 // src/Converter.cc:29-40 restated: one 1 x 32 row per descriptor
 std::vector<cv::Mat> Converter::toDescriptorVector(const cv::Mat& Descriptors)
 {
@@ -684,6 +699,12 @@ void* orbr_stereo_frame(const uint8_t* left, const uint8_t* right, int rows, int
     const float mb = mbf / fx;
     std::memcpy((char*)mem + offsetof(Frame, mb), &mb, sizeof(float));
     o->F = new (mem) Frame(imL, imR, 0.0, o->exL, o->exR, nullptr, K, D, mbf, 40.f * mb);
+#ifdef ORBR_GPU_ADAPTER
+    // the constructor above ran the reference's CPU ComputeStereoMatches on the pyramids the adapter extractor downloaded;
+    // replace its result by the body replacement INTEGRATION.md gives for src/Frame.cc:673-885
+    orbx_adapter::ComputeStereoMatches(o->exL, o->exR, o->F->mvKeys, o->F->mDescriptors, o->F->mvKeysRight, o->F->mDescriptorsRight,
+                                       o->F->mbf, o->F->mb, o->F->mvuRight, o->F->mvDepth);
+#endif
     return o;
 }
 int orbr_stereo_n(void* p, int right) { StereoOut* o = (StereoOut*)p; return right ? (int)o->F->mvKeysRight.size() : o->F->N; }
