@@ -1,9 +1,12 @@
 // oracle/match_oracle.cc -- TEST INFRASTRUCTURE (CPU oracle). Never linked into / called by the product path.
 //
-// Flat-array restatements of the reference's Hamming-matching loops.  ORBmatcher.cc cannot be compiled
-// here (it drags in Frame/KeyFrame/MapPoint/DBoW2/g2o/Eigen), so these follow the reference line by line
-// over plain arrays; parity for them is pinned only by construction + self-consistency ("parity
-// unpinned" by any reference-side test -- the reference has none).
+// Flat-array restatements of the reference's Hamming-matching loops (plain arrays in, plain arrays out, so the CUDA path
+// and the oracle can be compared on the same seeded inputs at any size).  PINNED against the reference's own code:
+// oracle/Makefile `ref` compiles src/ORBmatcher.cc, Frame.cc, KeyFrame.cc, MapPoint.cc, Map.cc, KeyFrameDatabase.cc and the
+// vendored DBoW2 UNMODIFIED against the mini-cv shim (oracle/_ref/libmatchref.so, harness oracle/matchref_wrap.cc), and
+// tests/test_oracle_matcher.py requires every function below to return what the reference's member function did to real
+// Frame / KeyFrame / MapPoint objects built from the same arrays; tests/golden/matcher_ref.npz freezes those outputs for
+// the GPU box (tests/test_gpu_matcher_ref.py, tests/test_gpu_adapter_objects.py).
 //
 //   orbo_descriptor_distance   <- ORBmatcher::DescriptorDistance            src/ORBmatcher.cc:1983-2003
 //   orbo_bruteforce            <- sequential best/second scan with that distance (north_star config 5)

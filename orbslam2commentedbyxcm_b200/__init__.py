@@ -3,7 +3,8 @@
 Hand-written CUDA kernels behind a C-ABI (include/orbx.h, built into liborbx.so) with host-side mirrors of the
 reference's ORBextractor / ORBmatcher interfaces:
 
-  C++ : host/ORBextractor.h, host/ORBmatcher.h   (drop-in classes for Frame / Tracking / LocalMapping)
+  C++ : host/ORBextractor.{h,cc} (drop-in class, replaces include/ORBextractor.h + src/ORBextractor.cc) and
+        host/ORBmatcher_gpu.cc (every member of the reference's own include/ORBmatcher.h, replaces src/ORBmatcher.cc)
   Py  : extractor.ORBextractor, matcher.ORBmatcher (used by tests/ and bench.py)
 
 There is no CPU fallback: compute entry points raise OrbxError when liborbx.so or a CUDA device is missing.

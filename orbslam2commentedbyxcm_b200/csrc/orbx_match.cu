@@ -1366,7 +1366,8 @@ struct orbm_db {
     int ndb = 0;
     long long rowsPad = 0;
     int8_t* exp = nullptr;
-    CUtensorMap map;
+    CUtensorMap map;      // stages of 256 rows (k_bruteforce_tc)
+    CUtensorMap map128;   // stages of 128 rows per CTA (k_bruteforce_tc2, CTA pairs)
 };
 
 namespace {
@@ -1374,8 +1375,13 @@ namespace {
 // chunk partials of one prepared database into m->partials, same layout as bruteforce_partials
 int bruteforce_partials_tc(orbm_context* m, const orbm_db* d, const uint8_t* dq, int nq, int idxOffset, int* nChunksOut)
 {
-    const int qTiles = (nq + tc::BM - 1) / tc::BM;
-    const long long nqPad = (long long)qTiles * tc::BM;
+    // default: one CTA per (128 queries, chunk).  ORBX_TC_PAIR=1 selects the CTA-pair kernel (cta_group::2, 256 queries per
+    // pair; measured slower on B200, see orbx_match_tc.cuh) when there is more than one query tile.
+    const char* pairEnv = std::getenv("ORBX_TC_PAIR");
+    const bool pair = pairEnv && std::atoi(pairEnv) != 0 && nq > tc::BM;
+    const int rowsPerTile = pair ? 2 * tc::BM : tc::BM;
+    const int qTiles = (nq + rowsPerTile - 1) / rowsPerTile;
+    const long long nqPad = (long long)qTiles * rowsPerTile;
     if ((size_t)nqPad * 256 > m->qExpBytes) {
         ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
         cudaFree(m->qExp); m->qExp = nullptr; m->qExpBytes = 0;
@@ -1386,8 +1392,9 @@ int bruteforce_partials_tc(orbm_context* m, const orbm_db* d, const uint8_t* dq,
     CUtensorMap mapA;
     int rc = tc::make_map(&mapA, m->qExp, nqPad, tc::BM);
     if (rc != ORBX_OK) return rc;
-    // one CTA per SM: (query tiles) x (database chunks); chunks are multiples of the 256-row tile
-    const int target = std::max(1, m->numSMs / qTiles);
+    // one CTA (or CTA pair) per SM (TPC): (query tiles) x (database chunks); chunks are multiples of the 256-row tile
+    const int units = pair ? m->numSMs / 2 : m->numSMs;
+    const int target = std::max(1, units / qTiles);
     long long chunk = (d->ndb + target - 1) / target;
     chunk = std::max<long long>(tc::BN, (chunk + tc::BN - 1) / tc::BN * tc::BN);
     chunk = std::min<long long>(chunk, 1 << 21);
@@ -1401,10 +1408,15 @@ int bruteforce_partials_tc(orbm_context* m, const orbm_db* d, const uint8_t* dq,
     static bool attr = false;
     if (!attr) {
         ORBX_CUDA_TRY(cudaFuncSetAttribute(tc::k_bruteforce_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+        ORBX_CUDA_TRY(cudaFuncSetAttribute(tc::k_bruteforce_tc2, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM2_BYTES));
         attr = true;
     }
-    tc::k_bruteforce_tc<<<dim3(nChunks, qTiles), tc::THREADS, tc::SMEM_BYTES, m->stream>>>(mapA, d->map, nq, d->ndb, (int)chunk, idxOffset,
-                                                                                       pBest, pIdx, pSecond);
+    if (pair)
+        tc::k_bruteforce_tc2<<<dim3(2 * nChunks, qTiles), tc::THREADS2, tc::SMEM2_BYTES, m->stream>>>(mapA, d->map128, nq, d->ndb, (int)chunk,
+                                                                                                 idxOffset, pBest, pIdx, pSecond);
+    else
+        tc::k_bruteforce_tc<<<dim3(nChunks, qTiles), tc::THREADS, tc::SMEM_BYTES, m->stream>>>(mapA, d->map, nq, d->ndb, (int)chunk, idxOffset,
+                                                                                           pBest, pIdx, pSecond);
     ORBX_CUDA_TRY(cudaGetLastError());
     *nChunksOut = nChunks;
     return ORBX_OK;
@@ -1581,6 +1593,7 @@ int orbm_db_create(orbm_context* m, const uint8_t* db, int ndb, int mem_kind, or
     if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
     cudaFree(tmp);
     int rc = e == cudaSuccess ? tc::make_map(&d->map, d->exp, d->rowsPad, tc::BN) : ORBX_ERR_CUDA;
+    if (rc == ORBX_OK) rc = tc::make_map(&d->map128, d->exp, d->rowsPad, 128);
     if (e != cudaSuccess) set_error("orbm_db_create: %s", cudaGetErrorString(e));
     if (rc != ORBX_OK) { cudaFree(d->exp); delete d; return rc; }
     *out = d;

@@ -82,3 +82,18 @@ def test_bruteforce_tc_full_size_equals_integer_pipe_kernel(gpu):
     got = np.unpackbits(np.bitwise_xor(q, db[idx]), axis=1).sum(1)
     assert np.array_equal(got, best) and (idx == pick).mean() > 0.99
     prep.close(); m.close()
+
+
+@pytest.mark.parametrize("nq,ndb", [(2000, 20000), (129, 257), (300, 130), (1025, 7777)])
+def test_bruteforce_tc_cta_pair_variant(gpu, oracle_mod, nq, ndb, monkeypatch):
+    """k_bruteforce_tc2 (cta_group::2: a CTA pair multiplies 256 queries x 256 rows as one UMMA of M = 256, each CTA loading half
+    of every database stage) returns the same triples; selected by ORBX_TC_PAIR=1 (measured slower than the default kernel)."""
+    monkeypatch.setenv("ORBX_TC_PAIR", "1")
+    db = synth.gen_descriptors(ndb, seed=ndb)
+    q, _ = synth.gen_queries(db, nq, seed=nq)
+    m = gpu.ORBmatcher()
+    prep = m.PrepareDatabase(db)
+    b, i, s = m.BruteForceTC(q, prep, idx_offset=11)
+    ob, oi, os_ = oracle_mod.bruteforce(q, db, threads=8)
+    assert np.array_equal(b, ob) and np.array_equal(i, oi + 11) and np.array_equal(s, os_)
+    prep.close(); m.close()
