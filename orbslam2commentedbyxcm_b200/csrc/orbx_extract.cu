@@ -13,6 +13,7 @@
 #include "orbx_common.cuh"
 #include "sincosf_dev.cuh"
 #include "orbx_internal.h"
+#include <cuda.h>   // CUtensorMap (the encoder is fetched through cudaGetDriverEntryPoint: no link against libcuda)
 #include <cmath>
 #include <cfloat>
 #include <cstdarg>
@@ -327,6 +328,20 @@ constexpr int FAST_GIT = 2;       // row sweeps (4 rows each, 4 px x 32 lanes pe
 static_assert(FAST_T == 128, "k_fast_band hard-codes 4 warps (queue quarters, sweeps of 4 rows)");
 
 __device__ __forceinline__ uint32_t swap16(uint32_t v) { return __byte_perm(v, 0, 0x1032); }
+// a | b | c and a & b & c as ONE LOP3 each (opaque to the optimiser, which otherwise re-associates the shared terms of the two
+// thresholds of pass 1 into more instructions)
+__device__ __forceinline__ uint32_t or3(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0xFE;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ uint32_t and3(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0x80;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
 
 // exact arc measure M(p) = max over 9-arcs of max(min d, min -d), d_k = I(p) - I(ring_k).  The differences are kept as
 // biased u16x2 pairs (d_k + 0x8000, d_{k+8} + 0x8000): one 32-bit subtraction makes both (no borrow can cross the
@@ -364,11 +379,25 @@ __device__ __forceinline__ int fast_measure_packed(const uint8_t* p)
     return max(A, -B);
 }
 
-__global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
+// Band staging, two variants of the same kernel (identical tile contents wherever the kernel reads them):
+//   TMA = true   one elected thread issues ONE cp.async.bulk.tensor.3d (box FAST_P bytes x (hCell + 6) rows x 1 frame of the
+//                level's [frame][row][byte] tensor map, completion on an mbarrier).  Default when nlevels <= FAST_TMA_LEVELS.
+//   TMA = false  16-byte cp.async copies issued by every thread (16 lanes per row).  ORBX_FAST_TMA=0 selects it (and it
+//                serves more than FAST_TMA_LEVELS levels).
+// Both start at the 16-byte aligned column at or left of the band (the tile is shifted by the band's misalignment): cp.async
+// needs it, and a TMA box whose innermost coordinate is off the 16-byte grid faults (tools/microbench/tma_probe.cu).
+constexpr int FAST_TMA_LEVELS = 8;
+struct FastMaps { CUtensorMap m[FAST_TMA_LEVELS]; };
+
+template <bool TMA>
+__global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf, const __grid_constant__ FastMaps maps)
 {
-    extern __shared__ __align__(16) unsigned char fsm[];
+    extern __shared__ __align__(128) unsigned char fsm[];
+    __shared__ __align__(8) unsigned long long sBar;
     __shared__ int sQ1[2], sQ3, sCnt, sBase, sPos;  // sQ1: one survivor counter per phase (no reset barrier between them)
-    __shared__ int sHasIni[FAST_MAXG], sSeg[FAST_T / 32];
+    __shared__ __align__(4) unsigned char sHasIni[FAST_MAXG];  // byte c = cell c kept a corner >= iniTh (read as one word)
+    __shared__ int sSeg[FAST_T / 32];
+    static_assert(FAST_MAXG == 4, "sHasIni is read as one 32-bit word");
 
     const int frame = blockIdx.y + buf.frameBase;
     const int4 fuw = __ldg(reinterpret_cast<const int4*>(buf.fastUnits) + blockIdx.x);
@@ -382,9 +411,21 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
     unsigned short* q1 = reinterpret_cast<unsigned short*>(fsm + 2 * plan.fastTileBytes);  // FAST_Q1CAP entries
     unsigned short* q3 = q1 + FAST_Q1CAP;                                                   // plan.fastQCap entries
 
-    // stage the band with 16-byte asynchronous copies (16 lanes per row, 8 rows per pass), zero the score tile
-    const int shift = (PAD_LEFT + iniX) & 15;
-    {
+    // stage the band (TMA: one bulk tensor copy; otherwise 16-byte asynchronous copies, 16 lanes per row, 8 rows per pass),
+    // zero the score tile meanwhile
+    const int shift = (PAD_LEFT + iniX) & 15;  // both variants copy from a 16-byte aligned column (TMA: a coordinate off that grid is an illegal instruction)
+    if (TMA) {
+        if (threadIdx.x == 0) {
+            const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&sBar);
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)((g.hCell + 6) * FAST_P)) : "memory");
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                         ::"r"((uint32_t)__cvta_generic_to_shared(tile)), "l"(&maps.m[level]), "r"(bar), "r"(PAD_LEFT + iniX - shift),
+                           "r"(PAD_TOP + iniY), "r"(frame)
+                         : "memory");
+        }
+    } else {
         const int nw16 = (shift + bw + 15) >> 4;  // <= 10
         const int c16 = threadIdx.x & 15, r0 = threadIdx.x >> 4;
         if (c16 < nw16) {
@@ -402,56 +443,80 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
         uint4* z = reinterpret_cast<uint4*>(sc) + threadIdx.x;
         for (int n = rh * (FAST_P / 16) - threadIdx.x; n > 0; n -= FAST_T, z += FAST_T) *z = make_uint4(0, 0, 0, 0);
     }
-    if (threadIdx.x < FAST_MAXG) sHasIni[threadIdx.x] = 0;
-    if (threadIdx.x == 0) { sQ1[0] = 0; sQ1[1] = 0; sQ3 = 0; sCnt = 0; sPos = 0; }
-    asm volatile("cp.async.wait_all;" ::: "memory");
+    if (threadIdx.x == 0) { *reinterpret_cast<uint32_t*>(sHasIni) = 0u; sQ1[0] = 0; sQ1[1] = 0; sQ3 = 0; sCnt = 0; sPos = 0; }
+    if (!TMA) asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
+    if (TMA) {  // (the barrier above orders the mbarrier's initialisation before these waits)
+        const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&sBar);
+        uint32_t done;
+        do {
+            asm volatile(
+                "{\n\t.reg .pred p;\n\t"
+                "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                "selp.u32 %0, 1, 0, p;\n\t}"
+                : "=r"(done)
+                : "r"(bar), "r"(0u)
+                : "memory");
+        } while (!done);
+    }
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int minTh = plan.minTh, iniTh = plan.iniTh;
     const int wCell = g.wCell;
     const int txFirst = shift + 3, txEnd = shift + 3 + evalW;  // evaluated tile columns [txFirst, txEnd)
-    const int gw = (txFirst >> 2) + lane;                        // ((txEnd-1)>>2) - (txFirst>>2) + 1 <= 32 words
+    const int gw0 = txFirst >> 2, gw = gw0 + lane;                      // ((txEnd-1)>>2) - (txFirst>>2) + 1 <= 32 words
     const int ncells = 1 + (evalW - 1 >= wCell) + (evalW - 1 >= 2 * wCell) + (evalW - 1 >= 3 * wCell);  // = min(4, (evalW-1)/wCell + 1), no division
     constexpr int FAST_RPW = (59 + FAST_T / 32 - 1) / (FAST_T / 32);  // sweeps: eh <= 59
     static_assert(FAST_RPW <= 16, "survivor nibbles must fit 64 bits");
-    // queue entry = tile row << 8 | tile column; bit b of sweep `it` is pixel (warp + 3 + 4 * it, 4 * gw + (b & 3))
-    const uint32_t e0 = ((uint32_t)(warp + 3) << 8) | (uint32_t)(4 * gw);
+    // Survivor masks: sweep `it` (rows warp + 3 + 4 * it) owns nibble 7 - it of the low word (it < 8) or nibble 15 - it of the
+    // high word; bit b of the nibble is pixel column 4 * gw + b.  Pass-1 queue entry = thread << 6 | code, code = bit index
+    // (+ 32 for the low word), so it = 15 - (code >> 2): one constant addition per entry on the divergent producer side,
+    // decoded by the dense consumer.
+    const uint32_t e0 = (uint32_t)threadIdx.x << 6;
     auto push = [&](uint32_t m, uint32_t ebase, int base) {
+        unsigned short* qp = q1 + base;
         while (m) {
-            const int bit = __ffs(m) - 1;
-            m &= m - 1;
-            q1[base++] = (unsigned short)(ebase + (((uint32_t)bit >> 2) * ((FAST_T / 32) << 8)) + (bit & 3));
+            uint32_t bit;
+            asm("bfind.u32 %0, %1;" : "=r"(bit) : "r"(m));  // position of the highest set bit (one FLO)
+            m ^= 1u << bit;
+            *qp++ = (unsigned short)(ebase + bit);
         }
     };
     // ---- pass 1: SWAR rejection, 4 pixels per lane, at both thresholds; the survivors of a lane's rows are kept as 4-bit
-    //      groups of a 60-bit mask per threshold (sweep `it` = rows warp + 4 * it) ----
+    //      groups of a 60-bit mask per threshold, shifted in from below (one funnel shift per sweep and threshold) ----
     uint32_t iniLo = 0, iniHi = 0, minLo = 0, minHi = 0;
     {
         const uint32_t Ki = (uint32_t)(0x7f - min(iniTh, 0x7f)) * 0x01010101u, Km = (uint32_t)(0x7f - min(minTh, 0x7f)) * 0x01010101u;
-        const bool filterIni = iniTh < 0x80, filterMin = minTh < 0x80;
+        // (a threshold >= 127 gives K = 0: the test degrades to |d| >= 128, still necessary for |d| > threshold)
         uint32_t vmask = 0;  // bytes of this word that are evaluated pixels
 #pragma unroll
         for (int bb = 0; bb < 4; bb++)
             if (4 * gw + bb >= txFirst && 4 * gw + bb < txEnd) vmask |= 0x80u << (8 * bb);
         const uint32_t* rowp = reinterpret_cast<const uint32_t*>(tile) + (warp + 3) * FAST_P4 + gw;
+        const int nIt = (eh - warp + FAST_T / 32 - 1) / (FAST_T / 32);  // sweeps of this warp (warp-uniform, <= FAST_RPW; <= 0: none)
 #pragma unroll
         for (int it = 0; it < FAST_RPW; it++) {
-            if (warp + it * (FAST_T / 32) >= eh) break;  // warp-uniform
+            if (it >= nIt) break;  // warp-uniform
             const uint32_t* cp = rowp + it * (FAST_T / 32) * FAST_P4;
             const uint32_t C = cp[0], Lw = cp[-1], Rw = cp[1], N = cp[-3 * FAST_P4], S = cp[3 * FAST_P4];
             const uint32_t W4 = __byte_perm(Lw, C, 0x4321);  // pixels x-3 .. x
             const uint32_t E4 = __byte_perm(C, Rw, 0x6543);  // pixels x+3 .. x+6
             const uint32_t an = __vabsdiffu4(C, N), as = __vabsdiffu4(C, S), aw = __vabsdiffu4(C, W4), ae = __vabsdiffu4(C, E4);
             const uint32_t ln = an & 0x7f7f7f7fu, ls = as & 0x7f7f7f7fu, lw = aw & 0x7f7f7f7fu, le = ae & 0x7f7f7f7fu;
+            uint32_t ns7, we7;  // bit 7 of a byte: one of the two differences is >= 128 (above any threshold < 128)
+            asm("lop3.b32 %0, %1, %2, 0, 0xFC;" : "=r"(ns7) : "r"(an), "r"(as));
+            asm("lop3.b32 %0, %1, %2, 0, 0xFC;" : "=r"(we7) : "r"(aw), "r"(ae));
             // bit 7 of each byte: |d| > threshold
-            uint32_t mi = vmask, mm = vmask;
-            if (filterIni) mi = (((ln + Ki) | an) | ((ls + Ki) | as)) & (((lw + Ki) | aw) | ((le + Ki) | ae)) & vmask;
-            if (filterMin) mm = (((ln + Km) | an) | ((ls + Km) | as)) & (((lw + Km) | aw) | ((le + Km) | ae)) & vmask;
-            const uint32_t ni = (mi * 0x00204081u) >> 28, nm = (mm * 0x00204081u) >> 28;  // bits 7, 15, 23, 31 -> 0..3
-            if (it < 8) { iniLo |= ni << (4 * it); minLo |= nm << (4 * it); }
-            else { iniHi |= ni << (4 * (it - 8)); minHi |= nm << (4 * (it - 8)); }
+            const uint32_t mi = and3(or3(ln + Ki, ls + Ki, ns7), or3(lw + Ki, le + Ki, we7), vmask);
+            const uint32_t mm = and3(or3(ln + Km, ls + Km, ns7), or3(lw + Km, le + Km, we7), vmask);
+            const uint32_t pi = mi * 0x00204081u, pm = mm * 0x00204081u;  // bits 7, 15, 23, 31 -> the top nibble
+            if (it < 8) { iniLo = __funnelshift_l(pi, iniLo, 4); minLo = __funnelshift_l(pm, minLo, 4); }
+            else { iniHi = __funnelshift_l(pi, iniHi, 4); minHi = __funnelshift_l(pm, minHi, 4); }
         }
+        // canonical positions: sweep 0 at the top nibble of the low word, sweep 8 at the top nibble of the high word
+        const int padLo = 4 * max(8 - max(nIt, 0), 0), padHi = 4 * min(16 - max(nIt, 8), 8);
+        iniLo = padLo < 32 ? iniLo << padLo : 0u; minLo = padLo < 32 ? minLo << padLo : 0u;
+        iniHi = padHi < 32 ? iniHi << padHi : 0u; minHi = padHi < 32 ? minHi << padHi : 0u;
     }
     // Two phases, as the reference calls cv::FAST twice: phase 0 scores the corners at iniTh (NMS among them is exact: a
     // kept pixel beats every neighbour below iniTh anyway); phase 1 repeats passes 2 and 3 at minTh for the cells that kept
@@ -477,8 +542,8 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
         if (cnt) {
             const int base = atomicAdd(&sQ1[phase], cnt);
             if (base + cnt <= FAST_Q1CAP) {
-                push(mlo, e0, base);
-                push(mhi, e0 + ((8u * (FAST_T / 32)) << 8), base + __popc(mlo));
+                push(mlo, e0 + 32u, base);
+                push(mhi, e0, base + __popc(mlo));
             }
         }
     }
@@ -494,13 +559,14 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
         for (int q0 = wbase; q0 < wend; q0 += 32) {
             const int q = q0 + lane;
             const int e = q < wend ? q1[q] : 0;
-            const int idx = (e >> 8) * FAST_P + (e & 0xff);
+            const int ty = (e >> 11) + 63 - 4 * ((e >> 2) & 15), tx = 4 * (gw0 + ((e >> 6) & 31)) + (e & 3);
+            const int idx = ty * FAST_P + tx;
             int mval = 0;
             if (q < wend) mval = fast_measure_packed(tile + idx);
             const bool corner = mval > th;
             if (corner) sc[idx] = (uint8_t)(mval - 1);
             const uint32_t bal = __ballot_sync(0xffffffffu, corner);
-            if (corner) q1[wbase + cnt + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)e;
+            if (corner) q1[wbase + cnt + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)((ty << 8) | tx);
             cnt += __popc(bal);
         }
         if (lane == 0) sSeg[warp] = cnt;
@@ -510,13 +576,14 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
             __syncthreads();
             if (threadIdx.x == 0) sQ1[phase] = 0;
             __syncthreads();
-            const uint32_t m = ((it0 < 8 ? mlo >> (4 * it0) : mhi >> (4 * (it0 - 8)))) & ((1u << (4 * FAST_GIT)) - 1u);
-            if (m) push(m, e0 + (((uint32_t)it0 * (FAST_T / 32)) << 8), atomicAdd(&sQ1[phase], __popc(m)));
+            static_assert(FAST_GIT == 2, "a round = the two nibbles of sweeps it0 (even), it0 + 1");
+            const uint32_t m = it0 < 8 ? mlo & (0xffu << (4 * (6 - it0))) : mhi & (0xffu << (4 * (14 - it0)));
+            if (m) push(m, e0 + (it0 < 8 ? 32u : 0u), atomicAdd(&sQ1[phase], __popc(m)));
             __syncthreads();
             const int n = sQ1[phase];
             for (int q = threadIdx.x; q < n; q += FAST_T) {
                 const int e = q1[q];
-                const int idx = (e >> 8) * FAST_P + (e & 0xff);
+                const int idx = ((e >> 11) + 63 - 4 * ((e >> 2) & 15)) * FAST_P + 4 * (gw0 + ((e >> 6) & 31)) + (e & 3);
                 const int mval = fast_measure_packed(tile + idx);
                 if (mval > th) sc[idx] = (uint8_t)(mval - 1);
             }
@@ -560,8 +627,8 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf)
     }
     __syncthreads();
     if (phase || minTh >= iniTh) break;  // (a retry at minTh >= iniTh can only find a subset of nothing)
-    retry = 0;
-    for (int c = 0; c < ncells; c++) retry |= (sHasIni[c] ? 0u : 1u) << c;
+    // bytes 0/1 of the cells -> bits 0..3 (no two partial products share a bit below bit 28)
+    retry = ~((*reinterpret_cast<const uint32_t*>(sHasIni) * 0x01020408u) >> 24) & ((1u << ncells) - 1u);
     if (!retry) break;  // CTA-uniform.  No barrier here: phase 1 writes q1 / sSeg / sHasIni only after its own barriers,
                         // which every thread reaches after it has read them above
     }
@@ -1390,6 +1457,8 @@ struct orbx_handle {
     int octNodeCap = 0;
     int octKeySmemCap[3] = {0, 0, 0};  // per k_octree variant: 128, 256, 512 threads
     size_t fastSmem = 0;
+    FastMaps fastMaps = {};      // per-level tensor maps of the pyramid arena (k_fast_band<true>)
+    bool fastTma = false;
     size_t octSmem[3] = {0, 0, 0};
     int lastFrames = 0;          // frames of the last batch
     // which frames of the last batch are still in the arena: the pipelined host path keeps only its last two chunks
@@ -1679,7 +1748,34 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
     ORBX_CUDA_TRY(cudaFuncSetAttribute(k_octree<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->octSmem[1]));
     ORBX_CUDA_TRY(cudaFuncSetAttribute(k_octree<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->octSmem[2]));
     h->fastSmem = 2 * (size_t)P.fastTileBytes + 2 * ((size_t)FAST_Q1CAP + (size_t)P.fastQCap);
-    ORBX_CUDA_TRY(cudaFuncSetAttribute(k_fast_band, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fastSmem));
+    ORBX_CUDA_TRY(cudaFuncSetAttribute(k_fast_band<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fastSmem));
+    ORBX_CUDA_TRY(cudaFuncSetAttribute(k_fast_band<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fastSmem));
+    // tensor maps for the TMA-staged FAST bands: level l of the pyramid arena as a [frame][row][byte] tensor, box = FAST_P
+    // bytes x (hCell + 6) rows x 1 frame, no swizzle, out-of-range bytes read as zero
+    static const bool tmaOff = [] { const char* e = std::getenv("ORBX_FAST_TMA"); return e && std::atoi(e) == 0; }();
+    h->fastTma = false;
+    if (!tmaOff && P.nlevels <= FAST_TMA_LEVELS) {
+        typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                     const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+        void* fp = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fp, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess && fp) {
+            bool ok = true;
+            for (int l = 0; l < P.nlevels && ok; l++) {
+                const LevelGeom& g = P.lv[l];
+                const cuuint64_t gdim[3] = {(cuuint64_t)g.pitch, (cuuint64_t)g.planeRows, (cuuint64_t)cap};
+                const cuuint64_t gstride[2] = {(cuuint64_t)g.pitch, (cuuint64_t)g.planeBytes};
+                const cuuint32_t box[3] = {(cuuint32_t)FAST_P, (cuuint32_t)(g.hCell + 6), 1};
+                const cuuint32_t estr[3] = {1, 1, 1};
+                ok = g.hCell + 6 <= 256 &&
+                     ((EncodeFn)fp)(&h->fastMaps.m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, B.pyr + g.planeOff, gdim, gstride, box, estr,
+                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+            }
+            h->fastTma = ok;
+        }
+    }
     ORBX_CUDA_TRY(cudaMalloc(&h->dKeyNode, sizeof(unsigned short) * (size_t)P.candFrame * cap));
     h->plan = P;
     h->frameCap = cap;
@@ -1700,6 +1796,17 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
     cudaStream_t s = slot ? h->stream2 : h->stream, sb = profile ? s : (slot ? h->streamBlur2 : h->streamBlur);
     cudaEvent_t evFork = slot ? h->evFork2 : h->evFork, evJoin = slot ? h->evJoin2 : h->evJoin;
     int nl = 0;
+    // ORBX_DEBUG_SYNC=1 (never during capture: use with the graph disabled): synchronise after every launch and name the
+    // kernel that failed
+    static const bool dbgSync = [] { const char* e = std::getenv("ORBX_DEBUG_SYNC"); return e && std::atoi(e) != 0; }();
+#define ORBX_DBG_SYNC(name)                                                                                   \
+    do {                                                                                                      \
+        if (dbgSync) {                                                                                        \
+            cudaError_t _e = cudaStreamSynchronize(s);                                                        \
+            if (_e == cudaSuccess) _e = cudaStreamSynchronize(sb);                                            \
+            if (_e != cudaSuccess) { set_error("%s failed: %s", name, cudaGetErrorString(_e)); return ORBX_ERR_CUDA; } \
+        }                                                                                                     \
+    } while (0)
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_PYRAMID], s));
     {
         const LevelGeom& g = P.lv[0];
@@ -1717,6 +1824,7 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
         else k_resize<<<grid, 128, 0, s>>>(P, B, l, rpt);
         nl++;
     }
+    ORBX_DBG_SYNC("pyramid kernels");
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_FAST], s));
     // The blur runs on its own branch of the graph.  A few frames: beside FAST (both grids fit the GPU at once, lowest
     // latency).  Batches: beside the quad-tree, whose barrier-bound CTAs leave most issue slots free (measured +2 % per
@@ -1726,8 +1834,10 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
         ORBX_CUDA_TRY(cudaEventRecord(evFork, s));
         ORBX_CUDA_TRY(cudaStreamWaitEvent(sb, evFork, 0));
     }
-    k_fast_band<<<dim3(P.totalFastUnits, n), FAST_T, h->fastSmem, s>>>(P, B);
+    if (h->fastTma) k_fast_band<true><<<dim3(P.totalFastUnits, n), FAST_T, h->fastSmem, s>>>(P, B, h->fastMaps);
+    else k_fast_band<false><<<dim3(P.totalFastUnits, n), FAST_T, h->fastSmem, s>>>(P, B, h->fastMaps);
     nl++;
+    ORBX_DBG_SYNC(h->fastTma ? "k_fast_band<TMA>" : "k_fast_band<cp.async>");
     if (!profile && blurAfterFast) {
         ORBX_CUDA_TRY(cudaEventRecord(evFork, s));
         ORBX_CUDA_TRY(cudaStreamWaitEvent(sb, evFork, 0));
