@@ -63,6 +63,8 @@ struct LevelGeom {
     int patchSize;       // (int)(31 * scale)
     int xTab, yTab;      // offsets into the resize coefficient tables
     int resizeWords;     // 1: k_resize_words applies (4-column groups read within 8 source columns)
+    int resizeRows;      // 1: k_resize_rows applies too (every destination row reads source rows r0, r0 + 1, r0 strictly increasing)
+    int sTab;            // offset of this level in the source-row table (k_resize_rows)
 };
 
 struct Plan {
@@ -105,6 +107,8 @@ struct Buffers {
     const short* yofs1;
     const short2* yw;
     const int4* yrow;    // k_resize_words row table: {r0 * srcPitch, r1 * srcPitch, b0 | b1 << 16, mirrored frame rows as deltas}
+    const int2* srow;    // k_resize_rows table, per SOURCE row r: {b0 | b1 << 16 of the destination row whose lower source row is r
+                         // (0: none), mirrored frame rows of that destination row as deltas}
     const FastUnit* fastUnits;  // [totalFastUnits]
     int* errFlag;        // device-side overflow flag
     int frames;
@@ -293,6 +297,105 @@ __global__ void __launch_bounds__(128) k_resize_words(Plan plan, Buffers buf, in
         }
         Dp += dpitch;
     }
+}
+
+// K1b, source-row walk (default for the pyramid's scale factors, 1 < f <= 2: LevelGeom::resizeRows): the same arithmetic as
+// k_resize_words, but a thread walks the SOURCE rows its destination rows read and interpolates each of them horizontally
+// ONCE -- at scale 1.2 five destination rows read six source rows, which k_resize_words interpolates ten times.  Source row r
+// is the lower row (r1) of at most one destination row; the per-source-row table says which weights that row has (0 = none:
+// warp-uniform branch) and where the REFLECT_101 frame repeats it.  The three source words of the next row are loaded before
+// the current row is processed (two register sets alternating by name; addresses are sequential, one pitch apart).
+template <bool DUP>
+__device__ __forceinline__ void resize_rows_walk(const uint8_t* __restrict__ S, uint8_t* __restrict__ D, const int2* __restrict__ srow,
+                                                 uint32_t soff, uint32_t doff, int n, const uint32_t spitch, const uint32_t dpitch,
+                                                 const uint32_t (&a)[4], const uint32_t (&sel)[4], const uint32_t sh)
+{
+    // S / D are CTA-uniform plane bases, soff / doff the thread's 32-bit byte offsets (uniform base + 32-bit offset addressing)
+    auto load3 = [&](uint32_t off, uint32_t* w) {
+        const uint32_t* R = reinterpret_cast<const uint32_t*>(S + off);
+        w[0] = __ldg(R); w[1] = __ldg(R + 1); w[2] = __ldg(R + 2);
+    };
+    auto hpass = [&](const uint32_t* w, uint32_t* t) {  // T >> 4 of the thread's 4 columns
+        const uint32_t u0 = __funnelshift_r(w[0], w[1], sh), u1 = __funnelshift_r(w[1], w[2], sh);
+#pragma unroll
+        for (int j = 0; j < 4; j++) t[j] = __dp2a_lo(a[j], __byte_perm(u0, u1, sel[j]), 0u) >> 4;
+    };
+    auto emit = [&](const uint32_t* t0, const uint32_t* t1, int2 e) {  // vertical pass (see k_resize_words) + stores
+        const uint32_t b0 = (uint32_t)e.x & 0xffffu, b1 = (uint32_t)e.x >> 16;
+        uint32_t o[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) o[j] = __dp2a_lo(__byte_perm(b0 * t0[j], b1 * t1[j], 0x7632), 0x4040u, 128u);
+        const uint32_t v = __byte_perm(__byte_perm(o[0], o[1], 0x0051), __byte_perm(o[2], o[3], 0x0051), 0x5410);
+        *reinterpret_cast<uint32_t*>(D + doff) = v;
+        if (DUP && e.y) {  // this row is also a row of the REFLECT_101 frame (above and / or below the interior)
+            const int up = (short)(e.y & 0xffff), down = e.y >> 16;
+            if (up) *reinterpret_cast<uint32_t*>(D + (doff + (uint32_t)(up * (int)dpitch))) = v;
+            if (down) *reinterpret_cast<uint32_t*>(D + (doff + (uint32_t)(down * (int)dpitch))) = v;
+        }
+        doff += dpitch;
+    };
+    // (one row below the last one is read ahead and never used: the first row of the lower frame at worst, inside the plane)
+    uint32_t wa[3], wb[3], ta[4], tb[4];
+    load3(soff, wa);
+    load3(soff + spitch, wb);
+    soff += 2 * spitch;
+    hpass(wa, ta);
+    while (n > 0) {  // n = source rows still to process (the first one is only the upper row of the first destination row)
+        load3(soff, wa);
+        hpass(wb, tb);
+        {
+            const int2 e = __ldg(srow + 1);
+            if (e.x) emit(ta, tb, e);
+        }
+        if (n == 1) break;
+        load3(soff + spitch, wb);
+        hpass(wa, ta);
+        {
+            const int2 e = __ldg(srow + 2);
+            if (e.x) emit(tb, ta, e);
+        }
+        soff += 2 * spitch;
+        srow += 2;
+        n -= 2;
+    }
+}
+
+__global__ void __launch_bounds__(128) k_resize_rows(Plan plan, Buffers buf, int level, int rowsPerThread, int spitchArg, int dpitchArg)
+{
+    const LevelGeom& g = plan.lv[level];
+    const LevelGeom& gp = plan.lv[level - 1];
+    const int bx = 4 * (blockIdx.x * 32 + (threadIdx.x & 31));  // pitch is a multiple of 128: always inside the row
+    const int frame = blockIdx.z + buf.frameBase;
+    const int dy0 = (blockIdx.y * 4 + (threadIdx.x >> 5)) * rowsPerThread;
+    if (dy0 >= g.h) return;
+    const int dy1 = min(dy0 + rowsPerThread, g.h);
+    int sx[4], sx1[4];
+    uint32_t a[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        int dx = min(max(bx + j - PAD_LEFT, -EDGE), g.w - 1 + EDGE);
+        dx = reflect101(dx, g.w);
+        sx[j] = buf.xofs[g.xTab + dx];
+        sx1[j] = min(sx[j] + 1, gp.w - 1);
+        const short2 w = buf.xw[g.xTab + dx];
+        a[j] = (uint32_t)(unsigned short)w.x | ((uint32_t)(unsigned short)w.y << 16);
+    }
+    const int base = min(min(sx[0], sx[1]), min(sx[2], sx[3]));
+    uint32_t sel[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) sel[j] = (uint32_t)(sx[j] - base) | ((uint32_t)(sx1[j] - base) << 4);
+    const uint32_t colOff = (uint32_t)(PAD_LEFT + base) & ~3u, sh = 8u * ((uint32_t)(PAD_LEFT + base) & 3u);
+    const uint32_t spitch = (uint32_t)spitchArg, dpitch = (uint32_t)dpitchArg;  // = gp.pitch, g.pitch (kernel arguments: constant-bank operands)
+    const int rFirst = buf.yofs0[g.yTab + dy0], rLast = buf.yofs1[g.yTab + dy1 - 1];  // source rows rFirst .. rLast
+    const uint8_t* S = plane_ptr(buf.pyr, gp, frame);
+    uint8_t* D = plane_ptr(buf.pyr, g, frame);
+    const uint32_t soff = (uint32_t)(PAD_TOP + rFirst) * spitch + colOff, doff = (uint32_t)(PAD_TOP + dy0) * dpitch + bx;
+    const int2* srow = buf.srow + g.sTab + rFirst;
+    // destination rows 1..19 and h-20..h-2 are repeated in the REFLECT_101 frame: only the threads that own such rows
+    // (warp-uniform) run the walk with the extra stores
+    const bool dup = dy0 <= EDGE || dy1 - 1 >= g.h - 1 - EDGE;
+    if (dup) resize_rows_walk<true>(S, D, srow, soff, doff, rLast - rFirst, spitch, dpitch, a, sel, sh);
+    else resize_rows_walk<false>(S, D, srow, soff, doff, rLast - rFirst, spitch, dpitch, a, sel, sh);
 }
 
 // ------------------------------------------------------------------------------------------------------
@@ -1496,7 +1599,7 @@ static void free_arenas(orbx_handle* h)
 }
 
 // Level geometry, cell grids, capacities, resize tables for one image shape.
-struct TabInfo { long long nx, ny, nxw, nyw, yrowOff; std::vector<FastUnit> units; };  // padded lengths of xofs / yofs and true lengths of the weight arrays
+struct TabInfo { long long nx, ny, nxw, nyw, yrowOff, srowOff; std::vector<FastUnit> units; };  // padded lengths of xofs / yofs and true lengths of the weight arrays
 
 static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<short>& tabs, long long& pyrBytesPerFrame,
                       TabInfo* ti = nullptr)
@@ -1509,6 +1612,7 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
     // tables: per level >= 1: xofs[w], xw[2w], yofs0[h], yofs1[h], yw[2h] -- stored in 5 separate arrays
     std::vector<short> xofs, xw, y0v, y1v, yw;
     std::vector<int> yrow;  // 4 ints per destination row, indexed like y0v
+    std::vector<int> srow;  // 2 ints per SOURCE row of every level >= 1's source level (k_resize_rows)
     for (int l = 0; l < c.nlevels; l++) {
         LevelGeom& g = P.lv[l];
         g.w = cv_round_f((float)cols * h->invScale[l]);
@@ -1560,6 +1664,7 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
         g.scale = h->scale[l];
         g.patchSize = (int)(31 * h->scale[l]);
         g.xTab = (int)xofs.size(); g.yTab = (int)y0v.size();
+        g.resizeWords = 0; g.resizeRows = 0; g.sTab = 0;
         if (l > 0) {
             const LevelGeom& gp = P.lv[l - 1];
             // cv::resize INTER_LINEAR coefficient tables (see oracle/cvprim.h: linear_coeffs)
@@ -1575,6 +1680,10 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
                     xw.push_back(sat_short((1.f - f) * 2048)); xw.push_back(sat_short(f * 2048));
                 }
             }
+            g.sTab = (int)(srow.size() / 2);
+            g.resizeRows = 1;
+            srow.resize(srow.size() + 2 * (size_t)gp.h, 0);
+            int prevR0 = -1;
             {
                 double scale = 1.0 / ((double)g.h / gp.h);
                 for (int d = 0; d < g.h; d++) {
@@ -1592,6 +1701,11 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
                     if (d >= g.h - 1 - EDGE && d <= g.h - 2) dup |= (2 * (g.h - 1 - d)) << 16;
                     yrow.push_back(clip(s) * gp.pitch); yrow.push_back(clip(s + 1) * gp.pitch);
                     yrow.push_back((int)((uint32_t)(unsigned short)wb0 | ((uint32_t)(unsigned short)wb1 << 16))); yrow.push_back(dup);
+                    // source-row walk: r1 = r0 + 1 with r0 strictly increasing makes r1 the lower row of exactly this destination row
+                    if (clip(s + 1) != clip(s) + 1 || clip(s) <= prevR0 || wb0 < 0 || wb1 < 0) g.resizeRows = 0;
+                    prevR0 = clip(s);
+                    srow[2 * ((size_t)g.sTab + clip(s + 1))] = (int)((uint32_t)(unsigned short)wb0 | ((uint32_t)(unsigned short)wb1 << 16));
+                    srow[2 * ((size_t)g.sTab + clip(s + 1)) + 1] = dup;
                 }
             }
             // k_resize_words eligibility: every aligned group of 4 buffer columns (frame columns map to the reflected
@@ -1631,6 +1745,11 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
         const short* yr = reinterpret_cast<const short*>(yrow.data());
         tabs.insert(tabs.end(), yr, yr + 2 * yrow.size());
     }
+    const long long srowOff = (long long)tabs.size();  // 16-byte aligned: the int4 table before it is
+    {
+        const short* sr = reinterpret_cast<const short*>(srow.data());
+        tabs.insert(tabs.end(), sr, sr + 2 * srow.size());
+    }
     std::vector<FastUnit> units;
     for (int l = 0; l < c.nlevels; l++) {
         const LevelGeom& g = P.lv[l];
@@ -1651,7 +1770,7 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
     }
     P.totalFastUnits = (int)units.size();
     if (ti) {
-        ti->nx = (long long)xofs.size(); ti->ny = (long long)y0v.size(); ti->nxw = (long long)xw.size(); ti->nyw = (long long)yw.size(); ti->yrowOff = yrowOff;
+        ti->nx = (long long)xofs.size(); ti->ny = (long long)y0v.size(); ti->nxw = (long long)xw.size(); ti->nyw = (long long)yw.size(); ti->yrowOff = yrowOff; ti->srowOff = srowOff;
         ti->units.swap(units);
     }
     P.pyrFrameStride = pyrBytesPerFrame;
@@ -1730,6 +1849,7 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
     B.xw = reinterpret_cast<const short2*>(h->dTabs + ti.nx + 2 * ti.ny);
     B.yw = reinterpret_cast<const short2*>(h->dTabs + ti.nx + 2 * ti.ny + ti.nxw);
     B.yrow = reinterpret_cast<const int4*>(h->dTabs + ti.yrowOff);
+    B.srow = reinterpret_cast<const int2*>(h->dTabs + ti.srowOff);
     // keys in shared memory when they fit in what is left, capped so that 1024 threads' worth of CTAs stay resident per SM
     // (the register file allows about that many at 58 registers per thread)
     h->octNodeCap = nodeCapMax;
@@ -1820,7 +1940,9 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
         int rpt = 16;
         while (rpt > 4 && (long long)(g.pitch / 4) * ((g.h + rpt - 1) / rpt) * n < 148LL * 2048) rpt >>= 1;
         dim3 grid(g.pitch / 128, (g.h + 4 * rpt - 1) / (4 * rpt), n);
-        if (g.resizeWords) k_resize_words<<<grid, 128, 0, s>>>(P, B, l, rpt);
+        static const bool rowsOff = [] { const char* e = std::getenv("ORBX_RESIZE_ROWS"); return e && std::atoi(e) == 0; }();  // A/B switch
+        if (g.resizeWords && g.resizeRows && !rowsOff) k_resize_rows<<<grid, 128, 0, s>>>(P, B, l, rpt, P.lv[l - 1].pitch, g.pitch);
+        else if (g.resizeWords) k_resize_words<<<grid, 128, 0, s>>>(P, B, l, rpt);
         else k_resize<<<grid, 128, 0, s>>>(P, B, l, rpt);
         nl++;
     }
