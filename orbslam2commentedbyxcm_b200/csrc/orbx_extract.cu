@@ -572,9 +572,9 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf, co
     constexpr int FAST_RPW = (59 + FAST_T / 32 - 1) / (FAST_T / 32);  // sweeps: eh <= 59
     static_assert(FAST_RPW <= 16, "survivor nibbles must fit 64 bits");
     // Survivor masks: sweep `it` (rows warp + 3 + 4 * it) owns nibble 7 - it of the low word (it < 8) or nibble 15 - it of the
-    // high word; bit b of the nibble is pixel column 4 * gw + b.  Pass-1 queue entry = thread << 6 | code, code = bit index
-    // (+ 32 for the low word), so it = 15 - (code >> 2): one constant addition per entry on the divergent producer side,
-    // decoded by the dense consumer.
+    // high word; bit b of the nibble is pixel column 4 * gw + b.  Pass-1 queue entry = (expanding) thread << 6 | code, code =
+    // bit index (+ 32 for the low word), so it = 15 - (code >> 2): one constant addition per entry on the divergent producer
+    // side, decoded by the dense consumer (the column's lane = expanding lane - 8 * (code >> 4), see the quarter hand-over).
     const uint32_t e0 = (uint32_t)threadIdx.x << 6;
     auto push = [&](uint32_t m, uint32_t ebase, int base) {
         unsigned short* qp = q1 + base;
@@ -640,6 +640,16 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf, co
         mlo = minLo & (nibOK * 0x11111111u);
         mhi = minHi & (nibOK * 0x11111111u);
     }
+    // Survivors cluster (a vertical edge puts a survivor in every sweep of ONE lane), and the expansion loop below runs as long
+    // as the busiest lane of the warp: the four 16-bit quarters of a lane's mask are handed to the lanes +0, +8, +16, +24, so a
+    // column's survivors are expanded by four lanes.  Quarter q = code >> 4 of processing lane P came from lane P - 8 q.
+    {
+        const uint32_t h8 = __shfl_sync(0xffffffffu, mhi, (lane - 8) & 31);
+        const uint32_t l16 = __shfl_sync(0xffffffffu, mlo, (lane - 16) & 31);
+        const uint32_t l24 = __shfl_sync(0xffffffffu, mlo, (lane - 24) & 31);
+        mhi = (mhi & 0x0000ffffu) | (h8 & 0xffff0000u);
+        mlo = (l16 & 0x0000ffffu) | (l24 & 0xffff0000u);
+    }
     {
         const int cnt = __popc(mlo) + __popc(mhi);
         if (cnt) {
@@ -662,7 +672,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf, co
         for (int q0 = wbase; q0 < wend; q0 += 32) {
             const int q = q0 + lane;
             const int e = q < wend ? q1[q] : 0;
-            const int ty = (e >> 11) + 63 - 4 * ((e >> 2) & 15), tx = 4 * (gw0 + ((e >> 6) & 31)) + (e & 3);
+            const int ty = (e >> 11) + 63 - 4 * ((e >> 2) & 15), tx = 4 * (gw0 + ((((e >> 6) & 31) - ((e >> 1) & 24)) & 31)) + (e & 3);
             const int idx = ty * FAST_P + tx;
             int mval = 0;
             if (q < wend) mval = fast_measure_packed(tile + idx);
@@ -686,7 +696,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf, co
             const int n = sQ1[phase];
             for (int q = threadIdx.x; q < n; q += FAST_T) {
                 const int e = q1[q];
-                const int idx = ((e >> 11) + 63 - 4 * ((e >> 2) & 15)) * FAST_P + 4 * (gw0 + ((e >> 6) & 31)) + (e & 3);
+                const int idx = ((e >> 11) + 63 - 4 * ((e >> 2) & 15)) * FAST_P + 4 * (gw0 + ((((e >> 6) & 31) - ((e >> 1) & 24)) & 31)) + (e & 3);
                 const int mval = fast_measure_packed(tile + idx);
                 if (mval > th) sc[idx] = (uint8_t)(mval - 1);
             }
