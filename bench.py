@@ -36,7 +36,9 @@ CONFIG = {"workload": WORKLOAD_NAME, "parallelism": "frames sharded by rank, no 
           "l2": "inputs larger than L2: every pass streams a frame buffer + pyramid of more than 126 MB"}
 BATCH = 256       # frames per GPU per pass (one device buffer, larger than L2 with its pyramid)
 INNER = 32        # passes per step: a step is INNER x BATCH frames per GPU, so 20 steps time >= 0.5 s
-E2E_INNER = 16    # host calls (BATCH frames each) per end-to-end step
+E2E_INNER = 8     # host calls (E2E_BATCH frames each) per end-to-end step
+E2E_BATCH = 512   # frames per end-to-end host call (measured sweep, tools/e2e_batch_sweep.py: 256 -> 148 k, 512 -> 160 k,
+                  # >= 1024 -> 122-128 k frames/s: the pipeline's fill / drain amortises, larger pinned buffers copy slower)
 C4_JOBS = 16      # repetitions of the 4096-frame config-4 job inside its timed region
 N_DISTINCT = 32   # distinct synthetic frames (seeds 0..31), tiled to BATCH
 
@@ -508,8 +510,9 @@ def run_ours(args):
     ex.set_profiling(False)
 
     # ---- end to end through the host C-ABI (pinned host input) ----
-    h_imgs = torch.from_numpy(frames).pin_memory()
-    out = ex.alloc_outputs(B, rows, cols, pinned=True)
+    EB = max(B, (args.e2e_batch // B) * B)   # frames per host call: the B-frame buffer tiled
+    h_imgs = torch.from_numpy(np.concatenate([frames] * (EB // B), axis=0) if EB > B else frames).pin_memory()
+    out = ex.alloc_outputs(EB, rows, cols, pinned=True)
     e2e_steps = max(2, args.steps)
     # warm-up: the first ~100 ms of back-to-back host calls run ~30 % slower than the steady state (PCIe link / host side
     # ramping up after the device-resident phase, tools/e2e_nvml_probe.py), so warm up by time, not only by count
@@ -651,7 +654,7 @@ def run_ours(args):
         dom = max(("pyramid", "fast", "octree", "blur", "desc"), key=lambda k: stage_ms.get(k, 0.0))
         frames_step = B * args.inner
         fps = world * frames_step * args.steps / (ms * 1e-3)
-        e2e_fps = world * B * args.e2e_inner * e2e_steps / e2e_s
+        e2e_fps = world * EB * args.e2e_inner * e2e_steps / e2e_s
         d2h = out[0].nbytes + out[1].nbytes + out[2].nbytes
         traffic, traffic_src = measured_traffic(dom, B)
         five = sum(ab[k] for k in ("pyramid", "fast", "blur", "desc"))   # pyramid + FAST + blur + orientation + descriptor
@@ -674,9 +677,9 @@ def run_ours(args):
                 "frames_per_gpu_per_step": frames_step,
                 "l2": "working set per pass (%d MB of frames + pyramid + blurred planes) exceeds the 126 MB L2" %
                       (B * (rows * cols + 2 * 1.2e6) / 1e6)},
-            "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": int(frames.nbytes) * args.e2e_inner,
+            "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": int(h_imgs.numel()) * args.e2e_inner,
                     "d2h_bytes_per_step": int(d2h) * args.e2e_inner, "steps": e2e_steps,
-                    "calls_per_step": args.e2e_inner, "frames_per_call": B, "timed_region_s": e2e_s},
+                    "calls_per_step": args.e2e_inner, "frames_per_call": EB, "timed_region_s": e2e_s},
             "gpu_launches": launches,
             "clocks": clocks,
             "parity_checked": bool(parity and parity["equal"]),
@@ -757,6 +760,7 @@ def main():
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--inner", type=int, default=INNER, help="passes over the device buffer per timed step")
     ap.add_argument("--e2e-inner", type=int, default=E2E_INNER, help="host calls per end-to-end step")
+    ap.add_argument("--e2e-batch", type=int, default=E2E_BATCH, help="frames per end-to-end host call")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the C2 / C3 side measurements")
     args = ap.parse_args()

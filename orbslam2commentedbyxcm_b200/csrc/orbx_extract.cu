@@ -1310,6 +1310,97 @@ __global__ void __launch_bounds__(128) k_blur(Plan plan, Buffers buf)
     }
 }
 
+// K5, TMA-staged variant (default when nlevels <= FAST_TMA_LEVELS; ORBX_BLUR_TMA=0 keeps k_blur): the CTA's source tile --
+// 128 + 2 x 16 columns (the box starts on the 16-byte grid left of the CTA's first column) x 4 x BLUR_ROWS + 8 rows -- arrives
+// through ONE cp.async.bulk.tensor.3d, and the threads run the same arithmetic from shared memory: no per-thread global
+// loads, no source words held two steps ahead in registers (k_blur's top stall was the latency of exactly those loads).
+constexpr int BLUR_TP = 160;                        // tile pitch in bytes = box width
+constexpr int BLUR_TROWS = 4 * BLUR_ROWS + 8;       // rows y - 3 .. y + 4 BLUR_ROWS + 4 (the last one belongs to an unused pair)
+struct BlurMaps { CUtensorMap m[FAST_TMA_LEVELS]; };
+
+__global__ void __launch_bounds__(128) k_blur_tma(Plan plan, Buffers buf, const __grid_constant__ BlurMaps maps)
+{
+    extern __shared__ __align__(128) unsigned char bsm[];
+    __shared__ __align__(8) unsigned long long sBar;
+    int level = 0;
+    while (level + 1 < plan.nlevels && (int)blockIdx.x >= plan.lv[level + 1].blurOff) level++;
+    const LevelGeom& g = plan.lv[level];
+    const int frame = blockIdx.y + buf.frameBase;
+    const int unit = blockIdx.x - g.blurOff;
+    const int cgroups = (g.w + 127) >> 7;  // CTAs across (32 threads x 4 columns)
+    const int cy = unit / cgroups, cxg = unit - cy * cgroups;
+    if (threadIdx.x == 0) {
+        const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&sBar);
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)(BLUR_TROWS * BLUR_TP)) : "memory");
+        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                     ::"r"((uint32_t)__cvta_generic_to_shared(bsm)), "l"(&maps.m[level]), "r"(bar), "r"(PAD_LEFT + 128 * cxg - 16),
+                       "r"(PAD_TOP + 4 * BLUR_ROWS * cy - 3), "r"(frame)
+                     : "memory");
+    }
+    __syncthreads();  // orders the mbarrier's initialisation before the waits
+    {
+        const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&sBar);
+        uint32_t done;
+        do {
+            asm volatile(
+                "{\n\t.reg .pred p;\n\t"
+                "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                "selp.u32 %0, 1, 0, p;\n\t}"
+                : "=r"(done)
+                : "r"(bar), "r"(0u)
+                : "memory");
+        } while (!done);
+    }
+    const int x = 4 * (cxg * 32 + (threadIdx.x & 31));
+    const int y0 = (cy * 4 + (threadIdx.x >> 5)) * BLUR_ROWS;
+    if (x >= g.w || y0 >= g.h) return;
+    const int y1 = min(y0 + BLUR_ROWS, g.h);
+    // tile row 0 = image row 4 BLUR_ROWS cy - 3, tile column 16 = the CTA's first column
+    const uint32_t* sp = reinterpret_cast<const uint32_t*>(bsm + (threadIdx.x >> 5) * BLUR_ROWS * BLUR_TP + 16 + 4 * (threadIdx.x & 31));
+    constexpr int RW = BLUR_TP / 4;  // words per tile row
+    uint8_t* dp = const_cast<uint8_t*>(interior_ptr(buf.blur, g, frame)) + x + (long long)y0 * g.pitch;
+    const long long pitch = g.pitch;
+    uint32_t P[4][4];  // window of 8 rows as 4 vertical pairs per column (see k_blur)
+    auto hpair = [&](const uint32_t* r, uint32_t (&Q)[4]) {  // rows r and r + 1 row
+        uint32_t n0[3] = {r[-1], r[0], r[1]}, n1[3] = {r[RW - 1], r[RW], r[RW + 1]}, ha[4], hb[4];
+        blur_hrow(n0, ha);
+        blur_hrow(n1, hb);
+#pragma unroll
+        for (int j = 0; j < 4; j++) Q[j] = __byte_perm(ha[j], hb[j], 0x5410);
+    };
+    hpair(sp, P[0]); hpair(sp + 2 * RW, P[1]); hpair(sp + 4 * RW, P[2]); hpair(sp + 6 * RW, P[3]);
+    sp += 8 * RW;
+    constexpr uint32_t TA = 0x12002212u, TB = 0x30223830u, TC = 0x30382230u, TD = 0x12220012u;  // vertical tap pairs (see k_blur)
+    auto vout = [&](const uint32_t (&A)[4], const uint32_t (&B)[4], const uint32_t (&C)[4], const uint32_t (&D)[4]) {
+        uint32_t a0[4], a1[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            a0[j] = __dp2a_lo(D[j], TD, __dp2a_lo(C[j], TC, __dp2a_lo(B[j], TB, __dp2a_lo(A[j], TA, 32768u))));
+            a1[j] = __dp2a_hi(D[j], TD, __dp2a_hi(C[j], TC, __dp2a_hi(B[j], TB, __dp2a_hi(A[j], TA, 32768u))));
+        }
+        *reinterpret_cast<uint32_t*>(dp) = __byte_perm(__byte_perm(a0[0], a0[1], 0x0062), __byte_perm(a0[2], a0[3], 0x0062), 0x5410);
+        *reinterpret_cast<uint32_t*>(dp + pitch) = __byte_perm(__byte_perm(a1[0], a1[1], 0x0062), __byte_perm(a1[2], a1[3], 0x0062), 0x5410);
+        dp += 2 * pitch;
+    };
+    for (int y = y0; y < y1; y += 8) {
+        vout(P[0], P[1], P[2], P[3]);
+        if (y + 2 >= y1) break;
+        hpair(sp, P[0]);
+        vout(P[1], P[2], P[3], P[0]);
+        if (y + 4 >= y1) break;
+        hpair(sp + 2 * RW, P[1]);
+        vout(P[2], P[3], P[0], P[1]);
+        if (y + 6 >= y1) break;
+        hpair(sp + 4 * RW, P[2]);
+        vout(P[3], P[0], P[1], P[2]);
+        if (y + 8 >= y1) break;
+        hpair(sp + 6 * RW, P[3]);
+        sp += 8 * RW;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------------
 // K4+K6: orientation (IC_Angle) and steered BRIEF.  One warp per keypoint (a warp loops over several keypoints).
 //   orientation: the 31 rows of the radius-15 disc are staged from the pyramid level into shared memory; lane r owns row
@@ -1572,6 +1663,8 @@ struct orbx_handle {
     size_t fastSmem = 0;
     FastMaps fastMaps = {};      // per-level tensor maps of the pyramid arena (k_fast_band<true>)
     bool fastTma = false;
+    BlurMaps blurMaps = {};      // same tensors, box BLUR_TP x BLUR_TROWS (k_blur_tma)
+    bool blurTma = false;
     size_t octSmem[3] = {0, 0, 0};
     int lastFrames = 0;          // frames of the last batch
     // which frames of the last batch are still in the arena: the pipelined host path keeps only its last two chunks
@@ -1884,6 +1977,7 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
     // bytes x (hCell + 6) rows x 1 frame, no swizzle, out-of-range bytes read as zero
     static const bool tmaOff = [] { const char* e = std::getenv("ORBX_FAST_TMA"); return e && std::atoi(e) == 0; }();
     h->fastTma = false;
+    h->blurTma = false;
     if (!tmaOff && P.nlevels <= FAST_TMA_LEVELS) {
         typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                      const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -1904,6 +1998,20 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
                                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
             }
             h->fastTma = ok;
+            static const bool blurOff = [] { const char* e = std::getenv("ORBX_BLUR_TMA"); return e && std::atoi(e) == 0; }();
+            bool okb = !blurOff;
+            for (int l = 0; l < P.nlevels && okb; l++) {
+                const LevelGeom& g = P.lv[l];
+                const cuuint64_t gdim[3] = {(cuuint64_t)g.pitch, (cuuint64_t)g.planeRows, (cuuint64_t)cap};
+                const cuuint64_t gstride[2] = {(cuuint64_t)g.pitch, (cuuint64_t)g.planeBytes};
+                const cuuint32_t box[3] = {(cuuint32_t)BLUR_TP, (cuuint32_t)BLUR_TROWS, 1};
+                const cuuint32_t estr[3] = {1, 1, 1};
+                okb = ((EncodeFn)fp)(&h->blurMaps.m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, B.pyr + g.planeOff, gdim, gstride, box, estr,
+                                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+            }
+            h->blurTma = okb;
+            if (okb) ORBX_CUDA_TRY(cudaFuncSetAttribute(k_blur_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, BLUR_TROWS * BLUR_TP));
         }
     }
     ORBX_CUDA_TRY(cudaMalloc(&h->dKeyNode, sizeof(unsigned short) * (size_t)P.candFrame * cap));
@@ -1983,7 +2091,8 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
     else k_octree<512><<<dim3(P.nlevels, n), 512, h->octSmem[2], s>>>(P, B, h->octNodeCap, h->octKeySmemCap[2], h->dKeyNode, P.candFrame);
     nl++;
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_BLUR], s));
-    k_blur<<<dim3(P.totalBlurUnits, n), 128, 0, sb>>>(P, B);
+    if (h->blurTma) k_blur_tma<<<dim3(P.totalBlurUnits, n), 128, BLUR_TROWS * BLUR_TP, sb>>>(P, B, h->blurMaps);
+    else k_blur<<<dim3(P.totalBlurUnits, n), 128, 0, sb>>>(P, B);
     nl++;
     if (!profile) {
         ORBX_CUDA_TRY(cudaEventRecord(evJoin, sb));
