@@ -65,6 +65,7 @@ struct LevelGeom {
     int resizeWords;     // 1: k_resize_words applies (4-column groups read within 8 source columns)
     int resizeRows;      // 1: k_resize_rows applies too (every destination row reads source rows r0, r0 + 1, r0 strictly increasing)
     int sTab;            // offset of this level in the source-row table (k_resize_rows)
+    int resizeTma;       // 1: every CTA's source window of k_resize_rows_tma fits its RZ_TP x RZ_TROWS tile
 };
 
 struct Plan {
@@ -77,6 +78,8 @@ struct Plan {
     long long candFrame;       // candidates per frame (sum of candCap)
     LevelGeom lv[ORBX_MAX_LEVELS];
 };
+
+constexpr int FAST_TMA_LEVELS = 8;  // levels served by the TMA-staged kernels (per-level tensor maps passed as kernel arguments)
 
 struct Cand {  // one FAST candidate
     uint32_t xy;  // x | y << 16, relative to (minBorderX, minBorderY) = (16, 16) like the reference's vToDistributeKeys
@@ -305,15 +308,17 @@ __global__ void __launch_bounds__(128) k_resize_words(Plan plan, Buffers buf, in
 // is the lower row (r1) of at most one destination row; the per-source-row table says which weights that row has (0 = none:
 // warp-uniform branch) and where the REFLECT_101 frame repeats it.  The three source words of the next row are loaded before
 // the current row is processed (two register sets alternating by name; addresses are sequential, one pitch apart).
-template <bool DUP>
+template <bool DUP, bool SMEM>
 __device__ __forceinline__ void resize_rows_walk(const uint8_t* __restrict__ S, uint8_t* __restrict__ D, const int2* __restrict__ srow,
                                                  uint32_t soff, uint32_t doff, int n, const uint32_t spitch, const uint32_t dpitch,
                                                  const uint32_t (&a)[4], const uint32_t (&sel)[4], const uint32_t sh)
 {
-    // S / D are CTA-uniform plane bases, soff / doff the thread's 32-bit byte offsets (uniform base + 32-bit offset addressing)
+    // S / D are CTA-uniform plane bases, soff / doff the thread's 32-bit byte offsets (uniform base + 32-bit offset addressing);
+    // SMEM: S is the CTA's TMA-staged source tile in shared memory
     auto load3 = [&](uint32_t off, uint32_t* w) {
         const uint32_t* R = reinterpret_cast<const uint32_t*>(S + off);
-        w[0] = __ldg(R); w[1] = __ldg(R + 1); w[2] = __ldg(R + 2);
+        if (SMEM) { w[0] = R[0]; w[1] = R[1]; w[2] = R[2]; }
+        else { w[0] = __ldg(R); w[1] = __ldg(R + 1); w[2] = __ldg(R + 2); }
     };
     auto hpass = [&](const uint32_t* w, uint32_t* t) {  // T >> 4 of the thread's 4 columns
         const uint32_t u0 = __funnelshift_r(w[0], w[1], sh), u1 = __funnelshift_r(w[1], w[2], sh);
@@ -394,8 +399,82 @@ __global__ void __launch_bounds__(128) k_resize_rows(Plan plan, Buffers buf, int
     // destination rows 1..19 and h-20..h-2 are repeated in the REFLECT_101 frame: only the threads that own such rows
     // (warp-uniform) run the walk with the extra stores
     const bool dup = dy0 <= EDGE || dy1 - 1 >= g.h - 1 - EDGE;
-    if (dup) resize_rows_walk<true>(S, D, srow, soff, doff, rLast - rFirst, spitch, dpitch, a, sel, sh);
-    else resize_rows_walk<false>(S, D, srow, soff, doff, rLast - rFirst, spitch, dpitch, a, sel, sh);
+    if (dup) resize_rows_walk<true, false>(S, D, srow, soff, doff, rLast - rFirst, spitch, dpitch, a, sel, sh);
+    else resize_rows_walk<false, false>(S, D, srow, soff, doff, rLast - rFirst, spitch, dpitch, a, sel, sh);
+}
+
+// K1b, source-row walk over a TMA-staged source tile (batches: rowsPerThread = RZ_RPT; LevelGeom::resizeTma says the tile of
+// every CTA of the level fits): the CTA's source window -- RZ_TP bytes from the 16-byte grid column left of its leftmost
+// source word x RZ_TROWS rows from the first source row of its first destination row -- arrives through ONE
+// cp.async.bulk.tensor.3d; the walk then reads shared memory (k_resize_rows' top stall was global-load latency).
+constexpr int RZ_RPT = 16;          // destination rows per thread
+constexpr int RZ_TP = 192;          // tile pitch = box width: 128 destination columns x scale <= 1.25 + 16-byte grid + word slack
+constexpr int RZ_TROWS = 84;        // 64 destination rows x scale <= 1.25 + 2, + the row the walk reads ahead
+struct ResizeMaps { CUtensorMap m[FAST_TMA_LEVELS]; };  // indexed by SOURCE level
+
+__global__ void __launch_bounds__(128) k_resize_rows_tma(Plan plan, Buffers buf, int level, int dpitchArg, const __grid_constant__ ResizeMaps maps)
+{
+    extern __shared__ __align__(128) unsigned char rsm[];
+    __shared__ __align__(8) unsigned long long sBar;
+    const LevelGeom& g = plan.lv[level];
+    const LevelGeom& gp = plan.lv[level - 1];
+    const int bx = 4 * (blockIdx.x * 32 + (threadIdx.x & 31));  // pitch is a multiple of 128: always inside the row
+    const int frame = blockIdx.z + buf.frameBase;
+    const int dyCta = blockIdx.y * 4 * RZ_RPT;                   // < g.h by the grid
+    const int dy0 = dyCta + (threadIdx.x >> 5) * RZ_RPT;
+    int sx[4], sx1[4];
+    uint32_t a[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        int dx = min(max(bx + j - PAD_LEFT, -EDGE), g.w - 1 + EDGE);
+        dx = reflect101(dx, g.w);
+        sx[j] = buf.xofs[g.xTab + dx];
+        sx1[j] = min(sx[j] + 1, gp.w - 1);
+        const short2 w = buf.xw[g.xTab + dx];
+        a[j] = (uint32_t)(unsigned short)w.x | ((uint32_t)(unsigned short)w.y << 16);
+    }
+    const int base = min(min(sx[0], sx[1]), min(sx[2], sx[3]));
+    uint32_t sel[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) sel[j] = (uint32_t)(sx[j] - base) | ((uint32_t)(sx1[j] - base) << 4);
+    const uint32_t colOff = (uint32_t)(PAD_LEFT + base) & ~3u, sh = 8u * ((uint32_t)(PAD_LEFT + base) & 3u);
+    // every warp of the CTA covers the same columns: the warp-wide minimum is the CTA's leftmost source word
+    const uint32_t tileX0 = __reduce_min_sync(0xffffffffu, colOff) & ~15u;
+    const int rTile0 = buf.yofs0[g.yTab + dyCta];
+    if (threadIdx.x == 0) {
+        const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&sBar);
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)(RZ_TROWS * RZ_TP)) : "memory");
+        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                     ::"r"((uint32_t)__cvta_generic_to_shared(rsm)), "l"(&maps.m[level - 1]), "r"(bar), "r"((int)tileX0),
+                       "r"(PAD_TOP + rTile0), "r"(frame)
+                     : "memory");
+    }
+    __syncthreads();  // orders the mbarrier's initialisation before the waits
+    {
+        const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&sBar);
+        uint32_t done;
+        do {
+            asm volatile(
+                "{\n\t.reg .pred p;\n\t"
+                "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                "selp.u32 %0, 1, 0, p;\n\t}"
+                : "=r"(done)
+                : "r"(bar), "r"(0u)
+                : "memory");
+        } while (!done);
+    }
+    if (dy0 >= g.h) return;
+    const int dy1 = min(dy0 + RZ_RPT, g.h);
+    const uint32_t dpitch = (uint32_t)dpitchArg;
+    const int rFirst = buf.yofs0[g.yTab + dy0], rLast = buf.yofs1[g.yTab + dy1 - 1];  // source rows rFirst .. rLast
+    uint8_t* D = plane_ptr(buf.pyr, g, frame);
+    const uint32_t soff = (uint32_t)(rFirst - rTile0) * RZ_TP + (colOff - tileX0), doff = (uint32_t)(PAD_TOP + dy0) * dpitch + bx;
+    const int2* srow = buf.srow + g.sTab + rFirst;
+    const bool dup = dy0 <= EDGE || dy1 - 1 >= g.h - 1 - EDGE;
+    if (dup) resize_rows_walk<true, true>(rsm, D, srow, soff, doff, rLast - rFirst, RZ_TP, dpitch, a, sel, sh);
+    else resize_rows_walk<false, true>(rsm, D, srow, soff, doff, rLast - rFirst, RZ_TP, dpitch, a, sel, sh);
 }
 
 // ------------------------------------------------------------------------------------------------------
@@ -489,7 +568,6 @@ __device__ __forceinline__ int fast_measure_packed(const uint8_t* p)
 //                serves more than FAST_TMA_LEVELS levels).
 // Both start at the 16-byte aligned column at or left of the band (the tile is shifted by the band's misalignment): cp.async
 // needs it, and a TMA box whose innermost coordinate is off the 16-byte grid faults (tools/microbench/tma_probe.cu).
-constexpr int FAST_TMA_LEVELS = 8;
 struct FastMaps { CUtensorMap m[FAST_TMA_LEVELS]; };
 
 template <bool TMA>
@@ -1665,6 +1743,8 @@ struct orbx_handle {
     bool fastTma = false;
     BlurMaps blurMaps = {};      // same tensors, box BLUR_TP x BLUR_TROWS (k_blur_tma)
     bool blurTma = false;
+    ResizeMaps resizeMaps = {};  // same tensors, box RZ_TP x RZ_TROWS (k_resize_rows_tma, indexed by source level)
+    bool resizeTma = false;
     size_t octSmem[3] = {0, 0, 0};
     int lastFrames = 0;          // frames of the last batch
     // which frames of the last batch are still in the arena: the pipelined host path keeps only its last two chunks
@@ -1767,7 +1847,7 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
         g.scale = h->scale[l];
         g.patchSize = (int)(31 * h->scale[l]);
         g.xTab = (int)xofs.size(); g.yTab = (int)y0v.size();
-        g.resizeWords = 0; g.resizeRows = 0; g.sTab = 0;
+        g.resizeWords = 0; g.resizeRows = 0; g.sTab = 0; g.resizeTma = 0;
         if (l > 0) {
             const LevelGeom& gp = P.lv[l - 1];
             // cv::resize INTER_LINEAR coefficient tables (see oracle/cvprim.h: linear_coeffs)
@@ -1824,6 +1904,28 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
                     lo = std::min(lo, sxv); hi = std::max(hi, std::min(sxv + 1, gp.w - 1));
                 }
                 if (hi - lo > 7) g.resizeWords = 0;
+            }
+            // k_resize_rows_tma eligibility: the source window of every CTA (128 buffer columns x 4 RZ_RPT destination rows)
+            // fits the RZ_TP x RZ_TROWS tile, and the box does not exceed the source plane
+            g.resizeTma = g.resizeWords && g.resizeRows && gp.pitch >= RZ_TP && gp.planeRows >= RZ_TROWS;
+            for (int bx0 = 0; bx0 < g.pitch && g.resizeTma; bx0 += 128) {
+                int lo = 1 << 30, hi = -1;
+                for (int bx = bx0; bx < bx0 + 128; bx += 4) {
+                    int base = 1 << 30;
+                    for (int j = 0; j < 4; j++) {
+                        int dx = std::min(std::max(bx + j - PAD_LEFT, -EDGE), g.w - 1 + EDGE);
+                        if (dx < 0) dx = -dx;
+                        if (dx >= g.w) dx = 2 * (g.w - 1) - dx;
+                        base = std::min(base, (int)xofs[g.xTab + dx]);
+                    }
+                    const int colOff = (PAD_LEFT + base) & ~3;
+                    lo = std::min(lo, colOff & ~15); hi = std::max(hi, colOff + 12);
+                }
+                if (hi - lo > RZ_TP) g.resizeTma = 0;
+            }
+            for (int d0 = 0; d0 < g.h && g.resizeTma; d0 += 4 * RZ_RPT) {
+                const int dl = std::min(d0 + 4 * RZ_RPT, g.h) - 1;
+                if (y1v[g.yTab + dl] - y0v[g.yTab + d0] + 2 > RZ_TROWS) g.resizeTma = 0;
             }
         }
     }
@@ -1978,6 +2080,7 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
     static const bool tmaOff = [] { const char* e = std::getenv("ORBX_FAST_TMA"); return e && std::atoi(e) == 0; }();
     h->fastTma = false;
     h->blurTma = false;
+    h->resizeTma = false;
     if (!tmaOff && P.nlevels <= FAST_TMA_LEVELS) {
         typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                      const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -2010,6 +2113,21 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
                                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
             }
+            static const bool rzOff = [] { const char* e = std::getenv("ORBX_RESIZE_TMA"); return e && std::atoi(e) == 0; }();
+            bool okr = !rzOff;
+            for (int l = 0; l + 1 < P.nlevels && okr; l++) {
+                const LevelGeom& g = P.lv[l];
+                const cuuint64_t gdim[3] = {(cuuint64_t)g.pitch, (cuuint64_t)g.planeRows, (cuuint64_t)cap};
+                const cuuint64_t gstride[2] = {(cuuint64_t)g.pitch, (cuuint64_t)g.planeBytes};
+                const cuuint32_t box[3] = {(cuuint32_t)RZ_TP, (cuuint32_t)RZ_TROWS, 1};
+                const cuuint32_t estr[3] = {1, 1, 1};
+                if (!P.lv[l + 1].resizeTma) { std::memset(&h->resizeMaps.m[l], 0, sizeof(CUtensorMap)); continue; }
+                okr = ((EncodeFn)fp)(&h->resizeMaps.m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, B.pyr + g.planeOff, gdim, gstride, box, estr,
+                                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+            }
+            h->resizeTma = okr;
+            if (okr) ORBX_CUDA_TRY(cudaFuncSetAttribute(k_resize_rows_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, RZ_TROWS * RZ_TP));
             h->blurTma = okb;
             if (okb) ORBX_CUDA_TRY(cudaFuncSetAttribute(k_blur_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, BLUR_TROWS * BLUR_TP));
         }
@@ -2059,7 +2177,9 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
         while (rpt > 4 && (long long)(g.pitch / 4) * ((g.h + rpt - 1) / rpt) * n < 148LL * 2048) rpt >>= 1;
         dim3 grid(g.pitch / 128, (g.h + 4 * rpt - 1) / (4 * rpt), n);
         static const bool rowsOff = [] { const char* e = std::getenv("ORBX_RESIZE_ROWS"); return e && std::atoi(e) == 0; }();  // A/B switch
-        if (g.resizeWords && g.resizeRows && !rowsOff) k_resize_rows<<<grid, 128, 0, s>>>(P, B, l, rpt, P.lv[l - 1].pitch, g.pitch);
+        if (h->resizeTma && g.resizeTma && rpt == RZ_RPT && !rowsOff)
+            k_resize_rows_tma<<<grid, 128, RZ_TROWS * RZ_TP, s>>>(P, B, l, g.pitch, h->resizeMaps);
+        else if (g.resizeWords && g.resizeRows && !rowsOff) k_resize_rows<<<grid, 128, 0, s>>>(P, B, l, rpt, P.lv[l - 1].pitch, g.pitch);
         else if (g.resizeWords) k_resize_words<<<grid, 128, 0, s>>>(P, B, l, rpt);
         else k_resize<<<grid, 128, 0, s>>>(P, B, l, rpt);
         nl++;

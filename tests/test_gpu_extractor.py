@@ -399,3 +399,48 @@ def test_device_api_reports_truncation(gpu):
     assert np.array_equal(got, full[:cap])
     ex.sync()   # the flag is cleared by the report
     ex.close()
+
+
+@pytest.mark.parametrize("shape_name", ["tum", "kitti"])
+def test_large_device_batch_stage_by_stage(gpu, oracle_mod, shape_name):
+    """The kernel variants that only batches select (k_resize_rows_tma at 16 rows per thread, 128-thread quad-tree CTAs, 12
+    keypoints per warp in k_describe, blur beside the quad-tree): a 160-frame device-resident batch, every stage of three
+    frames (first, middle, last) against the oracle."""
+    import torch
+
+    shape, cfg = synth.SHAPES[shape_name], synth.PRESETS[shape_name]
+    distinct = [synth.gen_frame(shape, 40 + s) for s in range(5)]
+    n = 160
+    imgs = np.stack([distinct[i % 5] for i in range(n)])
+    ex = gpu.ORBextractor(*cfg)
+    cap = ex.max_keypoints(*shape)
+    dev = torch.device("cuda", 0)
+    d_img = torch.from_numpy(imgs).to(dev)
+    d_kps = torch.zeros((n, cap, 6), dtype=torch.float32, device=dev)
+    d_desc = torch.zeros((n, cap, 32), dtype=torch.uint8, device=dev)
+    d_cnt = torch.zeros(n, dtype=torch.int32, device=dev)
+    ex.extract_batch_device(d_img.data_ptr(), n, shape[0], shape[1], d_kps.data_ptr(), d_desc.data_ptr(), d_cnt.data_ptr(), cap)
+    ex.sync()
+    counts = d_cnt.cpu().numpy()
+    kps = d_kps.cpu().numpy().view(gpu.KP_DTYPE).reshape(n, cap)
+    desc = d_desc.cpu().numpy()
+    ref = {}
+    for f in (0, 77, 159):
+        s = f % 5
+        o = oracle_mod.Extractor(*cfg)
+        okps, odesc = o.extract(distinct[s])
+        ref[s] = (okps, odesc)
+        for l in range(cfg[2]):
+            assert np.array_equal(ex.pyramid_level_padded(l, frame=f), o.pyramid(l)), "pyramid level %d frame %d" % (l, f)
+            assert np.array_equal(_sorted_rows(ex.debug_candidates(l, frame=f)), _sorted_rows(o.candidates(l))), "candidates %d/%d" % (l, f)
+            ob = o.blurred(l)
+            if ob is not None:
+                assert np.array_equal(ex.debug_blurred(l, frame=f), ob), "blur level %d frame %d" % (l, f)
+    for f in range(n):
+        if f % 5 not in ref:
+            continue
+        okps, odesc = ref[f % 5]
+        assert counts[f] == len(okps)
+        assert kps[f, : counts[f]].tobytes() == okps.tobytes()
+        assert np.array_equal(desc[f, : counts[f]], odesc)
+    ex.close()
