@@ -575,7 +575,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf, co
 {
     extern __shared__ __align__(128) unsigned char fsm[];
     __shared__ __align__(8) unsigned long long sBar;
-    __shared__ int sQ1[2], sQ3, sCnt, sBase, sPos;  // sQ1: one survivor counter per phase (no reset barrier between them)
+    __shared__ int sQ1[2], sQ3, sBase;  // sQ1: one survivor counter per phase (no reset barrier between them)
     __shared__ __align__(4) unsigned char sHasIni[FAST_MAXG];  // byte c = cell c kept a corner >= iniTh (read as one word)
     __shared__ int sSeg[FAST_T / 32];
     static_assert(FAST_MAXG == 4, "sHasIni is read as one 32-bit word");
@@ -624,7 +624,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf, co
         uint4* z = reinterpret_cast<uint4*>(sc) + threadIdx.x;
         for (int n = rh * (FAST_P / 16) - threadIdx.x; n > 0; n -= FAST_T, z += FAST_T) *z = make_uint4(0, 0, 0, 0);
     }
-    if (threadIdx.x == 0) { *reinterpret_cast<uint32_t*>(sHasIni) = 0u; sQ1[0] = 0; sQ1[1] = 0; sQ3 = 0; sCnt = 0; sPos = 0; }
+    if (threadIdx.x == 0) { *reinterpret_cast<uint32_t*>(sHasIni) = 0u; sQ1[0] = 0; sQ1[1] = 0; sQ3 = 0; }
     if (!TMA) asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
     if (TMA) {  // (the barrier above orders the mbarrier's initialisation before these waits)
@@ -823,21 +823,12 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf, co
     if (!retry) break;  // CTA-uniform.  No barrier here: phase 1 writes q1 / sSeg / sHasIni only after its own barriers,
                         // which every thread reaches after it has read them above
     }
-    // ---- pass 4: per-cell threshold, count, reserve, write ----
+    // ---- pass 4: reserve, write.  Every NMS survivor is an output: phase 0 keeps only corners >= iniTh (their cell then
+    //      "has an ini corner"), phase 1 runs only in the cells that kept nothing and keeps corners >= minTh -- the
+    //      per-cell threshold of the reference's two cv::FAST calls is already applied by which phase scored the pixel ----
     const int n3 = min(sQ3, plan.fastQCap);
-    int mine = 0;
-    for (int q = threadIdx.x; q < n3; q += FAST_T) {
-        const int e = q3[q];
-        const int ty = e >> 8, tx = e & 0xff;
-        const int ex = tx - (shift + 3);
-        const int c = (ex >= wCell) + (ex >= 2 * wCell) + (ex >= 3 * wCell);
-        mine += sc[ty * FAST_P + tx] >= (sHasIni[c] ? iniTh : minTh);
-    }
-    if (mine) atomicAdd(&sCnt, mine);
+    if (threadIdx.x == 0) sBase = n3 ? atomicAdd(buf.candCount + frame * plan.nlevels + level, n3) : 0;
     __syncthreads();
-    if (threadIdx.x == 0) sBase = sCnt ? atomicAdd(buf.candCount + frame * plan.nlevels + level, sCnt) : 0;
-    __syncthreads();
-    if (!mine) return;
     Cand* out = buf.cand + (long long)frame * plan.candFrame + g.candOff;
     for (int q = threadIdx.x; q < n3; q += FAST_T) {
         const int e = q3[q];
@@ -845,8 +836,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf, co
         const int ex = tx - (shift + 3), ey = ty - 3;
         const int c = (ex >= wCell) + (ex >= 2 * wCell) + (ex >= 3 * wCell);
         const int s = sc[ty * FAST_P + tx];
-        if (s < (sHasIni[c] ? iniTh : minTh)) continue;
-        const int pos = sBase + atomicAdd(&sPos, 1);
+        const int pos = sBase + q;
         if (pos >= g.candCap) { *reinterpret_cast<volatile int*>(buf.errFlag) = 1; break; }
         const int r = ex - c * wCell;
         const uint32_t xrel = (j0 + c) * wCell + r + 3, yrel = ci * g.hCell + ey + 3;
@@ -2189,7 +2179,8 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
     // The blur runs on its own branch of the graph.  A few frames: beside FAST (both grids fit the GPU at once, lowest
     // latency).  Batches: beside the quad-tree, whose barrier-bound CTAs leave most issue slots free (measured +2 % per
     // step against FAST || blur, where both kernels compete for the same issue slots).
-    const bool blurAfterFast = n >= 16;
+    static const int blurFork = [] { const char* e = std::getenv("ORBX_BLUR_FORK"); return e ? std::atoi(e) : -1; }();  // experiments: 0 = beside FAST, 1 = after FAST
+    const bool blurAfterFast = blurFork >= 0 ? blurFork != 0 : n >= 16;
     if (!profile && !blurAfterFast) {
         ORBX_CUDA_TRY(cudaEventRecord(evFork, s));
         ORBX_CUDA_TRY(cudaStreamWaitEvent(sb, evFork, 0));

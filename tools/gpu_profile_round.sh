@@ -12,9 +12,9 @@ python tools/profile_all.py > $out/${tag}_profall.log 2>&1 || { echo "profile_al
 timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off -f -o ${rep%.ncu-rep} \
     python tools/profile_all.py > $out/${tag}_ncu.log 2>&1
 ls -la $rep
-ALL='k_level0 k_resize_rows k_fast_band k_octree k_blur k_describe k_bruteforce$ k_bruteforce_tc k_expand_pm1 k_merge_partials k_bow_scatter12 k_proj_search k_stereo_rows k_stereo_refine k_stereo_medians k_stereo_reject k_bow_transform k_bow_nodes k_bow_rotation k_search_best k_init_search k_triang_nodes k_distinctive k_undistort k_assign_grid'
+ALL='k_level0 k_resize_rows_tma k_fast_band k_octree k_blur_tma k_describe k_bruteforce$ k_bruteforce_tc k_expand_pm1 k_merge_partials k_merge_exchange k_bow_scatter12 k_proj_search k_stereo_rows k_stereo_refine k_stereo_medians k_stereo_reject k_bow_transform k_bow_nodes k_bow_rotation k_search_best k_init_search k_triang_nodes k_distinctive k_undistort k_assign_grid'
 python tools/ncu_report.py $rep --sass $ALL > $out/${tag}_all_kernels.md 2> $out/${tag}_report.err
-for k in k_fast_band k_resize_rows k_describe k_blur k_octree k_bruteforce_tc; do
+for k in k_fast_band k_resize_rows_tma k_describe k_blur_tma k_octree k_bruteforce_tc; do
     python tools/ncu_hot.py $rep $k 60 > $out/${tag}_hot_$k.txt 2>&1
 done
 python tools/ncu_sass.py $rep k_fast_band > $out/${tag}_sass_k_fast_band.txt 2>&1

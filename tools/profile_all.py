@@ -70,6 +70,23 @@ def run_all():
     vocab, vdesc = mc.vocab_case(10, 4)
     voc = vocabulary.ORBVocabulary(vocab, mm)
     voc.transform_features(vdesc, 4)
+    # the fused merge + exchange kernel: two contexts of this process on cuda:0 (publish phase of both, then collect phase)
+    ws = [pkg.ORBmatcher(0.6, True, device=0) for _ in range(2)]
+    ptrs = [w.exchange_create(2, r, 2000)[1] for r, w in enumerate(ws)]
+    for w in ws:
+        w.exchange_connect_local(ptrs)
+    dq2, ddb2 = torch.from_numpy(q).to(dev), torch.from_numpy(db[:200_000]).to(dev)
+    outs = [[torch.empty(2000, dtype=torch.int32, device=dev) for _ in range(3)] for _ in range(2)]
+    for phase in (1, 2):
+        for r in range(2):
+            lo, hi = r * 100_000, (r + 1) * 100_000
+            ws[r].bruteforce_sharded_device(dq2.data_ptr(), 2000, ddb2.data_ptr() + 32 * lo, hi - lo, lo, *[t.data_ptr() for t in outs[r]], phases=phase)
+        for w in ws:
+            w.sync()
+    assert not any(w.exchange_timed_out() for w in ws)
+    for w in ws:
+        w.close()
+    print("exchange ok")
     x = np.random.default_rng(0).random(2000).astype(np.float32) * 600
     y = np.random.default_rng(1).random(2000).astype(np.float32) * 400
     ux, uy = mm.UndistortKeyPoints(x, y, 517.3, 516.5, 318.6, 255.3, [0.2624, -0.9531, -0.0054, 0.0026, 1.1633])
