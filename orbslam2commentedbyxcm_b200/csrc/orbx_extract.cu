@@ -49,6 +49,7 @@ struct LevelGeom {
     long long planeOff;  // byte offset of frame 0's plane of this level inside the pyramid (and blurred) arena
     long long planeBytes;
     int nCols, nRows, wCell, hCell;  // 30-px cell grid (src/ORBextractor.cc:1043-1051)
+    int wCellMagic;      // 65536 / wCell + 1: (x * wCellMagic) >> 16 == x / wCell for 0 <= x < 1024 (wCell >= 30)
     int maxBX, maxBY;    // w - 16, h - 16
     int blurOff;         // first CTA index of this level in k_blur
     int fastG, fastGroups, fastOff;  // k_fast_band: cells per CTA, CTAs per cell row, first CTA index of the level
@@ -646,7 +647,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf, co
     const int wCell = g.wCell;
     const int txFirst = shift + 3, txEnd = shift + 3 + evalW;  // evaluated tile columns [txFirst, txEnd)
     const int gw0 = txFirst >> 2, gw = gw0 + lane;                      // ((txEnd-1)>>2) - (txFirst>>2) + 1 <= 32 words
-    const int ncells = 1 + (evalW - 1 >= wCell) + (evalW - 1 >= 2 * wCell) + (evalW - 1 >= 3 * wCell);  // = min(4, (evalW-1)/wCell + 1), no division
+    const int ncells = min(4, (int)(((uint32_t)(evalW - 1) * (uint32_t)g.wCellMagic) >> 16) + 1);  // = min(4, (evalW-1)/wCell + 1), no division
     constexpr int FAST_RPW = (59 + FAST_T / 32 - 1) / (FAST_T / 32);  // sweeps: eh <= 59
     static_assert(FAST_RPW <= 16, "survivor nibbles must fit 64 bits");
     // Survivor masks: sweep `it` (rows warp + 3 + 4 * it) owns nibble 7 - it of the low word (it < 8) or nibble 15 - it of the
@@ -669,10 +670,9 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf, co
     {
         const uint32_t Ki = (uint32_t)(0x7f - min(iniTh, 0x7f)) * 0x01010101u, Km = (uint32_t)(0x7f - min(minTh, 0x7f)) * 0x01010101u;
         // (a threshold >= 127 gives K = 0: the test degrades to |d| >= 128, still necessary for |d| > threshold)
-        uint32_t vmask = 0;  // bytes of this word that are evaluated pixels
-#pragma unroll
-        for (int bb = 0; bb < 4; bb++)
-            if (4 * gw + bb >= txFirst && 4 * gw + bb < txEnd) vmask |= 0x80u << (8 * bb);
+        // bytes of this word that are evaluated pixels: columns [txFirst, txEnd) -> bytes [lo, hi) of the word
+        const int vlo = min(max(txFirst - 4 * gw, 0), 4), vhi = min(max(txEnd - 4 * gw, 0), 4);
+        const uint32_t vmask = 0x80808080u & __funnelshift_lc(0xffffffffu, 0u, 8 * vhi) & ~__funnelshift_lc(0xffffffffu, 0u, 8 * vlo);
         const uint32_t* rowp = reinterpret_cast<const uint32_t*>(tile) + (warp + 3) * FAST_P4 + gw;
         const int nIt = (eh - warp + FAST_T / 32 - 1) / (FAST_T / 32);  // sweeps of this warp (warp-uniform, <= FAST_RPW; <= 0: none)
 #pragma unroll
@@ -709,12 +709,13 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf, co
     const int th = phase ? minTh : iniTh;
     uint32_t mlo = iniLo, mhi = iniHi;
     if (phase) {
-        uint32_t nibOK = 0;  // pixels of this lane's word that lie in a cell to retry
-#pragma unroll
-        for (int bb = 0; bb < 4; bb++) {
-            const int ex = 4 * gw + bb - txFirst;
-            nibOK |= ((retry >> ((ex >= wCell) + (ex >= 2 * wCell) + (ex >= 3 * wCell))) & 1u) << bb;
-        }
+        // pixels of this lane's word that lie in a cell to retry: the word's first column is in cell c0, a cell border can
+        // fall on at most one of its four pixels (wCell >= 30): the pixels from kb on belong to cell c0 + 1
+        const int e0 = 4 * gw - txFirst;
+        const int c0 = (int)(((uint32_t)max(e0, 0) * (uint32_t)g.wCellMagic) >> 16);
+        const int kb = (c0 + 1) * wCell - e0;                       // >= 1
+        const uint32_t low = (1u << min(kb, 4)) - 1u, r0 = retry >> c0;
+        const uint32_t nibOK = ((r0 & 1u) ? low : 0u) | ((r0 & 2u) ? (low ^ 15u) : 0u);
         mlo = minLo & (nibOK * 0x11111111u);
         mhi = minHi & (nibOK * 0x11111111u);
     }
@@ -1803,6 +1804,7 @@ static int build_plan(orbx_handle* h, int rows, int cols, Plan& P, std::vector<s
             return ORBX_ERR_TOO_SMALL;
         }
         g.wCell = (int)std::ceil(width / g.nCols); g.hCell = (int)std::ceil(height / g.nRows);
+        g.wCellMagic = 65536 / g.wCell + 1;
         g.nIni = (int)std::round((float)(g.maxBX - minB) / (g.maxBY - minB));
         if (g.nIni < 1) {
             set_error("level %d is %dx%d: aspect ratio gives zero quad-tree roots", l, g.w, g.h);
