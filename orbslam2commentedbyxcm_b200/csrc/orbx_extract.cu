@@ -114,6 +114,7 @@ struct Buffers {
     const int2* srow;    // k_resize_rows table, per SOURCE row r: {b0 | b1 << 16 of the destination row whose lower source row is r
                          // (0: none), mirrored frame rows of that destination row as deltas}
     const FastUnit* fastUnits;  // [totalFastUnits]
+    const uint8_t* zeros;  // fastTileBytes zero bytes (k_fast_band<TMA> clears its score tile with a bulk copy of them)
     int* errFlag;        // device-side overflow flag
     int frames;
     int frameBase;       // arena slot offset: arena frame = launch-local frame index + frameBase
@@ -601,10 +602,14 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf, co
             const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&sBar);
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)((g.hCell + 6) * FAST_P)) : "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)((g.hCell + 6) * FAST_P + plan.fastTileBytes)) : "memory");
             asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
                          ::"r"((uint32_t)__cvta_generic_to_shared(tile)), "l"(&maps.m[level]), "r"(bar), "r"(PAD_LEFT + iniX - shift),
                            "r"(PAD_TOP + iniY), "r"(frame)
+                         : "memory");
+            // the score tile is zeroed by a second bulk copy (from a zero buffer that lives in L2) instead of by stores
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"((uint32_t)__cvta_generic_to_shared(sc)), "l"(buf.zeros), "r"((uint32_t)plan.fastTileBytes), "r"(bar)
                          : "memory");
         }
     } else {
@@ -621,7 +626,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf, co
             }
         }
     }
-    {
+    if (!TMA) {
         uint4* z = reinterpret_cast<uint4*>(sc) + threadIdx.x;
         for (int n = rh * (FAST_P / 16) - threadIdx.x; n > 0; n -= FAST_T, z += FAST_T) *z = make_uint4(0, 0, 0, 0);
     }
@@ -696,8 +701,9 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf, co
         }
         // canonical positions: sweep 0 at the top nibble of the low word, sweep 8 at the top nibble of the high word
         const int padLo = 4 * max(8 - max(nIt, 0), 0), padHi = 4 * min(16 - max(nIt, 8), 8);
-        iniLo = padLo < 32 ? iniLo << padLo : 0u; minLo = padLo < 32 ? minLo << padLo : 0u;
-        iniHi = padHi < 32 ? iniHi << padHi : 0u; minHi = padHi < 32 ? minHi << padHi : 0u;
+        // (clamped funnel shift: x << pad for pad < 32, 0 for pad = 32)
+        iniLo = __funnelshift_lc(0u, iniLo, padLo); minLo = __funnelshift_lc(0u, minLo, padLo);
+        iniHi = __funnelshift_lc(0u, iniHi, padHi); minHi = __funnelshift_lc(0u, minHi, padHi);
     }
     // Two phases, as the reference calls cv::FAST twice: phase 0 scores the corners at iniTh (NMS among them is exact: a
     // kept pixel beats every neighbour below iniTh anyway); phase 1 repeats passes 2 and 3 at minTh for the cells that kept
@@ -1727,6 +1733,7 @@ struct orbx_handle {
     short* dTabs = nullptr;
     unsigned short* dKeyNode = nullptr;
     FastUnit* dFastUnits = nullptr;
+    uint8_t* dZeros = nullptr;
     int octNodeCap = 0;
     int octKeySmemCap[3] = {0, 0, 0};  // per k_octree variant: 128, 256, 512 threads
     size_t fastSmem = 0;
@@ -2040,6 +2047,10 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
     ORBX_CUDA_TRY(cudaMemcpyAsync(h->dFastUnits, ti.units.data(), sizeof(FastUnit) * ti.units.size(), cudaMemcpyHostToDevice, h->stream));
     ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));  // ti.units is a local
     B.fastUnits = h->dFastUnits;
+    ORBX_CUDA_TRY(cudaMalloc(&h->dZeros, (size_t)P.fastTileBytes));
+    ORBX_CUDA_TRY(cudaMemsetAsync(h->dZeros, 0, (size_t)P.fastTileBytes, h->stream));
+    ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+    B.zeros = h->dZeros;
     B.xofs = h->dTabs;
     B.yofs0 = h->dTabs + ti.nx;
     B.yofs1 = h->dTabs + ti.nx + ti.ny;
