@@ -34,8 +34,9 @@ WORKLOAD_NAME = "C1 TUM 640x480, 1000 feats, scale 1.2, 8 levels, FAST 20/7"
 # identical in both arms' JSON lines (the driver compares them); what one step holds is in "step_detail"
 CONFIG = {"workload": WORKLOAD_NAME, "parallelism": "frames sharded by rank, no data-path collective",
           "l2": "inputs larger than L2: every pass streams a frame buffer + pyramid of more than 126 MB"}
-BATCH = 256       # frames per GPU per pass (one device buffer, larger than L2 with its pyramid)
-INNER = 32        # passes per step: a step is INNER x BATCH frames per GPU, so 20 steps time >= 0.5 s
+BATCH = 512       # frames per GPU per pass (one device buffer, larger than L2 with its pyramid; measured 256 -> 283 k,
+                  # 512 -> 290 k, 1024 -> 294 k frames/s: the small upper pyramid levels fill the GPU better)
+INNER = 16        # passes per step: a step is INNER x BATCH frames per GPU, so 20 steps time >= 0.5 s
 E2E_INNER = 8     # host calls (E2E_BATCH frames each) per end-to-end step
 E2E_BATCH = 512   # frames per end-to-end host call (measured sweep, tools/e2e_batch_sweep.py: 256 -> 148 k, 512 -> 160 k,
                   # >= 1024 -> 122-128 k frames/s: the pipeline's fill / drain amortises, larger pinned buffers copy slower)
