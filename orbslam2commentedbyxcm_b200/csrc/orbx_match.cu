@@ -1087,8 +1087,8 @@ struct InitArgs {
     int checkOri;
     int32_t* resA; int32_t* resB;   // [n1] accepted F2 feature or -1 (double buffered across sweeps)
     int32_t* distA; int32_t* distB; // [n1] Hamming distance of the accepted match
-    int32_t* head; int32_t* next;   // [n2], [n1]
-    int32_t* out12; int* nmatches; int* sweeps;
+    int32_t* head; int32_t* headB; int32_t* next;   // [n2] x 2 (the list heads the sweep reads / the next sweep's), [n1]
+    int32_t* out12; int* nmatches; int* sweeps; int* misc;
 };
 
 __device__ int init_one(const InitArgs& A, int i1, const int32_t* distPrev, int lane, int* distOut)
@@ -1133,59 +1133,62 @@ __device__ int init_one(const InitArgs& A, int i1, const int32_t* distPrev, int 
     return t.p1;
 }
 
-__global__ void __launch_bounds__(1024) k_init_search(InitArgs A)
+__global__ void __launch_bounds__(256) k_init_search(InitArgs A)
 {
-    __shared__ int changed;
-    __shared__ int hist[HISTO_LENGTH];
-    __shared__ int keepBin[HISTO_LENGTH];
-    __shared__ int total;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    // cooperative grid (one warp per F1 feature and sweep, as many CTAs as level-0 features need): the sweeps are separated by
+    // grid-wide barriers; flags, histogram and the kept bins live in A.misc
+    cg::grid_group grid = cg::this_grid();
+    int* changed = A.misc;             // [2], alternating by sweep
+    int* hist = A.misc + 8;            // [HISTO_LENGTH]
+    int* keepBin = A.misc + 8 + 32;    // [HISTO_LENGTH]
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gthreads = gridDim.x * blockDim.x;
+    const int lane = threadIdx.x & 31, warp = gtid >> 5, nwarps = gthreads >> 5;
     int32_t* resPrev = A.resA;
     int32_t* resNext = A.resB;
     int32_t* distPrev = A.distA;
     int32_t* distNext = A.distB;
-    for (int i = tid; i < A.n2; i += blockDim.x) A.head[i] = -1;
-    for (int i = tid; i < A.n1; i += blockDim.x) { resPrev[i] = -1; A.next[i] = -1; distPrev[i] = 0; }
-    if (tid < HISTO_LENGTH) hist[tid] = 0;
-    if (tid == 0) total = 0;
-    __syncthreads();
+    for (int i = gtid; i < A.n2; i += gthreads) A.head[i] = -1;   // no accepted matches yet: empty lists
+    for (int i = gtid; i < A.n1; i += gthreads) { resPrev[i] = -1; A.next[i] = -1; distPrev[i] = 0; }
+    if (gtid < HISTO_LENGTH) hist[gtid] = 0;
+    if (gtid == 0) { changed[0] = 0; changed[1] = 0; *A.nmatches = 0; }
+    grid.sync();
     int sweep = 0;
     for (;; sweep++) {
-        if (tid == 0) changed = 0;
-        __syncthreads();
+        int* chg = changed + (sweep & 1);
         for (int i1 = warp; i1 < A.n1; i1 += nwarps) {
             int d = 0;
             const int r = init_one(A, i1, distPrev, lane, &d);
             if (lane == 0) {
                 resNext[i1] = r;
                 distNext[i1] = d;
-                if (r != resPrev[i1]) changed = 1;
+                if (r != resPrev[i1]) *chg = 1;
             }
         }
-        __syncthreads();
-        if (!changed) break;
-        for (int i = tid; i < A.n2; i += blockDim.x) A.head[i] = -1;
-        __syncthreads();
-        for (int j = tid; j < A.n1; j += blockDim.x) {
+        // the next sweep's list heads are prepared in the OTHER array (this sweep's lists are still being read elsewhere)
+        for (int i = gtid; i < A.n2; i += gthreads) A.headB[i] = -1;
+        grid.sync();
+        if (*chg == 0) break;
+        if (gtid == 0) changed[(sweep + 1) & 1] = 0;
+        for (int j = gtid; j < A.n1; j += gthreads) {
             const int r = resNext[j];
-            A.next[j] = r >= 0 ? atomicExch(&A.head[r], j) : -1;
+            A.next[j] = r >= 0 ? atomicExch(&A.headB[r], j) : -1;
         }
-        __syncthreads();
+        grid.sync();
         int32_t* t = resPrev; resPrev = resNext; resNext = t;
         t = distPrev; distPrev = distNext; distNext = t;
+        t = A.head; A.head = A.headB; A.headB = t;
     }
     // resNext == resPrev == the sequential result.  vnMatches21[i2] = the LAST accepted i1 (later matches steal).
-    for (int i = tid; i < A.n2; i += blockDim.x) A.head[i] = -1;
-    __syncthreads();
-    for (int j = tid; j < A.n1; j += blockDim.x) {
+    // (A.headB was reset to -1 everywhere before the last barrier or at start-up and has not been written since)
+    for (int j = gtid; j < A.n1; j += gthreads) {
         const int r = resNext[j];
         if (r >= 0) {
-            atomicMax(&A.head[r], j);
+            atomicMax(&A.headB[r], j);
             if (A.checkOri) atomicAdd(&hist[rot_bin(A.angle1[j], A.kangle[r])], 1);   // stolen matches stay in rotHist
         }
     }
-    __syncthreads();
-    if (tid == 0) {
+    grid.sync();
+    if (gtid == 0) {
         int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
         for (int i = 0; i < HISTO_LENGTH; i++) {
             const int sN = hist[i];
@@ -1196,18 +1199,17 @@ __global__ void __launch_bounds__(1024) k_init_search(InitArgs A)
         if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
         else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) ind3 = -1;
         for (int i = 0; i < HISTO_LENGTH; i++) keepBin[i] = !A.checkOri || (i == ind1 || i == ind2 || i == ind3);
+        *A.sweeps = sweep + 1;
     }
-    __syncthreads();
+    grid.sync();
     int mine = 0;
-    for (int j = tid; j < A.n1; j += blockDim.x) {
+    for (int j = gtid; j < A.n1; j += gthreads) {
         const int r = resNext[j];
         int o = -1;
-        if (r >= 0 && A.head[r] == j && keepBin[A.checkOri ? rot_bin(A.angle1[j], A.kangle[r]) : 0]) { o = r; mine++; }
+        if (r >= 0 && A.headB[r] == j && keepBin[A.checkOri ? rot_bin(A.angle1[j], A.kangle[r]) : 0]) { o = r; mine++; }
         A.out12[j] = o;
     }
-    if (mine) atomicAdd(&total, mine);
-    __syncthreads();
-    if (tid == 0) { *A.nmatches = total; *A.sweeps = sweep + 1; }
+    if (mine) atomicAdd(A.nmatches, mine);
 }
 
 
@@ -2437,7 +2439,7 @@ int orbm_search_for_initialization(orbm_context* m, int n1, const int32_t* octav
     const size_t oKx = c.take(4 * (size_t)n2), oKy = c.take(4 * (size_t)n2), oKo = c.take(4 * (size_t)n2), oKa = c.take(4 * (size_t)n2),
                  oKd = c.take(32 * (size_t)n2), oCs = c.take(4 * (size_t)(ncell + 1)), oCi = c.take(4 * (size_t)std::max(nitems, 1));
     const size_t oRa = c.take(4 * (size_t)n1), oRb = c.take(4 * (size_t)n1), oDa = c.take(4 * (size_t)n1), oDb = c.take(4 * (size_t)n1),
-                 oHead = c.take(4 * (size_t)n2), oNext = c.take(4 * (size_t)n1), oOut = c.take(4 * (size_t)n1), oMisc = c.take(64);
+                 oHead = c.take(4 * (size_t)n2), oHeadB = c.take(4 * (size_t)n2), oNext = c.take(4 * (size_t)n1), oOut = c.take(4 * (size_t)n1), oMisc = c.take(512);
     int rc = ensure_arena(m, c.off);
     if (rc != ORBX_OK) return rc;
     char* A = m->arena;
@@ -2455,10 +2457,16 @@ int orbm_search_for_initialization(orbm_context* m, int n1, const int32_t* octav
     a.minX = f2->min_x; a.minY = f2->min_y; a.wInv = f2->grid_w_inv; a.hInv = f2->grid_h_inv;
     a.window = (float)window_size; a.nnratio = nnratio; a.checkOri = check_orientation ? 1 : 0;
     a.resA = (int32_t*)(A + oRa); a.resB = (int32_t*)(A + oRb); a.distA = (int32_t*)(A + oDa); a.distB = (int32_t*)(A + oDb);
-    a.head = (int32_t*)(A + oHead); a.next = (int32_t*)(A + oNext); a.out12 = (int32_t*)(A + oOut);
-    a.nmatches = (int*)(A + oMisc); a.sweeps = a.nmatches + 1;
-    k_init_search<<<1, 1024, 0, m->stream>>>(a);
-    ORBX_CUDA_TRY(cudaGetLastError());
+    a.head = (int32_t*)(A + oHead); a.headB = (int32_t*)(A + oHeadB); a.next = (int32_t*)(A + oNext); a.out12 = (int32_t*)(A + oOut);
+    a.nmatches = (int*)(A + oMisc); a.sweeps = a.nmatches + 1; a.misc = a.nmatches + 8;
+    {
+        int perSM = 0;
+        ORBX_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_init_search, 256, 0));
+        const int want = (n1 + 7) / 8;  // 8 warps per CTA, one warp per F1 feature
+        const int grid = std::max(1, std::min(want, perSM * m->numSMs));
+        void* args[] = {&a};
+        ORBX_CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_init_search, dim3(grid), dim3(256), args, 0, m->stream));
+    }
     ORBX_CUDA_TRY(cudaMemcpyAsync(out_match12, a.out12, 4 * (size_t)n1, cudaMemcpyDeviceToHost, m->stream));
     ORBX_CUDA_TRY(cudaMemcpyAsync(nmatches, a.nmatches, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
     ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));

@@ -26,7 +26,7 @@ def run_all():
     dev = torch.device("cuda", 0)
     shape, cfg = synth.SHAPES["tum"], synth.PRESETS["tum"]
     rows, cols = shape
-    B = 64
+    B = 128  # >= 76 frames: the batch variants of the kernels (k_resize_rows_tma at 16 rows per thread, 128-thread quad-tree CTAs)
     frames = bench.make_frames(shape, 32, B)
     ex = pkg.ORBextractor(*cfg)
     ex.set_use_graph(False)
