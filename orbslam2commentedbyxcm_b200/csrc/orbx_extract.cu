@@ -19,6 +19,7 @@
 #include <cstdarg>
 #include <cstdlib>
 #include <vector>
+#include <utility>
 #include <algorithm>
 #include <mutex>
 
@@ -125,6 +126,20 @@ __device__ const signed char d_pattern[1024] __attribute__((aligned(16))) = {
 #include "orb_pattern.inc"
 };
 
+// Programmatic dependent launch (the kernels of a batch are a chain; bench-sized launches last 20-100 us and the hand-over
+// between two of them costs a few us): every kernel lets its successor be scheduled as soon as all of its own CTAs have
+// started (pdl_trigger at entry), does the part of its prologue that reads only kernel arguments and plan-time tables, and
+// waits for its predecessor to COMPLETE (pdl_wait: all memory of the predecessor visible; also orders this kernel's writes
+// after the predecessor's reads) before it touches anything a batch kernel reads or writes.  Both are no-ops when the launch
+// does not carry the attribute (ORBX_PDL=0, profiling mode).
+__device__ __forceinline__ void pdl_trigger()
+{
+#ifdef ORBX_PDL_EARLY_TRIGGER
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 __device__ __forceinline__ uint8_t* plane_ptr(uint8_t* arena, const LevelGeom& g, int frame)
 {
     return arena + g.planeOff + (long long)frame * g.planeBytes;
@@ -145,9 +160,11 @@ constexpr int L0_ROWS = 8;
 __global__ void __launch_bounds__(16 * L0_ROWS) k_level0(Plan plan, Buffers buf, const uint8_t* __restrict__ in, long long inStep,
                                                          long long inFrameStride)
 {
+    pdl_trigger();
     const LevelGeom& g = plan.lv[0];
     const int lframe = blockIdx.y, frame = lframe + buf.frameBase;
     const int by = blockIdx.x * L0_ROWS + (threadIdx.x >> 4);
+    pdl_wait();
     if (by >= g.planeRows) return;
     const int l16 = threadIdx.x & 15;
     const int y = reflect101(by - PAD_TOP, g.h);
@@ -369,6 +386,7 @@ __device__ __forceinline__ void resize_rows_walk(const uint8_t* __restrict__ S, 
 
 __global__ void __launch_bounds__(128) k_resize_rows(Plan plan, Buffers buf, int level, int rowsPerThread, int spitchArg, int dpitchArg)
 {
+    pdl_trigger();
     const LevelGeom& g = plan.lv[level];
     const LevelGeom& gp = plan.lv[level - 1];
     const int bx = 4 * (blockIdx.x * 32 + (threadIdx.x & 31));  // pitch is a multiple of 128: always inside the row
@@ -397,6 +415,7 @@ __global__ void __launch_bounds__(128) k_resize_rows(Plan plan, Buffers buf, int
     const uint8_t* S = plane_ptr(buf.pyr, gp, frame);
     uint8_t* D = plane_ptr(buf.pyr, g, frame);
     const uint32_t soff = (uint32_t)(PAD_TOP + rFirst) * spitch + colOff, doff = (uint32_t)(PAD_TOP + dy0) * dpitch + bx;
+    pdl_wait();
     const int2* srow = buf.srow + g.sTab + rFirst;
     // destination rows 1..19 and h-20..h-2 are repeated in the REFLECT_101 frame: only the threads that own such rows
     // (warp-uniform) run the walk with the extra stores
@@ -416,6 +435,7 @@ struct ResizeMaps { CUtensorMap m[FAST_TMA_LEVELS]; };  // indexed by SOURCE lev
 
 __global__ void __launch_bounds__(128) k_resize_rows_tma(Plan plan, Buffers buf, int level, int dpitchArg, const __grid_constant__ ResizeMaps maps)
 {
+    pdl_trigger();
     extern __shared__ __align__(128) unsigned char rsm[];
     __shared__ __align__(8) unsigned long long sBar;
     const LevelGeom& g = plan.lv[level];
@@ -443,6 +463,7 @@ __global__ void __launch_bounds__(128) k_resize_rows_tma(Plan plan, Buffers buf,
     // every warp of the CTA covers the same columns: the warp-wide minimum is the CTA's leftmost source word
     const uint32_t tileX0 = __reduce_min_sync(0xffffffffu, colOff) & ~15u;
     const int rTile0 = buf.yofs0[g.yTab + dyCta];
+    pdl_wait();
     if (threadIdx.x == 0) {
         const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&sBar);
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
@@ -582,6 +603,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf, co
     __shared__ int sSeg[FAST_T / 32];
     static_assert(FAST_MAXG == 4, "sHasIni is read as one 32-bit word");
 
+    pdl_trigger();
     const int frame = blockIdx.y + buf.frameBase;
     const int4 fuw = __ldg(reinterpret_cast<const int4*>(buf.fastUnits) + blockIdx.x);
     const int level = (short)(fuw.x & 0xffff), ci = fuw.x >> 16, j0 = (short)(fuw.y & 0xffff), iniX = fuw.y >> 16;
@@ -596,6 +618,7 @@ __global__ void __launch_bounds__(FAST_T) k_fast_band(Plan plan, Buffers buf, co
 
     // stage the band (TMA: one bulk tensor copy; otherwise 16-byte asynchronous copies, 16 lanes per row, 8 rows per pass),
     // zero the score tile meanwhile
+    pdl_wait();  // the pyramid is complete (and the previous batch's readers of the candidate lists are done)
     const int shift = (PAD_LEFT + iniX) & 15;  // both variants copy from a 16-byte aligned column (TMA: a coordinate off that grid is an illegal instruction)
     if (TMA) {
         if (threadIdx.x == 0) {
@@ -976,9 +999,11 @@ __global__ void __launch_bounds__(OCT_T) k_octree(Plan plan, Buffers buf, int no
     __shared__ int warpSums[33];
     __shared__ int sN, sNV, sFinish, sCut, sCtot;
 
+    pdl_trigger();
     const int level = blockIdx.x, frame = blockIdx.y + buf.frameBase;
     const LevelGeom& g = plan.lv[level];
     int* counter = buf.candCount + frame * plan.nlevels + level;
+    pdl_wait();
     const int M = min(*counter, g.candCap);
     const Cand* __restrict__ cand = buf.cand + (long long)frame * plan.candFrame + g.candOff;
     StagedKp* staged = buf.staged + (long long)frame * plan.kpCapFrame + g.kpOff;
@@ -1312,6 +1337,8 @@ __device__ __forceinline__ void blur_hrow(const uint32_t (&n)[3], uint32_t h[4])
 
 __global__ void __launch_bounds__(128) k_blur(Plan plan, Buffers buf)
 {
+    pdl_trigger();
+    pdl_wait();
     int level = 0;
     while (level + 1 < plan.nlevels && (int)blockIdx.x >= plan.lv[level + 1].blurOff) level++;
     const LevelGeom& g = plan.lv[level];
@@ -1397,6 +1424,7 @@ __global__ void __launch_bounds__(128) k_blur_tma(Plan plan, Buffers buf, const 
 {
     extern __shared__ __align__(128) unsigned char bsm[];
     __shared__ __align__(8) unsigned long long sBar;
+    pdl_trigger();
     int level = 0;
     while (level + 1 < plan.nlevels && (int)blockIdx.x >= plan.lv[level + 1].blurOff) level++;
     const LevelGeom& g = plan.lv[level];
@@ -1404,6 +1432,7 @@ __global__ void __launch_bounds__(128) k_blur_tma(Plan plan, Buffers buf, const 
     const int unit = blockIdx.x - g.blurOff;
     const int cgroups = (g.w + 127) >> 7;  // CTAs across (32 threads x 4 columns)
     const int cy = unit / cgroups, cxg = unit - cy * cgroups;
+    pdl_wait();
     if (threadIdx.x == 0) {
         const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&sBar);
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
@@ -1520,22 +1549,10 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
 {
     // two staging buffers per warp: keypoint i is processed from one while cp.async fills the other for keypoint i+1
     __shared__ __align__(16) uint8_t stage[DESC_WARPS][2][DESC_STAGE];
+    pdl_trigger();
     const int lframe = blockIdx.y, frame = lframe + buf.frameBase;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     __shared__ int cum[ORBX_MAX_LEVELS + 1];
-    if (threadIdx.x == 0) {
-        const int* lc = buf.levelCount + frame * plan.nlevels;
-        int acc = 0;
-        cum[0] = 0;
-        for (int l = 0; l < plan.nlevels; l++) { acc += lc[l]; cum[l + 1] = acc; }
-    }
-    __syncthreads();  // cum and patF (filled below, before the first use after another barrier)
-    const int total = min(cum[plan.nlevels], capacity);
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        outCounts[lframe] = total;
-        // a caller's capacity below the frame's keypoint count truncates the output: report it instead of hiding it
-        if (cum[plan.nlevels] > capacity) *reinterpret_cast<volatile int*>(buf.errFlag) = 1;
-    }
 
     // per-lane constants of the orientation pass: row v = lane - 15, columns u = 4k + b - 16
     const int v = lane - 15;
@@ -1561,7 +1578,20 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
         const signed char* pp = d_pattern + 32 * ln + 4 * k;
         patF[i] = make_float4((float)pp[0], (float)pp[1], (float)pp[2], (float)pp[3]);
     }
-    __syncthreads();
+    pdl_wait();  // everything above reads only constants: it overlaps the tail of the previous kernel
+    if (threadIdx.x == 0) {
+        const int* lc = buf.levelCount + frame * plan.nlevels;
+        int acc = 0;
+        cum[0] = 0;
+        for (int l = 0; l < plan.nlevels; l++) { acc += lc[l]; cum[l + 1] = acc; }
+    }
+    __syncthreads();  // cum and patF
+    const int total = min(cum[plan.nlevels], capacity);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        outCounts[lframe] = total;
+        // a caller's capacity below the frame's keypoint count truncates the output: report it instead of hiding it
+        if (cum[plan.nlevels] > capacity) *reinterpret_cast<volatile int*>(buf.errFlag) = 1;
+    }
     const uint32_t stage0 = (uint32_t)__cvta_generic_to_shared(&stage[wid][0][0]);
 
     // staging maps: a lane copies 16-byte segments; blurred = 37 rows x 4 segments (lane -> segment lane & 3, rows
@@ -2142,6 +2172,19 @@ static int ensure_plan(orbx_handle* h, int rows, int cols, int frames)
     return ORBX_OK;
 }
 
+// Kernel launch with (pdl) or without the programmatic-stream-serialization attribute (see pdl_trigger / pdl_wait).
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_k(bool pdl, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(std::forward<Args>(args))...);
+}
+
 // Enqueue every kernel of one batch on h->stream (+ the blur branch on h->streamBlur).
 // slot 0 = the handle's main stream; slot 1 = a second compute lane (own streams / events, arena frames offset by
 // frameBase) used by the pipelined host path so that consecutive chunks overlap.
@@ -2155,6 +2198,10 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
     cudaStream_t s = slot ? h->stream2 : h->stream, sb = profile ? s : (slot ? h->streamBlur2 : h->streamBlur);
     cudaEvent_t evFork = slot ? h->evFork2 : h->evFork, evJoin = slot ? h->evJoin2 : h->evJoin;
     int nl = 0;
+    // ORBX_PDL=1 / 0 forces programmatic dependent launch on / off; default off: measured 287 k against 290 k frames/s with the
+    // early trigger (the successor's CTAs take SM slots while they wait) -- see profiles/r2_state.md
+    static const int pdlEnv = [] { const char* e = std::getenv("ORBX_PDL"); return e ? std::atoi(e) : -1; }();
+    const bool pdl = (pdlEnv >= 0 ? pdlEnv != 0 : false) && !profile;
     // ORBX_DEBUG_SYNC=1 (never during capture: use with the graph disabled): synchronise after every launch and name the
     // kernel that failed
     static const bool dbgSync = [] { const char* e = std::getenv("ORBX_DEBUG_SYNC"); return e && std::atoi(e) != 0; }();
@@ -2170,7 +2217,7 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
     {
         const LevelGeom& g = P.lv[0];
         dim3 grid((g.planeRows + L0_ROWS - 1) / L0_ROWS, n);
-        k_level0<<<grid, 16 * L0_ROWS, 0, s>>>(P, B, dIn, inStep, inFrameStride);
+        ORBX_CUDA_TRY(launch_k(pdl, k_level0, grid, dim3(16 * L0_ROWS), 0, s, P, B, dIn, inStep, inFrameStride));
         nl++;
     }
     for (int l = 1; l < P.nlevels; l++) {
@@ -2181,8 +2228,8 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
         dim3 grid(g.pitch / 128, (g.h + 4 * rpt - 1) / (4 * rpt), n);
         static const bool rowsOff = [] { const char* e = std::getenv("ORBX_RESIZE_ROWS"); return e && std::atoi(e) == 0; }();  // A/B switch
         if (h->resizeTma && g.resizeTma && rpt == RZ_RPT && !rowsOff)
-            k_resize_rows_tma<<<grid, 128, RZ_TROWS * RZ_TP, s>>>(P, B, l, g.pitch, h->resizeMaps);
-        else if (g.resizeWords && g.resizeRows && !rowsOff) k_resize_rows<<<grid, 128, 0, s>>>(P, B, l, rpt, P.lv[l - 1].pitch, g.pitch);
+            ORBX_CUDA_TRY(launch_k(pdl, k_resize_rows_tma, grid, dim3(128), RZ_TROWS * RZ_TP, s, P, B, l, g.pitch, h->resizeMaps));
+        else if (g.resizeWords && g.resizeRows && !rowsOff) ORBX_CUDA_TRY(launch_k(pdl, k_resize_rows, grid, dim3(128), 0, s, P, B, l, rpt, P.lv[l - 1].pitch, g.pitch));
         else if (g.resizeWords) k_resize_words<<<grid, 128, 0, s>>>(P, B, l, rpt);
         else k_resize<<<grid, 128, 0, s>>>(P, B, l, rpt);
         nl++;
@@ -2198,8 +2245,8 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
         ORBX_CUDA_TRY(cudaEventRecord(evFork, s));
         ORBX_CUDA_TRY(cudaStreamWaitEvent(sb, evFork, 0));
     }
-    if (h->fastTma) k_fast_band<true><<<dim3(P.totalFastUnits, n), FAST_T, h->fastSmem, s>>>(P, B, h->fastMaps);
-    else k_fast_band<false><<<dim3(P.totalFastUnits, n), FAST_T, h->fastSmem, s>>>(P, B, h->fastMaps);
+    if (h->fastTma) ORBX_CUDA_TRY(launch_k(pdl, k_fast_band<true>, dim3(P.totalFastUnits, n), dim3(FAST_T), h->fastSmem, s, P, B, h->fastMaps));
+    else ORBX_CUDA_TRY(launch_k(pdl, k_fast_band<false>, dim3(P.totalFastUnits, n), dim3(FAST_T), h->fastSmem, s, P, B, h->fastMaps));
     nl++;
     ORBX_DBG_SYNC(h->fastTma ? "k_fast_band<TMA>" : "k_fast_band<cp.async>");
     if (!profile && blurAfterFast) {
@@ -2210,13 +2257,13 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
     // large batches: many small CTAs per SM (throughput); up to a few dozen frames: more threads per level (latency)
     static const int octForce = [] { const char* e = std::getenv("ORBX_OCT_T"); return e ? std::atoi(e) : 0; }();  // experiments only
     const int octT = octForce ? octForce : (n >= 112 ? 128 : (n >= 48 ? 256 : 512));  // measured: tools/sweep_octree.sh, profiles/r1h_sweep_octree.txt
-    if (octT == 128) k_octree<128><<<dim3(P.nlevels, n), 128, h->octSmem[0], s>>>(P, B, h->octNodeCap, h->octKeySmemCap[0], h->dKeyNode, P.candFrame);
-    else if (octT == 256) k_octree<256><<<dim3(P.nlevels, n), 256, h->octSmem[1], s>>>(P, B, h->octNodeCap, h->octKeySmemCap[1], h->dKeyNode, P.candFrame);
-    else k_octree<512><<<dim3(P.nlevels, n), 512, h->octSmem[2], s>>>(P, B, h->octNodeCap, h->octKeySmemCap[2], h->dKeyNode, P.candFrame);
+    if (octT == 128) ORBX_CUDA_TRY(launch_k(pdl, k_octree<128>, dim3(P.nlevels, n), dim3(128), h->octSmem[0], s, P, B, h->octNodeCap, h->octKeySmemCap[0], h->dKeyNode, P.candFrame));
+    else if (octT == 256) ORBX_CUDA_TRY(launch_k(pdl, k_octree<256>, dim3(P.nlevels, n), dim3(256), h->octSmem[1], s, P, B, h->octNodeCap, h->octKeySmemCap[1], h->dKeyNode, P.candFrame));
+    else ORBX_CUDA_TRY(launch_k(pdl, k_octree<512>, dim3(P.nlevels, n), dim3(512), h->octSmem[2], s, P, B, h->octNodeCap, h->octKeySmemCap[2], h->dKeyNode, P.candFrame));
     nl++;
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_BLUR], s));
-    if (h->blurTma) k_blur_tma<<<dim3(P.totalBlurUnits, n), 128, BLUR_TROWS * BLUR_TP, sb>>>(P, B, h->blurMaps);
-    else k_blur<<<dim3(P.totalBlurUnits, n), 128, 0, sb>>>(P, B);
+    if (h->blurTma) ORBX_CUDA_TRY(launch_k(pdl, k_blur_tma, dim3(P.totalBlurUnits, n), dim3(128), BLUR_TROWS * BLUR_TP, sb, P, B, h->blurMaps));
+    else ORBX_CUDA_TRY(launch_k(pdl, k_blur, dim3(P.totalBlurUnits, n), dim3(128), 0, sb, P, B));
     nl++;
     if (!profile) {
         ORBX_CUDA_TRY(cudaEventRecord(evJoin, sb));
@@ -2226,7 +2273,7 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
     {
         // keypoints per warp: the per-CTA constants are amortised over more keypoints when the batch alone fills the GPU
         const int perWarp = n >= 16 ? 12 : (n >= 4 ? 6 : 2);
-        k_describe<<<dim3((capacity + perWarp * DESC_WARPS - 1) / (perWarp * DESC_WARPS), n), DESC_WARPS * 32, 0, s>>>(P, B, dKps, dDesc, dCounts, capacity);
+        ORBX_CUDA_TRY(launch_k(pdl, k_describe, dim3((capacity + perWarp * DESC_WARPS - 1) / (perWarp * DESC_WARPS), n), dim3(DESC_WARPS * 32), 0, s, P, B, dKps, dDesc, dCounts, capacity));
     }
     nl++;
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_D2H], s));

@@ -444,3 +444,57 @@ def test_large_device_batch_stage_by_stage(gpu, oracle_mod, shape_name):
         assert kps[f, : counts[f]].tobytes() == okps.tobytes()
         assert np.array_equal(desc[f, : counts[f]], odesc)
     ex.close()
+
+
+_VARIANT_SCRIPT = r"""
+import hashlib, sys
+import numpy as np, torch
+import orbslam2commentedbyxcm_b200 as pkg
+from orbslam2commentedbyxcm_b200 import synth
+shape, cfg = synth.SHAPES["tum"], synth.PRESETS["tum"]
+distinct = [synth.gen_frame(shape, 70 + s) for s in range(4)]
+n = 96
+imgs = np.stack([distinct[i % 4] for i in range(n)])
+ex = pkg.ORBextractor(*cfg)
+cap = ex.max_keypoints(*shape)
+dev = torch.device("cuda", 0)
+d_img = torch.from_numpy(imgs).to(dev)
+d_kps = torch.zeros((n, cap, 6), dtype=torch.float32, device=dev)
+d_desc = torch.zeros((n, cap, 32), dtype=torch.uint8, device=dev)
+d_cnt = torch.zeros(n, dtype=torch.int32, device=dev)
+ex.extract_batch_device(d_img.data_ptr(), n, shape[0], shape[1], d_kps.data_ptr(), d_desc.data_ptr(), d_cnt.data_ptr(), cap)
+ex.sync()
+h = hashlib.sha256()
+cnt = d_cnt.cpu().numpy(); kps = d_kps.cpu().numpy(); desc = d_desc.cpu().numpy()
+for f in range(n):
+    h.update(cnt[f].tobytes()); h.update(kps[f, : cnt[f]].tobytes()); h.update(desc[f, : cnt[f]].tobytes())
+for l in range(cfg[2]):
+    h.update(ex.pyramid_level_padded(l, frame=n - 1).tobytes()); h.update(ex.debug_blurred(l, frame=n - 1).tobytes())
+k1, d1 = ex(distinct[0])   # single frame through the host path (latency variants of the kernels)
+h.update(k1.tobytes()); h.update(d1.tobytes())
+print("DIGEST", h.hexdigest())
+"""
+
+
+def test_kernel_variants_agree(gpu):
+    """Every staging variant of the kernels (TMA bulk tensor copies by default; ORBX_*_TMA=0 / ORBX_RESIZE_ROWS=0 select the
+    cp.async / global-load / destination-row-walk variants that also serve more than 8 pyramid levels; ORBX_PDL=1 launches the
+    chain with programmatic dependent launch) produces the same bytes: a 96-frame device batch + one host frame, each variant
+    in its own process (the switches are read once per process)."""
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    digests = {}
+    for name, env in [("default", {}), ("fast_cp_async", {"ORBX_FAST_TMA": "0"}), ("blur_global", {"ORBX_BLUR_TMA": "0"}),
+                      ("resize_global", {"ORBX_RESIZE_TMA": "0"}), ("resize_words", {"ORBX_RESIZE_ROWS": "0"}),
+                      ("pdl_on", {"ORBX_PDL": "1"}), ("pdl_off", {"ORBX_PDL": "0"})]:
+        e = dict(os.environ)
+        e.update(env)
+        e["PYTHONPATH"] = root + os.pathsep + e.get("PYTHONPATH", "")
+        out = subprocess.run([sys.executable, "-c", _VARIANT_SCRIPT], env=e, capture_output=True, text=True, timeout=300)
+        assert out.returncode == 0, (name, out.stderr[-2000:])
+        line = [l for l in out.stdout.splitlines() if l.startswith("DIGEST")]
+        assert line, (name, out.stdout[-500:], out.stderr[-500:])
+        digests[name] = line[0].split()[1]
+    assert len(set(digests.values())) == 1, digests
