@@ -1578,14 +1578,26 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
         const signed char* pp = d_pattern + 32 * ln + 4 * k;
         patF[i] = make_float4((float)pp[0], (float)pp[1], (float)pp[2], (float)pp[3]);
     }
+    // per-level constants of this CTA's frame in shared memory (the keypoint loop would otherwise index the kernel-argument
+    // plan dynamically and redo 64-bit products per keypoint): record index offset, plane offsets of both arenas, pitch
+    __shared__ int recOff[ORBX_MAX_LEVELS];           // staged record of keypoint gi of level l = gi + recOff[l]
+    __shared__ long long lvPlane[ORBX_MAX_LEVELS];    // byte offset of interior pixel (0, 0) of the frame's level-l plane
+    __shared__ int lvPitch[ORBX_MAX_LEVELS];
     pdl_wait();  // everything above reads only constants: it overlaps the tail of the previous kernel
     if (threadIdx.x == 0) {
         const int* lc = buf.levelCount + frame * plan.nlevels;
         int acc = 0;
         cum[0] = 0;
-        for (int l = 0; l < plan.nlevels; l++) { acc += lc[l]; cum[l + 1] = acc; }
+        for (int l = 0; l < plan.nlevels; l++) {
+            recOff[l] = plan.lv[l].kpOff - acc;
+            acc += lc[l];
+            cum[l + 1] = acc;
+            const LevelGeom& gl = plan.lv[l];
+            lvPlane[l] = gl.planeOff + (long long)frame * gl.planeBytes + (long long)PAD_TOP * gl.pitch + PAD_LEFT;
+            lvPitch[l] = gl.pitch;
+        }
     }
-    __syncthreads();  // cum and patF
+    __syncthreads();  // cum, the per-level constants and patF
     const int total = min(cum[plan.nlevels], capacity);
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         outCounts[lframe] = total;
@@ -1603,20 +1615,21 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
     // the 16-byte record of i+2 is being loaded (the copy addresses of a keypoint depend on its record, so loading the
     // record one iteration earlier keeps that global-load latency off the warp's critical path).
     int nLevel = 0;  // gidx only grows: the level search resumes where it stopped
+    const StagedKp* __restrict__ stagedFrame = buf.staged + (long long)frame * plan.kpCapFrame;
     auto load_record = [&](int gi, StagedKp& rec, int& lev) {
         while (gi >= cum[nLevel + 1]) nLevel++;
         lev = nLevel;
-        rec = buf.staged[(long long)frame * plan.kpCapFrame + plan.lv[nLevel].kpOff + (gi - cum[nLevel])];
+        rec = stagedFrame[gi + recOff[nLevel]];
     };
     auto fetch = [&](const StagedKp& rec, int lev, int slot) {
-        const LevelGeom& g = plan.lv[lev];
         const int cx = (int)rec.x, cy = (int)rec.y;
-        const int pitch = g.pitch;
+        const int pitch = lvPitch[lev];
+        const long long plane = lvPlane[lev];
         // interior column 0 is 32-byte aligned in both arenas, so the alignment of a column is that of its index
         const int bsh = (cx - 18) & 15, rsh = (cx - 16) & 15;
         const uint32_t sb = stage0 + slot * DESC_STAGE;
         if (bseg * 16 < bsh + 37) {
-            const uint8_t* pb = interior_ptr(buf.blur, g, frame) + (long long)(cy - 18 + brow) * pitch + (cx - 18 - bsh) + 16 * bseg;
+            const uint8_t* pb = buf.blur + plane + ((cy - 18 + brow) * pitch + (cx - 18 - bsh) + 16 * bseg);
             uint32_t dst = sb + brow * DESC_PP + 16 * bseg;
 #pragma unroll
             for (int i = 0; i < 5; i++) {
@@ -1625,7 +1638,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
             }
         }
         if (lane < 30 && rseg * 16 < rsh + 32) {
-            const uint8_t* pr = interior_ptr(buf.pyr, g, frame) + (long long)(cy - 15 + rrow) * pitch + (cx - 16 - rsh) + 16 * rseg;
+            const uint8_t* pr = buf.pyr + plane + ((cy - 15 + rrow) * pitch + (cx - 16 - rsh) + 16 * rseg);
             uint32_t dst = sb + DESC_PBYTES + rrow * ORI_PB + 16 * rseg;
 #pragma unroll
             for (int i = 0; i < 4; i++) {
