@@ -401,14 +401,22 @@ def test_device_api_reports_truncation(gpu):
     ex.close()
 
 
-@pytest.mark.parametrize("shape_name", ["tum", "kitti"])
+@pytest.mark.parametrize("shape_name", ["tum", "kitti", "euroc", "odd_scale_1.3", "ten_levels_1.1", "scale_1.9"])
 def test_large_device_batch_stage_by_stage(gpu, oracle_mod, shape_name):
     """The kernel variants that only batches select (k_resize_rows_tma at 16 rows per thread, 128-thread quad-tree CTAs, 12
     keypoints per warp in k_describe, blur beside the quad-tree): a 160-frame device-resident batch, every stage of three
     frames (first, middle, last) against the oracle."""
     import torch
 
-    shape, cfg = synth.SHAPES[shape_name], synth.PRESETS[shape_name]
+    custom = {
+        # scale 1.3: a CTA's source window exceeds the TMA tile rows -> the level falls back to the global-load walk
+        "odd_scale_1.3": ((333, 517), (700, 1.3, 5, 20, 7)),
+        # more than 8 levels: every TMA-staged kernel falls back (tensor maps are passed for 8 levels)
+        "ten_levels_1.1": ((300, 400), (800, 1.1, 10, 20, 7)),
+        # close to the 2x limit of the word-based resize kernels
+        "scale_1.9": ((480, 640), (600, 1.9, 4, 20, 7)),
+    }
+    shape, cfg = custom[shape_name] if shape_name in custom else (synth.SHAPES[shape_name], synth.PRESETS[shape_name])
     distinct = [synth.gen_frame(shape, 40 + s) for s in range(5)]
     n = 160
     imgs = np.stack([distinct[i % 5] for i in range(n)])
