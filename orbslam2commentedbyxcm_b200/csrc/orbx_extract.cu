@@ -1419,8 +1419,10 @@ __global__ void __launch_bounds__(128) k_blur(Plan plan, Buffers buf)
 constexpr int BLUR_TP = 160;                        // tile pitch in bytes = box width
 constexpr int BLUR_TROWS = 4 * BLUR_ROWS + 8;       // rows y - 3 .. y + 4 BLUR_ROWS + 4 (the last one belongs to an unused pair)
 struct BlurMaps { CUtensorMap m[FAST_TMA_LEVELS]; };
+constexpr int BT_WARPS = 4;                         // warps per CTA of k_blur_tma; a thread slides down BT_ROWS rows of the tile
+constexpr int BT_ROWS = 4 * BLUR_ROWS / BT_WARPS;   // (measured: 2 warps x 64 rows -- a smaller window warm-up share, half the warps -- 0.139 against 0.131 ms / 256 frames)
 
-__global__ void __launch_bounds__(128) k_blur_tma(Plan plan, Buffers buf, const __grid_constant__ BlurMaps maps)
+__global__ void __launch_bounds__(32 * BT_WARPS) k_blur_tma(Plan plan, Buffers buf, const __grid_constant__ BlurMaps maps)
 {
     extern __shared__ __align__(128) unsigned char bsm[];
     __shared__ __align__(8) unsigned long long sBar;
@@ -1458,11 +1460,11 @@ __global__ void __launch_bounds__(128) k_blur_tma(Plan plan, Buffers buf, const 
         } while (!done);
     }
     const int x = 4 * (cxg * 32 + (threadIdx.x & 31));
-    const int y0 = (cy * 4 + (threadIdx.x >> 5)) * BLUR_ROWS;
+    const int y0 = cy * 4 * BLUR_ROWS + (threadIdx.x >> 5) * BT_ROWS;
     if (x >= g.w || y0 >= g.h) return;
-    const int y1 = min(y0 + BLUR_ROWS, g.h);
+    const int y1 = min(y0 + BT_ROWS, g.h);
     // tile row 0 = image row 4 BLUR_ROWS cy - 3, tile column 16 = the CTA's first column
-    const uint32_t* sp = reinterpret_cast<const uint32_t*>(bsm + (threadIdx.x >> 5) * BLUR_ROWS * BLUR_TP + 16 + 4 * (threadIdx.x & 31));
+    const uint32_t* sp = reinterpret_cast<const uint32_t*>(bsm + (threadIdx.x >> 5) * BT_ROWS * BLUR_TP + 16 + 4 * (threadIdx.x & 31));
     constexpr int RW = BLUR_TP / 4;  // words per tile row
     uint8_t* dp = const_cast<uint8_t*>(interior_ptr(buf.blur, g, frame)) + x + (long long)y0 * g.pitch;
     const long long pitch = g.pitch;
@@ -2275,7 +2277,7 @@ static int enqueue(orbx_handle* h, const uint8_t* dIn, long long inStep, long lo
     else ORBX_CUDA_TRY(launch_k(pdl, k_octree<512>, dim3(P.nlevels, n), dim3(512), h->octSmem[2], s, P, B, h->octNodeCap, h->octKeySmemCap[2], h->dKeyNode, P.candFrame));
     nl++;
     if (profile) ORBX_CUDA_TRY(cudaEventRecord(h->evStage[ORBX_STAGE_BLUR], s));
-    if (h->blurTma) ORBX_CUDA_TRY(launch_k(pdl, k_blur_tma, dim3(P.totalBlurUnits, n), dim3(128), BLUR_TROWS * BLUR_TP, sb, P, B, h->blurMaps));
+    if (h->blurTma) ORBX_CUDA_TRY(launch_k(pdl, k_blur_tma, dim3(P.totalBlurUnits, n), dim3(32 * BT_WARPS), BLUR_TROWS * BLUR_TP, sb, P, B, h->blurMaps));
     else ORBX_CUDA_TRY(launch_k(pdl, k_blur, dim3(P.totalBlurUnits, n), dim3(128), 0, sb, P, B));
     nl++;
     if (!profile) {
