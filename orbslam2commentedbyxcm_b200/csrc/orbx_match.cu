@@ -1305,6 +1305,11 @@ struct orbm_context {
     // growable device scratch
     char* arena = nullptr;
     size_t arenaBytes = 0;
+    // page-locked mirror of the arena: the host arrays of one call are gathered here (same offsets) and go to the device in
+    // ONE copy (a search uploads ~20 small pageable arrays; one cudaMemcpyAsync each costs more than the search kernel)
+    char* hStage = nullptr;
+    size_t upLo = ~size_t(0), upHi = 0;
+    cudaEvent_t evUp = nullptr;   // the last flush has read hStage
     // partial results of the brute-force kernel
     int32_t* partials = nullptr;
     size_t partialsBytes = 0;
@@ -1337,8 +1342,12 @@ int ensure_arena(orbm_context* m, size_t bytes)
     if (bytes <= m->arenaBytes) return ORBX_OK;
     ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
     cudaFree(m->arena); m->arena = nullptr; m->arenaBytes = 0;
+    if (m->hStage) { cudaFreeHost(m->hStage); m->hStage = nullptr; }
     ORBX_CUDA_TRY(cudaMalloc(&m->arena, bytes));
+    ORBX_CUDA_TRY(cudaHostAlloc((void**)&m->hStage, bytes, cudaHostAllocDefault));
+    if (!m->evUp) ORBX_CUDA_TRY(cudaEventCreateWithFlags(&m->evUp, cudaEventDisableTiming));
     m->arenaBytes = bytes;
+    m->upLo = ~size_t(0); m->upHi = 0;
     return ORBX_OK;
 }
 int ensure_partials(orbm_context* m, size_t bytes)
@@ -1351,9 +1360,33 @@ int ensure_partials(orbm_context* m, size_t bytes)
     return ORBX_OK;
 }
 
+// Host -> device upload of one array.  Destinations inside the arena are gathered in the page-locked mirror and sent by
+// flush_up() as one copy (everything between the lowest and the highest staged byte: the carve-up places a call's uploads
+// next to each other; work areas that fall in between are overwritten with the mirror's stale bytes, which no kernel reads
+// before writing).  Every function that stages calls flush_up() before its first launch.
 template <typename T> int up(orbm_context* m, T* dst, const T* src, size_t n)
 {
-    if (n) ORBX_CUDA_TRY(cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyHostToDevice, m->stream));
+    if (!n) return ORBX_OK;
+    const char* d = reinterpret_cast<const char*>(dst);
+    const size_t bytes = n * sizeof(T);
+    if (m->hStage && d >= m->arena && d + bytes <= m->arena + m->arenaBytes) {
+        const size_t off = (size_t)(d - m->arena);
+        if (m->upHi == 0 && m->evUp) ORBX_CUDA_TRY(cudaEventSynchronize(m->evUp));  // first array of a call: the previous flush is done
+        std::memcpy(m->hStage + off, src, bytes);
+        m->upLo = std::min(m->upLo, off);
+        m->upHi = std::max(m->upHi, off + bytes);
+        return ORBX_OK;
+    }
+    ORBX_CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, m->stream));
+    return ORBX_OK;
+}
+int flush_up(orbm_context* m)
+{
+    if (m->upHi > m->upLo) {
+        ORBX_CUDA_TRY(cudaMemcpyAsync(m->arena + m->upLo, m->hStage + m->upLo, m->upHi - m->upLo, cudaMemcpyHostToDevice, m->stream));
+        ORBX_CUDA_TRY(cudaEventRecord(m->evUp, m->stream));
+    }
+    m->upLo = ~size_t(0); m->upHi = 0;
     return ORBX_OK;
 }
 
@@ -1465,6 +1498,8 @@ void orbm_destroy(orbm_context* m)
     if (m->stream) cudaStreamSynchronize(m->stream);
     exchange_release(m);
     cudaFree(m->arena); cudaFree(m->partials); cudaFree(m->qExp);
+    if (m->hStage) cudaFreeHost(m->hStage);
+    if (m->evUp) cudaEventDestroy(m->evUp);
     if (m->pinned) cudaFreeHost(m->pinned);
     if (m->stream) cudaStreamDestroy(m->stream);
     delete m;
@@ -1936,6 +1971,7 @@ int orbm_search_window(orbm_context* m, const orbm_frame_view* f, const float* f
     if (q->angle) UP(oPa, q->angle, nmp, float);
     UP(oPva, q->valid, nmp, uint8_t); UP(oPo, q->claims_block, nmp, uint8_t); UP(oPd, q->desc, 32 * (size_t)nmp, uint8_t);
 #undef UP
+    if ((rc = flush_up(m)) != ORBX_OK) return rc;
     ProjArgs a;
     a.nkp = nkp;
     a.kx = (float*)(A + oKx); a.ky = (float*)(A + oKy); a.koct = (int32_t*)(A + oKo);
@@ -2018,6 +2054,7 @@ int orbm_stereo_rows(orbm_context* m, int nl, const float* lx, const float* ly, 
     UP(oRx, rx, nr, float); UP(oRy, ry, nr, float); UP(oRo, roct, nr, int32_t); UP(oRd, rdesc, 32 * (size_t)nr, uint8_t);
     UP(oSf, scale_factors, nlevels, float);
 #undef UP
+    if ((rc = flush_up(m)) != ORBX_OK) return rc;
     k_stereo_rows<<<(nl + 7) / 8, 256, 0, m->stream>>>(nl, (float*)(A + oLx), (float*)(A + oLy), (int32_t*)(A + oLo),
                                                       (uint8_t*)(A + oLd), nr, (float*)(A + oRx), (float*)(A + oRy),
                                                       (int32_t*)(A + oRo), (uint8_t*)(A + oRd), (float*)(A + oSf), n_rows,
@@ -2059,6 +2096,7 @@ int orbm_search_by_bow(orbm_context* m, int nkf, const uint8_t* kf_desc, const f
     UP(oFd, f_desc, 32 * (size_t)nf, uint8_t); UP(oFa, f_angle, nf, float);
     UP(oFi, f_fv->node_id, nnf, int32_t); UP(oFs, f_fv->node_start, nnf + 1, int32_t); UP(oFf, f_fv->node_feat, nff, int32_t);
 #undef UP
+    if ((rc = flush_up(m)) != ORBX_OK) return rc;
     ORBX_CUDA_TRY(cudaMemsetAsync(A + oOut, 0xff, 4 * (size_t)nf, m->stream));
     ORBX_CUDA_TRY(cudaMemsetAsync(A + oBin, 0, 4 * (size_t)nf, m->stream));
     k_bow_nodes<<<(nnk + 3) / 4, 128, 0, m->stream>>>((uint8_t*)(A + oKd), (float*)(A + oKa), (uint8_t*)(A + oKm), nnk,
@@ -2134,6 +2172,7 @@ int orbm_stereo_match(orbm_context* m, orbx_handle* ex_left, int frame_left, orb
     UP(oRx, rx, nr, float); UP(oRy, ry, nr, float); UP(oRo, roct, nr, int32_t); UP(oRd, rdesc, 32 * (size_t)nr, uint8_t);
     UP(oSf, vl.scale, vl.nlevels, float);
 #undef UP
+    if ((rc = flush_up(m)) != ORBX_OK) return rc;
     k_stereo_rows<<<(nl + 7) / 8, 256, 0, m->stream>>>(nl, (float*)(A + oLx), (float*)(A + oLy), (int32_t*)(A + oLo),
                                                       (uint8_t*)(A + oLd), nr, (float*)(A + oRx), (float*)(A + oRy),
                                                       (int32_t*)(A + oRo), (uint8_t*)(A + oRd), (float*)(A + oSf), nRows, minD,
@@ -2218,6 +2257,7 @@ int orbm_bow_transform(orbm_context* m, const orbm_vocab* v, const uint8_t* desc
     if (rc != ORBX_OK) return rc;
     char* A = m->arena;
     if ((rc = up<uint8_t>(m, (uint8_t*)(A + oD), desc, 32 * (size_t)n)) != ORBX_OK) return rc;
+    if ((rc = flush_up(m)) != ORBX_OK) return rc;
     k_bow_transform<<<(n + 7) / 8, 256, 0, m->stream>>>(v->L, v->childStart, v->childIds, v->nodeDesc, v->wordId, v->weight,
                                                        (uint8_t*)(A + oD), n, levelsup, (int32_t*)(A + oW), (int32_t*)(A + oN),
                                                        (double*)(A + oWt));
@@ -2246,6 +2286,7 @@ int orbm_distinctive_descriptors(orbm_context* m, int n_sets, const int32_t* set
     char* A = m->arena;
     if ((rc = up<int32_t>(m, (int32_t*)(A + oS), set_start, n_sets + 1)) != ORBX_OK) return rc;
     if ((rc = up<uint8_t>(m, (uint8_t*)(A + oD), desc, 32 * (size_t)total)) != ORBX_OK) return rc;
+    if ((rc = flush_up(m)) != ORBX_OK) return rc;
     k_distinctive<<<(n_sets + 3) / 4, 128, 0, m->stream>>>(n_sets, (int32_t*)(A + oS), (uint8_t*)(A + oD), (int32_t*)(A + oB));
     ORBX_CUDA_TRY(cudaGetLastError());
     ORBX_CUDA_TRY(cudaMemcpyAsync(best_idx, A + oB, 4 * (size_t)n_sets, cudaMemcpyDeviceToHost, m->stream));
@@ -2283,6 +2324,7 @@ int orbm_search_by_bow_kf(orbm_context* m, int n1, const uint8_t* desc1, const f
     UP(o2d, desc2, 32 * (size_t)n2, uint8_t); UP(o2a, angle2, n2, float); UP(o2m, has_mp2, n2, uint8_t);
     UP(o2i, fv2->node_id, nn2, int32_t); UP(o2s, fv2->node_start, nn2 + 1, int32_t); UP(o2f, fv2->node_feat, nf2, int32_t);
 #undef UP
+    if ((rc = flush_up(m)) != ORBX_OK) return rc;
     ORBX_CUDA_TRY(cudaMemsetAsync(A + o21, 0xff, 4 * (size_t)n2, m->stream));
     ORBX_CUDA_TRY(cudaMemsetAsync(A + oBin, 0, 4 * (size_t)n2, m->stream));
     ORBX_CUDA_TRY(cudaMemsetAsync(A + o12, 0xff, 4 * (size_t)n1, m->stream));
@@ -2335,6 +2377,7 @@ static int search_best_enqueue(orbm_context* m, const char* who, const orbm_fram
     UP(oPr, q->radius, nq, float); UP(oPmin, q->min_level, nq, int32_t); UP(oPmax, q->max_level, nq, int32_t);
     UP(oPva, q->valid, nq, uint8_t); UP(oPd, q->desc, 32 * (size_t)nq, uint8_t);
 #undef UP
+    if ((rc = flush_up(m)) != ORBX_OK) return rc;
     BestArgs a;
     a.kx = (float*)(A + oKx); a.ky = (float*)(A + oKy); a.koct = (int32_t*)(A + oKo);
     a.uright = f->u_right ? (float*)(A + oUr) : nullptr;
@@ -2449,6 +2492,7 @@ int orbm_search_for_initialization(orbm_context* m, int n1, const int32_t* octav
     UP(oKx, f2->x, n2, float); UP(oKy, f2->y, n2, float); UP(oKo, f2->octave, n2, int32_t); UP(oKd, f2->desc, 32 * (size_t)n2, uint8_t);
     UP(oCs, f2->cell_start, ncell + 1, int32_t); UP(oCi, f2->cell_items, nitems, int32_t);
 #undef UP
+    if ((rc = flush_up(m)) != ORBX_OK) return rc;
     InitArgs a;
     a.n1 = n1; a.oct1 = (int32_t*)(A + o1o); a.angle1 = (float*)(A + o1a); a.desc1 = (uint8_t*)(A + o1d);
     a.prevx = (float*)(A + o1x); a.prevy = (float*)(A + o1y);
@@ -2515,6 +2559,7 @@ int orbm_search_for_triangulation(orbm_context* m, const orbm_kf_view* kf1, cons
     UP(o2i, kf2->fv->node_id, nn2, int32_t); UP(o2s, kf2->fv->node_start, nn2 + 1, int32_t); UP(o2f, kf2->fv->node_feat, nf2, int32_t);
     UP(oSc, scale_factors2, nlevels2, float); UP(oSg, level_sigma2_2, nlevels2, float);
 #undef UP
+    if ((rc = flush_up(m)) != ORBX_OK) return rc;
     ORBX_CUDA_TRY(cudaMemsetAsync(A + oM2, 0, 4 * (size_t)n2, m->stream));
     ORBX_CUDA_TRY(cudaMemsetAsync(A + o12, 0xff, 4 * (size_t)n1, m->stream));
     ORBX_CUDA_TRY(cudaMemsetAsync(A + oBin, 0, 4 * (size_t)n1, m->stream));
