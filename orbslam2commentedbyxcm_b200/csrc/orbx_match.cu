@@ -446,6 +446,10 @@ struct ProjArgs {
     int32_t* res;       // per map point: claimed keypoint or -1
     int32_t* claimA;    // per keypoint: smallest blocking map point index claiming it (INT_MAX = none)
     int32_t* claimB;
+    int32_t* claimC;    // third buffer: reset while the other two are read / written (one grid barrier per sweep)
+    // candidate lists of sweep 0 (every keypoint that passes a query's static gates, with its distance / order key): the
+    // later sweeps only re-apply the claims to them
+    uint32_t* listKey; int32_t* listIdx; int32_t* listCnt;
     int32_t* outMatch;  // per keypoint: last writer or -1
     int* changed;       // [2]
     int* nmatches;
@@ -461,6 +465,36 @@ __device__ __forceinline__ int rot_bin(float a1, float a2)
     return bin == HISTO_LENGTH ? 0 : bin;
 }
 
+constexpr int PROJ_LIST = 32;  // cached candidates per query (one per lane); a query with more is recomputed in full every sweep
+
+__device__ __forceinline__ int proj_finish(const ProjArgs& A, Top2& t)
+{
+    top2_warp_reduce(t);
+    if (t.p1 < 0) return -1;
+    const int bestDist = t.k1 >> 23;
+    if (bestDist > A.maxDist) return -1;
+    if (A.ratioMode == 1) {
+        const int bestLevel = A.koct[t.p1];
+        const int bestLevel2 = t.p2 >= 0 ? A.koct[t.p2] : -1;
+        const int bestDist2 = t.p2 >= 0 ? (int)(t.k2 >> 23) : 256;
+        if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(A.nnratio, (float)bestDist2)) return -1;
+    }
+    return t.p1;
+}
+
+// sweeps >= 1: the query's cached candidates (lane = list entry) against the previous sweep's claims
+__device__ __forceinline__ int proj_cached(const ProjArgs& A, int m, const int32_t* claimPrev, int lane, int cnt)
+{
+    Top2 t;
+    top2_init(t);
+    if (lane < cnt) {
+        const int idx = A.listIdx[(size_t)m * PROJ_LIST + lane];
+        if (!(claimPrev[idx] < m)) top2_push(t, A.listKey[(size_t)m * PROJ_LIST + lane], idx);
+    }
+    return proj_finish(A, t);
+}
+
+template <bool BUILD>
 __device__ int proj_one(const ProjArgs& A, int m, const int32_t* claimPrev, int lane)
 {
     if (!A.pvalid[m]) return -1;
@@ -502,53 +536,57 @@ __device__ int proj_one(const ProjArgs& A, int m, const int32_t* claimPrev, int 
                 if (ur > 0 && fabsf(__fsub_rn(xr, ur)) > rr) continue;
             }
             const int dist = hamming(D, load_desc(A.kdesc + 32 * (size_t)idx));
-            top2_push(t, ((uint32_t)dist << 23) | ((uint32_t)qc << 11) | (uint32_t)(k - s), idx);
+            const uint32_t key = ((uint32_t)dist << 23) | ((uint32_t)qc << 11) | (uint32_t)(k - s);
+            if (BUILD) {  // sweep 0: nothing is claimed yet, every gated candidate is recorded
+                const int pos = atomicAdd(&A.listCnt[m], 1);
+                if (pos < PROJ_LIST) { A.listKey[(size_t)m * PROJ_LIST + pos] = key; A.listIdx[(size_t)m * PROJ_LIST + pos] = idx; }
+            }
+            top2_push(t, key, idx);
         }
     }
-    top2_warp_reduce(t);
-    if (t.p1 < 0) return -1;
-    const int bestDist = t.k1 >> 23;
-    if (bestDist > A.maxDist) return -1;
-    if (A.ratioMode == 1) {
-        const int bestLevel = A.koct[t.p1];
-        const int bestLevel2 = t.p2 >= 0 ? A.koct[t.p2] : -1;
-        const int bestDist2 = t.p2 >= 0 ? (int)(t.k2 >> 23) : 256;
-        if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(A.nnratio, (float)bestDist2)) return -1;
-    }
-    return t.p1;
+    return proj_finish(A, t);
 }
 
-__global__ void __launch_bounds__(256) k_proj_search(ProjArgs A)
+// threads per CTA: few large CTAs keep the grid-wide barriers between the sweeps cheap (one arrival per CTA)
+static const int PROJ_T = [] { const char* e = std::getenv("ORBX_PROJ_T"); const int v = e ? std::atoi(e) : 0; return v >= 32 && v <= 1024 && v % 32 == 0 ? v : 1024; }();
+
+__global__ void __launch_bounds__(1024) k_proj_search(ProjArgs A)
 {
     cg::grid_group grid = cg::this_grid();
     const int lane = threadIdx.x & 31;
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int nwarps = (gridDim.x * blockDim.x) >> 5;
     const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gthreads = gridDim.x * blockDim.x;
-    int32_t* claimPrev = A.claimA;
-    int32_t* claimNext = A.claimB;
-    for (int i = gtid; i < A.nkp; i += gthreads) { claimPrev[i] = 0x7fffffff; A.outMatch[i] = -1; }
-    for (int m = gtid; m < A.nmp; m += gthreads) A.res[m] = -1;
-    if (gtid == 0) { A.changed[0] = 0; A.changed[1] = 0; *A.nmatches = 0; }
+    int32_t* claimPrev = A.claimA;   // claims of the previous sweep's results (read)
+    int32_t* claimNext = A.claimB;   // claims of this sweep's results (atomicMin as the results are produced)
+    int32_t* claimSpare = A.claimC;  // reset during this sweep, the next sweep's claimNext
+    for (int i = gtid; i < A.nkp; i += gthreads) { claimPrev[i] = 0x7fffffff; claimNext[i] = 0x7fffffff; A.outMatch[i] = -1; }
+    for (int m = gtid; m < A.nmp; m += gthreads) { A.res[m] = -1; A.listCnt[m] = 0; }
+    if (gtid == 0) { A.changed[0] = 0; A.changed[1] = 0; A.changed[2] = 0; *A.nmatches = 0; }
     if (gtid < HISTO_LENGTH) A.hist[gtid] = 0;
     grid.sync();
     int sweep = 0;
     for (;; sweep++) {
-        int* chg = A.changed + (sweep & 1);
+        // three flags in rotation: with ONE barrier per sweep a thread may still be reading sweep k's flag (after that sweep's
+        // barrier) while a faster one is already in sweep k + 1, so the flag reset there is the one of sweep k + 2
+        int* chg = A.changed + sweep % 3;
         for (int m = warp; m < A.nmp; m += nwarps) {
-            const int r = proj_one(A, m, claimPrev, lane);
-            if (lane == 0 && r != A.res[m]) { A.res[m] = r; *chg = 1; }
+            int r;
+            if (sweep == 0) r = proj_one<true>(A, m, claimPrev, lane);
+            else {
+                const int cnt = A.listCnt[m];  // warp-uniform
+                r = cnt <= PROJ_LIST ? proj_cached(A, m, claimPrev, lane, cnt) : proj_one<false>(A, m, claimPrev, lane);
+            }
+            if (lane == 0) {
+                if (r != A.res[m]) { A.res[m] = r; *chg = 1; }
+                if (r >= 0 && A.pobs[m]) atomicMin(&claimNext[r], m);
+            }
         }
-        for (int i = gtid; i < A.nkp; i += gthreads) claimNext[i] = 0x7fffffff;
-        if (gtid == 0) A.changed[(sweep + 1) & 1] = 0;
+        for (int i = gtid; i < A.nkp; i += gthreads) claimSpare[i] = 0x7fffffff;
+        if (gtid == 0) A.changed[(sweep + 1) % 3] = 0;
         grid.sync();
         if (*chg == 0) break;  // fixed point: res == sequential result
-        for (int m = gtid; m < A.nmp; m += gthreads) {
-            const int r = A.res[m];
-            if (r >= 0 && A.pobs[m]) atomicMin(&claimNext[r], m);
-        }
-        grid.sync();
-        int32_t* t = claimPrev; claimPrev = claimNext; claimNext = t;
+        int32_t* t = claimPrev; claimPrev = claimNext; claimNext = claimSpare; claimSpare = t;
     }
     // F.mvpMapPoints[bestIdx] = pMP: the last writer wins
     int local = 0;
@@ -1955,7 +1993,8 @@ int orbm_search_window(orbm_context* m, const orbm_frame_view* f, const float* f
                  oPr = c.take(4 * (size_t)nmp), oPmin = c.take(4 * (size_t)nmp), oPmax = c.take(4 * (size_t)nmp),
                  oPa = c.take(4 * (size_t)nmp), oPva = c.take(nmp), oPo = c.take(nmp), oPd = c.take(32 * (size_t)nmp);
     const size_t oRes = c.take(4 * (size_t)nmp), oCa = c.take(4 * (size_t)nkp), oCb = c.take(4 * (size_t)nkp),
-                 oOut = c.take(4 * (size_t)nkp), oMisc = c.take(256);
+                 oCc = c.take(4 * (size_t)nkp), oLk = c.take(4 * (size_t)nmp * PROJ_LIST), oLi = c.take(4 * (size_t)nmp * PROJ_LIST),
+                 oLc = c.take(4 * (size_t)nmp), oOut = c.take(4 * (size_t)nkp), oMisc = c.take(256);
     int rc = ensure_arena(m, c.off);
     if (rc != ORBX_OK) return rc;
     char* A = m->arena;
@@ -1985,18 +2024,25 @@ int orbm_search_window(orbm_context* m, const orbm_frame_view* f, const float* f
     a.pmin = (int32_t*)(A + oPmin); a.pmax = (int32_t*)(A + oPmax); a.pangle = (float*)(A + oPa);
     a.pvalid = (uint8_t*)(A + oPva); a.pobs = (uint8_t*)(A + oPo); a.pdesc = (uint8_t*)(A + oPd);
     a.nnratio = nnratio; a.maxDist = max_dist; a.ratioMode = ratio_mode; a.checkOri = check_orientation ? 1 : 0;
-    a.res = (int32_t*)(A + oRes); a.claimA = (int32_t*)(A + oCa); a.claimB = (int32_t*)(A + oCb);
+    a.res = (int32_t*)(A + oRes); a.claimA = (int32_t*)(A + oCa); a.claimB = (int32_t*)(A + oCb); a.claimC = (int32_t*)(A + oCc);
+    a.listKey = (uint32_t*)(A + oLk); a.listIdx = (int32_t*)(A + oLi); a.listCnt = (int32_t*)(A + oLc);
     a.outMatch = (int32_t*)(A + oOut);
-    a.changed = (int*)(A + oMisc); a.nmatches = a.changed + 2; a.sweeps = a.changed + 3; a.hist = a.changed + 8;
+    a.changed = (int*)(A + oMisc); a.nmatches = a.changed + 3; a.sweeps = a.changed + 4; a.hist = a.changed + 8;  // changed[3]
     int perSM = 0;
-    ORBX_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_proj_search, 256, 0));
-    const int want = (nmp + 7) / 8;  // 8 warps per CTA, one warp per query
+    ORBX_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_proj_search, PROJ_T, 0));
+    const int want = (nmp + PROJ_T / 32 - 1) / (PROJ_T / 32);  // one warp per query
     const int grid = std::max(1, std::min(want, perSM * m->numSMs));
     void* args[] = {&a};
-    ORBX_CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_proj_search, dim3(grid), dim3(256), args, 0, m->stream));
+    ORBX_CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_proj_search, dim3(grid), dim3(PROJ_T), args, 0, m->stream));
     ORBX_CUDA_TRY(cudaMemcpyAsync(out_match, a.outMatch, 4 * (size_t)nkp, cudaMemcpyDeviceToHost, m->stream));
     ORBX_CUDA_TRY(cudaMemcpyAsync(nmatches, a.nmatches, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
     ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
+    static const bool projDebug = std::getenv("ORBX_PROJ_DEBUG") != nullptr;
+    if (projDebug) {
+        int sw = 0;
+        cudaMemcpy(&sw, a.sweeps, sizeof(int), cudaMemcpyDeviceToHost);
+        std::fprintf(stderr, "k_proj_search: %d queries, %d keypoints, grid %d x %d, %d sweeps\n", nmp, nkp, grid, PROJ_T, sw);
+    }
     return ORBX_OK;
 }
 

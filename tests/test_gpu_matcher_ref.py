@@ -192,3 +192,16 @@ def test_mono_frame(gpu, gold, shape_name, seed, cam, dist):
     cs, ci = m.AssignFeaturesToGrid(ux, uy, float(bounds[0]), float(bounds[1]), float(w_inv), float(h_inv))
     assert np.array_equal(cs, gold["mono_%s_cell_start" % shape_name]) and np.array_equal(ci, gold["mono_%s_cell_items" % shape_name])
     m.close(); ex.close()
+
+
+def test_search_by_projection_is_stable_across_fresh_contexts(gpu, oracle_mod, gold):
+    """The sweeps of k_proj_search are separated by ONE grid-wide barrier each (three convergence flags in rotation, three claim
+    buffers): a flag or buffer reused one sweep too early shows up as a run-to-run difference, mostly on a context's first call."""
+    c = mc.SBP_CASES[0]
+    frame, mps = mc.sbp_case(oracle_mod, *c)
+    for rep in range(6):
+        m = gpu.ORBmatcher(0.8, True)
+        for call in range(2):
+            n, out = m.SearchByProjection(frame, mps, c[3])
+            assert np.array_equal(_packed(n, out), gold["sbp_%s_%d" % (c[0], c[1])]), (rep, call)
+        m.close()
