@@ -308,10 +308,34 @@ def other_configs(pkg, torch, dev, local):
         dm, nl, nr, nmatch = stereo_frame()
         tt.append(time.perf_counter() - t0)
         tm.append(dm)
+    # the reference's own threading (src/Frame.cc:127-131): left and right extraction on two host threads, one extractor each
+    from concurrent.futures import ThreadPoolExecutor
+    pool = ThreadPoolExecutor(1)
+
+    def stereo_frame_threads():
+        fut = pool.submit(exR.extract_batch, right[None], oR)
+        kl, dl, cl = exL.extract_batch(left[None], out=oL)
+        kr, dr, cr = fut.result()
+        L = dict(x=kl[0, :cl[0]]["x"], y=kl[0, :cl[0]]["y"], octave=kl[0, :cl[0]]["octave"], desc=dl[0, :cl[0]])
+        R = dict(x=kr[0, :cr[0]]["x"], y=kr[0, :cr[0]]["y"], octave=kr[0, :cr[0]]["octave"], desc=dr[0, :cr[0]])
+        ur, dp = mt.ComputeStereoMatches(exL, exR, L, R, bf, mb)
+        return int((ur >= 0).sum())
+
+    for _ in range(10):
+        stereo_frame_threads()
+    t2 = []
+    for _ in range(100):
+        t0 = time.perf_counter()
+        nmatch2 = stereo_frame_threads()
+        t2.append(time.perf_counter() - t0)
+    pool.shutdown()
+    if nmatch2 != nmatch:
+        raise RuntimeError("bench: threaded stereo front-end disagrees with the sequential one")
     out["C2_euroc_stereo_752x480_1200"] = {
-        "ms_per_stereo_frame_e2e": 1e3 * float(np.median(tt)), "ms_stereo_match_e2e": 1e3 * float(np.median(tm)),
+        "ms_per_stereo_frame_e2e": 1e3 * float(np.median(tt)), "ms_per_stereo_frame_e2e_two_threads": 1e3 * float(np.median(t2)),
+        "ms_stereo_match_e2e": 1e3 * float(np.median(tm)),
         "keypoints_left": nl, "keypoints_right": nr, "stereo_matches": nmatch,
-        "note": "extract L + extract R (host in/out, sequential calls) + orbm_stereo_match (row search + SAD + outliers)"}
+        "note": "extract L + extract R (host in/out; sequential calls, and on two host threads like src/Frame.cc:127-131) + orbm_stereo_match (row search + SAD + outliers)"}
     exL.close(); exR.close()
     # ---- C3 ----
     shape, cfg = synth.SHAPES["kitti"], synth.PRESETS["kitti"]

@@ -1171,7 +1171,9 @@ __device__ int init_one(const InitArgs& A, int i1, const int32_t* distPrev, int 
     return t.p1;
 }
 
-__global__ void __launch_bounds__(256) k_init_search(InitArgs A)
+static const int INIT_T = [] { const char* e = std::getenv("ORBX_INIT_T"); const int v = e ? std::atoi(e) : 0; return v >= 32 && v <= 1024 && v % 32 == 0 ? v : 512; }();  // threads per CTA (grid barriers cost one arrival per CTA)
+
+__global__ void __launch_bounds__(1024) k_init_search(InitArgs A)
 {
     // cooperative grid (one warp per F1 feature and sweep, as many CTAs as level-0 features need): the sweeps are separated by
     // grid-wide barriers; flags, histogram and the kept bins live in A.misc
@@ -2551,11 +2553,11 @@ int orbm_search_for_initialization(orbm_context* m, int n1, const int32_t* octav
     a.nmatches = (int*)(A + oMisc); a.sweeps = a.nmatches + 1; a.misc = a.nmatches + 8;
     {
         int perSM = 0;
-        ORBX_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_init_search, 256, 0));
-        const int want = (n1 + 7) / 8;  // 8 warps per CTA, one warp per F1 feature
+        ORBX_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_init_search, INIT_T, 0));
+        const int want = (n1 + INIT_T / 32 - 1) / (INIT_T / 32);  // one warp per F1 feature
         const int grid = std::max(1, std::min(want, perSM * m->numSMs));
         void* args[] = {&a};
-        ORBX_CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_init_search, dim3(grid), dim3(256), args, 0, m->stream));
+        ORBX_CUDA_TRY(cudaLaunchCooperativeKernel((void*)k_init_search, dim3(grid), dim3(INIT_T), args, 0, m->stream));
     }
     ORBX_CUDA_TRY(cudaMemcpyAsync(out_match12, a.out12, 4 * (size_t)n1, cudaMemcpyDeviceToHost, m->stream));
     ORBX_CUDA_TRY(cudaMemcpyAsync(nmatches, a.nmatches, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
