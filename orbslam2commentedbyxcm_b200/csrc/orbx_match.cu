@@ -1171,7 +1171,7 @@ __device__ int init_one(const InitArgs& A, int i1, const int32_t* distPrev, int 
     return t.p1;
 }
 
-static const int INIT_T = [] { const char* e = std::getenv("ORBX_INIT_T"); const int v = e ? std::atoi(e) : 0; return v >= 32 && v <= 1024 && v % 32 == 0 ? v : 512; }();  // threads per CTA (grid barriers cost one arrival per CTA)
+static const int INIT_T = [] { const char* e = std::getenv("ORBX_INIT_T"); const int v = e ? std::atoi(e) : 0; return v >= 32 && v <= 1024 && v % 32 == 0 ? v : 1024; }();  // threads per CTA (grid barriers cost one arrival per CTA; measured 256 / 512 / 1024: 0.288 / 0.263 / 0.242 ms per call)
 
 __global__ void __launch_bounds__(1024) k_init_search(InitArgs A)
 {
