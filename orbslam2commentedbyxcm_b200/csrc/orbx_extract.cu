@@ -1616,12 +1616,26 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
     // Three keypoints are in flight per warp: i is processed from shared memory, the patches of i+1 are being copied, and
     // the 16-byte record of i+2 is being loaded (the copy addresses of a keypoint depend on its record, so loading the
     // record one iteration earlier keeps that global-load latency off the warp's critical path).
-    int nLevel = 0;  // gidx only grows: the level search resumes where it stopped
+    // The warp's keypoints are gidx0 + j * gstride, j < 32 (the grid gives a warp at most 12): lane j loads the 16-byte record
+    // of keypoint j once, up front (level by a per-lane search), and the loop broadcasts record i / i + 1 with shuffles.
     const StagedKp* __restrict__ stagedFrame = buf.staged + (long long)frame * plan.kpCapFrame;
-    auto load_record = [&](int gi, StagedKp& rec, int& lev) {
-        while (gi >= cum[nLevel + 1]) nLevel++;
-        lev = nLevel;
-        rec = stagedFrame[gi + recOff[nLevel]];
+    const int gstride = gridDim.x * DESC_WARPS;
+    const int gidx0 = blockIdx.x * DESC_WARPS + wid;
+    float myX = 0.f, myY = 0.f, myResp = 0.f;
+    int myLev = 0;
+    {
+        const int gi = gidx0 + lane * gstride;
+        if (gi < total) {
+            while (gi >= cum[myLev + 1]) myLev++;
+            const StagedKp rec = stagedFrame[gi + recOff[myLev]];
+            myX = rec.x; myY = rec.y; myResp = rec.response;
+        }
+    }
+    auto load_record = [&](int it, StagedKp& rec, int& lev) {  // it = index of the keypoint within the warp's sequence (< 32)
+        rec.x = __shfl_sync(0xffffffffu, myX, it);
+        rec.y = __shfl_sync(0xffffffffu, myY, it);
+        rec.response = __shfl_sync(0xffffffffu, myResp, it);
+        lev = __shfl_sync(0xffffffffu, myLev, it);
     };
     auto fetch = [&](const StagedKp& rec, int lev, int slot) {
         const int cx = (int)rec.x, cy = (int)rec.y;
@@ -1650,19 +1664,18 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
-    const int gstride = gridDim.x * DESC_WARPS;
-    int gidx = blockIdx.x * DESC_WARPS + wid;
-    int slot = 0;
-    StagedKp kp, kpN, kpNN;
-    int level = 0, levelN = 0, levelNN = 0;
+    int gidx = gidx0;
+    int slot = 0, it = 0;
+    StagedKp kp, kpN;
+    int level = 0, levelN = 0;
     kp.x = kp.y = kp.angle = kp.response = 0.f;
-    kpN = kp; kpNN = kp;
+    kpN = kp;
     if (gidx < total) {
-        load_record(gidx, kp, level);
+        load_record(0, kp, level);
         fetch(kp, level, 0);
-        if (gidx + gstride < total) load_record(gidx + gstride, kpN, levelN);
+        load_record(1, kpN, levelN);   // (lanes without a keypoint hold zeros: used only when gidx + gstride < total)
     }
-    for (; gidx < total; gidx += gstride, slot ^= 1) {
+    for (; gidx < total; gidx += gstride, slot ^= 1, it++) {
         const LevelGeom& g = plan.lv[level];
         // cx and the warp index are the same in every lane; taking them through REDUX tells the compiler so, which keeps the
         // patch base + alignment offset in a uniform register (shared-memory loads then address [R + UR])
@@ -1673,7 +1686,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
         asm volatile("cp.async.wait_all;" ::: "memory");
         __syncwarp();  // this keypoint's patches have landed (all lanes); the previous keypoint's reads of the other buffer are done
         if (gidx + gstride < total) fetch(kpN, levelN, slot ^ 1);
-        if (gidx + 2 * gstride < total) load_record(gidx + 2 * gstride, kpNN, levelNN);
+
         // ---- IC_Angle ----
         int m10 = 0, rs = 0;
         if (lane < 31) {
@@ -1730,7 +1743,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
             outKps[o] = r;
         }
         kp = kpN; level = levelN;
-        kpN = kpNN; levelN = levelNN;
+        load_record(it + 2, kpN, levelN);   // keypoint it + 2 of this warp (zeros past the end; lane index wraps harmlessly)
     }
 }
 
