@@ -1522,7 +1522,6 @@ constexpr int DESC_WARPS = 4;
 constexpr int DESC_PP = 64;   // blurred patch pitch in bytes: 37 columns at any 16-byte alignment span <= 15 + 37 = 52 bytes
 constexpr int ORI_PB = 48;    // raw patch pitch in bytes: 31 columns at any 16-byte alignment span <= 15 + 31 = 46 bytes
 constexpr int DESC_PBYTES = 37 * DESC_PP, ORI_BYTES = 31 * ORI_PB;
-constexpr int DESC_STAGE = DESC_PBYTES + ORI_BYTES;  // one staging buffer: blurred patch, then raw disc rows
 
 __device__ __forceinline__ int dp4a_u8s8(uint32_t a, uint32_t b, int c)
 {
@@ -1546,11 +1545,13 @@ __device__ __forceinline__ void ori_row(const uint4 q0, const uint4 q1, const ui
     }
 }
 
-__global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buffers buf, orbx_keypoint* outKps,
+__global__ void __launch_bounds__(DESC_WARPS * 32, 7) k_describe(Plan plan, Buffers buf, orbx_keypoint* outKps,
                                                                uint8_t* outDesc, int* outCounts, int capacity)
 {
-    // two staging buffers per warp: keypoint i is processed from one while cp.async fills the other for keypoint i+1
-    __shared__ __align__(16) uint8_t stage[DESC_WARPS][2][DESC_STAGE];
+    // per warp: two buffers for the blurred patch (keypoint i is sampled from one while cp.async fills the other for i + 1) and
+    // ONE for the raw disc rows (IC_Angle reads them into registers first thing; the copy for i + 1 starts right after)
+    __shared__ __align__(16) uint8_t stageB[DESC_WARPS][2][DESC_PBYTES];
+    __shared__ __align__(16) uint8_t stageR[DESC_WARPS][ORI_BYTES];
     pdl_trigger();
     const int lframe = blockIdx.y, frame = lframe + buf.frameBase;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -1606,7 +1607,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
         // a caller's capacity below the frame's keypoint count truncates the output: report it instead of hiding it
         if (cum[plan.nlevels] > capacity) *reinterpret_cast<volatile int*>(buf.errFlag) = 1;
     }
-    const uint32_t stage0 = (uint32_t)__cvta_generic_to_shared(&stage[wid][0][0]);
+    const uint32_t stage0 = (uint32_t)__cvta_generic_to_shared(&stageB[wid][0][0]);
+    const uint32_t stageR0 = (uint32_t)__cvta_generic_to_shared(&stageR[wid][0]);
 
     // staging maps: a lane copies 16-byte segments; blurred = 37 rows x 4 segments (lane -> segment lane & 3, rows
     // (lane >> 2) + 8 i), raw = 31 rows x 3 segments (lanes 0..29 -> segment lane % 3, rows lane / 3 + 10 i).  Segments
@@ -1637,25 +1639,29 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
         rec.response = __shfl_sync(0xffffffffu, myResp, it);
         lev = __shfl_sync(0xffffffffu, myLev, it);
     };
-    auto fetch = [&](const StagedKp& rec, int lev, int slot) {
+    auto fetch_blur = [&](const StagedKp& rec, int lev, int slot) {
         const int cx = (int)rec.x, cy = (int)rec.y;
         const int pitch = lvPitch[lev];
-        const long long plane = lvPlane[lev];
         // interior column 0 is 32-byte aligned in both arenas, so the alignment of a column is that of its index
-        const int bsh = (cx - 18) & 15, rsh = (cx - 16) & 15;
-        const uint32_t sb = stage0 + slot * DESC_STAGE;
+        const int bsh = (cx - 18) & 15;
         if (bseg * 16 < bsh + 37) {
-            const uint8_t* pb = buf.blur + plane + ((cy - 18 + brow) * pitch + (cx - 18 - bsh) + 16 * bseg);
-            uint32_t dst = sb + brow * DESC_PP + 16 * bseg;
+            const uint8_t* pb = buf.blur + lvPlane[lev] + ((cy - 18 + brow) * pitch + (cx - 18 - bsh) + 16 * bseg);
+            uint32_t dst = stage0 + slot * DESC_PBYTES + brow * DESC_PP + 16 * bseg;
 #pragma unroll
             for (int i = 0; i < 5; i++) {
                 if (brow + 8 * i < 37)
                     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 8 * i * DESC_PP), "l"(pb + (long long)(8 * i) * pitch) : "memory");
             }
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    auto fetch_raw = [&](const StagedKp& rec, int lev) {
+        const int cx = (int)rec.x, cy = (int)rec.y;
+        const int pitch = lvPitch[lev];
+        const int rsh = (cx - 16) & 15;
         if (lane < 30 && rseg * 16 < rsh + 32) {
-            const uint8_t* pr = buf.pyr + plane + ((cy - 15 + rrow) * pitch + (cx - 16 - rsh) + 16 * rseg);
-            uint32_t dst = sb + DESC_PBYTES + rrow * ORI_PB + 16 * rseg;
+            const uint8_t* pr = buf.pyr + lvPlane[lev] + ((cy - 15 + rrow) * pitch + (cx - 16 - rsh) + 16 * rseg);
+            uint32_t dst = stageR0 + rrow * ORI_PB + 16 * rseg;
 #pragma unroll
             for (int i = 0; i < 4; i++) {
                 if (rrow + 10 * i < 31)
@@ -1672,7 +1678,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
     kpN = kp;
     if (gidx < total) {
         load_record(0, kp, level);
-        fetch(kp, level, 0);
+        fetch_blur(kp, level, 0);
+        fetch_raw(kp, level);
         load_record(1, kpN, levelN);   // (lanes without a keypoint hold zeros: used only when gidx + gstride < total)
     }
     for (; gidx < total; gidx += gstride, slot ^= 1, it++) {
@@ -1681,11 +1688,11 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
         // patch base + alignment offset in a uniform register (shared-memory loads then address [R + UR])
         const int cx = __reduce_min_sync(0xffffffffu, (int)kp.x);
         const int widu = __reduce_min_sync(0xffffffffu, wid);
-        const uint8_t* P = &stage[widu][slot][0];
-        const uint8_t* R = P + DESC_PBYTES;
+        const uint8_t* P = &stageB[widu][slot][0];
+        const uint8_t* R = &stageR[widu][0];
         asm volatile("cp.async.wait_all;" ::: "memory");
         __syncwarp();  // this keypoint's patches have landed (all lanes); the previous keypoint's reads of the other buffer are done
-        if (gidx + gstride < total) fetch(kpN, levelN, slot ^ 1);
+        if (gidx + gstride < total) fetch_blur(kpN, levelN, slot ^ 1);
 
         // ---- IC_Angle ----
         int m10 = 0, rs = 0;
@@ -1703,6 +1710,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 6) k_describe(Plan plan, Buff
         }
         m10 = __reduce_add_sync(0xffffffffu, m10);
         const int m01 = __reduce_add_sync(0xffffffffu, v * rs);
+        // every lane has consumed its raw row (the reductions above are warp-wide): the raw buffer takes the next keypoint's rows
+        if (gidx + gstride < total) fetch_raw(kpN, levelN);
         const float angle = fast_atan2_dev((float)m01, (float)m10);
         // ---- descriptor ----
         const float factorPI = 0.0174532924f;  // (float)(CV_PI/180.f)
