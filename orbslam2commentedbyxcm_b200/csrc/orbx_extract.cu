@@ -3,13 +3,17 @@
 // and every pyramid level that stage can process concurrently.
 //
 // Reference behaviour reproduced (paths in the reference tree):
-//   k_level0 / k_resize  ORBextractor::ComputePyramid            src/ORBextractor.cc:1635-1694
+//   k_level0 / k_resize_rows(_tma)  ORBextractor::ComputePyramid src/ORBextractor.cc:1635-1694
+//                        (fallbacks k_resize_words, k_resize)
 //   k_fast_band          cell loop of ComputeKeyPointsOctTree    src/ORBextractor.cc:1017-1122 (+ cv::FAST 9/16, NMS)
 //   k_octree             DistributeOctTree / DivideNode          src/ORBextractor.cc:581-1013, :1124-1164
 //                        + IC_Angle / cv::fastAtan2              src/ORBextractor.cc:59-106, :559-570
-//   k_blur               cv::GaussianBlur 7x7 sigma 2            src/ORBextractor.cc:1587-1595
+//   k_blur_tma / k_blur  cv::GaussianBlur 7x7 sigma 2            src/ORBextractor.cc:1587-1595
 //   k_describe           computeOrbDescriptor                    src/ORBextractor.cc:118-172, :1613-1622
 // Results are bit-identical to the CPU oracle (oracle/orb_oracle.cc); tests/test_gpu_extractor.py checks that.
+// Blackwell paths: the FAST bands, the blur tiles and the resize source windows are staged by TMA bulk tensor copies
+// (cp.async.bulk.tensor.3d + mbarrier, per-level tensor maps as __grid_constant__ arguments); every such kernel has a
+// non-TMA variant of the same arithmetic (environment switches in INTEGRATION.md section 5, tested equal).
 #include "orbx_common.cuh"
 #include "sincosf_dev.cuh"
 #include "orbx_internal.h"
