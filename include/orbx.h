@@ -175,6 +175,40 @@ int orbm_sync(orbm_context* m);
 int orbm_bruteforce(orbm_context* m, const uint8_t* q, int nq, const uint8_t* db, int ndb, int idx_offset,
                     int32_t* best, int32_t* best_idx, int32_t* second, int mem_kind);
 
+/* orbm_bruteforce for callers that are not allowed to allocate device memory.  (No counterpart in the reference: it
+ * exists for the integration, not for parity -- the result is orbm_bruteforce's, bit for bit.)
+ *
+ * Who needs it: a SLAM front end that was handed a fixed device-memory budget and runs next to another owner of the GPU
+ * (a planner, an inference engine, a caching allocator that has already reserved the rest of the memory), where a
+ * cudaMalloc in the middle of tracking can fail or stall; and hard-real-time loops, because cudaMalloc / cudaFree
+ * serialise against all work on the device and have no latency bound.  orbm_bruteforce grows a scratch buffer with
+ * cudaMalloc whenever a larger search arrives; this entry point never does.  It needs no orbm_context, creates no
+ * stream or event, and calls no cudaMalloc, cudaFree or any other allocating routine.
+ *
+ * The scratch (one best / index / second triple per database chunk and query) is a fixed array inside liborbx.so:
+ * ORBM_NOALLOC_SCRATCH_BYTES = 12 MiB of device memory on EVERY GPU that loads the library, held from load to process
+ * exit, whether or not this function is called.  That bounds the search: nq <= ORBM_NOALLOC_MAX_NQ and
+ * ndb <= ORBM_NOALLOC_MAX_NDB, anything larger is refused with ORBX_ERR_CAPACITY (orbx_last_error() says why) and
+ * nothing is launched.
+ *
+ *   device       CUDA device ordinal (< 64); made current by the call
+ *   stream       a cudaStream_t of that device, or NULL for the default stream; both kernels are enqueued on it and the
+ *                call returns without waiting -- synchronise the stream before reading the outputs
+ *   q, db, best, best_idx, second   DEVICE pointers, laid out as for orbm_bruteforce with mem_kind = 1
+ *
+ * The first call on each device looks up the scratch array's device address and the SM count (a few microseconds of
+ * host work, no allocation) and caches them; make that first call during set-up, before any stream capture begins.
+ * All calls on one device share the one array.  Nothing in it has to be cleared between calls -- each call overwrites
+ * every slot it later reads -- but two calls whose kernels can overlap on the GPU (different streams, or different host
+ * threads on different streams) race on it and return garbage: keep calls on one device in one stream, or order them
+ * with events. */
+#define ORBM_NOALLOC_MAX_NQ 4096                /* queries per call (two frames' worth of features) */
+#define ORBM_NOALLOC_MAX_NDB (1 << 24)          /* database rows per call (512 MiB of descriptors) */
+#define ORBM_NOALLOC_SCRATCH_SLOTS (1 << 20)    /* (chunk, query) triples the static array holds */
+#define ORBM_NOALLOC_SCRATCH_BYTES (3 * 4 * ORBM_NOALLOC_SCRATCH_SLOTS)
+int orbm_bruteforce_noalloc(int device, void* stream, const uint8_t* q, int nq, const uint8_t* db, int ndb,
+                            int idx_offset, int32_t* best, int32_t* best_idx, int32_t* second);
+
 /* Deterministic merge of `nparts` partial results (e.g. one per database shard, parts ordered by ascending
  * index range): equals the sequential scan over the concatenated database.  DEVICE pointers,
  * best/best_idx/second laid out [part][nq].  Used after the all-gather in the sharded search. */

@@ -87,6 +87,7 @@ SIGNATURES = {
     "orbm_stream": (_vp, [_vp]),
     "orbm_sync": (_i, [_vp]),
     "orbm_bruteforce": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _i]),
+    "orbm_bruteforce_noalloc": (_i, [_i, _vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp]),
     "orbm_db_create": (_i, [_vp, _vp, _i, _i, C.POINTER(_vp)]),
     "orbm_db_destroy": (None, [_vp]),
     "orbm_bruteforce_db": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _i]),

@@ -16,6 +16,7 @@
 #include <cooperative_groups.h>
 #include <algorithm>
 #include <cstdlib>
+#include <mutex>
 #include <vector>
 
 namespace cg = cooperative_groups;
@@ -1499,6 +1500,44 @@ int bruteforce_partials_tc(orbm_context* m, const orbm_db* d, const uint8_t* dq,
 
 }  // namespace
 
+// ------------------------------------------------------------------------------------------------------
+// Scratch of orbm_bruteforce_noalloc (include/orbx.h): the per-chunk partial results of k_bruteforce live in this
+// array, which is part of the loaded module, instead of in a cudaMalloc'ed buffer of a context.  It costs
+// ORBM_NOALLOC_SCRATCH_BYTES (12 MiB) of device memory on every GPU that loads liborbx.so, from the load until the
+// process exits, whether the entry point is ever called or not.
+//
+// In HOST code the name g_bfNoAllocScratch is only a handle for the symbol, not a device address: handing it to a
+// kernel would fault (or, on a system where the GPU can reach host memory, scribble over host memory without any error).
+// noalloc_setup() asks the runtime for the real address, once per device, with that device current.
+// ------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) int32_t g_bfNoAllocScratch[3 * ORBM_NOALLOC_SCRATCH_SLOTS];
+static_assert(sizeof(g_bfNoAllocScratch) == ORBM_NOALLOC_SCRATCH_BYTES, "header and scratch array disagree");
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noallocMutex;
+int32_t* g_noallocPtr[NOALLOC_MAX_DEVICES] = {};  // device address of g_bfNoAllocScratch on each GPU (nullptr = not set up)
+int g_noallocSMs[NOALLOC_MAX_DEVICES] = {};
+
+// First call on `device` (which must be current): resolves the scratch symbol and caches the SM count.  No allocation.
+int noalloc_setup(int device, int32_t** scratch, int* numSMs)
+{
+    std::lock_guard<std::mutex> lock(g_noallocMutex);
+    if (!g_noallocPtr[device]) {
+        void* p = nullptr;
+        ORBX_CUDA_TRY(cudaGetSymbolAddress(&p, g_bfNoAllocScratch));
+        int sms = 0;
+        ORBX_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+        if (!p || sms <= 0) { set_error("orbm_bruteforce_noalloc: could not resolve the scratch symbol on device %d", device); return ORBX_ERR_CUDA; }
+        g_noallocSMs[device] = sms;
+        g_noallocPtr[device] = static_cast<int32_t*>(p);
+    }
+    *scratch = g_noallocPtr[device];
+    *numSMs = g_noallocSMs[device];
+    return ORBX_OK;
+}
+}  // namespace
+
 extern "C" {
 
 int orbm_descriptor_distance(const uint8_t* a, const uint8_t* b)
@@ -1633,6 +1672,48 @@ int orbm_merge_partials(orbm_context* m, const int32_t* best, const int32_t* bes
     }
     ORBX_CUDA_TRY(cudaSetDevice(m->device));
     k_merge_partials<<<(nq + 7) / 8, 256, 0, m->stream>>>(best, best_idx, second, nparts, nq, out_best, out_idx, out_second);
+    ORBX_CUDA_TRY(cudaGetLastError());
+    return ORBX_OK;
+}
+
+// orbm_bruteforce for callers that must not allocate: same two kernels (k_bruteforce<1>, k_merge_partials), the chunk
+// partials in the module's static scratch array instead of orbm_context::partials.  No context, no cudaMalloc / cudaFree.
+int orbm_bruteforce_noalloc(int device, void* stream, const uint8_t* q, int nq, const uint8_t* db, int ndb, int idx_offset,
+                            int32_t* best, int32_t* best_idx, int32_t* second)
+{
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES || !q || nq <= 0 || ndb < 0 || (ndb > 0 && !db) || !best || !best_idx || !second) {
+        set_error("orbm_bruteforce_noalloc: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    if (nq > ORBM_NOALLOC_MAX_NQ || ndb > ORBM_NOALLOC_MAX_NDB) {
+        set_error("orbm_bruteforce_noalloc: nq = %d / ndb = %d exceed the fixed scratch (at most %d queries x %d database rows); "
+                  "use orbm_bruteforce, which grows its scratch with cudaMalloc", nq, ndb, ORBM_NOALLOC_MAX_NQ, ORBM_NOALLOC_MAX_NDB);
+        return ORBX_ERR_CAPACITY;
+    }
+    ORBX_CUDA_TRY(cudaSetDevice(device));
+    int32_t* scratch = nullptr;
+    int numSMs = 0;
+    int rc = noalloc_setup(device, &scratch, &numSMs);
+    if (rc != ORBX_OK) return rc;
+    // chunking of bruteforce_partials, with the chunk count also bounded by the scratch slots
+    const int qBlocks = (nq + BF_T * BF_RQ - 1) / (BF_T * BF_RQ);
+    const int target = std::max(1, std::min((numSMs * 4) / qBlocks, ORBM_NOALLOC_SCRATCH_SLOTS / nq));
+    int chunk = (ndb + target - 1) / target;
+    chunk = std::max(BF_TILE, (chunk + BF_TILE - 1) / BF_TILE * BF_TILE);
+    const int nChunks = std::max(1, (ndb + chunk - 1) / chunk);
+    if (chunk > (1 << 21) || (size_t)nChunks * nq > (size_t)ORBM_NOALLOC_SCRATCH_SLOTS) {
+        set_error("orbm_bruteforce_noalloc: %d chunks of %d rows x %d queries do not fit the fixed scratch", nChunks, chunk, nq);
+        return ORBX_ERR_CAPACITY;
+    }
+    // every slot k_merge_partials reads ([chunk < nChunks][query < nq] of the three planes) is written by k_bruteforce of
+    // this same call, so what the previous call left in the array never needs clearing
+    int32_t* pBest = scratch;
+    int32_t* pIdx = pBest + (size_t)nChunks * nq;
+    int32_t* pSecond = pIdx + (size_t)nChunks * nq;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    k_bruteforce<BF_DEFAULT_VARIANT><<<dim3(nChunks, qBlocks), BF_T, 0, st>>>(q, nq, db, ndb, chunk, idx_offset, pBest, pIdx, pSecond);
+    ORBX_CUDA_TRY(cudaGetLastError());
+    k_merge_partials<<<(nq + 7) / 8, 256, 0, st>>>(pBest, pIdx, pSecond, nChunks, nq, best, best_idx, second);
     ORBX_CUDA_TRY(cudaGetLastError());
     return ORBX_OK;
 }
