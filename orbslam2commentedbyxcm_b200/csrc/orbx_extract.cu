@@ -1841,9 +1841,9 @@ static void free_arenas(orbx_handle* h)
 {
     cudaFree(h->buf.pyr); cudaFree(h->buf.blur); cudaFree(h->buf.cand); cudaFree(h->buf.candCount);
     cudaFree(h->buf.candCountDbg); cudaFree(h->buf.staged); cudaFree(h->buf.levelCount);
-    cudaFree(h->dTabs); cudaFree(h->dKeyNode); cudaFree(h->dFastUnits);
+    cudaFree(h->dTabs); cudaFree(h->dKeyNode); cudaFree(h->dFastUnits); cudaFree(h->dZeros);
     h->buf = Buffers{};
-    h->dTabs = nullptr; h->dKeyNode = nullptr; h->dFastUnits = nullptr;
+    h->dTabs = nullptr; h->dKeyNode = nullptr; h->dFastUnits = nullptr; h->dZeros = nullptr;
     for (auto& g : h->graphs) cudaGraphExecDestroy(g.exec);
     h->graphs.clear();
     h->havePlan = false;
