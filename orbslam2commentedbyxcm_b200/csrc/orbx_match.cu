@@ -1349,6 +1349,7 @@ struct orbm_context {
     // page-locked mirror of the arena: the host arrays of one call are gathered here (same offsets) and go to the device in
     // ONE copy (a search uploads ~20 small pageable arrays; one cudaMemcpyAsync each costs more than the search kernel)
     char* hStage = nullptr;
+    size_t hStageBytes = 0;
     size_t upLo = ~size_t(0), upHi = 0;
     cudaEvent_t evUp = nullptr;   // the last flush has read hStage
     // partial results of the brute-force kernel
@@ -1368,6 +1369,7 @@ struct orbm_context {
     // tensor-core search: +-1 expansion of the queries of the current call
     int8_t* qExp = nullptr;
     size_t qExpBytes = 0;
+    bool tcAttrSet = false;      // >48 KB dynamic shared memory opt-in of k_bruteforce_tc / tc2 done on this context's device
     int stereoOutlierMode = 0;   // 0 = this reference (block inside the keypoint loop), 1 = upstream ORB-SLAM2 (after the loop)
 };
 
@@ -1380,15 +1382,32 @@ struct Carver {
 
 int ensure_arena(orbm_context* m, size_t bytes)
 {
+    // every staging function calls this before its first up(): a call that returned early between up() and flush_up()
+    // must not leave its range behind for the next call to flush
+    m->upLo = ~size_t(0); m->upHi = 0;
     if (bytes <= m->arenaBytes) return ORBX_OK;
     ORBX_CUDA_TRY(cudaStreamSynchronize(m->stream));
     cudaFree(m->arena); m->arena = nullptr; m->arenaBytes = 0;
-    if (m->hStage) { cudaFreeHost(m->hStage); m->hStage = nullptr; }
     ORBX_CUDA_TRY(cudaMalloc(&m->arena, bytes));
-    ORBX_CUDA_TRY(cudaHostAlloc((void**)&m->hStage, bytes, cudaHostAllocDefault));
     if (!m->evUp) ORBX_CUDA_TRY(cudaEventCreateWithFlags(&m->evUp, cudaEventDisableTiming));
     m->arenaBytes = bytes;
-    m->upLo = ~size_t(0); m->upHi = 0;
+    return ORBX_OK;
+}
+// The page-locked mirror covers only the span that up() stages (offsets [0, need) of the arena): entry points that copy
+// straight from caller memory (orbm_bruteforce with a large host database, undistort, assign_grid) never pin anything.
+int ensure_stage(orbm_context* m, size_t need)
+{
+    if (need <= m->hStageBytes) return ORBX_OK;
+    const size_t nb = std::min(m->arenaBytes, std::max(std::max(need, 2 * m->hStageBytes), size_t(256) << 10));
+    char* p = nullptr;
+    ORBX_CUDA_TRY(cudaHostAlloc((void**)&p, nb, cudaHostAllocDefault));
+    if (m->hStage) {
+        if (m->evUp) cudaEventSynchronize(m->evUp);  // the last flush no longer reads the old mirror
+        if (m->upHi > m->upLo) std::memcpy(p + m->upLo, m->hStage + m->upLo, m->upHi - m->upLo);  // arrays staged earlier in this call
+        cudaFreeHost(m->hStage);
+    }
+    m->hStage = p;
+    m->hStageBytes = nb;
     return ORBX_OK;
 }
 int ensure_partials(orbm_context* m, size_t bytes)
@@ -1410,8 +1429,10 @@ template <typename T> int up(orbm_context* m, T* dst, const T* src, size_t n)
     if (!n) return ORBX_OK;
     const char* d = reinterpret_cast<const char*>(dst);
     const size_t bytes = n * sizeof(T);
-    if (m->hStage && d >= m->arena && d + bytes <= m->arena + m->arenaBytes) {
+    if (m->arena && d >= m->arena && d + bytes <= m->arena + m->arenaBytes) {
         const size_t off = (size_t)(d - m->arena);
+        const int rc = ensure_stage(m, off + bytes);
+        if (rc != ORBX_OK) return rc;
         if (m->upHi == 0 && m->evUp) ORBX_CUDA_TRY(cudaEventSynchronize(m->evUp));  // first array of a call: the previous flush is done
         std::memcpy(m->hStage + off, src, bytes);
         m->upLo = std::min(m->upLo, off);
@@ -1481,11 +1502,10 @@ int bruteforce_partials_tc(orbm_context* m, const orbm_db* d, const uint8_t* dq,
     int32_t* pBest = m->partials;
     int32_t* pIdx = pBest + (size_t)nChunks * nq;
     int32_t* pSecond = pIdx + (size_t)nChunks * nq;
-    static bool attr = false;
-    if (!attr) {
+    if (!m->tcAttrSet) {  // the opt-in is per device / context, and contexts may live on several threads: one flag per context
         ORBX_CUDA_TRY(cudaFuncSetAttribute(tc::k_bruteforce_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
         ORBX_CUDA_TRY(cudaFuncSetAttribute(tc::k_bruteforce_tc2, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM2_BYTES));
-        attr = true;
+        m->tcAttrSet = true;
     }
     if (pair)
         tc::k_bruteforce_tc2<<<dim3(2 * nChunks, qTiles), tc::THREADS2, tc::SMEM2_BYTES, m->stream>>>(mapA, d->map128, nq, d->ndb, (int)chunk,
