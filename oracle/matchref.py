@@ -103,6 +103,9 @@ def lib():
         L.orbr_stereo_n.argtypes = [_vp, _i]
         L.orbr_stereo_get.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
         L.orbr_stereo_free.argtypes = [_vp]
+        L.orbr_last_ms.restype = C.c_double
+        L.orbr_last_ms.argtypes = [_i]
+        L.orbr_set_timing.argtypes = [_i]
         _lib = L
         _libs[[k for k, v in _PATHS.items() if v == _PATH][0]] = L
     return _lib
@@ -408,6 +411,16 @@ class RefFrame:
         self.cell_items = ci[: self.cell_start[-1]]
         L.orbr_stereo_free(h)
         self.h = None
+
+
+def last_ms(which):
+    """Wall time (ms) of the reference call alone inside the last wrapper invocation: 0 = SearchByProjection(Frame, MPs, th),
+    1 = stereo Frame constructor, 2 = Frame::ComputeStereoMatches re-run (after set_timing(True))."""
+    return float(lib().orbr_last_ms(which))
+
+
+def set_timing(on):
+    lib().orbr_set_timing(1 if on else 0)
 
 
 def stereo_frame(left, right, cfg, fx, fy, cx, cy, mbf, dist4=None):

@@ -25,6 +25,7 @@
 #include "Map.h"
 #include "ORBVocabulary.h"
 #include "Converter.h"
+#include <chrono>
 #include <cstdint>
 #include <cstring>
 #include <cstddef>
@@ -49,6 +50,19 @@ extern "C" int orbr_is_gpu_adapter() { return 1; }
 #else
 extern "C" int orbr_is_gpu_adapter() { return 0; }
 #endif
+
+// Wall time of the REFERENCE call alone inside the last wrapper invocation (the World / MapPoint set-up around it is the
+// harness's, not the reference's): bench.py's cpu_baseline for configs 2 and 3.  0 = SearchByProjection(Frame, MapPoints, th),
+// 1 = the stereo Frame constructor (two extractor threads + ComputeStereoMatches + grid, src/Frame.cc:113-165),
+// 2 = Frame::ComputeStereoMatches run once more on the constructed frame (only after orbr_set_timing(1)).
+static double g_lastMs[3] = {0, 0, 0};
+static int g_timing = 0;
+static double ms_since(std::chrono::steady_clock::time_point t0)
+{
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+extern "C" double orbr_last_ms(int which) { return which >= 0 && which < 3 ? g_lastMs[which] : -1.0; }
+extern "C" void orbr_set_timing(int on) { g_timing = on; }
 
 // src/Converter.cc:29-40 restated: one 1 x 32 row per descriptor
 std::vector<cv::Mat> Converter::toDescriptorVector(const cv::Mat& Descriptors)
@@ -309,7 +323,9 @@ int orbr_search_by_projection(const orbr_frame_in* f, int nmp, const float* px, 
         index[mp] = m;
     }
     ORBmatcher matcher(nnratio, true);
+    const auto t0 = std::chrono::steady_clock::now();
     const int n = matcher.SearchByProjection(*F, v, th);
+    g_lastMs[0] = ms_since(t0);
     for (int i = 0; i < F->N; i++) {
         auto it = index.find(F->mvpMapPoints[i]);
         out_match[i] = it == index.end() ? -1 : it->second;
@@ -698,7 +714,16 @@ void* orbr_stereo_frame(const uint8_t* left, const uint8_t* right, int rows, int
     std::memset(mem, 0, sizeof(Frame));
     const float mb = mbf / fx;
     std::memcpy((char*)mem + offsetof(Frame, mb), &mb, sizeof(float));
+    const auto t0 = std::chrono::steady_clock::now();
     o->F = new (mem) Frame(imL, imR, 0.0, o->exL, o->exR, nullptr, K, D, mbf, 40.f * mb);
+    g_lastMs[1] = ms_since(t0);
+#ifndef ORBR_GPU_ADAPTER
+    if (g_timing) {  // same inputs -> same result: the call only exists to be timed
+        const auto t1 = std::chrono::steady_clock::now();
+        o->F->ComputeStereoMatches();
+        g_lastMs[2] = ms_since(t1);
+    }
+#endif
 #ifdef ORBR_GPU_ADAPTER
     // the constructor above ran the reference's CPU ComputeStereoMatches on the pyramids the adapter extractor downloaded;
     // replace its result by the body replacement INTEGRATION.md gives for src/Frame.cc:673-885

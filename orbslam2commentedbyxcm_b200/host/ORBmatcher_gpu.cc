@@ -137,16 +137,19 @@ void FromFrame(const Frame& F, Features& A)
 }
 
 // KeyFrame::mGrid is protected (include/KeyFrame.h:353).  It is a copy of the Frame's grid (src/KeyFrame.cc:53-59), which
-// Frame::AssignFeaturesToGrid fills in keypoint order, so rebuilding it from mvKeysUn with orbm_assign_grid (the same
-// PosInGrid arithmetic, parity-tested against the reference) gives the same cells in the same order.
+// Frame::AssignFeaturesToGrid fills in keypoint order with the Frame's FLOAT bounds (Frame::mnMinX / mnMinY, public statics,
+// src/Frame.cc:654): rebuilding it from mvKeysUn with orbm_assign_grid (the same PosInGrid arithmetic, parity-tested against
+// the reference) and those float bounds gives the same cells in the same order.  KeyFrame::mnMinX / mnMinY are the bounds
+// truncated to int (include/KeyFrame.h:331-332) and only the window arithmetic of KeyFrame::GetFeaturesInArea uses them
+// (src/KeyFrame.cc:630-640): the view is bound to those.  The two differ on a distorted camera (non-integral bounds).
 bool FromKeyFrame(orbm_context* ctx, const KeyFrame* pKF, Features& A)
 {
     A.Keypoints(pKF->mvKeysUn, pKF->mvuRight, pKF->mDescriptors);
     A.cellStart.assign(FRAME_GRID_COLS * FRAME_GRID_ROWS + 1, 0);
     A.cellItems.assign(A.v.n > 0 ? A.v.n : 1, 0);
     if (A.v.n > 0 &&
-        Failed(orbm_assign_grid(ctx, A.x.data(), A.y.data(), A.v.n, (float)pKF->mnMinX, (float)pKF->mnMinY, pKF->mfGridElementWidthInv,
-                                pKF->mfGridElementHeightInv, A.cellStart.data(), A.cellItems.data(), 0), "orbm_assign_grid"))
+        Failed(orbm_assign_grid(ctx, A.x.data(), A.y.data(), A.v.n, Frame::mnMinX, Frame::mnMinY, Frame::mfGridElementWidthInv,
+                                Frame::mfGridElementHeightInv, A.cellStart.data(), A.cellItems.data(), 0), "orbm_assign_grid"))
         return false;
     A.Bind((float)pKF->mnMinX, (float)pKF->mnMinY, pKF->mfGridElementWidthInv, pKF->mfGridElementHeightInv, pKF->mvScaleFactors);
     return true;

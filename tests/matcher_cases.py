@@ -252,6 +252,31 @@ def scw_case(oracle_mod, shape_name, seed):
     return frame, projected_points(frame, 2500, seed, th=10.0)
 
 
+# Key frames of a DISTORTED camera: the image bounds are non-integral and negative (src/Frame.cc:630-668), so the KeyFrame's
+# int bounds (include/KeyFrame.h:331-332, used by GetFeaturesInArea's window) differ from the Frame's float bounds its grid
+# was built with (src/KeyFrame.cc:53-59).  Object-level harness only (tests/test_gpu_adapter_objects.py): (shape, seed, kind).
+SHIFTED_BOUNDS = (-13.4, -7.7, 11.3, 9.6)   # min_x, min_y, max_x - cols, max_y - rows
+SHIFTED_CASES = [("tum", 6, "scw"), ("tum", 7, "fuse")]
+
+
+def shifted_case(oracle_mod, shape_name, seed, kind):
+    frame, kps = frame_view(oracle_mod, shape_name, seed, occupied_p=0.3 if kind == "scw" else 0.1)
+    rows, cols = synth.SHAPES[shape_name]
+    mnx, mny = np.float32(SHIFTED_BOUNDS[0]), np.float32(SHIFTED_BOUNDS[1])
+    mxx, mxy = np.float32(cols + SHIFTED_BOUNDS[2]), np.float32(rows + SHIFTED_BOUNDS[3])
+    frame["min_x"], frame["min_y"], frame["max_x"], frame["max_y"] = float(mnx), float(mny), float(mxx), float(mxy)
+    frame["w_inv"] = float(np.float32(64.0) / (mxx - mnx))
+    frame["h_inv"] = float(np.float32(48.0) / (mxy - mny))
+    frame["cell_start"], frame["cell_items"] = oracle_mod.assign_grid(frame["x"], frame["y"], frame["min_x"], frame["min_y"],
+                                                                      frame["w_inv"], frame["h_inv"])
+    q = projected_points(frame, 2500, seed, th=10.0 if kind == "scw" else 3.0)
+    # a share of the projections right at the low bounds, where float and truncated bounds pick different cell windows
+    rng = np.random.Generator(np.random.PCG64(seed + 31))
+    edge = rng.random(len(q["x"])) < 0.15
+    q["x"] = np.where(edge, frame["x"][rng.integers(0, len(frame["x"]), len(edge))] * np.float32(0.05), q["x"]).astype(np.float32)
+    return frame, q
+
+
 FUSE_CASES = [("tum", 0, 1, False), ("euroc", 1, 1, True), ("kitti", 2, 0, False), ("tum", 3, 0, True)]
 
 
@@ -386,6 +411,13 @@ def reference_outputs(oracle_mod, R):
         kf1, q21, kf2, q12 = sim3_case(oracle_mod, shape_name, seed)
         n, m = R.search_by_sim3(kf1, q21, kf2, q12, 7.5)
         out["sim3_%s_%d" % (shape_name, seed)] = np.concatenate([[n], m]).astype(np.int32)
+    for shape_name, seed, kind in SHIFTED_CASES:
+        frame, q = shifted_case(oracle_mod, shape_name, seed, kind)
+        if kind == "scw":
+            n, m = R.search_by_projection_scw(frame, q, int(q["th"]))
+        else:
+            n, m = R.fuse(frame, q, q["th"], mbf=MBF, scw=False)
+        out["shifted_%s_%s_%d" % (kind, shape_name, seed)] = np.concatenate([[n], m]).astype(np.int32)
     start, desc = distinctive_case()
     out["distinctive"] = R.distinctive_descriptors(start, desc)
     for k, L, levelsup in VOCAB_CASES:
