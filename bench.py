@@ -193,6 +193,55 @@ def measured_traffic(stage, frames):
     return None, "no ncu capture committed"
 
 
+def measured_warp_inst(stage, frames):
+    """(executed warp instructions per launch of a stage, source) from the committed ncu capture, scaled per frame; (None, why)."""
+    p = os.path.join(ROOT, "profiles", "r2_traffic.json")
+    try:
+        d = json.load(open(p))["warp_inst_per_frame"]
+        return float(d[stage]) * frames, d["_source"]
+    except Exception:
+        return None, "no ncu capture committed for this stage"
+
+
+def matcher_reference():
+    """(oracle.matchref, kind) with the -O3 build of the reference's own matcher side selected when it travelled with the
+    snapshot (oracle/_ref/libmatchref_fast.so), else the -O2 test build, else None.  CPU baselines only."""
+    try:
+        from oracle import matchref as R
+    except Exception:
+        return None, None
+    for v in ("ref_fast", "ref"):
+        if R.use(v):
+            return R, v
+    return None, None
+
+
+def hamming_cpu_baseline(pkg, local, q, db_sample):
+    """the reference's SWAR DescriptorDistance scan and a __builtin_popcountll variant, 1 thread and all cores,
+    on a bounded sample (all queries x the first rows of rank 0's shard); results checked equal to the GPU search of the sample."""
+    R, kind = matcher_reference()
+    if R is None:
+        return {"unavailable": "oracle/_ref/libmatchref*.so not present"}
+    threads = host_threads()
+    m = pkg.ORBmatcher(0.6, True, device=local)
+    gb, gi, gs = m.BruteForce(q, db_sample)
+    m.close()
+    nq1 = max(1, len(q) // 8)
+    out = {"kind": "reference", "cores": threads, "unit": "descriptor pairs/s",
+           "build": "src/ORBmatcher.cc unmodified, %s" % ("-O3 -march=x86-64-v3" if kind == "ref_fast" else "-O2"),
+           "sample": "%d queries x %d rows on all cores, %d queries x %d rows on one thread" % (len(q), len(db_sample), nq1, len(db_sample))}
+    for name, variant in (("reference_swar", 0), ("popcountll", 1)):
+        b, i, s2, ms_all = R.bruteforce_scan(q, db_sample, threads=threads, variant=variant)
+        if not (np.array_equal(b, gb) and np.array_equal(i, gi) and np.array_equal(s2, gs)):
+            raise RuntimeError("bench: host %s scan and the GPU search disagree on the sample" % name)
+        _b, _i, _s, ms_one = R.bruteforce_scan(q[:nq1], db_sample, threads=1, variant=variant)
+        out[name] = {"pairs_per_s_all_cores": len(q) * len(db_sample) / (ms_all * 1e-3),
+                     "pairs_per_s_one_thread": nq1 * len(db_sample) / (ms_one * 1e-3)}
+    out["value"] = out["reference_swar"]["pairs_per_s_all_cores"]
+    out["results_equal_gpu"] = True
+    return out
+
+
 def make_frames(shape, n_distinct, batch):
     base = np.stack([synth.gen_frame(shape, s) for s in range(n_distinct)])
     reps = (batch + n_distinct - 1) // n_distinct
@@ -336,6 +385,26 @@ def other_configs(pkg, torch, dev, local):
         "ms_stereo_match_e2e": 1e3 * float(np.median(tm)),
         "keypoints_left": nl, "keypoints_right": nr, "stereo_matches": nmatch,
         "note": "extract L + extract R (host in/out; sequential calls, and on two host threads like src/Frame.cc:127-131) + orbm_stereo_match (row search + SAD + outliers)"}
+    R, rkind = matcher_reference()
+    if R is not None:
+        # the reference's own stereo Frame constructor (src/Frame.cc:113-165: two extractor threads, ComputeStereoMatches,
+        # grid) on the same pair; its match count must equal the GPU path's
+        R.set_timing(True)
+        rows_, cols_ = shape
+        tc_, tm_ = [], []
+        for _ in range(12):
+            ref = R.stereo_frame(left, right, cfg, fx, fx, cols_ / 2.0, rows_ / 2.0, bf)
+            tc_.append(R.last_ms(1)); tm_.append(R.last_ms(2))
+        R.set_timing(False)
+        nref = int((ref.u_right >= 0).sum())
+        if nref != nmatch or ref.n != nl:
+            raise RuntimeError("bench: reference stereo frame (%d keypoints, %d matches) != GPU (%d, %d)" % (ref.n, nref, nl, nmatch))
+        out["C2_euroc_stereo_752x480_1200"]["cpu_baseline"] = {
+            "kind": "reference", "cores": 2, "unit": "ms per stereo frame", "value": float(np.median(tc_)),
+            "compute_stereo_matches_ms": float(np.median(tm_)), "stereo_matches": nref, "matches_equal_gpu": True,
+            "sample": "12 x Frame(imLeft, imRight, ...) of the unmodified src/Frame.cc + src/ORBextractor.cc over the mini-cv shim (%s); "
+                      "ComputeStereoMatches (src/Frame.cc:673-885) timed once more on the constructed frame"
+                      % ("-O3 -march=x86-64-v3" if rkind == "ref_fast" else "-O2")}
     exL.close(); exR.close()
     # ---- C3 ----
     shape, cfg = synth.SHAPES["kitti"], synth.PRESETS["kitti"]
@@ -386,6 +455,20 @@ def other_configs(pkg, torch, dev, local):
         "extract_frames_per_s_device_resident": fps, "frames_per_step": Bk, "keypoints_per_frame": n,
         "search_by_projection_ms_e2e": 1e3 * float(np.median(ts)), "map_points": nmp, "matches": int(nm),
         "note": "SearchByProjection(Frame, 4000 local map points, th=3) through the host C-ABI (uploads included)"}
+    if R is not None:
+        # the reference's own ORBmatcher::SearchByProjection(Frame, MapPoints, th) (src/ORBmatcher.cc:61-173) on the same frame and
+        # map points, timed inside the harness around the call alone
+        tr = []
+        for _ in range(12):
+            nref, _m = R.search_by_projection(frame, mps, 3.0, 0.8)
+            tr.append(R.last_ms(0))
+        if int(nref) != int(nm):
+            raise RuntimeError("bench: reference SearchByProjection found %d matches, the GPU path %d" % (nref, nm))
+        out["C3_kitti_1241x376_2000"]["cpu_baseline"] = {
+            "kind": "reference", "cores": 1, "unit": "ms per SearchByProjection call", "value": float(np.median(tr)),
+            "matches": int(nref), "matches_equal_gpu": True,
+            "sample": "12 calls of the unmodified src/ORBmatcher.cc:61-173 on Frame / MapPoint objects built from the same arrays (%s)"
+                      % ("-O3 -march=x86-64-v3" if rkind == "ref_fast" else "-O2")}
     ex.close(); mt.close(); mt2.close()
     return out
 
@@ -773,11 +856,18 @@ def run_ours(args):
         e2e_single_fps = world * EB * args.e2e_inner * e2e_steps / e2e_single_s
         d2h = out[0].nbytes + out[1].nbytes + out[2].nbytes
         traffic, traffic_src = measured_traffic(dom, B)
+        winst, winst_src = measured_warp_inst(dom, B)
+        sm_hz = ((clocks or {}).get("sm_mhz") or 1965.0) * 1e6
+        issue_peak = 148 * 4 * sm_hz     # one warp instruction per scheduler (4 per SM) per clock
+        issue = None if winst is None else {
+            "warp_instructions_per_launch": winst, "achieved": winst / (stage_ms[dom] * 1e-3), "peak": issue_peak,
+            "unit": "warp instructions/s", "frac": winst / (stage_ms[dom] * 1e-3) / issue_peak,
+            "source": winst_src + "; peak = 148 SMs x 4 schedulers x SM clock under load"}
         five = sum(ab[k] for k in ("pyramid", "fast", "blur", "desc"))   # pyramid + FAST + blur + orientation + descriptor
         peaks = measured_peaks_all()
         # tensor roof of the int8 search: int8 dense = 2 x bf16 dense on B200 (4.5 vs 2.25 PFLOP/s nominal); the measured
         # denominator is 2 x the driver's measured cuBLAS bf16 burst figure
-        tc_ops = 2.0 * ((nq + 127) // 128 * 128) * per * 256
+        tc_ops = 2.0 * nq * per * 256   # useful operations: the 48 zero rows that pad 2000 queries to 16 tiles of 128 are not counted
         tc_tops = world * tc_ops / (bf_ms * 1e-3) / 1e12
         int8_peak_burst = 2.0 * peaks["bf16_tflops"]
         int8_peak = 2.0 * peaks.get("bf16_tflops_sustained", peaks["bf16_tflops"])   # the timed region is a long back-to-back run
@@ -809,6 +899,8 @@ def run_ours(args):
                 "kernel": dom, "bound": "hbm", "achieved": stages[dom]["GB_per_s"], "peak": peak, "unit": "GB/s",
                 "frac": stages[dom]["frac_of_hbm_peak"], "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": ab[dom] * B,
+                "limited_by": "issue slots (the kernel is instruction-bound, not memory-bound: see issue.frac)" if issue and issue["frac"] > stages[dom]["frac_of_hbm_peak"] else "hbm",
+                "issue": issue,
                 "whole_step_GB_per_s": five * frames_step * args.steps / (ms * 1e-3) / 1e9,
             },
             "stages": stages,
@@ -817,6 +909,8 @@ def run_ours(args):
             "hamming": {
                 "pairs_per_s": world * nq * per / (bf_ms * 1e-3), "queries": nq, "db_rows_per_gpu": per,
                 "ms_per_search": bf_ms, "unit": "descriptor pairs/s",
+                "expand_ms_once_per_shard": expand_ms,
+                "pairs_per_s_expansion_amortised_over_100_searches": world * nq * per / ((bf_ms + expand_ms / 100.0) * 1e-3),
                 "kernel": "k_bruteforce_tc (tcgen05.mma kind::i8, TMA, TMEM; shard expanded once in %.2f ms)" % expand_ms,
                 "roofline": {"bound": "tensor", "achieved": tc_tops / world, "peak": int8_peak, "unit": "TOP/s (int8, per GPU)",
                              "frac": tc_tops / world / int8_peak,
@@ -851,6 +945,7 @@ def run_ours(args):
             line.setdefault("configs", {}).update(other_configs(pkg, torch, dev, local))
         # CPU baseline on rank 0 at N = 1 only (bounded sample)
         if world == 1 and not args.no_cpu_baseline:
+            line["hamming"]["cpu_baseline"] = hamming_cpu_baseline(pkg, local, q, db[:100000])
             import oracle
 
             threads = host_threads()

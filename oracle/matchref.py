@@ -17,7 +17,8 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _PATHS = {"ref": os.path.join(_HERE, "_ref", "libmatchref.so"),     # the reference's ORBmatcher.cc / ORBextractor.cc
-          "gpu": os.path.join(_HERE, "_ref", "libmatchgpu.so")}     # the product's host/ORBmatcher_gpu.cc / ORBextractor.cc instead
+          "gpu": os.path.join(_HERE, "_ref", "libmatchgpu.so"),     # the product's host/ORBmatcher_gpu.cc / ORBextractor.cc instead
+          "ref_fast": os.path.join(_HERE, "_ref", "libmatchref_fast.so")}   # "ref" at -O3 -march=x86-64-v3: timed baselines (bench.py)
 _PATH = _PATHS["ref"]
 _lib = None
 _libs = {}
@@ -103,6 +104,8 @@ def lib():
         L.orbr_stereo_n.argtypes = [_vp, _i]
         L.orbr_stereo_get.argtypes = [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
         L.orbr_stereo_free.argtypes = [_vp]
+        L.orbr_bruteforce_scan.restype = C.c_double
+        L.orbr_bruteforce_scan.argtypes = [_vp, _i, _vp, _i, _i, _i, _vp, _vp, _vp]
         L.orbr_last_ms.restype = C.c_double
         L.orbr_last_ms.argtypes = [_i]
         L.orbr_set_timing.argtypes = [_i]
@@ -411,6 +414,18 @@ class RefFrame:
         self.cell_items = ci[: self.cell_start[-1]]
         L.orbr_stereo_free(h)
         self.h = None
+
+
+def bruteforce_scan(q, db, threads=1, variant=0):
+    """Best / second-best scan on the host: variant 0 = the reference's own ORBmatcher::DescriptorDistance per pair,
+    1 = __builtin_popcountll.  Returns (best, idx, second, ms of the scan alone)."""
+    q = np.ascontiguousarray(q, np.uint8)
+    db = np.ascontiguousarray(db, np.uint8)
+    nq = len(q)
+    best, idx, second = (np.zeros(nq, np.int32) for _ in range(3))
+    ms = lib().orbr_bruteforce_scan(q.ctypes.data, nq, db.ctypes.data, len(db), int(threads), int(variant), best.ctypes.data,
+                                    idx.ctypes.data, second.ctypes.data)
+    return best, idx, second, float(ms)
 
 
 def last_ms(which):

@@ -32,6 +32,7 @@
 #include <cmath>
 #include <map>
 #include <new>
+#include <thread>
 #include <vector>
 
 using namespace ORB_SLAM2;
@@ -331,6 +332,53 @@ int orbr_search_by_projection(const orbr_frame_in* f, int nmp, const float* px, 
         out_match[i] = it == index.end() ? -1 : it->second;
     }
     return n;
+}
+
+// ---- config 5 on the host: best / second-best scan over a descriptor database ----
+// variant 0: every pair through the reference's own ORBmatcher::DescriptorDistance (SWAR popcount, src/ORBmatcher.cc:1983-2003)
+//            on cv::Mat row headers built up front, inside the reference's scan idiom (src/ORBmatcher.cc:134-151);
+// variant 1: the same scan with __builtin_popcountll on four 64-bit words (what a host port would use today).
+// Queries are split over `threads` std::threads.  Returns the wall time of the scan alone in ms (bench.py hamming.cpu_baseline).
+double orbr_bruteforce_scan(const uint8_t* q, int nq, const uint8_t* db, int ndb, int threads, int variant, int32_t* best,
+                            int32_t* best_idx, int32_t* second)
+{
+    if (threads < 1) threads = 1;
+    std::vector<cv::Mat> qm, dm;
+    if (variant == 0) {
+        qm.reserve(nq); dm.reserve(ndb);
+        for (int i = 0; i < nq; i++) qm.push_back(cv::Mat(1, 32, CV_8U, (void*)(q + 32 * (size_t)i), 32));
+        for (int j = 0; j < ndb; j++) dm.push_back(cv::Mat(1, 32, CV_8U, (void*)(db + 32 * (size_t)j), 32));
+    }
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<std::thread> th;
+    for (int t = 0; t < threads; t++)
+        th.emplace_back([&, t]() {
+            const int lo = (int)((long long)nq * t / threads), hi = (int)((long long)nq * (t + 1) / threads);
+            for (int i = lo; i < hi; i++) {
+                int bestDist = 256, bestDist2 = 256, bestIdx = -1;
+                if (variant == 0) {
+                    for (int j = 0; j < ndb; j++) {
+                        const int dist = ORBmatcher::DescriptorDistance(qm[i], dm[j]);
+                        if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx = j; }
+                        else if (dist < bestDist2) bestDist2 = dist;
+                    }
+                } else {
+                    uint64_t a[4];
+                    std::memcpy(a, q + 32 * (size_t)i, 32);
+                    for (int j = 0; j < ndb; j++) {
+                        uint64_t b[4];
+                        std::memcpy(b, db + 32 * (size_t)j, 32);
+                        const int dist = __builtin_popcountll(a[0] ^ b[0]) + __builtin_popcountll(a[1] ^ b[1]) +
+                                         __builtin_popcountll(a[2] ^ b[2]) + __builtin_popcountll(a[3] ^ b[3]);
+                        if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx = j; }
+                        else if (dist < bestDist2) bestDist2 = dist;
+                    }
+                }
+                best[i] = bestDist; best_idx[i] = bestIdx; second[i] = bestDist2;
+            }
+        });
+    for (auto& x : th) x.join();
+    return ms_since(t0);
 }
 
 // ---- ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&) (src/ORBmatcher.cc:228-392) ----
