@@ -522,10 +522,21 @@ def c4_leg(pkg, torch, dev, local, rank, world, barrier):
     dt = (time.perf_counter() - t0) / jobs
     barrier()
     kp = float(bouts[0][2][: min(call, mine)].mean())
+    # parity of the timed calls: the 8 distinct frames at the head of thread 0's last output batch against the reference's own
+    # ORBextractor.cc (rank 0; every rank extracts the same 8 distinct frames tiled)
+    parity = None
+    if rank == 0:
+        nd = min(8, call, mine)
+        ours = output_digest(bouts[0][0], bouts[0][1], bouts[0][2], nd)
+        ref_digest, ref_src = reference_digest(frames[:nd], cfg, exs[0].max_keypoints(rows, cols))
+        parity = {"frames": nd, "digest": ours, "reference_digest": ref_digest, "reference": ref_src,
+                  "equal": (ours == ref_digest) if ref_digest else None}
+        if ref_digest and ours != ref_digest:
+            raise RuntimeError("bench: config 4 outputs differ from the reference's ORBextractor.cc on the %d distinct frames" % nd)
     for e in exs:
         e.close()
     del bigs, bouts
-    return dt, mine, kp
+    return dt, mine, kp, parity
 
 
 def bind_to_gpu_numa_node(index):
@@ -805,6 +816,7 @@ def run_ours(args):
     bf_int_ms = timed(bf_int_step, 150)
     if not (torch.equal(ib, ob) and torch.equal(ii, oi) and torch.equal(is_, os_)):
         raise RuntimeError("brute force: tensor-core and integer-pipe kernels disagree")
+    unsharded_equal = None
     nccl_ms = None
     if dist is not None:
         if m.exchange_timed_out():
@@ -827,11 +839,27 @@ def run_ours(args):
         torch.cuda.synchronize()
         if not (torch.equal(nb, ob) and torch.equal(ni, oi) and torch.equal(ns, os_)):
             raise RuntimeError("sharded search: fused exchange and NCCL all-gather + merge disagree")
+        # independent answer: rank 0 regenerates EVERY shard and scans the concatenated map unsharded on its own GPU with the
+        # integer-pipe kernel (no shard search, no exchange, no merge across ranks); the fused-exchange result must equal it
+        bf_step()
+        m.sync()
+        if rank == 0:
+            full = np.concatenate([synth.gen_descriptors(sharding.db_shard(ndb_total, r, world)[1] - sharding.db_shard(ndb_total, r, world)[0],
+                                                         seed=12345 + r) for r in range(world)])
+            dfull = torch.from_numpy(full).to(dev)
+            ub, ui, us = torch.empty_like(pb), torch.empty_like(pb), torch.empty_like(pb)
+            torch.cuda.synchronize()
+            m.bruteforce_device(dq.data_ptr(), nq, dfull.data_ptr(), ndb_total, 0, ub.data_ptr(), ui.data_ptr(), us.data_ptr())
+            m.sync()
+            if not (torch.equal(ub, ob) and torch.equal(ui, oi) and torch.equal(us, os_)):
+                raise RuntimeError("sharded search: the fused-exchange result differs from the unsharded scan of the whole map")
+            unsharded_equal = True
+            del dfull, full
 
     # ---- config 4 (strong scaling over the ranks) ----
-    c4_s, c4_frames, c4_kp = (None, 0, None)
+    c4_s, c4_frames, c4_kp, c4_parity = (None, 0, None, None)
     if not args.no_extra:
-        c4_s, c4_frames, c4_kp = c4_leg(pkg, torch, dev, local, rank, world, barrier)
+        c4_s, c4_frames, c4_kp, c4_parity = c4_leg(pkg, torch, dev, local, rank, world, barrier)
 
     # ---- max over ranks ----
     t = torch.tensor([ms, e2e_s, bf_ms, bf_int_ms, nccl_ms or 0.0, c4_s or 0.0], dtype=torch.float64, device=dev)
@@ -926,6 +954,7 @@ def run_ours(args):
                                  "unit": "pairs/s per GPU", "frac": (nq * per / (bf_int_ms * 1e-3) / popc_roof) if popc_roof else None,
                                  "peak_source": "148 SMs x 16 POPC / clk x SM clock under load / 6 POPC per pair"}},
                 "results_equal": True,
+                "unsharded_scan_equal": unsharded_equal,
                 "exchange": ("none (one shard)" if world == 1 else
                              "fused: k_merge_exchange stores the per-query triples into every peer's buffer over NVLink "
                              "P2P and merges; checked equal to NCCL all-gather + merge"),
@@ -939,6 +968,7 @@ def run_ours(args):
                 "frames_per_s_e2e": 4096 / c4_s, "seconds_for_4096_frames": c4_s, "jobs_timed": C4_JOBS * world,
                 "timed_region_s": c4_s * C4_JOBS * world, "frames_per_rank": c4_frames,
                 "keypoints_per_frame": c4_kp, "scaling": "strong (4096 frames sharded by frame over %d rank(s))" % world,
+                "parity": c4_parity,
                 "note": "pinned host in / pinned host out through orbx_extract_batch from two host threads per rank (one extractor handle each), calls of <= 512 frames (8 distinct seeded "
                         "frames tiled), H2D | kernels | D2H pipelined; max over ranks"}
         if world == 1 and not args.no_extra:
