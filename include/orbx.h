@@ -117,6 +117,11 @@ void* orbx_stream(orbx_handle* h);
  * ORBX_ERR_BAD_ARG ("no longer resident"), never another frame's data. */
 int orbx_get_level_size(orbx_handle* h, int level, int* rows_l, int* cols_l);
 int orbx_get_pyramid_level(orbx_handle* h, int frame, int level, uint8_t* dst, size_t dst_step);
+/* Every padded level of one frame in ONE call (ORBextractor::mvImagePyramid, include/ORBextractor.h:162; consumer
+ * Frame::ComputeStereoMatches, src/Frame.cc:782-831): level l is written at dst + level_offsets[l] with row step
+ * level_steps[l] >= cols_l + 38, (rows_l + 38) rows.  The copies are enqueued back to back and waited for once; give it
+ * page-locked memory (orbx_alloc_pinned) and the copies run at link speed instead of through the driver's staging buffer. */
+int orbx_get_pyramid_all(orbx_handle* h, int frame, uint8_t* dst, const size_t* level_offsets, const size_t* level_steps);
 
 /* Per-stage device time of the last batch in milliseconds, measured with CUDA events when profiling is on
  * (profiling serialises the stages; leave it off for throughput).  Stage order: ORBX_STAGE_*. */

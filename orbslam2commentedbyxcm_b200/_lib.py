@@ -71,6 +71,7 @@ SIGNATURES = {
     "orbx_stream": (_vp, [_vp]),
     "orbx_get_level_size": (_i, [_vp, _i, _vp, _vp]),
     "orbx_get_pyramid_level": (_i, [_vp, _i, _i, _vp, _sz]),
+    "orbx_get_pyramid_all": (_i, [_vp, _i, _vp, _vp, _vp]),
     "orbx_set_profiling": (_i, [_vp, _i]),
     "orbx_stage_times": (_i, [_vp, _vp]),
     "orbx_last_launch_count": (_i, [_vp]),

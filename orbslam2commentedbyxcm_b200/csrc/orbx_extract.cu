@@ -2897,6 +2897,31 @@ int orbx_get_pyramid_level(orbx_handle* h, int frame, int level, uint8_t* dst, s
     return ORBX_OK;
 }
 
+int orbx_get_pyramid_all(orbx_handle* h, int frame, uint8_t* dst, const size_t* level_offsets, const size_t* level_steps)
+{
+    if (!h || !h->havePlan || !dst || !level_offsets || !level_steps || frame < 0 || frame >= h->lastFrames) {
+        set_error("orbx_get_pyramid_all: bad argument");
+        return ORBX_ERR_BAD_ARG;
+    }
+    const int arenaFrame = h->arena_frame(frame);
+    if (arenaFrame < 0) {
+        set_error("orbx_get_pyramid_all: frame %d of the last batch is no longer resident (a pipelined host batch keeps its last two chunks)", frame);
+        return ORBX_ERR_BAD_ARG;
+    }
+    for (int l = 0; l < h->cfg.nlevels; l++)
+        if (level_steps[l] < (size_t)(h->plan.lv[l].w + 2 * EDGE)) { set_error("orbx_get_pyramid_all: step of level %d too small", l); return ORBX_ERR_CAPACITY; }
+    ORBX_CUDA_TRY(cudaSetDevice(h->device));
+    // all levels are enqueued back to back and the stream is waited for ONCE (orbx_get_pyramid_level pays one wait per level)
+    for (int l = 0; l < h->cfg.nlevels; l++) {
+        const LevelGeom& g = h->plan.lv[l];
+        const uint8_t* src = h->buf.pyr + g.planeOff + (long long)arenaFrame * g.planeBytes + (PAD_LEFT - EDGE);
+        ORBX_CUDA_TRY(cudaMemcpy2DAsync(dst + level_offsets[l], level_steps[l], src, g.pitch, g.w + 2 * EDGE, g.planeRows,
+                                        cudaMemcpyDeviceToHost, h->stream));
+    }
+    ORBX_CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return ORBX_OK;
+}
+
 void* orbx_alloc_pinned(size_t bytes)
 {
     void* p = nullptr;

@@ -12,7 +12,7 @@ static const int EDGE_THRESHOLD = ORBX_EDGE;
 
 ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int _iniThFAST, int _minThFAST)
     : nfeatures(_nfeatures), scaleFactor(_scaleFactor), nlevels(_nlevels), iniThFAST(_iniThFAST), minThFAST(_minThFAST),
-      mpHandle(NULL), mbDownloadPyramid(true)
+      mpHandle(NULL), mbDownloadPyramid(true), mpPyramidPinned(NULL), mnPyramidBytes(0)
 {
     orbx_config cfg;
     cfg.nfeatures = _nfeatures;
@@ -41,6 +41,9 @@ ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int
 
 ORBextractor::~ORBextractor()
 {
+    mvImagePyramid.clear();
+    mvPaddedLevels.clear();
+    orbx_free_pinned(mpPyramidPinned);
     if (mpHandle) orbx_destroy(mpHandle);
 }
 
@@ -88,15 +91,28 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, s
         _keypoints.push_back(cv::KeyPoint(k.x, k.y, k.size, k.angle, k.response, k.octave, -1));
     }
     if (mbDownloadPyramid) {
+        // one page-locked staging buffer holds all padded planes (64-byte aligned rows); one call, one wait on the stream
+        std::vector<size_t> off(nlevels), step(nlevels);
+        std::vector<int> rows(nlevels), cols(nlevels);
+        size_t total = 0;
         for (int l = 0; l < nlevels; l++) {
-            int rows = 0, cols = 0;
-            if (orbx_get_level_size(mpHandle, l, &rows, &cols) != ORBX_OK) break;
-            mvPaddedLevels[l].create(rows + 2 * EDGE_THRESHOLD, cols + 2 * EDGE_THRESHOLD, CV_8UC1);
-            if (orbx_get_pyramid_level(mpHandle, 0, l, mvPaddedLevels[l].data, (size_t)mvPaddedLevels[l].step) != ORBX_OK) {
-                std::fprintf(stderr, "ORBextractor: %s\n", orbx_last_error());
-                break;
-            }
-            mvImagePyramid[l] = mvPaddedLevels[l](cv::Rect(EDGE_THRESHOLD, EDGE_THRESHOLD, cols, rows));
+            if (orbx_get_level_size(mpHandle, l, &rows[l], &cols[l]) != ORBX_OK) return;
+            step[l] = ((size_t)cols[l] + 2 * EDGE_THRESHOLD + 63) / 64 * 64;
+            off[l] = total;
+            total += step[l] * (size_t)(rows[l] + 2 * EDGE_THRESHOLD);
+        }
+        if (total > mnPyramidBytes) {
+            orbx_free_pinned(mpPyramidPinned);
+            mpPyramidPinned = (unsigned char*)orbx_alloc_pinned(total);
+            mnPyramidBytes = mpPyramidPinned ? total : 0;
+        }
+        if (!mpPyramidPinned || orbx_get_pyramid_all(mpHandle, 0, mpPyramidPinned, &off[0], &step[0]) != ORBX_OK) {
+            std::fprintf(stderr, "ORBextractor: %s\n", orbx_last_error());
+            return;
+        }
+        for (int l = 0; l < nlevels; l++) {
+            mvPaddedLevels[l] = cv::Mat(rows[l] + 2 * EDGE_THRESHOLD, cols[l] + 2 * EDGE_THRESHOLD, CV_8UC1, mpPyramidPinned + off[l], step[l]);
+            mvImagePyramid[l] = mvPaddedLevels[l](cv::Rect(EDGE_THRESHOLD, EDGE_THRESHOLD, cols[l], rows[l]));
         }
     }
 }

@@ -75,7 +75,9 @@ private:
     bool mbDownloadPyramid;
     std::vector<orbx_keypoint> mvKpBuffer;
     std::vector<unsigned char> mvDescBuffer;
-    std::vector<cv::Mat> mvPaddedLevels;  // owners of the padded pyramid planes
+    std::vector<cv::Mat> mvPaddedLevels;  // headers over the padded pyramid planes in mpPyramidPinned
+    unsigned char* mpPyramidPinned;       // page-locked staging buffer of all padded planes (valid until the next operator())
+    size_t mnPyramidBytes;
 };
 
 }  // namespace ORB_SLAM2

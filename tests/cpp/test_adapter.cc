@@ -3,6 +3,8 @@
 // the reference's own class, reached through oracle/_ref/liborbref.so's C entry points (both classes have the same
 // name, so the reference lives behind dlopen).  Exit code 0 = identical.  Needs a GPU (pytest -m gpu runs it).
 #include <dlfcn.h>
+#include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -70,5 +72,32 @@ int main(int argc, char** argv)
             if (std::memcmp(m.data + (ptrdiff_t)y * (ptrdiff_t)m.step - 19, &rp[(size_t)(y + 19) * (w + 38)], w + 38)) { bad++; break; }
     }
     std::printf("adapter vs reference: %d keypoints, %d mismatches\n", n, bad);
+    // latency of the call a stock Frame constructor makes (src/Frame.cc:377-386) at config 1 (640 x 480, 1000 features), with the
+    // pyramid download that Frame::ComputeStereoMatches needs switched on (default) and off
+    {
+        const int R = 480, C = 640;
+        cv::Mat big(R, C, CV_8UC1);
+        for (int y = 0; y < R; y++)
+            for (int x = 0; x < C; x++) {
+                int block = ((x / 8) * 31 + (y / 8) * 17) % 7;
+                big.at<uchar>(y, x) = (uchar)(40 + 30 * block + (lcg(seed) % 5));
+            }
+        ORB_SLAM2::ORBextractor ex1(1000, 1.2f, 8, 20, 7);
+        for (int mode = 0; mode < 2; mode++) {
+            ex1.SetPyramidDownload(mode == 0);
+            std::vector<double> t;
+            for (int it = 0; it < 220; it++) {
+                std::vector<cv::KeyPoint> k1;
+                cv::Mat d1;
+                const auto t0 = std::chrono::steady_clock::now();
+                ex1(big, cv::Mat(), k1, d1);
+                const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+                if (it >= 20) t.push_back(ms);
+            }
+            std::sort(t.begin(), t.end());
+            std::printf("adapter latency 640x480/1000 pyramid_%s: median %.4f ms, p90 %.4f ms\n", mode == 0 ? "on" : "off", t[t.size() / 2],
+                        t[t.size() * 9 / 10]);
+        }
+    }
     return bad ? 1 : 0;
 }
